@@ -1,0 +1,181 @@
+"""TEST INFRASTRUCTURE ONLY -- generates tests/golden/*.npz by running the UNMODIFIED reference.
+
+Run in the build container (needs /root/reference):  python -m oracle.make_golden
+The fixtures hold weights (reference state_dict), inputs (cond, the noise the reference drew)
+and the reference's outputs, so they can be checked anywhere (CPU oracle tests, GPU parity tests)
+without the reference tree.  torch version is stamped into every file.
+"""
+from __future__ import annotations
+
+import os
+from contextlib import contextmanager
+
+import numpy as np
+import torch
+
+from oracle.ref_harness import load_reference, set_reference_hparams
+
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+
+SMALL = dict(num_layers=4, num_channels=64, dilation_cycle_length=2)
+HIDDEN = 64
+
+
+@contextmanager
+def record_randn(log):
+    real = torch.randn
+
+    def fake(*a, **k):
+        out = real(*a, **k)
+        log.append(out.clone())
+        return out
+
+    torch.randn = fake
+    try:
+        yield
+    finally:
+        torch.randn = real
+
+
+def _np(sd):
+    return {k: v.detach().cpu().numpy() for k, v in sd.items()}
+
+
+def _save(name, **arrs):
+    os.makedirs(OUT, exist_ok=True)
+    arrs["torch_version"] = np.array(torch.__version__)
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **arrs)
+    print("wrote", name, {k: getattr(v, "shape", None) for k, v in arrs.items() if not k.startswith("w.")})
+
+
+def _randomise_out_proj(net, std=0.05):
+    torch.nn.init.normal_(net.output_projection.weight, 0.0, std)  # trap T1
+
+
+_W = {}
+
+
+def shared_weights(ref, M, F):
+    """One weight set per (M, F), saved once as weights_m{M}f{F}.npz and loaded into every model."""
+    tag = f"m{M}f{F}"
+    if tag not in _W:
+        set_reference_hparams(hidden_size=HIDDEN)
+        torch.manual_seed(100 + F)
+        net = ref.WaveNet(M, F, **SMALL).eval()
+        _randomise_out_proj(net, 0.1)
+        _W[tag] = {k: v.clone() for k, v in net.state_dict().items()}
+        _save("weights_" + tag, cfg=np.array([M, F, SMALL["num_layers"], SMALL["num_channels"],
+                                               SMALL["dilation_cycle_length"], HIDDEN]), **_np(_W[tag]))
+    return tag, _W[tag]
+
+
+def gen_backbone(ref):
+    for tag, M, F in (("f1", 16, 1), ("f2", 8, 2)):
+        set_reference_hparams(hidden_size=HIDDEN)
+        net = ref.WaveNet(M, F, **SMALL).eval()
+        wtag, sd = shared_weights(ref, M, F)
+        net.load_state_dict(sd)
+        torch.manual_seed(5)
+        B, T = 2, 37
+        spec = torch.randn(B, F, M, T)
+        cond = torch.randn(B, T, HIDDEN).transpose(1, 2)  # transposed view like the callers (T8)
+        t_long = torch.tensor([950, 3], dtype=torch.long)
+        t_float = torch.tensor([412.5])
+        with torch.no_grad():
+            y_long = net(spec, t_long, cond)
+            y_float = net(spec, t_float, cond)
+        _save(f"wavenet_{tag}", spec=spec.numpy(), cond=cond.contiguous().numpy(), t_long=t_long.numpy(),
+              t_float=t_float.numpy(), y_long=y_long.numpy(), y_float=y_float.numpy(),
+              weights=np.array(wtag))
+
+
+def gen_ddpm(ref):
+    M, B, T = 16, 2, 41
+    for algo, speedup, b in (("ddim", 50, B), ("pndm", 50, 1), ("dpm-solver", 50, B), ("unipc", 50, B),
+                             ("dpm-solver", 125, B), ("ddpm", 1, B), ("ddim_shallow", 20, B)):
+        shallow = algo in ("ddpm", "ddim_shallow")
+        k_step = 12 if algo == "ddpm" else (400 if shallow else 1000)
+        set_reference_hparams(hidden_size=HIDDEN, diff_accelerator=algo.split("_")[0], diff_speedup=speedup,
+                              use_shallow_diffusion=shallow, K_step=k_step, K_step_infer=k_step)
+        torch.manual_seed(7)
+        m = ref.ddpm.GaussianDiffusion(M, 1, 1000, k_step, "wavenet", SMALL, spec_min=[-12.0], spec_max=[0.0]).eval()
+        wtag, sd = shared_weights(ref, M, 1)
+        m.denoise_fn.load_state_dict(sd)
+        cond = torch.randn(b, T, HIDDEN)
+        src = torch.rand(b, T, M) * -10.0 if shallow else None
+        log = []
+        torch.manual_seed(11)
+        with torch.no_grad(), record_randn(log):
+            y = m(cond, src_spec=src, infer=True)
+        arrs = dict(cond=cond.numpy(), noise=log[0].numpy(), y=y.numpy(),
+                    meta=np.array([M, 1, 1000, k_step, speedup, int(shallow)]), weights=np.array(wtag))
+        if len(log) > 1:
+            arrs["step_noise"] = torch.stack(log[1:]).numpy()
+        if src is not None:
+            arrs["src"] = src.numpy()
+        _save("ddpm_" + algo.replace("-", "_") + (f"_s{speedup}" if algo == "dpm-solver" else ""), **arrs)
+
+
+def gen_reflow(ref):
+    M, B, T = 16, 2, 33
+    for algo, steps, t_start in (("euler", 20, 0.0), ("rk2", 6, 0.0), ("rk4", 4, 0.0), ("rk5", 3, 0.0), ("euler", 8, 0.4)):
+        shallow = t_start > 0
+        set_reference_hparams(hidden_size=HIDDEN, sampling_algorithm=algo, sampling_steps=steps,
+                              use_shallow_diffusion=shallow, T_start=t_start, T_start_infer=t_start)
+        torch.manual_seed(9)
+        m = ref.reflow.RectifiedFlow(M, 1, t_start, 1000, "wavenet", SMALL, spec_min=[-12.0], spec_max=[0.0]).eval()
+        wtag, sd = shared_weights(ref, M, 1)
+        m.velocity_fn.load_state_dict(sd)
+        cond = torch.randn(B, T, HIDDEN)
+        src = torch.rand(B, T, M) * -10.0 if shallow else None
+        log = []
+        torch.manual_seed(13)
+        with torch.no_grad(), record_randn(log):
+            y = m(cond, src_spec=src, infer=True)
+        arrs = dict(cond=cond.numpy(), noise=log[0].numpy(), y=y.numpy(),
+                    meta=np.array([M, 1, steps, int(shallow)]), t_start=np.array(t_start), weights=np.array(wtag))
+        if src is not None:
+            arrs["src"] = src.numpy()
+        _save(f"reflow_{algo}" + ("_shallow" if shallow else ""), **arrs)
+
+
+def gen_variance(ref):
+    B, T = 1, 29
+    # pitch (configs/variance.yaml:62-72 ranges, reduced repeat_bins)
+    set_reference_hparams(hidden_size=HIDDEN, diff_accelerator="ddim", diff_speedup=100)
+    torch.manual_seed(21)
+    m = ref.ddpm.PitchDiffusion(vmin=-8.0, vmax=8.0, cmin=-12.0, cmax=12.0, repeat_bins=16, timesteps=1000,
+                                k_step=1000, backbone_type="wavenet", backbone_args=SMALL).eval()
+    wtag, sd = shared_weights(ref, 16, 1)
+    m.denoise_fn.load_state_dict(sd)
+    cond = torch.randn(B, T, HIDDEN)
+    log = []
+    torch.manual_seed(23)
+    with torch.no_grad(), record_randn(log):
+        y = m(cond, infer=True)
+    _save("var_pitch_ddim", cond=cond.numpy(), noise=log[0].numpy(), y=y.numpy(), weights=np.array(wtag))
+    # multi-variance, reflow euler (configs/variance.yaml:74-95 ranges)
+    set_reference_hparams(hidden_size=HIDDEN, sampling_algorithm="euler", sampling_steps=10)
+    torch.manual_seed(25)
+    m = ref.reflow.MultiVarianceRectifiedFlow(ranges=[(-96.0, -12.0), (-96.0, -20.0)], clamps=[(-96.0, 0.0), (-96.0, 0.0)],
+                                              repeat_bins=8, backbone_type="wavenet", backbone_args=SMALL).eval()
+    wtag, sd = shared_weights(ref, 8, 2)
+    m.velocity_fn.load_state_dict(sd)
+    log = []
+    torch.manual_seed(27)
+    with torch.no_grad(), record_randn(log):
+        ys = m(cond, infer=True)
+    _save("var_multi_euler", cond=cond.numpy(), noise=log[0].numpy(), y=torch.stack(list(ys)).numpy(),
+          weights=np.array(wtag))
+
+
+def main():
+    ref = load_reference()
+    gen_backbone(ref)
+    gen_ddpm(ref)
+    gen_reflow(ref)
+    gen_variance(ref)
+
+
+if __name__ == "__main__":
+    main()

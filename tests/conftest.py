@@ -1,0 +1,40 @@
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+def pytest_collection_modifyitems(config, items):
+    if torch.cuda.is_available():
+        return
+    skip = pytest.mark.skip(reason="no CUDA device")
+    for item in items:
+        if "gpu" in item.keywords:
+            item.add_marker(skip)
+
+
+def load_golden(name):
+    """-> (dict of torch tensors / scalars, state_dict of the shared weight set, cfg)."""
+    z = np.load(os.path.join(GOLDEN, name + ".npz"))
+    d = {k: (torch.from_numpy(z[k]) if z[k].dtype.kind in "fi" and z[k].ndim > 0 else z[k]) for k in z.files}
+    w = np.load(os.path.join(GOLDEN, "weights_" + str(z["weights"]) + ".npz"))
+    sd = {k: torch.from_numpy(w[k]) for k in w.files if k not in ("cfg", "torch_version")}
+    M, F, L, C, cycle, H = [int(v) for v in w["cfg"]]
+    cfg = dict(in_dims=M, n_feats=F, num_layers=L, num_channels=C, dilation_cycle_length=cycle, hidden=H)
+    return d, sd, cfg
+
+
+def rel_l2(a, b):
+    a, b = a.double(), b.double()
+    return float((a - b).norm() / b.norm().clamp_min(1e-30))
