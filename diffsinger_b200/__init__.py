@@ -1,0 +1,11 @@
+"""diffsinger_b200 -- B200-native (sm_100a) drop-in for DiffSinger's diffusion-denoiser sampling path:
+the WaveNet backbone (BACKBONES['wavenet']) and the GaussianDiffusion / RectifiedFlow samplers.
+Host code is Python/PyTorch plumbing over the C ABI in include/dsb200.h (libdsb200.so)."""
+from .hparams import hparams, get_hparams
+from .backbones import BACKBONES, build_backbone, WaveNet
+from .core import (GaussianDiffusion, PitchDiffusion, MultiVarianceDiffusion,
+                   RectifiedFlow, PitchRectifiedFlow, MultiVarianceRectifiedFlow)
+
+__all__ = ["hparams", "get_hparams", "BACKBONES", "build_backbone", "WaveNet", "GaussianDiffusion",
+           "PitchDiffusion", "MultiVarianceDiffusion", "RectifiedFlow", "PitchRectifiedFlow",
+           "MultiVarianceRectifiedFlow"]

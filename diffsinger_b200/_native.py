@@ -1,0 +1,133 @@
+"""ctypes binding of libdsb200.so (include/dsb200.h).  No compute happens in Python.
+
+The library is built in-tree by ``build_native()`` (nvcc, sm_100a only).  There is NO fallback:
+if the shared object is missing or no B200 is visible, every entry point raises ``NativeError``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+import sys
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_ROOT = os.path.dirname(_HERE)
+LIB_PATH = os.path.join(_HERE, "libdsb200.so")
+SRC = os.path.join(_HERE, "csrc", "api.cu")
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+              "-Xcompiler", "-fPIC", "-shared"]
+
+DS_OP_EVAL, DS_OP_LINCOMB = 0, 1
+EXPORTS = [
+    "ds_last_error", "ds_abi_version", "ds_device_check", "ds_plan_create", "ds_plan_destroy",
+    "ds_plan_packed_bytes", "ds_plan_pack_weights", "ds_session_workspace_bytes", "ds_session_create",
+    "ds_session_destroy", "ds_session_set_cond", "ds_session_set_times", "ds_session_forward",
+    "ds_session_run", "ds_session_last_launches", "ds_lincomb", "ds_transpose", "ds_debug_gemm",
+]
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+class WaveNetConfig(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("in_dims", "n_feats", "num_layers", "num_channels",
+                                          "dilation_cycle_length", "hidden_size")]
+
+
+_FP = C.c_void_p  # const float*
+_FPP = C.POINTER(C.c_void_p)  # const float* const*
+
+
+class WaveNetWeights(C.Structure):
+    _fields_ = [(n, _FP) for n in (
+        "input_projection_weight", "input_projection_bias", "mlp0_weight", "mlp0_bias", "mlp2_weight",
+        "mlp2_bias", "skip_projection_weight", "skip_projection_bias", "output_projection_weight",
+        "output_projection_bias")] + [(n, _FPP) for n in (
+        "dilated_conv_weight", "dilated_conv_bias", "diffusion_projection_weight", "diffusion_projection_bias",
+        "conditioner_projection_weight", "conditioner_projection_bias", "layer_output_projection_weight",
+        "layer_output_projection_bias")]
+
+
+class Op(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("dst", C.c_int32), ("time", C.c_int32), ("n", C.c_int32),
+                ("src", C.c_int32 * 8), ("coef", C.c_float * 8)]
+
+
+class GemmDesc(C.Structure):
+    _fields_ = [
+        ("epi", C.c_int32), ("BN", C.c_int32), ("B", C.c_int32), ("T", C.c_int32),
+        ("a0", C.c_void_p), ("a0_channels", C.c_int32), ("a0_c0", C.c_int32), ("kb_a0", C.c_int32),
+        ("n_taps", C.c_int32), ("dil", C.c_int32),
+        ("a1", C.c_void_p), ("a1_channels", C.c_int32), ("kb_a1", C.c_int32),
+        ("w", C.c_void_p), ("w_rows", C.c_int32), ("w_k", C.c_int32), ("b_row0", C.c_int32), ("n_tiles", C.c_int32),
+        ("bias", C.c_void_p), ("vec_sub", C.c_void_p), ("vec_add", C.c_void_p), ("vec_bstride", C.c_int32),
+        ("res_in", C.c_void_p), ("ld_res", C.c_int32),
+        ("out", C.c_void_p), ("ld_out", C.c_int32), ("out_c0", C.c_int32), ("n_real", C.c_int32),
+        ("relu", C.c_int32), ("scale", C.c_float),
+    ]
+
+
+def build_native(force: bool = False, verbose: bool = False) -> str:
+    """Compile csrc/api.cu into diffsinger_b200/libdsb200.so (nvcc cross-compiles without a GPU)."""
+    srcs = [os.path.join(_HERE, "csrc", f) for f in os.listdir(os.path.join(_HERE, "csrc"))]
+    srcs.append(os.path.join(_ROOT, "include", "dsb200.h"))
+    if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(s) for s in srcs):
+        return LIB_PATH
+    nvcc = os.environ.get("NVCC", "nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH, SRC]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise NativeError("nvcc failed:\n" + res.stdout + res.stderr)
+    if verbose:
+        sys.stderr.write(res.stderr)
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Loads the library (building it if the sources are newer and nvcc is present)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    try:
+        build_native()  # no-op when the in-tree .so is newer than every source
+    except (OSError, NativeError) as e:
+        if not os.path.exists(LIB_PATH):
+            raise NativeError(f"libdsb200.so is missing and could not be built: {e}") from e
+    L = C.CDLL(LIB_PATH)
+    L.ds_last_error.restype = C.c_char_p
+    L.ds_plan_packed_bytes.restype = C.c_size_t
+    L.ds_plan_packed_bytes.argtypes = [C.c_void_p]
+    L.ds_session_workspace_bytes.restype = C.c_size_t
+    L.ds_session_workspace_bytes.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32]
+    L.ds_session_last_launches.restype = C.c_int64
+    L.ds_session_last_launches.argtypes = [C.c_void_p]
+    L.ds_plan_create.argtypes = [C.POINTER(WaveNetConfig), C.POINTER(C.c_void_p)]
+    L.ds_plan_destroy.argtypes = [C.c_void_p]
+    L.ds_plan_pack_weights.argtypes = [C.c_void_p, C.POINTER(WaveNetWeights), C.c_void_p, C.c_size_t, C.c_void_p]
+    L.ds_session_create.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_size_t,
+                                    C.POINTER(C.c_void_p)]
+    L.ds_session_destroy.argtypes = [C.c_void_p]
+    L.ds_session_set_cond.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    L.ds_session_set_times.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]
+    L.ds_session_forward.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
+    L.ds_session_run.argtypes = [C.c_void_p, C.POINTER(Op), C.c_int32, C.POINTER(C.c_void_p), C.c_int32, C.c_int32,
+                                 C.c_void_p]
+    L.ds_lincomb.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_float), C.c_int32, C.c_size_t, C.c_void_p]
+    L.ds_transpose.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
+    L.ds_debug_gemm.argtypes = [C.POINTER(GemmDesc), C.c_void_p]
+    _lib = L
+    return L
+
+
+def check(status: int) -> None:
+    if status != 0:
+        raise NativeError(f"dsb200 error {status}: {lib().ds_last_error().decode()}")
+
+
+def require_device() -> None:
+    """Fails loudly when the CUDA path cannot run (no silent CPU fallback anywhere)."""
+    check(lib().ds_device_check())

@@ -1,0 +1,153 @@
+"""Drop-in for the reference's ``modules/backbones/wavenet.py`` (registry key ``'wavenet'``).
+
+Same constructor signature, parameter names / shapes / dtypes (``load_ckpt(strict=True)`` works both
+ways) and ``forward(spec, diffusion_step, cond)`` contract.  Under
+``torch.no_grad()`` / inference the forward runs entirely in libdsb200.so (tcgen05 GEMMs, fused
+epilogues); with autograd enabled (training ``p_losses``, wavenet.py under ddpm.py:212-219) it is
+expressed with differentiable torch ops on the same device -- that branch exists for gradients only
+and is never taken by the samplers.
+"""
+import math
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from ..hparams import get_hparams
+
+
+class SinusoidalPosEmb(nn.Module):
+    """Step embedding (reference: modules/commons/common_layers.py:268-280). No parameters."""
+
+    def __init__(self, dim):
+        super().__init__()
+        self.dim = dim
+
+    def forward(self, x):
+        half = self.dim // 2
+        freq = torch.exp(torch.arange(half, device=x.device) * -(math.log(10000) / (half - 1)))
+        arg = x[:, None] * freq[None, :]
+        return torch.cat((arg.sin(), arg.cos()), dim=-1)
+
+
+class ResidualBlock(nn.Module):
+    """Parameter container + differentiable forward of one layer (reference wavenet.py:18-48)."""
+
+    def __init__(self, encoder_hidden, residual_channels, dilation):
+        super().__init__()
+        self.residual_channels = residual_channels
+        self.dilation = dilation
+        self.dilated_conv = nn.Conv1d(residual_channels, 2 * residual_channels, 3, padding=dilation, dilation=dilation)
+        self.diffusion_projection = nn.Linear(residual_channels, residual_channels)
+        self.conditioner_projection = nn.Conv1d(encoder_hidden, 2 * residual_channels, 1)
+        self.output_projection = nn.Conv1d(residual_channels, 2 * residual_channels, 1)
+
+    def forward(self, x, conditioner, diffusion_step):
+        C = self.residual_channels
+        y = self.dilated_conv(x + self.diffusion_projection(diffusion_step).unsqueeze(-1))
+        y = y + self.conditioner_projection(conditioner)
+        y = torch.sigmoid(y[:, :C]) * torch.tanh(y[:, C:])
+        y = self.output_projection(y)
+        return (x + y[:, :C]) / math.sqrt(2.0), y[:, C:]
+
+
+def _kaiming_conv1x1(cin, cout):
+    conv = nn.Conv1d(cin, cout, 1)
+    nn.init.kaiming_normal_(conv.weight)
+    return conv
+
+
+class WaveNet(nn.Module):
+    def __init__(self, in_dims, n_feats, *, num_layers=20, num_channels=256, dilation_cycle_length=4):
+        super().__init__()
+        self.in_dims = in_dims
+        self.n_feats = n_feats
+        self.num_layers = num_layers
+        self.num_channels = num_channels
+        self.dilation_cycle_length = dilation_cycle_length
+        self.hidden_size = get_hparams()['hidden_size']  # read at construct time like wavenet.py:65
+        self.input_projection = _kaiming_conv1x1(in_dims * n_feats, num_channels)
+        self.diffusion_embedding = SinusoidalPosEmb(num_channels)
+        self.mlp = nn.Sequential(
+            nn.Linear(num_channels, num_channels * 4),
+            nn.Mish(),
+            nn.Linear(num_channels * 4, num_channels),
+        )
+        self.residual_layers = nn.ModuleList([
+            ResidualBlock(self.hidden_size, num_channels, 2 ** (i % dilation_cycle_length))
+            for i in range(num_layers)
+        ])
+        self.skip_projection = _kaiming_conv1x1(num_channels, num_channels)
+        self.output_projection = _kaiming_conv1x1(num_channels, in_dims * n_feats)
+        nn.init.zeros_(self.output_projection.weight)
+        self._engine = None  # native plan, created lazily on the module's CUDA device
+
+    # ------------------------------------------------------------------ native engine plumbing
+    def __deepcopy__(self, memo):
+        import copy
+        cls = self.__class__
+        new = cls.__new__(cls)
+        memo[id(self)] = new
+        for k, v in self.__dict__.items():
+            new.__dict__[k] = None if k == '_engine' else copy.deepcopy(v, memo)
+        return new
+
+    def __getstate__(self):
+        d = self.__dict__.copy()
+        d['_engine'] = None
+        return d
+
+    def engine(self):
+        """Native plan with weights packed from the CURRENT parameters (repacked when they change)."""
+        from ..engine import WaveNetEngine
+        dev = self.input_projection.weight.device
+        if dev.type != 'cuda':
+            raise RuntimeError(
+                "diffsinger_b200.WaveNet has no CPU inference path: move the module to a B200 "
+                "(sm_100a) device; the torch-op branch is for autograd only.")
+        if self._engine is None or self._engine.device != dev:
+            if self._engine is not None:
+                self._engine.close()
+            self._engine = WaveNetEngine(self, dev)
+        if self._engine.weights_key != WaveNetEngine.weights_fingerprint(self):
+            self._engine.pack(self)
+        return self._engine
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, spec, diffusion_step, cond):
+        """
+        :param spec: [B, F, M, T]
+        :param diffusion_step: [B] or [1], long or float
+        :param cond: [B, H, T] (may be a transposed view of [B, T, H])
+        :return: [B, F, M, T]
+        """
+        if torch.is_grad_enabled() and (spec.requires_grad or any(p.requires_grad for p in self.parameters())):
+            return self._forward_autograd(spec, diffusion_step, cond)
+        return self._forward_native(spec, diffusion_step, cond)
+
+    @torch.no_grad()
+    def _forward_native(self, spec, diffusion_step, cond):
+        eng = self.engine()
+        B, Fn, M, T = spec.shape
+        per_sample = diffusion_step.numel() > 1
+        sess = eng.session(B, T, max_times=1, per_sample=per_sample)
+        sess.set_cond(cond.transpose(1, 2))  # [B, T, H]; a no-copy view when cond came from [B,T,H]
+        t = diffusion_step.to(torch.float32).reshape(1, -1) if per_sample else diffusion_step.to(torch.float32).reshape(1)
+        sess.set_times(t)
+        x = spec.reshape(B, Fn * M, T).transpose(1, 2).contiguous().float()  # time-major [B, T, F*M]
+        y = sess.forward(x, 0)
+        return y.transpose(1, 2).reshape(B, Fn, M, T)
+
+    def _forward_autograd(self, spec, diffusion_step, cond):
+        x = spec.squeeze(1) if self.n_feats == 1 else spec.flatten(start_dim=1, end_dim=2)
+        x = F.relu(self.input_projection(x))
+        d = self.mlp(self.diffusion_embedding(diffusion_step))
+        skip = 0
+        for layer in self.residual_layers:
+            x, s = layer(x, cond, d)
+            skip = skip + s
+        x = skip / math.sqrt(len(self.residual_layers))
+        x = self.output_projection(F.relu(self.skip_projection(x)))
+        if self.n_feats == 1:
+            return x[:, None, :, :]
+        return x.reshape(-1, self.n_feats, self.in_dims, x.shape[2])

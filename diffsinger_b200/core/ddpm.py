@@ -1,0 +1,286 @@
+"""Drop-in for the reference's ``modules/core/ddpm.py`` sampler classes.
+
+Same constructor signatures, buffers (names / shapes / persistence, ddpm.py:82-115), ``forward``
+contract and per-call ``hparams`` reads; ``inference()`` compiles the selected sampler into a
+Program (core/programs.py) and runs it through the native session (one CUDA graph per
+(sampler config, B, T)).  Training (`infer=False`) goes through the backbone's autograd branch.
+"""
+from __future__ import annotations
+
+from typing import List, Tuple
+
+import numpy as np
+import torch
+from torch import nn
+
+from ..backbones import build_backbone
+from ..hparams import get_hparams
+from . import programs
+from .runtime import run_program, to_time_major
+
+
+def linear_beta_schedule(timesteps, max_beta=0.01):
+    """reference ddpm.py:28-33 (called without max_beta at :67, so beta_max = 0.01)."""
+    return np.linspace(1e-4, max_beta, timesteps)
+
+
+def cosine_beta_schedule(timesteps, s=0.008):
+    """reference ddpm.py:36-46."""
+    steps = timesteps + 1
+    x = np.linspace(0, steps, steps)
+    alphas_cumprod = np.cos(((x / steps) + s) / (1 + s) * np.pi * 0.5) ** 2
+    alphas_cumprod = alphas_cumprod / alphas_cumprod[0]
+    betas = 1 - (alphas_cumprod[1:] / alphas_cumprod[:-1])
+    return np.clip(betas, a_min=0, a_max=0.999)
+
+
+beta_schedule = {"cosine": cosine_beta_schedule, "linear": linear_beta_schedule}
+
+
+class GaussianDiffusion(nn.Module):
+    def __init__(self, out_dims, num_feats=1, timesteps=1000, k_step=1000,
+                 backbone_type=None, backbone_args=None, betas=None,
+                 spec_min=None, spec_max=None):
+        super().__init__()
+        hparams = get_hparams()
+        self.denoise_fn: nn.Module = build_backbone(out_dims, num_feats, backbone_type, backbone_args)
+        self.out_dims = out_dims
+        self.num_feats = num_feats
+
+        if betas is not None:
+            betas = betas.detach().cpu().numpy() if isinstance(betas, torch.Tensor) else betas
+        else:
+            betas = beta_schedule[hparams['schedule_type']](timesteps)
+        alphas = 1. - betas
+        alphas_cumprod = np.cumprod(alphas, axis=0)
+        alphas_cumprod_prev = np.append(1., alphas_cumprod[:-1])
+
+        self.use_shallow_diffusion = hparams.get('use_shallow_diffusion', False)
+        if self.use_shallow_diffusion:
+            assert k_step <= timesteps, 'K_step should not be larger than timesteps.'
+        self.timesteps = timesteps
+        self.k_step = k_step if self.use_shallow_diffusion else timesteps
+
+        def reg(name, arr):
+            self.register_buffer(name, torch.tensor(arr, dtype=torch.float32))
+
+        reg('betas', betas)
+        reg('alphas_cumprod', alphas_cumprod)
+        reg('alphas_cumprod_prev', alphas_cumprod_prev)
+        reg('sqrt_alphas_cumprod', np.sqrt(alphas_cumprod))
+        reg('sqrt_one_minus_alphas_cumprod', np.sqrt(1. - alphas_cumprod))
+        reg('log_one_minus_alphas_cumprod', np.log(1. - alphas_cumprod))
+        reg('sqrt_recip_alphas_cumprod', np.sqrt(1. / alphas_cumprod))
+        reg('sqrt_recipm1_alphas_cumprod', np.sqrt(1. / alphas_cumprod - 1))
+        posterior_variance = betas * (1. - alphas_cumprod_prev) / (1. - alphas_cumprod)
+        reg('posterior_variance', posterior_variance)
+        reg('posterior_log_variance_clipped', np.log(np.maximum(posterior_variance, 1e-20)))
+        reg('posterior_mean_coef1', betas * np.sqrt(alphas_cumprod_prev) / (1. - alphas_cumprod))
+        reg('posterior_mean_coef2', (1. - alphas_cumprod_prev) * np.sqrt(alphas) / (1. - alphas_cumprod))
+
+        # spec_min / spec_max: [1, 1, M] or [1, F, 1, M] after the transpose (ddpm.py:104-109)
+        spec_min = torch.FloatTensor(spec_min)[None, None, :out_dims].transpose(-3, -2)
+        spec_max = torch.FloatTensor(spec_max)[None, None, :out_dims].transpose(-3, -2)
+        self.register_buffer('spec_min', spec_min)
+        self.register_buffer('spec_max', spec_max)
+
+        self.time_scale_factor = self.timesteps
+        self.t_start = 1 - self.k_step / self.timesteps
+        factors = torch.LongTensor([i for i in range(1, self.timesteps + 1) if self.timesteps % i == 0])
+        self.register_buffer('timestep_factors', factors, persistent=False)
+        self._programs = {}
+
+    # ------------------------------------------------------------------ training-side helpers
+    def q_sample(self, x_start, t, noise):
+        shape = (x_start.shape[0],) + (1,) * (x_start.dim() - 1)
+        return (self.sqrt_alphas_cumprod.gather(-1, t).reshape(shape) * x_start
+                + self.sqrt_one_minus_alphas_cumprod.gather(-1, t).reshape(shape) * noise)
+
+    def p_losses(self, x_start, t, cond, noise=None):
+        if noise is None:
+            noise = torch.randn_like(x_start)
+        x_noisy = self.q_sample(x_start=x_start, t=t, noise=noise)
+        x_recon = self.denoise_fn(x_noisy, t, cond)
+        return x_recon, noise
+
+    # ------------------------------------------------------------------ sampling
+    def _program(self, algorithm: str, t_max: int, speedup: int):
+        key = (algorithm, t_max, speedup)
+        prog = self._programs.get(key)
+        if prog is None:
+            if algorithm == 'ddim':
+                prog = programs.ddim_program(self.alphas_cumprod, t_max, speedup)
+            elif algorithm == 'pndm':
+                prog = programs.pndm_program(self.alphas_cumprod, t_max, speedup)
+            elif algorithm == 'dpm-solver':
+                prog = programs.dpm_solver_pp_program(self.betas[:t_max], t_max // speedup)
+            elif algorithm == 'unipc':
+                prog = programs.unipc_program(self.betas[:t_max], t_max // speedup)
+            elif algorithm == '__ancestral__':
+                prog = programs.ddpm_program(self, t_max)
+            else:
+                raise ValueError(f"Unsupported acceleration algorithm for DDPM: {algorithm}.")
+            self._programs[key] = prog
+        return prog
+
+    @torch.no_grad()
+    def inference(self, cond, b=1, x_start=None, device=None):
+        """cond [B, H, T]; x_start [B, F, M, T] or None -> [B, T, M] / [B, F, T, M] (ddpm.py:221-351)."""
+        hparams = get_hparams()
+        depth = hparams.get('K_step_infer', self.k_step)
+        speedup = hparams['diff_speedup']
+        if speedup > 0:
+            assert depth % speedup == 0, f'Acceleration ratio must be a factor of diffusion depth {depth}.'
+
+        T = cond.shape[2]
+        noise = torch.randn(b, self.num_feats, self.out_dims, T, device=device)
+        t_max = min(depth, self.k_step) if self.use_shallow_diffusion else self.k_step
+
+        if t_max >= self.timesteps:
+            x = noise
+        elif t_max > 0:
+            assert x_start is not None, 'Missing shallow diffusion source.'
+            x = self.q_sample(x_start, torch.full((b,), t_max - 1, device=device, dtype=torch.long), noise)
+        else:
+            assert x_start is not None, 'Missing shallow diffusion source.'
+            x = x_start
+
+        if t_max > 0:
+            if speedup > 1:
+                prog = self._program(hparams['diff_accelerator'], t_max, speedup)
+                extra = []
+            else:
+                prog = self._program('__ancestral__', t_max, 1)
+                # fresh noise per step from the global generator, same draw order as noise_like (ddpm.py:153)
+                extra = [torch.randn(b, self.num_feats, self.out_dims, T, device=device) for _ in range(t_max)]
+            x_tm = run_program(self.denoise_fn, prog, to_time_major(x), cond, [to_time_major(e) for e in extra])
+        else:
+            x_tm = to_time_major(x)
+        # [B, T, F*M] -> [B, T, M] (F == 1) or [B, F, T, M]
+        if self.num_feats == 1:
+            return x_tm
+        return x_tm.reshape(b, T, self.num_feats, self.out_dims).permute(0, 2, 1, 3)
+
+    def forward(self, condition, gt_spec=None, src_spec=None, infer=True):
+        """condition [B, T, H] (ddpm.py:353-377)."""
+        cond = condition.transpose(1, 2)
+        b, device = condition.shape[0], condition.device
+        if not infer:
+            spec = self.norm_spec(gt_spec).transpose(-2, -1)
+            if self.num_feats == 1:
+                spec = spec[:, None, :, :]
+            t = torch.randint(0, self.k_step, (b,), device=device).long()
+            return self.p_losses(spec, t, cond=cond)
+        if src_spec is not None:
+            spec = self.norm_spec(src_spec).transpose(-2, -1)
+            if self.num_feats == 1:
+                spec = spec[:, None, :, :]
+        else:
+            spec = None
+        x = self.inference(cond, b=b, x_start=spec, device=device)
+        return self.denorm_spec(x)
+
+    def norm_spec(self, x):
+        return (x - self.spec_min) / (self.spec_max - self.spec_min) * 2 - 1
+
+    def denorm_spec(self, x):
+        return (x + 1) / 2 * (self.spec_max - self.spec_min) + self.spec_min
+
+
+class RepetitiveDiffusion(GaussianDiffusion):
+    """reference ddpm.py:386-421: a scalar curve repeated over `repeat_bins`, mean over bins on the way out."""
+
+    def __init__(self, vmin: float | int | list, vmax: float | int | list,
+                 repeat_bins: int, timesteps=1000, k_step=1000,
+                 backbone_type=None, backbone_args=None,
+                 betas=None):
+        assert (isinstance(vmin, (float, int)) and isinstance(vmin, (float, int))) or len(vmin) == len(vmax)
+        num_feats = 1 if isinstance(vmin, (float, int)) else len(vmin)
+        spec_min = [vmin] if num_feats == 1 else [[v] for v in vmin]
+        spec_max = [vmax] if num_feats == 1 else [[v] for v in vmax]
+        self.repeat_bins = repeat_bins
+        super().__init__(
+            out_dims=repeat_bins, num_feats=num_feats,
+            timesteps=timesteps, k_step=k_step,
+            backbone_type=backbone_type, backbone_args=backbone_args,
+            betas=betas, spec_min=spec_min, spec_max=spec_max
+        )
+
+    def norm_spec(self, x):
+        """[B, T] or [B, F, T] -> [B, T, R] or [B, F, T, R]"""
+        repeats = [1, 1, self.repeat_bins] if self.num_feats == 1 else [1, 1, 1, self.repeat_bins]
+        return super().norm_spec(x.unsqueeze(-1).repeat(repeats))
+
+    def denorm_spec(self, x):
+        """[B, T, R] or [B, F, T, R] -> [B, T] or [B, F, T]"""
+        return super().denorm_spec(x).mean(dim=-1)
+
+
+class PitchDiffusion(RepetitiveDiffusion):
+    """reference ddpm.py:424-445."""
+
+    def __init__(self, vmin: float, vmax: float,
+                 cmin: float, cmax: float, repeat_bins,
+                 timesteps=1000, k_step=1000,
+                 backbone_type=None, backbone_args=None,
+                 betas=None):
+        self.vmin = vmin  # norm min
+        self.vmax = vmax  # norm max
+        self.cmin = cmin  # clip min
+        self.cmax = cmax  # clip max
+        super().__init__(
+            vmin=vmin, vmax=vmax, repeat_bins=repeat_bins,
+            timesteps=timesteps, k_step=k_step,
+            backbone_type=backbone_type, backbone_args=backbone_args,
+            betas=betas
+        )
+
+    def norm_spec(self, x):
+        return super().norm_spec(x.clamp(min=self.cmin, max=self.cmax))
+
+    def denorm_spec(self, x):
+        return super().denorm_spec(x).clamp(min=self.cmin, max=self.cmax)
+
+
+class MultiVarianceDiffusion(RepetitiveDiffusion):
+    """reference ddpm.py:448-505."""
+
+    def __init__(
+            self, ranges: List[Tuple[float, float]],
+            clamps: List[Tuple[float | None, float | None] | None],
+            repeat_bins, timesteps=1000, k_step=1000,
+            backbone_type=None, backbone_args=None,
+            betas=None
+    ):
+        assert len(ranges) == len(clamps)
+        self.clamps = clamps
+        vmin = [r[0] for r in ranges]
+        vmax = [r[1] for r in ranges]
+        if len(vmin) == 1:
+            vmin = vmin[0]
+        if len(vmax) == 1:
+            vmax = vmax[0]
+        super().__init__(
+            vmin=vmin, vmax=vmax, repeat_bins=repeat_bins,
+            timesteps=timesteps, k_step=k_step,
+            backbone_type=backbone_type, backbone_args=backbone_args,
+            betas=betas
+        )
+
+    def clamp_spec(self, xs: list | tuple):
+        return [x if c is None else x.clamp(min=c[0], max=c[1]) for x, c in zip(xs, self.clamps)]
+
+    def norm_spec(self, xs: list | tuple):
+        """sequence of [B, T] -> [B, F, T] -> [B, F, T, R]"""
+        assert len(xs) == self.num_feats
+        xs = torch.stack(self.clamp_spec(xs), dim=1)  # [B, F, T]
+        if self.num_feats == 1:
+            xs = xs.squeeze(1)  # [B, T]
+        return super().norm_spec(xs)
+
+    def denorm_spec(self, xs):
+        """[B, T, R] or [B, F, T, R] -> sequence of [B, T]"""
+        xs = super().denorm_spec(xs)
+        xs = [xs] if self.num_feats == 1 else xs.unbind(dim=1)
+        assert len(xs) == self.num_feats
+        return self.clamp_spec(xs)

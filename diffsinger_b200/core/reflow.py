@@ -1,0 +1,194 @@
+"""Drop-in for the reference's ``modules/core/reflow.py`` (RectifiedFlow and its variance wrappers).
+
+Same constructor signatures, non-persistent ``spec_min``/``spec_max`` buffers (reflow.py:33-34),
+``forward`` contract and per-call ``hparams`` reads; the ODE loop (:123-136) is compiled into a Program
+and run by the native session.
+"""
+from __future__ import annotations
+
+from typing import List, Tuple
+
+import torch
+import torch.nn as nn
+
+from ..backbones import build_backbone
+from ..hparams import get_hparams
+from . import programs
+from .runtime import run_program, to_time_major
+
+
+class RectifiedFlow(nn.Module):
+    def __init__(self, out_dims, num_feats=1, t_start=0., time_scale_factor=1000,
+                 backbone_type=None, backbone_args=None,
+                 spec_min=None, spec_max=None):
+        super().__init__()
+        hparams = get_hparams()
+        self.velocity_fn: nn.Module = build_backbone(out_dims, num_feats, backbone_type, backbone_args)
+        self.out_dims = out_dims
+        self.num_feats = num_feats
+        self.use_shallow_diffusion = hparams.get('use_shallow_diffusion', False)
+        if self.use_shallow_diffusion:
+            assert 0. <= t_start <= 1., 'T_start should be in [0, 1].'
+        else:
+            t_start = 0.
+        self.t_start = t_start
+        self.time_scale_factor = time_scale_factor
+        spec_min = torch.FloatTensor(spec_min)[None, None, :out_dims].transpose(-3, -2)
+        spec_max = torch.FloatTensor(spec_max)[None, None, :out_dims].transpose(-3, -2)
+        self.register_buffer('spec_min', spec_min, persistent=False)
+        self.register_buffer('spec_max', spec_max, persistent=False)
+        self._programs = {}
+
+    def p_losses(self, x_end, t, cond):
+        x_start = torch.randn_like(x_end)
+        x_t = x_start + t[:, None, None, None] * (x_end - x_start)
+        v_pred = self.velocity_fn(x_t, t * self.time_scale_factor, cond)
+        return v_pred, x_end - x_start
+
+    def forward(self, condition, gt_spec=None, src_spec=None, infer=True):
+        cond = condition.transpose(1, 2)
+        b, device = condition.shape[0], condition.device
+        if not infer:
+            spec = self.norm_spec(gt_spec).transpose(-2, -1)
+            if self.num_feats == 1:
+                spec = spec[:, None, :, :]
+            t = self.t_start + (1.0 - self.t_start) * torch.rand((b,), device=device)
+            v_pred, v_gt = self.p_losses(spec, t, cond=cond)
+            return v_pred, v_gt, t
+        if src_spec is not None:
+            spec = self.norm_spec(src_spec).transpose(-2, -1)
+            if self.num_feats == 1:
+                spec = spec[:, None, :, :]
+        else:
+            spec = None
+        x = self.inference(cond, b=b, x_end=spec, device=device)
+        return self.denorm_spec(x)
+
+    @torch.no_grad()
+    def inference(self, cond, b=1, x_end=None, device=None):
+        """cond [B, H, T]; x_end [B, F, M, T] or None -> [B, T, M] / [B, F, T, M] (reflow.py:104-138)."""
+        hparams = get_hparams()
+        T = cond.shape[2]
+        noise = torch.randn(b, self.num_feats, self.out_dims, T, device=device)
+        t_start = hparams.get('T_start_infer', self.t_start)
+        if self.use_shallow_diffusion and t_start > 0:
+            assert x_end is not None, 'Missing shallow diffusion source.'
+            if t_start >= 1.:
+                t_start = 1.
+                x = x_end
+            else:
+                x = t_start * x_end + (1 - t_start) * noise
+        else:
+            t_start = 0.
+            x = noise
+
+        algorithm = hparams['sampling_algorithm']
+        infer_step = hparams['sampling_steps']
+        x_tm = to_time_major(x)
+        if t_start < 1:
+            key = (algorithm, infer_step, float(t_start), float(self.time_scale_factor))
+            prog = self._programs.get(key)
+            if prog is None:
+                prog = self._programs[key] = programs.reflow_program(algorithm, infer_step, float(t_start),
+                                                                     float(self.time_scale_factor))
+            if infer_step > 0:
+                x_tm = run_program(self.velocity_fn, prog, x_tm, cond)
+        if self.num_feats == 1:
+            return x_tm
+        return x_tm.reshape(b, T, self.num_feats, self.out_dims).permute(0, 2, 1, 3)
+
+    def norm_spec(self, x):
+        return (x - self.spec_min) / (self.spec_max - self.spec_min) * 2 - 1
+
+    def denorm_spec(self, x):
+        return (x + 1) / 2 * (self.spec_max - self.spec_min) + self.spec_min
+
+
+class RepetitiveRectifiedFlow(RectifiedFlow):
+    """reference reflow.py:147-181."""
+
+    def __init__(self, vmin: float | int | list, vmax: float | int | list,
+                 repeat_bins: int, time_scale_factor=1000,
+                 backbone_type=None, backbone_args=None):
+        assert (isinstance(vmin, (float, int)) and isinstance(vmin, (float, int))) or len(vmin) == len(vmax)
+        num_feats = 1 if isinstance(vmin, (float, int)) else len(vmin)
+        spec_min = [vmin] if num_feats == 1 else [[v] for v in vmin]
+        spec_max = [vmax] if num_feats == 1 else [[v] for v in vmax]
+        self.repeat_bins = repeat_bins
+        super().__init__(
+            out_dims=repeat_bins, num_feats=num_feats,
+            time_scale_factor=time_scale_factor,
+            backbone_type=backbone_type, backbone_args=backbone_args,
+            spec_min=spec_min, spec_max=spec_max
+        )
+
+    def norm_spec(self, x):
+        repeats = [1, 1, self.repeat_bins] if self.num_feats == 1 else [1, 1, 1, self.repeat_bins]
+        return super().norm_spec(x.unsqueeze(-1).repeat(repeats))
+
+    def denorm_spec(self, x):
+        return super().denorm_spec(x).mean(dim=-1)
+
+
+class PitchRectifiedFlow(RepetitiveRectifiedFlow):
+    """reference reflow.py:184-203."""
+
+    def __init__(self, vmin: float, vmax: float,
+                 cmin: float, cmax: float, repeat_bins,
+                 time_scale_factor=1000,
+                 backbone_type=None, backbone_args=None):
+        self.vmin = vmin
+        self.vmax = vmax
+        self.cmin = cmin
+        self.cmax = cmax
+        super().__init__(
+            vmin=vmin, vmax=vmax, repeat_bins=repeat_bins,
+            time_scale_factor=time_scale_factor,
+            backbone_type=backbone_type, backbone_args=backbone_args
+        )
+
+    def norm_spec(self, x):
+        return super().norm_spec(x.clamp(min=self.cmin, max=self.cmax))
+
+    def denorm_spec(self, x):
+        return super().denorm_spec(x).clamp(min=self.cmin, max=self.cmax)
+
+
+class MultiVarianceRectifiedFlow(RepetitiveRectifiedFlow):
+    """reference reflow.py:206-261."""
+
+    def __init__(
+            self, ranges: List[Tuple[float, float]],
+            clamps: List[Tuple[float | None, float | None] | None],
+            repeat_bins, time_scale_factor=1000,
+            backbone_type=None, backbone_args=None
+    ):
+        assert len(ranges) == len(clamps)
+        self.clamps = clamps
+        vmin = [r[0] for r in ranges]
+        vmax = [r[1] for r in ranges]
+        if len(vmin) == 1:
+            vmin = vmin[0]
+        if len(vmax) == 1:
+            vmax = vmax[0]
+        super().__init__(
+            vmin=vmin, vmax=vmax, repeat_bins=repeat_bins,
+            time_scale_factor=time_scale_factor,
+            backbone_type=backbone_type, backbone_args=backbone_args
+        )
+
+    def clamp_spec(self, xs: list | tuple):
+        return [x if c is None else x.clamp(min=c[0], max=c[1]) for x, c in zip(xs, self.clamps)]
+
+    def norm_spec(self, xs: list | tuple):
+        assert len(xs) == self.num_feats
+        xs = torch.stack(self.clamp_spec(xs), dim=1)
+        if self.num_feats == 1:
+            xs = xs.squeeze(1)
+        return super().norm_spec(xs)
+
+    def denorm_spec(self, xs):
+        xs = super().denorm_spec(xs)
+        xs = [xs] if self.num_feats == 1 else xs.unbind(dim=1)
+        assert len(xs) == self.num_feats
+        return self.clamp_spec(xs)

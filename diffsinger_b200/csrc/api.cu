@@ -1,0 +1,586 @@
+// libdsb200.so -- C ABI (include/dsb200.h) over the sm_100a kernels in this directory.
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/dsb200.h"
+#include "aux_kernels.cuh"
+#include "gemm_epilogue.cuh"
+
+using namespace dsb;
+
+// ------------------------------------------------------------------------------------ errors
+static thread_local std::string g_err;
+
+static int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+#define CUDA_TRY(expr)                                                                             \
+  do {                                                                                             \
+    cudaError_t e__ = (expr);                                                                      \
+    if (e__ != cudaSuccess) return fail(DS_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+  } while (0)
+#define DS_TRY(expr)        \
+  do {                      \
+    int r__ = (expr);       \
+    if (r__ != 0) return r__; \
+  } while (0)
+
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+// ------------------------------------------------------------------------------------ driver entry (no -lcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+static int g_num_sms = 0;
+
+static int ensure_device() {
+  if (g_encode && g_num_sms) return 0;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    return fail(DS_ERR_NO_DEVICE, "no CUDA device visible");
+  }
+  int dev = 0;
+  CUDA_TRY(cudaGetDevice(&dev));
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, dev));
+  if (prop.major != 10) return fail(DS_ERR_NO_DEVICE, "device %s is sm_%d%d; this library is sm_100a only", prop.name, prop.major, prop.minor);
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  CUDA_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+  if (!fn || qres != cudaDriverEntryPointSuccess) return fail(DS_ERR_NO_DEVICE, "cuTensorMapEncodeTiled not available from the driver");
+  g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+  g_num_sms = prop.multiProcessorCount;
+  return 0;
+}
+
+// bf16 activation map: dims (channels, T, B), box (64, 128, 1), 128-byte swizzle, OOB -> zeros.
+static int make_act_map(CUtensorMap* m, const void* base, int channels, int T, int B) {
+  if (channels % 8) return fail(DS_ERR_INVALID, "activation channel count %d not a multiple of 8", channels);
+  cuuint64_t dims[3] = {(cuuint64_t)channels, (cuuint64_t)T, (cuuint64_t)B};
+  cuuint64_t strides[2] = {(cuuint64_t)channels * 2, (cuuint64_t)channels * 2 * (cuuint64_t)T};
+  cuuint32_t box[3] = {64, 128, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(DS_ERR_CUDA, "cuTensorMapEncodeTiled(activation %dx%dx%d) -> %d", channels, T, B, (int)r);
+  return 0;
+}
+// bf16 weight map: dims (K, rows), box (64, BN).
+static int make_weight_map(CUtensorMap* m, const void* base, int K, int rows, int BN) {
+  cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)K * 2};
+  cuuint32_t box[2] = {64, (cuuint32_t)BN};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(DS_ERR_CUDA, "cuTensorMapEncodeTiled(weights %dx%d box %d) -> %d", K, rows, BN, (int)r);
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------ GEMM launch
+template <int BN, int EPI>
+static int launch_gemm_t(const GemmParams& p, cudaStream_t st) {
+  static bool attr_done = false;
+  auto kern = ds_gemm_kernel<BN, EPI>;
+  if (!attr_done) {
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GemmCfg<BN>::kSmemBytes));
+    attr_done = true;
+  }
+  const int grid = p.total_tiles < g_num_sms ? p.total_tiles : g_num_sms;
+  kern<<<grid, 256, GemmCfg<BN>::kSmemBytes, st>>>(p);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+static int launch_gemm(int BN, int epi, const GemmParams& p, cudaStream_t st) {
+#define DS_CASE(bn, e) \
+  if (BN == bn && epi == e) return launch_gemm_t<bn, e>(p, st);
+  DS_CASE(64, EPI_LINEAR) DS_CASE(128, EPI_LINEAR) DS_CASE(256, EPI_LINEAR)
+  DS_CASE(128, EPI_GATE) DS_CASE(256, EPI_GATE)
+  DS_CASE(64, EPI_RES) DS_CASE(128, EPI_RES) DS_CASE(256, EPI_RES)
+  DS_CASE(64, EPI_OUTF32) DS_CASE(128, EPI_OUTF32) DS_CASE(256, EPI_OUTF32)
+#undef DS_CASE
+  return fail(DS_ERR_INVALID, "no GEMM instantiation for BN=%d epilogue=%d", BN, epi);
+}
+
+static inline int ew_grid(long n, int threads) {
+  long blocks = (n + threads - 1) / threads;
+  long cap = (long)(g_num_sms ? g_num_sms : 148) * 8;
+  return (int)(blocks < cap ? (blocks < 1 ? 1 : blocks) : cap);
+}
+
+// ------------------------------------------------------------------------------------ plan
+struct ds_plan {
+  ds_wavenet_config cfg;
+  int C, L, H, FM, FMp;  // FMp: F*M padded to the 64-wide K block of the head GEMM
+  int K1;                // gate GEMM K = 3C + H
+  int BN_G, BN_C, BN_O;  // N tile of the gate GEMM / the C-wide GEMMs / the output projection
+  int FMr;               // output-projection rows padded to BN_O
+  // byte offsets into the packed blob
+  size_t o_whead, o_w1, o_w2, o_wsk, o_wsp, o_wout;                 // bf16 matrices
+  size_t o_bhead, o_b1, o_b2, o_bsk, o_bsp, o_bout;                 // fp32 biases
+  size_t o_mlp0w, o_mlp0b, o_mlp2w, o_mlp2b, o_wd, o_bd;            // fp32 step-embedding weights
+  size_t packed_bytes;
+  uint8_t* packed = nullptr;
+  bool packed_ok = false;
+  CUtensorMap tm_whead, tm_w1, tm_w2, tm_wsk, tm_wsp, tm_wout;
+};
+
+static void plan_layout(ds_plan* p) {
+  const size_t C = p->C, L = p->L;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    size_t o = off;
+    off = align_up(off + bytes, 256);
+    return o;
+  };
+  const size_t Cr = align_up(C, p->BN_C);  // == C
+  p->o_whead = take(Cr * p->FMp * 2);
+  p->o_w1 = take(L * 2 * C * p->K1 * 2);
+  p->o_w2 = take(L * C * C * 2);
+  p->o_wsk = take(C * L * C * 2);
+  p->o_wsp = take(C * C * 2);
+  p->o_wout = take((size_t)p->FMr * C * 2);
+  p->o_bhead = take(C * 4);
+  p->o_b1 = take(L * 2 * C * 4);
+  p->o_b2 = take(L * C * 4);
+  p->o_bsk = take(C * 4);
+  p->o_bsp = take(C * 4);
+  p->o_bout = take((size_t)p->FMr * 4);
+  p->o_mlp0w = take(4 * C * C * 4);
+  p->o_mlp0b = take(4 * C * 4);
+  p->o_mlp2w = take(4 * C * C * 4);
+  p->o_mlp2b = take(C * 4);
+  p->o_wd = take(L * C * C * 4);
+  p->o_bd = take(L * C * 4);
+  p->packed_bytes = off;
+}
+
+extern "C" const char* ds_last_error(void) { return g_err.c_str(); }
+extern "C" int ds_abi_version(void) { return DSB200_ABI_VERSION; }
+extern "C" int ds_device_check(void) { return ensure_device(); }
+
+extern "C" int ds_plan_create(const ds_wavenet_config* cfg, ds_plan** out) {
+  if (!cfg || !out) return fail(DS_ERR_INVALID, "null argument");
+  const int C = cfg->num_channels, H = cfg->hidden_size, FM = cfg->in_dims * cfg->n_feats;
+  if (C <= 0 || C % 64) return fail(DS_ERR_INVALID, "num_channels=%d must be a positive multiple of 64", C);
+  if (H <= 0 || H % 64) return fail(DS_ERR_INVALID, "hidden_size=%d must be a positive multiple of 64", H);
+  if (FM <= 0 || FM % 4 || FM > 1024) return fail(DS_ERR_INVALID, "in_dims*n_feats=%d must be a multiple of 4 in (0,1024]", FM);
+  if (cfg->num_layers <= 0 || cfg->dilation_cycle_length <= 0 || cfg->dilation_cycle_length > 10)
+    return fail(DS_ERR_INVALID, "bad num_layers/dilation_cycle_length");
+  ds_plan* p = new ds_plan();
+  p->cfg = *cfg;
+  p->C = C; p->L = cfg->num_layers; p->H = H; p->FM = FM;
+  p->FMp = (int)align_up(FM, 64);
+  p->K1 = 3 * C + H;
+  p->BN_G = (C % 128 == 0) ? 256 : 128;
+  p->BN_C = (C % 256 == 0) ? 256 : ((C % 128 == 0) ? 128 : 64);
+  p->BN_O = FM > 128 ? 256 : (FM > 64 ? 128 : 64);
+  p->FMr = (int)align_up(FM, p->BN_O);
+  plan_layout(p);
+  *out = p;
+  return 0;
+}
+
+extern "C" int ds_plan_destroy(ds_plan* plan) {
+  delete plan;
+  return 0;
+}
+
+extern "C" size_t ds_plan_packed_bytes(const ds_plan* plan) { return plan ? plan->packed_bytes : 0; }
+
+extern "C" int ds_plan_pack_weights(ds_plan* p, const ds_wavenet_weights* w, void* packed, size_t packed_bytes, void* stream) {
+  if (!p || !w || !packed) return fail(DS_ERR_INVALID, "null argument");
+  if (packed_bytes < p->packed_bytes) return fail(DS_ERR_INVALID, "packed buffer too small: %zu < %zu", packed_bytes, p->packed_bytes);
+  if ((uintptr_t)packed % 256) return fail(DS_ERR_INVALID, "packed buffer must be 256-byte aligned");
+  DS_TRY(ensure_device());
+  cudaStream_t st = (cudaStream_t)stream;
+  uint8_t* base = (uint8_t*)packed;
+  const int C = p->C, L = p->L, H = p->H, FM = p->FM;
+  auto bf = [&](size_t o) { return (__nv_bfloat16*)(base + o); };
+  auto f32 = [&](size_t o) { return (float*)(base + o); };
+  const int TH = 256;
+  // head: input_projection.weight [C, FM, 1] -> [C][FMp]
+  pack_matrix_kernel<<<ew_grid((long)C * p->FMp, TH), TH, 0, st>>>(bf(p->o_whead), C, p->FMp, p->FMp, w->input_projection_weight, C, FM, FM, 1);
+  // skip_projection [C, C, 1]
+  pack_matrix_kernel<<<ew_grid((long)C * C, TH), TH, 0, st>>>(bf(p->o_wsp), C, C, C, w->skip_projection_weight, C, C, C, 1);
+  // output_projection [FM, C, 1] -> [FMr][C] (zero rows beyond FM)
+  pack_matrix_kernel<<<ew_grid((long)p->FMr * C, TH), TH, 0, st>>>(bf(p->o_wout), p->FMr, C, C, w->output_projection_weight, FM, C, C, 1);
+  CUDA_TRY(cudaMemsetAsync(f32(p->o_bout), 0, (size_t)p->FMr * 4, st));
+  CUDA_TRY(cudaMemcpyAsync(f32(p->o_bout), w->output_projection_bias, (size_t)FM * 4, cudaMemcpyDeviceToDevice, st));
+  CUDA_TRY(cudaMemcpyAsync(f32(p->o_bhead), w->input_projection_bias, (size_t)C * 4, cudaMemcpyDeviceToDevice, st));
+  CUDA_TRY(cudaMemcpyAsync(f32(p->o_bsp), w->skip_projection_bias, (size_t)C * 4, cudaMemcpyDeviceToDevice, st));
+  CUDA_TRY(cudaMemcpyAsync(f32(p->o_mlp0w), w->mlp0_weight, (size_t)4 * C * C * 4, cudaMemcpyDeviceToDevice, st));
+  CUDA_TRY(cudaMemcpyAsync(f32(p->o_mlp0b), w->mlp0_bias, (size_t)4 * C * 4, cudaMemcpyDeviceToDevice, st));
+  CUDA_TRY(cudaMemcpyAsync(f32(p->o_mlp2w), w->mlp2_weight, (size_t)4 * C * C * 4, cudaMemcpyDeviceToDevice, st));
+  CUDA_TRY(cudaMemcpyAsync(f32(p->o_mlp2b), w->mlp2_bias, (size_t)C * 4, cudaMemcpyDeviceToDevice, st));
+  // skip bias sum starts at zero; each layer adds its skip-half bias with a 2-term lincomb
+  CUDA_TRY(cudaMemsetAsync(f32(p->o_bsk), 0, (size_t)C * 4, st));
+  for (int l = 0; l < L; ++l) {
+    pack_gate_kernel<<<ew_grid((long)2 * C * p->K1, TH), TH, 0, st>>>(
+        bf(p->o_w1) + (size_t)l * 2 * C * p->K1, f32(p->o_b1) + (size_t)l * 2 * C, w->dilated_conv_weight[l], w->dilated_conv_bias[l],
+        w->conditioner_projection_weight[l], w->conditioner_projection_bias[l], C, H, p->BN_G);
+    // residual half: rows [0, C) of output_projection [2C, C, 1]
+    pack_matrix_kernel<<<ew_grid((long)C * C, TH), TH, 0, st>>>(bf(p->o_w2) + (size_t)l * C * C, C, C, C, w->layer_output_projection_weight[l], C, C, C, 1);
+    CUDA_TRY(cudaMemcpyAsync(f32(p->o_b2) + (size_t)l * C, w->layer_output_projection_bias[l], (size_t)C * 4, cudaMemcpyDeviceToDevice, st));
+    // skip half: rows [C, 2C) -> columns [l*C, (l+1)*C) of the [C][L*C] deferred-skip matrix
+    pack_matrix_kernel<<<ew_grid((long)C * C, TH), TH, 0, st>>>(bf(p->o_wsk) + (size_t)l * C, C, C, (long)L * C,
+                                                                w->layer_output_projection_weight[l] + (size_t)C * C, C, C, C, 1);
+    accum_kernel<<<ceil_div(C, TH), TH, 0, st>>>(f32(p->o_bsk), w->layer_output_projection_bias[l] + C, C);
+    CUDA_TRY(cudaMemcpyAsync(f32(p->o_wd) + (size_t)l * C * C, w->diffusion_projection_weight[l], (size_t)C * C * 4, cudaMemcpyDeviceToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(f32(p->o_bd) + (size_t)l * C, w->diffusion_projection_bias[l], (size_t)C * 4, cudaMemcpyDeviceToDevice, st));
+  }
+  CUDA_TRY(cudaGetLastError());
+  p->packed = base;
+  // weight tensor maps (K-major bf16, box 64 x BN)
+  DS_TRY(make_weight_map(&p->tm_whead, base + p->o_whead, p->FMp, C, p->BN_C));
+  DS_TRY(make_weight_map(&p->tm_w1, base + p->o_w1, p->K1, L * 2 * C, p->BN_G));
+  DS_TRY(make_weight_map(&p->tm_w2, base + p->o_w2, C, L * C, p->BN_C));
+  DS_TRY(make_weight_map(&p->tm_wsk, base + p->o_wsk, L * C, C, p->BN_C));
+  DS_TRY(make_weight_map(&p->tm_wsp, base + p->o_wsp, C, C, p->BN_C));
+  DS_TRY(make_weight_map(&p->tm_wout, base + p->o_wout, C, p->FMr, p->BN_O));
+  p->packed_ok = true;
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------ session
+struct GraphEntry {
+  cudaGraphExec_t exec = nullptr;
+  int64_t launches = 0;
+};
+
+struct ds_session {
+  ds_plan* plan;
+  int B, T, max_times, per_sample;
+  int n_times = 0;
+  uint8_t* ws;
+  // workspace offsets
+  size_t o_cond, o_xb, o_xt, o_z, o_s1, o_s2, o_g, o_d, o_tmp, ws_bytes;
+  CUtensorMap tm_cond, tm_xb, tm_xt, tm_z, tm_s1, tm_s2;
+  cudaStream_t cap_stream = nullptr;
+  std::map<std::string, GraphEntry> graphs;
+  int64_t last_launches = 0;
+  bool cond_set = false;
+};
+
+static void session_layout(const ds_plan* p, int B, int T, int max_times, int per_sample, ds_session* s) {
+  const size_t rows = (size_t)B * T;
+  const size_t C = p->C, L = p->L;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    size_t o = off;
+    off = align_up(off + bytes, 1024);
+    return o;
+  };
+  s->o_cond = take(rows * p->H * 2);
+  s->o_xb = take(rows * p->FMp * 2);
+  s->o_xt = take(rows * C * 2);
+  s->o_z = take(rows * L * C * 2);
+  s->o_s1 = take(rows * C * 2);
+  s->o_s2 = take(rows * C * 2);
+  const size_t nt = (size_t)max_times * (per_sample ? B : 1);
+  s->o_g = take(nt * C * 4);
+  s->o_d = take(nt * L * C * 4);
+  s->o_tmp = take(rows * p->FM * 4);
+  s->ws_bytes = off;
+}
+
+extern "C" size_t ds_session_workspace_bytes(const ds_plan* plan, int32_t B, int32_t T, int32_t max_times, int32_t per_sample_times) {
+  if (!plan || B <= 0 || T <= 0 || max_times <= 0) return 0;
+  ds_session tmp;
+  session_layout(plan, B, T, max_times, per_sample_times, &tmp);
+  return tmp.ws_bytes;
+}
+
+extern "C" int ds_session_create(ds_plan* plan, int32_t B, int32_t T, int32_t max_times, int32_t per_sample_times, void* workspace,
+                                 size_t workspace_bytes, ds_session** out) {
+  if (!plan || !workspace || !out) return fail(DS_ERR_INVALID, "null argument");
+  if (!plan->packed_ok) return fail(DS_ERR_STATE, "ds_plan_pack_weights has not been called");
+  if (B <= 0 || T <= 0 || max_times <= 0) return fail(DS_ERR_INVALID, "B, T, max_times must be positive");
+  if ((uintptr_t)workspace % 1024) return fail(DS_ERR_INVALID, "workspace must be 1024-byte aligned");
+  DS_TRY(ensure_device());
+  ds_session* s = new ds_session();
+  s->plan = plan; s->B = B; s->T = T; s->max_times = max_times; s->per_sample = per_sample_times ? 1 : 0;
+  session_layout(plan, B, T, max_times, s->per_sample, s);
+  if (workspace_bytes < s->ws_bytes) {
+    size_t need = s->ws_bytes;
+    delete s;
+    return fail(DS_ERR_INVALID, "workspace too small: %zu < %zu", workspace_bytes, need);
+  }
+  s->ws = (uint8_t*)workspace;
+  int r = 0;
+  r = r ? r : make_act_map(&s->tm_cond, s->ws + s->o_cond, plan->H, T, B);
+  r = r ? r : make_act_map(&s->tm_xb, s->ws + s->o_xb, plan->FMp, T, B);
+  r = r ? r : make_act_map(&s->tm_xt, s->ws + s->o_xt, plan->C, T, B);
+  r = r ? r : make_act_map(&s->tm_z, s->ws + s->o_z, plan->L * plan->C, T, B);
+  r = r ? r : make_act_map(&s->tm_s1, s->ws + s->o_s1, plan->C, T, B);
+  r = r ? r : make_act_map(&s->tm_s2, s->ws + s->o_s2, plan->C, T, B);
+  if (r) {
+    delete s;
+    return r;
+  }
+  *out = s;
+  return 0;
+}
+
+extern "C" int ds_session_destroy(ds_session* s) {
+  if (!s) return 0;
+  for (auto& kv : s->graphs)
+    if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+  if (s->cap_stream) cudaStreamDestroy(s->cap_stream);
+  delete s;
+  return 0;
+}
+
+extern "C" int ds_session_set_cond(ds_session* s, const float* cond_bth, void* stream) {
+  if (!s || !cond_bth) return fail(DS_ERR_INVALID, "null argument");
+  const long rows = (long)s->B * s->T;
+  const int H = s->plan->H;
+  f32_to_bf16_pad_kernel<<<ew_grid(rows * H / 4, 256), 256, 0, (cudaStream_t)stream>>>((__nv_bfloat16*)(s->ws + s->o_cond), cond_bth, rows, H, H);
+  CUDA_TRY(cudaGetLastError());
+  s->cond_set = true;
+  return 0;
+}
+
+extern "C" int ds_session_set_times(ds_session* s, const float* t_dev, int32_t n_times, void* stream) {
+  if (!s || !t_dev) return fail(DS_ERR_INVALID, "null argument");
+  if (n_times <= 0 || n_times > s->max_times) return fail(DS_ERR_INVALID, "n_times=%d outside (0, %d]", n_times, s->max_times);
+  const ds_plan* p = s->plan;
+  const int C = p->C, L = p->L;
+  const int n = n_times * (s->per_sample ? s->B : 1);
+  cudaStream_t st = (cudaStream_t)stream;
+  const uint8_t* pk = p->packed;
+  float* g = (float*)(s->ws + s->o_g);
+  float* d = (float*)(s->ws + s->o_d);
+  step_mlp_kernel<<<n, 256, 5 * C * sizeof(float), st>>>(g, t_dev, (const float*)(pk + p->o_mlp0w), (const float*)(pk + p->o_mlp0b),
+                                                         (const float*)(pk + p->o_mlp2w), (const float*)(pk + p->o_mlp2b), C);
+  step_proj_kernel<<<dim3(L, n), 256, C * sizeof(float), st>>>(d, g, (const float*)(pk + p->o_wd), (const float*)(pk + p->o_bd), C, L);
+  CUDA_TRY(cudaGetLastError());
+  s->n_times = n_times;
+  return 0;
+}
+
+// One backbone evaluation = 2L+4 launches on `st` (WaveNet.forward, wavenet.py:75-107).
+static int session_eval(ds_session* s, const float* x, int time_index, float* out, cudaStream_t st, int64_t* launches) {
+  const ds_plan* p = s->plan;
+  const int C = p->C, L = p->L, B = s->B, T = s->T;
+  const long rows = (long)B * T;
+  const uint8_t* pk = p->packed;
+  const int Bt = s->per_sample ? B : 1;
+  const float* dtab = (const float*)(s->ws + s->o_d) + (size_t)time_index * Bt * L * C;
+  const int vstride = s->per_sample ? L * C : 0;
+  __nv_bfloat16* xb = (__nv_bfloat16*)(s->ws + s->o_xb);
+  __nv_bfloat16* xt = (__nv_bfloat16*)(s->ws + s->o_xt);
+  __nv_bfloat16* z = (__nv_bfloat16*)(s->ws + s->o_z);
+  __nv_bfloat16* s1 = (__nv_bfloat16*)(s->ws + s->o_s1);
+  __nv_bfloat16* s2 = (__nv_bfloat16*)(s->ws + s->o_s2);
+  const int tiles_t = ceil_div(T, 128);
+
+  f32_to_bf16_pad_kernel<<<ew_grid(rows * p->FMp / 4, 256), 256, 0, st>>>(xb, x, rows, p->FM, p->FMp);
+  CUDA_TRY(cudaGetLastError());
+  ++*launches;
+
+  GemmParams g;
+  memset(&g, 0, sizeof(g));
+  g.T = T; g.B = B; g.tiles_t = tiles_t; g.scale = 1.0f; g.vec_bstride = vstride;
+  auto shape = [&](int n_tiles) {
+    g.n_tiles = n_tiles;
+    g.total_tiles = B * tiles_t * n_tiles;
+  };
+  // head: relu(input_projection(x)) (+ d_0 so that layer 0 reads x + d directly)      wavenet.py:86-88,36
+  g.tmA0 = s->tm_xb; g.tmB = p->tm_whead;
+  g.a0_c0 = 0; g.kb_a0 = p->FMp / 64; g.n_taps = 1; g.dil = 0; g.kb_a1 = 0; g.b_row0 = 0;
+  g.relu = 1; g.bias = (const float*)(pk + p->o_bhead); g.vec_add = dtab; g.vec_sub = nullptr;
+  g.out = xt; g.ld_out = C; g.out_c0 = 0;
+  shape(C / p->BN_C);
+  DS_TRY(launch_gemm(p->BN_C, EPI_LINEAR, g, st));
+  ++*launches;
+  for (int l = 0; l < L; ++l) {
+    // gate GEMM: dilated conv (3 taps) + conditioner projection, sigmoid*tanh epilogue   wavenet.py:35-42
+    g.tmA0 = s->tm_xt; g.tmA1 = s->tm_cond; g.tmB = p->tm_w1;
+    g.a0_c0 = 0; g.kb_a0 = C / 64; g.n_taps = 3; g.dil = 1 << (l % p->cfg.dilation_cycle_length); g.kb_a1 = p->H / 64;
+    g.b_row0 = l * 2 * C; g.relu = 0; g.bias = (const float*)(pk + p->o_b1) + (size_t)l * 2 * C;
+    g.vec_add = nullptr; g.vec_sub = nullptr;
+    g.out = z; g.ld_out = L * C; g.out_c0 = l * C;
+    shape(2 * C / p->BN_G);
+    DS_TRY(launch_gemm(p->BN_G, EPI_GATE, g, st));
+    ++*launches;
+    if (l + 1 < L) {
+      // residual half of output_projection + (x + res)/sqrt(2)                          wavenet.py:44-48
+      // (the last layer's residual is never used, wavenet.py:92-94, so it is not computed)
+      g.tmA0 = s->tm_z; g.tmB = p->tm_w2;
+      g.a0_c0 = l * C; g.kb_a0 = C / 64; g.n_taps = 1; g.dil = 0; g.kb_a1 = 0; g.b_row0 = l * C;
+      g.bias = (const float*)(pk + p->o_b2) + (size_t)l * C;
+      g.vec_sub = dtab + (size_t)l * C; g.vec_add = dtab + (size_t)(l + 1) * C;
+      g.res_in = xt; g.ld_res = C; g.out = xt; g.ld_out = C; g.out_c0 = 0;
+      shape(C / p->BN_C);
+      DS_TRY(launch_gemm(p->BN_C, EPI_RES, g, st));
+      ++*launches;
+    }
+  }
+  // deferred skip: sum_l skip_l = [z_0 | ... | z_{L-1}] x [Wskip_0 | ... | Wskip_{L-1}]^T, accumulated in TMEM;
+  // then / sqrt(L)                                                                       wavenet.py:44-48,96
+  g.tmA0 = s->tm_z; g.tmB = p->tm_wsk;
+  g.a0_c0 = 0; g.kb_a0 = L * C / 64; g.n_taps = 1; g.kb_a1 = 0; g.b_row0 = 0; g.relu = 0;
+  g.scale = 1.0f / sqrtf((float)L);
+  g.bias = (const float*)(pk + p->o_bsk); g.vec_add = nullptr; g.vec_sub = nullptr; g.res_in = nullptr;
+  g.out = s1; g.ld_out = C; g.out_c0 = 0;
+  shape(C / p->BN_C);
+  DS_TRY(launch_gemm(p->BN_C, EPI_LINEAR, g, st));
+  ++*launches;
+  // relu(skip_projection)                                                                wavenet.py:97-98
+  g.tmA0 = s->tm_s1; g.tmB = p->tm_wsp; g.kb_a0 = C / 64; g.relu = 1; g.scale = 1.0f;
+  g.bias = (const float*)(pk + p->o_bsp); g.out = s2;
+  DS_TRY(launch_gemm(p->BN_C, EPI_LINEAR, g, st));
+  ++*launches;
+  // output_projection -> fp32 [B][T][F*M]                                                 wavenet.py:99
+  g.tmA0 = s->tm_s2; g.tmB = p->tm_wout; g.relu = 0;
+  g.bias = (const float*)(pk + p->o_bout); g.out = out; g.ld_out = p->FM; g.n_real = p->FM;
+  shape(p->FMr / p->BN_O);
+  DS_TRY(launch_gemm(p->BN_O, EPI_OUTF32, g, st));
+  ++*launches;
+  return 0;
+}
+
+static int check_eval_ready(ds_session* s, int time_index) {
+  if (!s->cond_set) return fail(DS_ERR_STATE, "ds_session_set_cond has not been called");
+  if (time_index < 0 || time_index >= s->n_times) return fail(DS_ERR_STATE, "time index %d outside the %d installed times", time_index, s->n_times);
+  return 0;
+}
+
+extern "C" int ds_session_forward(ds_session* s, const float* x_btc, int32_t time_index, float* out_btc, void* stream) {
+  if (!s || !x_btc || !out_btc) return fail(DS_ERR_INVALID, "null argument");
+  DS_TRY(check_eval_ready(s, time_index));
+  s->last_launches = 0;
+  return session_eval(s, x_btc, time_index, out_btc, (cudaStream_t)stream, &s->last_launches);
+}
+
+static int launch_lincomb(float* dst, const float* const* srcs, const float* coefs, int n, size_t numel, cudaStream_t st) {
+  if (n <= 0 || n > 8) return fail(DS_ERR_INVALID, "lincomb term count %d outside [1,8]", n);
+  if (numel % 4) return fail(DS_ERR_INVALID, "lincomb numel must be a multiple of 4");
+  LincombArgs a;
+  memset(&a, 0, sizeof(a));
+  a.n = n;
+  for (int i = 0; i < n; ++i) {
+    a.src[i] = srcs[i];
+    a.coef[i] = coefs[i];
+  }
+  const long n4 = (long)(numel / 4);
+  lincomb_kernel<<<ew_grid(n4, 256), 256, 0, st>>>(dst, a, n4);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+static int run_ops(ds_session* s, const ds_op* ops, int n_ops, float* const* bufs, int n_bufs, cudaStream_t st, int64_t* launches) {
+  const size_t numel = (size_t)s->B * s->T * s->plan->FM;
+  for (int i = 0; i < n_ops; ++i) {
+    const ds_op& op = ops[i];
+    if (op.dst < 0 || op.dst >= n_bufs) return fail(DS_ERR_INVALID, "op %d: dst %d out of range", i, op.dst);
+    if (op.kind == DS_OP_EVAL) {
+      if (op.src[0] < 0 || op.src[0] >= n_bufs || op.src[0] == op.dst) return fail(DS_ERR_INVALID, "op %d: bad EVAL source", i);
+      DS_TRY(check_eval_ready(s, op.time));
+      DS_TRY(session_eval(s, bufs[op.src[0]], op.time, bufs[op.dst], st, launches));
+    } else if (op.kind == DS_OP_LINCOMB) {
+      const float* srcs[8];
+      if (op.n <= 0 || op.n > 8) return fail(DS_ERR_INVALID, "op %d: bad term count", i);
+      for (int k = 0; k < op.n; ++k) {
+        if (op.src[k] < 0 || op.src[k] >= n_bufs) return fail(DS_ERR_INVALID, "op %d: src %d out of range", i, op.src[k]);
+        srcs[k] = bufs[op.src[k]];
+      }
+      DS_TRY(launch_lincomb(bufs[op.dst], srcs, op.coef, op.n, numel, st));
+      ++*launches;
+    } else {
+      return fail(DS_ERR_INVALID, "op %d: unknown kind %d", i, op.kind);
+    }
+  }
+  return 0;
+}
+
+extern "C" int ds_session_run(ds_session* s, const ds_op* ops, int32_t n_ops, float* const* bufs, int32_t n_bufs, int32_t use_graph,
+                              void* stream) {
+  if (!s || !ops || !bufs || n_ops <= 0 || n_bufs <= 0) return fail(DS_ERR_INVALID, "bad argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!use_graph) {
+    s->last_launches = 0;
+    return run_ops(s, ops, n_ops, bufs, n_bufs, st, &s->last_launches);
+  }
+  std::string key((const char*)ops, sizeof(ds_op) * n_ops);
+  key.append((const char*)bufs, sizeof(float*) * n_bufs);
+  auto it = s->graphs.find(key);
+  if (it == s->graphs.end()) {
+    if (!s->cap_stream) CUDA_TRY(cudaStreamCreateWithFlags(&s->cap_stream, cudaStreamNonBlocking));
+    // warm every kernel variant once outside capture is unnecessary: attributes are set lazily by
+    // cudaFuncSetAttribute, which is legal during capture (it is not a stream operation).
+    GraphEntry e;
+    CUDA_TRY(cudaStreamBeginCapture(s->cap_stream, cudaStreamCaptureModeThreadLocal));
+    int r = run_ops(s, ops, n_ops, bufs, n_bufs, s->cap_stream, &e.launches);
+    cudaGraph_t graph = nullptr;
+    cudaError_t ce = cudaStreamEndCapture(s->cap_stream, &graph);
+    if (r != 0) {
+      if (graph) cudaGraphDestroy(graph);
+      return r;
+    }
+    if (ce != cudaSuccess) return fail(DS_ERR_CUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(ce));
+    ce = cudaGraphInstantiate(&e.exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ce != cudaSuccess) return fail(DS_ERR_CUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(ce));
+    it = s->graphs.emplace(key, e).first;
+  }
+  CUDA_TRY(cudaGraphLaunch(it->second.exec, st));
+  s->last_launches = it->second.launches;
+  return 0;
+}
+
+extern "C" int64_t ds_session_last_launches(const ds_session* s) { return s ? s->last_launches : 0; }
+
+// ------------------------------------------------------------------------------------ helpers
+extern "C" int ds_lincomb(float* dst, const float* const* srcs, const float* coefs, int32_t n, size_t numel, void* stream) {
+  if (!dst || !srcs || !coefs) return fail(DS_ERR_INVALID, "null argument");
+  DS_TRY(ensure_device());
+  return launch_lincomb(dst, srcs, coefs, n, numel, (cudaStream_t)stream);
+}
+
+extern "C" int ds_transpose(float* dst, const float* src, int32_t B, int32_t R, int32_t C, void* stream) {
+  if (!dst || !src || B <= 0 || R <= 0 || C <= 0) return fail(DS_ERR_INVALID, "bad argument");
+  if (B > 65535) return fail(DS_ERR_INVALID, "B too large for ds_transpose");
+  dim3 grid(ceil_div(C, 32), ceil_div(R, 32), B);
+  transpose_kernel<<<grid, dim3(32, 8), 0, (cudaStream_t)stream>>>(dst, src, R, C);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ds_debug_gemm(const ds_gemm_desc* d, void* stream) {
+  if (!d) return fail(DS_ERR_INVALID, "null argument");
+  DS_TRY(ensure_device());
+  GemmParams g;
+  memset(&g, 0, sizeof(g));
+  DS_TRY(make_act_map(&g.tmA0, d->a0, d->a0_channels, d->T, d->B));
+  if (d->kb_a1 > 0) DS_TRY(make_act_map(&g.tmA1, d->a1, d->a1_channels, d->T, d->B));
+  DS_TRY(make_weight_map(&g.tmB, d->w, d->w_k, d->w_rows, d->BN));
+  g.T = d->T; g.B = d->B; g.tiles_t = ceil_div(d->T, 128); g.n_tiles = d->n_tiles;
+  g.total_tiles = d->B * g.tiles_t * d->n_tiles;
+  g.a0_c0 = d->a0_c0; g.kb_a0 = d->kb_a0; g.n_taps = d->n_taps; g.dil = d->dil; g.kb_a1 = d->kb_a1; g.b_row0 = d->b_row0;
+  g.relu = d->relu; g.scale = d->scale; g.bias = d->bias; g.vec_sub = d->vec_sub; g.vec_add = d->vec_add;
+  g.vec_bstride = d->vec_bstride; g.res_in = (const __nv_bfloat16*)d->res_in; g.ld_res = d->ld_res;
+  g.out = d->out; g.ld_out = d->ld_out; g.out_c0 = d->out_c0; g.n_real = d->n_real;
+  return launch_gemm(d->BN, d->epi, g, (cudaStream_t)stream);
+}

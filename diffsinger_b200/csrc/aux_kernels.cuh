@@ -1,0 +1,173 @@
+// SIMT helper kernels around the tensor-core GEMMs: weight packing (once per checkpoint load),
+// step-embedding tables (once per sampler configuration), layout/precision conversion and the
+// vectorised sampler update (HBM-bound elementwise work).
+#pragma once
+#include <cstdint>
+#include <cuda_bf16.h>
+
+namespace dsb {
+
+// ------------------------------------------------------------------ weight packing
+// dst[r*dst_ld + k] (bf16) = src[r*src_rs + k*src_ks] for r < rows, k < cols; zero for the padding
+// (r < dst_rows, k < dst_cols).
+__global__ void pack_matrix_kernel(__nv_bfloat16* __restrict__ dst, int dst_rows, int dst_cols, long dst_ld,
+                                   const float* __restrict__ src, int rows, int cols, long src_rs, long src_ks) {
+  const long n = static_cast<long>(dst_rows) * dst_cols;
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n; i += static_cast<long>(gridDim.x) * blockDim.x) {
+    const int r = static_cast<int>(i / dst_cols), k = static_cast<int>(i % dst_cols);
+    float v = 0.f;
+    if (r < rows && k < cols) v = src[r * src_rs + k * src_ks];
+    dst[r * dst_ld + k] = __float2bfloat16_rn(v);
+  }
+}
+
+__global__ void accum_kernel(float* __restrict__ dst, const float* __restrict__ src, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] += src[i];
+}
+
+// Gate GEMM weights of one layer (reference: ResidualBlock.dilated_conv [2C,C,3] + conditioner_projection
+// [2C,H,1], wavenet.py:22-30).  Rows are permuted so each BN-row pass holds BN/2 gate rows followed by
+// the BN/2 filter rows of the SAME channels; K = [tap0 | tap1 | tap2 | cond].
+__global__ void pack_gate_kernel(__nv_bfloat16* __restrict__ dst, float* __restrict__ bias_dst,
+                                 const float* __restrict__ w_dil, const float* __restrict__ b_dil,
+                                 const float* __restrict__ w_cond, const float* __restrict__ b_cond, int C, int H, int BN) {
+  const int K = 3 * C + H;
+  const int half = BN / 2;
+  const long n = static_cast<long>(2 * C) * K;
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n; i += static_cast<long>(gridDim.x) * blockDim.x) {
+    const int r = static_cast<int>(i / K), k = static_cast<int>(i % K);
+    const int pass = r / BN, rr = r % BN;
+    const int src_row = (rr < half) ? pass * half + rr : C + pass * half + (rr - half);
+    float v;
+    if (k < 3 * C) {
+      const int tap = k / C, c = k % C;
+      v = w_dil[(static_cast<long>(src_row) * C + c) * 3 + tap];
+    } else {
+      v = w_cond[static_cast<long>(src_row) * H + (k - 3 * C)];
+    }
+    dst[i] = __float2bfloat16_rn(v);
+    if (k == 0) bias_dst[r] = b_dil[src_row] + b_cond[src_row];
+  }
+}
+
+// ------------------------------------------------------------------ step embedding
+// g[j][:] = mlp(SinusoidalPosEmb(t_j))   (common_layers.py:273-280, wavenet.py:58-62,89-90)
+// one block per time value; blockDim = 256; dynamic smem = 5*C floats.
+__global__ void step_mlp_kernel(float* __restrict__ g, const float* __restrict__ t, const float* __restrict__ w0,
+                                const float* __restrict__ b0, const float* __restrict__ w2, const float* __restrict__ b2, int C) {
+  extern __shared__ float sm[];
+  float* e = sm;       // [C]
+  float* h = sm + C;   // [4C]
+  const int j = blockIdx.x;
+  const float tj = t[j];
+  const int half = C / 2;
+  const float sc = logf(10000.0f) / static_cast<float>(half - 1);
+  for (int i = threadIdx.x; i < half; i += blockDim.x) {
+    const float a = tj * expf(static_cast<float>(i) * -sc);
+    e[i] = sinf(a);
+    e[half + i] = cosf(a);
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  for (int o = warp; o < 4 * C; o += nw) {
+    float acc = 0.f;
+    for (int k = lane; k < C; k += 32) acc = fmaf(w0[static_cast<long>(o) * C + k], e[k], acc);
+    for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
+    if (lane == 0) {
+      const float x = acc + b0[o];
+      const float sp = (x > 20.f) ? x : log1pf(expf(x));  // softplus, torch threshold 20
+      h[o] = x * tanhf(sp);                              // Mish
+    }
+  }
+  __syncthreads();
+  for (int o = warp; o < C; o += nw) {
+    float acc = 0.f;
+    for (int k = lane; k < 4 * C; k += 32) acc = fmaf(w2[static_cast<long>(o) * 4 * C + k], h[k], acc);
+    for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
+    if (lane == 0) g[static_cast<long>(j) * C + o] = acc + b2[o];
+  }
+}
+
+// d[j][l][:] = diffusion_projection_l(g[j])  (wavenet.py:29,34).  grid = (L, n); wd [L][C][C], bd [L][C].
+__global__ void step_proj_kernel(float* __restrict__ d, const float* __restrict__ g, const float* __restrict__ wd,
+                                 const float* __restrict__ bd, int C, int L) {
+  extern __shared__ float sg[];
+  const int l = blockIdx.x, j = blockIdx.y;
+  for (int i = threadIdx.x; i < C; i += blockDim.x) sg[i] = g[static_cast<long>(j) * C + i];
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  const float* w = wd + static_cast<long>(l) * C * C;
+  for (int o = warp; o < C; o += nw) {
+    float acc = 0.f;
+    for (int k = lane; k < C; k += 32) acc = fmaf(w[static_cast<long>(o) * C + k], sg[k], acc);
+    for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
+    if (lane == 0) d[(static_cast<long>(j) * L + l) * C + o] = acc + bd[l * C + o];
+  }
+}
+
+// ------------------------------------------------------------------ conversions
+// fp32 [rows][cols] -> bf16 [rows][ld] (zero padded columns).  cols, ld multiples of 4.
+__global__ void f32_to_bf16_pad_kernel(__nv_bfloat16* __restrict__ dst, const float* __restrict__ src, long rows, int cols, int ld) {
+  const int q = ld / 4;
+  const long n = rows * q;
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n; i += static_cast<long>(gridDim.x) * blockDim.x) {
+    const long r = i / q;
+    const int c = static_cast<int>(i % q) * 4;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c < cols) v = *reinterpret_cast<const float4*>(src + r * cols + c);
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+    uint2 o;
+    o.x = *reinterpret_cast<uint32_t*>(&lo);
+    o.y = *reinterpret_cast<uint32_t*>(&hi);
+    *reinterpret_cast<uint2*>(dst + r * ld + c) = o;
+  }
+}
+
+// [B][R][Cc] <-> [B][Cc][R] fp32 transpose through a 32x33 tile (coalesced both ways).
+__global__ void transpose_kernel(float* __restrict__ dst, const float* __restrict__ src, int R, int Cc) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z;
+  const float* s = src + static_cast<long>(b) * R * Cc;
+  float* d = dst + static_cast<long>(b) * R * Cc;
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int r = r0 + i, c = c0 + threadIdx.x;
+    if (r < R && c < Cc) tile[i][threadIdx.x] = s[static_cast<long>(r) * Cc + c];
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int c = c0 + i, r = r0 + threadIdx.x;
+    if (r < R && c < Cc) d[static_cast<long>(c) * R + r] = tile[threadIdx.x][i];
+  }
+}
+
+// ------------------------------------------------------------------ sampler update
+// dst = sum_i coef[i] * src[i]  (n <= 8 terms), fp32, float4-vectorised, grid-stride.
+// Covers every sampler family's tensor update (DDIM / PLMS / ancestral / DPM-Solver++ / UniPC /
+// Euler / RK stages) because all of them are linear in (x, model outputs, history) with scalar
+// coefficients that depend only on the schedule.  Optionally also writes a
+// bf16 copy (row-padded) that the next backbone evaluation's head GEMM reads.
+struct LincombArgs {
+  const float* src[8];
+  float coef[8];
+  int n;
+};
+__global__ void lincomb_kernel(float* __restrict__ dst, LincombArgs a, long n4) {
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n4; i += static_cast<long>(gridDim.x) * blockDim.x) {
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      if (k < a.n) {
+        const float4 v = reinterpret_cast<const float4*>(a.src[k])[i];
+        acc.x = fmaf(a.coef[k], v.x, acc.x);
+        acc.y = fmaf(a.coef[k], v.y, acc.y);
+        acc.z = fmaf(a.coef[k], v.z, acc.z);
+        acc.w = fmaf(a.coef[k], v.w, acc.w);
+      }
+    }
+    reinterpret_cast<float4*>(dst)[i] = acc;
+  }
+}
+
+}  // namespace dsb

@@ -1,0 +1,115 @@
+// Fused epilogues of ds_gemm_kernel: TMEM -> registers -> math -> global memory.
+// One thread owns one frame (TMEM lane); columns are output channels, so every thread writes
+// contiguous channel runs of its own [B][T][C] row (64-byte runs per 32-column chunk).
+#pragma once
+#include "gemm_kernel.cuh"
+
+namespace dsb {
+
+__device__ __forceinline__ void ld_f32x32(const float* __restrict__ ptr, float (&v)[32]) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float4 q = __ldg(reinterpret_cast<const float4*>(ptr) + i);
+    v[4 * i + 0] = q.x; v[4 * i + 1] = q.y; v[4 * i + 2] = q.z; v[4 * i + 3] = q.w;
+  }
+}
+
+__device__ __forceinline__ void st_bf16x32(__nv_bfloat16* ptr, const float (&v)[32]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    uint4 q;
+    q.x = pack_bf16(v[8 * i + 0], v[8 * i + 1]);
+    q.y = pack_bf16(v[8 * i + 2], v[8 * i + 3]);
+    q.z = pack_bf16(v[8 * i + 4], v[8 * i + 5]);
+    q.w = pack_bf16(v[8 * i + 6], v[8 * i + 7]);
+    reinterpret_cast<uint4*>(ptr)[i] = q;
+  }
+}
+
+template <int BN, int EPI>
+__device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t taddr, int b, int t, bool valid, int nt) {
+  const size_t row = static_cast<size_t>(b) * p.T + (valid ? t : 0);
+  if constexpr (EPI == EPI_GATE) {
+    // columns [0, BN/2) = gate pre-activations, [BN/2, BN) = filter pre-activations of the SAME channels
+    constexpr int H = BN / 2;
+    __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.out) + row * p.ld_out + p.out_c0 + nt * H;
+    const float* bias = p.bias + nt * BN;
+#pragma unroll 1
+    for (int c = 0; c < H / 32; ++c) {
+      uint32_t g[32], f[32];
+      tmem_ld_32x32(taddr + c * 32, g);
+      tmem_ld_32x32(taddr + H + c * 32, f);
+      float bg[32], bf[32], z[32];
+      ld_f32x32(bias + c * 32, bg);
+      ld_f32x32(bias + H + c * 32, bf);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const float gj = __uint_as_float(g[j]) + bg[j];
+        const float fj = __uint_as_float(f[j]) + bf[j];
+        const float sg = fmaf(0.5f, tanh_approx(0.5f * gj), 0.5f);  // sigmoid
+        z[j] = sg * tanh_approx(fj);
+      }
+      if (valid) st_bf16x32(out + c * 32, z);
+    }
+  } else {
+    const int n0 = nt * BN;
+    const float* bias = p.bias + n0;
+    const float* vadd = p.vec_add ? p.vec_add + static_cast<size_t>(b) * p.vec_bstride + n0 : nullptr;
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+      uint32_t a[32];
+      tmem_ld_32x32(taddr + c * 32, a);
+      float v[32], bb[32];
+      ld_f32x32(bias + c * 32, bb);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(a[j]) + bb[j];
+      if constexpr (EPI == EPI_RES) {
+        // x_next = (x + residual)/sqrt(2) with x = x~ - d_l; stored as x~_next = x_next + d_{l+1}
+        const float* vsub = p.vec_sub + static_cast<size_t>(b) * p.vec_bstride + n0 + c * 32;
+        const uint4* xin = reinterpret_cast<const uint4*>(p.res_in + row * p.ld_res + n0 + c * 32);
+        float ds[32];
+        ld_f32x32(vsub, ds);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint4 q = xin[i];
+          const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+          for (int h = 0; h < 4; ++h) {
+            const float x0 = __uint_as_float(w[h] << 16);
+            const float x1 = __uint_as_float(w[h] & 0xffff0000u);
+            v[8 * i + 2 * h + 0] = (v[8 * i + 2 * h + 0] + x0 - ds[8 * i + 2 * h + 0]) * 0.70710678118654752f;
+            v[8 * i + 2 * h + 1] = (v[8 * i + 2 * h + 1] + x1 - ds[8 * i + 2 * h + 1]) * 0.70710678118654752f;
+          }
+        }
+      } else {
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
+        }
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] *= p.scale;
+      }
+      if constexpr (EPI == EPI_OUTF32) {
+        if (valid) {
+          float* out = reinterpret_cast<float*>(p.out) + row * p.ld_out + n0 + c * 32;
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            if (n0 + c * 32 + 4 * i < p.n_real)
+              reinterpret_cast<float4*>(out)[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        }
+      } else {
+        if (vadd) {
+          float da[32];
+          ld_f32x32(vadd + c * 32, da);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] += da[j];
+        }
+        if (valid) st_bf16x32(reinterpret_cast<__nv_bfloat16*>(p.out) + row * p.ld_out + p.out_c0 + n0 + c * 32, v);
+      }
+    }
+  }
+}
+
+}  // namespace dsb

@@ -1,0 +1,192 @@
+// Persistent, warp-specialised tcgen05 GEMM for the WaveNet denoiser (sm_100a).
+//
+//   D[frame, n] = sum_k A[frame, k] * W[n, k]        (frames are the UMMA M dimension, 128 per tile)
+//
+// A is "time-major" activation memory [B][T][channels] (bf16) read through 3-D TMA tensor maps, so
+//   * a dilated-conv tap is just a shifted time coordinate (t0 + (tap-1)*dil) and TMA's out-of-bounds
+//     zero fill IS the conv's zero padding (per utterance, no cross-batch leakage),
+//   * the 1x1 conditioner projection is extra K blocks from a second tensor map (K-concatenation).
+// W is a packed bf16 matrix [rows][K] (K-major) read through a 2-D tensor map.
+// Accumulators live in TMEM (2 x BN fp32 columns, double buffered) and are drained by 4 epilogue warps
+// (thread <-> frame/TMEM lane) that apply the fused epilogue and write global memory directly.
+//
+// Warp roles (256 threads): warp0 = TMA producer (1 elected lane), warp1 = MMA issuer (1 lane),
+// warp2 = TMEM allocator, warp3 idle, warps4..7 = epilogue.
+#pragma once
+#include <cuda.h>
+#include "ptx.cuh"
+
+namespace dsb {
+
+enum : int { EPI_LINEAR = 0, EPI_GATE = 1, EPI_RES = 2, EPI_OUTF32 = 3 };
+
+struct GemmParams {
+  CUtensorMap tmA0;  // primary activation source  (dims: channels, T, B)
+  CUtensorMap tmA1;  // secondary activation source (conditioner), used when kb_a1 > 0
+  CUtensorMap tmB;   // packed weights (dims: K, rows)
+  int T, B, tiles_t, n_tiles, total_tiles;
+  int a0_c0;   // channel offset inside A0 (selects a layer's slice of the gated-activation store)
+  int kb_a0;   // 64-wide K blocks per tap from A0
+  int n_taps;  // 1 (plain 1x1) or 3 (dilated conv)
+  int dil;
+  int kb_a1;   // 64-wide K blocks from A1
+  int b_row0;  // first row of this GEMM inside the packed weight matrix
+  int relu;
+  float scale;
+  const float* bias;     // indexed by tile-global n (packed order for EPI_GATE)
+  const float* vec_sub;  // EPI_RES: step embedding of this layer   [vec_bstride * b + n]
+  const float* vec_add;  // step embedding of the NEXT layer (or null)
+  int vec_bstride;
+  const __nv_bfloat16* res_in;  // EPI_RES: x~ of this layer, [B][T][ld_res]
+  int ld_res;
+  void* out;   // bf16 (LINEAR/GATE/RES) or fp32 (OUTF32), [B][T][ld_out]
+  int ld_out;
+  int out_c0;  // channel offset in out
+  int n_real;  // EPI_OUTF32: number of valid output columns
+};
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int kStages = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr uint32_t kABytes = 128 * 128;  // 128 frames x 64 bf16
+  static constexpr uint32_t kBBytes = BN * 128;   // BN rows  x 64 bf16
+  static constexpr uint32_t kTmemCols = 2 * BN;   // 128 / 256 / 512: powers of two
+  static constexpr uint32_t kSmemBytes = 1024 + kStages * (kABytes + kBBytes) + 256;
+};
+
+template <int BN, int EPI>
+__device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t taddr, int b, int t, bool valid, int nt);
+
+template <int BN, int EPI>
+__global__ void __launch_bounds__(256, 1) ds_gemm_kernel(const __grid_constant__ GemmParams p) {
+  using Cfg = GemmCfg<BN>;
+  constexpr int S = Cfg::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);  // SWIZZLE_128B needs 1024-B alignment
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + S * Cfg::kABytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S * (Cfg::kABytes + Cfg::kBBytes));
+  uint64_t* full = bars;
+  uint64_t* empty = bars + S;
+  uint64_t* tmem_full = bars + 2 * S;
+  uint64_t* tmem_empty = bars + 2 * S + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tmA0);
+    tma_prefetch_desc(&p.tmB);
+    if (p.kb_a1 > 0) tma_prefetch_desc(&p.tmA1);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < S; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);
+      mbar_init(&tmem_empty[i], 128);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int num_kb = p.n_taps * p.kb_a0 + p.kb_a1;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ------------------------------------------------------------ TMA producer
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+        const int nt = tile % p.n_tiles;
+        const int tt = (tile / p.n_tiles) % p.tiles_t;
+        const int b = tile / (p.n_tiles * p.tiles_t);
+        const int t0 = tt * 128;
+        const int row0 = p.b_row0 + nt * BN;
+        const int kb_taps = p.n_taps * p.kb_a0;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full[stage], Cfg::kABytes + Cfg::kBBytes);
+          uint8_t* sa = smem_a + stage * Cfg::kABytes;
+          uint8_t* sb = smem_b + stage * Cfg::kBBytes;
+          if (kb < kb_taps) {
+            const int tap = kb / p.kb_a0;
+            const int cb = kb - tap * p.kb_a0;
+            tma_load_3d(&p.tmA0, &full[stage], sa, p.a0_c0 + cb * 64, t0 + (tap - p.n_taps / 2) * p.dil, b);
+          } else {
+            tma_load_3d(&p.tmA1, &full[stage], sa, (kb - kb_taps) * 64, t0, b);
+          }
+          tma_load_2d(&p.tmB, &full[stage], sb, kb * 64, row0);
+          if (++stage == S) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ------------------------------------------------------------ MMA issuer
+      constexpr uint32_t idesc = make_idesc_bf16_f32(BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+        const int as = it & 1;
+        const uint32_t aphase = (it >> 1) & 1;
+        mbar_wait(&tmem_empty[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + as * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint64_t da = make_kmajor_sw128_desc(smem_u32(smem_a + stage * Cfg::kABytes));
+          const uint64_t db = make_kmajor_sw128_desc(smem_u32(smem_b + stage * Cfg::kBBytes));
+#pragma unroll
+          for (int k = 0; k < 4; ++k)  // 4 x (K = 16) per 64-wide block: +32 B on the start address
+            umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          umma_commit(&empty[stage]);
+          if (kb == num_kb - 1) umma_commit(&tmem_full[as]);
+          if (++stage == S) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // -------------------------------------------------------------- epilogue (128 threads)
+    const int quad = warp & 3;  // TMEM lane quadrant this warp may read
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+      const int nt = tile % p.n_tiles;
+      const int tt = (tile / p.n_tiles) % p.tiles_t;
+      const int b = tile / (p.n_tiles * p.tiles_t);
+      const int as = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      mbar_wait(&tmem_full[as], aphase);
+      tc_fence_after();
+      const int t = tt * 128 + quad * 32 + lane;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * BN;
+      epilogue_tile<BN, EPI>(p, taddr, b, t, t < p.T, nt);
+      tc_fence_before();
+      mbar_arrive(&tmem_empty[as]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  }
+}
+
+}  // namespace dsb

@@ -1,0 +1,146 @@
+/* dsb200 -- C ABI of the B200-native DiffSinger denoiser sampling path (libdsb200.so).
+ *
+ * The reference (hrukalive/DiffSinger) is pure Python/PyTorch and has NO native interface; the
+ * "FFI" a maintainer binds is therefore new.  Each entry point below names the reference code it
+ * replaces (paths relative to the reference root).  Conventions:
+ *   - every function returns 0 on success, a negative ds_status on failure; ds_last_error() gives the
+ *     message (thread-local).  No exceptions cross the boundary.
+ *   - all tensors are BORROWED device pointers owned by the caller (PyTorch) for the duration of
+ *     the call / the object's life; no ownership is transferred.  `stream` is a cudaStream_t
+ *     passed as void* (0 = legacy default stream).  Nothing here synchronises the device.
+ *   - activations cross the ABI "time-major": x[B][T][F*M] fp32, cond[B][T][H] fp32 (the layout
+ *     GaussianDiffusion.forward receives `condition` in, modules/core/ddpm.py:353-357).
+ */
+#ifndef DSB200_H_
+#define DSB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DSB200_ABI_VERSION 1
+
+typedef enum {
+  DS_OK = 0,
+  DS_ERR_INVALID = -1,   /* bad argument / unsupported shape */
+  DS_ERR_CUDA = -2,      /* a CUDA runtime / driver call failed */
+  DS_ERR_NO_DEVICE = -3, /* no sm_100 device / driver entry point missing */
+  DS_ERR_STATE = -4      /* call order violated (weights not packed, times not set, ...) */
+} ds_status;
+
+typedef struct ds_plan ds_plan;       /* one WaveNet: configuration + packed weights */
+typedef struct ds_session ds_session; /* one (plan, B, T): workspace, tensor maps, captured graphs */
+
+/* WaveNet.__init__(in_dims, n_feats, *, num_layers, num_channels, dilation_cycle_length) and
+ * hparams['hidden_size']  -- modules/backbones/wavenet.py:52-73 */
+typedef struct {
+  int32_t in_dims;               /* M: mel bins / repeat bins */
+  int32_t n_feats;               /* F */
+  int32_t num_layers;            /* L */
+  int32_t num_channels;          /* C, multiple of 64 */
+  int32_t dilation_cycle_length; /* dilation of layer i = 2 ** (i % cycle) */
+  int32_t hidden_size;           /* H, multiple of 64 */
+} ds_wavenet_config;
+
+/* fp32 device pointers in the reference's state_dict layout (wavenet.py:22-31,56-73).
+ * The per-layer members are HOST arrays of num_layers device pointers. */
+typedef struct {
+  const float* input_projection_weight;  /* [C, F*M, 1] */
+  const float* input_projection_bias;    /* [C] */
+  const float* mlp0_weight;              /* [4C, C] */
+  const float* mlp0_bias;                /* [4C] */
+  const float* mlp2_weight;              /* [C, 4C] */
+  const float* mlp2_bias;                /* [C] */
+  const float* skip_projection_weight;   /* [C, C, 1] */
+  const float* skip_projection_bias;     /* [C] */
+  const float* output_projection_weight; /* [F*M, C, 1] */
+  const float* output_projection_bias;   /* [F*M] */
+  const float* const* dilated_conv_weight;           /* L x [2C, C, 3] */
+  const float* const* dilated_conv_bias;             /* L x [2C] */
+  const float* const* diffusion_projection_weight;   /* L x [C, C] */
+  const float* const* diffusion_projection_bias;     /* L x [C] */
+  const float* const* conditioner_projection_weight; /* L x [2C, H, 1] */
+  const float* const* conditioner_projection_bias;   /* L x [2C] */
+  const float* const* layer_output_projection_weight; /* L x [2C, C, 1] */
+  const float* const* layer_output_projection_bias;   /* L x [2C] */
+} ds_wavenet_weights;
+
+/* One instruction of a sampler program (see ds_session_run). */
+enum { DS_OP_EVAL = 0, DS_OP_LINCOMB = 1 };
+typedef struct {
+  int32_t kind;    /* DS_OP_EVAL: bufs[dst] = backbone(bufs[src[0]], time index `time`)          */
+                   /* DS_OP_LINCOMB: bufs[dst] = sum_{i<n} coef[i] * bufs[src[i]]  (dst may alias) */
+  int32_t dst;
+  int32_t time;    /* row of the step-embedding table installed by ds_session_set_times */
+  int32_t n;       /* number of terms (LINCOMB), <= 8 */
+  int32_t src[8];
+  float coef[8];
+} ds_op;
+
+const char* ds_last_error(void);
+int ds_abi_version(void);
+/* 0 when a compute-capability-10.x device and the driver's tensor-map encoder are usable. */
+int ds_device_check(void);
+
+/* ---- plan: replaces WaveNet.__init__ + load_state_dict (wavenet.py:52-73, utils/__init__.py:166-222) */
+int ds_plan_create(const ds_wavenet_config* cfg, ds_plan** out);
+int ds_plan_destroy(ds_plan* plan);
+size_t ds_plan_packed_bytes(const ds_plan* plan);
+/* Packs/permutes/casts the fp32 reference weights into `packed` (caller-allocated device memory of
+ * ds_plan_packed_bytes, 256-byte aligned, alive as long as the plan).  Re-call after a weight update. */
+int ds_plan_pack_weights(ds_plan* plan, const ds_wavenet_weights* w, void* packed, size_t packed_bytes, void* stream);
+
+/* ---- session: fixed (B, T) execution context */
+size_t ds_session_workspace_bytes(const ds_plan* plan, int32_t B, int32_t T, int32_t max_times, int32_t per_sample_times);
+int ds_session_create(ds_plan* plan, int32_t B, int32_t T, int32_t max_times, int32_t per_sample_times, void* workspace,
+                      size_t workspace_bytes, ds_session** out);
+int ds_session_destroy(ds_session* s);
+/* cond[B][T][H] fp32 -> internal bf16 copy.  Replaces the per-layer conditioner input of
+ * ResidualBlock.forward (wavenet.py:35); cond is step-invariant so it is staged once per call. */
+int ds_session_set_cond(ds_session* s, const float* cond_bth, void* stream);
+/* Step-embedding tables for n_times diffusion-step values (device fp32 array of n_times values; of
+ * n_times*B values ordered [time][batch] when the session was created with per_sample_times = 1).
+ * Replaces SinusoidalPosEmb + mlp + every layer's diffusion_projection
+ * (common_layers.py:273-280, wavenet.py:89-90, :34). */
+int ds_session_set_times(ds_session* s, const float* t_dev, int32_t n_times, void* stream);
+/* One backbone evaluation, out = WaveNet.forward(x, t[time_index], cond) (wavenet.py:75-107) with
+ * x/out time-major [B][T][F*M] fp32. */
+int ds_session_forward(ds_session* s, const float* x_btc, int32_t time_index, float* out_btc, void* stream);
+/* Runs a whole sampler program (the loop bodies of GaussianDiffusion.inference, ddpm.py:221-351,
+ * and RectifiedFlow.inference, reflow.py:104-138, flattened by the host into EVAL/LINCOMB ops).
+ * bufs: n_bufs fp32 device buffers of B*T*F*M elements.  use_graph != 0 captures the program into a
+ * CUDA graph on first use (keyed by ops + buffer addresses) and replays it afterwards. */
+int ds_session_run(ds_session* s, const ds_op* ops, int32_t n_ops, float* const* bufs, int32_t n_bufs, int32_t use_graph,
+                   void* stream);
+/* Number of kernel launches the last ds_session_forward / ds_session_run issued (or replayed). */
+int64_t ds_session_last_launches(const ds_session* s);
+
+/* ---- stand-alone helpers */
+/* dst = sum coef[i]*src[i] over numel fp32 elements (numel % 4 == 0): the sampler tensor update
+ * (ddpm.py:164-166,181-201; dpm_solver_pytorch.py:573-576,827-831; uni_pc.py:548-567; reflow.py:68-100). */
+int ds_lincomb(float* dst, const float* const* srcs, const float* coefs, int32_t n, size_t numel, void* stream);
+/* [B][R][C] -> [B][C][R] fp32 (spec [B,F*M,T] <-> time-major; ddpm.py:350, reflow.py:137). */
+int ds_transpose(float* dst, const float* src, int32_t B, int32_t R, int32_t C, void* stream);
+
+/* ---- debug / unit-test hook: one tcgen05 GEMM launch with an explicit epilogue */
+typedef struct {
+  int32_t epi;  /* 0 linear(bf16 out), 1 gate, 2 residual, 3 fp32 out */
+  int32_t BN;   /* 64 / 128 / 256 */
+  int32_t B, T;
+  const void* a0; int32_t a0_channels; int32_t a0_c0; int32_t kb_a0; int32_t n_taps; int32_t dil;
+  const void* a1; int32_t a1_channels; int32_t kb_a1;
+  const void* w; int32_t w_rows; int32_t w_k; int32_t b_row0; int32_t n_tiles;
+  const float* bias; const float* vec_sub; const float* vec_add; int32_t vec_bstride;
+  const void* res_in; int32_t ld_res;
+  void* out; int32_t ld_out; int32_t out_c0; int32_t n_real;
+  int32_t relu; float scale;
+} ds_gemm_desc;
+int ds_debug_gemm(const ds_gemm_desc* d, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DSB200_H_ */
