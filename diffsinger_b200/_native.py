@@ -22,7 +22,7 @@ EXPORTS = [
     "ds_last_error", "ds_abi_version", "ds_device_check", "ds_plan_create", "ds_plan_destroy",
     "ds_plan_packed_bytes", "ds_plan_pack_weights", "ds_session_workspace_bytes", "ds_session_create",
     "ds_session_destroy", "ds_session_set_cond", "ds_session_set_times", "ds_session_forward",
-    "ds_session_run", "ds_session_last_launches", "ds_lincomb", "ds_transpose", "ds_debug_gemm",
+    "ds_session_run", "ds_session_last_launches", "ds_lincomb", "ds_transpose", "ds_debug_gemm", "ds_debug_set_trace", "ds_debug_mma_rate",
 ]
 
 
@@ -119,6 +119,8 @@ def lib() -> C.CDLL:
     L.ds_lincomb.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_float), C.c_int32, C.c_size_t, C.c_void_p]
     L.ds_transpose.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
     L.ds_debug_gemm.argtypes = [C.POINTER(GemmDesc), C.c_void_p]
+    L.ds_debug_set_trace.argtypes = [C.c_void_p, C.c_int32]
+    L.ds_debug_mma_rate.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
     _lib = L
     return L
 

@@ -4,6 +4,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <string>
@@ -12,6 +13,9 @@
 #include "../../include/dsb200.h"
 #include "aux_kernels.cuh"
 #include "gemm_epilogue.cuh"
+#include "layer_kernel.cuh"
+#include "layer2_kernel.cuh"
+#include "mma_bench.cuh"
 
 using namespace dsb;
 
@@ -106,7 +110,7 @@ static int launch_gemm_t(const GemmParams& p, cudaStream_t st) {
     attr_done = true;
   }
   const int grid = p.total_tiles < g_num_sms ? p.total_tiles : g_num_sms;
-  kern<<<grid, 256, GemmCfg<BN>::kSmemBytes, st>>>(p);
+  kern<<<grid, kGemmThreads, GemmCfg<BN>::kSmemBytes, st>>>(p);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -122,6 +126,41 @@ static int launch_gemm(int BN, int epi, const GemmParams& p, cudaStream_t st) {
   return fail(DS_ERR_INVALID, "no GEMM instantiation for BN=%d epilogue=%d", BN, epi);
 }
 
+template <int BN2, bool kZSmem>
+static int launch_layer_t(const LayerParams& p, cudaStream_t st) {
+  static bool attr_done = false;
+  auto kern = ds_layer_kernel<BN2, kZSmem>;
+  if (!attr_done) {
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+    attr_done = true;
+  }
+  const int grid = p.total_tiles < g_num_sms ? p.total_tiles : g_num_sms;
+  kern<<<grid, kGemmThreads, layer_smem_bytes(p.kb_c, p.stages, kZSmem), st>>>(p);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+static int launch_layer_pair(const LayerParams& p, cudaStream_t st) {
+  static bool attr_done = false;
+  if (!attr_done) {
+    CUDA_TRY(cudaFuncSetAttribute(ds_layer_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmemBytes));
+    attr_done = true;
+  }
+  const int max_pairs = g_num_sms / 2;
+  const int pairs = p.total_tiles < max_pairs ? p.total_tiles : max_pairs;
+  ds_layer_pair_kernel<<<2 * pairs, kGemmThreads, kPairSmemBytes, st>>>(p);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+static unsigned long long* g_trace = nullptr;
+static int g_trace_cap = 0;
+extern "C" int ds_debug_set_trace(void* dev_buf, int32_t n_entries) {
+  g_trace = (unsigned long long*)dev_buf;
+  g_trace_cap = n_entries;
+  return 0;
+}
+
 static inline int ew_grid(long n, int threads) {
   long blocks = (n + threads - 1) / threads;
   long cap = (long)(g_num_sms ? g_num_sms : 148) * 8;
@@ -135,6 +174,9 @@ struct ds_plan {
   int K1;                // gate GEMM K = 3C + H
   int BN_G, BN_C, BN_O;  // N tile of the gate GEMM / the C-wide GEMMs / the output projection
   int FMr;               // output-projection rows padded to BN_O
+  int fused;             // 0: gate GEMM + residual GEMM; 1: one kernel per layer, z kept in smem; 2: one kernel per
+                         // layer, GEMM-2 re-reads z through TMA (4-deep operand ring); 3: as 2 on CTA pairs (cta_group::2)
+  int fused_stages;
   // byte offsets into the packed blob
   size_t o_whead, o_w1, o_w2, o_wsk, o_wsp, o_wout;                 // bf16 matrices
   size_t o_bhead, o_b1, o_b2, o_bsk, o_bsp, o_bout;                 // fp32 biases
@@ -143,6 +185,7 @@ struct ds_plan {
   uint8_t* packed = nullptr;
   bool packed_ok = false;
   CUtensorMap tm_whead, tm_w1, tm_w2, tm_wsk, tm_wsp, tm_wout;
+  CUtensorMap tm_w1h, tm_w2h;  // 128-row boxes: each CTA of a pair loads half of a 256-row weight tile
 };
 
 static void plan_layout(ds_plan* p) {
@@ -196,6 +239,20 @@ extern "C" int ds_plan_create(const ds_wavenet_config* cfg, ds_plan** out) {
   p->BN_C = (C % 256 == 0) ? 256 : ((C % 128 == 0) ? 128 : 64);
   p->BN_O = FM > 128 ? 256 : (FM > 64 ? 128 : 64);
   p->FMr = (int)align_up(FM, p->BN_O);
+  // fused layer kernel: needs N=256 gate passes and the whole gated tile (C x 128 bf16) in shared memory
+  p->fused_stages = 0;
+  if (C % 128 == 0) {
+    int st = (int)((232448 - 1280 - (C / 64) * (int)kLayerABytes) / (int)(kLayerABytes + kLayerBBytes));
+    p->fused_stages = st > kLayerMaxStages ? kLayerMaxStages : st;
+  }
+  // DSB200_LAYER_MODE = unfused | smem | global | pair.  Default: global (one kernel per layer, single CTA) when
+  // C % 128 == 0.  `pair` (cta_group::2, C % 256 == 0) is functional but measured slower on B200 (profiles/).
+  const char* env = getenv("DSB200_LAYER_MODE");
+  p->fused = (C % 128 == 0) ? 2 : 0;
+  if (env && !strcmp(env, "pair") && C % 256 == 0) p->fused = 3;
+  if (env && !strcmp(env, "unfused")) p->fused = 0;
+  if (env && !strcmp(env, "smem") && p->fused_stages >= 2) p->fused = 1;
+  if (p->fused == 2) p->fused_stages = kLayerMaxStages;
   plan_layout(p);
   *out = p;
   return 0;
@@ -255,6 +312,8 @@ extern "C" int ds_plan_pack_weights(ds_plan* p, const ds_wavenet_weights* w, voi
   DS_TRY(make_weight_map(&p->tm_whead, base + p->o_whead, p->FMp, C, p->BN_C));
   DS_TRY(make_weight_map(&p->tm_w1, base + p->o_w1, p->K1, L * 2 * C, p->BN_G));
   DS_TRY(make_weight_map(&p->tm_w2, base + p->o_w2, C, L * C, p->BN_C));
+  DS_TRY(make_weight_map(&p->tm_w1h, base + p->o_w1, p->K1, L * 2 * C, 128));
+  DS_TRY(make_weight_map(&p->tm_w2h, base + p->o_w2, C, L * C, 128));
   DS_TRY(make_weight_map(&p->tm_wsk, base + p->o_wsk, L * C, C, p->BN_C));
   DS_TRY(make_weight_map(&p->tm_wsp, base + p->o_wsp, C, C, p->BN_C));
   DS_TRY(make_weight_map(&p->tm_wout, base + p->o_wout, C, p->FMr, p->BN_O));
@@ -274,8 +333,8 @@ struct ds_session {
   int n_times = 0;
   uint8_t* ws;
   // workspace offsets
-  size_t o_cond, o_xb, o_xt, o_z, o_s1, o_s2, o_g, o_d, o_tmp, ws_bytes;
-  CUtensorMap tm_cond, tm_xb, tm_xt, tm_z, tm_s1, tm_s2;
+  size_t o_cond, o_xb, o_xt, o_xt1, o_z, o_s1, o_s2, o_g, o_d, o_r, o_tmp, ws_bytes;
+  CUtensorMap tm_cond, tm_xb, tm_xt, tm_xt1, tm_z, tm_s1, tm_s2;
   cudaStream_t cap_stream = nullptr;
   std::map<std::string, GraphEntry> graphs;
   int64_t last_launches = 0;
@@ -294,12 +353,14 @@ static void session_layout(const ds_plan* p, int B, int T, int max_times, int pe
   s->o_cond = take(rows * p->H * 2);
   s->o_xb = take(rows * p->FMp * 2);
   s->o_xt = take(rows * C * 2);
+  s->o_xt1 = take(rows * C * 2);
   s->o_z = take(rows * L * C * 2);
   s->o_s1 = take(rows * C * 2);
   s->o_s2 = take(rows * C * 2);
   const size_t nt = (size_t)max_times * (per_sample ? B : 1);
   s->o_g = take(nt * C * 4);
   s->o_d = take(nt * L * C * 4);
+  s->o_r = take(nt * L * C * 4);
   s->o_tmp = take(rows * p->FM * 4);
   s->ws_bytes = off;
 }
@@ -331,6 +392,7 @@ extern "C" int ds_session_create(ds_plan* plan, int32_t B, int32_t T, int32_t ma
   r = r ? r : make_act_map(&s->tm_cond, s->ws + s->o_cond, plan->H, T, B);
   r = r ? r : make_act_map(&s->tm_xb, s->ws + s->o_xb, plan->FMp, T, B);
   r = r ? r : make_act_map(&s->tm_xt, s->ws + s->o_xt, plan->C, T, B);
+  r = r ? r : make_act_map(&s->tm_xt1, s->ws + s->o_xt1, plan->C, T, B);
   r = r ? r : make_act_map(&s->tm_z, s->ws + s->o_z, plan->L * plan->C, T, B);
   r = r ? r : make_act_map(&s->tm_s1, s->ws + s->o_s1, plan->C, T, B);
   r = r ? r : make_act_map(&s->tm_s2, s->ws + s->o_s2, plan->C, T, B);
@@ -374,6 +436,7 @@ extern "C" int ds_session_set_times(ds_session* s, const float* t_dev, int32_t n
   step_mlp_kernel<<<n, 256, 5 * C * sizeof(float), st>>>(g, t_dev, (const float*)(pk + p->o_mlp0w), (const float*)(pk + p->o_mlp0b),
                                                          (const float*)(pk + p->o_mlp2w), (const float*)(pk + p->o_mlp2b), C);
   step_proj_kernel<<<dim3(L, n), 256, C * sizeof(float), st>>>(d, g, (const float*)(pk + p->o_wd), (const float*)(pk + p->o_bd), C, L);
+  res_vec_kernel<<<ew_grid((long)n * L * C, 256), 256, 0, st>>>((float*)(s->ws + s->o_r), d, (const float*)(pk + p->o_b2), C, L, n);
   CUDA_TRY(cudaGetLastError());
   s->n_times = n_times;
   return 0;
@@ -387,6 +450,7 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   const uint8_t* pk = p->packed;
   const int Bt = s->per_sample ? B : 1;
   const float* dtab = (const float*)(s->ws + s->o_d) + (size_t)time_index * Bt * L * C;
+  const float* rtab = (const float*)(s->ws + s->o_r) + (size_t)time_index * Bt * L * C;
   const int vstride = s->per_sample ? L * C : 0;
   __nv_bfloat16* xb = (__nv_bfloat16*)(s->ws + s->o_xb);
   __nv_bfloat16* xt = (__nv_bfloat16*)(s->ws + s->o_xt);
@@ -414,6 +478,37 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   shape(C / p->BN_C);
   DS_TRY(launch_gemm(p->BN_C, EPI_LINEAR, g, st));
   ++*launches;
+  if (p->fused) {
+    // one kernel per residual layer: gate GEMM -> gated tile in shared memory -> residual GEMM   wavenet.py:33-48
+    __nv_bfloat16* xts[2] = {xt, (__nv_bfloat16*)(s->ws + s->o_xt1)};
+    LayerParams lp;
+    memset(&lp, 0, sizeof(lp));
+    lp.tmCond = s->tm_cond; lp.tmW1 = p->tm_w1; lp.tmW2 = p->tm_w2; lp.tmZ = s->tm_z;
+    lp.T = T; lp.B = B; lp.tiles_t = tiles_t; lp.total_tiles = B * tiles_t;
+    lp.kb_c = C / 64; lp.kb_h = p->H / 64; lp.p1 = 2 * C / 256; lp.stages = p->fused_stages;
+    lp.vec_bstride = vstride; lp.z_out = z; lp.ld_z = L * C;
+    lp.trace = g_trace; lp.trace_cap = g_trace_cap;
+    { const char* de = getenv("DSB200_DBG"); lp.dbg = de ? atoi(de) : 0; }
+    const bool pair = p->fused == 3;
+    if (pair) {
+      lp.tmW1 = p->tm_w1h; lp.tmW2 = p->tm_w2h;
+      lp.tiles_t = ceil_div(tiles_t, 2); lp.total_tiles = B * lp.tiles_t;
+    }
+    for (int l = 0; l < L; ++l) {
+      lp.tmX = (l & 1) ? s->tm_xt1 : s->tm_xt;
+      lp.x_in = xts[l & 1]; lp.x_out = xts[(l + 1) & 1];
+      lp.dil = 1 << (l % p->cfg.dilation_cycle_length);
+      lp.p2 = (l + 1 < L) ? C / p->BN_C : 0;  // the last layer's residual is never used (wavenet.py:92-94)
+      lp.w1_row0 = l * 2 * C; lp.w2_row0 = l * C;
+      lp.bias1 = (const float*)(pk + p->o_b1) + (size_t)l * 2 * C;
+      lp.rvec = rtab + (size_t)l * C;
+      lp.z_c0 = l * C;
+      if (pair) DS_TRY(launch_layer_pair(lp, st));
+      else if (p->fused == 1) DS_TRY(p->BN_C == 256 ? (launch_layer_t<256, true>(lp, st)) : (launch_layer_t<128, true>(lp, st)));
+      else DS_TRY(p->BN_C == 256 ? (launch_layer_t<256, false>(lp, st)) : (launch_layer_t<128, false>(lp, st)));
+      ++*launches;
+    }
+  } else {
   for (int l = 0; l < L; ++l) {
     // gate GEMM: dilated conv (3 taps) + conditioner projection, sigmoid*tanh epilogue   wavenet.py:35-42
     g.tmA0 = s->tm_xt; g.tmA1 = s->tm_cond; g.tmB = p->tm_w1;
@@ -429,13 +524,13 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
       // (the last layer's residual is never used, wavenet.py:92-94, so it is not computed)
       g.tmA0 = s->tm_z; g.tmB = p->tm_w2;
       g.a0_c0 = l * C; g.kb_a0 = C / 64; g.n_taps = 1; g.dil = 0; g.kb_a1 = 0; g.b_row0 = l * C;
-      g.bias = (const float*)(pk + p->o_b2) + (size_t)l * C;
-      g.vec_sub = dtab + (size_t)l * C; g.vec_add = dtab + (size_t)(l + 1) * C;
+      g.bias = nullptr; g.vec_sub = nullptr; g.vec_add = rtab + (size_t)l * C;
       g.res_in = xt; g.ld_res = C; g.out = xt; g.ld_out = C; g.out_c0 = 0;
       shape(C / p->BN_C);
       DS_TRY(launch_gemm(p->BN_C, EPI_RES, g, st));
       ++*launches;
     }
+  }
   }
   // deferred skip: sum_l skip_l = [z_0 | ... | z_{L-1}] x [Wskip_0 | ... | Wskip_{L-1}]^T, accumulated in TMEM;
   // then / sqrt(L)                                                                       wavenet.py:44-48,96
@@ -583,4 +678,26 @@ extern "C" int ds_debug_gemm(const ds_gemm_desc* d, void* stream) {
   g.vec_bstride = d->vec_bstride; g.res_in = (const __nv_bfloat16*)d->res_in; g.ld_res = d->ld_res;
   g.out = d->out; g.ld_out = d->ld_out; g.out_c0 = d->out_c0; g.n_real = d->n_real;
   return launch_gemm(d->BN, d->epi, g, (cudaStream_t)stream);
+}
+
+// Debug: raw tensor-pipe rate.  out: 2*grid int64 device words {issue cycles, issue+drain cycles} per CTA.
+extern "C" int ds_debug_mma_rate(int32_t pair, int32_t grid, int32_t n_mma, int32_t commit_every, long long* out_dev, void* stream) {
+  DS_TRY(ensure_device());
+  const int smem = 1024 + 16384 + 32768 + 256;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (pair) {
+    CUDA_TRY(cudaFuncSetAttribute(mma_rate_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(128); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    CUDA_TRY(cudaLaunchKernelEx(&cfg, mma_rate_kernel<true>, (int)n_mma, (int)commit_every, out_dev));
+  } else {
+    CUDA_TRY(cudaFuncSetAttribute(mma_rate_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    mma_rate_kernel<false><<<grid, 128, smem, st>>>(n_mma, commit_every, out_dev);
+  }
+  CUDA_TRY(cudaGetLastError());
+  return 0;
 }

@@ -106,6 +106,17 @@ __global__ void step_proj_kernel(float* __restrict__ d, const float* __restrict_
   }
 }
 
+// r[j][l][:] = (b2_l - d[j][l]) / sqrt(2) + d[j][l+1]   for l < L-1: everything the residual epilogue adds to
+// (x~ + R)/sqrt(2), folded once per time value (wavenet.py:36,44-48).
+__global__ void res_vec_kernel(float* __restrict__ r, const float* __restrict__ d, const float* __restrict__ b2, int C, int L, int n) {
+  const long total = static_cast<long>(n) * L * C;
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < total; i += static_cast<long>(gridDim.x) * blockDim.x) {
+    const int o = static_cast<int>(i % C);
+    const int l = static_cast<int>((i / C) % L);
+    r[i] = (l + 1 < L) ? (b2[l * C + o] - d[i]) * 0.70710678118654752f + d[i + C] : 0.f;
+  }
+}
+
 // ------------------------------------------------------------------ conversions
 // fp32 [rows][cols] -> bf16 [rows][ld] (zero padded columns).  cols, ld multiples of 4.
 __global__ void f32_to_bf16_pad_kernel(__nv_bfloat16* __restrict__ dst, const float* __restrict__ src, long rows, int cols, int ld) {

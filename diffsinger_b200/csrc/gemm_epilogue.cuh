@@ -26,8 +26,14 @@ __device__ __forceinline__ void st_bf16x32(__nv_bfloat16* ptr, const float (&v)[
   }
 }
 
+__device__ __forceinline__ void ld_x4(const __nv_bfloat16* ptr, uint4 (&q)[4]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) q[i] = __ldg(reinterpret_cast<const uint4*>(ptr) + i);
+}
+
+// `half` in {0,1}: the two epilogue warps that share a TMEM lane quadrant interleave the 32-column chunks.
 template <int BN, int EPI>
-__device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t taddr, int b, int t, bool valid, int nt) {
+__device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t taddr, int b, int t, bool valid, int nt, int half) {
   const size_t row = static_cast<size_t>(b) * p.T + (valid ? t : 0);
   if constexpr (EPI == EPI_GATE) {
     // columns [0, BN/2) = gate pre-activations, [BN/2, BN) = filter pre-activations of the SAME channels
@@ -35,7 +41,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
     __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.out) + row * p.ld_out + p.out_c0 + nt * H;
     const float* bias = p.bias + nt * BN;
 #pragma unroll 1
-    for (int c = 0; c < H / 32; ++c) {
+    for (int c = half; c < H / 32; c += 2) {
       uint32_t g[32], f[32];
       tmem_ld_32x32(taddr + c * 32, g);
       tmem_ld_32x32(taddr + H + c * 32, f);
@@ -52,12 +58,44 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
       }
       if (valid) st_bf16x32(out + c * 32, z);
     }
+  } else if constexpr (EPI == EPI_RES) {
+    // x~_next = (x~ + R) / sqrt(2) + rvec,  rvec = (b - d_l)/sqrt(2) + d_{l+1}  (folded on the host side of the
+    // step-embedding table; wavenet.py:36,44-48).  x~ is prefetched one chunk ahead.
+    const int n0 = nt * BN;
+    const float* rv = p.vec_add + static_cast<size_t>(b) * p.vec_bstride + n0;
+    const __nv_bfloat16* xin = p.res_in + row * p.ld_res + n0;
+    __nv_bfloat16* xout = reinterpret_cast<__nv_bfloat16*>(p.out) + row * p.ld_out + p.out_c0 + n0;
+    uint4 xq[4];
+    ld_x4(xin + half * 32, xq);
+#pragma unroll 1
+    for (int c = half; c < BN / 32; c += 2) {
+      uint32_t a[32];
+      tmem_ld_32x32(taddr + c * 32, a);
+      float v[32], rr[32];
+      ld_f32x32(rv + c * 32, rr);
+      uint4 xn[4];
+      if (c + 2 < BN / 32) ld_x4(xin + (c + 2) * 32, xn);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint32_t w[4] = {xq[i].x, xq[i].y, xq[i].z, xq[i].w};
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          const int j = 8 * i + 2 * h;
+          v[j] = fmaf(__uint_as_float(a[j]) + __uint_as_float(w[h] << 16), 0.70710678118654752f, rr[j]);
+          v[j + 1] = fmaf(__uint_as_float(a[j + 1]) + __uint_as_float(w[h] & 0xffff0000u), 0.70710678118654752f, rr[j + 1]);
+        }
+      }
+      if (valid) st_bf16x32(xout + c * 32, v);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) xq[i] = xn[i];
+    }
   } else {
     const int n0 = nt * BN;
     const float* bias = p.bias + n0;
     const float* vadd = p.vec_add ? p.vec_add + static_cast<size_t>(b) * p.vec_bstride + n0 : nullptr;
 #pragma unroll 1
-    for (int c = 0; c < BN / 32; ++c) {
+    for (int c = half; c < BN / 32; c += 2) {
       uint32_t a[32];
       tmem_ld_32x32(taddr + c * 32, a);
       float v[32], bb[32];
@@ -65,32 +103,12 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
       tmem_ld_wait();
 #pragma unroll
       for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(a[j]) + bb[j];
-      if constexpr (EPI == EPI_RES) {
-        // x_next = (x + residual)/sqrt(2) with x = x~ - d_l; stored as x~_next = x_next + d_{l+1}
-        const float* vsub = p.vec_sub + static_cast<size_t>(b) * p.vec_bstride + n0 + c * 32;
-        const uint4* xin = reinterpret_cast<const uint4*>(p.res_in + row * p.ld_res + n0 + c * 32);
-        float ds[32];
-        ld_f32x32(vsub, ds);
+      if (p.relu) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const uint4 q = xin[i];
-          const uint32_t w[4] = {q.x, q.y, q.z, q.w};
-#pragma unroll
-          for (int h = 0; h < 4; ++h) {
-            const float x0 = __uint_as_float(w[h] << 16);
-            const float x1 = __uint_as_float(w[h] & 0xffff0000u);
-            v[8 * i + 2 * h + 0] = (v[8 * i + 2 * h + 0] + x0 - ds[8 * i + 2 * h + 0]) * 0.70710678118654752f;
-            v[8 * i + 2 * h + 1] = (v[8 * i + 2 * h + 1] + x1 - ds[8 * i + 2 * h + 1]) * 0.70710678118654752f;
-          }
-        }
-      } else {
-        if (p.relu) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
-        }
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] *= p.scale;
+        for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
       }
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] *= p.scale;
       if constexpr (EPI == EPI_OUTF32) {
         if (valid) {
           float* out = reinterpret_cast<float*>(p.out) + row * p.ld_out + n0 + c * 32;

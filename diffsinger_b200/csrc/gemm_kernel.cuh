@@ -10,13 +10,16 @@
 // Accumulators live in TMEM (2 x BN fp32 columns, double buffered) and are drained by 4 epilogue warps
 // (thread <-> frame/TMEM lane) that apply the fused epilogue and write global memory directly.
 //
-// Warp roles (256 threads): warp0 = TMA producer (1 elected lane), warp1 = MMA issuer (1 lane),
-// warp2 = TMEM allocator, warp3 idle, warps4..7 = epilogue.
+// Warp roles (384 threads): warp0 = TMA producer (1 elected lane), warp1 = MMA issuer (1 lane),
+// warp2 = TMEM allocator, warp3 idle, warps4..11 = epilogue (two warps per TMEM lane quadrant).
 #pragma once
 #include <cuda.h>
 #include "ptx.cuh"
 
 namespace dsb {
+
+constexpr int kGemmThreads = 384;  // 4 control warps + 8 epilogue warps (two per TMEM lane quadrant)
+constexpr int kEpiThreads = 256;
 
 enum : int { EPI_LINEAR = 0, EPI_GATE = 1, EPI_RES = 2, EPI_OUTF32 = 3 };
 
@@ -34,8 +37,8 @@ struct GemmParams {
   int relu;
   float scale;
   const float* bias;     // indexed by tile-global n (packed order for EPI_GATE)
-  const float* vec_sub;  // EPI_RES: step embedding of this layer   [vec_bstride * b + n]
-  const float* vec_add;  // step embedding of the NEXT layer (or null)
+  const float* vec_sub;  // unused (kept for ABI stability of the debug hook)
+  const float* vec_add;  // LINEAR: vector added after relu/scale; RES: folded (b - d_l)/sqrt(2) + d_{l+1}
   int vec_bstride;
   const __nv_bfloat16* res_in;  // EPI_RES: x~ of this layer, [B][T][ld_res]
   int ld_res;
@@ -55,10 +58,10 @@ struct GemmCfg {
 };
 
 template <int BN, int EPI>
-__device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t taddr, int b, int t, bool valid, int nt);
+__device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t taddr, int b, int t, bool valid, int nt, int half);
 
 template <int BN, int EPI>
-__global__ void __launch_bounds__(256, 1) ds_gemm_kernel(const __grid_constant__ GemmParams p) {
+__global__ void __launch_bounds__(kGemmThreads, 1) ds_gemm_kernel(const __grid_constant__ GemmParams p) {
   using Cfg = GemmCfg<BN>;
   constexpr int S = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
@@ -88,7 +91,7 @@ __global__ void __launch_bounds__(256, 1) ds_gemm_kernel(const __grid_constant__
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full[i], 1);
-      mbar_init(&tmem_empty[i], 128);
+      mbar_init(&tmem_empty[i], kEpiThreads);
     }
     fence_barrier_init();
   }
@@ -163,8 +166,9 @@ __global__ void __launch_bounds__(256, 1) ds_gemm_kernel(const __grid_constant__
       }
     }
   } else if (warp >= 4) {
-    // -------------------------------------------------------------- epilogue (128 threads)
+    // -------------------------------------------------------------- epilogue (256 threads)
     const int quad = warp & 3;  // TMEM lane quadrant this warp may read
+    const int half = (warp - 4) >> 2;
     int it = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
       const int nt = tile % p.n_tiles;
@@ -176,7 +180,7 @@ __global__ void __launch_bounds__(256, 1) ds_gemm_kernel(const __grid_constant__
       tc_fence_after();
       const int t = tt * 128 + quad * 32 + lane;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * BN;
-      epilogue_tile<BN, EPI>(p, taddr, b, t, t < p.T, nt);
+      epilogue_tile<BN, EPI>(p, taddr, b, t, t < p.T, nt, half);
       tc_fence_before();
       mbar_arrive(&tmem_empty[as]);
     }

