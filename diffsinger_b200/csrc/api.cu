@@ -15,6 +15,7 @@
 #include "gemm_epilogue.cuh"
 #include "layer_kernel.cuh"
 #include "layer2_kernel.cuh"
+#include "layer3_kernel.cuh"
 #include "mma_bench.cuh"
 
 using namespace dsb;
@@ -75,11 +76,11 @@ static int ensure_device() {
 }
 
 // bf16 activation map: dims (channels, T, B), box (64, 128, 1), 128-byte swizzle, OOB -> zeros.
-static int make_act_map(CUtensorMap* m, const void* base, int channels, int T, int B) {
+static int make_act_map(CUtensorMap* m, const void* base, int channels, int T, int B, int box_rows = 128) {
   if (channels % 8) return fail(DS_ERR_INVALID, "activation channel count %d not a multiple of 8", channels);
   cuuint64_t dims[3] = {(cuuint64_t)channels, (cuuint64_t)T, (cuuint64_t)B};
   cuuint64_t strides[2] = {(cuuint64_t)channels * 2, (cuuint64_t)channels * 2 * (cuuint64_t)T};
-  cuuint32_t box[3] = {64, 128, 1};
+  cuuint32_t box[3] = {64, (cuuint32_t)box_rows, 1};
   cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -153,6 +154,19 @@ static int launch_layer_pair(const LayerParams& p, cudaStream_t st) {
   return 0;
 }
 
+static int launch_layer_halo(const LayerParams& p, int max_dil, cudaStream_t st) {
+  static bool attr_done = false;
+  if (!attr_done) {
+    CUDA_TRY(cudaFuncSetAttribute(ds_layer_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kHaloSmemMax));
+    attr_done = true;
+  }
+  const int max_pairs = g_num_sms / 2;
+  const int pairs = p.total_tiles < max_pairs ? p.total_tiles : max_pairs;
+  ds_layer_halo_kernel<<<2 * pairs, kGemmThreads, halo_smem_bytes(max_dil), st>>>(p);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
 static unsigned long long* g_trace = nullptr;
 static int g_trace_cap = 0;
 extern "C" int ds_debug_set_trace(void* dev_buf, int32_t n_entries) {
@@ -175,7 +189,9 @@ struct ds_plan {
   int BN_G, BN_C, BN_O;  // N tile of the gate GEMM / the C-wide GEMMs / the output projection
   int FMr;               // output-projection rows padded to BN_O
   int fused;             // 0: gate GEMM + residual GEMM; 1: one kernel per layer, z kept in smem; 2: one kernel per
-                         // layer, GEMM-2 re-reads z through TMA (4-deep operand ring); 3: as 2 on CTA pairs (cta_group::2)
+                         // layer, GEMM-2 re-reads z through TMA (4-deep operand ring); 3: as 2 on CTA pairs (cta_group::2);
+                         // 4: CTA pairs + halo-carrying activation tiles shared by the three conv taps
+  int max_dil;
   int fused_stages;
   // byte offsets into the packed blob
   size_t o_whead, o_w1, o_w2, o_wsk, o_wsp, o_wout;                 // bf16 matrices
@@ -245,11 +261,16 @@ extern "C" int ds_plan_create(const ds_wavenet_config* cfg, ds_plan** out) {
     int st = (int)((232448 - 1280 - (C / 64) * (int)kLayerABytes) / (int)(kLayerABytes + kLayerBBytes));
     p->fused_stages = st > kLayerMaxStages ? kLayerMaxStages : st;
   }
-  // DSB200_LAYER_MODE = unfused | smem | global | pair.  Default: global (one kernel per layer, single CTA) when
-  // C % 128 == 0.  `pair` (cta_group::2, C % 256 == 0) is functional but measured slower on B200 (profiles/).
+  // DSB200_LAYER_MODE = unfused | smem | global | pair | halo.  Default: halo (CTA pairs, halo-carrying activation tiles)
+  // when C % 256 == 0 and the largest dilation is <= 16; else global (one kernel per layer, single CTA) when
+  // C % 128 == 0; else unfused.  The other modes stay selectable for the parity tests and the A/B numbers in profiles/.
   const char* env = getenv("DSB200_LAYER_MODE");
-  p->fused = (C % 128 == 0) ? 2 : 0;
-  if (env && !strcmp(env, "pair") && C % 256 == 0) p->fused = 3;
+  p->max_dil = 1 << ((cfg->dilation_cycle_length < cfg->num_layers ? cfg->dilation_cycle_length : cfg->num_layers) - 1);
+  const bool can_pair = C % 256 == 0, can_halo = can_pair && p->max_dil <= 16;
+  p->fused = can_halo ? 4 : ((C % 128 == 0) ? 2 : 0);
+  if (env && !strcmp(env, "halo") && can_halo) p->fused = 4;
+  if (env && !strcmp(env, "pair") && can_pair) p->fused = 3;
+  if (env && !strcmp(env, "global") && C % 128 == 0) p->fused = 2;
   if (env && !strcmp(env, "unfused")) p->fused = 0;
   if (env && !strcmp(env, "smem") && p->fused_stages >= 2) p->fused = 1;
   if (p->fused == 2) p->fused_stages = kLayerMaxStages;
@@ -335,6 +356,7 @@ struct ds_session {
   // workspace offsets
   size_t o_cond, o_xb, o_xt, o_xt1, o_z, o_s1, o_s2, o_g, o_d, o_r, o_tmp, ws_bytes;
   CUtensorMap tm_cond, tm_xb, tm_xt, tm_xt1, tm_z, tm_s1, tm_s2;
+  CUtensorMap tm_xh[2][5];  // halo maps of the two x~ buffers, one per dilation 2^k (k < 5)
   cudaStream_t cap_stream = nullptr;
   std::map<std::string, GraphEntry> graphs;
   int64_t last_launches = 0;
@@ -396,6 +418,11 @@ extern "C" int ds_session_create(ds_plan* plan, int32_t B, int32_t T, int32_t ma
   r = r ? r : make_act_map(&s->tm_z, s->ws + s->o_z, plan->L * plan->C, T, B);
   r = r ? r : make_act_map(&s->tm_s1, s->ws + s->o_s1, plan->C, T, B);
   r = r ? r : make_act_map(&s->tm_s2, s->ws + s->o_s2, plan->C, T, B);
+  if (plan->fused == 4)
+    for (int k = 0; (1 << k) <= plan->max_dil; ++k) {
+      r = r ? r : make_act_map(&s->tm_xh[0][k], s->ws + s->o_xt, plan->C, T, B, 128 + 2 * (1 << k));
+      r = r ? r : make_act_map(&s->tm_xh[1][k], s->ws + s->o_xt1, plan->C, T, B, 128 + 2 * (1 << k));
+    }
   if (r) {
     delete s;
     return r;
@@ -442,6 +469,46 @@ extern "C" int ds_session_set_times(ds_session* s, const float* t_dev, int32_t n
   return 0;
 }
 
+// One fused residual layer (modes 1-4): gate GEMM -> gated tile -> residual GEMM in ONE kernel   wavenet.py:33-48
+static int session_fused_layer(ds_session* s, int l, int time_index, cudaStream_t st) {
+  const ds_plan* p = s->plan;
+  const int C = p->C, L = p->L, B = s->B, T = s->T;
+  const uint8_t* pk = p->packed;
+  const int Bt = s->per_sample ? B : 1;
+  const float* rtab = (const float*)(s->ws + s->o_r) + (size_t)time_index * Bt * L * C;
+  const int tiles_t = ceil_div(T, 128);
+  __nv_bfloat16* xts[2] = {(__nv_bfloat16*)(s->ws + s->o_xt), (__nv_bfloat16*)(s->ws + s->o_xt1)};
+  LayerParams lp;
+  memset(&lp, 0, sizeof(lp));
+  lp.tmCond = s->tm_cond; lp.tmW1 = p->tm_w1; lp.tmW2 = p->tm_w2; lp.tmZ = s->tm_z;
+  lp.T = T; lp.B = B; lp.tiles_t = tiles_t; lp.total_tiles = B * tiles_t;
+  lp.kb_c = C / 64; lp.kb_h = p->H / 64; lp.p1 = 2 * C / 256; lp.stages = p->fused_stages;
+  lp.vec_bstride = s->per_sample ? L * C : 0; lp.z_out = (__nv_bfloat16*)(s->ws + s->o_z); lp.ld_z = L * C;
+  lp.trace = g_trace; lp.trace_cap = g_trace_cap;
+  { const char* de = getenv("DSB200_DBG"); lp.dbg = de ? atoi(de) : 0; }
+  const bool pair = p->fused >= 3;
+  lp.a_slot = halo_a_slot_bytes(p->max_dil); lp.n_a = halo_n_a(p->max_dil);
+  if (pair) {
+    lp.tmW1 = p->tm_w1h; lp.tmW2 = p->tm_w2h;
+    lp.tiles_t = ceil_div(tiles_t, 2); lp.total_tiles = B * lp.tiles_t;
+  }
+  lp.tmX = (l & 1) ? s->tm_xt1 : s->tm_xt;
+  lp.x_in = xts[l & 1]; lp.x_out = xts[(l + 1) & 1];
+  lp.dil = 1 << (l % p->cfg.dilation_cycle_length);
+  lp.p2 = (l + 1 < L) ? C / p->BN_C : 0;  // the last layer's residual is never used (wavenet.py:92-94)
+  lp.w1_row0 = l * 2 * C; lp.w2_row0 = l * C;
+  lp.bias1 = (const float*)(pk + p->o_b1) + (size_t)l * 2 * C;
+  lp.rvec = rtab + (size_t)l * C;
+  lp.z_c0 = l * C;
+  if (p->fused == 4) {
+    lp.tmXh = s->tm_xh[l & 1][l % p->cfg.dilation_cycle_length];
+    return launch_layer_halo(lp, p->max_dil, st);
+  }
+  if (pair) return launch_layer_pair(lp, st);
+  if (p->fused == 1) return p->BN_C == 256 ? launch_layer_t<256, true>(lp, st) : launch_layer_t<128, true>(lp, st);
+  return p->BN_C == 256 ? launch_layer_t<256, false>(lp, st) : launch_layer_t<128, false>(lp, st);
+}
+
 // One backbone evaluation = 2L+4 launches on `st` (WaveNet.forward, wavenet.py:75-107).
 static int session_eval(ds_session* s, const float* x, int time_index, float* out, cudaStream_t st, int64_t* launches) {
   const ds_plan* p = s->plan;
@@ -479,33 +546,8 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   DS_TRY(launch_gemm(p->BN_C, EPI_LINEAR, g, st));
   ++*launches;
   if (p->fused) {
-    // one kernel per residual layer: gate GEMM -> gated tile in shared memory -> residual GEMM   wavenet.py:33-48
-    __nv_bfloat16* xts[2] = {xt, (__nv_bfloat16*)(s->ws + s->o_xt1)};
-    LayerParams lp;
-    memset(&lp, 0, sizeof(lp));
-    lp.tmCond = s->tm_cond; lp.tmW1 = p->tm_w1; lp.tmW2 = p->tm_w2; lp.tmZ = s->tm_z;
-    lp.T = T; lp.B = B; lp.tiles_t = tiles_t; lp.total_tiles = B * tiles_t;
-    lp.kb_c = C / 64; lp.kb_h = p->H / 64; lp.p1 = 2 * C / 256; lp.stages = p->fused_stages;
-    lp.vec_bstride = vstride; lp.z_out = z; lp.ld_z = L * C;
-    lp.trace = g_trace; lp.trace_cap = g_trace_cap;
-    { const char* de = getenv("DSB200_DBG"); lp.dbg = de ? atoi(de) : 0; }
-    const bool pair = p->fused == 3;
-    if (pair) {
-      lp.tmW1 = p->tm_w1h; lp.tmW2 = p->tm_w2h;
-      lp.tiles_t = ceil_div(tiles_t, 2); lp.total_tiles = B * lp.tiles_t;
-    }
     for (int l = 0; l < L; ++l) {
-      lp.tmX = (l & 1) ? s->tm_xt1 : s->tm_xt;
-      lp.x_in = xts[l & 1]; lp.x_out = xts[(l + 1) & 1];
-      lp.dil = 1 << (l % p->cfg.dilation_cycle_length);
-      lp.p2 = (l + 1 < L) ? C / p->BN_C : 0;  // the last layer's residual is never used (wavenet.py:92-94)
-      lp.w1_row0 = l * 2 * C; lp.w2_row0 = l * C;
-      lp.bias1 = (const float*)(pk + p->o_b1) + (size_t)l * 2 * C;
-      lp.rvec = rtab + (size_t)l * C;
-      lp.z_c0 = l * C;
-      if (pair) DS_TRY(launch_layer_pair(lp, st));
-      else if (p->fused == 1) DS_TRY(p->BN_C == 256 ? (launch_layer_t<256, true>(lp, st)) : (launch_layer_t<128, true>(lp, st)));
-      else DS_TRY(p->BN_C == 256 ? (launch_layer_t<256, false>(lp, st)) : (launch_layer_t<128, false>(lp, st)));
+      DS_TRY(session_fused_layer(s, l, time_index, st));
       ++*launches;
     }
   } else {
@@ -679,6 +721,17 @@ extern "C" int ds_debug_gemm(const ds_gemm_desc* d, void* stream) {
   g.out = d->out; g.ld_out = d->ld_out; g.out_c0 = d->out_c0; g.n_real = d->n_real;
   return launch_gemm(d->BN, d->epi, g, (cudaStream_t)stream);
 }
+
+// Debug / bench: launch ONLY the fused kernel of residual layer `layer` on the session's current activation buffers
+// (whatever the last evaluation left there), for per-kernel CUDA-event timing.
+extern "C" int ds_debug_layer(ds_session* s, int32_t layer, int32_t time_index, void* stream) {
+  if (!s) return fail(DS_ERR_INVALID, "null argument");
+  if (!s->plan->fused) return fail(DS_ERR_STATE, "the plan runs the unfused two-GEMM layer path");
+  if (layer < 0 || layer >= s->plan->L) return fail(DS_ERR_INVALID, "layer %d out of range", layer);
+  DS_TRY(check_eval_ready(s, time_index));
+  return session_fused_layer(s, layer, time_index, (cudaStream_t)stream);
+}
+extern "C" int ds_plan_layer_mode(const ds_plan* plan) { return plan ? plan->fused : -1; }
 
 // Debug: raw tensor-pipe rate.  out: 2*grid int64 device words {issue cycles, issue+drain cycles} per CTA.
 extern "C" int ds_debug_mma_rate(int32_t pair, int32_t grid, int32_t n_mma, int32_t commit_every, long long* out_dev, void* stream) {

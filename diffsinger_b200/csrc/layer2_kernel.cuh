@@ -72,6 +72,11 @@ ds_layer_pair_kernel(const __grid_constant__ LayerParams p) {
   const int n_pairs = gridDim.x >> 1;
   const int n_local = (p.total_tiles > pair_id) ? (p.total_tiles - 1 - pair_id) / n_pairs + 1 : 0;
   const bool tracing = p.trace != nullptr && blockIdx.x == 0 && p.p2 > 0;
+  // De-synchronise the pairs: every pair walks the K blocks (and the passes) in its own rotated order, so that at any
+  // instant the chip reads many different weight blocks instead of all SMs hitting the same few L2 slices.
+  const int prot = (p.dbg & 8) ? 0 : pair_id % p.p1;
+  const int krot1 = (p.dbg & 4) ? 0 : (pair_id / p.p1 * 5) % kb1;
+  const int krot2 = (p.dbg & 4) ? 0 : pair_id % p.kb_c;
 
   if (warp == 0) {
     if (lane == 0) {
@@ -85,31 +90,37 @@ ds_layer_pair_kernel(const __grid_constant__ LayerParams p) {
         const int t0 = (tile % p.tiles_t) * 256 + rank * 128;
         const int b = tile / p.tiles_t;
         const int nkb = kind == 0 ? kb1 : p.kb_c;
-        const int row0 = (kind == 0 ? p.w1_row0 + idx * 256 : p.w2_row0 + idx * 256) + rank * 128;
+        const int pidx = kind == 0 ? (idx + prot) % p.p1 : idx;
+        const int row0 = (kind == 0 ? p.w1_row0 + pidx * 256 : p.w2_row0 + idx * 256) + rank * 128;
         if (kind == 1 && idx == 0) mbar_wait(z_full, j & 1);  // this CTA's z rows of tile j are in global memory
-        for (int kb = 0; kb < nkb; ++kb) {
+        for (int ki = 0; ki < nkb; ++ki) {
+          int kb = ki + (kind == 0 ? krot1 : krot2);
+          if (kb >= nkb) kb -= nkb;
           mbar_wait(&empty[stage], phase ^ 1);
           if (p.dbg & 2) {
             if (leader) mbar_arrive(&full[stage]); else mbar_arrive_cluster(&full[stage], 0);
             if (++stage == S) { stage = 0; phase ^= 1; }
             continue;
           }
-          if (leader) mbar_arrive_expect_tx(&full[stage], 2 * (kLayerABytes + kPairBBytes));
+          const bool ldA = !(p.dbg & 16), ldB = !(p.dbg & 32);
+          if (leader) mbar_arrive_expect_tx(&full[stage], 2 * ((ldA ? kLayerABytes : 0u) + (ldB ? kPairBBytes : 0u)));
           else mbar_arrive_cluster(&full[stage], 0);
           uint8_t* sa = smem_a + stage * kLayerABytes;
           uint8_t* sb = smem_b + stage * kPairBBytes;
           if (kind == 0) {
-            if (kb < kb_taps) {
-              const int tap = kb / p.kb_c;
-              const int cb = kb - tap * p.kb_c;
-              tma_load_3d_pair(&p.tmX, &full[stage], sa, cb * 64, t0 + (tap - 1) * p.dil, b);
-            } else {
-              tma_load_3d_pair(&p.tmCond, &full[stage], sa, (kb - kb_taps) * 64, t0, b);
+            if (ldA) {
+              if (kb < kb_taps) {
+                const int tap = kb / p.kb_c;
+                const int cb = kb - tap * p.kb_c;
+                tma_load_3d_pair(&p.tmX, &full[stage], sa, cb * 64, t0 + (tap - 1) * p.dil, b);
+              } else {
+                tma_load_3d_pair(&p.tmCond, &full[stage], sa, (kb - kb_taps) * 64, t0, b);
+              }
             }
-            tma_load_2d_pair(&p.tmW1, &full[stage], sb, kb * 64, row0);
+            if (ldB) tma_load_2d_pair(&p.tmW1, &full[stage], sb, kb * 64, row0);
           } else {
-            tma_load_3d_pair(&p.tmZ, &full[stage], sa, p.z_c0 + kb * 64, t0, b);
-            tma_load_2d_pair(&p.tmW2, &full[stage], sb, kb * 64, row0);
+            if (ldA) tma_load_3d_pair(&p.tmZ, &full[stage], sa, p.z_c0 + kb * 64, t0, b);
+            if (ldB) tma_load_2d_pair(&p.tmW2, &full[stage], sb, kb * 64, row0);
           }
           if (++stage == S) { stage = 0; phase ^= 1; }
         }
@@ -174,8 +185,9 @@ ds_layer_pair_kernel(const __grid_constant__ LayerParams p) {
       const uint32_t taddr = lane_addr + as * 256;
       if (p.dbg & 1) {
       } else if (kind == 0) {
-        const float* bias = p.bias1 + idx * 256;
-        __nv_bfloat16* zg = p.z_out + row * p.ld_z + p.z_c0 + idx * 128;
+        const int pidx = (idx + prot) % p.p1;
+        const float* bias = p.bias1 + pidx * 256;
+        __nv_bfloat16* zg = p.z_out + row * p.ld_z + p.z_c0 + pidx * 128;
 #pragma unroll 1
         for (int c = half; c < 4; c += 2) {
           uint32_t g[32], f[32];

@@ -37,6 +37,10 @@ struct LayerParams {
   unsigned long long* trace;  // optional: CTA 0 records {role*16 + kind, local tile*16 + idx, t0, t1} (debug)
   int trace_cap;
   int dbg;  // debug: bit0 = epilogue warps skip all work, bit1 = producer skips the TMA loads (barriers only)
+  // halo variant (layer3_kernel.cuh): x_in map with a (64 x (128 + 2*dil) x 1) box, A ring geometry
+  CUtensorMap tmXh;
+  uint32_t a_slot;
+  int n_a;
 };
 
 constexpr uint32_t kLayerABytes = 128 * 128;  // 128 frames x 64 bf16
@@ -143,6 +147,11 @@ __global__ void __launch_bounds__(kGemmThreads, 1) ds_layer_kernel(const __grid_
   const int n_local = (p.total_tiles > static_cast<int>(blockIdx.x))
                           ? (p.total_tiles - 1 - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x) + 1 : 0;
   const bool tracing = p.trace != nullptr && blockIdx.x == 0 && p.p2 > 0;
+  // De-synchronise the CTAs: each walks the K blocks (and the passes) in its own rotated order, so that at any instant
+  // the chip reads many different weight blocks instead of all SMs hitting the same few L2 slices.
+  const int prot = (p.dbg & 8) ? 0 : static_cast<int>(blockIdx.x) % p.p1;
+  const int krot1 = (p.dbg & 4) ? 0 : (static_cast<int>(blockIdx.x) / p.p1 * 5) % kb1;
+  const int krot2 = (p.dbg & 4) ? 0 : static_cast<int>(blockIdx.x) % p.kb_c;
 
   if (warp == 0) {
     if (lane == 0) {
@@ -156,8 +165,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) ds_layer_kernel(const __grid_
         const int t0 = (tile % p.tiles_t) * 128;
         const int b = tile / p.tiles_t;
         if (kind == 0) {
-          const int row0 = p.w1_row0 + idx * 256;
-          for (int kb = 0; kb < kb1; ++kb) {
+          const int row0 = p.w1_row0 + ((idx + prot) % p.p1) * 256;
+          for (int ki = 0; ki < kb1; ++ki) {
+            int kb = ki + krot1;
+            if (kb >= kb1) kb -= kb1;
             mbar_wait(&empty[stage], phase ^ 1);
             if (p.dbg & 2) { mbar_arrive(&full[stage]); if (++stage == S) { stage = 0; phase ^= 1; } continue; }
             mbar_arrive_expect_tx(&full[stage], kLayerABytes + kLayerBBytes);
@@ -175,7 +186,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) ds_layer_kernel(const __grid_
         } else {
           if (!kZSmem && idx == 0) mbar_wait(z_full, j & 1);  // tile j's z has been published to global memory
           const int row0 = p.w2_row0 + idx * BN2;
-          for (int kb = 0; kb < p.kb_c; ++kb) {
+          for (int ki = 0; ki < p.kb_c; ++ki) {
+            int kb = ki + krot2;
+            if (kb >= p.kb_c) kb -= p.kb_c;
             mbar_wait(&empty[stage], phase ^ 1);
             if (p.dbg & 2) { mbar_arrive(&full[stage]); if (++stage == S) { stage = 0; phase ^= 1; } continue; }
             mbar_arrive_expect_tx(&full[stage], BN2 * 128 + (kZSmem ? 0u : kLayerABytes));
@@ -212,7 +225,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) ds_layer_kernel(const __grid_
         for (int kb = 0; kb < nkb; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
-          const uint8_t* a_src = (kZSmem && kind == 1) ? smem_z + kb * kLayerABytes : smem_a + stage * kLayerABytes;
+          const uint8_t* a_src = (kZSmem && kind == 1) ? smem_z + ((kb + krot2) % p.kb_c) * kLayerABytes : smem_a + stage * kLayerABytes;
           const uint64_t da = make_kmajor_sw128_desc(smem_u32(a_src));
           const uint64_t db = make_kmajor_sw128_desc(smem_u32(smem_b + stage * kLayerBBytes));
           if (kind == 0) {
@@ -260,8 +273,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) ds_layer_kernel(const __grid_
         mbar_arrive(&tmem_empty[as]);
         if (kind == 0 && idx == p.p1 - 1 && p.p2 > 0) mbar_arrive(z_full);
       } else if (kind == 0) {
-        const float* bias = p.bias1 + idx * 256;
-        __nv_bfloat16* zg = p.z_out + row * p.ld_z + p.z_c0 + idx * 128;
+        const int pidx = (idx + prot) % p.p1;
+        const float* bias = p.bias1 + pidx * 256;
+        __nv_bfloat16* zg = p.z_out + row * p.ld_z + p.z_c0 + pidx * 128;
 #pragma unroll 1
         for (int c = half; c < 4; c += 2) {
           uint32_t g[32], f[32];
@@ -285,7 +299,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) ds_layer_kernel(const __grid_
           }
           if (kZSmem && p.p2 > 0) {
             // K-major SWIZZLE_128B: block = 64 channels, row pitch 128 B, 16-B piece q -> q ^ (row & 7)
-            uint8_t* blk = smem_z + (idx * 2 + (c >> 1)) * kLayerABytes + r * 128;
+            uint8_t* blk = smem_z + (pidx * 2 + (c >> 1)) * kLayerABytes + r * 128;
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
               const int q = (c & 1) * 4 + i;

@@ -126,7 +126,10 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t cta)
   asm volatile(
       "{\n\t.reg .b32 ra;\n\t"
       "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
-      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}\n"
+      // default (.release.cta) semantics on purpose: a cluster-scope release makes ptxas emit MEMBAR.ALL.GPU before
+      // every remote arrive (~1 us each).  The arrivals sent this way order only async-proxy work (TMA bytes are
+      // counted by the barrier itself; TMEM reads are closed by tcgen05.wait::ld + fence::before_thread_sync).
+      "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}\n"
       ::"r"(smem_u32(bar)), "r"(cta)
       : "memory");
 }

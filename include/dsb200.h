@@ -142,6 +142,11 @@ int ds_debug_gemm(const ds_gemm_desc* d, void* stream);
 /* Debug: device buffer of n_entries x 4 uint64 into which CTA 0 of every fused-layer launch records
  * {role*16+kind, tile*16+idx, t0_ns, t1_ns} (first half: MMA issuer, second half: epilogue). NULL disables. */
 int ds_debug_set_trace(void* dev_buf, int32_t n_entries);
+/* Debug / bench: launch ONLY the fused kernel of residual layer `layer` (ResidualBlock.forward, wavenet.py:33-48) on the
+ * session's current activation buffers -- the per-kernel timing hook bench.py's roofline uses. */
+int ds_debug_layer(ds_session* s, int32_t layer, int32_t time_index, void* stream);
+/* 0 unfused (two GEMM launches per layer), 1 smem-z, 2 global-z, 3 CTA pair, 4 CTA pair + halo tiles (csrc/api.cu). */
+int ds_plan_layer_mode(const ds_plan* plan);
 /* Debug: raw tcgen05.mma rate micro-benchmark (csrc/mma_bench.cuh). */
 int ds_debug_mma_rate(int32_t pair, int32_t grid, int32_t n_mma, int32_t commit_every, long long* out_dev, void* stream);
 

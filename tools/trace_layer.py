@@ -8,7 +8,7 @@ import diffsinger_b200 as ds  # noqa: E402
 from diffsinger_b200 import _native as nat  # noqa: E402
 from oracle.wavenet_oracle import random_state_dict  # noqa: E402
 
-B, T, C, L = 64, 2000, 512, 2
+B, T, C, L = int(os.environ.get("PB", 64)), 2000, 512, 2
 ds.hparams.update(hidden_size=256)
 net = ds.WaveNet(128, 1, num_layers=L, num_channels=C, dilation_cycle_length=4)
 net.load_state_dict(random_state_dict(128, 1, L, C, 256, seed=1))
