@@ -8,6 +8,7 @@ expressed with differentiable torch ops on the same device -- that branch exists
 and is never taken by the samplers.
 """
 import math
+import os
 
 import torch
 import torch.nn as nn
@@ -81,6 +82,18 @@ class WaveNet(nn.Module):
         self.output_projection = _kaiming_conv1x1(num_channels, in_dims * n_feats)
         nn.init.zeros_(self.output_projection.weight)
         self._engine = None  # native plan, created lazily on the module's CUDA device
+        # 'bf16' (default; final mel rel-L2 <= 1e-2) or 'fp32' (3 x bf16 split products; per-evaluation rel-L2 <= 1e-4)
+        self.precision = os.environ.get('DSB200_PRECISION', 'bf16')
+
+    def set_precision(self, precision: str):
+        """Select the arithmetic of the native path; drops the plan so that weights are repacked."""
+        if precision not in ('bf16', 'fp32'):
+            raise ValueError(f"precision must be 'bf16' or 'fp32', got {precision!r}")
+        if precision != self.precision and self._engine is not None:
+            self._engine.close()
+            self._engine = None
+        self.precision = precision
+        return self
 
     # ------------------------------------------------------------------ native engine plumbing
     def __deepcopy__(self, memo):
@@ -105,7 +118,7 @@ class WaveNet(nn.Module):
             raise RuntimeError(
                 "diffsinger_b200.WaveNet has no CPU inference path: move the module to a B200 "
                 "(sm_100a) device; the torch-op branch is for autograd only.")
-        if self._engine is None or self._engine.device != dev:
+        if self._engine is None or self._engine.device != dev or self._engine.precision != self.precision:
             if self._engine is not None:
                 self._engine.close()
             self._engine = WaveNetEngine(self, dev)

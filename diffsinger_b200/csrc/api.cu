@@ -102,10 +102,10 @@ static int make_weight_map(CUtensorMap* m, const void* base, int K, int rows, in
 }
 
 // ------------------------------------------------------------------------------------ GEMM launch
-template <int BN, int EPI>
+template <int BN, int EPI, bool kSplit>
 static int launch_gemm_t(const GemmParams& p, cudaStream_t st) {
   static bool attr_done = false;
-  auto kern = ds_gemm_kernel<BN, EPI>;
+  auto kern = ds_gemm_kernel<BN, EPI, kSplit>;
   if (!attr_done) {
     CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GemmCfg<BN>::kSmemBytes));
     attr_done = true;
@@ -116,9 +116,9 @@ static int launch_gemm_t(const GemmParams& p, cudaStream_t st) {
   return 0;
 }
 
-static int launch_gemm(int BN, int epi, const GemmParams& p, cudaStream_t st) {
+static int launch_gemm(int BN, int epi, const GemmParams& p, cudaStream_t st, bool split = false) {
 #define DS_CASE(bn, e) \
-  if (BN == bn && epi == e) return launch_gemm_t<bn, e>(p, st);
+  if (BN == bn && epi == e) return split ? launch_gemm_t<bn, e, true>(p, st) : launch_gemm_t<bn, e, false>(p, st);
   DS_CASE(64, EPI_LINEAR) DS_CASE(128, EPI_LINEAR) DS_CASE(256, EPI_LINEAR)
   DS_CASE(128, EPI_GATE) DS_CASE(256, EPI_GATE)
   DS_CASE(64, EPI_RES) DS_CASE(128, EPI_RES) DS_CASE(256, EPI_RES)
@@ -193,6 +193,8 @@ struct ds_plan {
                          // 4: CTA pairs + halo-carrying activation tiles shared by the three conv taps
   int max_dil;
   int fused_stages;
+  int split;             // fp32-accurate mode: every bf16 operand carries a lo half (3 x bf16 split products)
+  int S;                 // 2 when split, else 1: width multiplier of every bf16 matrix / activation buffer
   // byte offsets into the packed blob
   size_t o_whead, o_w1, o_w2, o_wsk, o_wsp, o_wout;                 // bf16 matrices
   size_t o_bhead, o_b1, o_b2, o_bsk, o_bsp, o_bout;                 // fp32 biases
@@ -213,12 +215,13 @@ static void plan_layout(ds_plan* p) {
     return o;
   };
   const size_t Cr = align_up(C, p->BN_C);  // == C
-  p->o_whead = take(Cr * p->FMp * 2);
-  p->o_w1 = take(L * 2 * C * p->K1 * 2);
-  p->o_w2 = take(L * C * C * 2);
-  p->o_wsk = take(C * L * C * 2);
-  p->o_wsp = take(C * C * 2);
-  p->o_wout = take((size_t)p->FMr * C * 2);
+  const size_t S = p->S;
+  p->o_whead = take(Cr * p->FMp * 2 * S);
+  p->o_w1 = take(L * 2 * C * p->K1 * 2 * S);
+  p->o_w2 = take(L * C * C * 2 * S);
+  p->o_wsk = take(C * L * C * 2 * S);
+  p->o_wsp = take(C * C * 2 * S);
+  p->o_wout = take((size_t)p->FMr * C * 2 * S);
   p->o_bhead = take(C * 4);
   p->o_b1 = take(L * 2 * C * 4);
   p->o_b2 = take(L * C * 4);
@@ -274,6 +277,16 @@ extern "C" int ds_plan_create(const ds_wavenet_config* cfg, ds_plan** out) {
   if (env && !strcmp(env, "unfused")) p->fused = 0;
   if (env && !strcmp(env, "smem") && p->fused_stages >= 2) p->fused = 1;
   if (p->fused == 2) p->fused_stages = kLayerMaxStages;
+  // precision 1 = fp32-accurate: 3 x bf16 split products on the unfused GEMM path (per-evaluation rel-L2 <= 1e-4 against
+  // the fp32 reference; tcgen05 has no fp32 MMA and one-pass TF32 gives ~6e-4).  DSB200_PRECISION=fp32 forces it.
+  const char* pe = getenv("DSB200_PRECISION");
+  p->split = (cfg->precision == 1 || (pe && !strcmp(pe, "fp32"))) ? 1 : 0;
+  if (cfg->precision != 0 && cfg->precision != 1) {
+    delete p;
+    return fail(DS_ERR_INVALID, "precision=%d must be 0 (bf16) or 1 (fp32-accurate)", cfg->precision);
+  }
+  p->S = p->split ? 2 : 1;
+  if (p->split) p->fused = 0;
   plan_layout(p);
   *out = p;
   return 0;
@@ -297,12 +310,14 @@ extern "C" int ds_plan_pack_weights(ds_plan* p, const ds_wavenet_weights* w, voi
   auto bf = [&](size_t o) { return (__nv_bfloat16*)(base + o); };
   auto f32 = [&](size_t o) { return (float*)(base + o); };
   const int TH = 256;
+  const long S = p->S;  // split mode: every matrix row is [hi (K) | lo (K)]
+  auto lo = [&](long k) { return p->split ? k : 0L; };
   // head: input_projection.weight [C, FM, 1] -> [C][FMp]
-  pack_matrix_kernel<<<ew_grid((long)C * p->FMp, TH), TH, 0, st>>>(bf(p->o_whead), C, p->FMp, p->FMp, w->input_projection_weight, C, FM, FM, 1);
+  pack_matrix_kernel<<<ew_grid((long)C * p->FMp, TH), TH, 0, st>>>(bf(p->o_whead), C, p->FMp, p->FMp * S, w->input_projection_weight, C, FM, FM, 1, lo(p->FMp));
   // skip_projection [C, C, 1]
-  pack_matrix_kernel<<<ew_grid((long)C * C, TH), TH, 0, st>>>(bf(p->o_wsp), C, C, C, w->skip_projection_weight, C, C, C, 1);
+  pack_matrix_kernel<<<ew_grid((long)C * C, TH), TH, 0, st>>>(bf(p->o_wsp), C, C, C * S, w->skip_projection_weight, C, C, C, 1, lo(C));
   // output_projection [FM, C, 1] -> [FMr][C] (zero rows beyond FM)
-  pack_matrix_kernel<<<ew_grid((long)p->FMr * C, TH), TH, 0, st>>>(bf(p->o_wout), p->FMr, C, C, w->output_projection_weight, FM, C, C, 1);
+  pack_matrix_kernel<<<ew_grid((long)p->FMr * C, TH), TH, 0, st>>>(bf(p->o_wout), p->FMr, C, C * S, w->output_projection_weight, FM, C, C, 1, lo(C));
   CUDA_TRY(cudaMemsetAsync(f32(p->o_bout), 0, (size_t)p->FMr * 4, st));
   CUDA_TRY(cudaMemcpyAsync(f32(p->o_bout), w->output_projection_bias, (size_t)FM * 4, cudaMemcpyDeviceToDevice, st));
   CUDA_TRY(cudaMemcpyAsync(f32(p->o_bhead), w->input_projection_bias, (size_t)C * 4, cudaMemcpyDeviceToDevice, st));
@@ -315,14 +330,14 @@ extern "C" int ds_plan_pack_weights(ds_plan* p, const ds_wavenet_weights* w, voi
   CUDA_TRY(cudaMemsetAsync(f32(p->o_bsk), 0, (size_t)C * 4, st));
   for (int l = 0; l < L; ++l) {
     pack_gate_kernel<<<ew_grid((long)2 * C * p->K1, TH), TH, 0, st>>>(
-        bf(p->o_w1) + (size_t)l * 2 * C * p->K1, f32(p->o_b1) + (size_t)l * 2 * C, w->dilated_conv_weight[l], w->dilated_conv_bias[l],
-        w->conditioner_projection_weight[l], w->conditioner_projection_bias[l], C, H, p->BN_G);
+        bf(p->o_w1) + (size_t)l * 2 * C * p->K1 * S, f32(p->o_b1) + (size_t)l * 2 * C, w->dilated_conv_weight[l], w->dilated_conv_bias[l],
+        w->conditioner_projection_weight[l], w->conditioner_projection_bias[l], C, H, p->BN_G, (long)p->K1 * S, lo(p->K1));
     // residual half: rows [0, C) of output_projection [2C, C, 1]
-    pack_matrix_kernel<<<ew_grid((long)C * C, TH), TH, 0, st>>>(bf(p->o_w2) + (size_t)l * C * C, C, C, C, w->layer_output_projection_weight[l], C, C, C, 1);
+    pack_matrix_kernel<<<ew_grid((long)C * C, TH), TH, 0, st>>>(bf(p->o_w2) + (size_t)l * C * C * S, C, C, C * S, w->layer_output_projection_weight[l], C, C, C, 1, lo(C));
     CUDA_TRY(cudaMemcpyAsync(f32(p->o_b2) + (size_t)l * C, w->layer_output_projection_bias[l], (size_t)C * 4, cudaMemcpyDeviceToDevice, st));
     // skip half: rows [C, 2C) -> columns [l*C, (l+1)*C) of the [C][L*C] deferred-skip matrix
-    pack_matrix_kernel<<<ew_grid((long)C * C, TH), TH, 0, st>>>(bf(p->o_wsk) + (size_t)l * C, C, C, (long)L * C,
-                                                                w->layer_output_projection_weight[l] + (size_t)C * C, C, C, C, 1);
+    pack_matrix_kernel<<<ew_grid((long)C * C, TH), TH, 0, st>>>(bf(p->o_wsk) + (size_t)l * C, C, C, (long)L * C * S,
+                                                                w->layer_output_projection_weight[l] + (size_t)C * C, C, C, C, 1, lo((long)L * C));
     accum_kernel<<<ceil_div(C, TH), TH, 0, st>>>(f32(p->o_bsk), w->layer_output_projection_bias[l] + C, C);
     CUDA_TRY(cudaMemcpyAsync(f32(p->o_wd) + (size_t)l * C * C, w->diffusion_projection_weight[l], (size_t)C * C * 4, cudaMemcpyDeviceToDevice, st));
     CUDA_TRY(cudaMemcpyAsync(f32(p->o_bd) + (size_t)l * C, w->diffusion_projection_bias[l], (size_t)C * 4, cudaMemcpyDeviceToDevice, st));
@@ -330,14 +345,15 @@ extern "C" int ds_plan_pack_weights(ds_plan* p, const ds_wavenet_weights* w, voi
   CUDA_TRY(cudaGetLastError());
   p->packed = base;
   // weight tensor maps (K-major bf16, box 64 x BN)
-  DS_TRY(make_weight_map(&p->tm_whead, base + p->o_whead, p->FMp, C, p->BN_C));
-  DS_TRY(make_weight_map(&p->tm_w1, base + p->o_w1, p->K1, L * 2 * C, p->BN_G));
-  DS_TRY(make_weight_map(&p->tm_w2, base + p->o_w2, C, L * C, p->BN_C));
-  DS_TRY(make_weight_map(&p->tm_w1h, base + p->o_w1, p->K1, L * 2 * C, 128));
-  DS_TRY(make_weight_map(&p->tm_w2h, base + p->o_w2, C, L * C, 128));
-  DS_TRY(make_weight_map(&p->tm_wsk, base + p->o_wsk, L * C, C, p->BN_C));
-  DS_TRY(make_weight_map(&p->tm_wsp, base + p->o_wsp, C, C, p->BN_C));
-  DS_TRY(make_weight_map(&p->tm_wout, base + p->o_wout, C, p->FMr, p->BN_O));
+  const int Sm = p->S;
+  DS_TRY(make_weight_map(&p->tm_whead, base + p->o_whead, p->FMp * Sm, C, p->BN_C));
+  DS_TRY(make_weight_map(&p->tm_w1, base + p->o_w1, p->K1 * Sm, L * 2 * C, p->BN_G));
+  DS_TRY(make_weight_map(&p->tm_w2, base + p->o_w2, C * Sm, L * C, p->BN_C));
+  DS_TRY(make_weight_map(&p->tm_w1h, base + p->o_w1, p->K1 * Sm, L * 2 * C, 128));
+  DS_TRY(make_weight_map(&p->tm_w2h, base + p->o_w2, C * Sm, L * C, 128));
+  DS_TRY(make_weight_map(&p->tm_wsk, base + p->o_wsk, L * C * Sm, C, p->BN_C));
+  DS_TRY(make_weight_map(&p->tm_wsp, base + p->o_wsp, C * Sm, C, p->BN_C));
+  DS_TRY(make_weight_map(&p->tm_wout, base + p->o_wout, C * Sm, p->FMr, p->BN_O));
   p->packed_ok = true;
   return 0;
 }
@@ -372,13 +388,14 @@ static void session_layout(const ds_plan* p, int B, int T, int max_times, int pe
     off = align_up(off + bytes, 1024);
     return o;
   };
-  s->o_cond = take(rows * p->H * 2);
-  s->o_xb = take(rows * p->FMp * 2);
-  s->o_xt = take(rows * C * 2);
-  s->o_xt1 = take(rows * C * 2);
-  s->o_z = take(rows * L * C * 2);
-  s->o_s1 = take(rows * C * 2);
-  s->o_s2 = take(rows * C * 2);
+  const size_t S = p->S;  // split mode: [hi | lo] halves per row
+  s->o_cond = take(rows * p->H * 2 * S);
+  s->o_xb = take(rows * p->FMp * 2 * S);
+  s->o_xt = take(rows * C * 2 * S);
+  s->o_xt1 = take(rows * C * 2 * S);
+  s->o_z = take(rows * L * C * 2 * S);
+  s->o_s1 = take(rows * C * 2 * S);
+  s->o_s2 = take(rows * C * 2 * S);
   const size_t nt = (size_t)max_times * (per_sample ? B : 1);
   s->o_g = take(nt * C * 4);
   s->o_d = take(nt * L * C * 4);
@@ -411,13 +428,14 @@ extern "C" int ds_session_create(ds_plan* plan, int32_t B, int32_t T, int32_t ma
   }
   s->ws = (uint8_t*)workspace;
   int r = 0;
-  r = r ? r : make_act_map(&s->tm_cond, s->ws + s->o_cond, plan->H, T, B);
-  r = r ? r : make_act_map(&s->tm_xb, s->ws + s->o_xb, plan->FMp, T, B);
-  r = r ? r : make_act_map(&s->tm_xt, s->ws + s->o_xt, plan->C, T, B);
-  r = r ? r : make_act_map(&s->tm_xt1, s->ws + s->o_xt1, plan->C, T, B);
-  r = r ? r : make_act_map(&s->tm_z, s->ws + s->o_z, plan->L * plan->C, T, B);
-  r = r ? r : make_act_map(&s->tm_s1, s->ws + s->o_s1, plan->C, T, B);
-  r = r ? r : make_act_map(&s->tm_s2, s->ws + s->o_s2, plan->C, T, B);
+  const int Sm = plan->S;
+  r = r ? r : make_act_map(&s->tm_cond, s->ws + s->o_cond, plan->H * Sm, T, B);
+  r = r ? r : make_act_map(&s->tm_xb, s->ws + s->o_xb, plan->FMp * Sm, T, B);
+  r = r ? r : make_act_map(&s->tm_xt, s->ws + s->o_xt, plan->C * Sm, T, B);
+  r = r ? r : make_act_map(&s->tm_xt1, s->ws + s->o_xt1, plan->C * Sm, T, B);
+  r = r ? r : make_act_map(&s->tm_z, s->ws + s->o_z, plan->L * plan->C * Sm, T, B);
+  r = r ? r : make_act_map(&s->tm_s1, s->ws + s->o_s1, plan->C * Sm, T, B);
+  r = r ? r : make_act_map(&s->tm_s2, s->ws + s->o_s2, plan->C * Sm, T, B);
   if (plan->fused == 4)
     for (int k = 0; (1 << k) <= plan->max_dil; ++k) {
       r = r ? r : make_act_map(&s->tm_xh[0][k], s->ws + s->o_xt, plan->C, T, B, 128 + 2 * (1 << k));
@@ -444,7 +462,8 @@ extern "C" int ds_session_set_cond(ds_session* s, const float* cond_bth, void* s
   if (!s || !cond_bth) return fail(DS_ERR_INVALID, "null argument");
   const long rows = (long)s->B * s->T;
   const int H = s->plan->H;
-  f32_to_bf16_pad_kernel<<<ew_grid(rows * H / 4, 256), 256, 0, (cudaStream_t)stream>>>((__nv_bfloat16*)(s->ws + s->o_cond), cond_bth, rows, H, H);
+  f32_to_bf16_pad_kernel<<<ew_grid(rows * H / 4, 256), 256, 0, (cudaStream_t)stream>>>((__nv_bfloat16*)(s->ws + s->o_cond), cond_bth, rows, H, H,
+                                                                                       (long)H * s->plan->S, s->plan->split ? H : 0);
   CUDA_TRY(cudaGetLastError());
   s->cond_set = true;
   return 0;
@@ -526,7 +545,9 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   __nv_bfloat16* s2 = (__nv_bfloat16*)(s->ws + s->o_s2);
   const int tiles_t = ceil_div(T, 128);
 
-  f32_to_bf16_pad_kernel<<<ew_grid(rows * p->FMp / 4, 256), 256, 0, st>>>(xb, x, rows, p->FM, p->FMp);
+  const int S = p->S;
+  const bool split = p->split != 0;
+  f32_to_bf16_pad_kernel<<<ew_grid(rows * p->FMp / 4, 256), 256, 0, st>>>(xb, x, rows, p->FM, p->FMp, (long)p->FMp * S, split ? p->FMp : 0);
   CUDA_TRY(cudaGetLastError());
   ++*launches;
 
@@ -541,9 +562,10 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   g.tmA0 = s->tm_xb; g.tmB = p->tm_whead;
   g.a0_c0 = 0; g.kb_a0 = p->FMp / 64; g.n_taps = 1; g.dil = 0; g.kb_a1 = 0; g.b_row0 = 0;
   g.relu = 1; g.bias = (const float*)(pk + p->o_bhead); g.vec_add = dtab; g.vec_sub = nullptr;
-  g.out = xt; g.ld_out = C; g.out_c0 = 0;
+  g.out = xt; g.ld_out = C * S; g.out_c0 = 0;
+  g.a0_lo = p->FMp; g.w_lo = p->FMp; g.out_lo = C;  // lo-half offsets: only read by the split instantiations
   shape(C / p->BN_C);
-  DS_TRY(launch_gemm(p->BN_C, EPI_LINEAR, g, st));
+  DS_TRY(launch_gemm(p->BN_C, EPI_LINEAR, g, st, split));
   ++*launches;
   if (p->fused) {
     for (int l = 0; l < L; ++l) {
@@ -557,9 +579,10 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
     g.a0_c0 = 0; g.kb_a0 = C / 64; g.n_taps = 3; g.dil = 1 << (l % p->cfg.dilation_cycle_length); g.kb_a1 = p->H / 64;
     g.b_row0 = l * 2 * C; g.relu = 0; g.bias = (const float*)(pk + p->o_b1) + (size_t)l * 2 * C;
     g.vec_add = nullptr; g.vec_sub = nullptr;
-    g.out = z; g.ld_out = L * C; g.out_c0 = l * C;
+    g.out = z; g.ld_out = L * C * S; g.out_c0 = l * C;
+    g.a0_lo = C; g.a1_lo = p->H; g.w_lo = p->K1; g.out_lo = L * C;
     shape(2 * C / p->BN_G);
-    DS_TRY(launch_gemm(p->BN_G, EPI_GATE, g, st));
+    DS_TRY(launch_gemm(p->BN_G, EPI_GATE, g, st, split));
     ++*launches;
     if (l + 1 < L) {
       // residual half of output_projection + (x + res)/sqrt(2)                          wavenet.py:44-48
@@ -567,9 +590,10 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
       g.tmA0 = s->tm_z; g.tmB = p->tm_w2;
       g.a0_c0 = l * C; g.kb_a0 = C / 64; g.n_taps = 1; g.dil = 0; g.kb_a1 = 0; g.b_row0 = l * C;
       g.bias = nullptr; g.vec_sub = nullptr; g.vec_add = rtab + (size_t)l * C;
-      g.res_in = xt; g.ld_res = C; g.out = xt; g.ld_out = C; g.out_c0 = 0;
+      g.res_in = xt; g.ld_res = C * S; g.out = xt; g.ld_out = C * S; g.out_c0 = 0;
+      g.a0_lo = L * C; g.w_lo = C; g.out_lo = C; g.res_lo = C;
       shape(C / p->BN_C);
-      DS_TRY(launch_gemm(p->BN_C, EPI_RES, g, st));
+      DS_TRY(launch_gemm(p->BN_C, EPI_RES, g, st, split));
       ++*launches;
     }
   }
@@ -580,20 +604,22 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   g.a0_c0 = 0; g.kb_a0 = L * C / 64; g.n_taps = 1; g.kb_a1 = 0; g.b_row0 = 0; g.relu = 0;
   g.scale = 1.0f / sqrtf((float)L);
   g.bias = (const float*)(pk + p->o_bsk); g.vec_add = nullptr; g.vec_sub = nullptr; g.res_in = nullptr;
-  g.out = s1; g.ld_out = C; g.out_c0 = 0;
+  g.out = s1; g.ld_out = C * S; g.out_c0 = 0;
+  g.a0_lo = L * C; g.w_lo = L * C; g.out_lo = C;
   shape(C / p->BN_C);
-  DS_TRY(launch_gemm(p->BN_C, EPI_LINEAR, g, st));
+  DS_TRY(launch_gemm(p->BN_C, EPI_LINEAR, g, st, split));
   ++*launches;
   // relu(skip_projection)                                                                wavenet.py:97-98
   g.tmA0 = s->tm_s1; g.tmB = p->tm_wsp; g.kb_a0 = C / 64; g.relu = 1; g.scale = 1.0f;
   g.bias = (const float*)(pk + p->o_bsp); g.out = s2;
-  DS_TRY(launch_gemm(p->BN_C, EPI_LINEAR, g, st));
+  g.a0_lo = C; g.w_lo = C;
+  DS_TRY(launch_gemm(p->BN_C, EPI_LINEAR, g, st, split));
   ++*launches;
   // output_projection -> fp32 [B][T][F*M]                                                 wavenet.py:99
   g.tmA0 = s->tm_s2; g.tmB = p->tm_wout; g.relu = 0;
   g.bias = (const float*)(pk + p->o_bout); g.out = out; g.ld_out = p->FM; g.n_real = p->FM;
   shape(p->FMr / p->BN_O);
-  DS_TRY(launch_gemm(p->BN_O, EPI_OUTF32, g, st));
+  DS_TRY(launch_gemm(p->BN_O, EPI_OUTF32, g, st, split));
   ++*launches;
   return 0;
 }
@@ -732,6 +758,7 @@ extern "C" int ds_debug_layer(ds_session* s, int32_t layer, int32_t time_index, 
   return session_fused_layer(s, layer, time_index, (cudaStream_t)stream);
 }
 extern "C" int ds_plan_layer_mode(const ds_plan* plan) { return plan ? plan->fused : -1; }
+extern "C" int ds_plan_precision(const ds_plan* plan) { return plan ? plan->split : -1; }
 
 // Debug: raw tensor-pipe rate.  out: 2*grid int64 device words {issue cycles, issue+drain cycles} per CTA.
 extern "C" int ds_debug_mma_rate(int32_t pair, int32_t grid, int32_t n_mma, int32_t commit_every, long long* out_dev, void* stream) {

@@ -9,15 +9,17 @@ namespace dsb {
 
 // ------------------------------------------------------------------ weight packing
 // dst[r*dst_ld + k] (bf16) = src[r*src_rs + k*src_ks] for r < rows, k < cols; zero for the padding
-// (r < dst_rows, k < dst_cols).
+// (r < dst_rows, k < dst_cols).  lo_off > 0 (fp32-accurate mode): also dst[.. + lo_off] = bf16(v - bf16(v)).
 __global__ void pack_matrix_kernel(__nv_bfloat16* __restrict__ dst, int dst_rows, int dst_cols, long dst_ld,
-                                   const float* __restrict__ src, int rows, int cols, long src_rs, long src_ks) {
+                                   const float* __restrict__ src, int rows, int cols, long src_rs, long src_ks, long lo_off) {
   const long n = static_cast<long>(dst_rows) * dst_cols;
   for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n; i += static_cast<long>(gridDim.x) * blockDim.x) {
     const int r = static_cast<int>(i / dst_cols), k = static_cast<int>(i % dst_cols);
     float v = 0.f;
     if (r < rows && k < cols) v = src[r * src_rs + k * src_ks];
-    dst[r * dst_ld + k] = __float2bfloat16_rn(v);
+    const __nv_bfloat16 hi = __float2bfloat16_rn(v);
+    dst[r * dst_ld + k] = hi;
+    if (lo_off > 0) dst[r * dst_ld + k + lo_off] = __float2bfloat16_rn(v - __bfloat162float(hi));
   }
 }
 
@@ -31,7 +33,8 @@ __global__ void accum_kernel(float* __restrict__ dst, const float* __restrict__ 
 // the BN/2 filter rows of the SAME channels; K = [tap0 | tap1 | tap2 | cond].
 __global__ void pack_gate_kernel(__nv_bfloat16* __restrict__ dst, float* __restrict__ bias_dst,
                                  const float* __restrict__ w_dil, const float* __restrict__ b_dil,
-                                 const float* __restrict__ w_cond, const float* __restrict__ b_cond, int C, int H, int BN) {
+                                 const float* __restrict__ w_cond, const float* __restrict__ b_cond, int C, int H, int BN,
+                                 long ld, long lo_off) {
   const int K = 3 * C + H;
   const int half = BN / 2;
   const long n = static_cast<long>(2 * C) * K;
@@ -46,7 +49,9 @@ __global__ void pack_gate_kernel(__nv_bfloat16* __restrict__ dst, float* __restr
     } else {
       v = w_cond[static_cast<long>(src_row) * H + (k - 3 * C)];
     }
-    dst[i] = __float2bfloat16_rn(v);
+    const __nv_bfloat16 hi = __float2bfloat16_rn(v);
+    dst[r * ld + k] = hi;
+    if (lo_off > 0) dst[r * ld + k + lo_off] = __float2bfloat16_rn(v - __bfloat162float(hi));
     if (k == 0) bias_dst[r] = b_dil[src_row] + b_cond[src_row];
   }
 }
@@ -118,8 +123,10 @@ __global__ void res_vec_kernel(float* __restrict__ r, const float* __restrict__ 
 }
 
 // ------------------------------------------------------------------ conversions
-// fp32 [rows][cols] -> bf16 [rows][ld] (zero padded columns).  cols, ld multiples of 4.
-__global__ void f32_to_bf16_pad_kernel(__nv_bfloat16* __restrict__ dst, const float* __restrict__ src, long rows, int cols, int ld) {
+// fp32 [rows][cols] -> bf16 [rows][ld] (zero padded columns).  cols, ld multiples of 4.  Row pitch `pitch` >= ld;
+// lo_off > 0 (fp32-accurate mode): the residual bf16(v - bf16(v)) goes lo_off elements further along the row.
+__global__ void f32_to_bf16_pad_kernel(__nv_bfloat16* __restrict__ dst, const float* __restrict__ src, long rows, int cols, int ld,
+                                       long pitch, int lo_off) {
   const int q = ld / 4;
   const long n = rows * q;
   for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n; i += static_cast<long>(gridDim.x) * blockDim.x) {
@@ -127,11 +134,19 @@ __global__ void f32_to_bf16_pad_kernel(__nv_bfloat16* __restrict__ dst, const fl
     const int c = static_cast<int>(i % q) * 4;
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
     if (c < cols) v = *reinterpret_cast<const float4*>(src + r * cols + c);
-    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+    __nv_bfloat162 p0 = __floats2bfloat162_rn(v.x, v.y), p1 = __floats2bfloat162_rn(v.z, v.w);
     uint2 o;
-    o.x = *reinterpret_cast<uint32_t*>(&lo);
-    o.y = *reinterpret_cast<uint32_t*>(&hi);
-    *reinterpret_cast<uint2*>(dst + r * ld + c) = o;
+    o.x = *reinterpret_cast<uint32_t*>(&p0);
+    o.y = *reinterpret_cast<uint32_t*>(&p1);
+    *reinterpret_cast<uint2*>(dst + r * pitch + c) = o;
+    if (lo_off > 0) {
+      const float2 h0 = __bfloat1622float2(p0), h1 = __bfloat1622float2(p1);
+      p0 = __floats2bfloat162_rn(v.x - h0.x, v.y - h0.y);
+      p1 = __floats2bfloat162_rn(v.z - h1.x, v.w - h1.y);
+      o.x = *reinterpret_cast<uint32_t*>(&p0);
+      o.y = *reinterpret_cast<uint32_t*>(&p1);
+      *reinterpret_cast<uint2*>(dst + r * pitch + c + lo_off) = o;
+    }
   }
 }
 

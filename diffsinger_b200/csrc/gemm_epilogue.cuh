@@ -26,13 +26,28 @@ __device__ __forceinline__ void st_bf16x32(__nv_bfloat16* ptr, const float (&v)[
   }
 }
 
+// fp32-accurate mode: v = hi + lo with hi = bf16(v), lo = bf16(v - hi); hi at ptr, lo at ptr + lo_off.
+__device__ __forceinline__ void st_split_bf16x32(__nv_bfloat16* ptr, int lo_off, const float (&v)[32]) {
+  float r[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) r[j] = v[j] - __bfloat162float(__float2bfloat16_rn(v[j]));
+  st_bf16x32(ptr, v);
+  st_bf16x32(ptr + lo_off, r);
+}
+template <bool kSplit>
+__device__ __forceinline__ void st_act32(__nv_bfloat16* ptr, int lo_off, const float (&v)[32]) {
+  if constexpr (kSplit) st_split_bf16x32(ptr, lo_off, v);
+  else st_bf16x32(ptr, v);
+}
+__device__ __forceinline__ float sigmoid_accurate(float x) { return 1.0f / (1.0f + expf(-x)); }
+
 __device__ __forceinline__ void ld_x4(const __nv_bfloat16* ptr, uint4 (&q)[4]) {
 #pragma unroll
   for (int i = 0; i < 4; ++i) q[i] = __ldg(reinterpret_cast<const uint4*>(ptr) + i);
 }
 
 // `half` in {0,1}: the two epilogue warps that share a TMEM lane quadrant interleave the 32-column chunks.
-template <int BN, int EPI>
+template <int BN, int EPI, bool kSplit>
 __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t taddr, int b, int t, bool valid, int nt, int half) {
   const size_t row = static_cast<size_t>(b) * p.T + (valid ? t : 0);
   if constexpr (EPI == EPI_GATE) {
@@ -53,10 +68,14 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
       for (int j = 0; j < 32; ++j) {
         const float gj = __uint_as_float(g[j]) + bg[j];
         const float fj = __uint_as_float(f[j]) + bf[j];
-        const float sg = fmaf(0.5f, tanh_approx(0.5f * gj), 0.5f);  // sigmoid
-        z[j] = sg * tanh_approx(fj);
+        if constexpr (kSplit) {
+          z[j] = sigmoid_accurate(gj) * tanhf(fj);
+        } else {
+          const float sg = fmaf(0.5f, tanh_approx(0.5f * gj), 0.5f);  // sigmoid
+          z[j] = sg * tanh_approx(fj);
+        }
       }
-      if (valid) st_bf16x32(out + c * 32, z);
+      if (valid) st_act32<kSplit>(out + c * 32, p.out_lo, z);
     }
   } else if constexpr (EPI == EPI_RES) {
     // x~_next = (x~ + R) / sqrt(2) + rvec,  rvec = (b - d_l)/sqrt(2) + d_{l+1}  (folded on the host side of the
@@ -75,7 +94,21 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
       ld_f32x32(rv + c * 32, rr);
       uint4 xn[4];
       if (c + 2 < BN / 32) ld_x4(xin + (c + 2) * 32, xn);
+      uint4 xl[4];
+      if constexpr (kSplit) ld_x4(xin + p.res_lo + c * 32, xl);
       tmem_ld_wait();
+      if constexpr (kSplit) {  // x = hi + lo: fold the lo half into the accumulator values
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint32_t w[4] = {xl[i].x, xl[i].y, xl[i].z, xl[i].w};
+#pragma unroll
+          for (int h = 0; h < 4; ++h) {
+            const int j = 8 * i + 2 * h;
+            a[j] = __float_as_uint(__uint_as_float(a[j]) + __uint_as_float(w[h] << 16));
+            a[j + 1] = __float_as_uint(__uint_as_float(a[j + 1]) + __uint_as_float(w[h] & 0xffff0000u));
+          }
+        }
+      }
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const uint32_t w[4] = {xq[i].x, xq[i].y, xq[i].z, xq[i].w};
@@ -86,7 +119,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
           v[j + 1] = fmaf(__uint_as_float(a[j + 1]) + __uint_as_float(w[h] & 0xffff0000u), 0.70710678118654752f, rr[j + 1]);
         }
       }
-      if (valid) st_bf16x32(xout + c * 32, v);
+      if (valid) st_act32<kSplit>(xout + c * 32, p.out_lo, v);
 #pragma unroll
       for (int i = 0; i < 4; ++i) xq[i] = xn[i];
     }
@@ -124,7 +157,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] += da[j];
         }
-        if (valid) st_bf16x32(reinterpret_cast<__nv_bfloat16*>(p.out) + row * p.ld_out + p.out_c0 + n0 + c * 32, v);
+        if (valid) st_act32<kSplit>(reinterpret_cast<__nv_bfloat16*>(p.out) + row * p.ld_out + p.out_c0 + n0 + c * 32, p.out_lo, v);
       }
     }
   }

@@ -46,6 +46,11 @@ struct GemmParams {
   int ld_out;
   int out_c0;  // channel offset in out
   int n_real;  // EPI_OUTF32: number of valid output columns
+  // fp32-accurate ("split") mode, kSplit instantiations only: every bf16 operand is stored as hi = bf16(v) followed,
+  // `*_lo` elements further along the channel / K axis, by lo = bf16(v - hi); each logical 64-wide K block is issued
+  // three times (hi*hi, lo*hi, hi*lo) into the same fp32 accumulator.
+  int a0_lo, a1_lo, w_lo;  // offsets of the lo halves in A0 / A1 (channels) and W (K)
+  int out_lo, res_lo;      // offsets of the lo halves in out / res_in (channels)
 };
 
 template <int BN>
@@ -57,11 +62,12 @@ struct GemmCfg {
   static constexpr uint32_t kSmemBytes = 1024 + kStages * (kABytes + kBBytes) + 256;
 };
 
-template <int BN, int EPI>
+template <int BN, int EPI, bool kSplit>
 __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t taddr, int b, int t, bool valid, int nt, int half);
 
-template <int BN, int EPI>
+template <int BN, int EPI, bool kSplit = false>
 __global__ void __launch_bounds__(kGemmThreads, 1) ds_gemm_kernel(const __grid_constant__ GemmParams p) {
+  constexpr int kSub = kSplit ? 3 : 1;  // sub-blocks per logical K block
   using Cfg = GemmCfg<BN>;
   constexpr int S = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
@@ -116,21 +122,25 @@ __global__ void __launch_bounds__(kGemmThreads, 1) ds_gemm_kernel(const __grid_c
         const int row0 = p.b_row0 + nt * BN;
         const int kb_taps = p.n_taps * p.kb_a0;
         for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(&empty[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&full[stage], Cfg::kABytes + Cfg::kBBytes);
-          uint8_t* sa = smem_a + stage * Cfg::kABytes;
-          uint8_t* sb = smem_b + stage * Cfg::kBBytes;
-          if (kb < kb_taps) {
-            const int tap = kb / p.kb_a0;
-            const int cb = kb - tap * p.kb_a0;
-            tma_load_3d(&p.tmA0, &full[stage], sa, p.a0_c0 + cb * 64, t0 + (tap - p.n_taps / 2) * p.dil, b);
-          } else {
-            tma_load_3d(&p.tmA1, &full[stage], sa, (kb - kb_taps) * 64, t0, b);
-          }
-          tma_load_2d(&p.tmB, &full[stage], sb, kb * 64, row0);
-          if (++stage == S) {
-            stage = 0;
-            phase ^= 1;
+#pragma unroll 1
+          for (int sub = 0; sub < kSub; ++sub) {  // split: (A hi, W hi), (A lo, W hi), (A hi, W lo)
+            mbar_wait(&empty[stage], phase ^ 1);
+            mbar_arrive_expect_tx(&full[stage], Cfg::kABytes + Cfg::kBBytes);
+            uint8_t* sa = smem_a + stage * Cfg::kABytes;
+            uint8_t* sb = smem_b + stage * Cfg::kBBytes;
+            if (kb < kb_taps) {
+              const int tap = kb / p.kb_a0;
+              const int cb = kb - tap * p.kb_a0;
+              tma_load_3d(&p.tmA0, &full[stage], sa, p.a0_c0 + cb * 64 + (sub == 1 ? p.a0_lo : 0),
+                          t0 + (tap - p.n_taps / 2) * p.dil, b);
+            } else {
+              tma_load_3d(&p.tmA1, &full[stage], sa, (kb - kb_taps) * 64 + (sub == 1 ? p.a1_lo : 0), t0, b);
+            }
+            tma_load_2d(&p.tmB, &full[stage], sb, kb * 64 + (sub == 2 ? p.w_lo : 0), row0);
+            if (++stage == S) {
+              stage = 0;
+              phase ^= 1;
+            }
           }
         }
       }
@@ -148,7 +158,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) ds_gemm_kernel(const __grid_c
         mbar_wait(&tmem_empty[as], aphase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + as * BN;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = 0; kb < num_kb * kSub; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           const uint64_t da = make_kmajor_sw128_desc(smem_u32(smem_a + stage * Cfg::kABytes));
@@ -157,7 +167,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) ds_gemm_kernel(const __grid_c
           for (int k = 0; k < 4; ++k)  // 4 x (K = 16) per 64-wide block: +32 B on the start address
             umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
           umma_commit(&empty[stage]);
-          if (kb == num_kb - 1) umma_commit(&tmem_full[as]);
+          if (kb == num_kb * kSub - 1) umma_commit(&tmem_full[as]);
           if (++stage == S) {
             stage = 0;
             phase ^= 1;
@@ -180,7 +190,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) ds_gemm_kernel(const __grid_c
       tc_fence_after();
       const int t = tt * 128 + quad * 32 + lane;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * BN;
-      epilogue_tile<BN, EPI>(p, taddr, b, t, t < p.T, nt, half);
+      epilogue_tile<BN, EPI, kSplit>(p, taddr, b, t, t < p.T, nt, half);
       tc_fence_before();
       mbar_arrive(&tmem_empty[as]);
     }

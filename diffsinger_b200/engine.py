@@ -136,7 +136,11 @@ class WaveNetEngine:
         self.M, self.F = module.in_dims, module.n_feats
         self.FM = self.M * self.F
         self.C, self.Lyr, self.H = module.num_channels, module.num_layers, module.hidden_size
-        cfg = nat.WaveNetConfig(self.M, self.F, self.Lyr, self.C, module.dilation_cycle_length, self.H)
+        self.precision = getattr(module, 'precision', 'bf16')
+        if self.precision not in ('bf16', 'fp32'):
+            raise ValueError(f"precision must be 'bf16' or 'fp32', got {self.precision!r}")
+        cfg = nat.WaveNetConfig(self.M, self.F, self.Lyr, self.C, module.dilation_cycle_length, self.H,
+                                1 if self.precision == 'fp32' else 0)
         self.plan = C.c_void_p()
         nat.check(L.ds_plan_create(C.byref(cfg), C.byref(self.plan)))
         self.packed = torch.empty(L.ds_plan_packed_bytes(self.plan) + 256, dtype=torch.uint8, device=device)

@@ -43,6 +43,8 @@ typedef struct {
   int32_t num_channels;          /* C, multiple of 64 */
   int32_t dilation_cycle_length; /* dilation of layer i = 2 ** (i % cycle) */
   int32_t hidden_size;           /* H, multiple of 64 */
+  int32_t precision;             /* 0: bf16 operands, fp32 accumulate (final mel rel-L2 <= 1e-2)                    */
+                                 /* 1: fp32-accurate, 3 x bf16 split products (per-evaluation rel-L2 <= 1e-4)       */
 } ds_wavenet_config;
 
 /* fp32 device pointers in the reference's state_dict layout (wavenet.py:22-31,56-73).
@@ -147,6 +149,8 @@ int ds_debug_set_trace(void* dev_buf, int32_t n_entries);
 int ds_debug_layer(ds_session* s, int32_t layer, int32_t time_index, void* stream);
 /* 0 unfused (two GEMM launches per layer), 1 smem-z, 2 global-z, 3 CTA pair, 4 CTA pair + halo tiles (csrc/api.cu). */
 int ds_plan_layer_mode(const ds_plan* plan);
+/* 0 bf16, 1 fp32-accurate (ds_wavenet_config.precision, or DSB200_PRECISION=fp32 in the environment). */
+int ds_plan_precision(const ds_plan* plan);
 /* Debug: raw tcgen05.mma rate micro-benchmark (csrc/mma_bench.cuh). */
 int ds_debug_mma_rate(int32_t pair, int32_t grid, int32_t n_mma, int32_t commit_every, long long* out_dev, void* stream);
 
