@@ -125,7 +125,7 @@ def workload_name():
 
 
 LAYER_KERNELS = {0: "ds_gemm_kernel<256, EPI_GATE> + ds_gemm_kernel<256, EPI_RES>", 1: "ds_layer_kernel<256, true>",
-                 2: "ds_layer_kernel<256, false>", 3: "ds_layer_pair_kernel", 4: "ds_layer_halo_kernel"}
+                 2: "ds_layer_kernel<256, false>", 3: "ds_layer_pair_kernel", 4: "ds_layer_halo_kernel", 5: "ds_layer_grp_kernel"}
 
 
 def time_layer_kernel(session, L, iters=3):

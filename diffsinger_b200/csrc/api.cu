@@ -16,6 +16,7 @@
 #include "layer_kernel.cuh"
 #include "layer2_kernel.cuh"
 #include "layer3_kernel.cuh"
+#include "layer4_kernel.cuh"
 #include "mma_bench.cuh"
 
 using namespace dsb;
@@ -167,6 +168,19 @@ static int launch_layer_halo(const LayerParams& p, int max_dil, cudaStream_t st)
   return 0;
 }
 
+static int launch_layer_grp(const LayerParams& p, int max_dil, cudaStream_t st) {
+  static bool attr_done = false;
+  if (!attr_done) {
+    CUDA_TRY(cudaFuncSetAttribute(ds_layer_grp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGrpSmemMax));
+    attr_done = true;
+  }
+  const int max_pairs = g_num_sms / 2;
+  const int pairs = p.total_tiles < max_pairs ? p.total_tiles : max_pairs;
+  ds_layer_grp_kernel<<<2 * pairs, kGemmThreads, grp_smem_bytes(max_dil), st>>>(p);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
 static unsigned long long* g_trace = nullptr;
 static int g_trace_cap = 0;
 extern "C" int ds_debug_set_trace(void* dev_buf, int32_t n_entries) {
@@ -191,6 +205,7 @@ struct ds_plan {
   int fused;             // 0: gate GEMM + residual GEMM; 1: one kernel per layer, z kept in smem; 2: one kernel per
                          // layer, GEMM-2 re-reads z through TMA (4-deep operand ring); 3: as 2 on CTA pairs (cta_group::2);
                          // 4: CTA pairs + halo-carrying activation tiles shared by the three conv taps
+                         // 5: as 4 with grouped pipeline stages (12 / 8 UMMAs per mbarrier hand-shake)
   int max_dil;
   int fused_stages;
   int split;             // fp32-accurate mode: every bf16 operand carries a lo half (3 x bf16 split products)
@@ -270,7 +285,8 @@ extern "C" int ds_plan_create(const ds_wavenet_config* cfg, ds_plan** out) {
   const char* env = getenv("DSB200_LAYER_MODE");
   p->max_dil = 1 << ((cfg->dilation_cycle_length < cfg->num_layers ? cfg->dilation_cycle_length : cfg->num_layers) - 1);
   const bool can_pair = C % 256 == 0, can_halo = can_pair && p->max_dil <= 16;
-  p->fused = can_halo ? 4 : ((C % 128 == 0) ? 2 : 0);
+  p->fused = can_halo ? 5 : ((C % 128 == 0) ? 2 : 0);
+  if (env && !strcmp(env, "grp") && can_halo) p->fused = 5;
   if (env && !strcmp(env, "halo") && can_halo) p->fused = 4;
   if (env && !strcmp(env, "pair") && can_pair) p->fused = 3;
   if (env && !strcmp(env, "global") && C % 128 == 0) p->fused = 2;
@@ -436,7 +452,7 @@ extern "C" int ds_session_create(ds_plan* plan, int32_t B, int32_t T, int32_t ma
   r = r ? r : make_act_map(&s->tm_z, s->ws + s->o_z, plan->L * plan->C * Sm, T, B);
   r = r ? r : make_act_map(&s->tm_s1, s->ws + s->o_s1, plan->C * Sm, T, B);
   r = r ? r : make_act_map(&s->tm_s2, s->ws + s->o_s2, plan->C * Sm, T, B);
-  if (plan->fused == 4)
+  if (plan->fused >= 4)
     for (int k = 0; (1 << k) <= plan->max_dil; ++k) {
       r = r ? r : make_act_map(&s->tm_xh[0][k], s->ws + s->o_xt, plan->C, T, B, 128 + 2 * (1 << k));
       r = r ? r : make_act_map(&s->tm_xh[1][k], s->ws + s->o_xt1, plan->C, T, B, 128 + 2 * (1 << k));
@@ -519,6 +535,11 @@ static int session_fused_layer(ds_session* s, int l, int time_index, cudaStream_
   lp.bias1 = (const float*)(pk + p->o_b1) + (size_t)l * 2 * C;
   lp.rvec = rtab + (size_t)l * C;
   lp.z_c0 = l * C;
+  if (p->fused == 5) {
+    lp.tmXh = s->tm_xh[l & 1][l % p->cfg.dilation_cycle_length];
+    lp.a_slot = halo_a_slot_bytes(p->max_dil); lp.n_a = grp_stages(p->max_dil);
+    return launch_layer_grp(lp, p->max_dil, st);
+  }
   if (p->fused == 4) {
     lp.tmXh = s->tm_xh[l & 1][l % p->cfg.dilation_cycle_length];
     return launch_layer_halo(lp, p->max_dil, st);

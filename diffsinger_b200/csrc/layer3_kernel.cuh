@@ -181,16 +181,26 @@ ds_layer_halo_kernel(const __grid_constant__ LayerParams p) {
       HaloRing r;
       auto a_item = [&](const CUtensorMap* map, uint32_t bytes, int c0, int t, int b) {
         mbar_wait(&a_empty[r.a], r.pa ^ 1);
-        if (leader) mbar_arrive_expect_tx(&a_full[r.a], 2 * bytes);
-        else mbar_arrive_cluster(&a_full[r.a], 0);
-        tma_load_3d_pair(map, &a_full[r.a], smem_a + r.a * p.a_slot, c0, t, b);
+        if (p.dbg & 2) {  // debug: barriers only, no bytes
+          if (leader) mbar_arrive(&a_full[r.a]);
+          else mbar_arrive_cluster(&a_full[r.a], 0);
+        } else {
+          if (leader) mbar_arrive_expect_tx(&a_full[r.a], 2 * bytes);
+          else mbar_arrive_cluster(&a_full[r.a], 0);
+          tma_load_3d_pair(map, &a_full[r.a], smem_a + r.a * p.a_slot, c0, t, b);
+        }
         r.next_a(NA);
       };
       auto b_item = [&](const CUtensorMap* map, int k0, int row0) {
         mbar_wait(&b_empty[r.b], r.pb ^ 1);
-        if (leader) mbar_arrive_expect_tx(&b_full[r.b], 2 * kPairBBytes);
-        else mbar_arrive_cluster(&b_full[r.b], 0);
-        tma_load_2d_pair(map, &b_full[r.b], smem_b + r.b * kPairBBytes, k0, row0);
+        if (p.dbg & 2) {
+          if (leader) mbar_arrive(&b_full[r.b]);
+          else mbar_arrive_cluster(&b_full[r.b], 0);
+        } else {
+          if (leader) mbar_arrive_expect_tx(&b_full[r.b], 2 * kPairBBytes);
+          else mbar_arrive_cluster(&b_full[r.b], 0);
+          tma_load_2d_pair(map, &b_full[r.b], smem_b + r.b * kPairBBytes, k0, row0);
+        }
         r.next_b();
       };
       LayerJobs jobs(n_local, p.p1, p.p2, true);
@@ -233,8 +243,10 @@ ds_layer_halo_kernel(const __grid_constant__ LayerParams p) {
         tc_fence_after();
         const uint64_t da = make_kmajor_sw128_desc_row(smem_u32(smem_a + r.a * p.a_slot), row);
         const uint64_t db = make_kmajor_sw128_desc(smem_u32(smem_b + r.b * kPairBBytes));
+        if (!(p.dbg & 4)) {  // debug bit 2: commits only, no MMAs (operand-delivery rate alone)
 #pragma unroll
-        for (int k = 0; k < 4; ++k) umma_bf16_pair(tmem_d, da + 2 * k, db + 2 * k, idesc, (!first_of_job) || k != 0);
+          for (int k = 0; k < 4; ++k) umma_bf16_pair(tmem_d, da + 2 * k, db + 2 * k, idesc, (!first_of_job) || k != 0);
+        }
         umma_commit_pair(&b_empty[r.b]);
         r.next_b();
         if (last_of_item) {

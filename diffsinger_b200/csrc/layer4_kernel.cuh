@@ -1,0 +1,232 @@
+// CTA-pair fused residual-layer kernel, "grouped stage" variant of layer3_kernel.cuh (reference: ResidualBlock.forward,
+// modules/backbones/wavenet.py:33-48).
+//
+// Measured on B200 (tools/layer_dbg_timing.py, profiles/r01_layer_dbg_timing.txt): with loads, MMAs and epilogue math all
+// switched off, the mbarrier skeleton of layer3 (one full/empty hand-shake per 64-wide K block = per 4 UMMAs, ~90 cycles
+// per already-complete try_wait, remote arrives, multicast commits) alone takes 223 us of the kernel's 428 us -- as long as
+// the 4 UMMAs it guards.  Here one pipeline stage carries a whole GROUP of K blocks under ONE full/empty barrier pair:
+//   conv stage    : one halo activation tile (64 channels x (128 + 2*dil) frames) + the THREE tap weight blocks of that
+//                   channel block                                   -> 12 UMMAs per hand-shake
+//   1x1 stage     : two activation blocks (conditioner or gated z) + their two weight blocks
+//                                                                   ->  8 UMMAs per hand-shake
+// i.e. 4x fewer synchronisation events per tile, and TMA transactions of 66 KB per barrier.
+// Roles, job order (LayerJobs, interleaved), TMEM double buffering and the epilogues are those of layer3_kernel.cuh.
+#pragma once
+#include "layer3_kernel.cuh"
+
+namespace dsb {
+
+constexpr int kGrpMaxStages = 3;
+constexpr uint32_t kGrpSmemMax = 232448;
+
+__host__ __device__ inline uint32_t grp_stage_bytes(int max_dil) { return halo_a_slot_bytes(max_dil) + 3u * kPairBBytes; }
+__host__ __device__ inline int grp_stages(int max_dil) {
+  const int n = static_cast<int>((kGrpSmemMax - 1024u - 256u) / grp_stage_bytes(max_dil));
+  return n > kGrpMaxStages ? kGrpMaxStages : n;
+}
+__host__ __device__ inline uint32_t grp_smem_bytes(int max_dil) {
+  return 1024u + grp_stages(max_dil) * grp_stage_bytes(max_dil) + 256u;
+}
+
+// Requires C % 256 == 0, H % 128 == 0 (two-block 1x1 stages) and 2^(cycle-1) <= 16.  LayerParams as for the halo kernel;
+// a_slot = halo_a_slot_bytes(max_dil), n_a = grp_stages(max_dil).
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+  const int NS = p.n_a;
+  const uint32_t stage_bytes = p.a_slot + 3u * kPairBBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NS * stage_bytes);
+  uint64_t* full = bars;                      // leader: 2 producer arrivals + the bytes of both CTAs
+  uint64_t* empty = full + kGrpMaxStages;     // per CTA: released by the leader's multicast commit
+  uint64_t* tmem_full = empty + kGrpMaxStages;
+  uint64_t* tmem_empty = tmem_full + 2;       // leader: 16 warp arrivals (8 per CTA)
+  uint64_t* z_full = tmem_empty + 2;          // per CTA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(z_full + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tmXh);
+    tma_prefetch_desc(&p.tmCond);
+    tma_prefetch_desc(&p.tmW1);
+    tma_prefetch_desc(&p.tmW2);
+    tma_prefetch_desc(&p.tmZ);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < NS; ++i) {
+      mbar_init(&full[i], 2);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);
+      mbar_init(&tmem_empty[i], 16);
+    }
+    mbar_init(z_full, kEpiThreads);
+    fence_barrier_init();
+  }
+  cluster_sync_all();  // peer barriers are initialised before any remote arrive / multicast commit
+  if (warp == 2) tmem_alloc_pair<512>(tmem_slot);
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int pair_id = blockIdx.x >> 1;
+  const int n_pairs = gridDim.x >> 1;
+  const int n_local = (p.total_tiles > pair_id) ? (p.total_tiles - 1 - pair_id) / n_pairs + 1 : 0;
+  const uint32_t halo_bytes = (128u + 2u * p.dil) * 128u;
+  // stage layout: conv  [halo A tile (a_slot)] [B tap0] [B tap1] [B tap2]
+  //               1x1   [A blk0 16K] [A blk1 16K] [B blk0 16K] [B blk1 16K]      (fits: a_slot + 48K >= 64K)
+  constexpr uint32_t kOne = kLayerABytes;  // 16 KB
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ------------------------------------------------------------ TMA producer (both CTAs)
+      int st = 0;
+      uint32_t ph = 0;
+      auto begin_stage = [&](uint32_t bytes_per_cta) -> uint8_t* {
+        mbar_wait(&empty[st], ph ^ 1);
+        if (leader) mbar_arrive_expect_tx(&full[st], 2 * bytes_per_cta);
+        else mbar_arrive_cluster(&full[st], 0);
+        return smem + st * stage_bytes;
+      };
+      auto end_stage = [&]() { if (++st == NS) { st = 0; ph ^= 1; } };
+      // 1x1 stages: blocks [k, k + n) of activation map `am` (channel offset ac0) against weight columns wk0 + ...
+      auto one_by_one = [&](const CUtensorMap* am, int ac0, const CUtensorMap* wm, int wk0, int nblk, int row0, int t0, int b) {
+        for (int k = 0; k < nblk; k += 2) {
+          const int n = nblk - k < 2 ? nblk - k : 2;
+          uint8_t* s = begin_stage(n * (kOne + kPairBBytes));
+          for (int j = 0; j < n; ++j) {
+            tma_load_3d_pair(am, &full[st], s + j * kOne, ac0 + (k + j) * 64, t0, b);
+            tma_load_2d_pair(wm, &full[st], s + 2 * kOne + j * kPairBBytes, wk0 + (k + j) * 64, row0);
+          }
+          end_stage();
+        }
+      };
+      LayerJobs jobs(n_local, p.p1, p.p2, true);
+      int kind, j, idx;
+      while (jobs.next(kind, j, idx)) {
+        const int tile = pair_id + j * n_pairs;
+        const int t0 = (tile % p.tiles_t) * 256 + rank * 128;
+        const int b = tile / p.tiles_t;
+        if (kind == 0) {
+          const int row0 = p.w1_row0 + idx * 256 + rank * 128;
+          for (int cb = 0; cb < p.kb_c; ++cb) {
+            uint8_t* s = begin_stage(halo_bytes + 3 * kPairBBytes);
+            tma_load_3d_pair(&p.tmXh, &full[st], s, cb * 64, t0 - p.dil, b);
+#pragma unroll
+            for (int tap = 0; tap < 3; ++tap)
+              tma_load_2d_pair(&p.tmW1, &full[st], s + p.a_slot + tap * kPairBBytes, (tap * p.kb_c + cb) * 64, row0);
+            end_stage();
+          }
+          one_by_one(&p.tmCond, 0, &p.tmW1, 3 * p.kb_c * 64, p.kb_h, row0, t0, b);
+        } else {
+          if (idx == 0) mbar_wait(z_full, j & 1);  // this CTA's z rows of tile j are in global memory
+          const int row0 = p.w2_row0 + idx * 256 + rank * 128;
+          one_by_one(&p.tmZ, p.z_c0, &p.tmW2, 0, p.kb_c, row0, t0, b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && leader) {
+      // ------------------------------------------------------------ MMA issuer (leader CTA only)
+      constexpr uint32_t idesc = make_idesc_bf16_f32_m(256, 256);
+      int st = 0;
+      uint32_t ph = 0;
+      uint32_t acc_it = 0;
+      auto mma4 = [&](uint32_t tmem_d, uint64_t da, uint64_t db, bool fresh) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_bf16_pair(tmem_d, da + 2 * k, db + 2 * k, idesc, (!fresh) || k != 0);
+      };
+      auto release = [&](bool last_of_job, uint32_t as) {
+        umma_commit_pair(&empty[st]);
+        if (last_of_job) umma_commit_pair(&tmem_full[as]);
+        if (++st == NS) { st = 0; ph ^= 1; }
+      };
+      auto one_by_one = [&](uint32_t tmem_d, int nblk, bool fresh_first, uint32_t as) {
+        for (int k = 0; k < nblk; k += 2) {
+          const int n = nblk - k < 2 ? nblk - k : 2;
+          mbar_wait(&full[st], ph);
+          tc_fence_after();
+          const uint32_t s = smem_u32(smem + st * stage_bytes);
+          for (int jj = 0; jj < n; ++jj)
+            mma4(tmem_d, make_kmajor_sw128_desc(s + jj * kOne), make_kmajor_sw128_desc(s + 2 * kOne + jj * kPairBBytes),
+                 fresh_first && k == 0 && jj == 0);
+          release(k + n >= nblk, as);
+        }
+      };
+      LayerJobs jobs(n_local, p.p1, p.p2, true);
+      int kind, j, idx;
+      while (jobs.next(kind, j, idx)) {
+        const uint32_t as = acc_it & 1;
+        mbar_wait(&tmem_empty[as], ((acc_it >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + as * 256;
+        if (kind == 0) {
+          for (int cb = 0; cb < p.kb_c; ++cb) {
+            mbar_wait(&full[st], ph);
+            tc_fence_after();
+            const uint32_t s = smem_u32(smem + st * stage_bytes);
+#pragma unroll
+            for (int tap = 0; tap < 3; ++tap)
+              mma4(tmem_d, make_kmajor_sw128_desc_row(s, tap * p.dil), make_kmajor_sw128_desc(s + p.a_slot + tap * kPairBBytes),
+                   cb == 0 && tap == 0);
+            release(false, as);
+          }
+          one_by_one(tmem_d, p.kb_h, false, as);
+        } else {
+          one_by_one(tmem_d, p.kb_c, true, as);
+        }
+        ++acc_it;
+      }
+    }
+  } else if (warp >= 4) {
+    // -------------------------------------------------------------- epilogue (both CTAs; 256 threads each)
+    const int quad = warp & 3;
+    const int half = (warp - 4) >> 2;
+    const int rr = quad * 32 + lane;
+    const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+    uint32_t acc_it = 0;
+    LayerJobs jobs(n_local, p.p1, p.p2, true);
+    int kind, j, idx;
+    while (jobs.next(kind, j, idx)) {
+      const int tile = pair_id + j * n_pairs;
+      const int b = tile / p.tiles_t;
+      const int t = (tile % p.tiles_t) * 256 + rank * 128 + rr;
+      const bool valid = t < p.T;
+      const size_t row = static_cast<size_t>(b) * p.T + (valid ? t : 0);
+      const uint32_t as = acc_it & 1;
+      mbar_wait(&tmem_full[as], (acc_it >> 1) & 1);
+      tc_fence_after();
+      const uint32_t taddr = lane_addr + as * 256;
+      if (kind == 0) pair_epilogue_gate(p, taddr, idx, row, valid, half);
+      else pair_epilogue_res(p, taddr, idx, b, row, valid, half);
+      // release the accumulator on the LEADER's barrier: one arrival per warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (leader) mbar_arrive(&tmem_empty[as]);
+        else mbar_arrive_cluster(&tmem_empty[as], 0);
+      }
+      if (kind == 0 && idx == p.p1 - 1 && p.p2 > 0) {
+        __threadfence();             // z stores reach L2 ...
+        fence_proxy_async_global();  // ... and are ordered before the TMA (async proxy) re-read
+        mbar_arrive(z_full);
+      }
+      ++acc_it;
+    }
+  }
+  tc_fence_before();
+  cluster_sync_all();  // the leader's MMAs read this CTA's shared memory and write its TMEM until the very end
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_pair<512>(tmem_base);
+  }
+}
+
+}  // namespace dsb

@@ -76,15 +76,15 @@ def test_fused_and_unfused_layer_paths_agree(monkeypatch):
     t = torch.tensor([123.0])
     ref = OracleWaveNet(sd, F, cycle)(spec, t, cond)
     outs, launches = [], []
-    for mode in ("halo", "pair", "global", "smem", "unfused"):
+    for mode in ("grp", "halo", "pair", "global", "smem", "unfused"):
         monkeypatch.setenv("DSB200_LAYER_MODE", mode)
         net = _net(sd, cfg)
         with torch.no_grad():
             outs.append(net(spec.to(dev), t.to(dev), cond.to(dev)).cpu())
         launches.append(next(iter(net.engine().sessions.values())).last_launches)
         assert rel_l2(outs[-1], ref) < EVAL_TOL
-    assert launches == [L + 5, L + 5, L + 5, L + 5, 2 * L + 4]
-    assert all(rel_l2(o, outs[4]) < 5e-3 for o in outs[:4])
+    assert launches == [L + 5] * 5 + [2 * L + 4]
+    assert all(rel_l2(o, outs[5]) < 5e-3 for o in outs[:5])
 
 
 def _diffusion(cls, sd, cfg, **kw):
