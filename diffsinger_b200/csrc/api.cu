@@ -89,6 +89,18 @@ static int make_act_map(CUtensorMap* m, const void* base, int channels, int T, i
   if (r != CUDA_SUCCESS) return fail(DS_ERR_CUDA, "cuTensorMapEncodeTiled(activation %dx%dx%d) -> %d", channels, T, B, (int)r);
   return 0;
 }
+// bf16 activation STORE map: dims (channels, T, B), box (32, 32, 1), 64-byte swizzle (epilogue warps of the grouped kernel).
+static int make_store_map(CUtensorMap* m, const void* base, int channels, int T, int B) {
+  cuuint64_t dims[3] = {(cuuint64_t)channels, (cuuint64_t)T, (cuuint64_t)B};
+  cuuint64_t strides[2] = {(cuuint64_t)channels * 2, (cuuint64_t)channels * 2 * (cuuint64_t)T};
+  cuuint32_t box[3] = {32, 32, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(DS_ERR_CUDA, "cuTensorMapEncodeTiled(store %dx%dx%d) -> %d", channels, T, B, (int)r);
+  return 0;
+}
 // bf16 weight map: dims (K, rows), box (64, BN).
 static int make_weight_map(CUtensorMap* m, const void* base, int K, int rows, int BN) {
   cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
@@ -389,6 +401,7 @@ struct ds_session {
   size_t o_cond, o_xb, o_xt, o_xt1, o_z, o_s1, o_s2, o_g, o_d, o_r, o_tmp, ws_bytes;
   CUtensorMap tm_cond, tm_xb, tm_xt, tm_xt1, tm_z, tm_s1, tm_s2;
   CUtensorMap tm_xh[2][5];  // halo maps of the two x~ buffers, one per dilation 2^k (k < 5)
+  CUtensorMap tm_zs, tm_xs[2];  // TMA store maps (grouped kernel)
   cudaStream_t cap_stream = nullptr;
   std::map<std::string, GraphEntry> graphs;
   int64_t last_launches = 0;
@@ -457,6 +470,11 @@ extern "C" int ds_session_create(ds_plan* plan, int32_t B, int32_t T, int32_t ma
       r = r ? r : make_act_map(&s->tm_xh[0][k], s->ws + s->o_xt, plan->C, T, B, 128 + 2 * (1 << k));
       r = r ? r : make_act_map(&s->tm_xh[1][k], s->ws + s->o_xt1, plan->C, T, B, 128 + 2 * (1 << k));
     }
+  if (plan->fused == 5) {
+    r = r ? r : make_store_map(&s->tm_zs, s->ws + s->o_z, plan->L * plan->C, T, B);
+    r = r ? r : make_store_map(&s->tm_xs[0], s->ws + s->o_xt, plan->C, T, B);
+    r = r ? r : make_store_map(&s->tm_xs[1], s->ws + s->o_xt1, plan->C, T, B);
+  }
   if (r) {
     delete s;
     return r;
@@ -538,6 +556,7 @@ static int session_fused_layer(ds_session* s, int l, int time_index, cudaStream_
   if (p->fused == 5) {
     lp.tmXh = s->tm_xh[l & 1][l % p->cfg.dilation_cycle_length];
     lp.a_slot = halo_a_slot_bytes(p->max_dil); lp.n_a = grp_stages(p->max_dil);
+    lp.tmZs = s->tm_zs; lp.tmXs = s->tm_xs[(l + 1) & 1];
     return launch_layer_grp(lp, p->max_dil, st);
   }
   if (p->fused == 4) {

@@ -21,11 +21,95 @@ constexpr uint32_t kGrpSmemMax = 232448;
 
 __host__ __device__ inline uint32_t grp_stage_bytes(int max_dil) { return halo_a_slot_bytes(max_dil) + 3u * kPairBBytes; }
 __host__ __device__ inline int grp_stages(int max_dil) {
-  const int n = static_cast<int>((kGrpSmemMax - 1024u - 256u) / grp_stage_bytes(max_dil));
+  const int n = static_cast<int>((kGrpSmemMax - 1024u - 2048u - 8u * 2048u) / grp_stage_bytes(max_dil));
   return n > kGrpMaxStages ? kGrpMaxStages : n;
 }
 __host__ __device__ inline uint32_t grp_smem_bytes(int max_dil) {
-  return 1024u + grp_stages(max_dil) * grp_stage_bytes(max_dil) + 256u;
+  return 1024u + grp_stages(max_dil) * grp_stage_bytes(max_dil) + 2048u + 8u * 2048u;
+}
+
+constexpr uint32_t kGrpWarpStage = 2048;  // per epilogue warp: 32 frames x 32 channels bf16, SWIZZLE_64B
+
+// One warp's 32 x 32 bf16 sub-tile: lane = frame row, v = its 32 channels as 16 packed pairs.  Rows go to shared memory in
+// the 64-byte swizzle the store map expects (16-byte chunk index ^= (row >> 1) & 3: conflict-free), then ONE TMA store
+// writes the tile (frames beyond T are clipped by the tensor map) -- instead of 4 STG.128 per lane that each touch 32
+// different 128-byte lines.
+__device__ __forceinline__ void grp_store_tile(const CUtensorMap* map, uint32_t sw, int lane, const uint32_t (&v)[16], int c0, int t0,
+                                               int b, bool any_valid) {
+  if (lane == 0) bulk_wait_read_all();  // the previous store of this warp has drained the staging tile
+  __syncwarp();
+  const uint32_t rowa = sw + lane * 64;
+  const uint32_t x = (lane >> 1) & 3;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) st_shared_v4(rowa + ((i ^ x) << 4), v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+  fence_proxy_async_smem();
+  __syncwarp();
+  if (lane == 0 && any_valid) {
+    tma_store_3d(map, reinterpret_cast<const void*>(__cvta_shared_to_generic(sw)), c0, t0, b);
+    bulk_commit_group();
+  }
+}
+
+__device__ __forceinline__ void grp_epilogue_gate(const LayerParams& p, uint32_t taddr, int idx, int b, int tw0, int half, int lane,
+                                                  uint32_t sw) {
+  const float* bias = p.bias1 + idx * 256;
+#pragma unroll 1
+  for (int c = half; c < 4; c += 2) {
+    uint32_t g[32], f[32];
+    tmem_ld_32x32(taddr + c * 32, g);
+    tmem_ld_32x32(taddr + 128 + c * 32, f);
+    float bg[32], bf[32];
+    ld_f32x32(bias + c * 32, bg);
+    ld_f32x32(bias + 128 + c * 32, bf);
+    tmem_ld_wait();
+    uint32_t zp[16];
+#pragma unroll
+    for (int q = 0; q < 16; ++q) {
+      float z2[2];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const float gj = __uint_as_float(g[2 * q + h]) + bg[2 * q + h];
+        const float fj = __uint_as_float(f[2 * q + h]) + bf[2 * q + h];
+        z2[h] = fmaf(0.5f, tanh_approx(0.5f * gj), 0.5f) * tanh_approx(fj);
+      }
+      zp[q] = pack_bf16(z2[0], z2[1]);
+    }
+    grp_store_tile(&p.tmZs, sw, lane, zp, p.z_c0 + idx * 128 + c * 32, tw0, b, tw0 < p.T);
+  }
+}
+
+__device__ __forceinline__ void grp_epilogue_res(const LayerParams& p, uint32_t taddr, int idx, int b, int tw0, size_t row, int half,
+                                                 int lane, uint32_t sw) {
+  const int n0 = idx * 256;
+  const float* rv = p.rvec + static_cast<size_t>(b) * p.vec_bstride + n0;
+  const __nv_bfloat16* xin = p.x_in + row * (p.kb_c * 64) + n0;
+  uint4 xq[4];
+  ld_x4(xin + half * 32, xq);
+#pragma unroll 1
+  for (int c = half; c < 8; c += 2) {
+    uint32_t a[32];
+    tmem_ld_32x32(taddr + c * 32, a);
+    float rr[32];
+    ld_f32x32(rv + c * 32, rr);
+    uint4 xn[4];
+    if (c + 2 < 8) ld_x4(xin + (c + 2) * 32, xn);
+    tmem_ld_wait();
+    uint32_t o[16];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint32_t w[4] = {xq[i].x, xq[i].y, xq[i].z, xq[i].w};
+#pragma unroll
+      for (int h = 0; h < 4; ++h) {
+        const int q = 8 * i + 2 * h;
+        const float v0 = fmaf(__uint_as_float(a[q]) + __uint_as_float(w[h] << 16), 0.70710678118654752f, rr[q]);
+        const float v1 = fmaf(__uint_as_float(a[q + 1]) + __uint_as_float(w[h] & 0xffff0000u), 0.70710678118654752f, rr[q + 1]);
+        o[4 * i + h] = pack_bf16(v0, v1);
+      }
+    }
+    grp_store_tile(&p.tmXs, sw, lane, o, n0 + c * 32, tw0, b, tw0 < p.T);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) xq[i] = xn[i];
+  }
 }
 
 // Requires C % 256 == 0, H % 128 == 0 (two-block 1x1 stages) and 2^(cycle-1) <= 16.  LayerParams as for the halo kernel;
@@ -44,6 +128,7 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
   uint64_t* tmem_empty = tmem_full + 2;       // leader: 16 warp arrivals (8 per CTA)
   uint64_t* z_full = tmem_empty + 2;          // per CTA
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(z_full + 1);
+  uint8_t* warp_stage = reinterpret_cast<uint8_t*>(bars) + 2048;  // 8 x kGrpWarpStage, 2 KB aligned (stage_bytes % 2048 == 0)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -91,8 +176,12 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
       uint32_t ph = 0;
       auto begin_stage = [&](uint32_t bytes_per_cta) -> uint8_t* {
         mbar_wait(&empty[st], ph ^ 1);
-        if (leader) mbar_arrive_expect_tx(&full[st], 2 * bytes_per_cta);
-        else mbar_arrive_cluster(&full[st], 0);
+        if (leader) {
+          if (p.dbg & 2) mbar_arrive(&full[st]);  // debug: barriers only, no bytes
+          else mbar_arrive_expect_tx(&full[st], 2 * bytes_per_cta);
+        } else {
+          mbar_arrive_cluster(&full[st], 0);
+        }
         return smem + st * stage_bytes;
       };
       auto end_stage = [&]() { if (++st == NS) { st = 0; ph ^= 1; } };
@@ -101,7 +190,7 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
         for (int k = 0; k < nblk; k += 2) {
           const int n = nblk - k < 2 ? nblk - k : 2;
           uint8_t* s = begin_stage(n * (kOne + kPairBBytes));
-          for (int j = 0; j < n; ++j) {
+          for (int j = 0; j < n && !(p.dbg & 2); ++j) {
             tma_load_3d_pair(am, &full[st], s + j * kOne, ac0 + (k + j) * 64, t0, b);
             tma_load_2d_pair(wm, &full[st], s + 2 * kOne + j * kPairBBytes, wk0 + (k + j) * 64, row0);
           }
@@ -118,9 +207,9 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
           const int row0 = p.w1_row0 + idx * 256 + rank * 128;
           for (int cb = 0; cb < p.kb_c; ++cb) {
             uint8_t* s = begin_stage(halo_bytes + 3 * kPairBBytes);
-            tma_load_3d_pair(&p.tmXh, &full[st], s, cb * 64, t0 - p.dil, b);
+            if (!(p.dbg & 2)) tma_load_3d_pair(&p.tmXh, &full[st], s, cb * 64, t0 - p.dil, b);
 #pragma unroll
-            for (int tap = 0; tap < 3; ++tap)
+            for (int tap = 0; tap < 3 && !(p.dbg & 2); ++tap)
               tma_load_2d_pair(&p.tmW1, &full[st], s + p.a_slot + tap * kPairBBytes, (tap * p.kb_c + cb) * 64, row0);
             end_stage();
           }
@@ -140,6 +229,7 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
       uint32_t ph = 0;
       uint32_t acc_it = 0;
       auto mma4 = [&](uint32_t tmem_d, uint64_t da, uint64_t db, bool fresh) {
+        if (p.dbg & 4) return;  // debug: commits only
 #pragma unroll
         for (int k = 0; k < 4; ++k) umma_bf16_pair(tmem_d, da + 2 * k, db + 2 * k, idesc, (!fresh) || k != 0);
       };
@@ -204,8 +294,14 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
       mbar_wait(&tmem_full[as], (acc_it >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = lane_addr + as * 256;
-      if (kind == 0) pair_epilogue_gate(p, taddr, idx, row, valid, half);
-      else pair_epilogue_res(p, taddr, idx, b, row, valid, half);
+      const int tw0 = (tile % p.tiles_t) * 256 + rank * 128 + quad * 32;  // first frame of this warp's 32 rows
+      const uint32_t sw = smem_u32(warp_stage + (warp - 4) * kGrpWarpStage);
+      if (p.dbg & 1) {  // debug: epilogue warps only hand the accumulator back
+      } else if (kind == 0) {
+        grp_epilogue_gate(p, taddr, idx, b, tw0, half, lane, sw);
+      } else {
+        grp_epilogue_res(p, taddr, idx, b, tw0, row, half, lane, sw);
+      }
       // release the accumulator on the LEADER's barrier: one arrival per warp
       tc_fence_before();
       __syncwarp();
@@ -214,13 +310,13 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
         else mbar_arrive_cluster(&tmem_empty[as], 0);
       }
       if (kind == 0 && idx == p.p1 - 1 && p.p2 > 0) {
-        __threadfence();             // z stores reach L2 ...
-        fence_proxy_async_global();  // ... and are ordered before the TMA (async proxy) re-read
+        bulk_wait_all();  // this warp's TMA stores of z are complete before the producer's TMA re-reads them
         mbar_arrive(z_full);
       }
       ++acc_it;
     }
   }
+  if (warp >= 4) bulk_wait_all();  // staging tiles are read out before the CTA's shared memory goes away
   tc_fence_before();
   cluster_sync_all();  // the leader's MMAs read this CTA's shared memory and write its TMEM until the very end
   if (warp == 2) {

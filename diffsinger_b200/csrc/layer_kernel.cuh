@@ -41,6 +41,9 @@ struct LayerParams {
   CUtensorMap tmXh;
   uint32_t a_slot;
   int n_a;
+  // grouped-stage variant (layer4_kernel.cuh): TMA STORE maps (box 32 channels x 32 frames, SWIZZLE_64B) of the
+  // gated-activation store and of x_out -- the epilogue warps stage their 32 x 32 sub-tiles in shared memory
+  CUtensorMap tmZs, tmXs;
 };
 
 constexpr uint32_t kLayerABytes = 128 * 128;  // 128 frames x 64 bf16
