@@ -1,10 +1,12 @@
 """Glue between the sampler classes and the native session (device-memory plumbing only)."""
 from __future__ import annotations
 
+import os
 from typing import List
 
 import torch
 
+from .. import _native as nat
 from ..engine import Program
 
 
@@ -12,6 +14,29 @@ def to_time_major(x: torch.Tensor) -> torch.Tensor:
     """[B, F, M, T] -> contiguous time-major [B, T, F*M] fp32 (the layout every kernel uses)."""
     B, F, M, T = x.shape
     return x.reshape(B, F * M, T).transpose(1, 2).contiguous().float()
+
+
+def max_chunk_batch(eng, B: int, T: int, n_bufs: int, n_times: int) -> int:
+    """Largest per-launch batch whose session workspace + sampler buffers fit the device (the gated-activation store
+    alone is L*C*2 bytes per frame: 20 KB at C=512, L=20, so B=1024 x T=8000 would need 168 GB).  Utterances are
+    independent end to end, so a big batch is simply run as consecutive chunks through the same session and graph.
+    DSB200_MAX_FRAMES (frames per chunk) overrides the memory probe (used by the tests)."""
+    cap = os.environ.get("DSB200_MAX_FRAMES")
+    if cap:
+        return max(1, min(B, int(cap) // T))
+    key = (B, T, False)
+    if key in eng.sessions:  # already allocated: it fits
+        return B
+    per_utt = nat.lib().ds_session_workspace_bytes(eng.plan, 1, T, max(n_times, 64), 0) + n_bufs * T * eng.FM * 4
+    free, _total = torch.cuda.mem_get_info(eng.device)
+    free += torch.cuda.memory_reserved(eng.device) - torch.cuda.memory_allocated(eng.device)
+    fit = int(0.8 * free) // max(per_utt, 1)
+    if fit < 1:
+        raise RuntimeError(f"not enough device memory for one utterance of {T} frames ({per_utt} bytes needed)")
+    if fit >= B:
+        return B
+    n_chunks = -(-B // fit)
+    return -(-B // n_chunks)  # equal-sized chunks: one session / graph serves all but possibly the last
 
 
 @torch.no_grad()
@@ -26,6 +51,18 @@ def run_program(backbone, prog: Program, x_tm: torch.Tensor, cond_bht: torch.Ten
         raise TypeError("run_program needs the diffsinger_b200 WaveNet backbone (native engine)")
     eng = backbone.engine()
     B, T, FM = x_tm.shape
+    bc = max_chunk_batch(eng, B, T, prog.n_bufs, len(prog.times))
+    if bc >= B:
+        return _run_chunk(eng, prog, x_tm, cond_bht, extra, use_graph).clone()
+    out = torch.empty_like(x_tm)
+    for lo in range(0, B, bc):
+        hi = min(B, lo + bc)
+        out[lo:hi] = _run_chunk(eng, prog, x_tm[lo:hi], cond_bht[lo:hi], [e[lo:hi] for e in extra], use_graph)
+    return out
+
+
+def _run_chunk(eng, prog: Program, x_tm, cond_bht, extra, use_graph) -> torch.Tensor:
+    B, T, FM = x_tm.shape
     sess = eng.session(B, T, max_times=len(prog.times), per_sample=False)
     bufs = sess_buffers(sess, prog.n_bufs)
     bufs[0].copy_(x_tm)
@@ -35,7 +72,7 @@ def run_program(backbone, prog: Program, x_tm: torch.Tensor, cond_bht: torch.Ten
     sess.set_times(torch.tensor(prog.times, dtype=torch.float32))
     # 1000-step ancestral programs would make ~45k-node graphs; launch those eagerly
     sess.run(prog, bufs, use_graph=use_graph and len(prog.ops) <= 1024)
-    return bufs[0].clone()
+    return bufs[0]
 
 
 def sess_buffers(sess, n: int):

@@ -170,3 +170,40 @@ def test_graph_replay_is_deterministic_and_counts_launches():
     sess = next(iter(m.velocity_fn.engine().sessions.values()))
     L = cfg["num_layers"]
     assert sess.last_launches == 20 * (2 * L + 4 + 1)  # C=64: unfused layers
+
+
+def test_batch_chunking_is_bitwise_identical(monkeypatch):
+    """Big batches are run as consecutive chunks when the workspace would not fit (runtime.max_chunk_batch); utterances are
+    independent end to end (no cross-sample op, wavenet.py:33-48), so chunked == unchunked bit for bit."""
+    M, F, L, C, H, cycle, B, T = 128, 1, 4, 256, 256, 4, 5, 150
+    sd = random_state_dict(M, F, L, C, H, seed=9)
+    ds.hparams.clear()
+    ds.hparams.update(hidden_size=H, schedule_type="linear", use_shallow_diffusion=False, diff_accelerator="dpm-solver",
+                      diff_speedup=100, K_step=1000, K_step_infer=1000, timesteps=1000)
+    m = ds.GaussianDiffusion(M, F, 1000, 1000, "wavenet", dict(num_layers=L, num_channels=C, dilation_cycle_length=cycle),
+                             spec_min=[-12.0], spec_max=[0.0])
+    m.denoise_fn.load_state_dict(sd)
+    m = m.eval().to(dev)
+    cond = torch.randn(B, T, H, generator=torch.Generator().manual_seed(1)).to(dev)
+    outs = []
+    for cap in (None, str(2 * T), str(T)):
+        if cap is None:
+            monkeypatch.delenv("DSB200_MAX_FRAMES", raising=False)
+        else:
+            monkeypatch.setenv("DSB200_MAX_FRAMES", cap)
+        torch.manual_seed(3)
+        with torch.no_grad():
+            outs.append(m(cond, infer=True).cpu())
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+    # ... and a shard of the batch run on its own (what another rank would do) gives the same rows
+    monkeypatch.delenv("DSB200_MAX_FRAMES", raising=False)
+    real = torch.randn
+    torch.manual_seed(3)
+    full_noise = real(B, F, M, T, device=dev)
+    torch.randn = lambda *a, **k: full_noise[1:3].clone()
+    try:
+        with torch.no_grad():
+            part = m(cond[1:3], infer=True).cpu()
+    finally:
+        torch.randn = real
+    assert torch.equal(part, outs[0][1:3])
