@@ -231,6 +231,11 @@ struct ds_plan {
   bool packed_ok = false;
   CUtensorMap tm_whead, tm_w1, tm_w2, tm_wsk, tm_wsp, tm_wout;
   CUtensorMap tm_w1h, tm_w2h;  // 128-row boxes: each CTA of a pair loads half of a 256-row weight tile
+  // "small problem" path (a session with too few frame tiles to fill the SMs runs the unfused GEMMs with narrow N tiles so
+  // that the work spreads over output channels instead): second gate pack permuted for 128-row passes + narrow-box maps
+  int has_small;
+  size_t o_w1s, o_b1s;
+  CUtensorMap tm_w1s, tm_w2s, tm_wsks, tm_wsps, tm_wheads;
 };
 
 static void plan_layout(ds_plan* p) {
@@ -261,6 +266,11 @@ static void plan_layout(ds_plan* p) {
   p->o_mlp2b = take(C * 4);
   p->o_wd = take(L * C * C * 4);
   p->o_bd = take(L * C * 4);
+  p->o_w1s = p->o_b1s = 0;
+  if (p->has_small) {
+    p->o_w1s = take(L * 2 * C * p->K1 * 2);
+    p->o_b1s = take(L * 2 * C * 4);
+  }
   p->packed_bytes = off;
 }
 
@@ -315,6 +325,7 @@ extern "C" int ds_plan_create(const ds_wavenet_config* cfg, ds_plan** out) {
   }
   p->S = p->split ? 2 : 1;
   if (p->split) p->fused = 0;
+  p->has_small = (!p->split && p->BN_G == 256) ? 1 : 0;
   plan_layout(p);
   *out = p;
   return 0;
@@ -367,6 +378,10 @@ extern "C" int ds_plan_pack_weights(ds_plan* p, const ds_wavenet_weights* w, voi
     pack_matrix_kernel<<<ew_grid((long)C * C, TH), TH, 0, st>>>(bf(p->o_wsk) + (size_t)l * C, C, C, (long)L * C * S,
                                                                 w->layer_output_projection_weight[l] + (size_t)C * C, C, C, C, 1, lo((long)L * C));
     accum_kernel<<<ceil_div(C, TH), TH, 0, st>>>(f32(p->o_bsk), w->layer_output_projection_bias[l] + C, C);
+    if (p->has_small)
+      pack_gate_kernel<<<ew_grid((long)2 * C * p->K1, TH), TH, 0, st>>>(
+          bf(p->o_w1s) + (size_t)l * 2 * C * p->K1, f32(p->o_b1s) + (size_t)l * 2 * C, w->dilated_conv_weight[l], w->dilated_conv_bias[l],
+          w->conditioner_projection_weight[l], w->conditioner_projection_bias[l], C, H, 128, (long)p->K1, 0L);
     CUDA_TRY(cudaMemcpyAsync(f32(p->o_wd) + (size_t)l * C * C, w->diffusion_projection_weight[l], (size_t)C * C * 4, cudaMemcpyDeviceToDevice, st));
     CUDA_TRY(cudaMemcpyAsync(f32(p->o_bd) + (size_t)l * C, w->diffusion_projection_bias[l], (size_t)C * 4, cudaMemcpyDeviceToDevice, st));
   }
@@ -382,6 +397,13 @@ extern "C" int ds_plan_pack_weights(ds_plan* p, const ds_wavenet_weights* w, voi
   DS_TRY(make_weight_map(&p->tm_wsk, base + p->o_wsk, L * C * Sm, C, p->BN_C));
   DS_TRY(make_weight_map(&p->tm_wsp, base + p->o_wsp, C * Sm, C, p->BN_C));
   DS_TRY(make_weight_map(&p->tm_wout, base + p->o_wout, C * Sm, p->FMr, p->BN_O));
+  if (p->has_small) {
+    DS_TRY(make_weight_map(&p->tm_w1s, base + p->o_w1s, p->K1, L * 2 * C, 128));
+    DS_TRY(make_weight_map(&p->tm_w2s, base + p->o_w2, C, L * C, 64));
+    DS_TRY(make_weight_map(&p->tm_wsks, base + p->o_wsk, L * C, C, 64));
+    DS_TRY(make_weight_map(&p->tm_wsps, base + p->o_wsp, C, C, 64));
+    DS_TRY(make_weight_map(&p->tm_wheads, base + p->o_whead, p->FMp, C, 64));
+  }
   p->packed_ok = true;
   return 0;
 }
@@ -406,6 +428,7 @@ struct ds_session {
   std::map<std::string, GraphEntry> graphs;
   int64_t last_launches = 0;
   bool cond_set = false;
+  bool small = false;  // too few frame tiles to fill the SMs: unfused GEMMs with narrow N tiles (plan->has_small)
 };
 
 static void session_layout(const ds_plan* p, int B, int T, int max_times, int per_sample, ds_session* s) {
@@ -456,6 +479,13 @@ extern "C" int ds_session_create(ds_plan* plan, int32_t B, int32_t T, int32_t ma
     return fail(DS_ERR_INVALID, "workspace too small: %zu < %zu", workspace_bytes, need);
   }
   s->ws = (uint8_t*)workspace;
+  {
+    // one CTA pair of the fused layer kernel owns a 256-frame tile and walks ALL output channels of it serially
+    // (~35 us at C=512); below ~1/4 occupancy of the 74 pairs it is faster to spread over output channels instead
+    const char* se = getenv("DSB200_SMALL");
+    const int pair_tiles = B * ceil_div(T, 256);
+    s->small = plan->has_small && (se ? atoi(se) != 0 : pair_tiles * 4 <= g_num_sms / 2);
+  }
   int r = 0;
   const int Sm = plan->S;
   r = r ? r : make_act_map(&s->tm_cond, s->ws + s->o_cond, plan->H * Sm, T, B);
@@ -587,6 +617,9 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
 
   const int S = p->S;
   const bool split = p->split != 0;
+  const bool small = s->small;  // narrow N tiles, unfused layers (see ds_session_create)
+  const int bnG = small ? 128 : p->BN_G, bnC = small ? 64 : p->BN_C;
+  const float* bias1 = (const float*)(pk + (small ? p->o_b1s : p->o_b1));
   f32_to_bf16_pad_kernel<<<ew_grid(rows * p->FMp / 4, 256), 256, 0, st>>>(xb, x, rows, p->FM, p->FMp, (long)p->FMp * S, split ? p->FMp : 0);
   CUDA_TRY(cudaGetLastError());
   ++*launches;
@@ -599,15 +632,15 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
     g.total_tiles = B * tiles_t * n_tiles;
   };
   // head: relu(input_projection(x)) (+ d_0 so that layer 0 reads x + d directly)      wavenet.py:86-88,36
-  g.tmA0 = s->tm_xb; g.tmB = p->tm_whead;
+  g.tmA0 = s->tm_xb; g.tmB = small ? p->tm_wheads : p->tm_whead;
   g.a0_c0 = 0; g.kb_a0 = p->FMp / 64; g.n_taps = 1; g.dil = 0; g.kb_a1 = 0; g.b_row0 = 0;
   g.relu = 1; g.bias = (const float*)(pk + p->o_bhead); g.vec_add = dtab; g.vec_sub = nullptr;
   g.out = xt; g.ld_out = C * S; g.out_c0 = 0;
   g.a0_lo = p->FMp; g.w_lo = p->FMp; g.out_lo = C;  // lo-half offsets: only read by the split instantiations
-  shape(C / p->BN_C);
-  DS_TRY(launch_gemm(p->BN_C, EPI_LINEAR, g, st, split));
+  shape(C / bnC);
+  DS_TRY(launch_gemm(bnC, EPI_LINEAR, g, st, split));
   ++*launches;
-  if (p->fused) {
+  if (p->fused && !small) {
     for (int l = 0; l < L; ++l) {
       DS_TRY(session_fused_layer(s, l, time_index, st));
       ++*launches;
@@ -615,45 +648,45 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   } else {
   for (int l = 0; l < L; ++l) {
     // gate GEMM: dilated conv (3 taps) + conditioner projection, sigmoid*tanh epilogue   wavenet.py:35-42
-    g.tmA0 = s->tm_xt; g.tmA1 = s->tm_cond; g.tmB = p->tm_w1;
+    g.tmA0 = s->tm_xt; g.tmA1 = s->tm_cond; g.tmB = small ? p->tm_w1s : p->tm_w1;
     g.a0_c0 = 0; g.kb_a0 = C / 64; g.n_taps = 3; g.dil = 1 << (l % p->cfg.dilation_cycle_length); g.kb_a1 = p->H / 64;
-    g.b_row0 = l * 2 * C; g.relu = 0; g.bias = (const float*)(pk + p->o_b1) + (size_t)l * 2 * C;
+    g.b_row0 = l * 2 * C; g.relu = 0; g.bias = bias1 + (size_t)l * 2 * C;
     g.vec_add = nullptr; g.vec_sub = nullptr;
     g.out = z; g.ld_out = L * C * S; g.out_c0 = l * C;
     g.a0_lo = C; g.a1_lo = p->H; g.w_lo = p->K1; g.out_lo = L * C;
-    shape(2 * C / p->BN_G);
-    DS_TRY(launch_gemm(p->BN_G, EPI_GATE, g, st, split));
+    shape(2 * C / bnG);
+    DS_TRY(launch_gemm(bnG, EPI_GATE, g, st, split));
     ++*launches;
     if (l + 1 < L) {
       // residual half of output_projection + (x + res)/sqrt(2)                          wavenet.py:44-48
       // (the last layer's residual is never used, wavenet.py:92-94, so it is not computed)
-      g.tmA0 = s->tm_z; g.tmB = p->tm_w2;
+      g.tmA0 = s->tm_z; g.tmB = small ? p->tm_w2s : p->tm_w2;
       g.a0_c0 = l * C; g.kb_a0 = C / 64; g.n_taps = 1; g.dil = 0; g.kb_a1 = 0; g.b_row0 = l * C;
       g.bias = nullptr; g.vec_sub = nullptr; g.vec_add = rtab + (size_t)l * C;
       g.res_in = xt; g.ld_res = C * S; g.out = xt; g.ld_out = C * S; g.out_c0 = 0;
       g.a0_lo = L * C; g.w_lo = C; g.out_lo = C; g.res_lo = C;
-      shape(C / p->BN_C);
-      DS_TRY(launch_gemm(p->BN_C, EPI_RES, g, st, split));
+      shape(C / bnC);
+      DS_TRY(launch_gemm(bnC, EPI_RES, g, st, split));
       ++*launches;
     }
   }
   }
   // deferred skip: sum_l skip_l = [z_0 | ... | z_{L-1}] x [Wskip_0 | ... | Wskip_{L-1}]^T, accumulated in TMEM;
   // then / sqrt(L)                                                                       wavenet.py:44-48,96
-  g.tmA0 = s->tm_z; g.tmB = p->tm_wsk;
+  g.tmA0 = s->tm_z; g.tmB = small ? p->tm_wsks : p->tm_wsk;
   g.a0_c0 = 0; g.kb_a0 = L * C / 64; g.n_taps = 1; g.kb_a1 = 0; g.b_row0 = 0; g.relu = 0;
   g.scale = 1.0f / sqrtf((float)L);
   g.bias = (const float*)(pk + p->o_bsk); g.vec_add = nullptr; g.vec_sub = nullptr; g.res_in = nullptr;
   g.out = s1; g.ld_out = C * S; g.out_c0 = 0;
   g.a0_lo = L * C; g.w_lo = L * C; g.out_lo = C;
-  shape(C / p->BN_C);
-  DS_TRY(launch_gemm(p->BN_C, EPI_LINEAR, g, st, split));
+  shape(C / bnC);
+  DS_TRY(launch_gemm(bnC, EPI_LINEAR, g, st, split));
   ++*launches;
   // relu(skip_projection)                                                                wavenet.py:97-98
-  g.tmA0 = s->tm_s1; g.tmB = p->tm_wsp; g.kb_a0 = C / 64; g.relu = 1; g.scale = 1.0f;
+  g.tmA0 = s->tm_s1; g.tmB = small ? p->tm_wsps : p->tm_wsp; g.kb_a0 = C / 64; g.relu = 1; g.scale = 1.0f;
   g.bias = (const float*)(pk + p->o_bsp); g.out = s2;
   g.a0_lo = C; g.w_lo = C;
-  DS_TRY(launch_gemm(p->BN_C, EPI_LINEAR, g, st, split));
+  DS_TRY(launch_gemm(bnC, EPI_LINEAR, g, st, split));
   ++*launches;
   // output_projection -> fp32 [B][T][F*M]                                                 wavenet.py:99
   g.tmA0 = s->tm_s2; g.tmB = p->tm_wout; g.relu = 0;
@@ -792,7 +825,7 @@ extern "C" int ds_debug_gemm(const ds_gemm_desc* d, void* stream) {
 // (whatever the last evaluation left there), for per-kernel CUDA-event timing.
 extern "C" int ds_debug_layer(ds_session* s, int32_t layer, int32_t time_index, void* stream) {
   if (!s) return fail(DS_ERR_INVALID, "null argument");
-  if (!s->plan->fused) return fail(DS_ERR_STATE, "the plan runs the unfused two-GEMM layer path");
+  if (!s->plan->fused || s->small) return fail(DS_ERR_STATE, "this session runs the unfused two-GEMM layer path");
   if (layer < 0 || layer >= s->plan->L) return fail(DS_ERR_INVALID, "layer %d out of range", layer);
   DS_TRY(check_eval_ready(s, time_index));
   return session_fused_layer(s, layer, time_index, (cudaStream_t)stream);
