@@ -162,7 +162,7 @@ def measured_traffic(kernel):
 def run_native(args, rank, world, local_rank):
     import torch.distributed as dist
     import diffsinger_b200 as ds
-    from oracle.wavenet_oracle import random_state_dict  # synthetic weights only (test infrastructure helper)
+    from diffsinger_b200.synthetic import random_state_dict
     c = CFG
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)

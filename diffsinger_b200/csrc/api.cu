@@ -235,6 +235,7 @@ struct ds_plan {
   // that the work spreads over output channels instead): second gate pack permuted for 128-row passes + narrow-box maps
   int has_small;
   size_t o_w1s, o_b1s;
+  size_t o_b1h;  // f16 gate bias for the packed-half gate epilogue of the grouped kernel
   CUtensorMap tm_w1s, tm_w2s, tm_wsks, tm_wsps, tm_wheads;
 };
 
@@ -266,6 +267,7 @@ static void plan_layout(ds_plan* p) {
   p->o_mlp2b = take(C * 4);
   p->o_wd = take(L * C * C * 4);
   p->o_bd = take(L * C * 4);
+  p->o_b1h = take(L * 2 * C * 2);
   p->o_w1s = p->o_b1s = 0;
   if (p->has_small) {
     p->o_w1s = take(L * 2 * C * p->K1 * 2);
@@ -378,6 +380,7 @@ extern "C" int ds_plan_pack_weights(ds_plan* p, const ds_wavenet_weights* w, voi
     pack_matrix_kernel<<<ew_grid((long)C * C, TH), TH, 0, st>>>(bf(p->o_wsk) + (size_t)l * C, C, C, (long)L * C * S,
                                                                 w->layer_output_projection_weight[l] + (size_t)C * C, C, C, C, 1, lo((long)L * C));
     accum_kernel<<<ceil_div(C, TH), TH, 0, st>>>(f32(p->o_bsk), w->layer_output_projection_bias[l] + C, C);
+    bias_half_kernel<<<ceil_div(2 * C, TH), TH, 0, st>>>((uint16_t*)(base + p->o_b1h) + (size_t)l * 2 * C, f32(p->o_b1) + (size_t)l * 2 * C, 2 * C, p->BN_G);
     if (p->has_small)
       pack_gate_kernel<<<ew_grid((long)2 * C * p->K1, TH), TH, 0, st>>>(
           bf(p->o_w1s) + (size_t)l * 2 * C * p->K1, f32(p->o_b1s) + (size_t)l * 2 * C, w->dilated_conv_weight[l], w->dilated_conv_bias[l],
@@ -587,6 +590,7 @@ static int session_fused_layer(ds_session* s, int l, int time_index, cudaStream_
     lp.tmXh = s->tm_xh[l & 1][l % p->cfg.dilation_cycle_length];
     lp.a_slot = halo_a_slot_bytes(p->max_dil); lp.n_a = grp_stages(p->max_dil);
     lp.tmZs = s->tm_zs; lp.tmXs = s->tm_xs[(l + 1) & 1];
+    lp.bias1h = (const uint16_t*)(pk + p->o_b1h) + (size_t)l * 2 * C;
     return launch_layer_grp(lp, p->max_dil, st);
   }
   if (p->fused == 4) {

@@ -4,6 +4,7 @@
 #pragma once
 #include <cstdint>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 namespace dsb {
 
@@ -53,6 +54,17 @@ __global__ void pack_gate_kernel(__nv_bfloat16* __restrict__ dst, float* __restr
     dst[r * ld + k] = hi;
     if (lo_off > 0) dst[r * ld + k + lo_off] = __float2bfloat16_rn(v - __bfloat162float(hi));
     if (k == 0) bias_dst[r] = b_dil[src_row] + b_cond[src_row];
+  }
+}
+
+// f16 copy of a packed gate bias (BN-row passes: BN/2 gate rows then BN/2 filter rows); gate entries are pre-multiplied by
+// 0.5 for the sigmoid-by-tanh identity used in the packed-half gate epilogue.
+__global__ void bias_half_kernel(uint16_t* __restrict__ dst, const float* __restrict__ src, int n, int BN) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    const float v = (i % BN < BN / 2) ? 0.5f * src[i] : src[i];
+    const __half h = __float2half_rn(v);
+    dst[i] = *reinterpret_cast<const uint16_t*>(&h);
   }
 }
 

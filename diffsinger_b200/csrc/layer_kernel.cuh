@@ -44,6 +44,7 @@ struct LayerParams {
   // grouped-stage variant (layer4_kernel.cuh): TMA STORE maps (box 32 channels x 32 frames, SWIZZLE_64B) of the
   // gated-activation store and of x_out -- the epilogue warps stage their 32 x 32 sub-tiles in shared memory
   CUtensorMap tmZs, tmXs;
+  const uint16_t* bias1h;  // [2C] f16 copy of bias1 in the same packed order, gate entries pre-multiplied by 0.5
 };
 
 constexpr uint32_t kLayerABytes = 128 * 128;  // 128 frames x 64 bf16

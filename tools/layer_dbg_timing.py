@@ -10,7 +10,7 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import diffsinger_b200 as ds  # noqa: E402
 from diffsinger_b200 import _native as nat  # noqa: E402
-from oracle.wavenet_oracle import random_state_dict  # noqa: E402  (synthetic weights only)
+from diffsinger_b200.synthetic import random_state_dict  # noqa: E402
 
 
 def main():

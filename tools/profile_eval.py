@@ -5,7 +5,7 @@ import sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch  # noqa: E402
 import diffsinger_b200 as ds  # noqa: E402
-from oracle.wavenet_oracle import random_state_dict  # noqa: E402
+from diffsinger_b200.synthetic import random_state_dict  # noqa: E402
 
 B, T, C, L = int(os.environ.get("PB", 64)), int(os.environ.get("PT", 2000)), 512, 20
 ds.hparams.update(hidden_size=256, schedule_type="linear", use_shallow_diffusion=False, diff_accelerator="dpm-solver",

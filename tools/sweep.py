@@ -11,7 +11,7 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import diffsinger_b200 as ds  # noqa: E402
-from oracle.wavenet_oracle import random_state_dict  # noqa: E402  (synthetic weights only)
+from diffsinger_b200.synthetic import random_state_dict  # noqa: E402
 
 dev = "cuda"
 

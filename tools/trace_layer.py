@@ -6,7 +6,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch  # noqa: E402
 import diffsinger_b200 as ds  # noqa: E402
 from diffsinger_b200 import _native as nat  # noqa: E402
-from oracle.wavenet_oracle import random_state_dict  # noqa: E402
+from diffsinger_b200.synthetic import random_state_dict  # noqa: E402
 
 B, T, C, L = int(os.environ.get("PB", 64)), 2000, 512, 2
 ds.hparams.update(hidden_size=256)
