@@ -88,21 +88,26 @@ __device__ __forceinline__ void grp_epilogue_gate(const LayerParams& p, uint32_t
   }
 }
 
-__device__ __forceinline__ void grp_epilogue_res(const LayerParams& p, uint32_t taddr, int idx, int b, int tw0, size_t row, int half,
-                                                 int lane, uint32_t sw) {
+// Residual epilogue.  `x0` = this lane's first 32-channel chunk of x~ (prefetched by the caller BEFORE it waits for the
+// accumulator: x~ does not depend on the MMAs).  The chunk loop is fully unrolled so that the one-chunk-ahead prefetch of
+// x~ lives in renamed registers (a rolled loop ends in register moves that wait for the prefetch at the END of each
+// iteration -- the top epilogue stall in the ncu source view).
+__device__ __forceinline__ void grp_epilogue_res(const LayerParams& p, uint32_t taddr, int idx, int b, int tw0, const __nv_bfloat16* xin,
+                                                 const uint4 (&x0)[4], int half, int lane, uint32_t sw) {
   const int n0 = idx * 256;
   const float* rv = p.rvec + static_cast<size_t>(b) * p.vec_bstride + n0;
-  const __nv_bfloat16* xin = p.x_in + row * (p.kb_c * 64) + n0;
   uint4 xq[4];
-  ld_x4(xin + half * 32, xq);
-#pragma unroll 1
-  for (int c = half; c < 8; c += 2) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) xq[i] = x0[i];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int c = half + 2 * k;
     uint32_t a[32];
     tmem_ld_32x32(taddr + c * 32, a);
     float rr[32];
     ld_f32x32(rv + c * 32, rr);
     uint4 xn[4];
-    if (c + 2 < 8) ld_x4(xin + (c + 2) * 32, xn);
+    if (k < 3) ld_x4(xin + (c + 2) * 32, xn);
     tmem_ld_wait();
     uint32_t o[16];
 #pragma unroll
@@ -117,8 +122,10 @@ __device__ __forceinline__ void grp_epilogue_res(const LayerParams& p, uint32_t 
       }
     }
     grp_store_tile(&p.tmXs, sw, lane, o, n0 + c * 32, tw0, b, tw0 < p.T);
+    if (k < 3) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) xq[i] = xn[i];
+      for (int i = 0; i < 4; ++i) xq[i] = xn[i];
+    }
   }
 }
 
@@ -301,6 +308,9 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
       const bool valid = t < p.T;
       const size_t row = static_cast<size_t>(b) * p.T + (valid ? t : 0);
       const uint32_t as = acc_it & 1;
+      const __nv_bfloat16* xin = p.x_in + row * (p.kb_c * 64) + idx * 256;
+      uint4 x0[4];
+      if (kind == 1 && !(p.dbg & 1)) ld_x4(xin + half * 32, x0);  // in flight while the chunk's MMAs finish
       mbar_wait(&tmem_full[as], (acc_it >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = lane_addr + as * 256;
@@ -310,7 +320,7 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
       } else if (kind == 0) {
         grp_epilogue_gate(p, taddr, idx, b, tw0, half, lane, sw);
       } else {
-        grp_epilogue_res(p, taddr, idx, b, tw0, row, half, lane, sw);
+        grp_epilogue_res(p, taddr, idx, b, tw0, xin, x0, half, lane, sw);
       }
       // release the accumulator on the LEADER's barrier: one arrival per warp
       tc_fence_before();
