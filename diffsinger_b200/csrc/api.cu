@@ -8,6 +8,7 @@
 #include <cstring>
 #include <map>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/dsb200.h"
@@ -114,6 +115,22 @@ static int make_weight_map(CUtensorMap* m, const void* base, int K, int rows, in
   return 0;
 }
 
+// ------------------------------------------------------------------------------------ launch helper
+// Programmatic dependent launch for the latency-bound small-problem graphs: when t_pdl is set the kernel is launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization, i.e. it may start (prologue only: every such kernel calls
+// grid_dep_wait() before touching global memory) while its predecessor drains.  DSB200_PDL=0 disables it.
+static thread_local bool t_pdl = false;
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = t_pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+}
+
 // ------------------------------------------------------------------------------------ GEMM launch
 template <int BN, int EPI, bool kSplit>
 static int launch_gemm_t(const GemmParams& p, cudaStream_t st) {
@@ -124,8 +141,7 @@ static int launch_gemm_t(const GemmParams& p, cudaStream_t st) {
     attr_done = true;
   }
   const int grid = p.total_tiles < g_num_sms ? p.total_tiles : g_num_sms;
-  kern<<<grid, kGemmThreads, GemmCfg<BN>::kSmemBytes, st>>>(p);
-  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(launch_k(kern, dim3(grid), dim3(kGemmThreads), GemmCfg<BN>::kSmemBytes, st, p));
   return 0;
 }
 
@@ -431,6 +447,7 @@ struct ds_session {
   std::map<std::string, GraphEntry> graphs;
   int64_t last_launches = 0;
   bool cond_set = false;
+  bool pdl = true;     // DSB200_PDL=0 turns programmatic dependent launch off
   bool small = false;  // too few frame tiles to fill the SMs: unfused GEMMs with narrow N tiles (plan->has_small)
 };
 
@@ -488,6 +505,8 @@ extern "C" int ds_session_create(ds_plan* plan, int32_t B, int32_t T, int32_t ma
     const char* se = getenv("DSB200_SMALL");
     const int pair_tiles = B * ceil_div(T, 256);
     s->small = plan->has_small && (se ? atoi(se) != 0 : pair_tiles * 4 <= g_num_sms / 2);
+    const char* pe = getenv("DSB200_PDL");
+    s->pdl = !(pe && atoi(pe) == 0);
   }
   int r = 0;
   const int Sm = plan->S;
@@ -624,8 +643,13 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   const bool small = s->small;  // narrow N tiles, unfused layers (see ds_session_create)
   const int bnG = small ? 128 : p->BN_G, bnC = small ? 64 : p->BN_C;
   const float* bias1 = (const float*)(pk + (small ? p->o_b1s : p->o_b1));
-  f32_to_bf16_pad_kernel<<<ew_grid(rows * p->FMp / 4, 256), 256, 0, st>>>(xb, x, rows, p->FM, p->FMp, (long)p->FMp * S, split ? p->FMp : 0);
-  CUDA_TRY(cudaGetLastError());
+  struct PdlScope {  // small-problem sessions chain their kernels with programmatic dependent launch
+    bool prev;
+    explicit PdlScope(bool on) : prev(t_pdl) { t_pdl = on; }
+    ~PdlScope() { t_pdl = prev; }
+  } pdl_scope((s->small || !s->plan->fused) && s->pdl);
+  CUDA_TRY(launch_k(f32_to_bf16_pad_kernel, dim3(ew_grid(rows * p->FMp / 4, 256)), dim3(256), 0, st, xb, x, rows, p->FM, p->FMp,
+                    (long)p->FMp * S, split ? p->FMp : 0));
   ++*launches;
 
   GemmParams g;
@@ -725,13 +749,17 @@ static int launch_lincomb(float* dst, const float* const* srcs, const float* coe
     a.coef[i] = coefs[i];
   }
   const long n4 = (long)(numel / 4);
-  lincomb_kernel<<<ew_grid(n4, 256), 256, 0, st>>>(dst, a, n4);
-  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(launch_k(lincomb_kernel, dim3(ew_grid(n4, 256)), dim3(256), 0, st, dst, a, n4));
   return 0;
 }
 
 static int run_ops(ds_session* s, const ds_op* ops, int n_ops, float* const* bufs, int n_bufs, cudaStream_t st, int64_t* launches) {
   const size_t numel = (size_t)s->B * s->T * s->plan->FM;
+  struct PdlScope {
+    bool prev;
+    explicit PdlScope(bool on) : prev(t_pdl) { t_pdl = on; }
+    ~PdlScope() { t_pdl = prev; }
+  } pdl_scope((s->small || !s->plan->fused) && s->pdl);
   for (int i = 0; i < n_ops; ++i) {
     const ds_op& op = ops[i];
     if (op.dst < 0 || op.dst >= n_bufs) return fail(DS_ERR_INVALID, "op %d: dst %d out of range", i, op.dst);

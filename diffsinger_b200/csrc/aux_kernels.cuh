@@ -5,6 +5,7 @@
 #include <cstdint>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
+#include "ptx.cuh"
 
 namespace dsb {
 
@@ -139,6 +140,8 @@ __global__ void res_vec_kernel(float* __restrict__ r, const float* __restrict__ 
 // lo_off > 0 (fp32-accurate mode): the residual bf16(v - bf16(v)) goes lo_off elements further along the row.
 __global__ void f32_to_bf16_pad_kernel(__nv_bfloat16* __restrict__ dst, const float* __restrict__ src, long rows, int cols, int ld,
                                        long pitch, int lo_off) {
+  grid_dep_launch();
+  grid_dep_wait();
   const int q = ld / 4;
   const long n = rows * q;
   for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n; i += static_cast<long>(gridDim.x) * blockDim.x) {
@@ -192,6 +195,8 @@ struct LincombArgs {
   int n;
 };
 __global__ void lincomb_kernel(float* __restrict__ dst, LincombArgs a, long n4) {
+  grid_dep_launch();
+  grid_dep_wait();
   for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n4; i += static_cast<long>(gridDim.x) * blockDim.x) {
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll

@@ -106,6 +106,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) ds_gemm_kernel(const __grid_c
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  grid_dep_launch();  // the next kernel may begin its own prologue now ...
+  grid_dep_wait();    // ... and this one touches global memory only after its predecessor has completed
 
   const int num_kb = p.n_taps * p.kb_a0 + p.kb_a1;
 
