@@ -152,6 +152,7 @@ static int launch_gemm(int BN, int epi, const GemmParams& p, cudaStream_t st, bo
   DS_CASE(128, EPI_GATE) DS_CASE(256, EPI_GATE)
   DS_CASE(64, EPI_RES) DS_CASE(128, EPI_RES) DS_CASE(256, EPI_RES)
   DS_CASE(64, EPI_OUTF32) DS_CASE(128, EPI_OUTF32) DS_CASE(256, EPI_OUTF32)
+  DS_CASE(256, EPI_CPROJ)
 #undef DS_CASE
   return fail(DS_ERR_INVALID, "no GEMM instantiation for BN=%d epilogue=%d", BN, epi);
 }
@@ -236,6 +237,8 @@ struct ds_plan {
                          // 5: as 4 with grouped pipeline stages (12 / 8 UMMAs per mbarrier hand-shake)
   int max_dil;
   int fused_stages;
+  int hoist;             // grouped kernel only: the step-invariant conditioner projection is computed once per sampler
+                         // call (ds_session_set_cond) into an f16 buffer and added in the gate epilogue
   int split;             // fp32-accurate mode: every bf16 operand carries a lo half (3 x bf16 split products)
   int S;                 // 2 when split, else 1: width multiplier of every bf16 matrix / activation buffer
   // byte offsets into the packed blob
@@ -344,6 +347,13 @@ extern "C" int ds_plan_create(const ds_wavenet_config* cfg, ds_plan** out) {
   p->S = p->split ? 2 : 1;
   if (p->split) p->fused = 0;
   p->has_small = (!p->split && p->BN_G == 256) ? 1 : 0;
+  {
+    // opt-in (DSB200_HOIST=1): measured on B200 it does NOT pay -- the MMA work drops 12.5 % (281 vs 325 us MMA-side) but
+    // the gate epilogue then reads its 2C f16 values per frame from HBM with per-lane row accesses and becomes the
+    // critical role (epilogue alone 154 -> 210 us), so the kernel stays at ~357 us and the per-call precompute is extra.
+    const char* he = getenv("DSB200_HOIST");
+    p->hoist = (p->fused == 5 && he && atoi(he) == 1) ? 1 : 0;
+  }
   plan_layout(p);
   *out = p;
   return 0;
@@ -439,7 +449,7 @@ struct ds_session {
   int n_times = 0;
   uint8_t* ws;
   // workspace offsets
-  size_t o_cond, o_xb, o_xt, o_xt1, o_z, o_s1, o_s2, o_g, o_d, o_r, o_tmp, ws_bytes;
+  size_t o_cond, o_xb, o_xt, o_xt1, o_z, o_s1, o_s2, o_g, o_d, o_r, o_tmp, o_cproj, ws_bytes;
   CUtensorMap tm_cond, tm_xb, tm_xt, tm_xt1, tm_z, tm_s1, tm_s2;
   CUtensorMap tm_xh[2][5];  // halo maps of the two x~ buffers, one per dilation 2^k (k < 5)
   CUtensorMap tm_zs, tm_xs[2];  // TMA store maps (grouped kernel)
@@ -450,6 +460,16 @@ struct ds_session {
   bool pdl = true;     // DSB200_PDL=0 turns programmatic dependent launch off
   bool small = false;  // too few frame tiles to fill the SMs: unfused GEMMs with narrow N tiles (plan->has_small)
 };
+
+// one CTA pair of the fused layer kernel owns a 256-frame tile and walks ALL output channels of it serially (~35 us at
+// C = 512); below ~1/4 occupancy of the 74 pairs it is faster to spread over output channels instead (unfused GEMMs with
+// narrow N tiles).  DSB200_SMALL=0/1 forces the choice.
+static bool session_is_small(const ds_plan* p, int B, int T) {
+  const char* se = getenv("DSB200_SMALL");
+  const int pair_tiles = B * ceil_div(T, 256);
+  const int sms = g_num_sms ? g_num_sms : 148;
+  return p->has_small && (se ? atoi(se) != 0 : pair_tiles * 4 <= sms / 2);
+}
 
 static void session_layout(const ds_plan* p, int B, int T, int max_times, int per_sample, ds_session* s) {
   const size_t rows = (size_t)B * T;
@@ -473,6 +493,9 @@ static void session_layout(const ds_plan* p, int B, int T, int max_times, int pe
   s->o_d = take(nt * L * C * 4);
   s->o_r = take(nt * L * C * 4);
   s->o_tmp = take(rows * p->FM * 4);
+  // hoisted conditioner projection: f16 [L][rows][2C] (40 KB per frame at C = 512, L = 20); small sessions never use it
+  s->o_cproj = 0;
+  if (p->hoist && !session_is_small(p, B, T)) s->o_cproj = take(rows * L * 2 * C * 2);
   s->ws_bytes = off;
 }
 
@@ -499,12 +522,8 @@ extern "C" int ds_session_create(ds_plan* plan, int32_t B, int32_t T, int32_t ma
     return fail(DS_ERR_INVALID, "workspace too small: %zu < %zu", workspace_bytes, need);
   }
   s->ws = (uint8_t*)workspace;
+  s->small = session_is_small(plan, B, T);
   {
-    // one CTA pair of the fused layer kernel owns a 256-frame tile and walks ALL output channels of it serially
-    // (~35 us at C=512); below ~1/4 occupancy of the 74 pairs it is faster to spread over output channels instead
-    const char* se = getenv("DSB200_SMALL");
-    const int pair_tiles = B * ceil_div(T, 256);
-    s->small = plan->has_small && (se ? atoi(se) != 0 : pair_tiles * 4 <= g_num_sms / 2);
     const char* pe = getenv("DSB200_PDL");
     s->pdl = !(pe && atoi(pe) == 0);
   }
@@ -551,6 +570,24 @@ extern "C" int ds_session_set_cond(ds_session* s, const float* cond_bth, void* s
   f32_to_bf16_pad_kernel<<<ew_grid(rows * H / 4, 256), 256, 0, (cudaStream_t)stream>>>((__nv_bfloat16*)(s->ws + s->o_cond), cond_bth, rows, H, H,
                                                                                        (long)H * s->plan->S, s->plan->split ? H : 0);
   CUDA_TRY(cudaGetLastError());
+  if (s->o_cproj) {
+    // hoisted conditioner projection: cproj[:, l*2C + n] = (W_cond_l * cond + b_dil_l + b_cond_l)[packed n], f16, gate
+    // columns * 0.5 -- L GEMMs over the conditioner K blocks of the packed gate weights            wavenet.py:35,38
+    const ds_plan* p = s->plan;
+    const int C = p->C, L = p->L;
+    GemmParams g;
+    memset(&g, 0, sizeof(g));
+    g.T = s->T; g.B = s->B; g.tiles_t = ceil_div(s->T, 128); g.scale = 1.0f;
+    g.tmA0 = s->tm_cond; g.tmB = p->tm_w1; g.kb_a0 = H / 64; g.n_taps = 1; g.b_k0 = 3 * C;
+    g.n_tiles = 2 * C / 256; g.total_tiles = s->B * g.tiles_t * g.n_tiles;
+    g.ld_out = 2 * C; g.out_c0 = 0;  // layout [L][rows][2C]: one layer's rows are contiguous (2 KB pitch at C = 512)
+    for (int l = 0; l < L; ++l) {
+      g.b_row0 = l * 2 * C;
+      g.out = s->ws + s->o_cproj + (size_t)l * s->B * s->T * 2 * C * 2;
+      g.bias = (const float*)(p->packed + p->o_b1) + (size_t)l * 2 * C;
+      DS_TRY(launch_gemm(256, EPI_CPROJ, g, (cudaStream_t)stream));
+    }
+  }
   s->cond_set = true;
   return 0;
 }
@@ -610,6 +647,10 @@ static int session_fused_layer(ds_session* s, int l, int time_index, cudaStream_
     lp.a_slot = halo_a_slot_bytes(p->max_dil); lp.n_a = grp_stages(p->max_dil);
     lp.tmZs = s->tm_zs; lp.tmXs = s->tm_xs[(l + 1) & 1];
     lp.bias1h = (const uint16_t*)(pk + p->o_b1h) + (size_t)l * 2 * C;
+    if (s->o_cproj) {
+      lp.cproj = (const uint16_t*)(s->ws + s->o_cproj) + (size_t)l * B * T * 2 * C; lp.ld_cproj = 2 * C;
+      lp.kb_h = 0;  // the conditioner K blocks are not run per evaluation
+    }
     return launch_layer_grp(lp, p->max_dil, st);
   }
   if (p->fused == 4) {

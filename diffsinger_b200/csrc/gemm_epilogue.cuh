@@ -77,6 +77,32 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
       }
       if (valid) st_act32<kSplit>(out + c * 32, p.out_lo, z);
     }
+  } else if constexpr (EPI == EPI_CPROJ) {
+    // hoisted conditioner projection (wavenet.py:35, step-invariant): f16 out = (acc + bias) in the gate kernel's packed
+    // column order, gate columns (first half of every BN-column pass) pre-multiplied by 0.5 for sigmoid-by-tanh
+    const int n0 = nt * BN;
+    const float* bias = p.bias + n0;
+    uint16_t* out = reinterpret_cast<uint16_t*>(p.out) + row * p.ld_out + p.out_c0 + n0;
+#pragma unroll 1
+    for (int c = half; c < BN / 32; c += 2) {
+      uint32_t a[32];
+      tmem_ld_32x32(taddr + c * 32, a);
+      float bb[32];
+      ld_f32x32(bias + c * 32, bb);
+      tmem_ld_wait();
+      const float sc = (c * 32 < BN / 2) ? 0.5f : 1.0f;
+      if (valid) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          uint4 q;
+          q.x = pack_f16(sc * (__uint_as_float(a[8 * i + 0]) + bb[8 * i + 0]), sc * (__uint_as_float(a[8 * i + 1]) + bb[8 * i + 1]));
+          q.y = pack_f16(sc * (__uint_as_float(a[8 * i + 2]) + bb[8 * i + 2]), sc * (__uint_as_float(a[8 * i + 3]) + bb[8 * i + 3]));
+          q.z = pack_f16(sc * (__uint_as_float(a[8 * i + 4]) + bb[8 * i + 4]), sc * (__uint_as_float(a[8 * i + 5]) + bb[8 * i + 5]));
+          q.w = pack_f16(sc * (__uint_as_float(a[8 * i + 6]) + bb[8 * i + 6]), sc * (__uint_as_float(a[8 * i + 7]) + bb[8 * i + 7]));
+          reinterpret_cast<uint4*>(out + c * 32)[i] = q;
+        }
+      }
+    }
   } else if constexpr (EPI == EPI_RES) {
     // x~_next = (x~ + R) / sqrt(2) + rvec,  rvec = (b - d_l)/sqrt(2) + d_{l+1}  (folded on the host side of the
     // step-embedding table; wavenet.py:36,44-48).  x~ is prefetched one chunk ahead.

@@ -21,7 +21,7 @@ namespace dsb {
 constexpr int kGemmThreads = 384;  // 4 control warps + 8 epilogue warps (two per TMEM lane quadrant)
 constexpr int kEpiThreads = 256;
 
-enum : int { EPI_LINEAR = 0, EPI_GATE = 1, EPI_RES = 2, EPI_OUTF32 = 3 };
+enum : int { EPI_LINEAR = 0, EPI_GATE = 1, EPI_RES = 2, EPI_OUTF32 = 3, EPI_CPROJ = 4 };
 
 struct GemmParams {
   CUtensorMap tmA0;  // primary activation source  (dims: channels, T, B)
@@ -34,6 +34,7 @@ struct GemmParams {
   int dil;
   int kb_a1;   // 64-wide K blocks from A1
   int b_row0;  // first row of this GEMM inside the packed weight matrix
+  int b_k0;    // first K column of this GEMM inside the packed weight matrix (hoisted conditioner projection: 3C)
   int relu;
   float scale;
   const float* bias;     // indexed by tile-global n (packed order for EPI_GATE)
@@ -138,7 +139,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) ds_gemm_kernel(const __grid_c
             } else {
               tma_load_3d(&p.tmA1, &full[stage], sa, (kb - kb_taps) * 64 + (sub == 1 ? p.a1_lo : 0), t0, b);
             }
-            tma_load_2d(&p.tmB, &full[stage], sb, kb * 64 + (sub == 2 ? p.w_lo : 0), row0);
+            tma_load_2d(&p.tmB, &full[stage], sb, p.b_k0 + kb * 64 + (sub == 2 ? p.w_lo : 0), row0);
             if (++stage == S) {
               stage = 0;
               phase ^= 1;

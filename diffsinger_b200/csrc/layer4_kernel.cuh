@@ -54,20 +54,31 @@ __device__ __forceinline__ void grp_store_tile(const CUtensorMap* map, uint32_t 
 // The fp32 accumulators are rounded to f16 (11-bit mantissa; pre-activations are O(1..10)), everything after that runs two
 // channels per instruction (HFMA2 / MUFU.TANH.F16x2), and z is rounded to bf16 as before -- 11 instructions per channel
 // pair instead of 15, half the MUFU work.  bias1h holds 0.5 * bg (gate) and bf (filter) as f16.
-__device__ __forceinline__ void grp_epilogue_gate(const LayerParams& p, uint32_t taddr, int idx, int b, int tw0, int half, int lane,
-                                                  uint32_t sw) {
-  const uint16_t* bias = p.bias1h + idx * 256;
+// `add` = the f16 row added to the pre-activations: the broadcast bias (bias1h) or, with the conditioner projection hoisted,
+// this lane's row of cproj; (bg0, bf0) = its first chunk, loaded by the caller before it waits for the accumulator.
+__device__ __forceinline__ void grp_load_add(const uint16_t* add, int c, uint4 (&bg)[4], uint4 (&bf)[4]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    bg[i] = __ldg(reinterpret_cast<const uint4*>(add + c * 32) + i);
+    bf[i] = __ldg(reinterpret_cast<const uint4*>(add + 128 + c * 32) + i);
+  }
+}
+__device__ __forceinline__ void grp_epilogue_gate(const LayerParams& p, uint32_t taddr, int idx, int b, int tw0, const uint16_t* add,
+                                                  const uint4 (&bg0)[4], const uint4 (&bf0)[4], int half, int lane, uint32_t sw) {
   constexpr uint32_t kHalf2 = 0x38003800u;  // (0.5h, 0.5h)
-#pragma unroll 1
-  for (int c = half; c < 4; c += 2) {
+  uint4 bg1[4], bf1[4];
+  grp_load_add(add, half + 2, bg1, bf1);  // second chunk's rows: issued first so that an HBM miss hides behind chunk one
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const int c = half + 2 * k;
     uint32_t g[32], f[32];
     tmem_ld_32x32(taddr + c * 32, g);
     tmem_ld_32x32(taddr + 128 + c * 32, f);
     uint4 bg[4], bf[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      bg[i] = __ldg(reinterpret_cast<const uint4*>(bias + c * 32) + i);
-      bf[i] = __ldg(reinterpret_cast<const uint4*>(bias + 128 + c * 32) + i);
+      bg[i] = k == 0 ? bg0[i] : bg1[i];
+      bf[i] = k == 0 ? bf0[i] : bf1[i];
     }
     tmem_ld_wait();
     uint32_t zp[16];
@@ -283,7 +294,7 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
             for (int tap = 0; tap < 3; ++tap)
               mma4(tmem_d, make_kmajor_sw128_desc_row(s, tap * p.dil), make_kmajor_sw128_desc(s + p.a_slot + tap * kPairBBytes),
                    cb == 0 && tap == 0);
-            release(false, as);
+            release(p.kb_h == 0 && cb == p.kb_c - 1, as);
           }
           one_by_one(tmem_d, p.kb_h, false, as);
         } else {
@@ -309,8 +320,12 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
       const size_t row = static_cast<size_t>(b) * p.T + (valid ? t : 0);
       const uint32_t as = acc_it & 1;
       const __nv_bfloat16* xin = p.x_in + row * (p.kb_c * 64) + idx * 256;
-      uint4 x0[4];
-      if (kind == 1 && !(p.dbg & 1)) ld_x4(xin + half * 32, x0);  // in flight while the chunk's MMAs finish
+      uint4 x0[4], bg0[4], bf0[4];
+      const uint16_t* add = p.cproj ? p.cproj + row * p.ld_cproj + idx * 256 : p.bias1h + idx * 256;
+      if (!(p.dbg & 1)) {  // in flight while the job's MMAs finish
+        if (kind == 1) ld_x4(xin + half * 32, x0);
+        else grp_load_add(add, half, bg0, bf0);
+      }
       mbar_wait(&tmem_full[as], (acc_it >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = lane_addr + as * 256;
@@ -318,7 +333,7 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
       const uint32_t sw = smem_u32(warp_stage + (warp - 4) * kGrpWarpStage);
       if (p.dbg & 1) {  // debug: epilogue warps only hand the accumulator back
       } else if (kind == 0) {
-        grp_epilogue_gate(p, taddr, idx, b, tw0, half, lane, sw);
+        grp_epilogue_gate(p, taddr, idx, b, tw0, add, bg0, bf0, half, lane, sw);
       } else {
         grp_epilogue_res(p, taddr, idx, b, tw0, xin, x0, half, lane, sw);
       }

@@ -45,6 +45,10 @@ struct LayerParams {
   // gated-activation store and of x_out -- the epilogue warps stage their 32 x 32 sub-tiles in shared memory
   CUtensorMap tmZs, tmXs;
   const uint16_t* bias1h;  // [2C] f16 copy of bias1 in the same packed order, gate entries pre-multiplied by 0.5
+  // hoisted conditioner projection (grouped kernel): f16 [B][T][ld_cproj = 2C] of THIS layer, packed column order; holds W_cond * cond + b_dil + b_cond (gate half * 0.5), computed once per sampler call.  NULL: not hoisted
+  // (kb_h conditioner K blocks run inside the kernel and bias1h is added instead).
+  const uint16_t* cproj;
+  int ld_cproj;
 };
 
 constexpr uint32_t kLayerABytes = 128 * 128;  // 128 frames x 64 bf16

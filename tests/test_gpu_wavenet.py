@@ -77,24 +77,26 @@ def test_fused_and_unfused_layer_paths_agree(monkeypatch):
     ref = OracleWaveNet(sd, F, cycle)(spec, t, cond)
     outs, launches = [], []
     monkeypatch.setenv("DSB200_SMALL", "0")  # 2 x 391 frames would otherwise take the small-problem path (see below)
-    for mode in ("grp", "halo", "pair", "global", "smem", "unfused"):
-        monkeypatch.setenv("DSB200_LAYER_MODE", mode)
+    for mode in ("grp", "grp+hoist", "halo", "pair", "global", "smem", "unfused"):
+        monkeypatch.setenv("DSB200_LAYER_MODE", mode.split("+")[0])
+        monkeypatch.setenv("DSB200_HOIST", "1" if mode.endswith("hoist") else "0")  # opt-in hoisted conditioner projection
         net = _net(sd, cfg)
         with torch.no_grad():
             outs.append(net(spec.to(dev), t.to(dev), cond.to(dev)).cpu())
         launches.append(next(iter(net.engine().sessions.values())).last_launches)
         assert rel_l2(outs[-1], ref) < EVAL_TOL
-    assert launches == [L + 5] * 5 + [2 * L + 4]
-    assert all(rel_l2(o, outs[5]) < 5e-3 for o in outs[:5])
+    assert launches == [L + 5] * 6 + [2 * L + 4]
+    assert all(rel_l2(o, outs[6]) < 5e-3 for o in outs[:6])
     # small-problem path (default for sessions with few frame tiles): unfused GEMMs with 128/64-wide N tiles and the
     # second gate-weight pack; same results to bf16 round-off
     monkeypatch.delenv("DSB200_LAYER_MODE")
     monkeypatch.delenv("DSB200_SMALL")
+    monkeypatch.delenv("DSB200_HOIST")
     net = _net(sd, cfg)
     with torch.no_grad():
         y = net(spec.to(dev), t.to(dev), cond.to(dev)).cpu()
     assert next(iter(net.engine().sessions.values())).last_launches == 2 * L + 4
-    assert rel_l2(y, ref) < EVAL_TOL and rel_l2(y, outs[5]) < 5e-3
+    assert rel_l2(y, ref) < EVAL_TOL and rel_l2(y, outs[6]) < 5e-3
 
 
 def _diffusion(cls, sd, cfg, **kw):
