@@ -127,7 +127,8 @@ class Session:
 class WaveNetEngine:
     """Plan + packed weights of one WaveNet module on one device; sessions cached per (B, T)."""
 
-    MAX_SESSIONS = 8
+    SESSION_MEM_FRACTION = 0.5  # cached session workspaces never hold more than this share of the device memory
+    MAX_SESSIONS = 32  # config #1 walks ~20 distinct segment lengths; a session of a few hundred frames is a few MB
 
     def __init__(self, module, device: torch.device):
         nat.require_device()
@@ -188,12 +189,16 @@ class WaveNetEngine:
         key = (B, T, per_sample)
         s = self.sessions.get(key)
         if s is not None and s.max_times >= max_times:
+            self.sessions[key] = self.sessions.pop(key)  # most recently used last: eviction below is LRU
             return s
         if s is not None:
             s.close()
             del self.sessions[key]
-        while len(self.sessions) >= self.MAX_SESSIONS:
-            old = next(iter(self.sessions))
+        need = nat.lib().ds_session_workspace_bytes(self.plan, B, T, max(max_times, 64), int(per_sample))
+        budget = self.SESSION_MEM_FRACTION * torch.cuda.get_device_properties(self.device).total_memory
+        while self.sessions and (len(self.sessions) >= self.MAX_SESSIONS
+                                 or need + sum(x.workspace.numel() for x in self.sessions.values()) > budget):
+            old = next(iter(self.sessions))  # least recently used
             self.sessions.pop(old).close()
         s = Session(self, B, T, max(max_times, 64), per_sample)
         self.sessions[key] = s

@@ -1,0 +1,89 @@
+"""Edge cases of the product path on the GPU against the CPU oracle: very short and tile-boundary sequence lengths (shorter
+than the largest dilation; one frame below / at / above the 128- and 256-frame tiles), on the fused CTA-pair kernel and
+on the small-problem GEMM path; ragged batches (each length its own session, padded frames are ordinary frames in the
+reference: SURVEY.md trap T4); argument validation surfacing as NativeError instead of a CPU fallback."""
+import pytest
+import torch
+
+import diffsinger_b200 as ds
+from conftest import rel_l2
+from diffsinger_b200 import _native as nat
+from oracle.wavenet_oracle import OracleWaveNet, random_state_dict
+
+pytestmark = pytest.mark.gpu
+dev = "cuda"
+EVAL_TOL = 2e-2
+
+
+def _net(sd, C, L, cycle, M, F, H=256):
+    ds.hparams.clear()
+    ds.hparams.update(hidden_size=H)
+    net = ds.WaveNet(M, F, num_layers=L, num_channels=C, dilation_cycle_length=cycle)
+    net.load_state_dict(sd, strict=True)
+    return net.eval().to(dev)
+
+
+@pytest.mark.parametrize("small", ["0", "1"])
+@pytest.mark.parametrize("T", [1, 5, 17, 127, 128, 129, 255, 256, 257, 383, 600])
+def test_sequence_length_edges(T, small, monkeypatch):
+    """cycle 5 -> dilations up to 16, so T = 1, 5 sit entirely inside the conv's zero padding."""
+    monkeypatch.setenv("DSB200_SMALL", small)
+    C, L, cycle, M, F, B = 256, 6, 5, 64, 1, 3
+    sd = random_state_dict(M, F, L, C, 256, seed=31)
+    net = _net(sd, C, L, cycle, M, F)
+    g = torch.Generator().manual_seed(T)
+    spec = torch.randn(B, F, M, T, generator=g)
+    cond = torch.randn(B, T, 256, generator=g).transpose(1, 2)
+    t = torch.tensor([250.5])
+    ref = OracleWaveNet(sd, F, cycle)(spec, t, cond)
+    with torch.no_grad():
+        y = net(spec.to(dev), t.to(dev), cond.to(dev)).cpu()
+    assert y.shape == ref.shape and torch.isfinite(y).all()
+    assert rel_l2(y, ref) < EVAL_TOL
+
+
+def test_ragged_lengths_one_session_each():
+    """A ragged set of utterances run one by one (what ds_acoustic.py does with segments): every length gets its own
+    session / graph, results match the oracle per utterance, and re-running an earlier length reuses its session."""
+    C, L, cycle, M, F = 256, 4, 4, 128, 1
+    sd = random_state_dict(M, F, L, C, 256, seed=5)
+    net = _net(sd, C, L, cycle, M, F)
+    oracle = OracleWaveNet(sd, F, cycle)
+    t = torch.tensor([10.0])
+    outs = {}
+    for T in (286, 504, 286, 1197, 504):
+        g = torch.Generator().manual_seed(T)
+        spec = torch.randn(1, F, M, T, generator=g)
+        cond = torch.randn(1, T, 256, generator=g).transpose(1, 2)
+        with torch.no_grad():
+            y = net(spec.to(dev), t.to(dev), cond.to(dev)).cpu()
+        assert rel_l2(y, oracle(spec, t, cond)) < EVAL_TOL
+        if T in outs:
+            assert torch.equal(outs[T], y)
+        outs[T] = y
+    assert len(net.engine().sessions) == 3
+
+
+def test_invalid_arguments_raise():
+    C, L, cycle, M, F = 64, 2, 2, 16, 1
+    sd = random_state_dict(M, F, L, C, 64, seed=1)
+    net = _net(sd, C, L, cycle, M, F, H=64)
+    eng = net.engine()
+    with pytest.raises(nat.NativeError):
+        eng.session(0, 10)
+    with pytest.raises(nat.NativeError):
+        eng.session(1, 0)
+    sess = eng.session(1, 8)
+    x = torch.zeros(1, 8, M, device=dev)
+    with pytest.raises(nat.NativeError, match="set_cond"):
+        sess.forward(x, 0)
+    sess.set_cond(torch.zeros(1, 8, 64, device=dev))
+    with pytest.raises(nat.NativeError, match="time index"):
+        sess.forward(x, 0)
+    # unsupported shapes are rejected at plan creation, not silently emulated
+    ds.hparams.update(hidden_size=64)
+    bad = ds.WaveNet(16, 1, num_layers=2, num_channels=96, dilation_cycle_length=2).to(dev)
+    with pytest.raises(nat.NativeError, match="multiple of 64"):
+        bad.engine()
+    with pytest.raises(RuntimeError, match="no CPU inference path"):
+        ds.WaveNet(16, 1, num_layers=2, num_channels=64, dilation_cycle_length=2).engine()
