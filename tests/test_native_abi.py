@@ -36,8 +36,18 @@ def test_plan_validation_without_device():
     good = nat.WaveNetConfig(128, 1, 20, 512, 4, 256)
     assert L.ds_plan_create(C.byref(good), C.byref(plan)) == 0
     nbytes = L.ds_plan_packed_bytes(plan)
-    # bf16 matrices of the 20x512 net are ~95 MB plus fp32 step-embedding weights
-    assert 90e6 < nbytes < 150e6
+    # bf16 matrices of the 20x512 net are ~95 MB, the second gate pack for the small-problem path
+    # 73 MB, plus fp32 step-embedding weights
+    assert 160e6 < nbytes < 220e6
+    assert L.ds_plan_precision(plan) == 0 and L.ds_plan_layer_mode(plan) == 5
+    # fp32-accurate plan: hi/lo halves of every bf16 matrix, unfused path, no second gate pack
+    p32 = C.c_void_p()
+    assert L.ds_plan_create(C.byref(nat.WaveNetConfig(128, 1, 20, 512, 4, 256, 1)), C.byref(p32)) == 0
+    assert L.ds_plan_precision(p32) == 1 and L.ds_plan_layer_mode(p32) == 0
+    assert 200e6 < L.ds_plan_packed_bytes(p32) < 260e6
+    L.ds_plan_destroy(p32)
+    assert L.ds_plan_create(C.byref(nat.WaveNetConfig(128, 1, 20, 512, 4, 256, 7)), C.byref(p32)) == -1
+    assert b"precision" in L.ds_last_error()
     assert L.ds_session_workspace_bytes(plan, 2, 300, 20, 0) > 2 * 300 * 20 * 512 * 2
     assert L.ds_plan_destroy(plan) == 0
 
