@@ -3,9 +3,10 @@ the WaveNet backbone (BACKBONES['wavenet']) and the GaussianDiffusion / Rectifie
 Host code is Python/PyTorch plumbing over the C ABI in include/dsb200.h (libdsb200.so)."""
 from .hparams import hparams, get_hparams
 from .backbones import BACKBONES, build_backbone, WaveNet
+from .segments import sample_segments
 from .core import (GaussianDiffusion, PitchDiffusion, MultiVarianceDiffusion,
                    RectifiedFlow, PitchRectifiedFlow, MultiVarianceRectifiedFlow)
 
 __all__ = ["hparams", "get_hparams", "BACKBONES", "build_backbone", "WaveNet", "GaussianDiffusion",
            "PitchDiffusion", "MultiVarianceDiffusion", "RectifiedFlow", "PitchRectifiedFlow",
-           "MultiVarianceRectifiedFlow"]
+           "MultiVarianceRectifiedFlow", "sample_segments"]

@@ -24,7 +24,7 @@ def max_chunk_batch(eng, B: int, T: int, n_bufs: int, n_times: int) -> int:
     cap = os.environ.get("DSB200_MAX_FRAMES")
     if cap:
         return max(1, min(B, int(cap) // T))
-    key = (B, T, False)
+    key = (B, T, False, torch.cuda.current_stream().cuda_stream)
     if key in eng.sessions:  # already allocated: it fits
         return B
     per_utt = nat.lib().ds_session_workspace_bytes(eng.plan, 1, T, max(n_times, 64), 0) + n_bufs * T * eng.FM * 4
@@ -69,7 +69,7 @@ def _run_chunk(eng, prog: Program, x_tm, cond_bht, extra, use_graph) -> torch.Te
     for k, e in enumerate(extra):
         bufs[2 + k].copy_(e)
     sess.set_cond(cond_bht.transpose(1, 2))
-    sess.set_times(torch.tensor(prog.times, dtype=torch.float32))
+    sess.set_program_times(prog.times)
     # 1000-step ancestral programs would make ~45k-node graphs; launch those eagerly
     sess.run(prog, bufs, use_graph=use_graph and len(prog.ops) <= 1024)
     return bufs[0]

@@ -91,7 +91,17 @@ class Session:
         n = t.shape[0]
         assert t.numel() == n * (self.B if self.per_sample else 1)
         self._t_dev = t  # keep alive until the kernels have run
+        self._times_key = None  # set_program_times re-validates
         nat.check(nat.lib().ds_session_set_times(self.handle, _ptr(t), n, _stream()))
+
+    def set_program_times(self, times: Sequence[float]):
+        """Step-embedding tables for a sampler program's time values.  They depend only on (times, weights), so a session
+        that runs the same program again (every call of a sampler configuration) skips the upload and the table kernels."""
+        key = (tuple(times), self.engine.weights_key)
+        if self._times_key == key:
+            return
+        self.set_times(torch.tensor(list(times), dtype=torch.float32))
+        self._times_key = key
 
     def forward(self, x_btc: torch.Tensor, time_index: int, out: torch.Tensor | None = None) -> torch.Tensor:
         assert x_btc.is_contiguous() and x_btc.dtype == torch.float32 and x_btc.numel() == self.numel
@@ -186,7 +196,7 @@ class WaveNetEngine:
         self.weights_key = self.weights_fingerprint(module)
 
     def session(self, B: int, T: int, max_times: int = 64, per_sample: bool = False) -> Session:
-        key = (B, T, per_sample)
+        key = (B, T, per_sample, _stream())  # a session's buffers belong to the stream its kernels run on
         s = self.sessions.get(key)
         if s is not None and s.max_times >= max_times:
             self.sessions[key] = self.sessions.pop(key)  # most recently used last: eviction below is LRU

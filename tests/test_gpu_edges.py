@@ -87,3 +87,27 @@ def test_invalid_arguments_raise():
         bad.engine()
     with pytest.raises(RuntimeError, match="no CPU inference path"):
         ds.WaveNet(16, 1, num_layers=2, num_channels=64, dilation_cycle_length=2).engine()
+
+
+def test_sample_segments_matches_sequential():
+    """Segment-parallel sampling on several streams == segment-by-segment sampling (same noise order, same kernels)."""
+    M, F, L, C, H, cycle = 128, 1, 4, 256, 256, 4
+    sd = random_state_dict(M, F, L, C, H, seed=13)
+    ds.hparams.clear()
+    ds.hparams.update(hidden_size=H, schedule_type="linear", use_shallow_diffusion=False, diff_accelerator="ddim",
+                      diff_speedup=100, K_step=1000, K_step_infer=1000, timesteps=1000)
+    m = ds.GaussianDiffusion(M, F, 1000, 1000, "wavenet", dict(num_layers=L, num_channels=C, dilation_cycle_length=cycle),
+                             spec_min=[-12.0], spec_max=[0.0])
+    m.denoise_fn.load_state_dict(sd)
+    m = m.eval().to(dev)
+    g = torch.Generator().manual_seed(2)
+    conds = [torch.randn(1, T, H, generator=g).to(dev) for T in (286, 504, 286, 130, 777, 504, 286)]
+    torch.manual_seed(11)
+    with torch.no_grad():
+        seq = [m(c, infer=True).cpu() for c in conds]
+    for n in (1, 3):
+        torch.manual_seed(11)
+        par = ds.sample_segments(m, conds, n_streams=n)
+        torch.cuda.synchronize()
+        assert all(torch.equal(a, b.cpu()) for a, b in zip(seq, par))
+    assert ds.sample_segments(m, []) == []

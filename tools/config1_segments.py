@@ -41,6 +41,19 @@ def main():
         dt = time.perf_counter() - t0
         print(json.dumps(dict(case=f"config1 C={C} {rnd}", segments=len(SEGMENTS), frames=sum(SEGMENTS), total_ms=round(dt * 1e3, 1),
                               frames_per_s=round(sum(SEGMENTS) / dt, 1), ms_min=round(min(per), 2), ms_max=round(max(per), 2))), flush=True)
+    streams_case(m, conds, C)
+
+
+def streams_case(m, conds, C):
+    for n in (1, 2, 4, 8):
+        for rnd in range(2):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            ys = ds.sample_segments(m, conds, n_streams=n)
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+        print(json.dumps(dict(case=f"config1 C={C} sample_segments n_streams={n} (second pass)", segments=len(SEGMENTS),
+                              frames=sum(SEGMENTS), total_ms=round(dt * 1e3, 1), frames_per_s=round(sum(SEGMENTS) / dt, 1))), flush=True)
 
 
 if __name__ == "__main__":
