@@ -153,6 +153,7 @@ static int launch_gemm(int BN, int epi, const GemmParams& p, cudaStream_t st, bo
   DS_CASE(64, EPI_RES) DS_CASE(128, EPI_RES) DS_CASE(256, EPI_RES)
   DS_CASE(64, EPI_OUTF32) DS_CASE(128, EPI_OUTF32) DS_CASE(256, EPI_OUTF32)
   DS_CASE(256, EPI_CPROJ)
+  DS_CASE(128, EPI_SWIGLU) DS_CASE(256, EPI_SWIGLU)
 #undef DS_CASE
   return fail(DS_ERR_INVALID, "no GEMM instantiation for BN=%d epilogue=%d", BN, epi);
 }
@@ -735,7 +736,9 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
       g.res_in = xt; g.ld_res = C * S; g.out = xt; g.ld_out = C * S; g.out_c0 = 0;
       g.a0_lo = L * C; g.w_lo = C; g.out_lo = C; g.res_lo = C;
       shape(C / bnC);
+      g.scale = 0.70710678118654752f;  // (x + residual) / sqrt(2)
       DS_TRY(launch_gemm(bnC, EPI_RES, g, st, split));
+      g.scale = 1.0f;
       ++*launches;
     }
   }
@@ -892,6 +895,56 @@ extern "C" int ds_debug_gemm(const ds_gemm_desc* d, void* stream) {
   g.vec_bstride = d->vec_bstride; g.res_in = (const __nv_bfloat16*)d->res_in; g.ld_res = d->ld_res;
   g.out = d->out; g.ld_out = d->ld_out; g.out_c0 = d->out_c0; g.n_real = d->n_real;
   return launch_gemm(d->BN, d->epi, g, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------ primitive ops
+// The same kernels as building blocks for the path's neighbours behind the BACKBONES registry (LYNXNet, lynxnet.py:90-163;
+// the ConvNeXt aux decoder, convnext.py:58-87): the host composes them per layer and captures the sequence in a CUDA graph.
+extern "C" int ds_gemm(const ds_gemm_desc* d, void* stream) { return ds_debug_gemm(d, stream); }
+
+extern "C" int ds_layernorm(void* y_bf16, const void* x_bf16, const float* gamma, const float* beta, int64_t rows, int32_t channels,
+                            float eps, void* stream) {
+  if (!y_bf16 || !x_bf16 || !gamma || !beta || rows <= 0) return fail(DS_ERR_INVALID, "bad argument");
+  if (channels <= 0 || channels % 8 || channels > 2048) return fail(DS_ERR_INVALID, "channels=%d must be a multiple of 8 in (0, 2048]", channels);
+  DS_TRY(ensure_device());
+  const long blocks = (rows + 7) / 8;  // 8 warps (rows) per 256-thread block
+  const long cap = (long)g_num_sms * 16;
+  layernorm_kernel<<<(int)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream>>>((__nv_bfloat16*)y_bf16, (const __nv_bfloat16*)x_bf16, gamma,
+                                                                                         beta, (long)rows, channels, eps);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ds_dwconv(void* y_bf16, const void* x_bf16, const float* w, const float* bias, const float* slope, int32_t B, int32_t T,
+                         int32_t channels, int32_t kernel_size, int32_t pad_left, int32_t act, void* stream) {
+  if (!y_bf16 || !x_bf16 || !w || B <= 0 || T <= 0) return fail(DS_ERR_INVALID, "bad argument");
+  if (channels <= 0 || channels % 2) return fail(DS_ERR_INVALID, "channels=%d must be even", channels);
+  if (act < 0 || act > 3 || (act == 2 && !slope)) return fail(DS_ERR_INVALID, "bad activation %d", act);
+  if (B > 65535) return fail(DS_ERR_INVALID, "B too large");
+  DS_TRY(ensure_device());
+  cudaStream_t st = (cudaStream_t)stream;
+  const int bx = ceil_div(channels / 2, 128);
+  __nv_bfloat16* y = (__nv_bfloat16*)y_bf16;
+  const __nv_bfloat16* x = (const __nv_bfloat16*)x_bf16;
+  if (kernel_size == 31) {
+    dwconv_kernel<31, 2><<<dim3(bx, ceil_div(T, 62), B), 128, 0, st>>>(y, x, w, bias, slope, T, channels, pad_left, act);
+  } else if (kernel_size == 7) {
+    dwconv_kernel<7, 8><<<dim3(bx, ceil_div(T, 56), B), 128, 0, st>>>(y, x, w, bias, slope, T, channels, pad_left, act);
+  } else if (kernel_size == 3) {
+    dwconv_kernel<3, 16><<<dim3(bx, ceil_div(T, 48), B), 128, 0, st>>>(y, x, w, bias, slope, T, channels, pad_left, act);
+  } else {
+    return fail(DS_ERR_INVALID, "depthwise kernel_size=%d not instantiated (3, 7, 31)", kernel_size);
+  }
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ds_cast_bf16(void* dst_bf16, const float* src, int64_t rows, int32_t cols, int32_t ld, void* stream) {
+  if (!dst_bf16 || !src || rows <= 0 || cols <= 0 || cols % 4 || ld % 4 || ld < cols) return fail(DS_ERR_INVALID, "bad argument");
+  DS_TRY(ensure_device());
+  CUDA_TRY(launch_k(f32_to_bf16_pad_kernel, dim3(ew_grid((long)rows * ld / 4, 256)), dim3(256), 0, (cudaStream_t)stream,
+                    (__nv_bfloat16*)dst_bf16, src, (long)rows, (int)cols, (int)ld, (long)ld, 0));
+  return 0;
 }
 
 // Debug / bench: launch ONLY the fused kernel of residual layer `layer` on the session's current activation buffers

@@ -214,3 +214,131 @@ __global__ void lincomb_kernel(float* __restrict__ dst, LincombArgs a, long n4) 
 }
 
 }  // namespace dsb
+
+namespace dsb {
+
+// ------------------------------------------------------------------ primitives for the other denoisers (LYNXNet, aux decoder)
+// LayerNorm over the channel axis of time-major bf16 activations: y[r][:] = (x[r][:] - mean) * rstd * gamma + beta.
+// One warp per row, the row lives in registers (C <= 2048, C % 8 == 0), two-pass statistics in fp32 (biased variance,
+// like torch.nn.LayerNorm; lynxnet.py:52,123).
+__global__ void layernorm_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
+                                 const float* __restrict__ beta, long rows, int C, float eps) {
+  grid_dep_launch();
+  grid_dep_wait();
+  constexpr int kMaxChunks = 8;  // 8 chunks x 32 lanes x 8 elements
+  const int lane = threadIdx.x & 31;
+  const long warp0 = (static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const long nwarps = (static_cast<long>(gridDim.x) * blockDim.x) >> 5;
+  const int nch = (C + 255) / 256;
+  for (long r = warp0; r < rows; r += nwarps) {
+    float v[kMaxChunks][8];
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < kMaxChunks; ++i) {
+      const int e = (i * 32 + lane) * 8;
+      if (i < nch && e < C) {
+        const uint4 q = *reinterpret_cast<const uint4*>(x + r * C + e);
+        const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          v[i][2 * h] = __uint_as_float(w[h] << 16);
+          v[i][2 * h + 1] = __uint_as_float(w[h] & 0xffff0000u);
+          sum += v[i][2 * h] + v[i][2 * h + 1];
+        }
+      } else {
+#pragma unroll
+        for (int h = 0; h < 8; ++h) v[i][h] = 0.f;
+      }
+    }
+    for (int s = 16; s > 0; s >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, s);
+    const float mean = sum / static_cast<float>(C);
+    float sq = 0.f;
+#pragma unroll
+    for (int i = 0; i < kMaxChunks; ++i) {
+      const int e = (i * 32 + lane) * 8;
+      if (i < nch && e < C) {
+#pragma unroll
+        for (int h = 0; h < 8; ++h) {
+          const float d = v[i][h] - mean;
+          sq = fmaf(d, d, sq);
+        }
+      }
+    }
+    for (int s = 16; s > 0; s >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, s);
+    const float rstd = rsqrtf(sq / static_cast<float>(C) + eps);
+#pragma unroll
+    for (int i = 0; i < kMaxChunks; ++i) {
+      const int e = (i * 32 + lane) * 8;
+      if (i < nch && e < C) {
+        float o[8];
+#pragma unroll
+        for (int h = 0; h < 8; ++h) o[h] = (v[i][h] - mean) * rstd * __ldg(gamma + e + h) + __ldg(beta + e + h);
+        uint4 q;
+        q.x = pack_bf16(o[0], o[1]); q.y = pack_bf16(o[2], o[3]); q.z = pack_bf16(o[4], o[5]); q.w = pack_bf16(o[6], o[7]);
+        *reinterpret_cast<uint4*>(y + r * C + e) = q;
+      }
+    }
+  }
+}
+
+// Depthwise Conv1d along time on time-major bf16 activations [B][T][CH] with zero padding, fused bias and activation
+// (0 none, 1 ReLU, 2 PReLU with per-channel slope, 3 SiLU): y[b][t][c] = act(bias[c] + sum_j w[c][j] * x[b][t + j - pad][c]).
+// One thread owns a channel PAIR and walks kFrames consecutive frames with a K-deep register window (one coalesced
+// 4-byte load and 2K FMAs per output; window slots are static because the frame loop is unrolled in groups of K).
+// grid = (CH / 2 / 128, ceil(T / kFrames), B), block = 128.   lynxnet.py:59 (k = 31, groups = inner_dim)
+template <int K, int kGroups>
+__global__ void __launch_bounds__(128) dwconv_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x,
+                                                     const float* __restrict__ w, const float* __restrict__ bias,
+                                                     const float* __restrict__ slope, int T, int CH, int pad, int act) {
+  grid_dep_launch();
+  grid_dep_wait();
+  constexpr int kFrames = K * kGroups;
+  const int cp = blockIdx.x * 128 + threadIdx.x;  // channel pair
+  if (2 * cp >= CH) return;
+  const int b = blockIdx.z;
+  const int t0 = blockIdx.y * kFrames;
+  const __nv_bfloat16* xb = x + static_cast<size_t>(b) * T * CH + 2 * cp;
+  __nv_bfloat16* yb = y + static_cast<size_t>(b) * T * CH + 2 * cp;
+  float w0[K], w1[K];
+#pragma unroll
+  for (int j = 0; j < K; ++j) {
+    w0[j] = __ldg(w + static_cast<size_t>(2 * cp) * K + j);
+    w1[j] = __ldg(w + static_cast<size_t>(2 * cp + 1) * K + j);
+  }
+  const float b0 = bias ? __ldg(bias + 2 * cp) : 0.f, b1 = bias ? __ldg(bias + 2 * cp + 1) : 0.f;
+  const float s0 = slope ? __ldg(slope + 2 * cp) : 0.f, s1 = slope ? __ldg(slope + 2 * cp + 1) : 0.f;
+  auto load = [&](int t, float& a, float& c) {
+    if (t >= 0 && t < T) {
+      const uint32_t q = *reinterpret_cast<const uint32_t*>(xb + static_cast<size_t>(t) * CH);
+      a = __uint_as_float(q << 16);
+      c = __uint_as_float(q & 0xffff0000u);
+    } else {
+      a = 0.f;
+      c = 0.f;
+    }
+  };
+  float win0[K], win1[K];  // slot i % K holds input row (t0 - pad + i)
+#pragma unroll
+  for (int i = 0; i < K - 1; ++i) load(t0 - pad + i, win0[i], win1[i]);
+#pragma unroll 1
+  for (int g = 0; g < kGroups; ++g) {
+    if (t0 + g * K >= T) break;
+#pragma unroll
+    for (int s = 0; s < K; ++s) {
+      const int o = g * K + s;  // output frame t0 + o needs rows o .. o + K - 1; row o + K - 1 goes to slot (s + K - 1) % K
+      load(t0 - pad + o + K - 1, win0[(s + K - 1) % K], win1[(s + K - 1) % K]);
+      float a0 = b0, a1 = b1;
+#pragma unroll
+      for (int j = 0; j < K; ++j) {
+        a0 = fmaf(w0[j], win0[(s + j) % K], a0);
+        a1 = fmaf(w1[j], win1[(s + j) % K], a1);
+      }
+      if (act == 1) { a0 = fmaxf(a0, 0.f); a1 = fmaxf(a1, 0.f); }
+      else if (act == 2) { a0 = a0 > 0.f ? a0 : s0 * a0; a1 = a1 > 0.f ? a1 : s1 * a1; }
+      else if (act == 3) { a0 = a0 / (1.f + expf(-a0)); a1 = a1 / (1.f + expf(-a1)); }
+      if (t0 + o < T) *reinterpret_cast<uint32_t*>(yb + static_cast<size_t>(t0 + o) * CH) = pack_bf16(a0, a1);
+    }
+  }
+}
+
+}  // namespace dsb

@@ -77,6 +77,29 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
       }
       if (valid) st_act32<kSplit>(out + c * 32, p.out_lo, z);
     }
+  } else if constexpr (EPI == EPI_SWIGLU) {
+    // columns [0, BN/2) = "out" half, [BN/2, BN) = "gate" half of the SAME channels (pack-time row permutation):
+    // z = out * silu(gate)   (SwiGLU, modules/commons/common_layers.py; LYNXConvModule, lynxnet.py:57)
+    constexpr int H = BN / 2;
+    __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.out) + row * p.ld_out + p.out_c0 + nt * H;
+    const float* bias = p.bias + nt * BN;
+#pragma unroll 1
+    for (int c = half; c < H / 32; c += 2) {
+      uint32_t a[32], g[32];
+      tmem_ld_32x32(taddr + c * 32, a);
+      tmem_ld_32x32(taddr + H + c * 32, g);
+      float ba[32], bgt[32], z[32];
+      ld_f32x32(bias + c * 32, ba);
+      ld_f32x32(bias + H + c * 32, bgt);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const float aj = __uint_as_float(a[j]) + ba[j];
+        const float gj = __uint_as_float(g[j]) + bgt[j];
+        z[j] = aj * gj * sigmoid_accurate(gj);
+      }
+      if (valid) st_act32<kSplit>(out + c * 32, p.out_lo, z);
+    }
   } else if constexpr (EPI == EPI_CPROJ) {
     // hoisted conditioner projection (wavenet.py:35, step-invariant): f16 out = (acc + bias) in the gate kernel's packed
     // column order, gate columns (first half of every BN-column pass) pre-multiplied by 0.5 for sigmoid-by-tanh
@@ -141,8 +164,8 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
 #pragma unroll
         for (int h = 0; h < 4; ++h) {
           const int j = 8 * i + 2 * h;
-          v[j] = fmaf(__uint_as_float(a[j]) + __uint_as_float(w[h] << 16), 0.70710678118654752f, rr[j]);
-          v[j + 1] = fmaf(__uint_as_float(a[j + 1]) + __uint_as_float(w[h] & 0xffff0000u), 0.70710678118654752f, rr[j + 1]);
+          v[j] = fmaf(__uint_as_float(a[j]) + __uint_as_float(w[h] << 16), p.scale, rr[j]);
+          v[j + 1] = fmaf(__uint_as_float(a[j + 1]) + __uint_as_float(w[h] & 0xffff0000u), p.scale, rr[j + 1]);
         }
       }
       if (valid) st_act32<kSplit>(xout + c * 32, p.out_lo, v);
@@ -162,9 +185,12 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
       tmem_ld_wait();
 #pragma unroll
       for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(a[j]) + bb[j];
-      if (p.relu) {
+      if (p.relu == 1) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
+      } else if (p.relu == 2) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = 0.5f * v[j] * (1.0f + erff(v[j] * 0.70710678118654752f));
       }
 #pragma unroll
       for (int j = 0; j < 32; ++j) v[j] *= p.scale;

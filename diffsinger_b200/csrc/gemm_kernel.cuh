@@ -21,7 +21,7 @@ namespace dsb {
 constexpr int kGemmThreads = 384;  // 4 control warps + 8 epilogue warps (two per TMEM lane quadrant)
 constexpr int kEpiThreads = 256;
 
-enum : int { EPI_LINEAR = 0, EPI_GATE = 1, EPI_RES = 2, EPI_OUTF32 = 3, EPI_CPROJ = 4 };
+enum : int { EPI_LINEAR = 0, EPI_GATE = 1, EPI_RES = 2, EPI_OUTF32 = 3, EPI_CPROJ = 4, EPI_SWIGLU = 5 };
 
 struct GemmParams {
   CUtensorMap tmA0;  // primary activation source  (dims: channels, T, B)
@@ -35,8 +35,8 @@ struct GemmParams {
   int kb_a1;   // 64-wide K blocks from A1
   int b_row0;  // first row of this GEMM inside the packed weight matrix
   int b_k0;    // first K column of this GEMM inside the packed weight matrix (hoisted conditioner projection: 3C)
-  int relu;
-  float scale;
+  int relu;    // activation of the LINEAR / OUTF32 epilogues: 0 none, 1 ReLU, 2 GELU (exact, erf)
+  float scale;  // LINEAR / OUTF32: multiplies act(acc + bias); RES: multiplies (acc + res_in)  (1/sqrt(2) in WaveNet)
   const float* bias;     // indexed by tile-global n (packed order for EPI_GATE)
   const float* vec_sub;  // unused (kept for ABI stability of the debug hook)
   const float* vec_add;  // LINEAR: vector added after relu/scale; RES: folded (b - d_l)/sqrt(2) + d_{l+1}

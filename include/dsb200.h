@@ -127,9 +127,13 @@ int ds_lincomb(float* dst, const float* const* srcs, const float* coefs, int32_t
 /* [B][R][C] -> [B][C][R] fp32 (spec [B,F*M,T] <-> time-major; ddpm.py:350, reflow.py:137). */
 int ds_transpose(float* dst, const float* src, int32_t B, int32_t R, int32_t C, void* stream);
 
-/* ---- debug / unit-test hook: one tcgen05 GEMM launch with an explicit epilogue */
+/* ---- primitive ops: one tcgen05 GEMM launch with an explicit epilogue, LayerNorm, depthwise conv.  They are the unit-test
+ * hooks of the kernels above and the building blocks of the path's neighbours behind the same registry (LYNXNet,
+ * modules/backbones/lynxnet.py:90-163).  Activations are time-major bf16 [B][T][channels]; weights bf16 [rows][K]. */
 typedef struct {
-  int32_t epi;  /* 0 linear(bf16 out), 1 gate, 2 residual, 3 fp32 out */
+  int32_t epi;  /* 0 linear: bf16 out = act(acc + bias) * scale + vec_add[b]      1 gate: sigmoid(first half) * tanh(second half)
+                   2 residual: bf16 out = (acc + res_in) * scale + vec_add[b]     3 fp32 out = act(acc + bias) * scale
+                   5 SwiGLU: first half * silu(second half)   (halves = BN/2-row blocks of the same channels, see pack order) */
   int32_t BN;   /* 64 / 128 / 256 */
   int32_t B, T;
   const void* a0; int32_t a0_channels; int32_t a0_c0; int32_t kb_a0; int32_t n_taps; int32_t dil;
@@ -138,9 +142,20 @@ typedef struct {
   const float* bias; const float* vec_sub; const float* vec_add; int32_t vec_bstride;
   const void* res_in; int32_t ld_res;
   void* out; int32_t ld_out; int32_t out_c0; int32_t n_real;
-  int32_t relu; float scale;
+  int32_t relu;  /* activation of epilogues 0 / 3: 0 none, 1 ReLU, 2 GELU (erf) */
+  float scale;
 } ds_gemm_desc;
 int ds_debug_gemm(const ds_gemm_desc* d, void* stream);
+int ds_gemm(const ds_gemm_desc* d, void* stream);
+/* y = LayerNorm(x) over `channels` (multiple of 8, <= 2048) for `rows` frames; torch.nn.LayerNorm semantics (lynxnet.py:52,123). */
+int ds_layernorm(void* y_bf16, const void* x_bf16, const float* gamma, const float* beta, int64_t rows, int32_t channels, float eps,
+                 void* stream);
+/* Depthwise Conv1d along time with zero padding (nn.Conv1d(ch, ch, k, padding=pad_left, groups=ch), lynxnet.py:59;
+ * convnext.py dwconv), w fp32 [channels][k], fused bias and activation: 0 none, 1 ReLU, 2 PReLU(slope[channels]), 3 SiLU. */
+int ds_dwconv(void* y_bf16, const void* x_bf16, const float* w, const float* bias, const float* slope, int32_t B, int32_t T,
+              int32_t channels, int32_t kernel_size, int32_t pad_left, int32_t act, void* stream);
+/* fp32 [rows][cols] -> bf16 [rows][ld] (columns >= cols zero filled); cols, ld multiples of 4. */
+int ds_cast_bf16(void* dst_bf16, const float* src, int64_t rows, int32_t cols, int32_t ld, void* stream);
 /* Debug: device buffer of n_entries x 4 uint64 into which CTA 0 of every fused-layer launch records
  * {role*16+kind, tile*16+idx, t0_ns, t1_ns} (first half: MMA issuer, second half: epilogue). NULL disables. */
 int ds_debug_set_trace(void* dev_buf, int32_t n_entries);

@@ -96,7 +96,7 @@ def test_residual_and_f32_out():
     # residual epilogue, in place on xt, A = channels [Cc, 2Cc) of zin, weight rows [Cc, 2Cc)
     d = _desc(epi=2, BN=64, B=B, T=T, a0=zin, a0_channels=3 * Cc, a0_c0=Cc, kb_a0=Cc // 64, n_taps=1, dil=0, kb_a1=0,
               w=w, w_rows=2 * Cc, w_k=Cc, b_row0=Cc, n_tiles=Cc // 64, bias=bias[Cc:].contiguous(), vec_sub=dsub,
-              vec_add=dadd, vec_bstride=Cc, res_in=xt, ld_res=Cc, out=xt, ld_out=Cc, out_c0=0, relu=0, scale=1.0)
+              vec_add=dadd, vec_bstride=Cc, res_in=xt, ld_res=Cc, out=xt, ld_out=Cc, out_c0=0, relu=0, scale=0.5 ** 0.5)
     _run(d)
     acc = zin[..., Cc:2 * Cc].float() @ w[Cc:].float().T + bias[Cc:]
     ref = (xt0.float() + zin[..., Cc:2 * Cc].float() @ w[Cc:].float().T) * (0.5 ** 0.5) + dadd[:, None]  # bias/vec_sub are folded into vec_add by the caller

@@ -1,0 +1,96 @@
+"""GPU unit tests of the primitive ops of the C ABI (ds_gemm epilogues GELU / SwiGLU / residual-with-scale, ds_layernorm,
+ds_dwconv, ds_cast_bf16) against plain torch fp32 math on the same bf16-rounded operands.  Tolerances: bf16 output
+rounding (2^-9 relative) dominates -> rel-L2 <= 4e-3."""
+import ctypes as C
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from conftest import rel_l2
+from diffsinger_b200 import _native as nat
+
+pytestmark = pytest.mark.gpu
+dev = "cuda"
+
+
+def _st():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _bf(*shape, scale=1.0):
+    return (torch.randn(*shape, device=dev) * scale).to(torch.bfloat16)
+
+
+def _desc(**kw):
+    d = nat.GemmDesc()
+    for k, v in kw.items():
+        setattr(d, k, v.data_ptr() if isinstance(v, torch.Tensor) else v)
+    return d
+
+
+@pytest.mark.parametrize("rows,Cc", [(1000, 512), (77, 192), (5, 2048), (300, 8)])
+def test_layernorm(rows, Cc):
+    torch.manual_seed(0)
+    x = _bf(rows, Cc) * 3 + 1
+    g, b = torch.randn(Cc, device=dev), torch.randn(Cc, device=dev)
+    y = torch.empty_like(x)
+    nat.check(nat.lib().ds_layernorm(y.data_ptr(), x.data_ptr(), g.data_ptr(), b.data_ptr(), rows, Cc, 1e-5, _st()))
+    ref = F.layer_norm(x.float(), (Cc,), g, b, 1e-5)
+    assert rel_l2(y.float(), ref) < 4e-3
+
+
+@pytest.mark.parametrize("k,pad,act,B,T,CH", [(31, 15, 2, 2, 700, 1024), (31, 15, 3, 1, 40, 256), (7, 3, 0, 3, 129, 512),
+                                            (3, 1, 1, 1, 5, 64)])
+def test_dwconv(k, pad, act, B, T, CH):
+    torch.manual_seed(1)
+    x = _bf(B, T, CH)
+    w = torch.randn(CH, k, device=dev) * k ** -0.5
+    bias = torch.randn(CH, device=dev)
+    slope = torch.rand(CH, device=dev) * 0.5
+    y = torch.empty_like(x)
+    nat.check(nat.lib().ds_dwconv(y.data_ptr(), x.data_ptr(), w.data_ptr(), bias.data_ptr(), slope.data_ptr(), B, T, CH, k, pad, act, _st()))
+    ref = F.conv1d(x.float().transpose(1, 2), w[:, None, :], bias, padding=pad, groups=CH)
+    ref = {0: lambda v: v, 1: F.relu, 2: lambda v: torch.where(v > 0, v, slope[None, :, None] * v), 3: F.silu}[act](ref).transpose(1, 2)
+    assert y.shape == ref.shape
+    assert rel_l2(y.float(), ref) < 4e-3
+
+
+def test_gemm_gelu_swiglu_and_residual_scale():
+    torch.manual_seed(2)
+    B, T, K, N = 2, 300, 128, 256
+    a, w = _bf(B, T, K), _bf(N, K, scale=K ** -0.5)
+    bias = torch.randn(N, device=dev)
+    lib = nat.lib()
+    # GELU(acc + bias)
+    out = torch.empty(B, T, N, device=dev, dtype=torch.bfloat16)
+    d = _desc(epi=0, BN=128, B=B, T=T, a0=a, a0_channels=K, a0_c0=0, kb_a0=K // 64, n_taps=1, dil=0, kb_a1=0, w=w, w_rows=N, w_k=K,
+              b_row0=0, n_tiles=N // 128, bias=bias, out=out, ld_out=N, out_c0=0, relu=2, scale=1.0)
+    nat.check(lib.ds_gemm(C.byref(d), _st()))
+    acc = a.float() @ w.float().T + bias
+    assert rel_l2(out.float(), F.gelu(acc)) < 4e-3
+    # SwiGLU: rows packed per BN=128 pass as 64 "out" rows + the 64 "gate" rows of the same channels
+    half = N // 2
+    perm = torch.cat([torch.cat([torch.arange(p * 64, p * 64 + 64), half + torch.arange(p * 64, p * 64 + 64)]) for p in range(N // 128)]).to(dev)
+    wp, bp = w[perm].contiguous(), bias[perm].contiguous()
+    z = torch.empty(B, T, half, device=dev, dtype=torch.bfloat16)
+    d = _desc(epi=5, BN=128, B=B, T=T, a0=a, a0_channels=K, a0_c0=0, kb_a0=K // 64, n_taps=1, dil=0, kb_a1=0, w=wp, w_rows=N, w_k=K,
+              b_row0=0, n_tiles=N // 128, bias=bp, out=z, ld_out=half, out_c0=0, relu=0, scale=1.0)
+    nat.check(lib.ds_gemm(C.byref(d), _st()))
+    assert rel_l2(z.float(), acc[..., :half] * F.silu(acc[..., half:])) < 4e-3
+    # residual with scale 1: out = acc + res + per-batch vector
+    res, vec = _bf(B, T, N), torch.randn(B, N, device=dev)
+    o = torch.empty_like(res)
+    d = _desc(epi=2, BN=128, B=B, T=T, a0=a, a0_channels=K, a0_c0=0, kb_a0=K // 64, n_taps=1, dil=0, kb_a1=0, w=w, w_rows=N, w_k=K,
+              b_row0=0, n_tiles=N // 128, vec_add=vec, vec_bstride=N, res_in=res, ld_res=N, out=o, ld_out=N, out_c0=0, relu=0, scale=1.0)
+    nat.check(lib.ds_gemm(C.byref(d), _st()))
+    assert rel_l2(o.float(), a.float() @ w.float().T + res.float() + vec[:, None]) < 4e-3
+
+
+def test_cast_bf16_pads():
+    x = torch.randn(37, 48, device=dev)
+    y = torch.full((37, 64), 7.0, device=dev, dtype=torch.bfloat16)
+    nat.check(nat.lib().ds_cast_bf16(y.data_ptr(), x.data_ptr(), 37, 48, 64, _st()))
+    assert torch.equal(y[:, :48], x.to(torch.bfloat16)) and (y[:, 48:] == 0).all()
+    with pytest.raises(nat.NativeError):
+        nat.check(nat.lib().ds_dwconv(y.data_ptr(), y.data_ptr(), x.data_ptr(), None, None, 1, 8, 64, 5, 2, 0, _st()))
