@@ -2,11 +2,11 @@
 the WaveNet backbone (BACKBONES['wavenet']) and the GaussianDiffusion / RectifiedFlow samplers.
 Host code is Python/PyTorch plumbing over the C ABI in include/dsb200.h (libdsb200.so)."""
 from .hparams import hparams, get_hparams
-from .backbones import BACKBONES, build_backbone, WaveNet
+from .backbones import BACKBONES, build_backbone, WaveNet, LYNXNet
 from .segments import sample_segments
 from .core import (GaussianDiffusion, PitchDiffusion, MultiVarianceDiffusion,
                    RectifiedFlow, PitchRectifiedFlow, MultiVarianceRectifiedFlow)
 
-__all__ = ["hparams", "get_hparams", "BACKBONES", "build_backbone", "WaveNet", "GaussianDiffusion",
+__all__ = ["hparams", "get_hparams", "BACKBONES", "build_backbone", "WaveNet", "LYNXNet", "GaussianDiffusion",
            "PitchDiffusion", "MultiVarianceDiffusion", "RectifiedFlow", "PitchRectifiedFlow",
            "MultiVarianceRectifiedFlow", "sample_segments"]

@@ -4,9 +4,11 @@ import inspect
 import torch.nn
 
 from .wavenet import WaveNet
+from .lynxnet import LYNXNet
 
 BACKBONES = {
     'wavenet': WaveNet,
+    'lynxnet': LYNXNet,
 }
 
 
@@ -29,4 +31,5 @@ def install_into_reference():
     """Drop-in: replace ``modules.backbones.BACKBONES['wavenet']`` of an importable DiffSinger tree."""
     import modules.backbones as ref_backbones  # the reference package, must be on sys.path
     ref_backbones.BACKBONES['wavenet'] = WaveNet
+    ref_backbones.BACKBONES['lynxnet'] = LYNXNet
     return ref_backbones.BACKBONES

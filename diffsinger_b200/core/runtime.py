@@ -45,11 +45,13 @@ def run_program(backbone, prog: Program, x_tm: torch.Tensor, cond_bht: torch.Ten
     """Runs `prog` with buffer 0 = x_tm (time-major start state), buffers 2.. optionally preset from
     `extra`.  cond_bht is the [B, H, T] tensor the reference passes to the backbone.  Returns buffer 0.
 
-    The backbone must be the native WaveNet; anything else (e.g. the reference's LYNXNet, which stays on
-    the PyTorch path) is rejected rather than silently emulated."""
+    The backbone must be one of this package's native backbones (WaveNet, LYNXNet); anything else is rejected rather
+    than silently emulated in PyTorch."""
     if not hasattr(backbone, 'engine'):
-        raise TypeError("run_program needs the diffsinger_b200 WaveNet backbone (native engine)")
+        raise TypeError("run_program needs a diffsinger_b200 backbone with a native engine (WaveNet, LYNXNet)")
     eng = backbone.engine()
+    if hasattr(eng, 'run_program'):  # LYNXNet: host-composed primitive ops, one torch CUDA graph per (program, B, T)
+        return eng.run_program(backbone, prog, x_tm, cond_bht, extra, use_graph)
     B, T, FM = x_tm.shape
     bc = max_chunk_batch(eng, B, T, prog.n_bufs, len(prog.times))
     if bc >= B:

@@ -903,14 +903,15 @@ extern "C" int ds_debug_gemm(const ds_gemm_desc* d, void* stream) {
 extern "C" int ds_gemm(const ds_gemm_desc* d, void* stream) { return ds_debug_gemm(d, stream); }
 
 extern "C" int ds_layernorm(void* y_bf16, const void* x_bf16, const float* gamma, const float* beta, int64_t rows, int32_t channels,
-                            float eps, void* stream) {
+                            float eps, const float* vec, int64_t rows_per_vec, void* stream) {
+  if (vec && rows_per_vec <= 0) return fail(DS_ERR_INVALID, "rows_per_vec must be positive");
   if (!y_bf16 || !x_bf16 || !gamma || !beta || rows <= 0) return fail(DS_ERR_INVALID, "bad argument");
   if (channels <= 0 || channels % 8 || channels > 2048) return fail(DS_ERR_INVALID, "channels=%d must be a multiple of 8 in (0, 2048]", channels);
   DS_TRY(ensure_device());
   const long blocks = (rows + 7) / 8;  // 8 warps (rows) per 256-thread block
   const long cap = (long)g_num_sms * 16;
   layernorm_kernel<<<(int)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream>>>((__nv_bfloat16*)y_bf16, (const __nv_bfloat16*)x_bf16, gamma,
-                                                                                         beta, (long)rows, channels, eps);
+                                                                                         beta, (long)rows, channels, eps, vec, (long)rows_per_vec);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }

@@ -218,11 +218,13 @@ __global__ void lincomb_kernel(float* __restrict__ dst, LincombArgs a, long n4) 
 namespace dsb {
 
 // ------------------------------------------------------------------ primitives for the other denoisers (LYNXNet, aux decoder)
-// LayerNorm over the channel axis of time-major bf16 activations: y[r][:] = (x[r][:] - mean) * rstd * gamma + beta.
+// LayerNorm over the channel axis of time-major bf16 activations: y[r][:] = (x'[r][:] - mean) * rstd * gamma + beta with
+// x'[r] = x[r] + vec[r / rows_per_vec] (optional fp32 per-utterance vector: the diffusion-step projection, lynxnet.py:89).
 // One warp per row, the row lives in registers (C <= 2048, C % 8 == 0), two-pass statistics in fp32 (biased variance,
 // like torch.nn.LayerNorm; lynxnet.py:52,123).
 __global__ void layernorm_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
-                                 const float* __restrict__ beta, long rows, int C, float eps) {
+                                 const float* __restrict__ beta, long rows, int C, float eps, const float* __restrict__ vec,
+                                 long rows_per_vec) {
   grid_dep_launch();
   grid_dep_wait();
   constexpr int kMaxChunks = 8;  // 8 chunks x 32 lanes x 8 elements
@@ -243,6 +245,11 @@ __global__ void layernorm_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloa
         for (int h = 0; h < 4; ++h) {
           v[i][2 * h] = __uint_as_float(w[h] << 16);
           v[i][2 * h + 1] = __uint_as_float(w[h] & 0xffff0000u);
+          if (vec) {
+            const float* vr = vec + (r / rows_per_vec) * C + e;
+            v[i][2 * h] += __ldg(vr + 2 * h);
+            v[i][2 * h + 1] += __ldg(vr + 2 * h + 1);
+          }
           sum += v[i][2 * h] + v[i][2 * h + 1];
         }
       } else {

@@ -169,8 +169,50 @@ def gen_variance(ref):
           weights=np.array(wtag))
 
 
+LYNX_SMALL = dict(num_layers=3, num_channels=64, expansion_factor=2, kernel_size=31)
+
+
+def gen_lynxnet(ref):
+    """LYNXNet (modules/backbones/lynxnet.py), the reference's other registry entry: forward fixtures for the three
+    activations, F = 1 / F = 2 and strong_cond, with non-trivial norm / PReLU parameters and a re-randomised output
+    projection (it is zero-initialised like WaveNet's, trap T1)."""
+    from modules.backbones.lynxnet import LYNXNet
+    for tag, M, Fn, act, strong in (("prelu_f1", 16, 1, "PReLU", False), ("silu_f2", 8, 2, "SiLU", False),
+                                    ("relu_strong", 16, 1, "ReLU", True)):
+        set_reference_hparams(hidden_size=HIDDEN)
+        torch.manual_seed(300 + Fn)
+        net = LYNXNet(M, Fn, activation=act, strong_cond=strong, **LYNX_SMALL).eval()
+        _randomise_out_proj(net, 0.1)
+        with torch.no_grad():
+            for k, v in net.state_dict().items():  # LayerNorm affine and PReLU slopes away from their (1, 0, 0.25) defaults
+                if k.endswith("net.0.weight") or k == "norm.weight":
+                    v.copy_(1.0 + 0.2 * torch.randn_like(v))
+                elif k.endswith("net.0.bias") or k == "norm.bias":
+                    v.copy_(0.1 * torch.randn_like(v))
+                elif k.endswith("net.5.weight"):
+                    v.copy_(0.05 + 0.4 * torch.rand_like(v))
+        torch.manual_seed(5)
+        B, T = 2, 45
+        spec = torch.randn(B, Fn, M, T)
+        cond = torch.randn(B, T, HIDDEN).transpose(1, 2)
+        t_long = torch.tensor([950, 3], dtype=torch.long)
+        t_float = torch.tensor([412.5])
+        with torch.no_grad():
+            y_long = net(spec, t_long, cond)
+            y_float = net(spec, t_float, cond)
+        _save(f"lynxnet_{tag}", spec=spec.numpy(), cond=cond.contiguous().numpy(), t_long=t_long.numpy(), t_float=t_float.numpy(),
+              y_long=y_long.numpy(), y_float=y_float.numpy(),
+              cfg=np.array([M, Fn, LYNX_SMALL["num_layers"], LYNX_SMALL["num_channels"], LYNX_SMALL["expansion_factor"],
+                            LYNX_SMALL["kernel_size"], HIDDEN, int(strong)]), activation=np.array(act),
+              **{"w." + k: v.numpy() for k, v in net.state_dict().items()})
+
+
 def main():
     ref = load_reference()
+    if "lynxnet" in os.environ.get("GOLDEN_ONLY", "lynxnet"):
+        gen_lynxnet(ref)
+    if os.environ.get("GOLDEN_ONLY"):
+        return
     gen_backbone(ref)
     gen_ddpm(ref)
     gen_reflow(ref)

@@ -38,3 +38,14 @@ def load_golden(name):
 def rel_l2(a, b):
     a, b = a.double(), b.double()
     return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+def load_lynx_golden(name):
+    """-> (dict of tensors, state_dict, cfg) for a tests/golden/lynxnet_*.npz fixture."""
+    z = np.load(os.path.join(GOLDEN, name + ".npz"))
+    d = {k: torch.from_numpy(z[k]) for k in ("spec", "cond", "t_long", "t_float", "y_long", "y_float")}
+    sd = {k[2:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("w.")}
+    M, F, L, C, ef, ks, H, strong = [int(v) for v in z["cfg"]]
+    cfg = dict(in_dims=M, n_feats=F, num_layers=L, num_channels=C, expansion_factor=ef, kernel_size=ks, hidden=H,
+               strong_cond=bool(strong), activation=str(z["activation"]))
+    return d, sd, cfg

@@ -91,3 +91,17 @@ def test_variance_wrappers():
     y = so.finish(x, smin, smax).mean(-1)  # [B,F,T]
     ys = torch.stack([v.clamp(-96.0, 0.0) for v in y.unbind(1)])
     assert rel_l2(ys, d["y"]) < TOL
+
+
+@pytest.mark.parametrize("tag", ["prelu_f1", "silu_f2", "relu_strong"])
+def test_lynxnet_forward(tag):
+    """The LYNXNet restatement against the imported reference's outputs (modules/backbones/lynxnet.py:133-172)."""
+    from conftest import load_lynx_golden
+    from oracle.lynxnet_oracle import OracleLYNXNet
+    d, sd, cfg = load_lynx_golden("lynxnet_" + tag)
+    net = OracleLYNXNet(sd, cfg["n_feats"], cfg["kernel_size"], cfg["activation"], cfg["strong_cond"])
+    assert net.num_layers == cfg["num_layers"]
+    for tk, yk in (("t_long", "y_long"), ("t_float", "y_float")):
+        y = net(d["spec"], d[tk], d["cond"])
+        assert y.shape == d[yk].shape
+        assert rel_l2(y, d[yk]) < 2e-6
