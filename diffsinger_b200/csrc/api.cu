@@ -909,9 +909,16 @@ extern "C" int ds_layernorm(void* y_bf16, const void* x_bf16, const float* gamma
   if (channels <= 0 || channels % 8 || channels > 2048) return fail(DS_ERR_INVALID, "channels=%d must be a multiple of 8 in (0, 2048]", channels);
   DS_TRY(ensure_device());
   const long blocks = (rows + 7) / 8;  // 8 warps (rows) per 256-thread block
-  const long cap = (long)g_num_sms * 16;
-  layernorm_kernel<<<(int)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream>>>((__nv_bfloat16*)y_bf16, (const __nv_bfloat16*)x_bf16, gamma,
-                                                                                         beta, (long)rows, channels, eps, vec, (long)rows_per_vec);
+  const long cap = (long)g_num_sms * 32;
+  const int grid = (int)(blocks < cap ? blocks : cap);
+  cudaStream_t st = (cudaStream_t)stream;
+  __nv_bfloat16* yp = (__nv_bfloat16*)y_bf16;
+  const __nv_bfloat16* xp = (const __nv_bfloat16*)x_bf16;
+  const int nch = ceil_div(channels, 256);
+  if (nch <= 1) layernorm_kernel<1><<<grid, 256, 0, st>>>(yp, xp, gamma, beta, (long)rows, channels, eps, vec, (long)rows_per_vec);
+  else if (nch <= 2) layernorm_kernel<2><<<grid, 256, 0, st>>>(yp, xp, gamma, beta, (long)rows, channels, eps, vec, (long)rows_per_vec);
+  else if (nch <= 4) layernorm_kernel<4><<<grid, 256, 0, st>>>(yp, xp, gamma, beta, (long)rows, channels, eps, vec, (long)rows_per_vec);
+  else layernorm_kernel<8><<<grid, 256, 0, st>>>(yp, xp, gamma, beta, (long)rows, channels, eps, vec, (long)rows_per_vec);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -928,11 +935,14 @@ extern "C" int ds_dwconv(void* y_bf16, const void* x_bf16, const float* w, const
   __nv_bfloat16* y = (__nv_bfloat16*)y_bf16;
   const __nv_bfloat16* x = (const __nv_bfloat16*)x_bf16;
   if (kernel_size == 31) {
-    dwconv_kernel<31, 2><<<dim3(bx, ceil_div(T, 62), B), 128, 0, st>>>(y, x, w, bias, slope, T, channels, pad_left, act);
+    CUDA_TRY(cudaFuncSetAttribute(dwconv_kernel<31, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (62 + 30) * 512));
+    dwconv_kernel<31, 2><<<dim3(bx, ceil_div(T, 62), B), 128, (62 + 30) * 512, st>>>(y, x, w, bias, slope, T, channels, pad_left, act);
   } else if (kernel_size == 7) {
-    dwconv_kernel<7, 8><<<dim3(bx, ceil_div(T, 56), B), 128, 0, st>>>(y, x, w, bias, slope, T, channels, pad_left, act);
+    CUDA_TRY(cudaFuncSetAttribute(dwconv_kernel<7, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (56 + 6) * 512));
+    dwconv_kernel<7, 8><<<dim3(bx, ceil_div(T, 56), B), 128, (56 + 6) * 512, st>>>(y, x, w, bias, slope, T, channels, pad_left, act);
   } else if (kernel_size == 3) {
-    dwconv_kernel<3, 16><<<dim3(bx, ceil_div(T, 48), B), 128, 0, st>>>(y, x, w, bias, slope, T, channels, pad_left, act);
+    CUDA_TRY(cudaFuncSetAttribute(dwconv_kernel<3, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (48 + 2) * 512));
+    dwconv_kernel<3, 16><<<dim3(bx, ceil_div(T, 48), B), 128, (48 + 2) * 512, st>>>(y, x, w, bias, slope, T, channels, pad_left, act);
   } else {
     return fail(DS_ERR_INVALID, "depthwise kernel_size=%d not instantiated (3, 7, 31)", kernel_size);
   }

@@ -222,12 +222,12 @@ namespace dsb {
 // x'[r] = x[r] + vec[r / rows_per_vec] (optional fp32 per-utterance vector: the diffusion-step projection, lynxnet.py:89).
 // One warp per row, the row lives in registers (C <= 2048, C % 8 == 0), two-pass statistics in fp32 (biased variance,
 // like torch.nn.LayerNorm; lynxnet.py:52,123).
+template <int kMaxChunks>  // ceil(C / 256): the row lives in kMaxChunks x 8 registers per lane
 __global__ void layernorm_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
                                  const float* __restrict__ beta, long rows, int C, float eps, const float* __restrict__ vec,
                                  long rows_per_vec) {
   grid_dep_launch();
   grid_dep_wait();
-  constexpr int kMaxChunks = 8;  // 8 chunks x 32 lanes x 8 elements
   const int lane = threadIdx.x & 31;
   const long warp0 = (static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   const long nwarps = (static_cast<long>(gridDim.x) * blockDim.x) >> 5;
@@ -290,56 +290,68 @@ __global__ void layernorm_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloa
 
 // Depthwise Conv1d along time on time-major bf16 activations [B][T][CH] with zero padding, fused bias and activation
 // (0 none, 1 ReLU, 2 PReLU with per-channel slope, 3 SiLU): y[b][t][c] = act(bias[c] + sum_j w[c][j] * x[b][t + j - pad][c]).
-// One thread owns a channel PAIR and walks kFrames consecutive frames with a K-deep register window (one coalesced
-// 4-byte load and 2K FMAs per output; window slots are static because the frame loop is unrolled in groups of K).
-// grid = (CH / 2 / 128, ceil(T / kFrames), B), block = 128.   lynxnet.py:59 (k = 31, groups = inner_dim)
+// One thread owns a channel PAIR and kFrames = K * kGroups consecutive frames.  All kFrames + K - 1 input rows of its pair
+// are fetched up front with 4-byte cp.async (zero fill outside [0, T)) into the thread's own column of a shared-memory
+// tile -- one exposed memory latency per block instead of one per output -- and then walked with a K-deep register
+// window: per output one LDS and K packed fp32 FMAs (fma.rn.f32x2, both channels per instruction, two chains).
+// grid = (CH / 2 / 128, ceil(T / kFrames), B), block = 128, dynamic smem = (kFrames + K - 1) * 512 B.   lynxnet.py:59
+__device__ __forceinline__ void cp_async_4_zfill(uint32_t smem_addr, const void* gptr, bool valid) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_addr), "l"(gptr), "r"(valid ? 4 : 0) : "memory");
+}
 template <int K, int kGroups>
 __global__ void __launch_bounds__(128) dwconv_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x,
                                                      const float* __restrict__ w, const float* __restrict__ bias,
                                                      const float* __restrict__ slope, int T, int CH, int pad, int act) {
+  extern __shared__ uint32_t dw_tile[];  // [kRows][128 channel pairs]
   grid_dep_launch();
   grid_dep_wait();
   constexpr int kFrames = K * kGroups;
+  constexpr int kRows = kFrames + K - 1;
   const int cp = blockIdx.x * 128 + threadIdx.x;  // channel pair
   if (2 * cp >= CH) return;
   const int b = blockIdx.z;
   const int t0 = blockIdx.y * kFrames;
   const __nv_bfloat16* xb = x + static_cast<size_t>(b) * T * CH + 2 * cp;
   __nv_bfloat16* yb = y + static_cast<size_t>(b) * T * CH + 2 * cp;
-  float w0[K], w1[K];
-#pragma unroll
-  for (int j = 0; j < K; ++j) {
-    w0[j] = __ldg(w + static_cast<size_t>(2 * cp) * K + j);
-    w1[j] = __ldg(w + static_cast<size_t>(2 * cp + 1) * K + j);
+  const uint32_t col = smem_u32(dw_tile + threadIdx.x);
+#pragma unroll 4
+  for (int r = 0; r < kRows; ++r) {
+    const int t = t0 - pad + r;
+    const bool valid = t >= 0 && t < T;
+    cp_async_4_zfill(col + r * 512, xb + static_cast<size_t>(valid ? t : 0) * CH, valid);
   }
-  const float b0 = bias ? __ldg(bias + 2 * cp) : 0.f, b1 = bias ? __ldg(bias + 2 * cp + 1) : 0.f;
-  const float s0 = slope ? __ldg(slope + 2 * cp) : 0.f, s1 = slope ? __ldg(slope + 2 * cp + 1) : 0.f;
-  auto load = [&](int t, float& a, float& c) {
-    if (t >= 0 && t < T) {
-      const uint32_t q = *reinterpret_cast<const uint32_t*>(xb + static_cast<size_t>(t) * CH);
-      a = __uint_as_float(q << 16);
-      c = __uint_as_float(q & 0xffff0000u);
-    } else {
-      a = 0.f;
-      c = 0.f;
-    }
-  };
-  float win0[K], win1[K];  // slot i % K holds input row (t0 - pad + i)
+  unsigned long long wv[K];
 #pragma unroll
-  for (int i = 0; i < K - 1; ++i) load(t0 - pad + i, win0[i], win1[i]);
+  for (int j = 0; j < K; ++j)
+    wv[j] = pack_f32x2(__ldg(w + static_cast<size_t>(2 * cp) * K + j), __ldg(w + static_cast<size_t>(2 * cp + 1) * K + j));
+  const unsigned long long bv = pack_f32x2(bias ? __ldg(bias + 2 * cp) : 0.f, bias ? __ldg(bias + 2 * cp + 1) : 0.f);
+  const float s0 = slope ? __ldg(slope + 2 * cp) : 0.f, s1 = slope ? __ldg(slope + 2 * cp + 1) : 0.f;
+  asm volatile("cp.async.wait_all;" ::: "memory");  // each thread reads back only the column it filled itself
+  auto row = [&](int r) -> unsigned long long {
+    const uint32_t q = dw_tile[r * 128 + threadIdx.x];
+    return pack_f32x2(__uint_as_float(q << 16), __uint_as_float(q & 0xffff0000u));
+  };
+  unsigned long long win[K];  // slot i % K holds input row (t0 - pad + i)
+#pragma unroll
+  for (int i = 0; i < K - 1; ++i) win[i] = row(i);
 #pragma unroll 1
   for (int g = 0; g < kGroups; ++g) {
     if (t0 + g * K >= T) break;
 #pragma unroll
     for (int s = 0; s < K; ++s) {
       const int o = g * K + s;  // output frame t0 + o needs rows o .. o + K - 1; row o + K - 1 goes to slot (s + K - 1) % K
-      load(t0 - pad + o + K - 1, win0[(s + K - 1) % K], win1[(s + K - 1) % K]);
-      float a0 = b0, a1 = b1;
+      win[(s + K - 1) % K] = row(o + K - 1);
+      unsigned long long acc_e = bv, acc_o = 0ull;
 #pragma unroll
       for (int j = 0; j < K; ++j) {
-        a0 = fmaf(w0[j], win0[(s + j) % K], a0);
-        a1 = fmaf(w1[j], win1[(s + j) % K], a1);
+        if (j & 1) acc_o = fma_f32x2(wv[j], win[(s + j) % K], acc_o);
+        else acc_e = fma_f32x2(wv[j], win[(s + j) % K], acc_e);
       }
+      float a0, a1, o0, o1;
+      unpack_f32x2(acc_e, a0, a1);
+      unpack_f32x2(acc_o, o0, o1);
+      a0 += o0;
+      a1 += o1;
       if (act == 1) { a0 = fmaxf(a0, 0.f); a1 = fmaxf(a1, 0.f); }
       else if (act == 2) { a0 = a0 > 0.f ? a0 : s0 * a0; a1 = a1 > 0.f ? a1 : s1 * a1; }
       else if (act == 3) { a0 = a0 / (1.f + expf(-a0)); a1 = a1 / (1.f + expf(-a1)); }

@@ -11,7 +11,7 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import diffsinger_b200 as ds  # noqa: E402
-from diffsinger_b200.synthetic import random_state_dict  # noqa: E402
+from diffsinger_b200.synthetic import random_state_dict, random_lynx_state_dict  # noqa: E402
 
 dev = "cuda"
 
@@ -67,6 +67,25 @@ def acoustic(kind, algo, B, T, C=512, L=20, iters=3, precision="bf16"):
     return out
 
 
+def lynx(algo, B, T, iters=3):
+    """The reference's default acoustic backbone (LYNXNet 6 x 512, expansion 2, k = 31; configs/acoustic.yaml:73-79)."""
+    M, L, C = 128, 6, 512
+    hp(diff_accelerator=algo)
+    m = ds.GaussianDiffusion(M, 1, 1000, 1000, "lynxnet", dict(num_layers=L, num_channels=C, expansion_factor=2, kernel_size=31),
+                             spec_min=[-12.0], spec_max=[0.0])
+    m.denoise_fn.load_state_dict(random_lynx_state_dict(M, 1, L, C, 256, seed=1234))
+    m = m.eval().to(dev)
+    cond = torch.randn(B, T, 256, device=dev)
+    with torch.no_grad():
+        ms = timed(lambda: m(cond, infer=True), iters)
+    ws = next(iter(m.denoise_fn.engine().workspaces.values()))
+    flops = 2.0 * B * T * 20 * (L * (256 * C + C * 4 * C + 2 * C * C) + 2 * M * C)  # 1x1 convs only (depthwise / norms are HBM-bound)
+    print(json.dumps(dict(case=f"lynxnet/{algo}", C=C, L=L, B=B, T=T, ms=round(ms, 3), frames_per_s=round(B * T / ms * 1e3, 1),
+                          gemm_tflops=round(flops / ms / 1e9, 1), launches=ws.last_launches)), flush=True)
+    del m, cond
+    torch.cuda.empty_cache()
+
+
 def variance(T, iters=20):
     """config #4: PitchDiffusion (C256 L20 cycle5, 64 repeat bins) + MultiVarianceDiffusion (C192 L10 cycle4, 2 x 24 bins), B=1."""
     for algo in ("ddim", "dpm-solver", "unipc"):
@@ -94,13 +113,16 @@ def variance(T, iters=20):
 
 
 def main():
-    what = sys.argv[1:] or ["acoustic", "reflow", "variance", "grid"]
+    what = sys.argv[1:] or ["acoustic", "lynxnet", "reflow", "variance", "grid"]
     if "acoustic" in what:
         for algo in ("ddim", "pndm", "dpm-solver", "unipc"):
             if algo == "pndm":
                 acoustic("ddpm", algo, 1, 2000)  # the reference's PNDM is batch-1 only
             acoustic("ddpm", algo, 64, 2000)
         acoustic("ddpm", "dpm-solver", 8, 1000, iters=2, precision="fp32")
+    if "lynxnet" in what:
+        for B, T in ((64, 2000), (8, 1000), (1, 500)):
+            lynx("dpm-solver", B, T)
     if "reflow" in what:
         for algo in ("euler", "rk2", "rk4"):
             acoustic("reflow", algo, 64, 2000, iters=2)
