@@ -4,9 +4,10 @@ Host code is Python/PyTorch plumbing over the C ABI in include/dsb200.h (libdsb2
 from .hparams import hparams, get_hparams
 from .backbones import BACKBONES, build_backbone, WaveNet, LYNXNet
 from .segments import sample_segments
+from .aux_decoder import AUX_DECODERS, AuxDecoderAdaptor, ConvNeXtDecoder, build_aux_decoder
 from .core import (GaussianDiffusion, PitchDiffusion, MultiVarianceDiffusion,
                    RectifiedFlow, PitchRectifiedFlow, MultiVarianceRectifiedFlow)
 
 __all__ = ["hparams", "get_hparams", "BACKBONES", "build_backbone", "WaveNet", "LYNXNet", "GaussianDiffusion",
            "PitchDiffusion", "MultiVarianceDiffusion", "RectifiedFlow", "PitchRectifiedFlow",
-           "MultiVarianceRectifiedFlow", "sample_segments"]
+           "MultiVarianceRectifiedFlow", "sample_segments", "AUX_DECODERS", "AuxDecoderAdaptor", "ConvNeXtDecoder", "build_aux_decoder"]

@@ -21,21 +21,11 @@ import torch
 import torch.nn.functional as F
 
 from . import _native as nat
+from . import ops
 from .engine import Program
 
 
-def _st() -> int:
-    return torch.cuda.current_stream().cuda_stream
-
-
-def _bn(n: int) -> int:
-    if n % 64:
-        raise nat.NativeError(f"GEMM width {n} must be a multiple of 64")
-    return 256 if n % 256 == 0 else (128 if n % 128 == 0 else 64)
-
-
-def _pad64(n: int) -> int:
-    return (n + 63) // 64 * 64
+_st, _bn, _pad64 = ops.stream, ops.tile_n, ops.pad64
 
 
 class LynxWorkspace:
@@ -54,7 +44,7 @@ class LynxWorkspace:
     def set_cond(self, cond_bth: torch.Tensor):
         c = cond_bth.detach().to(torch.float32).contiguous()
         assert c.shape == (self.B, self.T, self.eng.H), c.shape
-        nat.check(nat.lib().ds_cast_bf16(self.cond.data_ptr(), c.data_ptr(), self.B * self.T, self.eng.H, self.eng.H, _st()))
+        ops.cast_bf16(self.cond, c.view(self.B * self.T, self.eng.H))
 
     def bufs(self, n: int) -> List[torch.Tensor]:
         while len(self._bufs) < n:
@@ -153,50 +143,28 @@ class LynxEngine:
         return ws
 
     # ------------------------------------------------------------------ one evaluation
-    def _gemm(self, epi, BN, B, T, a, a_ch, w, w_rows, w_k, out, ld_out, bias=None, vec=None, vec_bstride=0, res=None, act=0,
-              n_real=0, scale=1.0):
-        d = nat.GemmDesc()
-        d.epi, d.BN, d.B, d.T = epi, BN, B, T
-        d.a0, d.a0_channels, d.a0_c0, d.kb_a0, d.n_taps, d.dil = a.data_ptr(), a_ch, 0, w_k // 64, 1, 0
-        d.a1, d.a1_channels, d.kb_a1 = None, 0, 0
-        d.w, d.w_rows, d.w_k, d.b_row0, d.n_tiles = w.data_ptr(), w_rows, w_k, 0, w_rows // BN
-        d.bias = bias.data_ptr() if bias is not None else None
-        d.vec_sub = None
-        d.vec_add, d.vec_bstride = (vec.data_ptr() if vec is not None else None), vec_bstride
-        d.res_in, d.ld_res = (res.data_ptr() if res is not None else None), (res.shape[1] if res is not None else 0)
-        d.out, d.ld_out, d.out_c0, d.n_real = out.data_ptr(), ld_out, 0, n_real
-        d.relu, d.scale = act, scale
-        nat.check(nat.lib().ds_gemm(C.byref(d), _st()))
-
     def eval(self, ws: LynxWorkspace, x_f32: torch.Tensor, vecs: torch.Tensor, out_f32: torch.Tensor) -> int:
         """x / out: fp32 [B, T, F*M] time-major; vecs: fp32 [L, Bt, C] step vectors of this evaluation.  Returns #launches."""
-        L, w, B, T, Cc, I = nat.lib(), self.w, ws.B, ws.T, self.C, self.I
+        w, B, T, Cc = self.w, ws.B, ws.T, self.C
         rows = B * T
         Bt = vecs.shape[1]
-        nat.check(L.ds_cast_bf16(ws.xb.data_ptr(), x_f32.data_ptr(), rows, self.FM, self.FMp, _st()))
-        self._gemm(0, self.bn_c, B, T, ws.xb, self.FMp, w["w_in"], Cc, self.FMp, ws.h, Cc, bias=w["b_in"], act=0 if self.strong else 2)
-        n = 2
+        ops.cast_bf16(ws.xb, x_f32.view(rows, self.FM))
+        ops.gemm(ops.EPI_LINEAR, self.bn_c, B, T, ws.xb, w["w_in"], ws.h, bias=w["b_in"], act=ops.ACT_NONE if self.strong else ops.ACT_GELU)
         for i, lw in enumerate(w["layers"]):
             dvec = vecs[i]  # [Bt, C]
             if self.strong:  # res_x = x + cond projection; the step vector is added on the way into the norm
-                self._gemm(2, self.bn_c, B, T, ws.cond, self.H, lw["wc"], Cc, self.H, ws.u, Cc, vec=lw["bc"], vec_bstride=0, res=ws.h)
+                ops.gemm(ops.EPI_RES, self.bn_c, B, T, ws.cond, lw["wc"], ws.u, vec=lw["bc"], vec_bstride=0, res=ws.h)
                 res, ln_vec = ws.u, dvec
             else:            # res_x = x; u = x + cond projection + (bias + step vector)
-                self._gemm(2, self.bn_c, B, T, ws.cond, self.H, lw["wc"], Cc, self.H, ws.u, Cc, vec=dvec,
-                           vec_bstride=Cc if Bt > 1 else 0, res=ws.h)
+                ops.gemm(ops.EPI_RES, self.bn_c, B, T, ws.cond, lw["wc"], ws.u, vec=dvec, vec_bstride=Cc if Bt > 1 else 0, res=ws.h)
                 res, ln_vec = ws.h, None
-            nat.check(L.ds_layernorm(ws.n.data_ptr(), ws.u.data_ptr(), lw["ln_g"].data_ptr(), lw["ln_b"].data_ptr(), rows, Cc, 1e-5,
-                                     ln_vec.data_ptr() if ln_vec is not None else None, T if Bt > 1 else rows, _st()))
-            self._gemm(5, self.bn_g, B, T, ws.n, Cc, lw["w2"], 2 * I, Cc, ws.g, I, bias=lw["b2"])
-            nat.check(L.ds_dwconv(ws.dw.data_ptr(), ws.g.data_ptr(), lw["dw_w"].data_ptr(), lw["dw_b"].data_ptr(),
-                                  lw["slope"].data_ptr() if lw["slope"] is not None else None, B, T, I, self.k, self.k // 2,
-                                  self.act, _st()))
-            self._gemm(2, self.bn_c, B, T, ws.dw, I, lw["w6"], Cc, I, ws.h, Cc, vec=lw["b6"], vec_bstride=0, res=res)
-            n += 5
-        nat.check(L.ds_layernorm(ws.n.data_ptr(), ws.h.data_ptr(), w["norm_g"].data_ptr(), w["norm_b"].data_ptr(), rows, Cc, 1e-5,
-                                 None, 0, _st()))
-        self._gemm(3, self.bn_o, B, T, ws.n, Cc, w["w_out"], self.FMr, Cc, out_f32, self.FM, bias=w["b_out"], n_real=self.FM)
-        return n + 2
+            ops.layernorm(ws.n, ws.u, lw["ln_g"], lw["ln_b"], 1e-5, ln_vec, T if Bt > 1 else rows)
+            ops.gemm(ops.EPI_SWIGLU, self.bn_g, B, T, ws.n, lw["w2"], ws.g, bias=lw["b2"])
+            ops.dwconv(ws.dw, ws.g, lw["dw_w"], lw["dw_b"], B, T, self.k, self.act, lw["slope"])
+            ops.gemm(ops.EPI_RES, self.bn_c, B, T, ws.dw, lw["w6"], ws.h, vec=lw["b6"], vec_bstride=0, res=res)
+        ops.layernorm(ws.n, ws.h, w["norm_g"], w["norm_b"], 1e-5)
+        ops.gemm(ops.EPI_OUTF32, self.bn_o, B, T, ws.n, w["w_out"], out_f32.view(rows, self.FM), bias=w["b_out"], n_real=self.FM)
+        return 5 * self.L + 4
 
     # ------------------------------------------------------------------ sampler programs
     @torch.no_grad()
@@ -233,15 +201,11 @@ class LynxEngine:
         return bufs[0].clone()
 
     def _run_ops(self, ws: LynxWorkspace, prog: Program, bufs: List[torch.Tensor], vecs: torch.Tensor) -> int:
-        L = nat.lib()
-        numel = bufs[0].numel()
         launches = 0
         for kind, dst, time, srcs, coefs in prog.ops:
             if kind == nat.DS_OP_EVAL:
                 launches += self.eval(ws, bufs[srcs[0]], vecs[time], bufs[dst])
             else:
-                ptrs = (C.c_void_p * len(srcs))(*[bufs[s].data_ptr() for s in srcs])
-                cf = (C.c_float * len(coefs))(*coefs)
-                nat.check(L.ds_lincomb(bufs[dst].data_ptr(), ptrs, cf, len(srcs), numel, _st()))
+                ops.lincomb(bufs[dst], [bufs[s] for s in srcs], coefs)
                 launches += 1
         return launches

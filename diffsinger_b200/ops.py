@@ -1,0 +1,80 @@
+"""Thin host wrappers of the primitive ops of libdsb200.so (include/dsb200.h: ds_gemm, ds_layernorm, ds_dwconv, ds_cast_bf16,
+ds_lincomb).  Tensors are time-major: bf16 activations [B*T, channels], bf16 weights [rows][K], fp32 vectors.  Every call
+launches on the current CUDA stream and returns immediately; nothing here computes in PyTorch."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import torch
+
+from . import _native as nat
+
+EPI_LINEAR, EPI_GATE, EPI_RES, EPI_OUTF32, EPI_SWIGLU = 0, 1, 2, 3, 5
+ACT_NONE, ACT_RELU, ACT_GELU = 0, 1, 2
+DW_NONE, DW_RELU, DW_PRELU, DW_SILU = 0, 1, 2, 3
+
+
+def stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def tile_n(n: int) -> int:
+    """N tile of a GEMM with n output rows (multiple of 64)."""
+    if n % 64:
+        raise nat.NativeError(f"GEMM width {n} must be a multiple of 64")
+    return 256 if n % 256 == 0 else (128 if n % 128 == 0 else 64)
+
+
+def pad64(n: int) -> int:
+    return (n + 63) // 64 * 64
+
+
+def _p(t: Optional[torch.Tensor]):
+    return t.data_ptr() if t is not None else None
+
+
+def gemm(epi: int, BN: int, B: int, T: int, a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, k_per_tap: Optional[int] = None,
+         n_taps: int = 1, bias: Optional[torch.Tensor] = None, vec: Optional[torch.Tensor] = None, vec_bstride: int = 0,
+         res: Optional[torch.Tensor] = None, act: int = ACT_NONE, n_real: int = 0, scale: float = 1.0):
+    """out[b, t, n] = epilogue(sum_tap sum_k a[b, t + tap - n_taps // 2, k] * w[n, tap * K + k]); frames outside [0, T) read as
+    zeros (the conv's zero padding).  a: [B*T, K_in] bf16, w: [rows, n_taps * K] bf16, out: bf16 (fp32 for EPI_OUTF32)."""
+    a_ch = a.shape[1]
+    k = a_ch if k_per_tap is None else k_per_tap
+    rows, w_k = w.shape
+    assert w_k == n_taps * k and k % 64 == 0 and rows % BN == 0, (w.shape, n_taps, k, BN)
+    d = nat.GemmDesc()
+    d.epi, d.BN, d.B, d.T = epi, BN, B, T
+    d.a0, d.a0_channels, d.a0_c0, d.kb_a0, d.n_taps, d.dil = a.data_ptr(), a_ch, 0, k // 64, n_taps, 1
+    d.a1, d.a1_channels, d.kb_a1 = None, 0, 0
+    d.w, d.w_rows, d.w_k, d.b_row0, d.n_tiles = w.data_ptr(), rows, w_k, 0, rows // BN
+    d.bias, d.vec_sub, d.vec_add, d.vec_bstride = _p(bias), None, _p(vec), vec_bstride
+    d.res_in, d.ld_res = _p(res), (res.shape[1] if res is not None else 0)
+    d.out, d.ld_out, d.out_c0, d.n_real = out.data_ptr(), out.shape[-1], 0, n_real
+    d.relu, d.scale = act, scale
+    nat.check(nat.lib().ds_gemm(C.byref(d), stream()))
+
+
+def layernorm(y: torch.Tensor, x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float = 1e-5,
+              vec: Optional[torch.Tensor] = None, rows_per_vec: int = 0):
+    rows, ch = x.shape
+    nat.check(nat.lib().ds_layernorm(y.data_ptr(), x.data_ptr(), gamma.data_ptr(), beta.data_ptr(), rows, ch, eps, _p(vec), rows_per_vec,
+                                     stream()))
+
+
+def dwconv(y: torch.Tensor, x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], B: int, T: int, kernel_size: int,
+           act: int = DW_NONE, slope: Optional[torch.Tensor] = None):
+    nat.check(nat.lib().ds_dwconv(y.data_ptr(), x.data_ptr(), w.data_ptr(), _p(bias), _p(slope), B, T, x.shape[1], kernel_size,
+                                  kernel_size // 2, act, stream()))
+
+
+def cast_bf16(dst: torch.Tensor, src: torch.Tensor):
+    """fp32 [rows, cols] -> bf16 [rows, ld >= cols] (zero padded)."""
+    rows, cols = src.shape[0], src.shape[1]
+    nat.check(nat.lib().ds_cast_bf16(dst.data_ptr(), src.data_ptr(), rows, cols, dst.shape[1], stream()))
+
+
+def lincomb(dst: torch.Tensor, srcs: Sequence[torch.Tensor], coefs: Sequence[float]):
+    ptrs = (C.c_void_p * len(srcs))(*[s.data_ptr() for s in srcs])
+    cf = (C.c_float * len(coefs))(*coefs)
+    nat.check(nat.lib().ds_lincomb(dst.data_ptr(), ptrs, cf, len(srcs), dst.numel(), stream()))

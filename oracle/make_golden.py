@@ -207,11 +207,38 @@ def gen_lynxnet(ref):
               **{"w." + k: v.numpy() for k, v in net.state_dict().items()})
 
 
+def gen_aux_decoder(ref):
+    """ConvNeXt aux decoder through AuxDecoderAdaptor (modules/aux_decoder/__init__.py:30-75, convnext.py:58-87) with
+    non-trivial layer scales (they are initialised to 1e-6, which would hide the blocks)."""
+    from modules.aux_decoder import AuxDecoderAdaptor
+    for tag, Fn in (("f1", 1), ("f2", 2)):
+        torch.manual_seed(400 + Fn)
+        M = 16 // Fn
+        smin, smax = ([-12.0] if Fn == 1 else [[-96.0], [-80.0]]), ([0.0] if Fn == 1 else [[-12.0], [-20.0]])
+        ad = AuxDecoderAdaptor(HIDDEN, M, Fn, smin, smax, "convnext",
+                               dict(num_channels=64, num_layers=2, kernel_size=7, dropout_rate=0.1)).eval()
+        with torch.no_grad():
+            for blk in ad.decoder.conv:
+                blk.gamma.copy_(0.5 + torch.rand_like(blk.gamma))
+                blk.norm.weight.copy_(1.0 + 0.2 * torch.randn_like(blk.norm.weight))
+                blk.norm.bias.copy_(0.1 * torch.randn_like(blk.norm.bias))
+        cond = torch.randn(2, 53, HIDDEN)
+        with torch.no_grad():
+            y = ad(cond, infer=True)
+            y_raw = ad(cond, infer=False)
+        _save(f"auxdec_{tag}", cond=cond.numpy(), y=y.numpy(), y_raw=y_raw.numpy(), cfg=np.array([HIDDEN, M, Fn, 64, 2, 7]),
+              spec_min=np.array(smin, dtype=np.float32), spec_max=np.array(smax, dtype=np.float32),
+              **{"w." + k: v.numpy() for k, v in ad.state_dict().items()})
+
+
 def main():
     ref = load_reference()
-    if "lynxnet" in os.environ.get("GOLDEN_ONLY", "lynxnet"):
+    only = os.environ.get("GOLDEN_ONLY", "")
+    if not only or "auxdec" in only:
+        gen_aux_decoder(ref)
+    if not only or "lynxnet" in only:
         gen_lynxnet(ref)
-    if os.environ.get("GOLDEN_ONLY"):
+    if only:
         return
     gen_backbone(ref)
     gen_ddpm(ref)

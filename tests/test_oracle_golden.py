@@ -105,3 +105,20 @@ def test_lynxnet_forward(tag):
         y = net(d["spec"], d[tk], d["cond"])
         assert y.shape == d[yk].shape
         assert rel_l2(y, d[yk]) < 2e-6
+
+
+@pytest.mark.parametrize("tag", ["f1", "f2"])
+def test_aux_decoder(tag):
+    """The ConvNeXt aux decoder restatement against the imported reference's outputs (modules/aux_decoder)."""
+    import os
+    import numpy as np
+    from conftest import GOLDEN
+    from oracle.auxdec_oracle import aux_decoder
+    z = np.load(os.path.join(GOLDEN, f"auxdec_{tag}.npz"))
+    H, M, Fn, C, L, k = [int(v) for v in z["cfg"]]
+    sd = {key[2:]: torch.from_numpy(z[key]) for key in z.files if key.startswith("w.")}
+    cond = torch.from_numpy(z["cond"])
+    y = aux_decoder(sd, cond, Fn, M, z["spec_min"], z["spec_max"], infer=True)
+    assert y.shape == z["y"].shape and rel_l2(y, torch.from_numpy(z["y"])) < 2e-6
+    y = aux_decoder(sd, cond, Fn, M, infer=False)
+    assert rel_l2(y, torch.from_numpy(z["y_raw"])) < 2e-6
