@@ -908,7 +908,7 @@ extern "C" int ds_layernorm(void* y_bf16, const void* x_bf16, const float* gamma
   if (!y_bf16 || !x_bf16 || !gamma || !beta || rows <= 0) return fail(DS_ERR_INVALID, "bad argument");
   if (channels <= 0 || channels % 8 || channels > 2048) return fail(DS_ERR_INVALID, "channels=%d must be a multiple of 8 in (0, 2048]", channels);
   DS_TRY(ensure_device());
-  const long blocks = (rows + 7) / 8;  // 8 warps (rows) per 256-thread block
+  const long blocks = (rows + 15) / 16;  // 8 warps per 256-thread block, up to two rows per warp iteration
   const long cap = (long)g_num_sms * 32;
   const int grid = (int)(blocks < cap ? blocks : cap);
   cudaStream_t st = (cudaStream_t)stream;

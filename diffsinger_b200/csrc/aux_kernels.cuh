@@ -222,67 +222,90 @@ namespace dsb {
 // x'[r] = x[r] + vec[r / rows_per_vec] (optional fp32 per-utterance vector: the diffusion-step projection, lynxnet.py:89).
 // One warp per row, the row lives in registers (C <= 2048, C % 8 == 0), two-pass statistics in fp32 (biased variance,
 // like torch.nn.LayerNorm; lynxnet.py:52,123).
-template <int kMaxChunks>  // ceil(C / 256): the row lives in kMaxChunks x 8 registers per lane
+template <int kMaxChunks>  // ceil(C / 256): a row lives in kMaxChunks x 8 registers per lane
 __global__ void layernorm_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
                                  const float* __restrict__ beta, long rows, int C, float eps, const float* __restrict__ vec,
                                  long rows_per_vec) {
   grid_dep_launch();
   grid_dep_wait();
+  constexpr int kRows = kMaxChunks <= 2 ? 2 : 1;  // rows per warp iteration: two independent rows keep more bytes in flight
   const int lane = threadIdx.x & 31;
   const long warp0 = (static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   const long nwarps = (static_cast<long>(gridDim.x) * blockDim.x) >> 5;
   const int nch = (C + 255) / 256;
-  for (long r = warp0; r < rows; r += nwarps) {
-    float v[kMaxChunks][8];
-    float sum = 0.f;
+  for (long r0 = warp0 * kRows; r0 < rows; r0 += nwarps * kRows) {
+    float v[kRows][kMaxChunks][8];
+    float sum[kRows];
 #pragma unroll
-    for (int i = 0; i < kMaxChunks; ++i) {
-      const int e = (i * 32 + lane) * 8;
-      if (i < nch && e < C) {
-        const uint4 q = *reinterpret_cast<const uint4*>(x + r * C + e);
-        const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+    for (int q = 0; q < kRows; ++q) {
+      const long r = r0 + q < rows ? r0 + q : rows - 1;  // the tail warp recomputes the last row (same values rewritten)
+      sum[q] = 0.f;
 #pragma unroll
-        for (int h = 0; h < 4; ++h) {
-          v[i][2 * h] = __uint_as_float(w[h] << 16);
-          v[i][2 * h + 1] = __uint_as_float(w[h] & 0xffff0000u);
+      for (int i = 0; i < kMaxChunks; ++i) {
+        const int e = (i * 32 + lane) * 8;
+        if (i < nch && e < C) {
+          const uint4 qv = *reinterpret_cast<const uint4*>(x + r * C + e);
+          const uint32_t w[4] = {qv.x, qv.y, qv.z, qv.w};
+#pragma unroll
+          for (int h = 0; h < 4; ++h) {
+            v[q][i][2 * h] = __uint_as_float(w[h] << 16);
+            v[q][i][2 * h + 1] = __uint_as_float(w[h] & 0xffff0000u);
+          }
           if (vec) {
             const float* vr = vec + (r / rows_per_vec) * C + e;
-            v[i][2 * h] += __ldg(vr + 2 * h);
-            v[i][2 * h + 1] += __ldg(vr + 2 * h + 1);
+#pragma unroll
+            for (int h = 0; h < 8; ++h) v[q][i][h] += __ldg(vr + h);
           }
-          sum += v[i][2 * h] + v[i][2 * h + 1];
-        }
-      } else {
 #pragma unroll
-        for (int h = 0; h < 8; ++h) v[i][h] = 0.f;
-      }
-    }
-    for (int s = 16; s > 0; s >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, s);
-    const float mean = sum / static_cast<float>(C);
-    float sq = 0.f;
+          for (int h = 0; h < 8; ++h) sum[q] += v[q][i][h];
+        } else {
 #pragma unroll
-    for (int i = 0; i < kMaxChunks; ++i) {
-      const int e = (i * 32 + lane) * 8;
-      if (i < nch && e < C) {
-#pragma unroll
-        for (int h = 0; h < 8; ++h) {
-          const float d = v[i][h] - mean;
-          sq = fmaf(d, d, sq);
+          for (int h = 0; h < 8; ++h) v[q][i][h] = 0.f;
         }
       }
     }
-    for (int s = 16; s > 0; s >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, s);
-    const float rstd = rsqrtf(sq / static_cast<float>(C) + eps);
 #pragma unroll
-    for (int i = 0; i < kMaxChunks; ++i) {
-      const int e = (i * 32 + lane) * 8;
-      if (i < nch && e < C) {
-        float o[8];
+    for (int q = 0; q < kRows; ++q)
+      for (int s = 16; s > 0; s >>= 1) sum[q] += __shfl_xor_sync(0xffffffffu, sum[q], s);
+    float mean[kRows], sq[kRows];
 #pragma unroll
-        for (int h = 0; h < 8; ++h) o[h] = (v[i][h] - mean) * rstd * __ldg(gamma + e + h) + __ldg(beta + e + h);
-        uint4 q;
-        q.x = pack_bf16(o[0], o[1]); q.y = pack_bf16(o[2], o[3]); q.z = pack_bf16(o[4], o[5]); q.w = pack_bf16(o[6], o[7]);
-        *reinterpret_cast<uint4*>(y + r * C + e) = q;
+    for (int q = 0; q < kRows; ++q) {
+      mean[q] = sum[q] / static_cast<float>(C);
+      sq[q] = 0.f;
+#pragma unroll
+      for (int i = 0; i < kMaxChunks; ++i) {
+        const int e = (i * 32 + lane) * 8;
+        if (i < nch && e < C) {
+#pragma unroll
+          for (int h = 0; h < 8; ++h) {
+            const float d = v[q][i][h] - mean[q];
+            sq[q] = fmaf(d, d, sq[q]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < kRows; ++q)
+      for (int s = 16; s > 0; s >>= 1) sq[q] += __shfl_xor_sync(0xffffffffu, sq[q], s);
+#pragma unroll
+    for (int q = 0; q < kRows; ++q) {
+      const long r = r0 + q < rows ? r0 + q : rows - 1;
+      const float rstd = rsqrtf(sq[q] / static_cast<float>(C) + eps);
+#pragma unroll
+      for (int i = 0; i < kMaxChunks; ++i) {
+        const int e = (i * 32 + lane) * 8;
+        if (i < nch && e < C) {
+          const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + e)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + e) + 1);
+          const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + e)), b1 = __ldg(reinterpret_cast<const float4*>(beta + e) + 1);
+          const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+          const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+          float o[8];
+#pragma unroll
+          for (int h = 0; h < 8; ++h) o[h] = (v[q][i][h] - mean[q]) * rstd * gg[h] + bb[h];
+          uint4 qo;
+          qo.x = pack_bf16(o[0], o[1]); qo.y = pack_bf16(o[2], o[3]); qo.z = pack_bf16(o[4], o[5]); qo.w = pack_bf16(o[6], o[7]);
+          *reinterpret_cast<uint4*>(y + r * C + e) = qo;
+        }
       }
     }
   }
