@@ -127,7 +127,7 @@ def lib() -> C.CDLL:
     L.ds_plan_precision.argtypes = [C.c_void_p]
     L.ds_gemm.argtypes = [C.POINTER(GemmDesc), C.c_void_p]
     L.ds_layernorm.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_float, C.c_void_p,
-                               C.c_int64, C.c_void_p]
+                               C.c_int64, C.c_void_p, C.c_void_p]
     L.ds_dwconv.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                             C.c_int32, C.c_int32, C.c_void_p]
     L.ds_cast_bf16.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p]

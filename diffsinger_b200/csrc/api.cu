@@ -882,6 +882,9 @@ extern "C" int ds_transpose(float* dst, const float* src, int32_t B, int32_t R, 
 
 extern "C" int ds_debug_gemm(const ds_gemm_desc* d, void* stream) {
   if (!d) return fail(DS_ERR_INVALID, "null argument");
+  if (!d->a0 || !d->w || !d->out) return fail(DS_ERR_INVALID, "ds_gemm: null operand");
+  if (d->epi == EPI_RES ? (!d->res_in || !d->vec_add) : !d->bias)
+    return fail(DS_ERR_INVALID, "ds_gemm: epilogue %d needs %s", d->epi, d->epi == EPI_RES ? "res_in and vec_add" : "bias");
   DS_TRY(ensure_device());
   GemmParams g;
   memset(&g, 0, sizeof(g));
@@ -903,7 +906,7 @@ extern "C" int ds_debug_gemm(const ds_gemm_desc* d, void* stream) {
 extern "C" int ds_gemm(const ds_gemm_desc* d, void* stream) { return ds_debug_gemm(d, stream); }
 
 extern "C" int ds_layernorm(void* y_bf16, const void* x_bf16, const float* gamma, const float* beta, int64_t rows, int32_t channels,
-                            float eps, const float* vec, int64_t rows_per_vec, void* stream) {
+                            float eps, const float* vec, int64_t rows_per_vec, const void* add_bf16, void* stream) {
   if (vec && rows_per_vec <= 0) return fail(DS_ERR_INVALID, "rows_per_vec must be positive");
   if (!y_bf16 || !x_bf16 || !gamma || !beta || rows <= 0) return fail(DS_ERR_INVALID, "bad argument");
   if (channels <= 0 || channels % 8 || channels > 2048) return fail(DS_ERR_INVALID, "channels=%d must be a multiple of 8 in (0, 2048]", channels);
@@ -914,11 +917,12 @@ extern "C" int ds_layernorm(void* y_bf16, const void* x_bf16, const float* gamma
   cudaStream_t st = (cudaStream_t)stream;
   __nv_bfloat16* yp = (__nv_bfloat16*)y_bf16;
   const __nv_bfloat16* xp = (const __nv_bfloat16*)x_bf16;
+  const __nv_bfloat16* ap = (const __nv_bfloat16*)add_bf16;
   const int nch = ceil_div(channels, 256);
-  if (nch <= 1) layernorm_kernel<1><<<grid, 256, 0, st>>>(yp, xp, gamma, beta, (long)rows, channels, eps, vec, (long)rows_per_vec);
-  else if (nch <= 2) layernorm_kernel<2><<<grid, 256, 0, st>>>(yp, xp, gamma, beta, (long)rows, channels, eps, vec, (long)rows_per_vec);
-  else if (nch <= 4) layernorm_kernel<4><<<grid, 256, 0, st>>>(yp, xp, gamma, beta, (long)rows, channels, eps, vec, (long)rows_per_vec);
-  else layernorm_kernel<8><<<grid, 256, 0, st>>>(yp, xp, gamma, beta, (long)rows, channels, eps, vec, (long)rows_per_vec);
+  if (nch <= 1) layernorm_kernel<1><<<grid, 256, 0, st>>>(yp, xp, gamma, beta, (long)rows, channels, eps, vec, (long)rows_per_vec, ap);
+  else if (nch <= 2) layernorm_kernel<2><<<grid, 256, 0, st>>>(yp, xp, gamma, beta, (long)rows, channels, eps, vec, (long)rows_per_vec, ap);
+  else if (nch <= 4) layernorm_kernel<4><<<grid, 256, 0, st>>>(yp, xp, gamma, beta, (long)rows, channels, eps, vec, (long)rows_per_vec, ap);
+  else layernorm_kernel<8><<<grid, 256, 0, st>>>(yp, xp, gamma, beta, (long)rows, channels, eps, vec, (long)rows_per_vec, ap);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }

@@ -219,13 +219,14 @@ namespace dsb {
 
 // ------------------------------------------------------------------ primitives for the other denoisers (LYNXNet, aux decoder)
 // LayerNorm over the channel axis of time-major bf16 activations: y[r][:] = (x'[r][:] - mean) * rstd * gamma + beta with
-// x'[r] = x[r] + vec[r / rows_per_vec] (optional fp32 per-utterance vector: the diffusion-step projection, lynxnet.py:89).
+// x'[r] = x[r] + add[r] + vec[r / rows_per_vec] (both optional: a second bf16 operand and an fp32 per-utterance vector -- the
+// conditioner projection and the diffusion-step projection of lynxnet.py:82-89).
 // One warp per row, the row lives in registers (C <= 2048, C % 8 == 0), two-pass statistics in fp32 (biased variance,
 // like torch.nn.LayerNorm; lynxnet.py:52,123).
 template <int kMaxChunks>  // ceil(C / 256): a row lives in kMaxChunks x 8 registers per lane
 __global__ void layernorm_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
                                  const float* __restrict__ beta, long rows, int C, float eps, const float* __restrict__ vec,
-                                 long rows_per_vec) {
+                                 long rows_per_vec, const __nv_bfloat16* __restrict__ add) {
   grid_dep_launch();
   grid_dep_wait();
   constexpr int kRows = kMaxChunks <= 2 ? 2 : 1;  // rows per warp iteration: two independent rows keep more bytes in flight
@@ -250,6 +251,15 @@ __global__ void layernorm_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloa
           for (int h = 0; h < 4; ++h) {
             v[q][i][2 * h] = __uint_as_float(w[h] << 16);
             v[q][i][2 * h + 1] = __uint_as_float(w[h] & 0xffff0000u);
+          }
+          if (add) {  // second bf16 operand (LYNXNet: the step-invariant conditioner projection, hoisted out of the loop)
+            const uint4 qa = *reinterpret_cast<const uint4*>(add + r * C + e);
+            const uint32_t wa[4] = {qa.x, qa.y, qa.z, qa.w};
+#pragma unroll
+            for (int h = 0; h < 4; ++h) {
+              v[q][i][2 * h] += __uint_as_float(wa[h] << 16);
+              v[q][i][2 * h + 1] += __uint_as_float(wa[h] & 0xffff0000u);
+            }
           }
           if (vec) {
             const float* vr = vec + (r / rows_per_vec) * C + e;
@@ -364,17 +374,17 @@ __global__ void __launch_bounds__(128) dwconv_kernel(__nv_bfloat16* __restrict__
     for (int s = 0; s < K; ++s) {
       const int o = g * K + s;  // output frame t0 + o needs rows o .. o + K - 1; row o + K - 1 goes to slot (s + K - 1) % K
       win[(s + K - 1) % K] = row(o + K - 1);
-      unsigned long long acc_e = bv, acc_o = 0ull;
+      unsigned long long acc[4] = {bv, 0ull, 0ull, 0ull};  // four independent chains over the taps
 #pragma unroll
-      for (int j = 0; j < K; ++j) {
-        if (j & 1) acc_o = fma_f32x2(wv[j], win[(s + j) % K], acc_o);
-        else acc_e = fma_f32x2(wv[j], win[(s + j) % K], acc_e);
+      for (int j = 0; j < K; ++j) acc[j & 3] = fma_f32x2(wv[j], win[(s + j) % K], acc[j & 3]);
+      float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        float p0, p1;
+        unpack_f32x2(acc[c], p0, p1);
+        a0 += p0;
+        a1 += p1;
       }
-      float a0, a1, o0, o1;
-      unpack_f32x2(acc_e, a0, a1);
-      unpack_f32x2(acc_o, o0, o1);
-      a0 += o0;
-      a1 += o1;
       if (act == 1) { a0 = fmaxf(a0, 0.f); a1 = fmaxf(a1, 0.f); }
       else if (act == 2) { a0 = a0 > 0.f ? a0 : s0 * a0; a1 = a1 > 0.f ? a1 : s1 * a1; }
       else if (act == 3) { a0 = a0 / (1.f + expf(-a0)); a1 = a1 / (1.f + expf(-a1)); }

@@ -5,6 +5,8 @@ One evaluation (reference ``LYNXNet.forward``, modules/backbones/lynxnet.py:133-
 
     cast x -> bf16 | GEMM input_projection (+GELU)                                             lynxnet.py:145-147
     per layer:       GEMM conditioner_projection, epilogue  + x + (b_c + W_d d + b_d)[b]       :82-89
+                     (sampler programs, strong_cond = False: W_c cond is step-invariant, so it is computed once per
+                     run for all layers and added -- with the step vector -- on the way into the LayerNorm)
                      LayerNorm | GEMM C -> 2I, SwiGLU epilogue | depthwise k conv + act        :52-60
                      GEMM I -> C, epilogue + residual + bias                                   :61,92
     LayerNorm | GEMM output_projection -> fp32                                                 :157-160
@@ -37,6 +39,7 @@ class LynxWorkspace:
         mk = lambda ch: torch.empty(rows, ch, dtype=bf, device=dev)
         self.xb, self.cond = mk(eng.FMp), mk(eng.H)
         self.h, self.u, self.n, self.g, self.dw = mk(eng.C), mk(eng.C), mk(eng.C), mk(eng.I), mk(eng.I)
+        self.cproj = None  # [L, rows, C] bf16: W_c cond of every layer, hoisted out of a sampler program's loop
         self._bufs: List[torch.Tensor] = []
         self.graphs: Dict[Tuple, torch.cuda.CUDAGraph] = {}
         self.last_launches = 0
@@ -45,6 +48,15 @@ class LynxWorkspace:
         c = cond_bth.detach().to(torch.float32).contiguous()
         assert c.shape == (self.B, self.T, self.eng.H), c.shape
         ops.cast_bf16(self.cond, c.view(self.B * self.T, self.eng.H))
+
+    def hoist_cond(self):
+        """cproj[l] = W_c_l cond (bias excluded: it travels with the step vector).  L launches, once per sampler run."""
+        eng = self.eng
+        if self.cproj is None:
+            self.cproj = torch.empty(eng.L, self.B * self.T, eng.C, dtype=torch.bfloat16, device=eng.device)
+        for i, lw in enumerate(eng.w["layers"]):
+            ops.gemm(ops.EPI_LINEAR, eng.bn_c, self.B, self.T, self.cond, lw["wc"], self.cproj[i], bias=eng.zero_c)
+        return eng.L
 
     def bufs(self, n: int) -> List[torch.Tensor]:
         while len(self._bufs) < n:
@@ -74,6 +86,7 @@ class LynxEngine:
         self.bn_o = 256 if self.FM > 128 else (128 if self.FM > 64 else 64)
         self.FMr = (self.FM + self.bn_o - 1) // self.bn_o * self.bn_o
         self.workspaces: Dict[Tuple, LynxWorkspace] = {}
+        self.zero_c = torch.zeros(self.C, dtype=torch.float32, device=device)
         self.weights_key = None
         self._vec_cache: Dict[Tuple, torch.Tensor] = {}
 
@@ -143,8 +156,10 @@ class LynxEngine:
         return ws
 
     # ------------------------------------------------------------------ one evaluation
-    def eval(self, ws: LynxWorkspace, x_f32: torch.Tensor, vecs: torch.Tensor, out_f32: torch.Tensor) -> int:
-        """x / out: fp32 [B, T, F*M] time-major; vecs: fp32 [L, Bt, C] step vectors of this evaluation.  Returns #launches."""
+    def eval(self, ws: LynxWorkspace, x_f32: torch.Tensor, vecs: torch.Tensor, out_f32: torch.Tensor, hoisted: bool = False) -> int:
+        """x / out: fp32 [B, T, F*M] time-major; vecs: fp32 [L, Bt, C] step vectors of this evaluation.  hoisted: ws.cproj
+        holds W_c cond of every layer (strong_cond = False only).  Returns #launches."""
+        hoisted = hoisted and not self.strong
         w, B, T, Cc = self.w, ws.B, ws.T, self.C
         rows = B * T
         Bt = vecs.shape[1]
@@ -152,19 +167,23 @@ class LynxEngine:
         ops.gemm(ops.EPI_LINEAR, self.bn_c, B, T, ws.xb, w["w_in"], ws.h, bias=w["b_in"], act=ops.ACT_NONE if self.strong else ops.ACT_GELU)
         for i, lw in enumerate(w["layers"]):
             dvec = vecs[i]  # [Bt, C]
-            if self.strong:  # res_x = x + cond projection; the step vector is added on the way into the norm
+            if hoisted:      # res_x = x; LayerNorm(x + cproj + (bias + step vector))
+                ops.layernorm(ws.n, ws.h, lw["ln_g"], lw["ln_b"], 1e-5, dvec, T if Bt > 1 else rows, add=ws.cproj[i])
+                res = ws.h
+            elif self.strong:  # res_x = x + cond projection; the step vector is added on the way into the norm
                 ops.gemm(ops.EPI_RES, self.bn_c, B, T, ws.cond, lw["wc"], ws.u, vec=lw["bc"], vec_bstride=0, res=ws.h)
                 res, ln_vec = ws.u, dvec
             else:            # res_x = x; u = x + cond projection + (bias + step vector)
                 ops.gemm(ops.EPI_RES, self.bn_c, B, T, ws.cond, lw["wc"], ws.u, vec=dvec, vec_bstride=Cc if Bt > 1 else 0, res=ws.h)
                 res, ln_vec = ws.h, None
-            ops.layernorm(ws.n, ws.u, lw["ln_g"], lw["ln_b"], 1e-5, ln_vec, T if Bt > 1 else rows)
+            if not hoisted:
+                ops.layernorm(ws.n, ws.u, lw["ln_g"], lw["ln_b"], 1e-5, ln_vec, T if Bt > 1 else rows)
             ops.gemm(ops.EPI_SWIGLU, self.bn_g, B, T, ws.n, lw["w2"], ws.g, bias=lw["b2"])
             ops.dwconv(ws.dw, ws.g, lw["dw_w"], lw["dw_b"], B, T, self.k, self.act, lw["slope"])
             ops.gemm(ops.EPI_RES, self.bn_c, B, T, ws.dw, lw["w6"], ws.h, vec=lw["b6"], vec_bstride=0, res=res)
         ops.layernorm(ws.n, ws.h, w["norm_g"], w["norm_b"], 1e-5)
         ops.gemm(ops.EPI_OUTF32, self.bn_o, B, T, ws.n, w["w_out"], out_f32.view(rows, self.FM), bias=w["b_out"], n_real=self.FM)
-        return 5 * self.L + 4
+        return (4 if hoisted else 5) * self.L + 4
 
     # ------------------------------------------------------------------ sampler programs
     @torch.no_grad()
@@ -179,6 +198,8 @@ class LynxEngine:
         for k, e in enumerate(extra):
             bufs[2 + k].copy_(e)
         ws.set_cond(cond_bht.transpose(1, 2))
+        hoist = (not self.strong) and prog.nfe > 1
+        pre = ws.hoist_cond() if hoist else 0
         vkey = (tuple(prog.times), self.weights_key)
         vecs = self._vec_cache.get(vkey)
         if vecs is None:
@@ -187,24 +208,24 @@ class LynxEngine:
             vecs = self._vec_cache[vkey] = self.step_vectors(module, torch.tensor(prog.times, dtype=torch.float32), B, False)
         gkey = (id(prog), vkey)
         if not use_graph or len(prog.ops) > 1024:
-            ws.last_launches = self._run_ops(ws, prog, bufs, vecs)
+            ws.last_launches = pre + self._run_ops(ws, prog, bufs, vecs, hoist)
             return bufs[0].clone()
         graph = ws.graphs.get(gkey)
         if graph is None:
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
-                ws.graph_launches = self._run_ops(ws, prog, bufs, vecs)
+                ws.graph_launches = self._run_ops(ws, prog, bufs, vecs, hoist)
             ws.graphs[gkey] = graph
             ws._graph_refs = getattr(ws, "_graph_refs", []) + [prog, vecs]  # keep ids / device pointers valid
         graph.replay()
-        ws.last_launches = ws.graph_launches
+        ws.last_launches = pre + ws.graph_launches
         return bufs[0].clone()
 
-    def _run_ops(self, ws: LynxWorkspace, prog: Program, bufs: List[torch.Tensor], vecs: torch.Tensor) -> int:
+    def _run_ops(self, ws: LynxWorkspace, prog: Program, bufs: List[torch.Tensor], vecs: torch.Tensor, hoisted: bool = False) -> int:
         launches = 0
         for kind, dst, time, srcs, coefs in prog.ops:
             if kind == nat.DS_OP_EVAL:
-                launches += self.eval(ws, bufs[srcs[0]], vecs[time], bufs[dst])
+                launches += self.eval(ws, bufs[srcs[0]], vecs[time], bufs[dst], hoisted)
             else:
                 ops.lincomb(bufs[dst], [bufs[s] for s in srcs], coefs)
                 launches += 1

@@ -56,10 +56,11 @@ def gemm(epi: int, BN: int, B: int, T: int, a: torch.Tensor, w: torch.Tensor, ou
 
 
 def layernorm(y: torch.Tensor, x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float = 1e-5,
-              vec: Optional[torch.Tensor] = None, rows_per_vec: int = 0):
+              vec: Optional[torch.Tensor] = None, rows_per_vec: int = 0, add: Optional[torch.Tensor] = None):
+    """y = LayerNorm(x + add + vec[row // rows_per_vec]); add bf16 [rows, ch], vec fp32 [n, ch], both optional."""
     rows, ch = x.shape
     nat.check(nat.lib().ds_layernorm(y.data_ptr(), x.data_ptr(), gamma.data_ptr(), beta.data_ptr(), rows, ch, eps, _p(vec), rows_per_vec,
-                                     stream()))
+                                     _p(add), stream()))
 
 
 def dwconv(y: torch.Tensor, x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], B: int, T: int, kernel_size: int,

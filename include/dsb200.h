@@ -147,11 +147,12 @@ typedef struct {
 } ds_gemm_desc;
 int ds_debug_gemm(const ds_gemm_desc* d, void* stream);
 int ds_gemm(const ds_gemm_desc* d, void* stream);
-/* y = LayerNorm(x + vec[row / rows_per_vec]) over `channels` (multiple of 8, <= 2048) for `rows` frames; torch.nn.LayerNorm
- * semantics (lynxnet.py:52,123).  vec (fp32 [rows / rows_per_vec][channels], may be NULL) is the per-utterance
- * diffusion-step projection added before the norm (lynxnet.py:89). */
+/* y = LayerNorm(x + add + vec[row / rows_per_vec]) over `channels` (multiple of 8, <= 2048) for `rows` frames;
+ * torch.nn.LayerNorm semantics (lynxnet.py:52,123).  add (bf16 [rows][channels]) and vec (fp32 [rows / rows_per_vec][channels])
+ * may be NULL: the conditioner projection and the per-utterance diffusion-step projection added before the norm
+ * (lynxnet.py:82-89). */
 int ds_layernorm(void* y_bf16, const void* x_bf16, const float* gamma, const float* beta, int64_t rows, int32_t channels, float eps,
-                 const float* vec, int64_t rows_per_vec, void* stream);
+                 const float* vec, int64_t rows_per_vec, const void* add_bf16, void* stream);
 /* Depthwise Conv1d along time with zero padding (nn.Conv1d(ch, ch, k, padding=pad_left, groups=ch), lynxnet.py:59;
  * convnext.py dwconv), w fp32 [channels][k], fused bias and activation: 0 none, 1 ReLU, 2 PReLU(slope[channels]), 3 SiLU. */
 int ds_dwconv(void* y_bf16, const void* x_bf16, const float* w, const float* bias, const float* slope, int32_t B, int32_t T,

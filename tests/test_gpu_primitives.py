@@ -35,15 +35,21 @@ def test_layernorm(rows, Cc):
     x = _bf(rows, Cc) * 3 + 1
     g, b = torch.randn(Cc, device=dev), torch.randn(Cc, device=dev)
     y = torch.empty_like(x)
-    nat.check(nat.lib().ds_layernorm(y.data_ptr(), x.data_ptr(), g.data_ptr(), b.data_ptr(), rows, Cc, 1e-5, None, 0, _st()))
+    nat.check(nat.lib().ds_layernorm(y.data_ptr(), x.data_ptr(), g.data_ptr(), b.data_ptr(), rows, Cc, 1e-5, None, 0, None, _st()))
     ref = F.layer_norm(x.float(), (Cc,), g, b, 1e-5)
     assert rel_l2(y.float(), ref) < 4e-3
     # with a per-utterance additive vector (rows_per_vec frames share one)
     rpv = max(1, rows // 3)
     nvec = (rows + rpv - 1) // rpv
     vec = torch.randn(nvec, Cc, device=dev)
-    nat.check(nat.lib().ds_layernorm(y.data_ptr(), x.data_ptr(), g.data_ptr(), b.data_ptr(), rows, Cc, 1e-5, vec.data_ptr(), rpv, _st()))
+    nat.check(nat.lib().ds_layernorm(y.data_ptr(), x.data_ptr(), g.data_ptr(), b.data_ptr(), rows, Cc, 1e-5, vec.data_ptr(), rpv, None, _st()))
     ref = F.layer_norm(x.float() + vec.repeat_interleave(rpv, 0)[:rows], (Cc,), g, b, 1e-5)
+    assert rel_l2(y.float(), ref) < 4e-3
+    # ... and a second bf16 operand
+    add = _bf(rows, Cc)
+    nat.check(nat.lib().ds_layernorm(y.data_ptr(), x.data_ptr(), g.data_ptr(), b.data_ptr(), rows, Cc, 1e-5, vec.data_ptr(), rpv,
+                                     add.data_ptr(), _st()))
+    ref = F.layer_norm(x.float() + add.float() + vec.repeat_interleave(rpv, 0)[:rows], (Cc,), g, b, 1e-5)
     assert rel_l2(y.float(), ref) < 4e-3
 
 
