@@ -3,9 +3,10 @@
 Same constructor signature, parameter names / shapes / dtypes (``load_ckpt(strict=True)`` works both
 ways) and ``forward(spec, diffusion_step, cond)`` contract.  Under
 ``torch.no_grad()`` / inference the forward runs entirely in libdsb200.so (tcgen05 GEMMs, fused
-epilogues); with autograd enabled (training ``p_losses``, wavenet.py under ddpm.py:212-219) it is
-expressed with differentiable torch ops on the same device -- that branch exists for gradients only
-and is never taken by the samplers.
+epilogues); with autograd enabled (training ``p_losses``, wavenet.py under ddpm.py:212-219) the residual
+stack runs as ``training.WaveNetStack`` (native forward and data-gradient kernels, cuBLAS weight
+gradients) on CUDA, or as differentiable torch ops (``train_path = 'torch'``, and on CPU tensors) --
+that branch exists for gradients only and is never taken by the samplers.
 """
 import math
 import os
@@ -84,6 +85,9 @@ class WaveNet(nn.Module):
         self._engine = None  # native plan, created lazily on the module's CUDA device
         # 'bf16' (default; final mel rel-L2 <= 1e-2) or 'fp32' (3 x bf16 split products; per-evaluation rel-L2 <= 1e-4)
         self.precision = os.environ.get('DSB200_PRECISION', 'bf16')
+        # autograd (training) path on CUDA: 'native' = the residual stack's forward / data gradients on the tcgen05 kernels
+        # (training.py), 'torch' = differentiable torch ops throughout (the fp32 reference the parity tests compare with)
+        self.train_path = os.environ.get('DSB200_TRAIN', 'native')
 
     def set_precision(self, precision: str):
         """Select the arithmetic of the native path; drops the plan so that weights are repacked."""
@@ -134,7 +138,10 @@ class WaveNet(nn.Module):
         :param cond: [B, H, T] (may be a transposed view of [B, T, H])
         :return: [B, F, M, T]
         """
-        if torch.is_grad_enabled() and (spec.requires_grad or any(p.requires_grad for p in self.parameters())):
+        if torch.is_grad_enabled() and (spec.requires_grad or cond.requires_grad or any(p.requires_grad for p in self.parameters())):
+            if spec.is_cuda and self.train_path == 'native':
+                from ..training import wavenet_forward_train
+                return wavenet_forward_train(self, spec, diffusion_step, cond)
             return self._forward_autograd(spec, diffusion_step, cond)
         return self._forward_native(spec, diffusion_step, cond)
 

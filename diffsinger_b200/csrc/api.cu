@@ -962,6 +962,31 @@ extern "C" int ds_cast_bf16(void* dst_bf16, const float* src, int64_t rows, int3
   return 0;
 }
 
+extern "C" int ds_gate_fwd(void* y_bf16, int64_t ld_y, const void* z_bf16, int64_t ld_z, int64_t rows, int32_t channels, void* stream) {
+  if (!y_bf16 || !z_bf16 || rows <= 0 || channels <= 0 || channels % 8 || ld_y % 8 || ld_z % 8 || ld_y < channels || ld_z < 2 * channels)
+    return fail(DS_ERR_INVALID, "ds_gate_fwd: bad argument");
+  if (((uintptr_t)y_bf16 | (uintptr_t)z_bf16) & 15) return fail(DS_ERR_INVALID, "ds_gate_fwd: operands must be 16-byte aligned");
+  DS_TRY(ensure_device());
+  gate_fwd_kernel<<<ew_grid((long)rows * channels / 8, 256), 256, 0, (cudaStream_t)stream>>>(
+      (__nv_bfloat16*)y_bf16, (long)ld_y, (const __nv_bfloat16*)z_bf16, (long)ld_z, (long)rows, channels);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ds_gate_bwd(void* dz_bf16, int64_t ld_dz, const void* dy_bf16, int64_t ld_dy, const void* z_bf16, int64_t ld_z, int64_t rows,
+                           int32_t channels, void* stream) {
+  if (!dz_bf16 || !dy_bf16 || !z_bf16 || rows <= 0 || channels <= 0 || channels % 8 || ld_dz % 8 || ld_dy % 8 || ld_z % 8 ||
+      ld_dz < 2 * channels || ld_dy < channels || ld_z < 2 * channels)
+    return fail(DS_ERR_INVALID, "ds_gate_bwd: bad argument");
+  if (((uintptr_t)dz_bf16 | (uintptr_t)dy_bf16 | (uintptr_t)z_bf16) & 15) return fail(DS_ERR_INVALID, "ds_gate_bwd: operands must be 16-byte aligned");
+  DS_TRY(ensure_device());
+  gate_bwd_kernel<<<ew_grid((long)rows * channels / 8, 256), 256, 0, (cudaStream_t)stream>>>(
+      (__nv_bfloat16*)dz_bf16, (long)ld_dz, (const __nv_bfloat16*)dy_bf16, (long)ld_dy, (const __nv_bfloat16*)z_bf16, (long)ld_z, (long)rows,
+      channels);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
 // Debug / bench: launch ONLY the fused kernel of residual layer `layer` on the session's current activation buffers
 // (whatever the last evaluation left there), for per-kernel CUDA-event timing.
 extern "C" int ds_debug_layer(ds_session* s, int32_t layer, int32_t time_index, void* stream) {

@@ -394,3 +394,71 @@ __global__ void __launch_bounds__(128) dwconv_kernel(__nv_bfloat16* __restrict__
 }
 
 }  // namespace dsb
+
+// ------------------------------------------------------------------------------------ training: gated activation, fwd / bwd
+// The training path (ddpm.py:212-219 under autograd) keeps the pre-activations z = [gate | filter]
+// (wavenet.py:40, plain channel order, bf16) of every layer instead of fusing the gate into the GEMM epilogue, so the
+// backward pass needs no recomputation.  Both kernels are HBM-bound streaming passes: 8 channels (16 B) per thread per operand.
+namespace dsb {
+
+__device__ __forceinline__ void unpack_bf16x8(const uint4& q, float (&v)[8]) {
+  const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+  for (int h = 0; h < 4; ++h) {
+    v[2 * h] = __uint_as_float(w[h] << 16);
+    v[2 * h + 1] = __uint_as_float(w[h] & 0xffff0000u);
+  }
+}
+__device__ __forceinline__ uint4 pack_bf16x8(const float (&v)[8]) {
+  uint4 q;
+  uint32_t* w = reinterpret_cast<uint32_t*>(&q);
+#pragma unroll
+  for (int h = 0; h < 4; ++h) {
+    const __nv_bfloat162 b = __floats2bfloat162_rn(v[2 * h], v[2 * h + 1]);
+    w[h] = *reinterpret_cast<const uint32_t*>(&b);
+  }
+  return q;
+}
+
+// y[r][c] = sigmoid(z[r][c]) * tanh(z[r][C + c])                                        wavenet.py:40-42
+__global__ void __launch_bounds__(256) gate_fwd_kernel(__nv_bfloat16* __restrict__ y, long ld_y, const __nv_bfloat16* __restrict__ z,
+                                                       long ld_z, long rows, int C) {
+  const int cg = C / 8;
+  const long n = rows * cg;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+    const long r = i / cg;
+    const int c = (int)(i - r * cg) * 8;
+    float g[8], f[8], o[8];
+    unpack_bf16x8(__ldg(reinterpret_cast<const uint4*>(z + r * ld_z + c)), g);
+    unpack_bf16x8(__ldg(reinterpret_cast<const uint4*>(z + r * ld_z + C + c)), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = tanhf(f[j]) / (1.0f + __expf(-g[j]));
+    *reinterpret_cast<uint4*>(y + r * ld_y + c) = pack_bf16x8(o);
+  }
+}
+
+// dz_gate = dy * tanh(f) * s (1 - s),  dz_filter = dy * s * (1 - tanh(f)^2),  s = sigmoid(g)
+__global__ void __launch_bounds__(256) gate_bwd_kernel(__nv_bfloat16* __restrict__ dz, long ld_dz, const __nv_bfloat16* __restrict__ dy,
+                                                       long ld_dy, const __nv_bfloat16* __restrict__ z, long ld_z, long rows, int C) {
+  const int cg = C / 8;
+  const long n = rows * cg;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+    const long r = i / cg;
+    const int c = (int)(i - r * cg) * 8;
+    float g[8], f[8], d[8], og[8], of[8];
+    unpack_bf16x8(__ldg(reinterpret_cast<const uint4*>(z + r * ld_z + c)), g);
+    unpack_bf16x8(__ldg(reinterpret_cast<const uint4*>(z + r * ld_z + C + c)), f);
+    unpack_bf16x8(__ldg(reinterpret_cast<const uint4*>(dy + r * ld_dy + c)), d);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float s = 1.0f / (1.0f + __expf(-g[j]));
+      const float th = tanhf(f[j]);
+      og[j] = d[j] * th * s * (1.0f - s);
+      of[j] = d[j] * s * (1.0f - th * th);
+    }
+    *reinterpret_cast<uint4*>(dz + r * ld_dz + c) = pack_bf16x8(og);
+    *reinterpret_cast<uint4*>(dz + r * ld_dz + C + c) = pack_bf16x8(of);
+  }
+}
+
+}  // namespace dsb

@@ -35,24 +35,42 @@ def _p(t: Optional[torch.Tensor]):
 
 
 def gemm(epi: int, BN: int, B: int, T: int, a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, k_per_tap: Optional[int] = None,
-         n_taps: int = 1, bias: Optional[torch.Tensor] = None, vec: Optional[torch.Tensor] = None, vec_bstride: int = 0,
-         res: Optional[torch.Tensor] = None, act: int = ACT_NONE, n_real: int = 0, scale: float = 1.0):
-    """out[b, t, n] = epilogue(sum_tap sum_k a[b, t + tap - n_taps // 2, k] * w[n, tap * K + k]); frames outside [0, T) read as
-    zeros (the conv's zero padding).  a: [B*T, K_in] bf16, w: [rows, n_taps * K] bf16, out: bf16 (fp32 for EPI_OUTF32)."""
+         n_taps: int = 1, dil: int = 1, a_c0: int = 0, a1: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None,
+         vec: Optional[torch.Tensor] = None, vec_bstride: int = 0, res: Optional[torch.Tensor] = None, act: int = ACT_NONE,
+         n_real: int = 0, scale: float = 1.0, out_c0: int = 0):
+    """out[b, t, out_c0 + n] = epilogue(sum_tap sum_k a[b, t + (tap - n_taps // 2) * dil, a_c0 + k] * w[n, tap * K + k]
+    + sum_h a1[b, t, h] * w[n, n_taps * K + h]); frames outside [0, T) read as zeros (the conv's zero padding).
+    a: [B*T, ld_a] bf16 (K = k_per_tap columns from a_c0), a1: optional second operand [B*T, H] (one tap),
+    w: [rows, n_taps * K (+ H)] bf16, out: [B*T, ld_out] bf16 (fp32 for EPI_OUTF32), res: [B*T, ld_res] bf16 (EPI_RES)."""
     a_ch = a.shape[1]
     k = a_ch if k_per_tap is None else k_per_tap
+    h = a1.shape[1] if a1 is not None else 0
     rows, w_k = w.shape
-    assert w_k == n_taps * k and k % 64 == 0 and rows % BN == 0, (w.shape, n_taps, k, BN)
+    assert w_k == n_taps * k + h and k % 64 == 0 and h % 64 == 0 and rows % BN == 0 and a_c0 + k <= a_ch, (w.shape, n_taps, k, h, BN)
     d = nat.GemmDesc()
     d.epi, d.BN, d.B, d.T = epi, BN, B, T
-    d.a0, d.a0_channels, d.a0_c0, d.kb_a0, d.n_taps, d.dil = a.data_ptr(), a_ch, 0, k // 64, n_taps, 1
-    d.a1, d.a1_channels, d.kb_a1 = None, 0, 0
+    d.a0, d.a0_channels, d.a0_c0, d.kb_a0, d.n_taps, d.dil = a.data_ptr(), a_ch, a_c0, k // 64, n_taps, dil
+    d.a1, d.a1_channels, d.kb_a1 = _p(a1), h, h // 64
     d.w, d.w_rows, d.w_k, d.b_row0, d.n_tiles = w.data_ptr(), rows, w_k, 0, rows // BN
     d.bias, d.vec_sub, d.vec_add, d.vec_bstride = _p(bias), None, _p(vec), vec_bstride
     d.res_in, d.ld_res = _p(res), (res.shape[1] if res is not None else 0)
-    d.out, d.ld_out, d.out_c0, d.n_real = out.data_ptr(), out.shape[-1], 0, n_real
+    d.out, d.ld_out, d.out_c0, d.n_real = out.data_ptr(), out.shape[-1], out_c0, n_real
     d.relu, d.scale = act, scale
     nat.check(nat.lib().ds_gemm(C.byref(d), stream()))
+
+
+def gate_fwd(y: torch.Tensor, y_c0: int, z: torch.Tensor, z_c0: int, channels: int):
+    """y[:, y_c0 + c] = sigmoid(z[:, z_c0 + c]) * tanh(z[:, z_c0 + channels + c]); bf16 [rows, ld] buffers."""
+    es = 2
+    nat.check(nat.lib().ds_gate_fwd(y.data_ptr() + y_c0 * es, y.shape[1], z.data_ptr() + z_c0 * es, z.shape[1], y.shape[0], channels,
+                                    stream()))
+
+
+def gate_bwd(dz: torch.Tensor, dz_c0: int, dy: torch.Tensor, z: torch.Tensor, z_c0: int, channels: int):
+    """dz[:, dz_c0 : dz_c0 + 2 channels] = d(sigmoid(g) tanh(f)) / d[g | f] * dy; bf16 [rows, ld] buffers."""
+    es = 2
+    nat.check(nat.lib().ds_gate_bwd(dz.data_ptr() + dz_c0 * es, dz.shape[1], dy.data_ptr(), dy.shape[1], z.data_ptr() + z_c0 * es,
+                                    z.shape[1], dz.shape[0], channels, stream()))
 
 
 def layernorm(y: torch.Tensor, x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float = 1e-5,

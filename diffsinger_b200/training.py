@@ -1,0 +1,172 @@
+"""Training forward / backward of the WaveNet residual stack on the native kernels.
+
+Reference: ``GaussianDiffusion.p_losses`` (modules/core/ddpm.py:212-219) and ``RectifiedFlow.p_losses``
+(modules/core/reflow.py:36-41) call the backbone once under autograd with a per-sample step ``t[B]``; 99 % of that
+evaluation's FLOPs are the L residual blocks (modules/backbones/wavenet.py:33-48).  ``WaveNetStack`` is a
+``torch.autograd.Function`` over exactly those blocks, time-major ``[B*T, channels]`` bf16 like the sampling path:
+
+forward, per layer l (dilation dl):
+    z_l  = [W1_l taps | Wc_l] x [xt_l(t-dl), xt_l(t), xt_l(t+dl), cond] + b1 + bc     ds_gemm EPI_LINEAR, kept for backward
+    y_l  = sigmoid(z_gate) * tanh(z_filter)                                             ds_gate_fwd
+    xt_{l+1} = (xt_l + W2res_l y_l) / sqrt(2) + rvec_l[b]                               ds_gemm EPI_RES
+  with xt_l = x_l + d_l[b] (the step vector is added before the conv's zero padding, wavenet.py:36) and
+  rvec_l = (b2res_l - d_l) / sqrt(2) + d_{l+1};  skip_sum = [y_0 | ... | y_{L-1}] x Wskip^T + sum_l b2skip_l (one GEMM, K = L*C).
+
+backward, per layer in reverse, with h_l = dLoss/dx_l / sqrt(2) kept in the left half of G2 = [h_{l+1} | dskip]:
+    dy   = W2_l^T G2                                                                     ds_gemm EPI_LINEAR
+    dz_l = gate'(z_l) * dy                                                               ds_gate_bwd
+    h_l  = (sum_tap W1_tap^T dz_l(t - (tap-1) dl) + h_{l+1}) / sqrt(2)                   ds_gemm EPI_RES (taps mirrored)
+  then dcond = [Wc_0^T | ... ] x [dz_0 | ... | dz_{L-1}] (one GEMM, K = 2LC).
+
+Every data-gradient GEMM and the gate passes are this repo's tcgen05 / streaming kernels.  The weight gradients are plain
+``dz^T x`` products with K = B*T (activations as the K-major operand of both sides), which is a library GEMM: they go to
+cuBLAS through ``torch.matmul``, as do the O(C) bias reductions.  Head (input projection), step-embedding MLP and tail
+(skip / output projections, < 1 % of the FLOPs) stay ordinary torch modules around the Function.
+"""
+from __future__ import annotations
+
+import math
+from typing import List
+
+import torch
+
+from . import _native as nat
+from . import ops
+
+_bn = ops.tile_n
+_RS2 = 0.7071067811865476
+
+
+def _bf(t: torch.Tensor) -> torch.Tensor:
+    return t.to(torch.bfloat16).contiguous()
+
+
+class WaveNetStack(torch.autograd.Function):
+    """skip_sum[B, T, C] = sum_l skip_l(x0, cond, dvecs; weights) -- the L residual blocks of wavenet.py:91-96 before / sqrt(L).
+
+    Arguments (all on one CUDA device):
+        x0    [B, T, C]   fp32, relu(input_projection(spec)) time-major
+        cond  [B, T, H]   fp32
+        dvecs [L, B, C]   fp32, diffusion_projection_l(mlp(emb(t)))                      wavenet.py:35-36
+        w1 [L, 2C, C, 3], b1 [L, 2C], wc [L, 2C, H], bc [L, 2C], w2 [L, 2C, C], b2 [L, 2C]  stacked layer parameters
+        dilations: list of L ints
+    """
+
+    @staticmethod
+    def forward(ctx, x0, cond, dvecs, w1, b1, wc, bc, w2, b2, dilations: List[int]):
+        nat.require_device()
+        B, T, Cc = x0.shape
+        H, L = cond.shape[2], w1.shape[0]
+        rows, dev, bf = B * T, x0.device, torch.bfloat16
+        if Cc % 64 or H % 64:
+            raise nat.NativeError(f"num_channels={Cc} and hidden_size={H} must be multiples of 64")
+        # per-step weight layouts (weights change every optimiser step; 8C^2 + 2HC elements per layer)
+        wcat = _bf(torch.cat([w1.permute(0, 1, 3, 2).reshape(L, 2 * Cc, 3 * Cc), wc], dim=2))   # [L][2C][3C + H]
+        w2res = _bf(w2[:, :Cc])                                                                    # [L][C][C]
+        wskip = _bf(w2[:, Cc:].permute(1, 0, 2).reshape(Cc, L * Cc))                               # [C][L*C]
+        bias1 = (b1 + bc).float().contiguous()
+        bskip = b2[:, Cc:].sum(0).float().contiguous()
+        dv = dvecs.float()
+        rvec = ((b2[:, None, :Cc] - dv) * _RS2)[:-1] + dv[1:] if L > 1 else None                  # [L-1][B][C]
+        if rvec is not None:
+            rvec = rvec.contiguous()
+        cond_bf = torch.empty(rows, H, dtype=bf, device=dev)
+        ops.cast_bf16(cond_bf, cond.detach().float().contiguous().view(rows, H))
+        XT = torch.empty(L, rows, Cc, dtype=bf, device=dev)
+        Z = torch.empty(rows, L * 2 * Cc, dtype=bf, device=dev)
+        Y = torch.empty(rows, L * Cc, dtype=bf, device=dev)
+        XT[0] = (x0.detach() + dv[0][:, None, :]).reshape(rows, Cc)
+        for l in range(L):
+            ops.gemm(ops.EPI_LINEAR, _bn(2 * Cc), B, T, XT[l], wcat[l], Z, k_per_tap=Cc, n_taps=3, dil=dilations[l], a1=cond_bf,
+                     bias=bias1[l], out_c0=l * 2 * Cc)
+            ops.gate_fwd(Y, l * Cc, Z, l * 2 * Cc, Cc)
+            if l + 1 < L:  # the last layer's residual half is never used (wavenet.py:92-94)
+                ops.gemm(ops.EPI_RES, _bn(Cc), B, T, Y, w2res[l], XT[l + 1], k_per_tap=Cc, a_c0=l * Cc, vec=rvec[l], vec_bstride=Cc,
+                         res=XT[l], scale=_RS2)
+        S = torch.empty(rows, Cc, dtype=bf, device=dev)
+        ops.gemm(ops.EPI_LINEAR, _bn(Cc), B, T, Y, wskip, S, bias=bskip)
+        ctx.save_for_backward(XT, Z, Y, cond_bf, w1, wc, w2)
+        ctx.dilations, ctx.shape = list(dilations), (B, T, Cc, H, L)
+        return S.float().view(B, T, Cc)
+
+    @staticmethod
+    def backward(ctx, dS):
+        XT, Z, Y, cond_bf, w1, wc, w2 = ctx.saved_tensors
+        B, T, Cc, H, L = ctx.shape
+        dil = ctx.dilations
+        rows, dev, bf = B * T, dS.device, torch.bfloat16
+        # data-gradient weight layouts
+        w2t = _bf(w2.transpose(1, 2))                                                             # [L][C][2C]
+        w1t = _bf(w1.flip(-1).permute(0, 2, 3, 1).reshape(L, Cc, 6 * Cc))                         # [L][C][3 taps mirrored x 2C]
+        wct = _bf(wc.permute(2, 0, 1).reshape(H, L * 2 * Cc))                                     # [H][L*2C]
+        zero_c = torch.zeros(max(2 * Cc, H), dtype=torch.float32, device=dev)
+        G2 = torch.zeros(rows, 2 * Cc, dtype=bf, device=dev)                                      # [h_{l+1} | dskip]
+        G2[:, Cc:] = dS.reshape(rows, Cc)
+        DY = torch.empty(rows, Cc, dtype=bf, device=dev)
+        DZ = torch.empty(rows, L * 2 * Cc, dtype=bf, device=dev)
+        hsum = torch.zeros(L + 1, B, Cc, dtype=torch.float32, device=dev)                         # sum_t h_l per utterance
+        dw2 = torch.empty(L, 2 * Cc, Cc, dtype=torch.float32, device=dev)
+        G2v, Yv = G2.view(B, T, 2 * Cc), Y.view(rows, L, Cc)
+        for l in range(L - 1, -1, -1):
+            if l + 1 < L:  # residual half of dW2_l = h_{l+1}^T y_l * sqrt(2)^0: d(x_{l+1})/d(res) = 1/sqrt(2), already in h
+                dw2[l, :Cc] = torch.matmul(G2[:, :Cc].t(), Yv[:, l]).float()
+                ops.gemm(ops.EPI_LINEAR, _bn(Cc), B, T, G2, w2t[l], DY, bias=zero_c)
+            else:
+                dw2[l, :Cc] = 0
+                ops.gemm(ops.EPI_LINEAR, _bn(Cc), B, T, G2, w2t[l][:, Cc:].contiguous(), DY, k_per_tap=Cc, a_c0=Cc, bias=zero_c)
+            ops.gate_bwd(DZ, l * 2 * Cc, DY, Z, l * 2 * Cc, Cc)
+            ops.gemm(ops.EPI_RES, _bn(Cc), B, T, DZ, w1t[l], G2, k_per_tap=2 * Cc, n_taps=3, dil=dil[l], a_c0=l * 2 * Cc,
+                     vec=zero_c, vec_bstride=0, res=G2, scale=_RS2)
+            hsum[l] = torch.sum(G2v[:, :, :Cc], 1, dtype=torch.float32)
+        dcond = torch.empty(rows, H, dtype=bf, device=dev)
+        ops.gemm(ops.EPI_LINEAR, _bn(H), B, T, DZ, wct, dcond, bias=zero_c)
+        # ---- weight / bias / step-vector gradients: K = B*T library GEMMs and reductions
+        DZv = DZ.view(B, T, L, 2 * Cc)
+        XTv = XT.view(L, B, T, Cc)
+        dw1 = torch.empty(L, 2 * Cc, Cc, 3, dtype=torch.float32, device=dev)
+        for l in range(L):
+            d = dil[l]
+            dzl = DZv[:, :, l]                                                                    # [B, T, 2C]
+            for tap in range(3):
+                s = (tap - 1) * d                                                                 # z[t] += W_tap xt[t + s]
+                lo, hi = max(0, -s), min(T, T - s)
+                if hi <= lo:
+                    dw1[l, :, :, tap] = 0
+                    continue
+                g = torch.matmul(dzl[:, lo:hi].transpose(1, 2), XTv[l, :, lo + s:hi + s])         # [B, 2C, C]
+                dw1[l, :, :, tap] = torch.sum(g, 0, dtype=torch.float32)
+        dwc = torch.matmul(DZ.t(), cond_bf).float().view(L, 2 * Cc, H)
+        dw2[:, Cc:] = torch.matmul(G2[:, Cc:].t(), Y).float().view(Cc, L, Cc).permute(1, 0, 2)
+        db1 = torch.sum(DZ, 0, dtype=torch.float32).view(L, 2 * Cc)
+        db2 = torch.empty(L, 2 * Cc, dtype=torch.float32, device=dev)
+        db2[:, :Cc] = hsum[1:].sum(1)
+        db2[:, Cc:] = torch.sum(G2[:, Cc:], 0, dtype=torch.float32)
+        # d_l only enters through the conv input: sum_t (sqrt(2) h_l - h_{l+1})
+        ddv = math.sqrt(2.0) * hsum[:L] - hsum[1:]
+        dx0 = (G2v[:, :, :Cc].float() * math.sqrt(2.0))
+        return dx0, dcond.float().view(B, T, H), ddv, dw1, db1, dwc, db1.clone(), dw2, db2, None
+
+
+def wavenet_forward_train(module, spec, diffusion_step, cond):
+    """``WaveNet.forward`` under autograd on a CUDA device (wavenet.py:75-107): torch head / tail around ``WaveNetStack``."""
+    import torch.nn.functional as F
+    x = spec.squeeze(1) if module.n_feats == 1 else spec.flatten(start_dim=1, end_dim=2)
+    B = x.shape[0]
+    x0 = F.relu(module.input_projection(x)).transpose(1, 2)                                       # [B, T, C]
+    d = module.mlp(module.diffusion_embedding(diffusion_step))                                    # [B or 1, C]
+    if d.shape[0] != B:
+        d = d.expand(B, -1)
+    layers = module.residual_layers
+    dvecs = torch.stack([l.diffusion_projection(d) for l in layers])                              # [L, B, C]
+    st = lambda f: torch.stack([f(l) for l in layers])
+    skip = WaveNetStack.apply(
+        x0, cond.transpose(1, 2), dvecs,
+        st(lambda l: l.dilated_conv.weight), st(lambda l: l.dilated_conv.bias),
+        st(lambda l: l.conditioner_projection.weight[:, :, 0]), st(lambda l: l.conditioner_projection.bias),
+        st(lambda l: l.output_projection.weight[:, :, 0]), st(lambda l: l.output_projection.bias),
+        [l.dilation for l in layers])
+    x = skip.transpose(1, 2) / math.sqrt(len(layers))
+    x = module.output_projection(F.relu(module.skip_projection(x)))
+    if module.n_feats == 1:
+        return x[:, None, :, :]
+    return x.reshape(-1, module.n_feats, module.in_dims, x.shape[2])

@@ -159,6 +159,14 @@ int ds_dwconv(void* y_bf16, const void* x_bf16, const float* w, const float* bia
               int32_t channels, int32_t kernel_size, int32_t pad_left, int32_t act, void* stream);
 /* fp32 [rows][cols] -> bf16 [rows][ld] (columns >= cols zero filled); cols, ld multiples of 4. */
 int ds_cast_bf16(void* dst_bf16, const float* src, int64_t rows, int32_t cols, int32_t ld, void* stream);
+/* Training path (ddpm.py:212-219 / reflow.py:36-41 under autograd).  z = [gate | filter] pre-activations of
+ * one residual layer (wavenet.py:40), bf16 [rows][ld_z], plain channel order:
+ *   ds_gate_fwd:  y[r][c] = sigmoid(z[r][c]) * tanh(z[r][channels + c])                                       (wavenet.py:41-42)
+ *   ds_gate_bwd:  dz[r][c] = dy * tanh(f) * s (1 - s),  dz[r][channels + c] = dy * s * (1 - tanh(f)^2),  s = sigmoid(g)
+ * channels and every ld multiple of 8, pointers 16-byte aligned (column slices of wider buffers are fine). */
+int ds_gate_fwd(void* y_bf16, int64_t ld_y, const void* z_bf16, int64_t ld_z, int64_t rows, int32_t channels, void* stream);
+int ds_gate_bwd(void* dz_bf16, int64_t ld_dz, const void* dy_bf16, int64_t ld_dy, const void* z_bf16, int64_t ld_z, int64_t rows,
+                int32_t channels, void* stream);
 /* Debug: device buffer of n_entries x 4 uint64 into which CTA 0 of every fused-layer launch records
  * {role*16+kind, tile*16+idx, t0_ns, t1_ns} (first half: MMA issuer, second half: epilogue). NULL disables. */
 int ds_debug_set_trace(void* dev_buf, int32_t n_entries);

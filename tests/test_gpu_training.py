@@ -1,0 +1,148 @@
+"""Training path: the native forward / backward of the WaveNet residual stack against fp32 torch
+autograd of the same module (``train_path='torch'``: plain differentiable torch ops, wavenet.py:33-48,75-107)."""
+import copy
+
+import pytest
+import torch
+
+from conftest import rel_l2
+
+pytestmark = pytest.mark.gpu
+
+# bf16 activations / gradients between kernels, fp32 accumulation inside them.  The residual stack itself is smooth
+# (sigmoid * tanh); through the whole module the two ReLUs (wavenet.py:88,98) sit on values that carry bf16 rounding, so a
+# fraction ~3e-3 of their masks flips against the fp32 run and every gradient behind them inherits sqrt(3e-3) ~ 5e-2 of
+# relative noise -- the same property bf16 autocast has in the reference's trainer.
+OUT_TOL, STACK_GRAD_TOL, MODULE_GRAD_TOL = 1e-2, 1e-2, 9e-2
+
+
+def _model(C, L, M, F, cycle, hidden=256):
+    import diffsinger_b200 as ds
+    from diffsinger_b200.synthetic import random_state_dict
+    ds.hparams.update(hidden_size=hidden)
+    m = ds.WaveNet(M, F, num_layers=L, num_channels=C, dilation_cycle_length=cycle)
+    m.load_state_dict(random_state_dict(M, F, L, C, hidden, seed=3), strict=True)
+    return m.cuda()
+
+
+def _check(grads, tol):
+    errs = {}
+    for name, g_ref in grads[1].items():
+        g = grads[0][name]
+        assert g is not None and g.shape == g_ref.shape, name
+        errs[name] = rel_l2(g, g_ref)
+    worst = max(errs, key=errs.get)
+    print(f"worst gradient rel-L2 {errs[worst]:.3e} ({worst})")
+    bad = {n: f"{e:.3e}" for n, e in errs.items() if not e < tol}
+    assert not bad, bad
+
+
+SHAPES = [
+    (256, 4, 128, 1, 4, 2, 300),
+    (192, 3, 24, 2, 2, 3, 131),   # ragged tile, multi-variance shape, dilations 1, 2, 1
+    (512, 2, 128, 1, 4, 1, 257),
+    (256, 5, 64, 1, 5, 2, 140),   # pitch predictor shape: dilation 16 next to short utterances
+]
+
+
+@pytest.mark.parametrize("C,L,M,F,cycle,B,T", SHAPES)
+def test_stack_matches_fp32_autograd(C, L, M, F, cycle, B, T):
+    """WaveNetStack (native forward, data gradients, cuBLAS weight gradients) against the same L residual blocks as fp32
+    torch ops (wavenet.py:33-48, 91-96), TF32 off."""
+    import math
+    from diffsinger_b200.training import WaveNetStack
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(11)
+    m = _model(C, L, M, F, cycle)
+    layers = m.residual_layers
+    x0 = torch.randn(B, T, C, device='cuda').relu()
+    cond = torch.randn(B, T, 256, device='cuda')
+    emb = torch.randn(B, C, device='cuda')
+    w = torch.randn(B, T, C, device='cuda')
+    outs, grads = [], []
+    for native in (True, False):
+        m.zero_grad()
+        xs, cs, es = (v.clone().requires_grad_(True) for v in (x0, cond, emb))
+        if native:
+            st = lambda f: torch.stack([f(l) for l in layers])
+            skip = WaveNetStack.apply(
+                xs, cs, torch.stack([l.diffusion_projection(es) for l in layers]),
+                st(lambda l: l.dilated_conv.weight), st(lambda l: l.dilated_conv.bias),
+                st(lambda l: l.conditioner_projection.weight[:, :, 0]), st(lambda l: l.conditioner_projection.bias),
+                st(lambda l: l.output_projection.weight[:, :, 0]), st(lambda l: l.output_projection.bias),
+                [l.dilation for l in layers])
+        else:
+            x, c, skip = xs.transpose(1, 2), cs.transpose(1, 2), 0
+            for l in layers:
+                x, sk = l(x, c, es)
+                skip = skip + sk
+            skip = skip.transpose(1, 2)
+        (skip * w).sum().backward()
+        outs.append(skip.detach())
+        g = {"x0": xs.grad, "cond": cs.grad, "emb": es.grad}
+        g.update({n: p.grad.clone() for n, p in layers.named_parameters() if p.grad is not None})
+        grads.append(g)
+    # the last layer's residual half is unused (wavenet.py:92-94): its parameters get a zero gradient on the native path
+    # and none from autograd
+    for n in list(grads[0]):
+        if n not in grads[1]:
+            assert float(grads[0][n].abs().max()) == 0.0, n
+    err = rel_l2(outs[0], outs[1])
+    print(f"stack forward rel-L2 {err:.3e}")
+    assert err < OUT_TOL
+    _check(grads, STACK_GRAD_TOL)
+
+
+@pytest.mark.parametrize("C,L,M,F,cycle,B,T", SHAPES[:3])
+def test_module_forward_backward_match_torch_autograd(C, L, M, F, cycle, B, T):
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(11)
+    native = _model(C, L, M, F, cycle)
+    ref = copy.deepcopy(native)
+    ref.train_path = 'torch'
+    spec = torch.randn(B, F, M, T, device='cuda')
+    cond = torch.randn(B, 256, T, device='cuda')
+    t = torch.randint(0, 1000, (B,), device='cuda')
+    w = torch.randn(B, F, M, T, device='cuda')
+    outs, grads = [], []
+    for m in (native, ref):
+        s, c = spec.clone().requires_grad_(True), cond.clone().requires_grad_(True)
+        y = m(s, t, c)
+        (y * w).sum().backward()
+        outs.append(y.detach())
+        g = {"spec": s.grad, "cond": c.grad}
+        g.update({n: p.grad for n, p in m.named_parameters()})
+        grads.append(g)
+    assert outs[0].shape == outs[1].shape == (B, F, M, T)
+    err = rel_l2(outs[0], outs[1])
+    print(f"train forward rel-L2 {err:.3e}")
+    assert err < OUT_TOL
+    _check(grads, MODULE_GRAD_TOL)
+
+
+def test_p_losses_step_trains():
+    """One optimiser step of GaussianDiffusion.p_losses (ddpm.py:212-219) through the native stack lowers the loss."""
+    import diffsinger_b200 as ds
+    from diffsinger_b200.synthetic import random_state_dict
+    ds.hparams.update(hidden_size=256, schedule_type='linear', use_shallow_diffusion=False, diff_accelerator='ddim',
+                      diff_speedup=50, K_step=1000, timesteps=1000)
+    m = ds.GaussianDiffusion(128, 1, 1000, 1000, 'wavenet', dict(num_layers=4, num_channels=256, dilation_cycle_length=4),
+                             spec_min=[-12.], spec_max=[0.]).cuda()
+    m.denoise_fn.load_state_dict(random_state_dict(128, 1, 4, 256, 256, seed=5), strict=True)
+    opt = torch.optim.SGD(m.denoise_fn.parameters(), lr=1e-3)
+    torch.manual_seed(0)
+    cond = torch.randn(2, 200, 256, device='cuda')
+    gt = torch.rand(2, 200, 128, device='cuda') * -12.0
+    losses = []
+    for _ in range(3):
+        torch.manual_seed(1)  # same t / noise every iteration
+        x_recon, noise = m(cond, gt_spec=gt, infer=False)
+        loss = torch.nn.functional.mse_loss(x_recon, noise)
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+        losses.append(loss.item())
+    print("p_losses:", losses)
+    assert losses[-1] < losses[0]
