@@ -123,7 +123,7 @@ class WaveNetStack(torch.autograd.Function):
         # ---- weight / bias / step-vector gradients: K = B*T library GEMMs and reductions
         DZv = DZ.view(B, T, L, 2 * Cc)
         XTv = XT.view(L, B, T, Cc)
-        dw1 = torch.empty(L, 2 * Cc, Cc, 3, dtype=torch.float32, device=dev)
+        dw1 = torch.empty(L, 3, 2 * Cc, Cc, dtype=torch.float32, device=dev)           # tap-major: contiguous per-tap writes
         for l in range(L):
             d = dil[l]
             dzl = DZv[:, :, l]                                                                    # [B, T, 2C]
@@ -131,10 +131,10 @@ class WaveNetStack(torch.autograd.Function):
                 s = (tap - 1) * d                                                                 # z[t] += W_tap xt[t + s]
                 lo, hi = max(0, -s), min(T, T - s)
                 if hi <= lo:
-                    dw1[l, :, :, tap] = 0
+                    dw1[l, tap] = 0
                     continue
                 g = torch.matmul(dzl[:, lo:hi].transpose(1, 2), XTv[l, :, lo + s:hi + s])         # [B, 2C, C]
-                dw1[l, :, :, tap] = torch.sum(g, 0, dtype=torch.float32)
+                torch.sum(g, 0, dtype=torch.float32, out=dw1[l, tap])
         dwc = torch.matmul(DZ.t(), cond_bf).float().view(L, 2 * Cc, H)
         dw2[:, Cc:] = torch.matmul(G2[:, Cc:].t(), Y).float().view(Cc, L, Cc).permute(1, 0, 2)
         db1 = torch.sum(DZ, 0, dtype=torch.float32).view(L, 2 * Cc)
@@ -144,7 +144,7 @@ class WaveNetStack(torch.autograd.Function):
         # d_l only enters through the conv input: sum_t (sqrt(2) h_l - h_{l+1})
         ddv = math.sqrt(2.0) * hsum[:L] - hsum[1:]
         dx0 = (G2v[:, :, :Cc].float() * math.sqrt(2.0))
-        return dx0, dcond.float().view(B, T, H), ddv, dw1, db1, dwc, db1.clone(), dw2, db2, None
+        return dx0, dcond.float().view(B, T, H), ddv, dw1.permute(0, 2, 3, 1), db1, dwc, db1.clone(), dw2, db2, None
 
 
 def wavenet_forward_train(module, spec, diffusion_step, cond):

@@ -5,6 +5,7 @@ trainer runs, ddpm.py:212-219 through Lightning's precision plugin).  Prints one
     PYTHONPATH=. python tools/train_bench.py [B T [C L]]
 """
 import json
+import os
 import sys
 import time
 
@@ -38,13 +39,16 @@ def main():
             y = m(spec, t, cond)
         (y.float() * w).sum().backward()
 
+    arms = os.environ.get("ARMS", "native,torch_bf16_autocast,torch_fp32").split(",")
+    n_warm, n = int(os.environ.get("WARM", 2)), int(os.environ.get("STEPS", 5))
     for name, path, autocast in (("native", "native", False), ("torch_bf16_autocast", "torch", True), ("torch_fp32", "torch", False)):
+        if name not in arms:
+            continue
         try:
-            for _ in range(2):
+            for _ in range(n_warm):
                 step(path, autocast)
             torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            n = 5
             e0.record()
             for _ in range(n):
                 step(path, autocast)
