@@ -17,6 +17,7 @@ only torch arithmetic (O(C^2) per step value, computed once per sampler configur
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Dict, List, Sequence, Tuple
 
 import torch
@@ -155,6 +156,25 @@ class LynxEngine:
             self.workspaces[key] = self.workspaces.pop(key)
         return ws
 
+    def max_chunk_batch(self, B: int, T: int, n_bufs: int) -> int:
+        """Largest per-run batch whose workspace (activations, hoisted conditioner projections, sampler buffers) fits the
+        device; DSB200_MAX_FRAMES (frames per chunk) overrides the memory probe (core/runtime.py:max_chunk_batch)."""
+        cap = os.environ.get("DSB200_MAX_FRAMES")
+        if cap:
+            return max(1, min(B, int(cap) // T))
+        if (B, T, _st()) in self.workspaces:
+            return B
+        per_utt = T * (2 * (self.FMp + self.H + 3 * self.C + 2 * self.I + self.L * self.C) + 4 * n_bufs * self.FM)
+        free, _total = torch.cuda.mem_get_info(self.device)
+        free += torch.cuda.memory_reserved(self.device) - torch.cuda.memory_allocated(self.device)
+        fit = int(0.8 * free) // per_utt
+        if fit < 1:
+            raise RuntimeError(f"not enough device memory for one utterance of {T} frames ({per_utt} bytes needed)")
+        if fit >= B:
+            return B
+        n_chunks = -(-B // fit)
+        return -(-B // n_chunks)
+
     # ------------------------------------------------------------------ one evaluation
     def eval(self, ws: LynxWorkspace, x_f32: torch.Tensor, vecs: torch.Tensor, out_f32: torch.Tensor, hoisted: bool = False) -> int:
         """x / out: fp32 [B, T, F*M] time-major; vecs: fp32 [L, Bt, C] step vectors of this evaluation.  hoisted: ws.cproj
@@ -192,6 +212,16 @@ class LynxEngine:
         """Runs a sampler Program (core/programs.py) with this backbone: EVAL = self.eval, LINCOMB = ds_lincomb, the whole op
         list captured in one CUDA graph per (program, B, T) and replayed on later calls."""
         B, T, FM = x_tm.shape
+        bc = self.max_chunk_batch(B, T, prog.n_bufs)
+        if bc < B:  # utterances are independent: a batch that does not fit runs as consecutive chunks (same graph)
+            out = torch.empty_like(x_tm)
+            launches = 0
+            for lo in range(0, B, bc):
+                hi = min(B, lo + bc)
+                out[lo:hi] = self.run_program(module, prog, x_tm[lo:hi], cond_bht[lo:hi], [e[lo:hi] for e in extra], use_graph)
+                launches += self.workspace(hi - lo, T).last_launches
+            self.last_launches = launches
+            return out
         ws = self.workspace(B, T)
         bufs = ws.bufs(prog.n_bufs)
         bufs[0].copy_(x_tm)

@@ -53,6 +53,7 @@ class WaveNetStack(torch.autograd.Function):
     """
 
     @staticmethod
+    @torch.amp.custom_fwd(device_type='cuda', cast_inputs=torch.float32)  # under the trainer's autocast: fp32 in, own bf16 inside
     def forward(ctx, x0, cond, dvecs, w1, b1, wc, bc, w2, b2, dilations: List[int]):
         nat.require_device()
         B, T, Cc = x0.shape
@@ -90,6 +91,7 @@ class WaveNetStack(torch.autograd.Function):
         return S.float().view(B, T, Cc)
 
     @staticmethod
+    @torch.amp.custom_bwd(device_type='cuda')
     def backward(ctx, dS):
         XT, Z, Y, cond_bf, w1, wc, w2 = ctx.saved_tensors
         B, T, Cc, H, L = ctx.shape

@@ -104,3 +104,29 @@ def test_samplers_with_lynxnet(algo):
     prog = next(iter(m._programs.values()))
     # strong_cond = False: the conditioner projections (L GEMMs) are hoisted out of the loop, 4 launches per layer inside it
     assert prog.nfe == 10 and ws.last_launches == L + prog.nfe * (4 * L + 4) + (len(prog.ops) - prog.nfe)
+
+
+def test_lynxnet_batch_chunking_is_bitwise_identical(monkeypatch):
+    """LynxEngine.max_chunk_batch: a batch that would not fit runs as consecutive chunks; utterances are independent end to
+    end (LayerNorm, depthwise conv and the 1x1 GEMMs are per frame / per utterance, lynxnet.py:82-99), so the rows agree bit
+    for bit."""
+    M, F, L, C, H, k, B, T = 128, 1, 2, 256, 256, 31, 5, 150
+    sd = random_lynx_state_dict(M, F, L, C, H, expansion_factor=2, kernel_size=k, activation="PReLU", seed=4)
+    ds.hparams.clear()
+    ds.hparams.update(hidden_size=H, schedule_type="linear", use_shallow_diffusion=False, diff_accelerator="dpm-solver",
+                      diff_speedup=100, K_step=1000, K_step_infer=1000, timesteps=1000)
+    m = ds.GaussianDiffusion(M, F, 1000, 1000, "lynxnet", dict(num_layers=L, num_channels=C, expansion_factor=2, kernel_size=k),
+                             spec_min=[-12.0], spec_max=[0.0])
+    m.denoise_fn.load_state_dict(sd)
+    m = m.eval().to(dev)
+    cond = torch.randn(B, T, H, generator=torch.Generator().manual_seed(1)).to(dev)
+    outs = []
+    for cap in (None, str(2 * T), str(T)):
+        if cap is None:
+            monkeypatch.delenv("DSB200_MAX_FRAMES", raising=False)
+        else:
+            monkeypatch.setenv("DSB200_MAX_FRAMES", cap)
+        torch.manual_seed(3)
+        with torch.no_grad():
+            outs.append(m(cond, infer=True).cpu())
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])

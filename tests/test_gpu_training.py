@@ -122,6 +122,23 @@ def test_module_forward_backward_match_torch_autograd(C, L, M, F, cycle, B, T):
     _check(grads, MODULE_GRAD_TOL)
 
 
+def test_native_stack_under_autocast():
+    """The reference's trainer may run the step under bf16 autocast (Lightning precision plugin): the Function takes fp32
+    copies of autocast's bf16 tensors, and gradients reach the fp32 parameters."""
+    torch.manual_seed(2)
+    m = _model(256, 3, 128, 1, 4)
+    spec = torch.randn(2, 1, 128, 160, device='cuda')
+    cond = torch.randn(2, 256, 160, device='cuda')
+    t = torch.randint(0, 1000, (2,), device='cuda')
+    y0 = m(spec, t, cond)
+    with torch.autocast('cuda', dtype=torch.bfloat16):
+        y1 = m(spec, t, cond)
+    y1.float().square().mean().backward()
+    assert rel_l2(y1.detach().float(), y0.detach().float()) < 3e-2
+    for n, p in m.named_parameters():
+        assert p.grad is not None and p.grad.dtype == torch.float32 and torch.isfinite(p.grad).all(), n
+
+
 def test_p_losses_step_trains():
     """One optimiser step of GaussianDiffusion.p_losses (ddpm.py:212-219) through the native stack lowers the loss."""
     import diffsinger_b200 as ds
