@@ -19,6 +19,7 @@
 #include "layer3_kernel.cuh"
 #include "layer4_kernel.cuh"
 #include "mma_bench.cuh"
+#include "wgrad_kernel.cuh"
 
 using namespace dsb;
 
@@ -985,6 +986,42 @@ extern "C" int ds_gate_bwd(void* dz_bf16, int64_t ld_dz, const void* dy_bf16, in
       channels);
   CUDA_TRY(cudaGetLastError());
   return 0;
+}
+
+template <int BN>
+static int launch_wgrad_t(const WgradParams& p, int n_jobs, cudaStream_t st) {
+  static bool attr_done = false;
+  auto kern = ds_wgrad_kernel<BN>;
+  if (!attr_done) {
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WgradCfg<BN>::kSmemBytes));
+    attr_done = true;
+  }
+  kern<<<n_jobs, kWgradThreads, WgradCfg<BN>::kSmemBytes, st>>>(p);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ds_wgrad(const void* g_bf16, int32_t g_channels, int32_t g_batch_rows, const void* x_bf16, int32_t x_channels,
+                        int32_t x_batch_rows, int32_t T, int32_t B, int32_t BN, const ds_wgrad_job* jobs_dev, int32_t n_jobs,
+                        float* out, void* stream) {
+  static_assert(sizeof(ds_wgrad_job) == sizeof(WgradJob), "job layouts must agree");
+  if (!g_bf16 || !x_bf16 || !jobs_dev || !out) return fail(DS_ERR_INVALID, "ds_wgrad: null argument");
+  if (T <= 0 || B <= 0 || n_jobs <= 0 || g_batch_rows < B || x_batch_rows < B) return fail(DS_ERR_INVALID, "ds_wgrad: bad shape");
+  if (((uintptr_t)out) & 15) return fail(DS_ERR_INVALID, "ds_wgrad: out must be 16-byte aligned");
+  DS_TRY(ensure_device());
+  WgradParams p;
+  memset(&p, 0, sizeof(p));
+  DS_TRY(make_act_map(&p.tmG, g_bf16, g_channels, T, g_batch_rows, 64));
+  DS_TRY(make_act_map(&p.tmX, x_bf16, x_channels, T, x_batch_rows, 64));
+  p.jobs = reinterpret_cast<const WgradJob*>(jobs_dev);
+  p.out = out;
+  p.T = T;
+  p.B = B;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (BN == 256) return launch_wgrad_t<256>(p, n_jobs, st);
+  if (BN == 128) return launch_wgrad_t<128>(p, n_jobs, st);
+  if (BN == 64) return launch_wgrad_t<64>(p, n_jobs, st);
+  return fail(DS_ERR_INVALID, "ds_wgrad: BN=%d not in {64, 128, 256}", BN);
 }
 
 // Debug / bench: launch ONLY the fused kernel of residual layer `layer` on the session's current activation buffers

@@ -73,6 +73,25 @@ def gate_bwd(dz: torch.Tensor, dz_c0: int, dy: torch.Tensor, z: torch.Tensor, z_
                                     z.shape[1], dz.shape[0], channels, stream()))
 
 
+WGRAD_JOB_DTYPE = [("g_c0", "<i4"), ("g_b0", "<i4"), ("x_c0", "<i4"), ("x_b0", "<i4"), ("shift", "<i4"), ("m_valid", "<i4"),
+                   ("n_valid", "<i4"), ("ld_out", "<i4"), ("out_off", "<i8")]
+
+
+def wgrad_jobs(jobs, device) -> torch.Tensor:
+    """Device copy of a ds_wgrad_job table: jobs = iterable of (g_c0, g_b0, x_c0, x_b0, shift, m_valid, n_valid, ld_out, out_off)."""
+    import numpy as np
+    arr = np.array([tuple(j) for j in jobs], dtype=WGRAD_JOB_DTYPE)
+    return torch.from_numpy(arr.view(np.uint8).copy()).to(device)
+
+
+def wgrad(out: torch.Tensor, g: torch.Tensor, x: torch.Tensor, T: int, B: int, BN: int, jobs: torch.Tensor):
+    """out (fp32, flat) tiles = sum over frames of g^T x per job (include/dsb200.h: ds_wgrad).  g: [batch rows * T, g_channels]
+    bf16, x: [batch rows * T, x_channels] bf16; jobs from wgrad_jobs()."""
+    n_jobs = jobs.numel() // 40
+    nat.check(nat.lib().ds_wgrad(g.data_ptr(), g.shape[1], g.shape[0] // T, x.data_ptr(), x.shape[1], x.shape[0] // T, T, B, BN,
+                                 jobs.data_ptr(), n_jobs, out.data_ptr(), stream()))
+
+
 def layernorm(y: torch.Tensor, x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float = 1e-5,
               vec: Optional[torch.Tensor] = None, rows_per_vec: int = 0, add: Optional[torch.Tensor] = None):
     """y = LayerNorm(x + add + vec[row // rows_per_vec]); add bf16 [rows, ch], vec fp32 [n, ch], both optional."""

@@ -18,9 +18,12 @@ backward, per layer in reverse, with h_l = dLoss/dx_l / sqrt(2) kept in the left
     h_l  = (sum_tap W1_tap^T dz_l(t - (tap-1) dl) + h_{l+1}) / sqrt(2)                   ds_gemm EPI_RES (taps mirrored)
   then dcond = [Wc_0^T | ... ] x [dz_0 | ... | dz_{L-1}] (one GEMM, K = 2LC).
 
-Every data-gradient GEMM and the gate passes are this repo's tcgen05 / streaming kernels.  The weight gradients are plain
-``dz^T x`` products with K = B*T (activations as the K-major operand of both sides), which is a library GEMM: they go to
-cuBLAS through ``torch.matmul``, as do the O(C) bias reductions.  Head (input projection), step-embedding MLP and tail
+  weight gradients: dW1_l[:, :, tap] = dz_l^T xt_l(t + (tap-1) dl), dWc_l = dz_l^T cond, dW2_l = [h_{l+1} | dskip]^T y_l --
+  frame reductions with both operands MN-major (ds_wgrad: the tap shift and the utterance edges are TMA coordinates),
+  four launches for all layers.
+
+Every GEMM and the gate passes are this repo's tcgen05 / streaming kernels; torch supplies memory, the weight-layout
+permutations and the O(channels) bias / step-vector reductions.  Head (input projection), step-embedding MLP and tail
 (skip / output projections, < 1 % of the FLOPs) stay ordinary torch modules around the Function.
 """
 from __future__ import annotations
@@ -98,55 +101,75 @@ class WaveNetStack(torch.autograd.Function):
         dil = ctx.dilations
         rows, dev, bf = B * T, dS.device, torch.bfloat16
         # data-gradient weight layouts
-        w2t = _bf(w2.transpose(1, 2))                                                             # [L][C][2C]
+        w2t = _bf(w2.transpose(1, 2))                                                             # [L][C][2C] = [W2res^T | W2skip^T]
         w1t = _bf(w1.flip(-1).permute(0, 2, 3, 1).reshape(L, Cc, 6 * Cc))                         # [L][C][3 taps mirrored x 2C]
         wct = _bf(wc.permute(2, 0, 1).reshape(H, L * 2 * Cc))                                     # [H][L*2C]
         zero_c = torch.zeros(max(2 * Cc, H), dtype=torch.float32, device=dev)
-        G2 = torch.zeros(rows, 2 * Cc, dtype=bf, device=dev)                                      # [h_{l+1} | dskip]
-        G2[:, Cc:] = dS.reshape(rows, Cc)
+        dS_bf = torch.empty(rows, Cc, dtype=bf, device=dev)
+        ops.cast_bf16(dS_bf, dS.float().contiguous().view(rows, Cc))
+        HALL = torch.empty(L + 1, rows, Cc, dtype=bf, device=dev)                                 # h_l; h_L = 0 (last residual unused)
+        HALL[L].zero_()
         DY = torch.empty(rows, Cc, dtype=bf, device=dev)
         DZ = torch.empty(rows, L * 2 * Cc, dtype=bf, device=dev)
-        hsum = torch.zeros(L + 1, B, Cc, dtype=torch.float32, device=dev)                         # sum_t h_l per utterance
-        dw2 = torch.empty(L, 2 * Cc, Cc, dtype=torch.float32, device=dev)
-        G2v, Yv = G2.view(B, T, 2 * Cc), Y.view(rows, L, Cc)
         for l in range(L - 1, -1, -1):
-            if l + 1 < L:  # residual half of dW2_l = h_{l+1}^T y_l * sqrt(2)^0: d(x_{l+1})/d(res) = 1/sqrt(2), already in h
-                dw2[l, :Cc] = torch.matmul(G2[:, :Cc].t(), Yv[:, l]).float()
-                ops.gemm(ops.EPI_LINEAR, _bn(Cc), B, T, G2, w2t[l], DY, bias=zero_c)
-            else:
-                dw2[l, :Cc] = 0
-                ops.gemm(ops.EPI_LINEAR, _bn(Cc), B, T, G2, w2t[l][:, Cc:].contiguous(), DY, k_per_tap=Cc, a_c0=Cc, bias=zero_c)
+            ops.gemm(ops.EPI_LINEAR, _bn(Cc), B, T, HALL[l + 1], w2t[l], DY, a1=dS_bf, bias=zero_c)
             ops.gate_bwd(DZ, l * 2 * Cc, DY, Z, l * 2 * Cc, Cc)
-            ops.gemm(ops.EPI_RES, _bn(Cc), B, T, DZ, w1t[l], G2, k_per_tap=2 * Cc, n_taps=3, dil=dil[l], a_c0=l * 2 * Cc,
-                     vec=zero_c, vec_bstride=0, res=G2, scale=_RS2)
-            hsum[l] = torch.sum(G2v[:, :, :Cc], 1, dtype=torch.float32)
+            ops.gemm(ops.EPI_RES, _bn(Cc), B, T, DZ, w1t[l], HALL[l], k_per_tap=2 * Cc, n_taps=3, dil=dil[l], a_c0=l * 2 * Cc,
+                     vec=zero_c, vec_bstride=0, res=HALL[l + 1], scale=_RS2)
         dcond = torch.empty(rows, H, dtype=bf, device=dev)
         ops.gemm(ops.EPI_LINEAR, _bn(H), B, T, DZ, wct, dcond, bias=zero_c)
-        # ---- weight / bias / step-vector gradients: K = B*T library GEMMs and reductions
-        DZv = DZ.view(B, T, L, 2 * Cc)
-        XTv = XT.view(L, B, T, Cc)
-        dw1 = torch.empty(L, 3, 2 * Cc, Cc, dtype=torch.float32, device=dev)           # tap-major: contiguous per-tap writes
-        for l in range(L):
-            d = dil[l]
-            dzl = DZv[:, :, l]                                                                    # [B, T, 2C]
-            for tap in range(3):
-                s = (tap - 1) * d                                                                 # z[t] += W_tap xt[t + s]
-                lo, hi = max(0, -s), min(T, T - s)
-                if hi <= lo:
-                    dw1[l, tap] = 0
-                    continue
-                g = torch.matmul(dzl[:, lo:hi].transpose(1, 2), XTv[l, :, lo + s:hi + s])         # [B, 2C, C]
-                torch.sum(g, 0, dtype=torch.float32, out=dw1[l, tap])
-        dwc = torch.matmul(DZ.t(), cond_bf).float().view(L, 2 * Cc, H)
-        dw2[:, Cc:] = torch.matmul(G2[:, Cc:].t(), Y).float().view(Cc, L, Cc).permute(1, 0, 2)
+        # ---- weight gradients: frame reductions dz^T x with the tap shift as a TMA coordinate (ds_wgrad), fp32 out
+        jt = _wgrad_tables(B, T, Cc, H, L, tuple(dil), dev)
+        dw1 = torch.empty(L, 3, 2 * Cc, Cc, dtype=torch.float32, device=dev)                      # tap-major
+        dwc = torch.empty(L, 2 * Cc, H, dtype=torch.float32, device=dev)
+        dw2 = torch.empty(L, 2 * Cc, Cc, dtype=torch.float32, device=dev)
+        ops.wgrad(dw1, DZ, XT.view(L * rows, Cc), T, B, _bn(Cc), jt["w1"])
+        ops.wgrad(dwc, DZ, cond_bf, T, B, _bn(H), jt["wc"])
+        ops.wgrad(dw2, HALL.view((L + 1) * rows, Cc), Y, T, B, _bn(Cc), jt["w2res"])
+        ops.wgrad(dw2, dS_bf, Y, T, B, _bn(Cc), jt["w2skip"])
+        # ---- bias / step-vector gradients: O(channels) reductions
+        hsum = torch.sum(HALL.view(L + 1, B, T, Cc), 2, dtype=torch.float32)                      # sum_t h_l per utterance
         db1 = torch.sum(DZ, 0, dtype=torch.float32).view(L, 2 * Cc)
         db2 = torch.empty(L, 2 * Cc, dtype=torch.float32, device=dev)
         db2[:, :Cc] = hsum[1:].sum(1)
-        db2[:, Cc:] = torch.sum(G2[:, Cc:], 0, dtype=torch.float32)
+        db2[:, Cc:] = torch.sum(dS_bf, 0, dtype=torch.float32)
         # d_l only enters through the conv input: sum_t (sqrt(2) h_l - h_{l+1})
         ddv = math.sqrt(2.0) * hsum[:L] - hsum[1:]
-        dx0 = (G2v[:, :, :Cc].float() * math.sqrt(2.0))
+        dx0 = HALL[0].view(B, T, Cc).float() * math.sqrt(2.0)
         return dx0, dcond.float().view(B, T, H), ddv, dw1.permute(0, 2, 3, 1), db1, dwc, db1.clone(), dw2, db2, None
+
+
+_WGRAD_TABLES = {}
+
+
+def _wgrad_tables(B, T, Cc, H, L, dil, dev):
+    """Device job tables of the four ds_wgrad launches of one backward pass (ops.wgrad_jobs), cached per shape.
+    Layer-major order: the tiles of one layer share their operand columns and run concurrently (L2 reuse)."""
+    key = (B, T, Cc, H, L, dil, str(dev))
+    tabs = _WGRAD_TABLES.get(key)
+    if tabs is not None:
+        return tabs
+    if len(_WGRAD_TABLES) > 64:
+        _WGRAD_TABLES.clear()
+    bn_c, bn_h = _bn(Cc), _bn(H)
+    w1, wcj, w2r, w2s = [], [], [], []
+    for l in range(L):
+        for tap in range(3):
+            for m0 in range(0, 2 * Cc, 128):
+                for n0 in range(0, Cc, bn_c):
+                    w1.append((l * 2 * Cc + m0, 0, n0, l * B, (tap - 1) * dil[l], min(128, 2 * Cc - m0), min(bn_c, Cc - n0), Cc,
+                               ((l * 3 + tap) * 2 * Cc + m0) * Cc + n0))
+        for m0 in range(0, 2 * Cc, 128):
+            for n0 in range(0, H, bn_h):
+                wcj.append((l * 2 * Cc + m0, 0, n0, 0, 0, min(128, 2 * Cc - m0), min(bn_h, H - n0), H, (l * 2 * Cc + m0) * H + n0))
+        for m0 in range(0, Cc, 128):
+            for n0 in range(0, Cc, bn_c):
+                mv, nv = min(128, Cc - m0), min(bn_c, Cc - n0)
+                # residual half: rows [0, C) of dW2_l = h_{l+1}^T y_l;  skip half: rows [C, 2C) = dskip^T y_l
+                w2r.append((m0, (l + 1) * B, l * Cc + n0, 0, 0, mv, nv, Cc, (l * 2 * Cc + m0) * Cc + n0))
+                w2s.append((m0, 0, l * Cc + n0, 0, 0, mv, nv, Cc, (l * 2 * Cc + Cc + m0) * Cc + n0))
+    tabs = _WGRAD_TABLES[key] = {k: ops.wgrad_jobs(v, dev) for k, v in (("w1", w1), ("wc", wcj), ("w2res", w2r), ("w2skip", w2s))}
+    return tabs
 
 
 def wavenet_forward_train(module, spec, diffusion_step, cond):

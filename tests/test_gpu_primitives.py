@@ -107,3 +107,34 @@ def test_cast_bf16_pads():
     assert torch.equal(y[:, :48], x.to(torch.bfloat16)) and (y[:, 48:] == 0).all()
     with pytest.raises(nat.NativeError):
         nat.check(nat.lib().ds_dwconv(y.data_ptr(), y.data_ptr(), x.data_ptr(), None, None, 1, 8, 64, 5, 2, 0, _st()))
+
+
+@pytest.mark.parametrize("BN", [64, 128, 256])
+@pytest.mark.parametrize("B,T", [(3, 150), (1, 64), (2, 333)])
+def test_wgrad_shifted_frame_reductions(BN, B, T):
+    """ds_wgrad: out = sum_{b,t} G[b,t,:]^T X[b,t+shift,:] with zero padding outside [0, T) -- the weight gradients of a dilated
+    conv tap / 1x1 conv (wavenet.py:36-44 under autograd).  fp32 accumulation of bf16 products: rel-L2 <= 1e-5 vs fp64."""
+    from diffsinger_b200 import ops
+    torch.manual_seed(B * 1000 + T + BN)
+    Lg, Cg, Cx = 2, 320, 448              # G: two "layers" side by side in one buffer; X with its own batch-row offset
+    G = _bf(B * T, Lg * Cg)
+    X = _bf(2 * B * T, Cx)                # batch rows [B, 2B) are used
+    jobs, refs = [], []
+    ld_out, off = Cx, 0
+    out = torch.full((Lg * 3 * Cg * ld_out,), float("nan"), device=dev)
+    Gv, Xv = G.view(B, T, Lg * Cg).double(), X.view(2 * B, T, Cx).double()[B:]
+    for l in range(Lg):
+        for shift in (-4, 0, 16):
+            lo, hi = max(0, -shift), min(T, T - shift)
+            ref = torch.einsum("btm,btn->mn", Gv[:, lo:hi, l * Cg:(l + 1) * Cg], Xv[:, lo + shift:hi + shift]) if hi > lo else \
+                torch.zeros(Cg, Cx, dtype=torch.float64, device=dev)
+            refs.append((off, ref))
+            for m0 in range(0, Cg, 128):
+                for n0 in range(0, Cx, BN):
+                    jobs.append((l * Cg + m0, 0, n0, B, shift, min(128, Cg - m0), min(BN, Cx - n0), ld_out, off + m0 * ld_out + n0))
+            off += Cg * ld_out
+    ops.wgrad(out, G, X, T, B, BN, ops.wgrad_jobs(jobs, dev))
+    for o, ref in refs:
+        got = out[o:o + Cg * ld_out].view(Cg, ld_out)
+        assert torch.isfinite(got).all()
+        assert rel_l2(got, ref) < 1e-5
