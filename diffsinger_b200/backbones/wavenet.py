@@ -4,8 +4,8 @@ Same constructor signature, parameter names / shapes / dtypes (``load_ckpt(stric
 ways) and ``forward(spec, diffusion_step, cond)`` contract.  Under
 ``torch.no_grad()`` / inference the forward runs entirely in libdsb200.so (tcgen05 GEMMs, fused
 epilogues); with autograd enabled (training ``p_losses``, wavenet.py under ddpm.py:212-219) the residual
-stack runs as ``training.WaveNetStack`` (native forward and data-gradient kernels, cuBLAS weight
-gradients) on CUDA, or as differentiable torch ops (``train_path = 'torch'``, and on CPU tensors) --
+stack runs as ``training.WaveNetStack`` (native forward, data-gradient and weight-gradient kernels)
+on CUDA, or as differentiable torch ops (``train_path = 'torch'``, and on CPU tensors) --
 that branch exists for gradients only and is never taken by the samplers.
 """
 import math

@@ -182,8 +182,10 @@ def wavenet_forward_train(module, spec, diffusion_step, cond):
     if d.shape[0] != B:
         d = d.expand(B, -1)
     layers = module.residual_layers
-    dvecs = torch.stack([l.diffusion_projection(d) for l in layers])                              # [L, B, C]
     st = lambda f: torch.stack([f(l) for l in layers])
+    # all L diffusion projections as one batched product (wavenet.py:35): [L, C, C] x [B, C] -> [L, B, C]
+    dvecs = torch.baddbmm(st(lambda l: l.diffusion_projection.bias)[:, None, :], d.expand(len(layers), -1, -1),
+                          st(lambda l: l.diffusion_projection.weight).transpose(1, 2))
     skip = WaveNetStack.apply(
         x0, cond.transpose(1, 2), dvecs,
         st(lambda l: l.dilated_conv.weight), st(lambda l: l.dilated_conv.bias),

@@ -47,7 +47,7 @@ SHAPES = [
 
 @pytest.mark.parametrize("C,L,M,F,cycle,B,T", SHAPES)
 def test_stack_matches_fp32_autograd(C, L, M, F, cycle, B, T):
-    """WaveNetStack (native forward, data gradients, cuBLAS weight gradients) against the same L residual blocks as fp32
+    """WaveNetStack (native forward, data gradients, ds_wgrad weight gradients) against the same L residual blocks as fp32
     torch ops (wavenet.py:33-48, 91-96), TF32 off."""
     import math
     from diffsinger_b200.training import WaveNetStack
