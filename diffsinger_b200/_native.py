@@ -55,6 +55,12 @@ class Op(C.Structure):
                 ("src", C.c_int32 * 8), ("coef", C.c_float * 8)]
 
 
+class WgradOperands(C.Structure):
+    """ds_wgrad_operands (include/dsb200.h)."""
+    _fields_ = [("g_bf16", C.c_void_p), ("x_bf16", C.c_void_p), ("g_channels", C.c_int32), ("g_batch_rows", C.c_int32),
+                ("x_channels", C.c_int32), ("x_batch_rows", C.c_int32)]
+
+
 class GemmDesc(C.Structure):
     _fields_ = [
         ("epi", C.c_int32), ("BN", C.c_int32), ("B", C.c_int32), ("T", C.c_int32),
@@ -128,8 +134,8 @@ def lib() -> C.CDLL:
     L.ds_gemm.argtypes = [C.POINTER(GemmDesc), C.c_void_p]
     L.ds_gate_fwd.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_void_p]
     L.ds_gate_bwd.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_void_p]
-    L.ds_wgrad.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
-                           C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
+    L.ds_wgrad.argtypes = [C.POINTER(WgradOperands), C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p,
+                           C.c_void_p]
     L.ds_layernorm.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_float, C.c_void_p,
                                C.c_int64, C.c_void_p, C.c_void_p]
     L.ds_dwconv.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32,

@@ -1001,18 +1001,22 @@ static int launch_wgrad_t(const WgradParams& p, int n_jobs, cudaStream_t st) {
   return 0;
 }
 
-extern "C" int ds_wgrad(const void* g_bf16, int32_t g_channels, int32_t g_batch_rows, const void* x_bf16, int32_t x_channels,
-                        int32_t x_batch_rows, int32_t T, int32_t B, int32_t BN, const ds_wgrad_job* jobs_dev, int32_t n_jobs,
-                        float* out, void* stream) {
+extern "C" int ds_wgrad(const ds_wgrad_operands* pairs, int32_t n_pairs, int32_t T, int32_t B, int32_t BN, const ds_wgrad_job* jobs_dev,
+                        int32_t n_jobs, float* out, void* stream) {
   static_assert(sizeof(ds_wgrad_job) == sizeof(WgradJob), "job layouts must agree");
-  if (!g_bf16 || !x_bf16 || !jobs_dev || !out) return fail(DS_ERR_INVALID, "ds_wgrad: null argument");
-  if (T <= 0 || B <= 0 || n_jobs <= 0 || g_batch_rows < B || x_batch_rows < B) return fail(DS_ERR_INVALID, "ds_wgrad: bad shape");
+  if (!pairs || !jobs_dev || !out) return fail(DS_ERR_INVALID, "ds_wgrad: null argument");
+  if (n_pairs <= 0 || n_pairs > kWgradMaxPairs) return fail(DS_ERR_INVALID, "ds_wgrad: n_pairs=%d outside [1, %d]", n_pairs, kWgradMaxPairs);
+  if (T <= 0 || B <= 0 || n_jobs <= 0) return fail(DS_ERR_INVALID, "ds_wgrad: bad shape");
   if (((uintptr_t)out) & 15) return fail(DS_ERR_INVALID, "ds_wgrad: out must be 16-byte aligned");
   DS_TRY(ensure_device());
   WgradParams p;
   memset(&p, 0, sizeof(p));
-  DS_TRY(make_act_map(&p.tmG, g_bf16, g_channels, T, g_batch_rows, 64));
-  DS_TRY(make_act_map(&p.tmX, x_bf16, x_channels, T, x_batch_rows, 64));
+  for (int i = 0; i < kWgradMaxPairs; ++i) {
+    const ds_wgrad_operands& o = pairs[i < n_pairs ? i : 0];  // unused slots repeat pair 0 (always a valid map)
+    if (!o.g_bf16 || !o.x_bf16 || o.g_batch_rows < B || o.x_batch_rows < B) return fail(DS_ERR_INVALID, "ds_wgrad: bad operand pair %d", i);
+    DS_TRY(make_act_map(&p.tmG[i], o.g_bf16, o.g_channels, T, o.g_batch_rows, 64));
+    DS_TRY(make_act_map(&p.tmX[i], o.x_bf16, o.x_channels, T, o.x_batch_rows, 64));
+  }
   p.jobs = reinterpret_cast<const WgradJob*>(jobs_dev);
   p.out = out;
   p.T = T;

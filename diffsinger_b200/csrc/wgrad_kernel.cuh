@@ -13,7 +13,9 @@
 // so there is no im2col, no per-utterance batched product and no reduction over utterances afterwards.
 //
 // One CTA = one output tile, K loop over all B * ceil(T / 64) frame blocks; tiles of one launch come from a job table
-// (all layers and taps at once), ordered so that tiles sharing operand columns run concurrently and share L2.
+// (all layers, taps and weight tensors at once: up to four (G, X) operand pairs per launch, so that one backward pass
+// is ~10 full waves instead of several launches with a partial last wave each), ordered so that tiles sharing operand
+// columns run concurrently and share L2.
 // Warp roles: 0 = TMA producer, 1 = MMA issuer, 2..5 = epilogue (TMEM -> fp32 global).
 #pragma once
 #include <cuda.h>
@@ -30,10 +32,14 @@ struct WgradJob {
   int n_valid;       // columns of this tile that exist (<= BN)
   int ld_out;        // fp32 elements between output rows
   long long out_off; // element offset of out[0][0] of this tile
+  int pair;          // which (G, X) operand pair of the launch this tile reads
+  int pad;
 };
 
+constexpr int kWgradMaxPairs = 4;
+
 struct WgradParams {
-  CUtensorMap tmG, tmX;  // bf16 (channels, T, batch rows), box (64, 64, 1), SWIZZLE_128B
+  CUtensorMap tmG[kWgradMaxPairs], tmX[kWgradMaxPairs];  // bf16 (channels, T, batch rows), box (64, 64, 1), SWIZZLE_128B
   const WgradJob* jobs;
   float* out;
   int T, B;
@@ -77,9 +83,12 @@ __global__ void __launch_bounds__(kWgradThreads, 1) ds_wgrad_kernel(const __grid
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const WgradJob job = p.jobs[blockIdx.x];
+  const CUtensorMap* tmG = &p.tmG[job.pair];
+  const CUtensorMap* tmX = &p.tmX[job.pair];
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&p.tmG);
-    tma_prefetch_desc(&p.tmX);
+    tma_prefetch_desc(tmG);
+    tma_prefetch_desc(tmX);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < S; ++i) {
@@ -95,7 +104,6 @@ __global__ void __launch_bounds__(kWgradThreads, 1) ds_wgrad_kernel(const __grid
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const WgradJob job = p.jobs[blockIdx.x];
   const int tiles_t = (p.T + 63) / 64;
   const int num_kb = p.B * tiles_t;
 
@@ -110,11 +118,11 @@ __global__ void __launch_bounds__(kWgradThreads, 1) ds_wgrad_kernel(const __grid
           mbar_arrive_expect_tx(&full[stage], Cfg::kABytes + Cfg::kBBytes);
           uint8_t* sa = smem_a + stage * Cfg::kABytes;
           uint8_t* sb = smem_b + stage * Cfg::kBBytes;
-          tma_load_3d(&p.tmG, &full[stage], sa, job.g_c0, t0, job.g_b0 + b);
-          tma_load_3d(&p.tmG, &full[stage], sa + kWgradBox, job.g_c0 + 64, t0, job.g_b0 + b);
+          tma_load_3d(tmG, &full[stage], sa, job.g_c0, t0, job.g_b0 + b);
+          tma_load_3d(tmG, &full[stage], sa + kWgradBox, job.g_c0 + 64, t0, job.g_b0 + b);
 #pragma unroll
           for (int j = 0; j < BN / 64; ++j)
-            tma_load_3d(&p.tmX, &full[stage], sb + j * kWgradBox, job.x_c0 + j * 64, t0 + job.shift, job.x_b0 + b);
+            tma_load_3d(tmX, &full[stage], sb + j * kWgradBox, job.x_c0 + j * 64, t0 + job.shift, job.x_b0 + b);
           if (++stage == S) {
             stage = 0;
             phase ^= 1;

@@ -4,7 +4,7 @@ launches on the current CUDA stream and returns immediately; nothing here comput
 from __future__ import annotations
 
 import ctypes as C
-from typing import Optional, Sequence
+from typing import Optional, Sequence, Tuple
 
 import torch
 
@@ -74,22 +74,27 @@ def gate_bwd(dz: torch.Tensor, dz_c0: int, dy: torch.Tensor, z: torch.Tensor, z_
 
 
 WGRAD_JOB_DTYPE = [("g_c0", "<i4"), ("g_b0", "<i4"), ("x_c0", "<i4"), ("x_b0", "<i4"), ("shift", "<i4"), ("m_valid", "<i4"),
-                   ("n_valid", "<i4"), ("ld_out", "<i4"), ("out_off", "<i8")]
+                   ("n_valid", "<i4"), ("ld_out", "<i4"), ("out_off", "<i8"), ("pair", "<i4"), ("reserved", "<i4")]
+WGRAD_JOB_BYTES = 48
 
 
 def wgrad_jobs(jobs, device) -> torch.Tensor:
-    """Device copy of a ds_wgrad_job table: jobs = iterable of (g_c0, g_b0, x_c0, x_b0, shift, m_valid, n_valid, ld_out, out_off)."""
+    """Device copy of a ds_wgrad_job table: jobs = iterable of (g_c0, g_b0, x_c0, x_b0, shift, m_valid, n_valid, ld_out, out_off,
+    pair)."""
     import numpy as np
-    arr = np.array([tuple(j) for j in jobs], dtype=WGRAD_JOB_DTYPE)
+    arr = np.array([tuple(j) + (0,) for j in jobs], dtype=WGRAD_JOB_DTYPE)
+    assert arr.itemsize == WGRAD_JOB_BYTES
     return torch.from_numpy(arr.view(np.uint8).copy()).to(device)
 
 
-def wgrad(out: torch.Tensor, g: torch.Tensor, x: torch.Tensor, T: int, B: int, BN: int, jobs: torch.Tensor):
-    """out (fp32, flat) tiles = sum over frames of g^T x per job (include/dsb200.h: ds_wgrad).  g: [batch rows * T, g_channels]
-    bf16, x: [batch rows * T, x_channels] bf16; jobs from wgrad_jobs()."""
-    n_jobs = jobs.numel() // 40
-    nat.check(nat.lib().ds_wgrad(g.data_ptr(), g.shape[1], g.shape[0] // T, x.data_ptr(), x.shape[1], x.shape[0] // T, T, B, BN,
-                                 jobs.data_ptr(), n_jobs, out.data_ptr(), stream()))
+def wgrad(out: torch.Tensor, pairs: Sequence[Tuple[torch.Tensor, torch.Tensor]], T: int, B: int, BN: int, jobs: torch.Tensor):
+    """out (fp32, flat) tiles = sum over frames of g^T x per job (include/dsb200.h: ds_wgrad).  pairs: up to four (g, x) operand
+    pairs, g: [batch rows * T, g_channels] bf16, x: [batch rows * T, x_channels] bf16; jobs from wgrad_jobs()."""
+    arr = (nat.WgradOperands * len(pairs))()
+    for o, (g, x) in zip(arr, pairs):
+        o.g_bf16, o.x_bf16 = g.data_ptr(), x.data_ptr()
+        o.g_channels, o.g_batch_rows, o.x_channels, o.x_batch_rows = g.shape[1], g.shape[0] // T, x.shape[1], x.shape[0] // T
+    nat.check(nat.lib().ds_wgrad(arr, len(pairs), T, B, BN, jobs.data_ptr(), jobs.numel() // WGRAD_JOB_BYTES, out.data_ptr(), stream()))
 
 
 def layernorm(y: torch.Tensor, x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float = 1e-5,

@@ -20,7 +20,7 @@ backward, per layer in reverse, with h_l = dLoss/dx_l / sqrt(2) kept in the left
 
   weight gradients: dW1_l[:, :, tap] = dz_l^T xt_l(t + (tap-1) dl), dWc_l = dz_l^T cond, dW2_l = [h_{l+1} | dskip]^T y_l --
   frame reductions with both operands MN-major (ds_wgrad: the tap shift and the utterance edges are TMA coordinates),
-  four launches for all layers.
+  one launch for all layers, taps and weight tensors (two when C and H need different tile widths).
 
 Every GEMM and the gate passes are this repo's tcgen05 / streaming kernels; torch supplies memory, the weight-layout
 permutations and the O(channels) bias / step-vector reductions.  Head (input projection), step-embedding MLP and tail
@@ -119,14 +119,14 @@ class WaveNetStack(torch.autograd.Function):
         dcond = torch.empty(rows, H, dtype=bf, device=dev)
         ops.gemm(ops.EPI_LINEAR, _bn(H), B, T, DZ, wct, dcond, bias=zero_c)
         # ---- weight gradients: frame reductions dz^T x with the tap shift as a TMA coordinate (ds_wgrad), fp32 out
-        jt = _wgrad_tables(B, T, Cc, H, L, tuple(dil), dev)
-        dw1 = torch.empty(L, 3, 2 * Cc, Cc, dtype=torch.float32, device=dev)                      # tap-major
-        dwc = torch.empty(L, 2 * Cc, H, dtype=torch.float32, device=dev)
-        dw2 = torch.empty(L, 2 * Cc, Cc, dtype=torch.float32, device=dev)
-        ops.wgrad(dw1, DZ, XT.view(L * rows, Cc), T, B, _bn(Cc), jt["w1"])
-        ops.wgrad(dwc, DZ, cond_bf, T, B, _bn(H), jt["wc"])
-        ops.wgrad(dw2, HALL.view((L + 1) * rows, Cc), Y, T, B, _bn(Cc), jt["w2res"])
-        ops.wgrad(dw2, dS_bf, Y, T, B, _bn(Cc), jt["w2skip"])
+        n1, nc, n2 = L * 3 * 2 * Cc * Cc, L * 2 * Cc * H, L * 2 * Cc * Cc
+        dw_all = torch.empty(n1 + nc + n2, dtype=torch.float32, device=dev)
+        dw1 = dw_all[:n1].view(L, 3, 2 * Cc, Cc)                                                  # tap-major
+        dwc = dw_all[n1:n1 + nc].view(L, 2 * Cc, H)
+        dw2 = dw_all[n1 + nc:].view(L, 2 * Cc, Cc)
+        pairs = [(DZ, XT.view(L * rows, Cc)), (DZ, cond_bf), (HALL.view((L + 1) * rows, Cc), Y), (dS_bf, Y)]
+        for bn, table in _wgrad_tables(B, T, Cc, H, L, tuple(dil), dev):
+            ops.wgrad(dw_all, pairs, T, B, bn, table)
         # ---- bias / step-vector gradients: O(channels) reductions
         hsum = torch.sum(HALL.view(L + 1, B, T, Cc), 2, dtype=torch.float32)                      # sum_t h_l per utterance
         db1 = torch.sum(DZ, 0, dtype=torch.float32).view(L, 2 * Cc)
@@ -143,8 +143,10 @@ _WGRAD_TABLES = {}
 
 
 def _wgrad_tables(B, T, Cc, H, L, dil, dev):
-    """Device job tables of the four ds_wgrad launches of one backward pass (ops.wgrad_jobs), cached per shape.
-    Layer-major order: the tiles of one layer share their operand columns and run concurrently (L2 reuse)."""
+    """[(BN, device job table)] of one backward pass (ops.wgrad_jobs), cached per shape: every tile of dW1 (operand pair 0),
+    dWc (1), dW2 residual half (2) and skip half (3) with offsets into one flat fp32 buffer [dW1 | dWc | dW2] -- one launch
+    when C and H share a tile width.  Layer-major order: the tiles of one layer share their operand columns and run
+    concurrently (L2 reuse)."""
     key = (B, T, Cc, H, L, dil, str(dev))
     tabs = _WGRAD_TABLES.get(key)
     if tabs is not None:
@@ -152,23 +154,25 @@ def _wgrad_tables(B, T, Cc, H, L, dil, dev):
     if len(_WGRAD_TABLES) > 64:
         _WGRAD_TABLES.clear()
     bn_c, bn_h = _bn(Cc), _bn(H)
-    w1, wcj, w2r, w2s = [], [], [], []
+    o_c, o_2 = L * 3 * 2 * Cc * Cc, L * 3 * 2 * Cc * Cc + L * 2 * Cc * H
+    jobs = {bn_c: [], bn_h: []}
     for l in range(L):
         for tap in range(3):
             for m0 in range(0, 2 * Cc, 128):
                 for n0 in range(0, Cc, bn_c):
-                    w1.append((l * 2 * Cc + m0, 0, n0, l * B, (tap - 1) * dil[l], min(128, 2 * Cc - m0), min(bn_c, Cc - n0), Cc,
-                               ((l * 3 + tap) * 2 * Cc + m0) * Cc + n0))
+                    jobs[bn_c].append((l * 2 * Cc + m0, 0, n0, l * B, (tap - 1) * dil[l], min(128, 2 * Cc - m0), min(bn_c, Cc - n0), Cc,
+                                       ((l * 3 + tap) * 2 * Cc + m0) * Cc + n0, 0))
         for m0 in range(0, 2 * Cc, 128):
             for n0 in range(0, H, bn_h):
-                wcj.append((l * 2 * Cc + m0, 0, n0, 0, 0, min(128, 2 * Cc - m0), min(bn_h, H - n0), H, (l * 2 * Cc + m0) * H + n0))
+                jobs[bn_h].append((l * 2 * Cc + m0, 0, n0, 0, 0, min(128, 2 * Cc - m0), min(bn_h, H - n0), H,
+                                   o_c + (l * 2 * Cc + m0) * H + n0, 1))
         for m0 in range(0, Cc, 128):
             for n0 in range(0, Cc, bn_c):
                 mv, nv = min(128, Cc - m0), min(bn_c, Cc - n0)
                 # residual half: rows [0, C) of dW2_l = h_{l+1}^T y_l;  skip half: rows [C, 2C) = dskip^T y_l
-                w2r.append((m0, (l + 1) * B, l * Cc + n0, 0, 0, mv, nv, Cc, (l * 2 * Cc + m0) * Cc + n0))
-                w2s.append((m0, 0, l * Cc + n0, 0, 0, mv, nv, Cc, (l * 2 * Cc + Cc + m0) * Cc + n0))
-    tabs = _WGRAD_TABLES[key] = {k: ops.wgrad_jobs(v, dev) for k, v in (("w1", w1), ("wc", wcj), ("w2res", w2r), ("w2skip", w2s))}
+                jobs[bn_c].append((m0, (l + 1) * B, l * Cc + n0, 0, 0, mv, nv, Cc, o_2 + (l * 2 * Cc + m0) * Cc + n0, 2))
+                jobs[bn_c].append((m0, 0, l * Cc + n0, 0, 0, mv, nv, Cc, o_2 + (l * 2 * Cc + Cc + m0) * Cc + n0, 3))
+    tabs = _WGRAD_TABLES[key] = [(bn, ops.wgrad_jobs(j, dev)) for bn, j in jobs.items() if j]
     return tabs
 
 

@@ -170,15 +170,21 @@ int ds_gate_bwd(void* dz_bf16, int64_t ld_dz, const void* dy_bf16, int64_t ld_dy
 /* Weight-gradient GEMMs of the training path: for every job (one 128 x BN output tile, BN in {64, 128, 256})
  *   out[out_off + m * ld_out + n] = sum_{b < B, t < T} G[g_b0 + b][t][g_c0 + m] * X[x_b0 + b][t + shift][x_c0 + n],
  *   m < m_valid <= 128, n < n_valid <= BN, frames outside [0, T) read as zeros (the conv's padding);
- * e.g. d(dilated_conv.weight)[:, :, tap] = dz^T x(t + (tap - 1) dil) (wavenet.py:36-38 under autograd).  G / X: bf16
+ * e.g. d(dilated_conv.weight)[:, :, tap] = dz^T x(t + (tap - 1) dil) (wavenet.py:36-38 under autograd).  (G, X) = operand
+ * pair `pair` of the launch (up to 4 pairs, so that all weight tensors of one backward pass share a launch): bf16
  * [batch rows][T][channels]; channel offsets multiples of 8; ld_out and out_off multiples of 4; jobs in DEVICE memory. */
+typedef struct ds_wgrad_operands {
+  const void* g_bf16;
+  const void* x_bf16;
+  int32_t g_channels, g_batch_rows, x_channels, x_batch_rows;
+} ds_wgrad_operands;
 typedef struct ds_wgrad_job {
   int32_t g_c0, g_b0, x_c0, x_b0, shift, m_valid, n_valid, ld_out;
   int64_t out_off;
+  int32_t pair, reserved;
 } ds_wgrad_job;
-int ds_wgrad(const void* g_bf16, int32_t g_channels, int32_t g_batch_rows, const void* x_bf16, int32_t x_channels,
-             int32_t x_batch_rows, int32_t T, int32_t B, int32_t BN, const ds_wgrad_job* jobs_dev, int32_t n_jobs, float* out,
-             void* stream);
+int ds_wgrad(const ds_wgrad_operands* pairs, int32_t n_pairs, int32_t T, int32_t B, int32_t BN, const ds_wgrad_job* jobs_dev,
+             int32_t n_jobs, float* out, void* stream);
 /* Debug: device buffer of n_entries x 4 uint64 into which CTA 0 of every fused-layer launch records
  * {role*16+kind, tile*16+idx, t0_ns, t1_ns} (first half: MMA issuer, second half: epilogue). NULL disables. */
 int ds_debug_set_trace(void* dev_buf, int32_t n_entries);

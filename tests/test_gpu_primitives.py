@@ -131,9 +131,10 @@ def test_wgrad_shifted_frame_reductions(BN, B, T):
             refs.append((off, ref))
             for m0 in range(0, Cg, 128):
                 for n0 in range(0, Cx, BN):
-                    jobs.append((l * Cg + m0, 0, n0, B, shift, min(128, Cg - m0), min(BN, Cx - n0), ld_out, off + m0 * ld_out + n0))
+                    jobs.append((l * Cg + m0, 0, n0, B, shift, min(128, Cg - m0), min(BN, Cx - n0), ld_out, off + m0 * ld_out + n0, 1))
             off += Cg * ld_out
-    ops.wgrad(out, G, X, T, B, BN, ops.wgrad_jobs(jobs, dev))
+    decoy = _bf(B * T, 64)  # operand pair 0 is not the one the jobs name
+    ops.wgrad(out, [(decoy, decoy), (G, X)], T, B, BN, ops.wgrad_jobs(jobs, dev))
     for o, ref in refs:
         got = out[o:o + Cg * ld_out].view(Cg, ld_out)
         assert torch.isfinite(got).all()
