@@ -163,3 +163,47 @@ def test_p_losses_step_trains():
         losses.append(loss.item())
     print("p_losses:", losses)
     assert losses[-1] < losses[0]
+
+
+def test_reflow_and_variance_p_losses_match_torch_path():
+    """RectifiedFlow.p_losses (reflow.py:36-41; float per-sample t) and MultiVarianceDiffusion training (ddpm.py:212-219 through the
+    repeat-bins wrapper, F = 2) through the native stack: same loss as the torch-op path on the same draws, finite gradients."""
+    import diffsinger_b200 as ds
+    from diffsinger_b200.synthetic import random_state_dict
+    ds.hparams.clear()
+    ds.hparams.update(hidden_size=256, schedule_type='linear', use_shallow_diffusion=False, diff_accelerator='ddim', diff_speedup=50,
+                      K_step=1000, timesteps=1000, sampling_algorithm='euler', sampling_steps=20)
+    cond = torch.randn(2, 180, 256, device='cuda', generator=torch.Generator('cuda').manual_seed(0))
+    gt = torch.rand(2, 180, 128, device='cuda', generator=torch.Generator('cuda').manual_seed(1)) * -12.0
+    rf = ds.RectifiedFlow(128, 1, 0.0, 1000, 'wavenet', dict(num_layers=3, num_channels=256, dilation_cycle_length=4),
+                          spec_min=[-12.], spec_max=[0.]).cuda()
+    rf.velocity_fn.load_state_dict(random_state_dict(128, 1, 3, 256, 256, seed=6), strict=True)
+    losses = {}
+    for path in ('native', 'torch'):
+        rf.velocity_fn.train_path = path
+        rf.zero_grad()
+        torch.manual_seed(4)
+        v_pred, v_gt, t = rf(cond, gt_spec=gt, infer=False)
+        assert t.dtype == torch.float32 and t.shape == (2,)
+        loss = torch.nn.functional.mse_loss(v_pred, v_gt)
+        loss.backward()
+        losses[path] = loss.item()
+        assert all(torch.isfinite(p.grad).all() for p in rf.velocity_fn.parameters())
+    assert abs(losses['native'] - losses['torch']) < 2e-3 * abs(losses['torch']), losses
+
+    mv = ds.MultiVarianceDiffusion(ranges=[(-96.0, -12.0), (-96.0, -20.0)], clamps=[(-96.0, 0.0), (-96.0, 0.0)], repeat_bins=24,
+                                   timesteps=1000, k_step=1000, backbone_type='wavenet',
+                                   backbone_args=dict(num_layers=2, num_channels=192, dilation_cycle_length=2)).cuda()
+    mv.denoise_fn.load_state_dict(random_state_dict(24, 2, 2, 192, 256, seed=7), strict=True)
+    curves = [torch.rand(2, 180, device='cuda') * -60.0 - 20.0 for _ in range(2)]
+    losses = {}
+    for path in ('native', 'torch'):
+        mv.denoise_fn.train_path = path
+        mv.zero_grad()
+        torch.manual_seed(5)
+        x_recon, noise = mv(cond, curves, infer=False)
+        loss = torch.nn.functional.mse_loss(x_recon, noise)
+        loss.backward()
+        losses[path] = loss.item()
+        assert all(torch.isfinite(p.grad).all() for p in mv.denoise_fn.parameters())
+    assert abs(losses['native'] - losses['torch']) < 2e-3 * abs(losses['torch']), losses
