@@ -898,6 +898,7 @@ extern "C" int ds_debug_gemm(const ds_gemm_desc* d, void* stream) {
   g.relu = d->relu; g.scale = d->scale; g.bias = d->bias; g.vec_sub = d->vec_sub; g.vec_add = d->vec_add;
   g.vec_bstride = d->vec_bstride; g.res_in = (const __nv_bfloat16*)d->res_in; g.ld_res = d->ld_res;
   g.out = d->out; g.ld_out = d->ld_out; g.out_c0 = d->out_c0; g.n_real = d->n_real;
+  g.out2 = (__nv_bfloat16*)d->out2; g.slope2 = d->slope2;
   return launch_gemm(d->BN, d->epi, g, (cudaStream_t)stream);
 }
 
@@ -984,6 +985,29 @@ extern "C" int ds_gate_bwd(void* dz_bf16, int64_t ld_dz, const void* dy_bf16, in
   gate_bwd_kernel<<<ew_grid((long)rows * channels / 8, 256), 256, 0, (cudaStream_t)stream>>>(
       (__nv_bfloat16*)dz_bf16, (long)ld_dz, (const __nv_bfloat16*)dy_bf16, (long)ld_dy, (const __nv_bfloat16*)z_bf16, (long)ld_z, (long)rows,
       channels);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ds_source_conv(void* y_bf16, const float* src, const float* w, const float* bias, int32_t B, int64_t n_src, int64_t n_out,
+                              int32_t channels, int32_t ld, int32_t kernel_size, int32_t stride, int32_t pad, void* stream) {
+  if (!y_bf16 || !src || !w || !bias || B <= 0 || n_src <= 0 || n_out <= 0) return fail(DS_ERR_INVALID, "ds_source_conv: bad argument");
+  if (channels <= 0 || ld < channels || ld % 8 || kernel_size <= 0 || kernel_size > 256 || stride <= 0 || pad < 0)
+    return fail(DS_ERR_INVALID, "ds_source_conv: bad shape");
+  DS_TRY(ensure_device());
+  const long groups = (long)B * n_out * (ld / 8);
+  source_conv_kernel<<<ew_grid(groups, 256), 256, 0, (cudaStream_t)stream>>>((__nv_bfloat16*)y_bf16, src, w, bias, B, (long)n_src,
+                                                                             (long)n_out, channels, ld, kernel_size, stride, pad);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ds_mean3_lrelu(void* y_bf16, const void* a_bf16, const void* b_bf16, const void* c_bf16, int64_t n, float slope,
+                              void* stream) {
+  if (!y_bf16 || !a_bf16 || !b_bf16 || !c_bf16 || n <= 0 || n % 8) return fail(DS_ERR_INVALID, "ds_mean3_lrelu: bad argument");
+  DS_TRY(ensure_device());
+  mean3_lrelu_kernel<<<ew_grid((long)n / 8, 256), 256, 0, (cudaStream_t)stream>>>(
+      (__nv_bfloat16*)y_bf16, (const __nv_bfloat16*)a_bf16, (const __nv_bfloat16*)b_bf16, (const __nv_bfloat16*)c_bf16, (long)n / 8, slope);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }

@@ -462,3 +462,57 @@ __global__ void __launch_bounds__(256) gate_bwd_kernel(__nv_bfloat16* __restrict
 }
 
 }  // namespace dsb
+
+// ------------------------------------------------------------------------------------ NSF-HiFiGAN helpers
+namespace dsb {
+
+// Conv1d(1 -> channels, k, stride, pad) over the single-channel harmonic source (nsf_hifigan/models.py:237-241, 281):
+// y[b][n][c] = bias[c] + sum_k w[c][k] * src[b][n * stride + k - pad].  One thread per (b, n, 8 channels); the k source
+// samples of a frame are shared by all its channel groups through L1.  Columns [channels, ld) are written as zeros.
+__global__ void __launch_bounds__(256) source_conv_kernel(__nv_bfloat16* __restrict__ y, const float* __restrict__ src,
+                                                          const float* __restrict__ w, const float* __restrict__ bias, int B, long n_src,
+                                                          long n_out, int channels, int ld, int K, int stride, int pad) {
+  const int cg = ld / 8;
+  const long total = (long)B * n_out * cg;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % cg);
+    const long bn = i / cg;
+    const long n = bn % n_out;
+    const long b = bn / n_out;
+    const int c0 = g * 8;
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = (c0 + j < channels) ? __ldg(bias + c0 + j) : 0.0f;
+    const float* sb = src + b * n_src;
+    const long s0 = n * stride - pad;
+    for (int k = 0; k < K; ++k) {
+      const long si = s0 + k;
+      if (si < 0 || si >= n_src) continue;
+      const float sv = __ldg(sb + si);
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (c0 + j < channels) acc[j] = fmaf(__ldg(w + (long)(c0 + j) * K + k), sv, acc[j]);
+    }
+    *reinterpret_cast<uint4*>(y + bn * ld + c0) = pack_bf16x8(acc);
+  }
+}
+
+// y = LeakyReLU((a + b + c) / 3, slope): the ResBlock average and the next stage's activation (models.py:286-294).
+__global__ void __launch_bounds__(256) mean3_lrelu_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ a,
+                                                          const __nv_bfloat16* __restrict__ b, const __nv_bfloat16* __restrict__ c,
+                                                          long n8, float slope) {
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n8; i += (long)gridDim.x * blockDim.x) {
+    float va[8], vb[8], vc[8], o[8];
+    unpack_bf16x8(__ldg(reinterpret_cast<const uint4*>(a) + i), va);
+    unpack_bf16x8(__ldg(reinterpret_cast<const uint4*>(b) + i), vb);
+    unpack_bf16x8(__ldg(reinterpret_cast<const uint4*>(c) + i), vc);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float m = (va[j] + vb[j] + vc[j]) * (1.0f / 3.0f);
+      o[j] = m > 0.0f ? m : m * slope;
+    }
+    reinterpret_cast<uint4*>(y)[i] = pack_bf16x8(o);
+  }
+}
+
+}  // namespace dsb

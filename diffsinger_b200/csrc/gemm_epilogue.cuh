@@ -170,6 +170,11 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
         }
       }
       if (valid) st_act32<kSplit>(xout + c * 32, p.out_lo, v);
+      if (p.out2) {  // pre-activated copy for the next convolution (HiFi-GAN ResBlock, nsf_hifigan/models.py:60-67)
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = v[j] > 0.0f ? v[j] : v[j] * p.slope2;
+        if (valid) st_act32<false>(p.out2 + row * p.ld_out + p.out_c0 + n0 + c * 32, 0, v);
+      }
 #pragma unroll
       for (int i = 0; i < 4; ++i) xq[i] = xn[i];
     }
@@ -192,6 +197,12 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
       } else if (p.relu == 2) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = 0.5f * v[j] * (1.0f + erff(v[j] * 0.70710678118654752f));
+      } else if (p.relu == 3) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = v[j] > 0.0f ? v[j] : v[j] * p.slope2;
+      } else if (p.relu == 4) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = tanhf(v[j]);
       }
 #pragma unroll
       for (int j = 0; j < 32; ++j) v[j] *= p.scale;

@@ -35,7 +35,9 @@ struct GemmParams {
   int kb_a1;   // 64-wide K blocks from A1
   int b_row0;  // first row of this GEMM inside the packed weight matrix
   int b_k0;    // first K column of this GEMM inside the packed weight matrix (hoisted conditioner projection: 3C)
-  int relu;    // activation of the LINEAR / OUTF32 epilogues: 0 none, 1 ReLU, 2 GELU (exact, erf)
+  int relu;    // activation of the LINEAR / OUTF32 epilogues: 0 none, 1 ReLU, 2 GELU (exact, erf), 3 LeakyReLU(slope2), 4 tanh
+  __nv_bfloat16* out2;  // EPI_RES, optional: second output LeakyReLU(out, slope2) with out's ld / offset
+  float slope2;
   float scale;  // LINEAR / OUTF32: multiplies act(acc + bias); RES: multiplies (acc + res_in)  (1/sqrt(2) in WaveNet)
   const float* bias;     // indexed by tile-global n (packed order for EPI_GATE)
   const float* vec_sub;  // unused (kept for ABI stability of the debug hook)

@@ -11,7 +11,7 @@ import torch
 from . import _native as nat
 
 EPI_LINEAR, EPI_GATE, EPI_RES, EPI_OUTF32, EPI_SWIGLU = 0, 1, 2, 3, 5
-ACT_NONE, ACT_RELU, ACT_GELU = 0, 1, 2
+ACT_NONE, ACT_RELU, ACT_GELU, ACT_LRELU, ACT_TANH = 0, 1, 2, 3, 4
 DW_NONE, DW_RELU, DW_PRELU, DW_SILU = 0, 1, 2, 3
 
 
@@ -37,7 +37,7 @@ def _p(t: Optional[torch.Tensor]):
 def gemm(epi: int, BN: int, B: int, T: int, a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, k_per_tap: Optional[int] = None,
          n_taps: int = 1, dil: int = 1, a_c0: int = 0, a1: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None,
          vec: Optional[torch.Tensor] = None, vec_bstride: int = 0, res: Optional[torch.Tensor] = None, act: int = ACT_NONE,
-         n_real: int = 0, scale: float = 1.0, out_c0: int = 0):
+         n_real: int = 0, scale: float = 1.0, out_c0: int = 0, out2: Optional[torch.Tensor] = None, slope2: float = 0.0):
     """out[b, t, out_c0 + n] = epilogue(sum_tap sum_k a[b, t + (tap - n_taps // 2) * dil, a_c0 + k] * w[n, tap * K + k]
     + sum_h a1[b, t, h] * w[n, n_taps * K + h]); frames outside [0, T) read as zeros (the conv's zero padding).
     a: [B*T, ld_a] bf16 (K = k_per_tap columns from a_c0), a1: optional second operand [B*T, H] (one tap),
@@ -56,6 +56,7 @@ def gemm(epi: int, BN: int, B: int, T: int, a: torch.Tensor, w: torch.Tensor, ou
     d.res_in, d.ld_res = _p(res), (res.shape[1] if res is not None else 0)
     d.out, d.ld_out, d.out_c0, d.n_real = out.data_ptr(), out.shape[-1], out_c0, n_real
     d.relu, d.scale = act, scale
+    d.out2, d.slope2 = _p(out2), slope2
     nat.check(nat.lib().ds_gemm(C.byref(d), stream()))
 
 
@@ -95,6 +96,17 @@ def wgrad(out: torch.Tensor, pairs: Sequence[Tuple[torch.Tensor, torch.Tensor]],
         o.g_bf16, o.x_bf16 = g.data_ptr(), x.data_ptr()
         o.g_channels, o.g_batch_rows, o.x_channels, o.x_batch_rows = g.shape[1], g.shape[0] // T, x.shape[1], x.shape[0] // T
     nat.check(nat.lib().ds_wgrad(arr, len(pairs), T, B, BN, jobs.data_ptr(), jobs.numel() // WGRAD_JOB_BYTES, out.data_ptr(), stream()))
+
+
+def source_conv(y: torch.Tensor, src: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, channels: int, stride: int, pad: int):
+    """y[b, n, c] = bias[c] + sum_k w[c, k] * src[b, n * stride + k - pad]; y bf16 [B, n_out, ld], src fp32 [B, n_src], w fp32 [channels, k]."""
+    B, n_out, ld = y.shape
+    nat.check(nat.lib().ds_source_conv(y.data_ptr(), src.data_ptr(), w.data_ptr(), bias.data_ptr(), B, src.shape[1], n_out, channels, ld,
+                                       w.shape[1], stride, pad, stream()))
+
+
+def mean3_lrelu(y: torch.Tensor, a: torch.Tensor, b: torch.Tensor, c: torch.Tensor, slope: float):
+    nat.check(nat.lib().ds_mean3_lrelu(y.data_ptr(), a.data_ptr(), b.data_ptr(), c.data_ptr(), y.numel(), slope, stream()))
 
 
 def layernorm(y: torch.Tensor, x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float = 1e-5,

@@ -1,0 +1,333 @@
+"""NSF-HiFiGAN generator on the native kernels (the vocoder right after the sampling loop).
+
+Drop-in for the reference's ``modules/nsf_hifigan/models.py:206-302`` (``Generator``) and ``modules/vocoders/nsf_hifigan.py``
+(``NsfHifiGAN.spec2wav_torch``): same sub-module / parameter names, so a reference checkpoint's ``generator`` state dict
+loads unchanged (weight-norm ``weight_g`` / ``weight_v`` pairs are folded on load), same ``forward(x[B, mels, T], f0[B, T])
+-> [B, 1, T * hop]``.  Supported configuration: ``resblock == '1'``, ``mini_nsf == False`` (the published 44.1 kHz models).
+
+Native path (no-grad, CUDA), time-major bf16 activations ``[B][T_s][channels padded to 64]`` at every sample rate T_s:
+
+    conv_pre (k = 7)                     7-tap implicit GEMM, LeakyReLU(0.1) epilogue                        models.py:279,284
+    per upsampling stage (rate u):
+      ConvTranspose1d(k = 2u, stride u)  ONE 3-tap GEMM with N = u * C_out: output phase r of frame t reads frames
+                                         t-1, t, t+1 (polyphase form), so the [T][u * C_out] result IS the [T * u][C_out]
+                                         activation of the next rate; epilogue adds the bias and the source branch and
+                                         writes both x and LeakyReLU(x)                                         :285-289
+      noise_convs[i](har_source)         ds_source_conv (1 input channel: a streaming kernel)                 :237-241,288
+      3 ResBlock1 (k = 3, 7, 11; 3 x {dilated conv, conv}):  k-tap GEMMs; conv1 with LeakyReLU epilogue, conv2 with the
+                                         residual epilogue writing x and LeakyReLU(x)                          :35-67
+      mean of the three + next LeakyReLU ds_mean3_lrelu                                                        :290-295
+    conv_post (k = 7) + tanh             7-tap GEMM, fp32 output epilogue with tanh                            :296-298
+
+The harmonic source (``SineGen`` / ``SourceModuleHnNSF``, models.py:99-203: 9 sines per sample, elementwise + one cumsum
+over frames) is evaluated with torch ops on the device; its random initial phases and noise come from the global torch
+generator like the reference's, or are injected (``rand_ini=``, ``noise=``) for parity tests.  With autograd enabled, or on
+CPU tensors, the forward is the plain differentiable torch-op composition (fine-tuning; also the eager baseline timed by
+tools/vocoder_bench.py).
+"""
+from __future__ import annotations
+
+import json
+import math
+import pathlib
+from typing import Dict, List, Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import _native as nat
+from . import ops
+
+LRELU_SLOPE = 0.1
+_pad64 = ops.pad64
+
+DEFAULT_CONFIG = dict(
+    sampling_rate=44100, num_mels=128, hop_size=512, n_fft=2048, win_size=2048, fmin=40, fmax=16000,
+    upsample_rates=[8, 8, 2, 2, 2], upsample_kernel_sizes=[16, 16, 4, 4, 4], upsample_initial_channel=512,
+    resblock='1', resblock_kernel_sizes=[3, 7, 11], resblock_dilation_sizes=[[1, 3, 5], [1, 3, 5], [1, 3, 5]],
+    mini_nsf=False, noise_sigma=None,
+)
+
+
+class AttrDict(dict):
+    """Attribute access to the vocoder's config.json; missing keys read as None (reference modules/nsf_hifigan/env.py)."""
+
+    def __getattr__(self, name):
+        return self.get(name)
+
+    __setattr__ = dict.__setitem__
+
+
+def _same_pad(kernel_size, dilation=1):
+    return (kernel_size * dilation - dilation) // 2
+
+
+class ResBlock1(nn.Module):
+    def __init__(self, channels, kernel_size=3, dilation=(1, 3, 5)):
+        super().__init__()
+        self.kernel_size, self.dilation = kernel_size, tuple(dilation)
+        self.convs1 = nn.ModuleList([nn.Conv1d(channels, channels, kernel_size, 1, dilation=d, padding=_same_pad(kernel_size, d))
+                                     for d in dilation])
+        self.convs2 = nn.ModuleList([nn.Conv1d(channels, channels, kernel_size, 1, dilation=1, padding=_same_pad(kernel_size, 1))
+                                     for _ in dilation])
+        for c in list(self.convs1) + list(self.convs2):
+            c.weight.data.normal_(0.0, 0.01)
+
+    def forward(self, x):
+        for c1, c2 in zip(self.convs1, self.convs2):
+            x = c2(F.leaky_relu(c1(F.leaky_relu(x, LRELU_SLOPE)), LRELU_SLOPE)) + x
+        return x
+
+
+class HarmonicSource(nn.Module):
+    """f0 -> one excitation channel at the output rate (reference SineGen + SourceModuleHnNSF, models.py:99-203)."""
+
+    def __init__(self, sampling_rate, harmonic_num=8, sine_amp=0.1, noise_std=0.003, voiced_threshold=0.0):
+        super().__init__()
+        self.sampling_rate, self.dim = sampling_rate, harmonic_num + 1
+        self.sine_amp, self.noise_std, self.voiced_threshold = sine_amp, noise_std, voiced_threshold
+        self.l_linear = nn.Linear(self.dim, 1)
+
+    @torch.no_grad()
+    def sines(self, f0, upp, rand_ini=None, noise=None):
+        """f0 [B, T] -> [B, T * upp, dim]: harmonics k * f0 with phase continuity across frames, voiced/unvoiced mixing."""
+        B, T = f0.shape
+        f0 = f0.unsqueeze(-1)
+        dev = f0.device
+        cycles = f0 / self.sampling_rate * torch.arange(1, upp + 1, device=dev)               # [B, T, upp] within-frame phase
+        wrapped = torch.fmod(cycles[..., -1:].float() + 0.5, 1.0) - 0.5                        # per-frame advance in (-0.5, 0.5]
+        start = wrapped.cumsum(dim=1).fmod(1.0).to(f0)
+        cycles = cycles + F.pad(start[:, :-1, :], (0, 0, 1, 0))                                # phase at each frame's first sample
+        cycles = cycles.reshape(B, -1, 1) * torch.arange(1, self.dim + 1, device=dev).reshape(1, 1, -1)
+        if rand_ini is None:
+            rand_ini = torch.rand(1, 1, self.dim, device=dev)
+            rand_ini[..., 0] = 0
+        waves = torch.sin(2 * np.pi * (cycles + rand_ini.to(dev))) * self.sine_amp
+        uv = (f0 > self.voiced_threshold).float()
+        uv = F.interpolate(uv.transpose(2, 1), scale_factor=upp, mode='nearest').transpose(2, 1)
+        if noise is None:
+            noise = torch.randn_like(waves)
+        amp = uv * self.noise_std + (1 - uv) * self.sine_amp / 3
+        return waves * uv + amp * noise.to(dev)
+
+    def forward(self, f0, upp, rand_ini=None, noise=None):
+        return torch.tanh(self.l_linear(self.sines(f0, upp, rand_ini, noise)))                # [B, T * upp, 1]
+
+
+def _fold_weight_norm(state_dict, prefix, *_):
+    """load_state_dict pre-hook: a reference checkpoint stores weight-normed convs as (weight_g, weight_v)
+    (models.py:215,224,247 before remove_weight_norm); fold them into the plain ``weight`` this module keeps."""
+    for key in [k for k in state_dict if k.startswith(prefix) and k.endswith('.weight_g')]:
+        base = key[:-len('weight_g')]
+        g, v = state_dict.pop(key), state_dict.pop(base + 'weight_v')
+        norm = v.reshape(v.shape[0], -1).norm(dim=1).reshape(-1, *([1] * (v.dim() - 1)))
+        state_dict[base + 'weight'] = v * (g / norm)
+
+
+class Generator(nn.Module):
+    def __init__(self, h):
+        super().__init__()
+        h = AttrDict(h)
+        if str(h.resblock) != '1' or h.mini_nsf:
+            raise NotImplementedError("diffsinger_b200.vocoder supports resblock == '1' and mini_nsf == False")
+        self.h = h
+        self.num_kernels, self.num_upsamples = len(h.resblock_kernel_sizes), len(h.upsample_rates)
+        if self.num_kernels != 3:
+            raise NotImplementedError("the native path averages exactly three ResBlocks per stage")
+        self.noise_sigma = h.noise_sigma
+        self.upp = int(np.prod(h.upsample_rates))
+        self.m_source = HarmonicSource(h.sampling_rate, harmonic_num=8)
+        self.conv_pre = nn.Conv1d(h.num_mels, h.upsample_initial_channel, 7, 1, padding=3)
+        self.ups, self.resblocks, self.noise_convs = nn.ModuleList(), nn.ModuleList(), nn.ModuleList()
+        ch = h.upsample_initial_channel
+        for i, (u, k) in enumerate(zip(h.upsample_rates, h.upsample_kernel_sizes)):
+            ch //= 2
+            self.ups.append(nn.ConvTranspose1d(2 * ch, ch, k, u, padding=(k - u) // 2))
+            self.ups[-1].weight.data.normal_(0.0, 0.01)
+            for k_r, d_r in zip(h.resblock_kernel_sizes, h.resblock_dilation_sizes):
+                self.resblocks.append(ResBlock1(ch, k_r, d_r))
+            if i + 1 < self.num_upsamples:
+                s = int(np.prod(h.upsample_rates[i + 1:]))
+                self.noise_convs.append(nn.Conv1d(1, ch, kernel_size=s * 2, stride=s, padding=s // 2))
+            else:
+                self.noise_convs.append(nn.Conv1d(1, ch, kernel_size=1))
+        self.conv_post = nn.Conv1d(ch, 1, 7, 1, padding=3)
+        self.conv_post.weight.data.normal_(0.0, 0.01)
+        self._register_load_state_dict_pre_hook(_fold_weight_norm)
+        self._packed = None
+
+    def remove_weight_norm(self):  # kept for callers of the reference API: weights are stored folded already
+        return self
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, x, f0, rand_ini=None, noise=None):
+        """x [B, num_mels, T] (natural-log mel), f0 [B, T] (Hz, 0 = unvoiced) -> [B, 1, T * hop]."""
+        har = self.m_source(f0, self.upp, rand_ini, noise).transpose(1, 2)                    # [B, 1, T * upp]
+        if torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in self.parameters())) or not x.is_cuda:
+            return self._forward_torch(x, har)
+        return self._forward_native(x, har)
+
+    def _forward_torch(self, x, har_source):
+        x = self.conv_pre(x)
+        if self.noise_sigma is not None and self.noise_sigma > 0:
+            x = x + self.noise_sigma * torch.randn_like(x)
+        for i in range(self.num_upsamples):
+            x = self.ups[i](F.leaky_relu(x, LRELU_SLOPE)) + self.noise_convs[i](har_source)
+            x = sum(self.resblocks[i * self.num_kernels + j](x) for j in range(self.num_kernels)) / self.num_kernels
+        return torch.tanh(self.conv_post(F.leaky_relu(x)))
+
+    # ------------------------------------------------------------------ native path
+    @staticmethod
+    def _fingerprint(module) -> tuple:
+        return tuple((p.data_ptr(), p._version) for p in module.parameters())
+
+    @torch.no_grad()
+    def _pack(self):
+        """bf16 K-major GEMM matrices [rows][taps * K] with every channel count padded to a multiple of 64 (zero rows /
+        columns / biases, so padded channels stay exactly zero through LeakyReLU and the residual adds)."""
+        dev, bf = self.conv_pre.weight.device, torch.bfloat16
+
+        def conv_matrix(w, rows_p, cin_p):                        # Conv1d weight [cout, cin, k] -> [rows_p][k * cin_p]
+            cout, cin, k = w.shape
+            m = torch.zeros(rows_p, k, cin_p, dtype=torch.float32, device=dev)
+            m[:cout, :, :cin] = w.detach().float().permute(0, 2, 1)
+            return m.reshape(rows_p, k * cin_p).to(bf).contiguous()
+
+        def padded(v, n):
+            out = torch.zeros(n, dtype=torch.float32, device=dev)
+            out[:v.numel()] = v.detach().float()
+            return out
+
+        h = self.h
+        c0 = h.upsample_initial_channel
+        P = dict(mel_p=_pad64(h.num_mels), c0_p=_pad64(c0))
+        P["w_pre"], P["b_pre"] = conv_matrix(self.conv_pre.weight, P["c0_p"], P["mel_p"]), padded(self.conv_pre.bias, P["c0_p"])
+        stages, ch = [], c0
+        for i, (u, k) in enumerate(zip(h.upsample_rates, h.upsample_kernel_sizes)):
+            cin, ch = ch, ch // 2
+            cin_p, ch_p, pad = _pad64(cin), _pad64(ch), (k - u) // 2
+            if (k - u) % 2 or k > 2 * u + pad or pad > u:
+                raise NotImplementedError(f"ConvTranspose1d(kernel {k}, stride {u}) is outside the 3-tap polyphase form")
+            # polyphase ConvTranspose1d: out[t * u + r] = sum_{dt in -1, 0, 1} W[:, :, (-dt) * u + r + pad]^T a[t + dt]
+            wt = self.ups[i].weight.detach().float()                                           # [cin, cout, k]
+            m = torch.zeros(u, ch_p, 3, cin_p, dtype=torch.float32, device=dev)
+            for r in range(u):
+                for tap, dt in enumerate((-1, 0, 1)):
+                    kk = -dt * u + r + pad
+                    if 0 <= kk < k:
+                        m[r, :ch, tap, :cin] = wt[:, :, kk].t()
+            st = dict(u=u, cin_p=cin_p, ch=ch, ch_p=ch_p,
+                      w_up=m.reshape(u * ch_p, 3 * cin_p).to(bf).contiguous(), b_up=padded(self.ups[i].bias, ch_p).repeat(u).contiguous(),
+                      w_src=self.noise_convs[i].weight.detach().float()[:, 0, :].contiguous(), b_src=self.noise_convs[i].bias.detach().float().contiguous(),
+                      src_stride=self.noise_convs[i].stride[0], src_pad=self.noise_convs[i].padding[0], blocks=[])
+            for j in range(self.num_kernels):
+                rb = self.resblocks[i * self.num_kernels + j]
+                st["blocks"].append(dict(k=rb.kernel_size, dil=rb.dilation,
+                                         w1=[conv_matrix(c.weight, ch_p, ch_p) for c in rb.convs1], b1=[padded(c.bias, ch_p) for c in rb.convs1],
+                                         w2=[conv_matrix(c.weight, ch_p, ch_p) for c in rb.convs2], b2=[padded(c.bias, ch_p) for c in rb.convs2]))
+            stages.append(st)
+        P["stages"] = stages
+        P["w_post"], P["b_post"] = conv_matrix(self.conv_post.weight, 64, _pad64(ch)), padded(self.conv_post.bias, 64)
+        P["key"] = self._fingerprint(self)
+        self._packed = P
+        return P
+
+    @torch.no_grad()
+    def _forward_native(self, x, har_source):
+        nat.require_device()
+        if self.noise_sigma is not None and self.noise_sigma > 0:
+            raise NotImplementedError("noise_sigma > 0 is not supported on the native path")
+        P = self._packed
+        if P is None or P["key"] != self._fingerprint(self) or P["w_pre"].device != x.device:
+            P = self._pack()
+        B, M, T = x.shape
+        dev, bf = x.device, torch.bfloat16
+        src = har_source.reshape(B, -1).float().contiguous()                                   # [B, T * upp]
+        mel = torch.empty(B * T, P["mel_p"], dtype=bf, device=dev)
+        ops.cast_bf16(mel, x.transpose(1, 2).float().contiguous().view(B * T, M))
+        a = torch.empty(B * T, P["c0_p"], dtype=bf, device=dev)                                # LeakyReLU(conv_pre(x))
+        ops.gemm(ops.EPI_LINEAR, ops.tile_n(P["c0_p"]), B, T, mel, P["w_pre"], a, n_taps=7, bias=P["b_pre"], act=ops.ACT_LRELU,
+                 slope2=LRELU_SLOPE)
+        launches, Ts = 2, T
+        for i, st in enumerate(P["stages"]):
+            u, cp = st["u"], st["ch_p"]
+            Tn = Ts * u
+            mk = lambda: torch.empty(B * Tn, cp, dtype=bf, device=dev)
+            xs, X, XA, T1 = mk(), mk(), mk(), mk()
+            ops.source_conv(xs.view(B, Tn, cp), src, st["w_src"], st["b_src"], st["ch"], st["src_stride"], st["src_pad"])
+            # transposed conv: [B * Ts][u * cp] == [B * Tn][cp]; + bias + source branch; x and LeakyReLU(x)
+            ops.gemm(ops.EPI_RES, ops.tile_n(u * cp), B, Ts, a, st["w_up"], X.view(B * Ts, u * cp), n_taps=3, vec=st["b_up"],
+                     vec_bstride=0, res=xs.view(B * Ts, u * cp), out2=XA.view(B * Ts, u * cp), slope2=LRELU_SLOPE)
+            launches += 2
+            bn = ops.tile_n(cp)
+            finals = []
+            for blk in st["blocks"]:
+                Fx, FA = mk(), mk()
+                src_x, src_a = X, XA
+                for m_i, d in enumerate(blk["dil"]):
+                    ops.gemm(ops.EPI_LINEAR, bn, B, Tn, src_a, blk["w1"][m_i], T1, n_taps=blk["k"], dil=d, bias=blk["b1"][m_i],
+                             act=ops.ACT_LRELU, slope2=LRELU_SLOPE)
+                    last = m_i + 1 == len(blk["dil"])
+                    ops.gemm(ops.EPI_RES, bn, B, Tn, T1, blk["w2"][m_i], Fx, n_taps=blk["k"], vec=blk["b2"][m_i], vec_bstride=0,
+                             res=src_x, out2=None if last else FA, slope2=LRELU_SLOPE)
+                    src_x, src_a = Fx, FA
+                    launches += 2
+                finals.append(Fx)
+            a = XA  # reuse: the stage's activated input is dead once the three blocks have run
+            ops.mean3_lrelu(a, finals[0], finals[1], finals[2], LRELU_SLOPE if i + 1 < self.num_upsamples else 0.01)
+            launches += 1
+            Ts = Tn
+        out = torch.empty(B * Ts, 4, dtype=torch.float32, device=dev)                          # fp32 epilogue stores 4-wide; column 0 is real
+        ops.gemm(ops.EPI_OUTF32, 64, B, Ts, a, P["w_post"], out, n_taps=7, bias=P["b_post"], act=ops.ACT_TANH, n_real=1)
+        self.last_launches = launches + 1
+        return out[:, 0].reshape(B, 1, Ts)
+
+
+def load_model(model_path, device='cpu'):
+    """Reference ``load_model`` (models.py:18-33): config.json beside the checkpoint, ``generator`` state dict inside it."""
+    model_path = pathlib.Path(model_path)
+    with open(model_path.with_name('config.json')) as f:
+        h = AttrDict(json.load(f))
+    gen = Generator(h)
+    gen.load_state_dict(torch.load(model_path, map_location='cpu')['generator'])
+    return gen.eval().to(device), h
+
+
+class NsfHifiGAN:
+    """Reference ``modules/vocoders/nsf_hifigan.py:NsfHifiGAN`` (registry name ``'NsfHifiGAN'``): ``spec2wav_torch(mel, f0=)``."""
+
+    def __init__(self, model_path=None, generator: Optional[Generator] = None, mel_base=10):
+        if generator is None:
+            model_path = pathlib.Path(model_path)
+            if not model_path.exists():
+                raise FileNotFoundError(f"NSF-HiFiGAN vocoder model is not found at '{model_path}'.")
+            generator, _ = load_model(model_path)
+        self.model, self.h, self.mel_base = generator.eval(), generator.h, mel_base
+
+    @property
+    def device(self):
+        return next(self.model.parameters()).device
+
+    def to_device(self, device):
+        self.model.to(device)
+
+    def get_device(self):
+        return self.device
+
+    def spec2wav_torch(self, mel, **kwargs):  # mel [B, T, bins] -> flat waveform
+        with torch.no_grad():
+            c = mel.transpose(2, 1)
+            if self.mel_base != 'e':
+                assert self.mel_base in [10, '10'], "mel_base must be 'e', '10' or 10."
+                c = 2.30259 * c  # log10 -> ln
+            return self.model(c, kwargs['f0']).view(-1)
+
+    def spec2wav(self, mel, **kwargs):
+        dev = self.device
+        f0 = torch.as_tensor(kwargs['f0'], dtype=torch.float32, device=dev)[None, :]
+        return self.spec2wav_torch(torch.as_tensor(mel, dtype=torch.float32, device=dev)[None], f0=f0).cpu().numpy()
+
+
+VOCODERS = {'NsfHifiGAN': NsfHifiGAN, 'nsfhifigan': NsfHifiGAN}

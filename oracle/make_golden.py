@@ -231,9 +231,66 @@ def gen_aux_decoder(ref):
               **{"w." + k: v.numpy() for k, v in ad.state_dict().items()})
 
 
+NSF_SMALL = dict(sampling_rate=44100, num_mels=32, upsample_rates=[4, 2, 2], upsample_kernel_sizes=[8, 4, 4],
+                 upsample_initial_channel=64, resblock="1", resblock_kernel_sizes=[3, 7, 11],
+                 resblock_dilation_sizes=[[1, 3, 5], [1, 3, 5], [1, 3, 5]], mini_nsf=False, noise_sigma=None)
+
+
+def gen_nsf_hifigan(ref):
+    """NSF-HiFiGAN generator (modules/nsf_hifigan/models.py:206-302) with weight norm removed, and its source module with
+    the two random draws of SineGen recorded (torch.rand at :147, torch.randn_like at :166)."""
+    from modules.nsf_hifigan.models import Generator
+    from modules.nsf_hifigan.env import AttrDict
+    for tag, B, T in (("a", 2, 37), ("b", 1, 64)):
+        torch.manual_seed(500 + T)
+        gen = Generator(AttrDict(NSF_SMALL)).eval()
+        with torch.no_grad():  # the 0.01-std initialisers would make every conv a near no-op
+            for n, p in gen.named_parameters():
+                if n.endswith("weight_v") or (n.endswith("weight") and p.dim() == 3):
+                    p.mul_(6.0 if "ups" not in n else 3.0)
+        gen.remove_weight_norm()
+        mel = torch.randn(B, NSF_SMALL["num_mels"], T) * 2.0 - 4.0
+        f0 = 220.0 * torch.exp2(torch.rand(B, T) * 1.5)
+        f0[:, T // 3: T // 3 + 5] = 0.0  # an unvoiced stretch
+        draws = []
+        real_rand, real_randn_like = torch.rand, torch.randn_like
+
+        def rand(*a, **k):
+            draws.append(real_rand(*a, **k))
+            return draws[-1]
+
+        def randn_like(*a, **k):
+            draws.append(real_randn_like(*a, **k))
+            return draws[-1]
+
+        torch.rand, torch.randn_like = rand, randn_like
+        try:
+            with torch.no_grad():
+                wav = gen(mel, f0)
+        finally:
+            torch.rand, torch.randn_like = real_rand, real_randn_like
+        rand_ini, noise = draws[0].clone(), draws[1]
+        rand_ini[..., 0] = 0  # models.py:148 zeroes the fundamental's phase in place after the draw
+        with torch.no_grad():
+            torch.manual_seed(1)
+            har = None
+            real = gen.m_source.l_sin_gen._f02sine
+            torch.rand = lambda *a, **k: draws[0].clone()
+            torch.randn_like = lambda *a, **k: noise
+            try:
+                har = gen.m_source(f0, gen.upp).transpose(1, 2)
+            finally:
+                torch.rand, torch.randn_like = real_rand, real_randn_like
+        _save(f"nsf_hifigan_{tag}", mel=mel.numpy(), f0=f0.numpy(), rand_ini=rand_ini.numpy(), noise=noise.numpy(), har_source=har.numpy(),
+              wav=wav.numpy(), cfg_json=np.array(__import__("json").dumps(NSF_SMALL)),
+              **{"w." + k: v.numpy() for k, v in gen.state_dict().items()})
+
+
 def main():
     ref = load_reference()
     only = os.environ.get("GOLDEN_ONLY", "")
+    if not only or "nsf" in only:
+        gen_nsf_hifigan(ref)
     if not only or "auxdec" in only:
         gen_aux_decoder(ref)
     if not only or "lynxnet" in only:

@@ -49,3 +49,18 @@ def load_lynx_golden(name):
     cfg = dict(in_dims=M, n_feats=F, num_layers=L, num_channels=C, expansion_factor=ef, kernel_size=ks, hidden=H,
                strong_cond=bool(strong), activation=str(z["activation"]))
     return d, sd, cfg
+
+
+def load_nsf_golden(tag):
+    """-> (dict of tensors, state_dict, cfg dict) for a tests/golden/nsf_hifigan_*.npz fixture."""
+    import json
+    z = np.load(os.path.join(GOLDEN, f"nsf_hifigan_{tag}.npz"))
+    d = {k: torch.from_numpy(z[k]) for k in ("mel", "f0", "rand_ini", "noise", "har_source", "wav")}
+    sd = {k[2:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("w.")}
+    return d, sd, json.loads(str(z["cfg_json"]))
+
+
+def centered_rel_l2(a, b):
+    """rel-L2 of a - b against the VARIATION of b (outputs that sit on a large constant would flatter a plain rel-L2)."""
+    a, b = a.double(), b.double()
+    return float((a - b).norm() / (b - b.mean()).norm().clamp_min(1e-30))
