@@ -5,9 +5,11 @@ from .hparams import hparams, get_hparams
 from .backbones import BACKBONES, build_backbone, WaveNet, LYNXNet
 from .segments import sample_segments
 from .aux_decoder import AUX_DECODERS, AuxDecoderAdaptor, ConvNeXtDecoder, build_aux_decoder
+from .vocoder import VOCODERS, NsfHifiGAN
 from .core import (GaussianDiffusion, PitchDiffusion, MultiVarianceDiffusion,
                    RectifiedFlow, PitchRectifiedFlow, MultiVarianceRectifiedFlow)
 
 __all__ = ["hparams", "get_hparams", "BACKBONES", "build_backbone", "WaveNet", "LYNXNet", "GaussianDiffusion",
            "PitchDiffusion", "MultiVarianceDiffusion", "RectifiedFlow", "PitchRectifiedFlow",
-           "MultiVarianceRectifiedFlow", "sample_segments", "AUX_DECODERS", "AuxDecoderAdaptor", "ConvNeXtDecoder", "build_aux_decoder"]
+           "MultiVarianceRectifiedFlow", "sample_segments", "AUX_DECODERS", "AuxDecoderAdaptor", "ConvNeXtDecoder", "build_aux_decoder",
+           "VOCODERS", "NsfHifiGAN"]

@@ -138,7 +138,7 @@ def lib() -> C.CDLL:
     L.ds_wgrad.argtypes = [C.POINTER(WgradOperands), C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p,
                            C.c_void_p]
     L.ds_source_conv.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_int64, C.c_int32, C.c_int32,
-                                 C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
+                                 C.c_int32, C.c_int32, C.c_void_p]
     L.ds_mean3_lrelu.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p]
     L.ds_layernorm.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_float, C.c_void_p,
                                C.c_int64, C.c_void_p, C.c_void_p]

@@ -990,14 +990,14 @@ extern "C" int ds_gate_bwd(void* dz_bf16, int64_t ld_dz, const void* dy_bf16, in
 }
 
 extern "C" int ds_source_conv(void* y_bf16, const float* src, const float* w, const float* bias, int32_t B, int64_t n_src, int64_t n_out,
-                              int32_t channels, int32_t ld, int32_t kernel_size, int32_t stride, int32_t pad, void* stream) {
+                              int32_t ld, int32_t kernel_size, int32_t stride, int32_t pad, void* stream) {
   if (!y_bf16 || !src || !w || !bias || B <= 0 || n_src <= 0 || n_out <= 0) return fail(DS_ERR_INVALID, "ds_source_conv: bad argument");
-  if (channels <= 0 || ld < channels || ld % 8 || kernel_size <= 0 || kernel_size > 256 || stride <= 0 || pad < 0)
-    return fail(DS_ERR_INVALID, "ds_source_conv: bad shape");
+  if (ld <= 0 || ld % 8 || kernel_size <= 0 || stride <= 0 || pad < 0) return fail(DS_ERR_INVALID, "ds_source_conv: bad shape");
+  if (((uintptr_t)w | (uintptr_t)bias | (uintptr_t)y_bf16) & 15) return fail(DS_ERR_INVALID, "ds_source_conv: operands must be 16-byte aligned");
   DS_TRY(ensure_device());
   const long groups = (long)B * n_out * (ld / 8);
   source_conv_kernel<<<ew_grid(groups, 256), 256, 0, (cudaStream_t)stream>>>((__nv_bfloat16*)y_bf16, src, w, bias, B, (long)n_src,
-                                                                             (long)n_out, channels, ld, kernel_size, stride, pad);
+                                                                             (long)n_out, ld, kernel_size, stride, pad);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }

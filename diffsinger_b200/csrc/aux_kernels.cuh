@@ -467,11 +467,12 @@ __global__ void __launch_bounds__(256) gate_bwd_kernel(__nv_bfloat16* __restrict
 namespace dsb {
 
 // Conv1d(1 -> channels, k, stride, pad) over the single-channel harmonic source (nsf_hifigan/models.py:237-241, 281):
-// y[b][n][c] = bias[c] + sum_k w[c][k] * src[b][n * stride + k - pad].  One thread per (b, n, 8 channels); the k source
-// samples of a frame are shared by all its channel groups through L1.  Columns [channels, ld) are written as zeros.
+// y[b][n][c] = bias[c] + sum_k w[k][c] * src[b][n * stride + k - pad], w tap-major [k][ld] with zero columns >= channels.
+// One thread per (b, n, 8 channels): a warp covers consecutive channel groups of one output sample, so the source sample
+// is a broadcast load and the weight row a coalesced one.
 __global__ void __launch_bounds__(256) source_conv_kernel(__nv_bfloat16* __restrict__ y, const float* __restrict__ src,
                                                           const float* __restrict__ w, const float* __restrict__ bias, int B, long n_src,
-                                                          long n_out, int channels, int ld, int K, int stride, int pad) {
+                                                          long n_out, int ld, int K, int stride, int pad) {
   const int cg = ld / 8;
   const long total = (long)B * n_out * cg;
   for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -481,17 +482,19 @@ __global__ void __launch_bounds__(256) source_conv_kernel(__nv_bfloat16* __restr
     const long b = bn / n_out;
     const int c0 = g * 8;
     float acc[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = (c0 + j < channels) ? __ldg(bias + c0 + j) : 0.0f;
+    const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + c0)), b1 = __ldg(reinterpret_cast<const float4*>(bias + c0) + 1);
+    acc[0] = b0.x; acc[1] = b0.y; acc[2] = b0.z; acc[3] = b0.w; acc[4] = b1.x; acc[5] = b1.y; acc[6] = b1.z; acc[7] = b1.w;
     const float* sb = src + b * n_src;
     const long s0 = n * stride - pad;
-    for (int k = 0; k < K; ++k) {
-      const long si = s0 + k;
-      if (si < 0 || si >= n_src) continue;
-      const float sv = __ldg(sb + si);
-#pragma unroll
-      for (int j = 0; j < 8; ++j)
-        if (c0 + j < channels) acc[j] = fmaf(__ldg(w + (long)(c0 + j) * K + k), sv, acc[j]);
+    const int k_lo = s0 < 0 ? (int)(-s0) : 0;
+    const int k_hi = (s0 + K > n_src) ? (int)(n_src - s0) : K;
+#pragma unroll 4
+    for (int k = k_lo; k < k_hi; ++k) {
+      const float sv = __ldg(sb + s0 + k);
+      const float4 w0 = __ldg(reinterpret_cast<const float4*>(w + (long)k * ld + c0));
+      const float4 w1 = __ldg(reinterpret_cast<const float4*>(w + (long)k * ld + c0) + 1);
+      acc[0] = fmaf(w0.x, sv, acc[0]); acc[1] = fmaf(w0.y, sv, acc[1]); acc[2] = fmaf(w0.z, sv, acc[2]); acc[3] = fmaf(w0.w, sv, acc[3]);
+      acc[4] = fmaf(w1.x, sv, acc[4]); acc[5] = fmaf(w1.y, sv, acc[5]); acc[6] = fmaf(w1.z, sv, acc[6]); acc[7] = fmaf(w1.w, sv, acc[7]);
     }
     *reinterpret_cast<uint4*>(y + bn * ld + c0) = pack_bf16x8(acc);
   }

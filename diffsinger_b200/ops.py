@@ -98,11 +98,13 @@ def wgrad(out: torch.Tensor, pairs: Sequence[Tuple[torch.Tensor, torch.Tensor]],
     nat.check(nat.lib().ds_wgrad(arr, len(pairs), T, B, BN, jobs.data_ptr(), jobs.numel() // WGRAD_JOB_BYTES, out.data_ptr(), stream()))
 
 
-def source_conv(y: torch.Tensor, src: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, channels: int, stride: int, pad: int):
-    """y[b, n, c] = bias[c] + sum_k w[c, k] * src[b, n * stride + k - pad]; y bf16 [B, n_out, ld], src fp32 [B, n_src], w fp32 [channels, k]."""
+def source_conv(y: torch.Tensor, src: torch.Tensor, w_t: torch.Tensor, bias: torch.Tensor, stride: int, pad: int):
+    """y[b, n, c] = bias[c] + sum_k w_t[k, c] * src[b, n * stride + k - pad]; y bf16 [B, n_out, ld], src fp32 [B, n_src],
+    w_t fp32 [k, ld] (tap-major), bias fp32 [ld]."""
     B, n_out, ld = y.shape
-    nat.check(nat.lib().ds_source_conv(y.data_ptr(), src.data_ptr(), w.data_ptr(), bias.data_ptr(), B, src.shape[1], n_out, channels, ld,
-                                       w.shape[1], stride, pad, stream()))
+    assert w_t.shape[1] == ld and bias.numel() == ld
+    nat.check(nat.lib().ds_source_conv(y.data_ptr(), src.data_ptr(), w_t.data_ptr(), bias.data_ptr(), B, src.shape[1], n_out, ld,
+                                       w_t.shape[0], stride, pad, stream()))
 
 
 def mean3_lrelu(y: torch.Tensor, a: torch.Tensor, b: torch.Tensor, c: torch.Tensor, slope: float):

@@ -220,7 +220,8 @@ class Generator(nn.Module):
                         m[r, :ch, tap, :cin] = wt[:, :, kk].t()
             st = dict(u=u, cin_p=cin_p, ch=ch, ch_p=ch_p,
                       w_up=m.reshape(u * ch_p, 3 * cin_p).to(bf).contiguous(), b_up=padded(self.ups[i].bias, ch_p).repeat(u).contiguous(),
-                      w_src=self.noise_convs[i].weight.detach().float()[:, 0, :].contiguous(), b_src=self.noise_convs[i].bias.detach().float().contiguous(),
+                      w_src=F.pad(self.noise_convs[i].weight.detach().float()[:, 0, :].t(), (0, ch_p - ch)).contiguous(),  # [k][ch_p]
+                      b_src=padded(self.noise_convs[i].bias, ch_p),
                       src_stride=self.noise_convs[i].stride[0], src_pad=self.noise_convs[i].padding[0], blocks=[])
             for j in range(self.num_kernels):
                 rb = self.resblocks[i * self.num_kernels + j]
@@ -256,7 +257,7 @@ class Generator(nn.Module):
             Tn = Ts * u
             mk = lambda: torch.empty(B * Tn, cp, dtype=bf, device=dev)
             xs, X, XA, T1 = mk(), mk(), mk(), mk()
-            ops.source_conv(xs.view(B, Tn, cp), src, st["w_src"], st["b_src"], st["ch"], st["src_stride"], st["src_pad"])
+            ops.source_conv(xs.view(B, Tn, cp), src, st["w_src"], st["b_src"], st["src_stride"], st["src_pad"])
             # transposed conv: [B * Ts][u * cp] == [B * Tn][cp]; + bias + source branch; x and LeakyReLU(x)
             ops.gemm(ops.EPI_RES, ops.tile_n(u * cp), B, Ts, a, st["w_up"], X.view(B * Ts, u * cp), n_taps=3, vec=st["b_up"],
                      vec_bstride=0, res=xs.view(B * Ts, u * cp), out2=XA.view(B * Ts, u * cp), slope2=LRELU_SLOPE)

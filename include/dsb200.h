@@ -163,12 +163,13 @@ int ds_dwconv(void* y_bf16, const void* x_bf16, const float* w, const float* bia
 /* fp32 [rows][cols] -> bf16 [rows][ld] (columns >= cols zero filled); cols, ld multiples of 4. */
 int ds_cast_bf16(void* dst_bf16, const float* src, int64_t rows, int32_t cols, int32_t ld, void* stream);
 /* NSF-HiFiGAN vocoder, streaming helpers around ds_gemm:
- *   ds_source_conv: y[b][n][c] = bias[c] + sum_k w[c][k] * src[b][n * stride + k - pad] (zero padded), c < channels; columns
- *     [channels, ld) zero -- the noise_convs Conv1d(1, ch, k, stride) over the harmonic source (nsf_hifigan/models.py:237-241, 281).
+ *   ds_source_conv: y[b][n][c] = bias[c] + sum_k w[k][c] * src[b][n * stride + k - pad] (zero padded), c < ld; w fp32 tap-major
+ *     [kernel_size][ld], bias fp32 [ld] (pad columns zero) -- the noise_convs Conv1d(1, ch, k, stride) over the harmonic source
+ *     (nsf_hifigan/models.py:237-241, 281).
  *   ds_mean3_lrelu: y = LeakyReLU((a + b + c) / 3, slope) -- the average of the three ResBlocks followed by the next
  *     stage's activation (models.py:286-294); n multiple of 8. */
 int ds_source_conv(void* y_bf16, const float* src, const float* w, const float* bias, int32_t B, int64_t n_src, int64_t n_out,
-                   int32_t channels, int32_t ld, int32_t kernel_size, int32_t stride, int32_t pad, void* stream);
+                   int32_t ld, int32_t kernel_size, int32_t stride, int32_t pad, void* stream);
 int ds_mean3_lrelu(void* y_bf16, const void* a_bf16, const void* b_bf16, const void* c_bf16, int64_t n, float slope, void* stream);
 /* Training path (ddpm.py:212-219 / reflow.py:36-41 under autograd).  z = [gate | filter] pre-activations of
  * one residual layer (wavenet.py:40), bf16 [rows][ld_z], plain channel order:
