@@ -23,7 +23,7 @@ EXPORTS = [
     "ds_plan_packed_bytes", "ds_plan_pack_weights", "ds_session_workspace_bytes", "ds_session_create",
     "ds_session_destroy", "ds_session_set_cond", "ds_session_set_times", "ds_session_forward",
     "ds_session_run", "ds_session_last_launches", "ds_lincomb", "ds_transpose", "ds_debug_gemm", "ds_debug_set_trace", "ds_debug_mma_rate",
-    "ds_debug_layer", "ds_plan_layer_mode", "ds_plan_precision", "ds_gemm", "ds_layernorm", "ds_dwconv", "ds_cast_bf16", "ds_gate_fwd", "ds_gate_bwd", "ds_wgrad", "ds_source_conv", "ds_mean3_lrelu",
+    "ds_debug_layer", "ds_plan_layer_mode", "ds_plan_precision", "ds_gemm", "ds_layernorm", "ds_dwconv", "ds_cast_bf16", "ds_gate_fwd", "ds_gate_bwd", "ds_wgrad", "ds_source_conv", "ds_mean3_lrelu", "ds_conv_small",
 ]
 
 
@@ -139,6 +139,8 @@ def lib() -> C.CDLL:
                            C.c_void_p]
     L.ds_source_conv.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_int64, C.c_int32, C.c_int32,
                                  C.c_int32, C.c_int32, C.c_void_p]
+    L.ds_conv_small.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
+                                C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_void_p]
     L.ds_mean3_lrelu.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p]
     L.ds_layernorm.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_float, C.c_void_p,
                                C.c_int64, C.c_void_p, C.c_void_p]

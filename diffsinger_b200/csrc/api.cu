@@ -20,6 +20,7 @@
 #include "layer4_kernel.cuh"
 #include "mma_bench.cuh"
 #include "wgrad_kernel.cuh"
+#include "conv_small_kernel.cuh"
 
 using namespace dsb;
 
@@ -1010,6 +1011,54 @@ extern "C" int ds_mean3_lrelu(void* y_bf16, const void* a_bf16, const void* b_bf
       (__nv_bfloat16*)y_bf16, (const __nv_bfloat16*)a_bf16, (const __nv_bfloat16*)b_bf16, (const __nv_bfloat16*)c_bf16, (long)n / 8, slope);
   CUDA_TRY(cudaGetLastError());
   return 0;
+}
+
+template <int CIN, int COUT>
+static int launch_conv_small_t(const ConvSmallParams& p, cudaStream_t st) {
+  static bool attr_done = false;
+  auto kern = ds_conv_small_kernel<CIN, COUT>;
+  if (!attr_done) {
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ConvSmallCfg<CIN, COUT>::kSmemBytes));
+    attr_done = true;
+  }
+  const int grid = p.total_tiles < g_num_sms ? p.total_tiles : g_num_sms;
+  kern<<<grid, kConvSmallThreads, ConvSmallCfg<CIN, COUT>::kSmemBytes, st>>>(p);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ds_conv_small(const void* x_bf16, int32_t c_in, const void* w_img_bf16, int32_t c_out, const float* bias, const void* res_bf16,
+                             void* out, void* out2_bf16, int32_t B, int32_t T, int32_t taps, int32_t dil, int32_t act, float slope,
+                             void* stream) {
+  if (!x_bf16 || !w_img_bf16 || !bias || !out || B <= 0 || T <= 0) return fail(DS_ERR_INVALID, "ds_conv_small: bad argument");
+  if (taps <= 0 || taps > kConvSmallMaxTaps || taps % 2 == 0 || dil <= 0) return fail(DS_ERR_INVALID, "ds_conv_small: taps=%d dil=%d unsupported", taps, dil);
+  const int rows = (128 + (taps - 1) * dil + 7) / 8 * 8;
+  if (rows > kConvSmallMaxRows) return fail(DS_ERR_INVALID, "ds_conv_small: halo of %d rows exceeds %d", rows, kConvSmallMaxRows);
+  if (act != 0 && act != 3 && act != 4) return fail(DS_ERR_INVALID, "ds_conv_small: bad activation %d", act);
+  if (((uintptr_t)x_bf16 | (uintptr_t)w_img_bf16 | (uintptr_t)out | (uintptr_t)res_bf16 | (uintptr_t)out2_bf16) & 15)
+    return fail(DS_ERR_INVALID, "ds_conv_small: operands must be 16-byte aligned");
+  DS_TRY(ensure_device());
+  ConvSmallParams p;
+  memset(&p, 0, sizeof(p));
+  {
+    cuuint64_t dims[3] = {(cuuint64_t)c_in, (cuuint64_t)T, (cuuint64_t)B};
+    cuuint64_t strides[2] = {(cuuint64_t)c_in * 2, (cuuint64_t)c_in * 2 * (cuuint64_t)T};
+    cuuint32_t box[3] = {8, (cuuint32_t)rows, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = g_encode(&p.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(x_bf16), dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(DS_ERR_CUDA, "cuTensorMapEncodeTiled(conv_small %dx%dx%d) -> %d", c_in, T, B, (int)r);
+  }
+  p.w = (const __nv_bfloat16*)w_img_bf16; p.bias = bias; p.res = (const __nv_bfloat16*)res_bf16;
+  p.out = out; p.out2 = (__nv_bfloat16*)out2_bf16;
+  p.T = T; p.B = B; p.taps = taps; p.dil = dil; p.rows = rows;
+  p.tiles_t = ceil_div(T, 128); p.total_tiles = B * p.tiles_t;
+  p.act = act; p.slope = slope;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (c_in == 32 && c_out == 32) return launch_conv_small_t<32, 32>(p, st);
+  if (c_in == 16 && c_out == 16) return launch_conv_small_t<16, 16>(p, st);
+  return fail(DS_ERR_INVALID, "ds_conv_small: no instantiation for %d -> %d channels", c_in, c_out);
 }
 
 template <int BN>

@@ -107,6 +107,20 @@ def source_conv(y: torch.Tensor, src: torch.Tensor, w_t: torch.Tensor, bias: tor
                                        w_t.shape[0], stride, pad, stream()))
 
 
+def conv_small_weights(w: torch.Tensor) -> torch.Tensor:
+    """Conv1d weight [c_out, c_in, k] -> the bf16 shared-memory image [k][c_in / 8][c_out][8] ds_conv_small reads."""
+    c_out, c_in, k = w.shape
+    return w.detach().float().permute(2, 1, 0).reshape(k, c_in // 8, 8, c_out).permute(0, 1, 3, 2).to(torch.bfloat16).contiguous()
+
+
+def conv_small(x: torch.Tensor, w_img: torch.Tensor, bias: torch.Tensor, out: torch.Tensor, B: int, T: int, dil: int = 1,
+               res: Optional[torch.Tensor] = None, out2: Optional[torch.Tensor] = None, act: int = ACT_NONE, slope: float = 0.0):
+    """out = act(conv_k(x) + bias + res) for c_in = c_out in {16, 32} (include/dsb200.h: ds_conv_small); x bf16 [B * T, c_in]."""
+    taps, _, c_out, _ = w_img.shape
+    nat.check(nat.lib().ds_conv_small(x.data_ptr(), x.shape[1], w_img.data_ptr(), c_out, bias.data_ptr(), _p(res), out.data_ptr(), _p(out2),
+                                      B, T, taps, dil, act, slope, stream()))
+
+
 def mean3_lrelu(y: torch.Tensor, a: torch.Tensor, b: torch.Tensor, c: torch.Tensor, slope: float):
     nat.check(nat.lib().ds_mean3_lrelu(y.data_ptr(), a.data_ptr(), b.data_ptr(), c.data_ptr(), y.numel(), slope, stream()))
 

@@ -170,6 +170,13 @@ int ds_cast_bf16(void* dst_bf16, const float* src, int64_t rows, int32_t cols, i
  *     stage's activation (models.py:286-294); n multiple of 8. */
 int ds_source_conv(void* y_bf16, const float* src, const float* w, const float* bias, int32_t B, int64_t n_src, int64_t n_out,
                    int32_t ld, int32_t kernel_size, int32_t stride, int32_t pad, void* stream);
+/* k-tap dilated Conv1d along time for narrow channel counts (c_in = c_out in {16, 32}; taps odd <= 11, 128 + (taps - 1) * dil
+ * <= 192): the 32- / 16-channel ResBlock convolutions, the last transposed conv in polyphase form and conv_post of the
+ * generator (models.py:35-67, 285-298).  x bf16 [B][T][c_in]; w_img bf16 [taps][c_in / 8][c_out][8] (w_img[k][p][n][j] =
+ * weight[n][8 p + j][k]); out = act(conv + bias + res) bf16 [B][T][c_out], out2 (optional) = LeakyReLU(out, slope);
+ * act: 0 none, 3 LeakyReLU(slope), 4 tanh with out = fp32 [B][T] holding output channel 0 only. */
+int ds_conv_small(const void* x_bf16, int32_t c_in, const void* w_img_bf16, int32_t c_out, const float* bias, const void* res_bf16,
+                  void* out, void* out2_bf16, int32_t B, int32_t T, int32_t taps, int32_t dil, int32_t act, float slope, void* stream);
 int ds_mean3_lrelu(void* y_bf16, const void* a_bf16, const void* b_bf16, const void* c_bf16, int64_t n, float slope, void* stream);
 /* Training path (ddpm.py:212-219 / reflow.py:36-41 under autograd).  z = [gate | filter] pre-activations of
  * one residual layer (wavenet.py:40), bf16 [rows][ld_z], plain channel order:

@@ -139,3 +139,37 @@ def test_wgrad_shifted_frame_reductions(BN, B, T):
         got = out[o:o + Cg * ld_out].view(Cg, ld_out)
         assert torch.isfinite(got).all()
         assert rel_l2(got, ref) < 1e-5
+
+
+@pytest.mark.parametrize("C", [16, 32])
+@pytest.mark.parametrize("taps,dil", [(3, 1), (7, 3), (11, 5), (11, 1), (3, 5)])
+def test_conv_small(C, taps, dil):
+    """ds_conv_small: narrow-channel k-tap dilated conv on tcgen05 (no-swizzle plane layout, one halo tile per 128 samples)
+    against F.conv1d on the same bf16-rounded operands; LeakyReLU, residual + activated copy, tanh-to-fp32 epilogues."""
+    from diffsinger_b200 import ops
+    torch.manual_seed(C * 100 + taps * 10 + dil)
+    B, T = 3, 517
+    x = _bf(B * T, C)
+    w = torch.randn(C, C, taps, device=dev) * (1.0 / (C * taps) ** 0.5)
+    bias = torch.randn(C, device=dev) * 0.1
+    res = _bf(B * T, C)
+    w_img = ops.conv_small_weights(w)
+    ref = F.conv1d(x.float().view(B, T, C).transpose(1, 2), w.to(torch.bfloat16).float(), bias, dilation=dil,
+                   padding=(taps // 2) * dil).transpose(1, 2).reshape(B * T, C)
+    # conv1 of a ResBlock: LeakyReLU epilogue
+    y = torch.empty_like(x)
+    ops.conv_small(x, w_img, bias, y, B, T, dil=dil, act=ops.ACT_LRELU, slope=0.1)
+    assert rel_l2(y.float(), F.leaky_relu(ref, 0.1)) < 4e-3
+    # conv2: residual + activated copy
+    y2 = torch.empty_like(x)
+    ops.conv_small(x, w_img, bias, y, B, T, dil=dil, res=res, out2=y2, slope=0.1)
+    assert rel_l2(y.float(), ref + res.float()) < 4e-3
+    assert rel_l2(y2.float(), F.leaky_relu(ref + res.float(), 0.1)) < 4e-3
+    # in place on the residual
+    r2 = res.clone()
+    ops.conv_small(x, w_img, bias, r2, B, T, dil=dil, res=r2)
+    assert rel_l2(r2.float(), ref + res.float()) < 4e-3
+    # conv_post: tanh of output channel 0 -> fp32 [B * T]
+    wav = torch.empty(B * T, device=dev)
+    ops.conv_small(x, w_img, bias, wav, B, T, dil=dil, act=ops.ACT_TANH)
+    assert rel_l2(wav, torch.tanh(ref[:, 0])) < 1e-3
