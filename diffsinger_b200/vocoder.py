@@ -5,7 +5,8 @@ Drop-in for the reference's ``modules/nsf_hifigan/models.py:206-302`` (``Generat
 loads unchanged (weight-norm ``weight_g`` / ``weight_v`` pairs are folded on load), same ``forward(x[B, mels, T], f0[B, T])
 -> [B, 1, T * hop]``.  Supported configuration: ``resblock == '1'``, ``mini_nsf == False`` (the published 44.1 kHz models).
 
-Native path (no-grad, CUDA), time-major bf16 activations ``[B][T_s][channels padded to 64]`` at every sample rate T_s:
+Native path (no-grad, CUDA), time-major bf16 activations ``[B][T_s][channels]`` at every sample rate T_s; channel counts are
+padded to a multiple of 64 for ds_gemm, except the 32- / 16-channel stages, which run unpadded through ds_conv_small:
 
     conv_pre (k = 7)                     7-tap implicit GEMM, LeakyReLU(0.1) epilogue                        models.py:279,284
     per upsampling stage (rate u):
@@ -29,6 +30,7 @@ from __future__ import annotations
 
 import json
 import math
+import os
 import pathlib
 from typing import Dict, List, Optional
 
@@ -183,10 +185,42 @@ class Generator(nn.Module):
     def _fingerprint(module) -> tuple:
         return tuple((p.data_ptr(), p._version) for p in module.parameters())
 
+    def _plan_widths(self):
+        """Stored channel width of every stage: the real count for the 16- / 32-channel stages ds_conv_small covers (when the
+        up-sampling into and out of them can hand over that layout), else padded to a multiple of 64 for ds_gemm."""
+        h = self.h
+        chans, ch = [], h.upsample_initial_channel
+        for _ in h.upsample_rates:
+            ch //= 2
+            chans.append(ch)
+        n = len(chans)
+        narrow = [False] * n
+        # ds_conv_small: odd kernels up to 11 taps whose halo tile (128 + (k - 1) * dilation rows) fits 192 rows
+        fits = all(k % 2 == 1 and k <= 11 and 128 + (k - 1) * max(d) <= 192
+                   for k, d in zip(h.resblock_kernel_sizes, h.resblock_dilation_sizes))
+        if os.environ.get("DSB200_VOC_NARROW", "1") == "0":  # debug: every stage on the 64-padded ds_gemm path
+            fits = False
+        for i, (u, c) in enumerate(zip(h.upsample_rates, chans)):
+            if not fits:
+                break
+            by_gemm = c in (16, 32) and (u * c) % 64 == 0 and (i == 0 or not narrow[i - 1])     # wide input, N = u * c
+            by_small = c == 16 and u * c == 32 and i > 0 and narrow[i - 1] and chans[i - 1] == 32   # 32 -> 2 x 16, 3 taps
+            narrow[i] = by_gemm or by_small
+        changed = True
+        while changed:  # a narrow stage must be consumed by a narrow one (or be the last); undo chains that are not
+            changed = False
+            for i in range(n):
+                if narrow[i] and i + 1 < n and not narrow[i + 1]:
+                    narrow[i], changed = False, True
+                if narrow[i] and i > 0 and not narrow[i - 1] and not (chans[i] in (16, 32) and (h.upsample_rates[i] * chans[i]) % 64 == 0):
+                    narrow[i], changed = False, True
+        return chans, narrow
+
     @torch.no_grad()
     def _pack(self):
-        """bf16 K-major GEMM matrices [rows][taps * K] with every channel count padded to a multiple of 64 (zero rows /
-        columns / biases, so padded channels stay exactly zero through LeakyReLU and the residual adds)."""
+        """bf16 weight images.  Wide stages: K-major GEMM matrices [rows][taps * K] with channel counts padded to a multiple
+        of 64 (zero rows / columns / biases, so padded channels stay exactly zero through LeakyReLU and the residual adds).
+        Narrow stages (16 / 32 channels): ds_conv_small images [taps][C / 8][C][8], no padding."""
         dev, bf = self.conv_pre.weight.device, torch.bfloat16
 
         def conv_matrix(w, rows_p, cin_p):                        # Conv1d weight [cout, cin, k] -> [rows_p][k * cin_p]
@@ -202,35 +236,46 @@ class Generator(nn.Module):
 
         h = self.h
         c0 = h.upsample_initial_channel
+        chans, narrow = self._plan_widths()
         P = dict(mel_p=_pad64(h.num_mels), c0_p=_pad64(c0))
         P["w_pre"], P["b_pre"] = conv_matrix(self.conv_pre.weight, P["c0_p"], P["mel_p"]), padded(self.conv_pre.bias, P["c0_p"])
-        stages, ch = [], c0
+        stages, cin, cin_w = [], c0, P["c0_p"]
         for i, (u, k) in enumerate(zip(h.upsample_rates, h.upsample_kernel_sizes)):
-            cin, ch = ch, ch // 2
-            cin_p, ch_p, pad = _pad64(cin), _pad64(ch), (k - u) // 2
+            ch = chans[i]
+            ch_w, pad = (ch if narrow[i] else _pad64(ch)), (k - u) // 2
             if (k - u) % 2 or k > 2 * u + pad or pad > u:
                 raise NotImplementedError(f"ConvTranspose1d(kernel {k}, stride {u}) is outside the 3-tap polyphase form")
             # polyphase ConvTranspose1d: out[t * u + r] = sum_{dt in -1, 0, 1} W[:, :, (-dt) * u + r + pad]^T a[t + dt]
             wt = self.ups[i].weight.detach().float()                                           # [cin, cout, k]
-            m = torch.zeros(u, ch_p, 3, cin_p, dtype=torch.float32, device=dev)
+            m = torch.zeros(u, ch_w, 3, cin_w, dtype=torch.float32, device=dev)
             for r in range(u):
                 for tap, dt in enumerate((-1, 0, 1)):
                     kk = -dt * u + r + pad
                     if 0 <= kk < k:
                         m[r, :ch, tap, :cin] = wt[:, :, kk].t()
-            st = dict(u=u, cin_p=cin_p, ch=ch, ch_p=ch_p,
-                      w_up=m.reshape(u * ch_p, 3 * cin_p).to(bf).contiguous(), b_up=padded(self.ups[i].bias, ch_p).repeat(u).contiguous(),
-                      w_src=F.pad(self.noise_convs[i].weight.detach().float()[:, 0, :].t(), (0, ch_p - ch)).contiguous(),  # [k][ch_p]
-                      b_src=padded(self.noise_convs[i].bias, ch_p),
+            up_small = narrow[i] and cin_w == 32                                               # 32 -> u * ch = 32 columns
+            st = dict(u=u, ch=ch, ch_w=ch_w, narrow=narrow[i], up_small=up_small,
+                      w_up=(ops.conv_small_weights(m.reshape(u * ch_w, 3, cin_w).permute(0, 2, 1)) if up_small
+                            else m.reshape(u * ch_w, 3 * cin_w).to(bf).contiguous()),
+                      b_up=padded(self.ups[i].bias, ch_w).repeat(u).contiguous(),
+                      w_src=F.pad(self.noise_convs[i].weight.detach().float()[:, 0, :].t(), (0, ch_w - ch)).contiguous(),  # [k][ch_w]
+                      b_src=padded(self.noise_convs[i].bias, ch_w),
                       src_stride=self.noise_convs[i].stride[0], src_pad=self.noise_convs[i].padding[0], blocks=[])
             for j in range(self.num_kernels):
                 rb = self.resblocks[i * self.num_kernels + j]
+                wfn = ops.conv_small_weights if narrow[i] else (lambda w: conv_matrix(w, ch_w, ch_w))
                 st["blocks"].append(dict(k=rb.kernel_size, dil=rb.dilation,
-                                         w1=[conv_matrix(c.weight, ch_p, ch_p) for c in rb.convs1], b1=[padded(c.bias, ch_p) for c in rb.convs1],
-                                         w2=[conv_matrix(c.weight, ch_p, ch_p) for c in rb.convs2], b2=[padded(c.bias, ch_p) for c in rb.convs2]))
+                                         w1=[wfn(c.weight) for c in rb.convs1], b1=[padded(c.bias, ch_w) for c in rb.convs1],
+                                         w2=[wfn(c.weight) for c in rb.convs2], b2=[padded(c.bias, ch_w) for c in rb.convs2]))
             stages.append(st)
+            cin, cin_w = ch, ch_w
         P["stages"] = stages
-        P["w_post"], P["b_post"] = conv_matrix(self.conv_post.weight, 64, _pad64(ch)), padded(self.conv_post.bias, 64)
+        if stages[-1]["narrow"]:  # output channel 0 is the waveform; rows 1.. of the image are zero
+            w_post = torch.zeros(cin_w, cin_w, 7, dtype=torch.float32, device=dev)
+            w_post[:1] = self.conv_post.weight.detach().float()
+            P["w_post"], P["b_post"] = ops.conv_small_weights(w_post), padded(self.conv_post.bias, cin_w)
+        else:
+            P["w_post"], P["b_post"] = conv_matrix(self.conv_post.weight, 64, cin_w), padded(self.conv_post.bias, 64)
         P["key"] = self._fingerprint(self)
         self._packed = P
         return P
@@ -253,26 +298,34 @@ class Generator(nn.Module):
                  slope2=LRELU_SLOPE)
         launches, Ts = 2, T
         for i, st in enumerate(P["stages"]):
-            u, cp = st["u"], st["ch_p"]
+            u, cw, narrow = st["u"], st["ch_w"], st["narrow"]
             Tn = Ts * u
-            mk = lambda: torch.empty(B * Tn, cp, dtype=bf, device=dev)
+            mk = lambda: torch.empty(B * Tn, cw, dtype=bf, device=dev)
             xs, X, XA, T1 = mk(), mk(), mk(), mk()
-            ops.source_conv(xs.view(B, Tn, cp), src, st["w_src"], st["b_src"], st["src_stride"], st["src_pad"])
-            # transposed conv: [B * Ts][u * cp] == [B * Tn][cp]; + bias + source branch; x and LeakyReLU(x)
-            ops.gemm(ops.EPI_RES, ops.tile_n(u * cp), B, Ts, a, st["w_up"], X.view(B * Ts, u * cp), n_taps=3, vec=st["b_up"],
-                     vec_bstride=0, res=xs.view(B * Ts, u * cp), out2=XA.view(B * Ts, u * cp), slope2=LRELU_SLOPE)
+            ops.source_conv(xs.view(B, Tn, cw), src, st["w_src"], st["b_src"], st["src_stride"], st["src_pad"])
+            # transposed conv: [B * Ts][u * cw] == [B * Tn][cw]; + bias + source branch; x and LeakyReLU(x)
+            if st["up_small"]:
+                ops.conv_small(a, st["w_up"], st["b_up"], X, B, Ts, res=xs, out2=XA, slope=LRELU_SLOPE)
+            else:
+                ops.gemm(ops.EPI_RES, ops.tile_n(u * cw), B, Ts, a, st["w_up"], X.view(B * Ts, u * cw), n_taps=3, vec=st["b_up"],
+                         vec_bstride=0, res=xs.view(B * Ts, u * cw), out2=XA.view(B * Ts, u * cw), slope2=LRELU_SLOPE)
             launches += 2
-            bn = ops.tile_n(cp)
             finals = []
             for blk in st["blocks"]:
                 Fx, FA = mk(), mk()
                 src_x, src_a = X, XA
                 for m_i, d in enumerate(blk["dil"]):
-                    ops.gemm(ops.EPI_LINEAR, bn, B, Tn, src_a, blk["w1"][m_i], T1, n_taps=blk["k"], dil=d, bias=blk["b1"][m_i],
-                             act=ops.ACT_LRELU, slope2=LRELU_SLOPE)
                     last = m_i + 1 == len(blk["dil"])
-                    ops.gemm(ops.EPI_RES, bn, B, Tn, T1, blk["w2"][m_i], Fx, n_taps=blk["k"], vec=blk["b2"][m_i], vec_bstride=0,
-                             res=src_x, out2=None if last else FA, slope2=LRELU_SLOPE)
+                    if narrow:
+                        ops.conv_small(src_a, blk["w1"][m_i], blk["b1"][m_i], T1, B, Tn, dil=d, act=ops.ACT_LRELU, slope=LRELU_SLOPE)
+                        ops.conv_small(T1, blk["w2"][m_i], blk["b2"][m_i], Fx, B, Tn, res=src_x, out2=None if last else FA,
+                                       slope=LRELU_SLOPE)
+                    else:
+                        bn = ops.tile_n(cw)
+                        ops.gemm(ops.EPI_LINEAR, bn, B, Tn, src_a, blk["w1"][m_i], T1, n_taps=blk["k"], dil=d, bias=blk["b1"][m_i],
+                                 act=ops.ACT_LRELU, slope2=LRELU_SLOPE)
+                        ops.gemm(ops.EPI_RES, bn, B, Tn, T1, blk["w2"][m_i], Fx, n_taps=blk["k"], vec=blk["b2"][m_i], vec_bstride=0,
+                                 res=src_x, out2=None if last else FA, slope2=LRELU_SLOPE)
                     src_x, src_a = Fx, FA
                     launches += 2
                 finals.append(Fx)
@@ -280,9 +333,13 @@ class Generator(nn.Module):
             ops.mean3_lrelu(a, finals[0], finals[1], finals[2], LRELU_SLOPE if i + 1 < self.num_upsamples else 0.01)
             launches += 1
             Ts = Tn
+        self.last_launches = launches + 1
+        if P["stages"][-1]["narrow"]:
+            wav = torch.empty(B * Ts, dtype=torch.float32, device=dev)
+            ops.conv_small(a, P["w_post"], P["b_post"], wav, B, Ts, act=ops.ACT_TANH)
+            return wav.reshape(B, 1, Ts)
         out = torch.empty(B * Ts, 4, dtype=torch.float32, device=dev)                          # fp32 epilogue stores 4-wide; column 0 is real
         ops.gemm(ops.EPI_OUTF32, 64, B, Ts, a, P["w_post"], out, n_taps=7, bias=P["b_post"], act=ops.ACT_TANH, n_real=1)
-        self.last_launches = launches + 1
         return out[:, 0].reshape(B, 1, Ts)
 
 

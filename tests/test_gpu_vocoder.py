@@ -65,3 +65,36 @@ def test_spec2wav_torch_wrapper():
     f0 = torch.full((1, 30), 261.6, device="cuda")
     y = voc.spec2wav_torch(mel, f0=f0)
     assert y.shape == (30 * 512,) and torch.isfinite(y).all() and float(y.abs().max()) <= 1.0
+
+
+@pytest.mark.parametrize("c0,rates,ks", [(256, [4, 2, 2], [8, 4, 4]), (128, [4, 2, 2], [8, 4, 4])])
+def test_native_generator_narrow_stage_plans(c0, rates, ks, monkeypatch):
+    """Stage-width planning: (256 -> 128, 64, 32): last stage narrow through the GEMM up-sampler; (128 -> 64, 32, 16): the last
+    two narrow, the final up-sampling through ds_conv_small; conv_post narrow in both."""
+    from diffsinger_b200.vocoder import DEFAULT_CONFIG, Generator
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(c0)
+    cfg = dict(DEFAULT_CONFIG, upsample_initial_channel=c0, upsample_rates=rates, upsample_kernel_sizes=ks, num_mels=64)
+    gen = Generator(cfg).eval()
+    assert gen._plan_widths()[1] == ([False, False, True] if c0 == 256 else [False, True, True])
+    with torch.no_grad():
+        for n, p in gen.named_parameters():
+            if p.dim() == 3 and "noise_convs" not in n and "conv_pre" not in n:
+                p.mul_(3.0 if "ups" in n else 5.0)
+    gen = gen.cuda()
+    B, T, upp = 2, 50, 16
+    mel = torch.randn(B, 64, T, device="cuda") * 2.0 - 4.0
+    f0 = 220.0 * torch.exp2(torch.rand(B, T, device="cuda"))
+    rand_ini = torch.zeros(1, 1, 9, device="cuda")
+    noise = torch.randn(B, T * upp, 9, device="cuda")
+    with torch.no_grad():
+        wav = gen(mel, f0, rand_ini=rand_ini, noise=noise)
+        ref = gen._forward_torch(mel, gen.m_source(f0, gen.upp, rand_ini, noise).transpose(1, 2))
+        monkeypatch.setenv("DSB200_VOC_NARROW", "0")  # the same network with every stage on the 64-padded GEMM path
+        gen._packed = None
+        wide = gen(mel, f0, rand_ini=rand_ini, noise=noise)
+    err, err_wide, mutual = centered_rel_l2(wav, ref), centered_rel_l2(wide, ref), centered_rel_l2(wav, wide)
+    print(f"nsf-hifigan c0={c0}: centered rel-L2 narrow {err:.3e}, padded {err_wide:.3e}, narrow vs padded {mutual:.3e}")
+    # three stages with 5x-amplified weights: looser than the published configuration, but both layouts must agree
+    assert wav.shape == ref.shape and err < 5e-2 and err_wide < 5e-2 and mutual < 3e-2
