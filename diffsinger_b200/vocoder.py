@@ -159,9 +159,23 @@ class Generator(nn.Module):
         self.conv_post.weight.data.normal_(0.0, 0.01)
         self._register_load_state_dict_pre_hook(_fold_weight_norm)
         self._packed = None
+        self._graphs = {}
 
     def remove_weight_norm(self):  # kept for callers of the reference API: weights are stored folded already
         return self
+
+    def __deepcopy__(self, memo):  # packed weights and captured graphs are per-instance caches, rebuilt on first use
+        import copy
+        new = self.__class__.__new__(self.__class__)
+        memo[id(self)] = new
+        for k, v in self.__dict__.items():
+            new.__dict__[k] = (None if k == '_packed' else {}) if k in ('_packed', '_graphs') else copy.deepcopy(v, memo)
+        return new
+
+    def __getstate__(self):
+        d = self.__dict__.copy()
+        d['_packed'], d['_graphs'] = None, {}
+        return d
 
     # ------------------------------------------------------------------ forward
     def forward(self, x, f0, rand_ini=None, noise=None):
@@ -280,19 +294,49 @@ class Generator(nn.Module):
         self._packed = P
         return P
 
+    MAX_GRAPHS = 8
+
     @torch.no_grad()
     def _forward_native(self, x, har_source):
+        """The ~110 kernel launches of one call are captured in a CUDA graph per (B, T) (static input / output buffers,
+        activations from the graph's private pool) and replayed; DSB200_VOC_GRAPH=0 launches them eagerly."""
         nat.require_device()
         if self.noise_sigma is not None and self.noise_sigma > 0:
             raise NotImplementedError("noise_sigma > 0 is not supported on the native path")
         P = self._packed
         if P is None or P["key"] != self._fingerprint(self) or P["w_pre"].device != x.device:
             P = self._pack()
+            self._graphs = {}
         B, M, T = x.shape
-        dev, bf = x.device, torch.bfloat16
+        x_tm = x.transpose(1, 2).float().contiguous().view(B * T, M)
         src = har_source.reshape(B, -1).float().contiguous()                                   # [B, T * upp]
+        if os.environ.get("DSB200_VOC_GRAPH", "1") == "0":
+            return self._run_native(P, x_tm, src, B, T)
+        graphs = self.__dict__.setdefault("_graphs", {})
+        key = (B, T, torch.cuda.current_stream().cuda_stream)
+        entry = graphs.get(key)
+        if entry is None:
+            while len(graphs) >= self.MAX_GRAPHS:
+                graphs.pop(next(iter(graphs)))
+            sx, ss = torch.empty_like(x_tm), torch.empty_like(src)
+            sx.copy_(x_tm)
+            ss.copy_(src)
+            self._run_native(P, sx, ss, B, T)  # warm-up outside capture: function attributes, lazy module loading
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                out = self._run_native(P, sx, ss, B, T)
+            entry = graphs[key] = (g, sx, ss, out)
+        g, sx, ss, out = entry
+        sx.copy_(x_tm)
+        ss.copy_(src)
+        g.replay()
+        return out.clone()
+
+    def _run_native(self, P, x_tm, src, B, T):
+        M = x_tm.shape[1]
+        dev, bf = x_tm.device, torch.bfloat16
         mel = torch.empty(B * T, P["mel_p"], dtype=bf, device=dev)
-        ops.cast_bf16(mel, x.transpose(1, 2).float().contiguous().view(B * T, M))
+        ops.cast_bf16(mel, x_tm)
         a = torch.empty(B * T, P["c0_p"], dtype=bf, device=dev)                                # LeakyReLU(conv_pre(x))
         ops.gemm(ops.EPI_LINEAR, ops.tile_n(P["c0_p"]), B, T, mel, P["w_pre"], a, n_taps=7, bias=P["b_pre"], act=ops.ACT_LRELU,
                  slope2=LRELU_SLOPE)

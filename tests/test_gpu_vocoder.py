@@ -56,6 +56,24 @@ def test_native_generator_published_config(B, T):
     assert err < WAV_TOL
 
 
+def test_graph_replay_and_deepcopy():
+    """Second call replays the captured CUDA graph (same result, new inputs honoured); the module stays deep-copyable."""
+    import copy
+    from diffsinger_b200.vocoder import DEFAULT_CONFIG, Generator
+    torch.manual_seed(3)
+    gen = Generator(dict(DEFAULT_CONFIG, upsample_initial_channel=128)).eval().cuda()
+    mel = torch.randn(1, 128, 25, device="cuda") - 3.0
+    f0 = torch.full((1, 25), 300.0, device="cuda")
+    ri, nz = torch.zeros(1, 1, 9, device="cuda"), torch.randn(1, 25 * 512, 9, device="cuda")
+    with torch.no_grad():
+        y1 = gen(mel, f0, rand_ini=ri, noise=nz)
+        y2 = gen(mel, f0, rand_ini=ri, noise=nz)
+        y3 = gen(mel * 0.5, f0, rand_ini=ri, noise=nz)
+        y4 = copy.deepcopy(gen)(mel, f0, rand_ini=ri, noise=nz)
+    assert torch.equal(y1, y2) and torch.equal(y1, y4) and not torch.equal(y1, y3)
+    assert len(gen._graphs) == 1
+
+
 def test_spec2wav_torch_wrapper():
     from diffsinger_b200.vocoder import DEFAULT_CONFIG, Generator, NsfHifiGAN
     cfg = dict(DEFAULT_CONFIG, upsample_initial_channel=128)
