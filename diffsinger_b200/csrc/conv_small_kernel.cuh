@@ -9,7 +9,7 @@
 // One UMMA (M = 128, N = C_out, K = 16) per tap and 16-channel slice; accumulators double-buffered in TMEM.
 // HBM-bound by design: per output sample C_in + C_out (+ residual, + activated copy) bf16 values.
 //
-// Warp roles: 0 = TMA producer, 1 = MMA issuer, 2..5 = epilogue.  Persistent over tiles.
+// Warp roles: 0 = TMA producer, 1 = MMA issuer, 2..5 and 6..9 = two epilogue groups (even / odd tiles).  Persistent over tiles.
 #pragma once
 #include <cuda.h>
 
@@ -32,7 +32,7 @@ struct ConvSmallParams {
   float slope;
 };
 
-constexpr int kConvSmallThreads = 192;
+constexpr int kConvSmallThreads = 320;  // 2 control warps + two epilogue groups of 4 warps (one per TMEM accumulator buffer)
 constexpr int kConvSmallStages = 4;
 constexpr int kConvSmallMaxRows = 192;  // 128 + 10 * 5 = 178 -> 184
 constexpr int kConvSmallMaxTaps = 11;
@@ -148,12 +148,15 @@ __global__ void __launch_bounds__(kConvSmallThreads, 1) ds_conv_small_kernel(con
       }
     }
   } else {
+    // epilogue group g = accumulator buffer g: the two groups alternate tiles, so one tile's residual loads / stores
+    // (a global-memory round trip per tile) overlap the other's
     const int quad = warp & 3;
+    const int grp = (warp - 2) >> 2;
     float bias[COUT];
 #pragma unroll
     for (int j = 0; j < COUT; ++j) bias[j] = __ldg(p.bias + j);
-    int it = 0;
-    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+    for (int it = grp; blockIdx.x + static_cast<long>(it) * gridDim.x < p.total_tiles; it += 2) {
+      const int tile = blockIdx.x + it * gridDim.x;
       const int tt = tile % p.tiles_t, b = tile / p.tiles_t;
       const int as = it & 1;
       mbar_wait(&tmem_full[as], (it >> 1) & 1);
