@@ -295,6 +295,10 @@ def main():
     if world > 1:
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
+        # NCCL's own log lines (e.g. the version banner under NCCL_DEBUG=VERSION) go to stderr: stdout carries ONE JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":  # that level printf()s its banner to stdout
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     try:
         run_native(args, rank, world, local_rank)
