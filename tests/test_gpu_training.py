@@ -38,6 +38,7 @@ def _check(grads, tol):
 
 
 SHAPES = [
+    (512, 20, 128, 1, 4, 4, 700),  # the acoustic backbone at its real depth / width (configs[1]), ragged last tile
     (256, 4, 128, 1, 4, 2, 300),
     (192, 3, 24, 2, 2, 3, 131),   # ragged tile, multi-variance shape, dilations 1, 2, 1
     (512, 2, 128, 1, 4, 1, 257),
@@ -94,7 +95,7 @@ def test_stack_matches_fp32_autograd(C, L, M, F, cycle, B, T):
     _check(grads, STACK_GRAD_TOL)
 
 
-@pytest.mark.parametrize("C,L,M,F,cycle,B,T", SHAPES[:3])
+@pytest.mark.parametrize("C,L,M,F,cycle,B,T", SHAPES[1:4])
 def test_module_forward_backward_match_torch_autograd(C, L, M, F, cycle, B, T):
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
