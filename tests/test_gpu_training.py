@@ -43,6 +43,8 @@ SHAPES = [
     (192, 3, 24, 2, 2, 3, 131),   # ragged tile, multi-variance shape, dilations 1, 2, 1
     (512, 2, 128, 1, 4, 1, 257),
     (256, 5, 64, 1, 5, 2, 140),   # pitch predictor shape: dilation 16 next to short utterances
+    (256, 4, 128, 1, 4, 1, 7),    # shorter than the largest dilation and than one 64-frame reduction block
+    (192, 2, 24, 2, 2, 5, 1),     # single-frame utterances: every off-centre tap is padding
 ]
 
 

@@ -27,7 +27,7 @@ def test_native_generator_matches_reference_golden(tag):
     assert gen.last_launches == 2 + n_stage * (2 + 18 + 1) + 1
 
 
-@pytest.mark.parametrize("B,T", [(1, 40), (2, 23)])
+@pytest.mark.parametrize("B,T", [(1, 40), (2, 23), (3, 1)])
 def test_native_generator_published_config(B, T):
     """upsample 8-8-2-2-2 from 512 channels (256 / 128 / 64 / 32 / 16: the last two padded to 64), hop 512."""
     from diffsinger_b200.vocoder import DEFAULT_CONFIG, Generator
@@ -42,7 +42,7 @@ def test_native_generator_published_config(B, T):
     gen = gen.cuda()
     mel = torch.randn(B, 128, T, device="cuda") * 2.0 - 4.0
     f0 = 220.0 * torch.exp2(torch.rand(B, T, device="cuda"))
-    f0[:, 5:9] = 0.0
+    f0[:, 5:9] = 0.0  # an unvoiced stretch (no-op for T < 6)
     rand_ini = torch.rand(1, 1, 9, device="cuda")
     rand_ini[..., 0] = 0
     noise = torch.randn(B, T * 512, 9, device="cuda")
