@@ -156,6 +156,7 @@ static int launch_gemm(int BN, int epi, const GemmParams& p, cudaStream_t st, bo
   DS_CASE(64, EPI_OUTF32) DS_CASE(128, EPI_OUTF32) DS_CASE(256, EPI_OUTF32)
   DS_CASE(256, EPI_CPROJ)
   DS_CASE(128, EPI_SWIGLU) DS_CASE(256, EPI_SWIGLU)
+  DS_CASE(64, EPI_GATEBWD) DS_CASE(128, EPI_GATEBWD) DS_CASE(256, EPI_GATEBWD)
 #undef DS_CASE
   return fail(DS_ERR_INVALID, "no GEMM instantiation for BN=%d epilogue=%d", BN, epi);
 }
@@ -885,8 +886,11 @@ extern "C" int ds_transpose(float* dst, const float* src, int32_t B, int32_t R, 
 extern "C" int ds_debug_gemm(const ds_gemm_desc* d, void* stream) {
   if (!d) return fail(DS_ERR_INVALID, "null argument");
   if (!d->a0 || !d->w || !d->out) return fail(DS_ERR_INVALID, "ds_gemm: null operand");
-  if (d->epi == EPI_RES ? (!d->res_in || !d->vec_add) : !d->bias)
+  if (d->epi == EPI_GATEBWD) {
+    if (!d->res_in || d->n_real <= 0) return fail(DS_ERR_INVALID, "ds_gemm: the gate-backward epilogue needs res_in (z) and n_real (channels)");
+  } else if (d->epi == EPI_RES ? (!d->res_in || !d->vec_add) : !d->bias) {
     return fail(DS_ERR_INVALID, "ds_gemm: epilogue %d needs %s", d->epi, d->epi == EPI_RES ? "res_in and vec_add" : "bias");
+  }
   DS_TRY(ensure_device());
   GemmParams g;
   memset(&g, 0, sizeof(g));

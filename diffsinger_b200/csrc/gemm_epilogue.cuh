@@ -101,6 +101,47 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
       }
       if (valid) st_act32<kSplit>(out + c * 32, p.out_lo, z);
     }
+  } else if constexpr (EPI == EPI_GATEBWD) {
+    // training backward of the gated activation, fused behind dy = W2^T [h | dskip] (wavenet.py:41-44 under autograd):
+    // z = [gate | filter] pre-activations of this layer (res_in, plain channel order, filter half n_real columns on),
+    // dz_gate = dy * tanh(f) * s (1 - s),  dz_filter = dy * s * (1 - tanh(f)^2),  s = sigmoid(g); both halves written.
+    const int n0 = nt * BN;
+    const int Ch = p.n_real;
+    const __nv_bfloat16* zr = p.res_in + row * p.ld_res + n0;
+    __nv_bfloat16* dz = reinterpret_cast<__nv_bfloat16*>(p.out) + row * p.ld_out + p.out_c0 + n0;
+#pragma unroll 1
+    for (int c = half; c < BN / 32; c += 2) {
+      uint32_t a[32];
+      tmem_ld_32x32(taddr + c * 32, a);
+      uint4 gq[4], fq[4];
+      ld_x4(zr + c * 32, gq);
+      ld_x4(zr + Ch + c * 32, fq);
+      tmem_ld_wait();
+      float og[32], of[32];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint32_t gw[4] = {gq[i].x, gq[i].y, gq[i].z, gq[i].w};
+        const uint32_t fw[4] = {fq[i].x, fq[i].y, fq[i].z, fq[i].w};
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const int j = 8 * i + 2 * h + e;
+            const float g = __uint_as_float(e ? (gw[h] & 0xffff0000u) : (gw[h] << 16));
+            const float f = __uint_as_float(e ? (fw[h] & 0xffff0000u) : (fw[h] << 16));
+            const float sg = fmaf(0.5f, tanh_approx(0.5f * g), 0.5f);  // MUFU: 2^-11 relative, below the bf16 rounding of dz
+            const float th = tanh_approx(f);
+            const float dy = __uint_as_float(a[j]);
+            og[j] = dy * th * sg * (1.0f - sg);
+            of[j] = dy * sg * (1.0f - th * th);
+          }
+        }
+      }
+      if (valid) {
+        st_bf16x32(dz + c * 32, og);
+        st_bf16x32(dz + Ch + c * 32, of);
+      }
+    }
   } else if constexpr (EPI == EPI_CPROJ) {
     // hoisted conditioner projection (wavenet.py:35, step-invariant): f16 out = (acc + bias) in the gate kernel's packed
     // column order, gate columns (first half of every BN-column pass) pre-multiplied by 0.5 for sigmoid-by-tanh

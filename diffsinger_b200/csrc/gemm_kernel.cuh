@@ -21,7 +21,7 @@ namespace dsb {
 constexpr int kGemmThreads = 384;  // 4 control warps + 8 epilogue warps (two per TMEM lane quadrant)
 constexpr int kEpiThreads = 256;
 
-enum : int { EPI_LINEAR = 0, EPI_GATE = 1, EPI_RES = 2, EPI_OUTF32 = 3, EPI_CPROJ = 4, EPI_SWIGLU = 5 };
+enum : int { EPI_LINEAR = 0, EPI_GATE = 1, EPI_RES = 2, EPI_OUTF32 = 3, EPI_CPROJ = 4, EPI_SWIGLU = 5, EPI_GATEBWD = 6 };
 
 struct GemmParams {
   CUtensorMap tmA0;  // primary activation source  (dims: channels, T, B)

@@ -10,7 +10,7 @@ import torch
 
 from . import _native as nat
 
-EPI_LINEAR, EPI_GATE, EPI_RES, EPI_OUTF32, EPI_SWIGLU = 0, 1, 2, 3, 5
+EPI_LINEAR, EPI_GATE, EPI_RES, EPI_OUTF32, EPI_SWIGLU, EPI_GATEBWD = 0, 1, 2, 3, 5, 6
 ACT_NONE, ACT_RELU, ACT_GELU, ACT_LRELU, ACT_TANH = 0, 1, 2, 3, 4
 DW_NONE, DW_RELU, DW_PRELU, DW_SILU = 0, 1, 2, 3
 
@@ -37,7 +37,8 @@ def _p(t: Optional[torch.Tensor]):
 def gemm(epi: int, BN: int, B: int, T: int, a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, k_per_tap: Optional[int] = None,
          n_taps: int = 1, dil: int = 1, a_c0: int = 0, a1: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None,
          vec: Optional[torch.Tensor] = None, vec_bstride: int = 0, res: Optional[torch.Tensor] = None, act: int = ACT_NONE,
-         n_real: int = 0, scale: float = 1.0, out_c0: int = 0, out2: Optional[torch.Tensor] = None, slope2: float = 0.0):
+         n_real: int = 0, scale: float = 1.0, out_c0: int = 0, out2: Optional[torch.Tensor] = None, slope2: float = 0.0,
+         res_c0: int = 0):
     """out[b, t, out_c0 + n] = epilogue(sum_tap sum_k a[b, t + (tap - n_taps // 2) * dil, a_c0 + k] * w[n, tap * K + k]
     + sum_h a1[b, t, h] * w[n, n_taps * K + h]); frames outside [0, T) read as zeros (the conv's zero padding).
     a: [B*T, ld_a] bf16 (K = k_per_tap columns from a_c0), a1: optional second operand [B*T, H] (one tap),
@@ -53,7 +54,7 @@ def gemm(epi: int, BN: int, B: int, T: int, a: torch.Tensor, w: torch.Tensor, ou
     d.a1, d.a1_channels, d.kb_a1 = _p(a1), h, h // 64
     d.w, d.w_rows, d.w_k, d.b_row0, d.n_tiles = w.data_ptr(), rows, w_k, 0, rows // BN
     d.bias, d.vec_sub, d.vec_add, d.vec_bstride = _p(bias), None, _p(vec), vec_bstride
-    d.res_in, d.ld_res = _p(res), (res.shape[1] if res is not None else 0)
+    d.res_in, d.ld_res = (res.data_ptr() + 2 * res_c0 if res is not None else None), (res.shape[1] if res is not None else 0)
     d.out, d.ld_out, d.out_c0, d.n_real = out.data_ptr(), out.shape[-1], out_c0, n_real
     d.relu, d.scale = act, scale
     d.out2, d.slope2 = _p(out2), slope2

@@ -12,9 +12,8 @@ forward, per layer l (dilation dl):
   with xt_l = x_l + d_l[b] (the step vector is added before the conv's zero padding, wavenet.py:36) and
   rvec_l = (b2res_l - d_l) / sqrt(2) + d_{l+1};  skip_sum = [y_0 | ... | y_{L-1}] x Wskip^T + sum_l b2skip_l (one GEMM, K = L*C).
 
-backward, per layer in reverse, with h_l = dLoss/dx_l / sqrt(2) kept in the left half of G2 = [h_{l+1} | dskip]:
-    dy   = W2_l^T G2                                                                     ds_gemm EPI_LINEAR
-    dz_l = gate'(z_l) * dy                                                               ds_gate_bwd
+backward, per layer in reverse, with h_l = dLoss/dx_l / sqrt(2) (all layers kept: the weight gradients read them):
+    dy   = W2_l^T [h_{l+1} | dskip];  dz_l = gate'(z_l) * dy                             ds_gemm, gate-backward epilogue
     h_l  = (sum_tap W1_tap^T dz_l(t - (tap-1) dl) + h_{l+1}) / sqrt(2)                   ds_gemm EPI_RES (taps mirrored)
   then dcond = [Wc_0^T | ... ] x [dz_0 | ... | dz_{L-1}] (one GEMM, K = 2LC).
 
@@ -109,11 +108,11 @@ class WaveNetStack(torch.autograd.Function):
         ops.cast_bf16(dS_bf, dS.float().contiguous().view(rows, Cc))
         HALL = torch.empty(L + 1, rows, Cc, dtype=bf, device=dev)                                 # h_l; h_L = 0 (last residual unused)
         HALL[L].zero_()
-        DY = torch.empty(rows, Cc, dtype=bf, device=dev)
         DZ = torch.empty(rows, L * 2 * Cc, dtype=bf, device=dev)
         for l in range(L - 1, -1, -1):
-            ops.gemm(ops.EPI_LINEAR, _bn(Cc), B, T, HALL[l + 1], w2t[l], DY, a1=dS_bf, bias=zero_c)
-            ops.gate_bwd(DZ, l * 2 * Cc, DY, Z, l * 2 * Cc, Cc)
+            # dy = W2^T [h_{l+1} | dskip] with the gate's derivative in the epilogue: dz_l straight from the accumulators
+            ops.gemm(ops.EPI_GATEBWD, _bn(Cc), B, T, HALL[l + 1], w2t[l], DZ, a1=dS_bf, res=Z, res_c0=l * 2 * Cc, n_real=Cc,
+                     out_c0=l * 2 * Cc)
             ops.gemm(ops.EPI_RES, _bn(Cc), B, T, DZ, w1t[l], HALL[l], k_per_tap=2 * Cc, n_taps=3, dil=dil[l], a_c0=l * 2 * Cc,
                      vec=zero_c, vec_bstride=0, res=HALL[l + 1], scale=_RS2)
         dcond = torch.empty(rows, H, dtype=bf, device=dev)

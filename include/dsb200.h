@@ -133,7 +133,9 @@ int ds_transpose(float* dst, const float* src, int32_t B, int32_t R, int32_t C, 
 typedef struct {
   int32_t epi;  /* 0 linear: bf16 out = act(acc + bias) * scale + vec_add[b]      1 gate: sigmoid(first half) * tanh(second half)
                    2 residual: bf16 out = (acc + res_in) * scale + vec_add[b]     3 fp32 out = act(acc + bias) * scale
-                   5 SwiGLU: first half * silu(second half)   (halves = BN/2-row blocks of the same channels, see pack order) */
+                   5 SwiGLU: first half * silu(second half)   (halves = BN/2-row blocks of the same channels, see pack order)
+                   6 gate backward (training): acc = dy; res_in = z = [gate | filter] of the layer (filter half n_real columns
+                     on); out[n] = dy * tanh(f) * s (1 - s), out[n_real + n] = dy * s * (1 - tanh(f)^2), s = sigmoid(g) */
   int32_t BN;   /* 64 / 128 / 256 */
   int32_t B, T;
   const void* a0; int32_t a0_channels; int32_t a0_c0; int32_t kb_a0; int32_t n_taps; int32_t dil;

@@ -173,3 +173,31 @@ def test_conv_small(C, taps, dil):
     wav = torch.empty(B * T, device=dev)
     ops.conv_small(x, w_img, bias, wav, B, T, dil=dil, act=ops.ACT_TANH)
     assert rel_l2(wav, torch.tanh(ref[:, 0])) < 1e-3
+
+
+def test_gate_fwd_bwd_and_fused_gate_backward_epilogue():
+    """ds_gate_fwd / ds_gate_bwd (wavenet.py:41-42 and its derivative) on column slices of wider buffers, and the same
+    derivative fused behind a GEMM (ds_gemm epilogue 6), against torch autograd on the bf16-rounded pre-activations."""
+    from diffsinger_b200 import ops
+    torch.manual_seed(5)
+    B, T, Cc, L = 2, 150, 128, 3
+    rows = B * T
+    Z = _bf(rows, L * 2 * Cc) * 2
+    Y = torch.zeros(rows, L * Cc, dtype=torch.bfloat16, device=dev)
+    DZ = torch.zeros_like(Z)
+    l = 1
+    z = Z[:, l * 2 * Cc:(l + 1) * 2 * Cc].float().requires_grad_(True)
+    y_ref = torch.sigmoid(z[:, :Cc]) * torch.tanh(z[:, Cc:])
+    dy = _bf(rows, Cc)
+    y_ref.backward(dy.float())
+    ops.gate_fwd(Y, l * Cc, Z, l * 2 * Cc, Cc)
+    assert rel_l2(Y[:, l * Cc:(l + 1) * Cc].float(), y_ref.detach()) < 4e-3
+    assert float(Y[:, :l * Cc].abs().max()) == 0 and float(Y[:, (l + 1) * Cc:].abs().max()) == 0
+    ops.gate_bwd(DZ, l * 2 * Cc, dy, Z, l * 2 * Cc, Cc)
+    assert rel_l2(DZ[:, l * 2 * Cc:(l + 1) * 2 * Cc].float(), z.grad) < 4e-3
+    # fused: dy = A W^T with W = identity, so the epilogue sees exactly dy
+    DZ2 = torch.zeros_like(Z)
+    eye = torch.eye(Cc, device=dev, dtype=torch.bfloat16)
+    ops.gemm(ops.EPI_GATEBWD, 128, B, T, dy, eye, DZ2, res=Z, res_c0=l * 2 * Cc, n_real=Cc, out_c0=l * 2 * Cc)
+    assert rel_l2(DZ2[:, l * 2 * Cc:(l + 1) * 2 * Cc].float(), z.grad) < 6e-3
+    assert float(DZ2[:, :l * 2 * Cc].abs().max()) == 0
