@@ -5,6 +5,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <cstring>
 #include <map>
 #include <string>
@@ -21,6 +22,7 @@
 #include "mma_bench.cuh"
 #include "wgrad_kernel.cuh"
 #include "conv_small_kernel.cuh"
+#include "dwconv_mma_kernel.cuh"
 
 using namespace dsb;
 
@@ -945,7 +947,22 @@ extern "C" int ds_dwconv(void* y_bf16, const void* x_bf16, const float* w, const
   const int bx = ceil_div(channels / 2, 128);
   __nv_bfloat16* y = (__nv_bfloat16*)y_bf16;
   const __nv_bfloat16* x = (const __nv_bfloat16*)x_bf16;
-  if (kernel_size == 31) {
+  // tensor-core Toeplitz path (dwconv_mma_kernel.cuh) for the two kernel sizes the models use; DSB200_DWCONV=fma keeps the
+  // fp32-FMA kernel for A/B runs and for channel counts that are not a multiple of 32
+  static const bool force_fma = [] { const char* e = getenv("DSB200_DWCONV"); return e && !strcmp(e, "fma"); }();
+  if (!force_fma && channels % 32 == 0 && (kernel_size == 31 || kernel_size == 7)) {
+    const int n_tiles = ceil_div(T, 128);
+    const long units = (long)n_tiles * B * (channels / 32);
+    const int chunks = (int)std::min<long>(8, std::max<long>(1, units / (148 * 8)));
+    const dim3 grid(channels / 32, ceil_div(n_tiles, chunks), B);
+    if (kernel_size == 31) {
+      CUDA_TRY(cudaFuncSetAttribute(dwconv_mma_kernel<31>, cudaFuncAttributeMaxDynamicSharedMemorySize, DwMma<31>::kSmemBytes));
+      dwconv_mma_kernel<31><<<grid, 128, DwMma<31>::kSmemBytes, st>>>(y, x, w, bias, slope, T, channels, pad_left, act, chunks);
+    } else {
+      CUDA_TRY(cudaFuncSetAttribute(dwconv_mma_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, DwMma<7>::kSmemBytes));
+      dwconv_mma_kernel<7><<<grid, 128, DwMma<7>::kSmemBytes, st>>>(y, x, w, bias, slope, T, channels, pad_left, act, chunks);
+    }
+  } else if (kernel_size == 31) {
     CUDA_TRY(cudaFuncSetAttribute(dwconv_kernel<31, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (62 + 30) * 512));
     dwconv_kernel<31, 2><<<dim3(bx, ceil_div(T, 62), B), 128, (62 + 30) * 512, st>>>(y, x, w, bias, slope, T, channels, pad_left, act);
   } else if (kernel_size == 7) {
