@@ -920,14 +920,15 @@ extern "C" int ds_layernorm(void* y_bf16, const void* x_bf16, const float* gamma
   if (!y_bf16 || !x_bf16 || !gamma || !beta || rows <= 0) return fail(DS_ERR_INVALID, "bad argument");
   if (channels <= 0 || channels % 8 || channels > 2048) return fail(DS_ERR_INVALID, "channels=%d must be a multiple of 8 in (0, 2048]", channels);
   DS_TRY(ensure_device());
-  const long blocks = (rows + 15) / 16;  // 8 warps per 256-thread block, up to two rows per warp iteration
+  const int nch = ceil_div(channels, 256);
+  const int rows_per_block = 8 * (nch <= 2 ? kLnRows<2> : (nch <= 4 ? kLnRows<4> : kLnRows<8>));  // 8 warps per 256-thread block
+  const long blocks = (rows + rows_per_block - 1) / rows_per_block;
   const long cap = (long)g_num_sms * 32;
   const int grid = (int)(blocks < cap ? blocks : cap);
   cudaStream_t st = (cudaStream_t)stream;
   __nv_bfloat16* yp = (__nv_bfloat16*)y_bf16;
   const __nv_bfloat16* xp = (const __nv_bfloat16*)x_bf16;
   const __nv_bfloat16* ap = (const __nv_bfloat16*)add_bf16;
-  const int nch = ceil_div(channels, 256);
   if (nch <= 1) layernorm_kernel<1><<<grid, 256, 0, st>>>(yp, xp, gamma, beta, (long)rows, channels, eps, vec, (long)rows_per_vec, ap);
   else if (nch <= 2) layernorm_kernel<2><<<grid, 256, 0, st>>>(yp, xp, gamma, beta, (long)rows, channels, eps, vec, (long)rows_per_vec, ap);
   else if (nch <= 4) layernorm_kernel<4><<<grid, 256, 0, st>>>(yp, xp, gamma, beta, (long)rows, channels, eps, vec, (long)rows_per_vec, ap);
@@ -955,13 +956,17 @@ extern "C" int ds_dwconv(void* y_bf16, const void* x_bf16, const float* w, const
     const long units = (long)n_tiles * B * (channels / 32);
     const int chunks = (int)std::min<long>(8, std::max<long>(1, units / (148 * 8)));
     const dim3 grid(channels / 32, ceil_div(n_tiles, chunks), B);
+#define DS_DW_MMA(KS, ACT)                                                                                                   \
+  do {                                                                                                                       \
+    CUDA_TRY(cudaFuncSetAttribute(dwconv_mma_kernel<KS, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, DwMma<KS>::kSmemBytes)); \
+    dwconv_mma_kernel<KS, ACT><<<grid, 256, DwMma<KS>::kSmemBytes, st>>>(y, x, w, bias, slope, T, channels, pad_left, chunks); \
+  } while (0)
     if (kernel_size == 31) {
-      CUDA_TRY(cudaFuncSetAttribute(dwconv_mma_kernel<31>, cudaFuncAttributeMaxDynamicSharedMemorySize, DwMma<31>::kSmemBytes));
-      dwconv_mma_kernel<31><<<grid, 128, DwMma<31>::kSmemBytes, st>>>(y, x, w, bias, slope, T, channels, pad_left, act, chunks);
+      if (act == 0) DS_DW_MMA(31, 0); else if (act == 1) DS_DW_MMA(31, 1); else if (act == 2) DS_DW_MMA(31, 2); else DS_DW_MMA(31, 3);
     } else {
-      CUDA_TRY(cudaFuncSetAttribute(dwconv_mma_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, DwMma<7>::kSmemBytes));
-      dwconv_mma_kernel<7><<<grid, 128, DwMma<7>::kSmemBytes, st>>>(y, x, w, bias, slope, T, channels, pad_left, act, chunks);
+      if (act == 0) DS_DW_MMA(7, 0); else if (act == 1) DS_DW_MMA(7, 1); else if (act == 2) DS_DW_MMA(7, 2); else DS_DW_MMA(7, 3);
     }
+#undef DS_DW_MMA
   } else if (kernel_size == 31) {
     CUDA_TRY(cudaFuncSetAttribute(dwconv_kernel<31, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (62 + 30) * 512));
     dwconv_kernel<31, 2><<<dim3(bx, ceil_div(T, 62), B), 128, (62 + 30) * 512, st>>>(y, x, w, bias, slope, T, channels, pad_left, act);

@@ -223,13 +223,15 @@ namespace dsb {
 // conditioner projection and the diffusion-step projection of lynxnet.py:82-89).
 // One warp per row, the row lives in registers (C <= 2048, C % 8 == 0), two-pass statistics in fp32 (biased variance,
 // like torch.nn.LayerNorm; lynxnet.py:52,123).
+template <int kMaxChunks>
+constexpr int kLnRows = kMaxChunks <= 2 ? 2 : 1;
 template <int kMaxChunks>  // ceil(C / 256): a row lives in kMaxChunks x 8 registers per lane
-__global__ void layernorm_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
+__global__ void __launch_bounds__(256) layernorm_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
                                  const float* __restrict__ beta, long rows, int C, float eps, const float* __restrict__ vec,
                                  long rows_per_vec, const __nv_bfloat16* __restrict__ add) {
   grid_dep_launch();
   grid_dep_wait();
-  constexpr int kRows = kMaxChunks <= 2 ? 2 : 1;  // rows per warp iteration: two independent rows keep more bytes in flight
+  constexpr int kRows = kLnRows<kMaxChunks>;  // rows per warp iteration: independent rows keep more bytes in flight
   const int lane = threadIdx.x & 31;
   const long warp0 = (static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   const long nwarps = (static_cast<long>(gridDim.x) * blockDim.x) >> 5;
