@@ -954,7 +954,7 @@ extern "C" int ds_dwconv(void* y_bf16, const void* x_bf16, const float* w, const
   if (!force_fma && channels % 32 == 0 && (kernel_size == 31 || kernel_size == 7)) {
     const int n_tiles = ceil_div(T, 128);
     const long units = (long)n_tiles * B * (channels / 32);
-    const int chunks = (int)std::min<long>(8, std::max<long>(1, units / (148 * 8)));
+    const int chunks = (int)std::min<long>(16, std::max<long>(1, units / (148 * 6)));
     const dim3 grid(channels / 32, ceil_div(n_tiles, chunks), B);
 #define DS_DW_MMA(KS, ACT)                                                                                                   \
   do {                                                                                                                       \

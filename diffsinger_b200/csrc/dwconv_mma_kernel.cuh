@@ -12,8 +12,8 @@
 // Activations arrive time-major ([T][CH]), so every tile is transposed once on its way in: cp.async (16 B, zero fill outside
 // [0, T) = the conv's zero padding) into a natural-layout staging tile, then LDS.128 of two consecutive frames, 8 PRMTs and
 // 8 STS.32 per thread unit into the channel-major tile.  Outputs go back through a time-major tile to 16-byte coalesced stores.
-// A CTA (8 warps x 4 channels) walks `chunks` consecutive 128-frame tiles of one utterance; the next tile's cp.async overlaps
-// the current tile's MMAs.  Weights are rounded to bf16 (as in every GEMM of the same model); accumulation is fp32.
+// A CTA (8 warps x 4 channels) walks `chunks` consecutive 128-frame tiles of one utterance; cp.async runs two tiles ahead
+// (double-buffered staging tile).  Weights are rounded to bf16 (as in every GEMM of the same model); accumulation is fp32.
 #pragma once
 #include <cuda_bf16.h>
 #include <cstdint>
@@ -59,7 +59,7 @@ struct DwMma {
   static constexpr int kXtRow = 24 * 16;               // bytes per channel row: even chunks in slots 0.., odd chunks in slots 12..
   static constexpr int kXtBytes = 32 * kXtRow;
   static constexpr int kOutBytes = 128 * 64;           // [frame][32 channels], 8-byte groups XOR-swizzled per frame
-  static constexpr int kSmemBytes = kStageBytes + kXtBytes + kOutBytes;
+  static constexpr int kSmemBytes = 2 * kStageBytes + kXtBytes + kOutBytes;  // staging tile double buffered
   static_assert(kTW / 8 <= 2 * kHalf && (kTW / 8 + 1) / 2 <= kHalf, "channel row too short");
 };
 
@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(256) dwconv_mma_kernel(__nv_bfloat16* __restri
   using S = DwMma<K>;
   extern __shared__ __align__(16) uint8_t dwm_smem[];
   grid_dep_launch();
-  const uint32_t stage = smem_u32(dwm_smem), xt = stage + S::kStageBytes, ot = xt + S::kXtBytes;
+  const uint32_t stage = smem_u32(dwm_smem), xt = stage + 2 * S::kStageBytes, ot = xt + S::kXtBytes;
   const int tid = threadIdx.x, lane = tid & 31, wq = tid >> 5, g = lane >> 2, q = lane & 3;
   const int c0 = blockIdx.x * 32, b = blockIdx.z;
   const int n_tiles = (T + 127) / 128;
@@ -100,29 +100,35 @@ __global__ void __launch_bounds__(256) dwconv_mma_kernel(__nv_bfloat16* __restri
   }
   grid_dep_wait();
 
+  // tile -> staging buffer (tile - tile0) % 2; always commits a group (possibly empty) so that wait_group 1 = "all but the newest"
   auto issue_loads = [&](int tile) {
-    const int tb = tile * 128 - pad;
-    for (int idx = tid; idx < S::kTW * 4; idx += 256) {
-      const int i = idx >> 2, o = idx & 3, t = tb + i;
-      const bool valid = t >= 0 && t < T;
-      cp_async_16_zfill(stage + i * S::kStageRow + o * 16, xb + static_cast<size_t>(valid ? t : 0) * CH + o * 8, valid);
+    if (tile < tile1) {
+      const int tb = tile * 128 - pad;
+      const uint32_t st = stage + ((tile - tile0) & 1) * S::kStageBytes;
+      for (int idx = tid; idx < S::kTW * 4; idx += 256) {
+        const int i = idx >> 2, o = idx & 3, t = tb + i;
+        const bool valid = t >= 0 && t < T;
+        cp_async_16_zfill(st + i * S::kStageRow + o * 16, xb + static_cast<size_t>(valid ? t : 0) * CH + o * 8, valid);
+      }
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
-  if (tile0 < tile1) issue_loads(tile0);
+  issue_loads(tile0);
+  issue_loads(tile0 + 1);
 
   // ldmatrix lane address inside a channel row: matrix mi = lane / 8 holds chunks 2r + mi (+ 2 per k16 step), r = lane % 8
   const int mi = lane >> 3, r = lane & 7;
   const uint32_t b_lane = xt + (wq * 4) * S::kXtRow + (r + (mi >> 1) + (mi & 1) * S::kHalf) * 16;
 
   for (int tile = tile0; tile < tile1; ++tile) {
-    asm volatile("cp.async.wait_all;" ::: "memory");
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
     __syncthreads();  // staged tile visible; the previous tile's output tile has been read out
+    const uint8_t* sg = dwm_smem + ((tile - tile0) & 1) * S::kStageBytes;
     // transpose: unit = (frame pair tp, channel octet o) -> 8 words (c @ 2tp, c @ 2tp + 1) of the channel-major tile
     for (int u = tid; u < (S::kTW / 2) * 4; u += 256) {
       const int o = u / (S::kTW / 2), tp = u - o * (S::kTW / 2);
-      const uint4 r0 = *reinterpret_cast<const uint4*>(dwm_smem + (2 * tp) * S::kStageRow + o * 16);
-      const uint4 r1 = *reinterpret_cast<const uint4*>(dwm_smem + (2 * tp + 1) * S::kStageRow + o * 16);
+      const uint4 r0 = *reinterpret_cast<const uint4*>(sg + (2 * tp) * S::kStageRow + o * 16);
+      const uint4 r1 = *reinterpret_cast<const uint4*>(sg + (2 * tp + 1) * S::kStageRow + o * 16);
       const uint32_t a[4] = {r0.x, r0.y, r0.z, r0.w}, c[4] = {r1.x, r1.y, r1.z, r1.w};
       const int ch = tp >> 2;  // 16-byte chunk (8 frames) -> slot (ch / 2) + (ch % 2) * kHalf
       const uint32_t dst = xt + (o * 8) * S::kXtRow + ((ch >> 1) + (ch & 1) * S::kHalf) * 16 + (tp & 3) * 4;
@@ -132,8 +138,8 @@ __global__ void __launch_bounds__(256) dwconv_mma_kernel(__nv_bfloat16* __restri
         asm volatile("st.shared.b32 [%0], %1;" ::"r"(dst + (2 * p + 1) * S::kXtRow), "r"(prmt(a[p], c[p], 0x7632)) : "memory");
       }
     }
-    __syncthreads();  // channel-major tile complete, staging tile free
-    if (tile + 1 < tile1) issue_loads(tile + 1);
+    __syncthreads();  // channel-major tile complete, this staging buffer free
+    issue_loads(tile + 2);
 
     // 4 channels x (ldmatrix.x4 [+ .x2] + kNK mma); D[g (+8)][2q (+1)] = frame 16 (2q (+1)) + g (+8)
     uint32_t ow[4][2];  // [frame slot v][channel pair] packed bf16
@@ -173,7 +179,7 @@ __global__ void __launch_bounds__(256) dwconv_mma_kernel(__nv_bfloat16* __restri
       const int idx = tid + 256 * it, t = idx >> 2, o = idx & 3;
       if (tb + t < T) {
         const int sw = ((t >> 5) & 3) | (((t >> 1) & 1) << 2);
-        uint4 v = *reinterpret_cast<const uint4*>(dwm_smem + S::kStageBytes + S::kXtBytes + t * 64 + ((o ^ (sw >> 1)) << 4));
+        uint4 v = *reinterpret_cast<const uint4*>(dwm_smem + 2 * S::kStageBytes + S::kXtBytes + t * 64 + ((o ^ (sw >> 1)) << 4));
         if (sw & 1) v = make_uint4(v.z, v.w, v.x, v.y);  // the two 8-byte groups of the chunk sit swapped
         *reinterpret_cast<uint4*>(yb + static_cast<size_t>(tb + t) * CH + o * 8) = v;
       }
