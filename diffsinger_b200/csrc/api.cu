@@ -923,7 +923,7 @@ extern "C" int ds_layernorm(void* y_bf16, const void* x_bf16, const float* gamma
   const int nch = ceil_div(channels, 256);
   const int rows_per_block = 8 * (nch <= 2 ? kLnRows<2> : (nch <= 4 ? kLnRows<4> : kLnRows<8>));  // 8 warps per 256-thread block
   const long blocks = (rows + rows_per_block - 1) / rows_per_block;
-  const long cap = (long)g_num_sms * 32;
+  const long cap = (long)g_num_sms * (nch <= 2 ? 2 : 4);  // resident blocks: the warps are persistent and prefetch their next rows
   const int grid = (int)(blocks < cap ? blocks : cap);
   cudaStream_t st = (cudaStream_t)stream;
   __nv_bfloat16* yp = (__nv_bfloat16*)y_bf16;

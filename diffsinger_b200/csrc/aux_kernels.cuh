@@ -225,38 +225,71 @@ namespace dsb {
 // like torch.nn.LayerNorm; lynxnet.py:52,123).
 template <int kMaxChunks>
 constexpr int kLnRows = kMaxChunks <= 2 ? 2 : 1;
+// Persistent warps (the host sizes the grid to the resident warps): gamma / beta of the lane's columns are loaded once
+// (kMaxChunks <= 2; re-read from L1 per row they cost 4x the row's own bytes in LSU wavefronts), and the raw 16-byte loads of
+// the next row group are issued before the current one is reduced, so every warp keeps two row groups in flight.
 template <int kMaxChunks>  // ceil(C / 256): a row lives in kMaxChunks x 8 registers per lane
-__global__ void __launch_bounds__(256) layernorm_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
-                                 const float* __restrict__ beta, long rows, int C, float eps, const float* __restrict__ vec,
-                                 long rows_per_vec, const __nv_bfloat16* __restrict__ add) {
+__global__ void __launch_bounds__(256) layernorm_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x,
+                                 const float* __restrict__ gamma, const float* __restrict__ beta, long rows, int C, float eps,
+                                 const float* __restrict__ vec, long rows_per_vec, const __nv_bfloat16* __restrict__ add) {
   grid_dep_launch();
-  grid_dep_wait();
   constexpr int kRows = kLnRows<kMaxChunks>;  // rows per warp iteration: independent rows keep more bytes in flight
+  constexpr bool kHoist = kMaxChunks <= 2;
   const int lane = threadIdx.x & 31;
   const long warp0 = (static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   const long nwarps = (static_cast<long>(gridDim.x) * blockDim.x) >> 5;
   const int nch = (C + 255) / 256;
-  for (long r0 = warp0 * kRows; r0 < rows; r0 += nwarps * kRows) {
+  const float inv_c = 1.f / static_cast<float>(C);
+  float gg[kHoist ? kMaxChunks : 1][8], bb[kHoist ? kMaxChunks : 1][8];
+  auto load_gb = [&](int i, float (&g8)[8], float (&b8)[8]) {
+    const int e = (i * 32 + lane) * 8;
+    const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + e)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + e) + 1);
+    const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + e)), b1 = __ldg(reinterpret_cast<const float4*>(beta + e) + 1);
+    g8[0] = g0.x; g8[1] = g0.y; g8[2] = g0.z; g8[3] = g0.w; g8[4] = g1.x; g8[5] = g1.y; g8[6] = g1.z; g8[7] = g1.w;
+    b8[0] = b0.x; b8[1] = b0.y; b8[2] = b0.z; b8[3] = b0.w; b8[4] = b1.x; b8[5] = b1.y; b8[6] = b1.z; b8[7] = b1.w;
+  };
+  if (kHoist) {
+#pragma unroll
+    for (int i = 0; i < kMaxChunks; ++i)
+      if (i < nch && (i * 32 + lane) * 8 < C) load_gb(i, gg[kHoist ? i : 0], bb[kHoist ? i : 0]);
+  }
+  grid_dep_wait();
+  uint4 raw[kRows][kMaxChunks], rawa[kRows][kMaxChunks];
+  auto fetch = [&](long r0) {
+#pragma unroll
+    for (int q = 0; q < kRows; ++q) {
+      const long r = r0 + q < rows ? r0 + q : rows - 1;  // the tail warp recomputes the last row (same values rewritten)
+#pragma unroll
+      for (int i = 0; i < kMaxChunks; ++i) {
+        const int e = (i * 32 + lane) * 8;
+        if (i < nch && e < C) {
+          raw[q][i] = *reinterpret_cast<const uint4*>(x + r * C + e);
+          if (add) rawa[q][i] = *reinterpret_cast<const uint4*>(add + r * C + e);
+        }
+      }
+    }
+  };
+  long r0 = warp0 * kRows;
+  if (r0 < rows) fetch(r0);
+  for (; r0 < rows; r0 += nwarps * kRows) {
     float v[kRows][kMaxChunks][8];
     float sum[kRows];
 #pragma unroll
     for (int q = 0; q < kRows; ++q) {
-      const long r = r0 + q < rows ? r0 + q : rows - 1;  // the tail warp recomputes the last row (same values rewritten)
+      const long r = r0 + q < rows ? r0 + q : rows - 1;
       sum[q] = 0.f;
 #pragma unroll
       for (int i = 0; i < kMaxChunks; ++i) {
         const int e = (i * 32 + lane) * 8;
         if (i < nch && e < C) {
-          const uint4 qv = *reinterpret_cast<const uint4*>(x + r * C + e);
-          const uint32_t w[4] = {qv.x, qv.y, qv.z, qv.w};
+          const uint32_t w[4] = {raw[q][i].x, raw[q][i].y, raw[q][i].z, raw[q][i].w};
 #pragma unroll
           for (int h = 0; h < 4; ++h) {
             v[q][i][2 * h] = __uint_as_float(w[h] << 16);
             v[q][i][2 * h + 1] = __uint_as_float(w[h] & 0xffff0000u);
           }
           if (add) {  // second bf16 operand (LYNXNet: the step-invariant conditioner projection, hoisted out of the loop)
-            const uint4 qa = *reinterpret_cast<const uint4*>(add + r * C + e);
-            const uint32_t wa[4] = {qa.x, qa.y, qa.z, qa.w};
+            const uint32_t wa[4] = {rawa[q][i].x, rawa[q][i].y, rawa[q][i].z, rawa[q][i].w};
 #pragma unroll
             for (int h = 0; h < 4; ++h) {
               v[q][i][2 * h] += __uint_as_float(wa[h] << 16);
@@ -276,13 +309,14 @@ __global__ void __launch_bounds__(256) layernorm_kernel(__nv_bfloat16* __restric
         }
       }
     }
+    if (r0 + nwarps * kRows < rows) fetch(r0 + nwarps * kRows);  // next row group in flight during the reductions below
 #pragma unroll
     for (int q = 0; q < kRows; ++q)
       for (int s = 16; s > 0; s >>= 1) sum[q] += __shfl_xor_sync(0xffffffffu, sum[q], s);
     float mean[kRows], sq[kRows];
 #pragma unroll
     for (int q = 0; q < kRows; ++q) {
-      mean[q] = sum[q] / static_cast<float>(C);
+      mean[q] = sum[q] * inv_c;
       sq[q] = 0.f;
 #pragma unroll
       for (int i = 0; i < kMaxChunks; ++i) {
@@ -290,8 +324,8 @@ __global__ void __launch_bounds__(256) layernorm_kernel(__nv_bfloat16* __restric
         if (i < nch && e < C) {
 #pragma unroll
           for (int h = 0; h < 8; ++h) {
-            const float d = v[q][i][h] - mean[q];
-            sq[q] = fmaf(d, d, sq[q]);
+            v[q][i][h] -= mean[q];
+            sq[q] = fmaf(v[q][i][h], v[q][i][h], sq[q]);
           }
         }
       }
@@ -302,18 +336,17 @@ __global__ void __launch_bounds__(256) layernorm_kernel(__nv_bfloat16* __restric
 #pragma unroll
     for (int q = 0; q < kRows; ++q) {
       const long r = r0 + q < rows ? r0 + q : rows - 1;
-      const float rstd = rsqrtf(sq[q] / static_cast<float>(C) + eps);
+      const float rstd = rsqrtf(sq[q] * inv_c + eps);
 #pragma unroll
       for (int i = 0; i < kMaxChunks; ++i) {
         const int e = (i * 32 + lane) * 8;
         if (i < nch && e < C) {
-          const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + e)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + e) + 1);
-          const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + e)), b1 = __ldg(reinterpret_cast<const float4*>(beta + e) + 1);
-          const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-          const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+          float g8[8], b8[8];
+          if (!kHoist) load_gb(i, g8, b8);
           float o[8];
 #pragma unroll
-          for (int h = 0; h < 8; ++h) o[h] = (v[q][i][h] - mean[q]) * rstd * gg[h] + bb[h];
+          for (int h = 0; h < 8; ++h)
+            o[h] = fmaf(v[q][i][h] * rstd, kHoist ? gg[kHoist ? i : 0][h] : g8[h], kHoist ? bb[kHoist ? i : 0][h] : b8[h]);
           uint4 qo;
           qo.x = pack_bf16(o[0], o[1]); qo.y = pack_bf16(o[2], o[3]); qo.z = pack_bf16(o[4], o[5]); qo.w = pack_bf16(o[6], o[7]);
           *reinterpret_cast<uint4*>(y + r * C + e) = qo;
