@@ -23,6 +23,7 @@
 #include "wgrad_kernel.cuh"
 #include "conv_small_kernel.cuh"
 #include "dwconv_mma_kernel.cuh"
+#include "gemm_pair_kernel.cuh"
 
 using namespace dsb;
 
@@ -149,7 +150,44 @@ static int launch_gemm_t(const GemmParams& p, cudaStream_t st) {
   return 0;
 }
 
+// CTA-pair kernel (gemm_pair_kernel.cuh): 256-frame x 256-column tiles on cluster pairs.
+template <int EPI>
+static int launch_gemm_pair_t(const GemmParams& p0, cudaStream_t st) {
+  static bool attr_done = false;
+  auto kern = ds_gemm_pair_kernel<EPI>;
+  if (!attr_done) {
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGpSmemBytes));
+    attr_done = true;
+  }
+  GemmParams p = p0;
+  p.tiles_t = ceil_div(p.T, 256);
+  p.total_tiles = p.B * p.tiles_t * p.n_tiles;
+  const int max_pairs = g_num_sms / 2;
+  const int pairs = p.total_tiles < max_pairs ? p.total_tiles : max_pairs;
+  CUDA_TRY(launch_k(kern, dim3(2 * pairs), dim3(kGemmThreads), kGpSmemBytes, st, p));
+  return 0;
+}
+// The pair kernel takes over a BN = 256 GEMM when the weights came with a 128-row map and 256-frame tiles do not pad the
+// utterances much more than 128-frame tiles do and there are at least four waves of tiles.  DSB200_GEMM_PAIR=0 keeps the single-CTA kernel (A/B runs, parity tests).
+static bool gemm_pair_eligible(int BN, const GemmParams& p, bool split) {
+  static const bool off = [] { const char* e = getenv("DSB200_GEMM_PAIR"); return e && !strcmp(e, "0"); }();
+  if (off || split || BN != 256 || !p.has_pair) return false;
+  if ((long)p.B * ceil_div(p.T, 128) * p.n_tiles < 4L * g_num_sms) return false;  // few tiles: 128-frame tiles spread wider (measured)
+  return (long)ceil_div(p.T, 256) * 256 * 8 <= (long)ceil_div(p.T, 128) * 128 * 9;
+}
+
 static int launch_gemm(int BN, int epi, const GemmParams& p, cudaStream_t st, bool split = false) {
+  if (gemm_pair_eligible(BN, p, split)) {
+    switch (epi) {
+      case EPI_LINEAR: return launch_gemm_pair_t<EPI_LINEAR>(p, st);
+      case EPI_RES: return launch_gemm_pair_t<EPI_RES>(p, st);
+      case EPI_OUTF32: return launch_gemm_pair_t<EPI_OUTF32>(p, st);
+      case EPI_SWIGLU: return launch_gemm_pair_t<EPI_SWIGLU>(p, st);
+      case EPI_GATEBWD: return launch_gemm_pair_t<EPI_GATEBWD>(p, st);
+      case EPI_GATE: return launch_gemm_pair_t<EPI_GATE>(p, st);
+      default: break;
+    }
+  }
 #define DS_CASE(bn, e) \
   if (BN == bn && epi == e) return split ? launch_gemm_t<bn, e, true>(p, st) : launch_gemm_t<bn, e, false>(p, st);
   DS_CASE(64, EPI_LINEAR) DS_CASE(128, EPI_LINEAR) DS_CASE(256, EPI_LINEAR)
@@ -256,6 +294,7 @@ struct ds_plan {
   bool packed_ok = false;
   CUtensorMap tm_whead, tm_w1, tm_w2, tm_wsk, tm_wsp, tm_wout;
   CUtensorMap tm_w1h, tm_w2h;  // 128-row boxes: each CTA of a pair loads half of a 256-row weight tile
+  CUtensorMap tm_wheadh, tm_wskh, tm_wsph;  // the same for the head / deferred-skip / skip-projection GEMMs (gemm_pair_kernel.cuh)
   // "small problem" path (a session with too few frame tiles to fill the SMs runs the unfused GEMMs with narrow N tiles so
   // that the work spreads over output channels instead): second gate pack permuted for 128-row passes + narrow-box maps
   int has_small;
@@ -430,6 +469,11 @@ extern "C" int ds_plan_pack_weights(ds_plan* p, const ds_wavenet_weights* w, voi
   DS_TRY(make_weight_map(&p->tm_w1h, base + p->o_w1, p->K1 * Sm, L * 2 * C, 128));
   DS_TRY(make_weight_map(&p->tm_w2h, base + p->o_w2, C * Sm, L * C, 128));
   DS_TRY(make_weight_map(&p->tm_wsk, base + p->o_wsk, L * C * Sm, C, p->BN_C));
+  if (p->BN_C == 256) {
+    DS_TRY(make_weight_map(&p->tm_wheadh, base + p->o_whead, p->FMp * Sm, C, 128));
+    DS_TRY(make_weight_map(&p->tm_wskh, base + p->o_wsk, L * C * Sm, C, 128));
+    DS_TRY(make_weight_map(&p->tm_wsph, base + p->o_wsp, C * Sm, C, 128));
+  }
   DS_TRY(make_weight_map(&p->tm_wsp, base + p->o_wsp, C * Sm, C, p->BN_C));
   DS_TRY(make_weight_map(&p->tm_wout, base + p->o_wout, C * Sm, p->FMr, p->BN_O));
   if (p->has_small) {
@@ -708,6 +752,8 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   };
   // head: relu(input_projection(x)) (+ d_0 so that layer 0 reads x + d directly)      wavenet.py:86-88,36
   g.tmA0 = s->tm_xb; g.tmB = small ? p->tm_wheads : p->tm_whead;
+  const bool pair_ok = !small && !split && p->BN_C == 256;
+  g.has_pair = pair_ok; if (pair_ok) g.tmBh = p->tm_wheadh;
   g.a0_c0 = 0; g.kb_a0 = p->FMp / 64; g.n_taps = 1; g.dil = 0; g.kb_a1 = 0; g.b_row0 = 0;
   g.relu = 1; g.bias = (const float*)(pk + p->o_bhead); g.vec_add = dtab; g.vec_sub = nullptr;
   g.out = xt; g.ld_out = C * S; g.out_c0 = 0;
@@ -723,6 +769,7 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   } else {
   for (int l = 0; l < L; ++l) {
     // gate GEMM: dilated conv (3 taps) + conditioner projection, sigmoid*tanh epilogue   wavenet.py:35-42
+    g.has_pair = 0;  // the unfused layer GEMMs stay on the single-CTA kernel (their fused replacement is the pair kernel)
     g.tmA0 = s->tm_xt; g.tmA1 = s->tm_cond; g.tmB = small ? p->tm_w1s : p->tm_w1;
     g.a0_c0 = 0; g.kb_a0 = C / 64; g.n_taps = 3; g.dil = 1 << (l % p->cfg.dilation_cycle_length); g.kb_a1 = p->H / 64;
     g.b_row0 = l * 2 * C; g.relu = 0; g.bias = bias1 + (size_t)l * 2 * C;
@@ -751,6 +798,7 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   // deferred skip: sum_l skip_l = [z_0 | ... | z_{L-1}] x [Wskip_0 | ... | Wskip_{L-1}]^T, accumulated in TMEM;
   // then / sqrt(L)                                                                       wavenet.py:44-48,96
   g.tmA0 = s->tm_z; g.tmB = small ? p->tm_wsks : p->tm_wsk;
+  g.has_pair = pair_ok; if (pair_ok) g.tmBh = p->tm_wskh;
   g.a0_c0 = 0; g.kb_a0 = L * C / 64; g.n_taps = 1; g.kb_a1 = 0; g.b_row0 = 0; g.relu = 0;
   g.scale = 1.0f / sqrtf((float)L);
   g.bias = (const float*)(pk + p->o_bsk); g.vec_add = nullptr; g.vec_sub = nullptr; g.res_in = nullptr;
@@ -761,12 +809,14 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   ++*launches;
   // relu(skip_projection)                                                                wavenet.py:97-98
   g.tmA0 = s->tm_s1; g.tmB = small ? p->tm_wsps : p->tm_wsp; g.kb_a0 = C / 64; g.relu = 1; g.scale = 1.0f;
+  if (pair_ok) g.tmBh = p->tm_wsph;
   g.bias = (const float*)(pk + p->o_bsp); g.out = s2;
   g.a0_lo = C; g.w_lo = C;
   DS_TRY(launch_gemm(bnC, EPI_LINEAR, g, st, split));
   ++*launches;
   // output_projection -> fp32 [B][T][F*M]                                                 wavenet.py:99
   g.tmA0 = s->tm_s2; g.tmB = p->tm_wout; g.relu = 0;
+  g.has_pair = 0;
   g.bias = (const float*)(pk + p->o_bout); g.out = out; g.ld_out = p->FM; g.n_real = p->FM;
   shape(p->FMr / p->BN_O);
   DS_TRY(launch_gemm(p->BN_O, EPI_OUTF32, g, st, split));
@@ -899,6 +949,10 @@ extern "C" int ds_debug_gemm(const ds_gemm_desc* d, void* stream) {
   DS_TRY(make_act_map(&g.tmA0, d->a0, d->a0_channels, d->T, d->B));
   if (d->kb_a1 > 0) DS_TRY(make_act_map(&g.tmA1, d->a1, d->a1_channels, d->T, d->B));
   DS_TRY(make_weight_map(&g.tmB, d->w, d->w_k, d->w_rows, d->BN));
+  if (d->BN == 256) {
+    DS_TRY(make_weight_map(&g.tmBh, d->w, d->w_k, d->w_rows, 128));
+    g.has_pair = 1;
+  }
   g.T = d->T; g.B = d->B; g.tiles_t = ceil_div(d->T, 128); g.n_tiles = d->n_tiles;
   g.total_tiles = d->B * g.tiles_t * d->n_tiles;
   g.a0_c0 = d->a0_c0; g.kb_a0 = d->kb_a0; g.n_taps = d->n_taps; g.dil = d->dil; g.kb_a1 = d->kb_a1; g.b_row0 = d->b_row0;

@@ -27,6 +27,8 @@ struct GemmParams {
   CUtensorMap tmA0;  // primary activation source  (dims: channels, T, B)
   CUtensorMap tmA1;  // secondary activation source (conditioner), used when kb_a1 > 0
   CUtensorMap tmB;   // packed weights (dims: K, rows)
+  CUtensorMap tmBh;  // the same weights with a 128-row box (CTA-pair kernel, gemm_pair_kernel.cuh); valid when has_pair
+  int has_pair;
   int T, B, tiles_t, n_tiles, total_tiles;
   int a0_c0;   // channel offset inside A0 (selects a layer's slice of the gated-activation store)
   int kb_a0;   // 64-wide K blocks per tap from A0

@@ -31,7 +31,10 @@ def _bf(*shape, scale=1.0):
     return (torch.randn(*shape, device=dev) * scale).to(torch.bfloat16)
 
 
-@pytest.mark.parametrize("BN,B,T,K,N", [(64, 2, 200, 128, 64), (128, 1, 37, 64, 256), (256, 3, 7000, 512, 512)])
+# the last case has >= 4 x 148 tiles: it runs on the CTA-pair kernel (gemm_pair_kernel.cuh) with an odd number of K blocks and
+# a ragged last 256-frame tile
+@pytest.mark.parametrize("BN,B,T,K,N", [(64, 2, 200, 128, 64), (128, 1, 37, 64, 256), (256, 3, 7000, 512, 512),
+                                        (256, 6, 3300, 192, 1024)])
 def test_linear(BN, B, T, K, N):
     torch.manual_seed(0)
     a, w = _bf(B, T, K), _bf(N, K, scale=K ** -0.5)
@@ -46,7 +49,7 @@ def test_linear(BN, B, T, K, N):
     assert rel_l2(out.float(), ref) < 4e-3
 
 
-@pytest.mark.parametrize("BN,dil,T", [(128, 1, 300), (256, 8, 129), (128, 16, 40)])
+@pytest.mark.parametrize("BN,dil,T", [(128, 1, 300), (256, 8, 129), (128, 16, 40), (256, 4, 38000)])  # the last one: CTA-pair kernel
 def test_gate_dilated(BN, dil, T):
     """3 shifted taps (zero padded per utterance) + K-concatenated conditioner, sigmoid*tanh epilogue."""
     torch.manual_seed(1)

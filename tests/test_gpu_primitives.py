@@ -100,6 +100,31 @@ def test_gemm_gelu_swiglu_and_residual_scale():
     assert rel_l2(o.float(), a.float() @ w.float().T + res.float() + vec[:, None]) < 4e-3
 
 
+def test_gemm_pair_kernel_swiglu_and_residual():
+    """The same epilogues at a size the CTA-pair kernel takes (BN = 256, >= 4 x 148 tiles; gemm_pair_kernel.cuh)."""
+    torch.manual_seed(3)
+    B, T, K, N = 5, 2000, 128, 2048
+    a, w = _bf(B, T, K), _bf(N, K, scale=K ** -0.5)
+    bias = torch.randn(N, device=dev)
+    lib = nat.lib()
+    acc = a.float() @ w.float().T + bias
+    half = N // 2
+    perm = torch.cat([torch.cat([torch.arange(p * 128, p * 128 + 128), half + torch.arange(p * 128, p * 128 + 128)])
+                      for p in range(N // 256)]).to(dev)
+    wp, bp = w[perm].contiguous(), bias[perm].contiguous()
+    z = torch.empty(B, T, half, device=dev, dtype=torch.bfloat16)
+    d = _desc(epi=5, BN=256, B=B, T=T, a0=a, a0_channels=K, a0_c0=0, kb_a0=K // 64, n_taps=1, dil=0, kb_a1=0, w=wp, w_rows=N, w_k=K,
+              b_row0=0, n_tiles=N // 256, bias=bp, out=z, ld_out=half, out_c0=0, relu=0, scale=1.0)
+    nat.check(lib.ds_gemm(C.byref(d), _st()))
+    assert rel_l2(z.float(), acc[..., :half] * F.silu(acc[..., half:])) < 4e-3
+    res, vec = _bf(B, T, N), torch.randn(B, N, device=dev)
+    o = torch.empty_like(res)
+    d = _desc(epi=2, BN=256, B=B, T=T, a0=a, a0_channels=K, a0_c0=0, kb_a0=K // 64, n_taps=1, dil=0, kb_a1=0, w=w, w_rows=N, w_k=K,
+              b_row0=0, n_tiles=N // 256, vec_add=vec, vec_bstride=N, res_in=res, ld_res=N, out=o, ld_out=N, out_c0=0, relu=0, scale=0.5)
+    nat.check(lib.ds_gemm(C.byref(d), _st()))
+    assert rel_l2(o.float(), (a.float() @ w.float().T + res.float()) * 0.5 + vec[:, None]) < 4e-3
+
+
 def test_cast_bf16_pads():
     x = torch.randn(37, 48, device=dev)
     y = torch.full((37, 64), 7.0, device=dev, dtype=torch.bfloat16)
