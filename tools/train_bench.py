@@ -2,7 +2,7 @@
 (diffsinger_b200/training.py) beside the same module as torch ops in fp32 and under bf16 autocast (what the reference's
 trainer runs, ddpm.py:212-219 through Lightning's precision plugin).  Prints one JSON line per arm.
 
-    PYTHONPATH=. python tools/train_bench.py [B T [C L]]
+    python tools/train_bench.py [B T [C L]]
 """
 import json
 import os
@@ -11,7 +11,8 @@ import time
 
 import torch
 
-import diffsinger_b200 as ds
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import diffsinger_b200 as ds  # noqa: E402
 from diffsinger_b200.synthetic import random_state_dict
 
 

@@ -1,7 +1,7 @@
 """NSF-HiFiGAN generator on one B200: the native path (diffsinger_b200/vocoder.py) beside the same module
 as plain torch ops (fp32 / TF32 and bf16 autocast) -- mel frames per second, 44.1 kHz configuration (hop 512).
 
-    PYTHONPATH=. python tools/vocoder_bench.py [B T]
+    python tools/vocoder_bench.py [B T]
 """
 import json
 import os
@@ -9,6 +9,7 @@ import sys
 
 import torch
 
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from diffsinger_b200.vocoder import DEFAULT_CONFIG, Generator
 
 
