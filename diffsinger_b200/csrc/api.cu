@@ -24,6 +24,7 @@
 #include "conv_small_kernel.cuh"
 #include "dwconv_mma_kernel.cuh"
 #include "gemm_pair_kernel.cuh"
+#include "gemm_splitk_kernel.cuh"
 
 using namespace dsb;
 
@@ -176,7 +177,33 @@ static bool gemm_pair_eligible(int BN, const GemmParams& p, bool split) {
   return (long)ceil_div(p.T, 256) * 256 * 8 <= (long)ceil_div(p.T, 128) * 128 * 9;
 }
 
+// Split-K kernel (gemm_splitk_kernel.cuh): a cluster of 4 CTAs per tile when the tiles would leave 3/4 of the SMs idle.
+template <int BN, int EPI>
+static int launch_gemm_splitk_t(const GemmParams& p, cudaStream_t st) {
+  static bool attr_done = false;
+  auto kern = ds_gemm_splitk_kernel<BN, EPI>;
+  if (!attr_done) {
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SplitKCfg<BN>::kSmemBytes));
+    attr_done = true;
+  }
+  CUDA_TRY(launch_k(kern, dim3(kSplitK * p.total_tiles), dim3(kGemmThreads), SplitKCfg<BN>::kSmemBytes, st, p));
+  return 0;
+}
+static bool gemm_splitk_eligible(int BN, const GemmParams& p, bool split) {
+  static const bool off = [] { const char* e = getenv("DSB200_SPLITK"); return e && !strcmp(e, "0"); }();
+  if (off || split || (BN != 64 && BN != 128)) return false;
+  // measured (profiles/r01_launches_small.txt): a GEMM of this size costs ~7 us before its first K block and ~0.3 us per K block
+  // after it, so the cluster's two barriers and the reduction only pay for long K (the deferred skip GEMM, K = L*C; dcond, K = 2LC)
+  return p.total_tiles * kSplitK <= g_num_sms && p.n_taps * p.kb_a0 + p.kb_a1 >= 64;
+}
+
 static int launch_gemm(int BN, int epi, const GemmParams& p, cudaStream_t st, bool split = false) {
+  if (gemm_splitk_eligible(BN, p, split)) {
+#define DS_SK(bn, e) if (BN == bn && epi == e) return launch_gemm_splitk_t<bn, e>(p, st);
+    DS_SK(64, EPI_LINEAR) DS_SK(128, EPI_LINEAR) DS_SK(64, EPI_RES) DS_SK(128, EPI_RES) DS_SK(64, EPI_OUTF32) DS_SK(128, EPI_OUTF32)
+    DS_SK(64, EPI_GATEBWD) DS_SK(128, EPI_GATEBWD) DS_SK(128, EPI_GATE) DS_SK(128, EPI_SWIGLU)
+#undef DS_SK
+  }
   if (gemm_pair_eligible(BN, p, split)) {
     switch (epi) {
       case EPI_LINEAR: return launch_gemm_pair_t<EPI_LINEAR>(p, st);

@@ -34,7 +34,9 @@ def _bf(*shape, scale=1.0):
 # the last case has >= 4 x 148 tiles: it runs on the CTA-pair kernel (gemm_pair_kernel.cuh) with an odd number of K blocks and
 # a ragged last 256-frame tile
 @pytest.mark.parametrize("BN,B,T,K,N", [(64, 2, 200, 128, 64), (128, 1, 37, 64, 256), (256, 3, 7000, 512, 512),
-                                        (256, 6, 3300, 192, 1024)])
+                                        (256, 6, 3300, 192, 1024),
+                                        # few tiles x long K: the split-K cluster kernel (gemm_splitk_kernel.cuh), ragged last tile
+                                        (64, 1, 300, 4096, 512), (128, 2, 200, 4160, 256)])
 def test_linear(BN, B, T, K, N):
     torch.manual_seed(0)
     a, w = _bf(B, T, K), _bf(N, K, scale=K ** -0.5)

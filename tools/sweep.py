@@ -114,6 +114,10 @@ def variance(T, iters=20):
 
 def main():
     what = sys.argv[1:] or ["acoustic", "lynxnet", "reflow", "variance", "grid"]
+    if what[0] == "one":  # one case, e.g. for a launch list:  sweep.py one ddpm dpm-solver B T [C L]
+        a = what[1:]
+        acoustic(a[0], a[1], int(a[2]), int(a[3]), *(int(v) for v in a[4:6]))
+        return
     if "acoustic" in what:
         for algo in ("ddim", "pndm", "dpm-solver", "unipc"):
             if algo == "pndm":
