@@ -536,16 +536,30 @@ struct ds_session {
   bool cond_set = false;
   bool pdl = true;     // DSB200_PDL=0 turns programmatic dependent launch off
   bool small = false;  // too few frame tiles to fill the SMs: unfused GEMMs with narrow N tiles (plan->has_small)
+  bool medium = false; // between the two: unfused GEMMs with the plan's 256-wide tiles (session_is_medium)
 };
 
 // one CTA pair of the fused layer kernel owns a 256-frame tile and walks ALL output channels of it serially (~35 us at
 // C = 512); below ~1/4 occupancy of the 74 pairs it is faster to spread over output channels instead (unfused GEMMs with
 // narrow N tiles).  DSB200_SMALL=0/1 forces the choice.
+constexpr int kMediumLo = 12, kMediumHi = 44;  // CTA-pair tiles (256 frames each) of the session
 static bool session_is_small(const ds_plan* p, int B, int T) {
   const char* se = getenv("DSB200_SMALL");
   const int pair_tiles = B * ceil_div(T, 256);
   const int sms = g_num_sms ? g_num_sms : 148;
-  return p->has_small && (se ? atoi(se) != 0 : pair_tiles * 4 <= sms / 2);
+  return p->has_small && (se ? atoi(se) != 0 : (pair_tiles * 4 <= sms / 2 && pair_tiles < kMediumLo));
+}
+
+// Between the small path and a full wave of the fused kernel (74 CTA pairs x 256 frames) the fused kernel's tile pairs are too
+// few to fill the SMs but each still walks all output channels serially; the unfused GEMMs with 256-wide tiles spread the same
+// work over frames x channels.  Measured (B200, C = 512, L = 20, DPM-Solver++ 20): 4000 frames 14.9 (small) -> 13.1 ms,
+// 8000 frames 22.4 (fused) -> 17.2 ms, 16000 frames 26.7 (fused) vs 31.9 ms.  DSB200_MEDIUM=0/1 forces the choice.
+static bool session_is_medium(const ds_plan* p, int B, int T) {
+  const char* se = getenv("DSB200_MEDIUM");
+  const int pair_tiles = B * ceil_div(T, 256);
+  if (!p->fused || p->split) return false;
+  if (se) return atoi(se) != 0;
+  return pair_tiles >= kMediumLo && pair_tiles <= kMediumHi;
 }
 
 static void session_layout(const ds_plan* p, int B, int T, int max_times, int per_sample, ds_session* s) {
@@ -600,6 +614,7 @@ extern "C" int ds_session_create(ds_plan* plan, int32_t B, int32_t T, int32_t ma
   }
   s->ws = (uint8_t*)workspace;
   s->small = session_is_small(plan, B, T);
+  s->medium = !s->small && session_is_medium(plan, B, T);
   {
     const char* pe = getenv("DSB200_PDL");
     s->pdl = !(pe && atoi(pe) == 0);
@@ -765,7 +780,7 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
     bool prev;
     explicit PdlScope(bool on) : prev(t_pdl) { t_pdl = on; }
     ~PdlScope() { t_pdl = prev; }
-  } pdl_scope((s->small || !s->plan->fused) && s->pdl);
+  } pdl_scope((s->small || s->medium || !s->plan->fused) && s->pdl);
   CUDA_TRY(launch_k(f32_to_bf16_pad_kernel, dim3(ew_grid(rows * p->FMp / 4, 256)), dim3(256), 0, st, xb, x, rows, p->FM, p->FMp,
                     (long)p->FMp * S, split ? p->FMp : 0));
   ++*launches;
@@ -788,7 +803,7 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   shape(C / bnC);
   DS_TRY(launch_gemm(bnC, EPI_LINEAR, g, st, split));
   ++*launches;
-  if (p->fused && !small) {
+  if (p->fused && !small && !s->medium) {
     for (int l = 0; l < L; ++l) {
       DS_TRY(session_fused_layer(s, l, time_index, st));
       ++*launches;
@@ -885,7 +900,7 @@ static int run_ops(ds_session* s, const ds_op* ops, int n_ops, float* const* buf
     bool prev;
     explicit PdlScope(bool on) : prev(t_pdl) { t_pdl = on; }
     ~PdlScope() { t_pdl = prev; }
-  } pdl_scope((s->small || !s->plan->fused) && s->pdl);
+  } pdl_scope((s->small || s->medium || !s->plan->fused) && s->pdl);
   for (int i = 0; i < n_ops; ++i) {
     const ds_op& op = ops[i];
     if (op.dst < 0 || op.dst >= n_bufs) return fail(DS_ERR_INVALID, "op %d: dst %d out of range", i, op.dst);

@@ -241,6 +241,12 @@ def test_full_size_batch_rows_match_oracle_and_are_independent(monkeypatch):
     ref = OracleWaveNet(sd, F, cycle)(spec[rows], t, cond[rows])
     assert rel_l2(y[rows], ref) < EVAL_TOL
     monkeypatch.setenv("DSB200_SMALL", "0")  # keep the 3-row session on the fused kernel so the comparison is bitwise
+    monkeypatch.setenv("DSB200_MEDIUM", "0")  # (24 tile pairs would otherwise take the unfused 256-wide path)
     with torch.no_grad():
         part = net(spec[30:33].to(dev), t.to(dev), cond[30:33].to(dev)).cpu()
     assert torch.equal(part, y[30:33])
+    # the medium path (unfused GEMMs, 256-wide tiles) on the same rows: same values up to bf16 rounding of z / x~
+    monkeypatch.setenv("DSB200_MEDIUM", "1")
+    with torch.no_grad():
+        med = net(spec[29:33].to(dev), t.to(dev), cond[29:33].to(dev)).cpu()
+    assert rel_l2(med, y[29:33]) < EVAL_TOL
