@@ -547,7 +547,11 @@ static bool session_is_small(const ds_plan* p, int B, int T) {
   const char* se = getenv("DSB200_SMALL");
   const int pair_tiles = B * ceil_div(T, 256);
   const int sms = g_num_sms ? g_num_sms : 148;
-  return p->has_small && (se ? atoi(se) != 0 : (pair_tiles * 4 <= sms / 2 && pair_tiles < kMediumLo));
+  (void)sms;
+  // measured crossovers (20-step calls, B200): C = 512: narrow tiles win below 12 tile pairs (then the medium path takes over);
+  // C = 256: 3000 frames 6.9 (small) vs 9.7 / 10.1 ms (256-wide unfused / fused), 8000 frames 10.4 vs 10.3 / 10.7 ms
+  const int limit = p->C >= 512 ? kMediumLo : 36;
+  return p->has_small && (se ? atoi(se) != 0 : pair_tiles < limit);
 }
 
 // Between the small path and a full wave of the fused kernel (74 CTA pairs x 256 frames) the fused kernel's tile pairs are too
@@ -559,6 +563,7 @@ static bool session_is_medium(const ds_plan* p, int B, int T) {
   const int pair_tiles = B * ceil_div(T, 256);
   if (!p->fused || p->split) return false;
   if (se) return atoi(se) != 0;
+  if (p->C < 512) return false;  // narrower layers: the small path stays ahead until the fused kernel fills up
   return pair_tiles >= kMediumLo && pair_tiles <= kMediumHi;
 }
 
