@@ -1148,7 +1148,8 @@ static int launch_conv_small_t(const ConvSmallParams& p, cudaStream_t st) {
     CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ConvSmallCfg<CIN, COUT>::kSmemBytes));
     attr_done = true;
   }
-  const int grid = p.total_tiles < g_num_sms ? p.total_tiles : g_num_sms;
+  const int cap = g_num_sms * kConvSmallCtasPerSm;  // per-tile latency chains (TMA -> UMMAs -> epilogue) of co-resident CTAs overlap
+  const int grid = p.total_tiles < cap ? p.total_tiles : cap;
   kern<<<grid, kConvSmallThreads, ConvSmallCfg<CIN, COUT>::kSmemBytes, st>>>(p);
   CUDA_TRY(cudaGetLastError());
   return 0;

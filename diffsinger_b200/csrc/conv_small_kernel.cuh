@@ -34,6 +34,7 @@ struct ConvSmallParams {
 
 constexpr int kConvSmallThreads = 320;  // 2 control warps + two epilogue groups of 4 warps (one per TMEM accumulator buffer)
 constexpr int kConvSmallStages = 4;
+constexpr int kConvSmallCtasPerSm = 2;  // ~40-60 KB of shared memory and 64 TMEM columns each
 constexpr int kConvSmallMaxRows = 192;  // 128 + 10 * 5 = 178 -> 184
 constexpr int kConvSmallMaxTaps = 11;
 
@@ -55,7 +56,7 @@ __device__ __forceinline__ uint64_t make_kmajor_noswz_desc(uint32_t smem_addr, u
 }
 
 template <int CIN, int COUT>
-__global__ void __launch_bounds__(kConvSmallThreads, 1) ds_conv_small_kernel(const __grid_constant__ ConvSmallParams p) {
+__global__ void __launch_bounds__(kConvSmallThreads, kConvSmallCtasPerSm) ds_conv_small_kernel(const __grid_constant__ ConvSmallParams p) {
   using Cfg = ConvSmallCfg<CIN, COUT>;
   constexpr int S = kConvSmallStages;
   extern __shared__ uint8_t smem_raw[];
@@ -159,20 +160,25 @@ __global__ void __launch_bounds__(kConvSmallThreads, 1) ds_conv_small_kernel(con
       const int tile = blockIdx.x + it * gridDim.x;
       const int tt = tile % p.tiles_t, b = tile / p.tiles_t;
       const int as = it & 1;
-      mbar_wait(&tmem_full[as], (it >> 1) & 1);
-      tc_fence_after();
       const int t = tt * 128 + quad * 32 + lane;
       const bool valid = t < p.T;
       const size_t row = static_cast<size_t>(b) * p.T + (valid ? t : 0);
+      uint4 rq[COUT / 8];  // the residual row does not depend on the MMAs: in flight while this tile's accumulator completes
+      if (p.res) {
+        const uint4* rp = reinterpret_cast<const uint4*>(p.res + row * COUT);
+#pragma unroll
+        for (int i = 0; i < COUT / 8; ++i) rq[i] = __ldg(rp + i);
+      }
+      mbar_wait(&tmem_full[as], (it >> 1) & 1);
+      tc_fence_after();
       uint32_t acc[32];
       tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * 32, acc);
       float v[COUT];
       if (p.res) {
-        const uint4* rp = reinterpret_cast<const uint4*>(p.res + row * COUT);
 #pragma unroll
         for (int i = 0; i < COUT / 8; ++i) {
           float r8[8];
-          unpack_bf16x8(__ldg(rp + i), r8);
+          unpack_bf16x8(rq[i], r8);
 #pragma unroll
           for (int j = 0; j < 8; ++j) v[8 * i + j] = r8[j] + bias[8 * i + j];
         }
