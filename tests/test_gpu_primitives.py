@@ -53,8 +53,12 @@ def test_layernorm(rows, Cc):
     assert rel_l2(y.float(), ref) < 4e-3
 
 
+# k = 31 / 7 with channels % 32 == 0 run on the mma.sync Toeplitz kernel (128-frame tiles, chains of up to 16 tiles per CTA), the rest
+# on the fp32-FMA kernel: single frames, tile boundaries, a 17-tile utterance (two chained CTAs), asymmetric padding, 32 and 48 channels
 @pytest.mark.parametrize("k,pad,act,B,T,CH", [(31, 15, 2, 2, 700, 1024), (31, 15, 3, 1, 40, 256), (7, 3, 0, 3, 129, 512),
-                                            (3, 1, 1, 1, 5, 64)])
+                                            (3, 1, 1, 1, 5, 64), (31, 15, 0, 2, 1, 32), (31, 15, 1, 1, 127, 64), (31, 15, 2, 3, 128, 32),
+                                            (7, 3, 3, 2, 257, 96), (31, 30, 0, 1, 300, 64), (31, 0, 2, 2, 300, 64), (7, 6, 1, 1, 2100, 32),
+                                            (31, 15, 2, 70, 33, 32), (31, 15, 2, 1, 200, 48), (7, 3, 0, 1, 64, 16)])
 def test_dwconv(k, pad, act, B, T, CH):
     torch.manual_seed(1)
     x = _bf(B, T, CH)
@@ -63,7 +67,7 @@ def test_dwconv(k, pad, act, B, T, CH):
     slope = torch.rand(CH, device=dev) * 0.5
     y = torch.empty_like(x)
     nat.check(nat.lib().ds_dwconv(y.data_ptr(), x.data_ptr(), w.data_ptr(), bias.data_ptr(), slope.data_ptr(), B, T, CH, k, pad, act, _st()))
-    ref = F.conv1d(x.float().transpose(1, 2), w[:, None, :], bias, padding=pad, groups=CH)
+    ref = F.conv1d(F.pad(x.float().transpose(1, 2), (pad, k - 1 - pad)), w[:, None, :], bias, groups=CH)  # pad = zeros on the left
     ref = {0: lambda v: v, 1: F.relu, 2: lambda v: torch.where(v > 0, v, slope[None, :, None] * v), 3: F.silu}[act](ref).transpose(1, 2)
     assert y.shape == ref.shape
     assert rel_l2(y.float(), ref) < 4e-3
