@@ -801,13 +801,22 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   g.tmA0 = s->tm_xb; g.tmB = small ? p->tm_wheads : p->tm_whead;
   const bool pair_ok = !small && !split && p->BN_C == 256;
   g.has_pair = pair_ok; if (pair_ok) g.tmBh = p->tm_wheadh;
+  auto out_map = [&](void* base, int ld) -> int {  // store map of a pair-kernel GEMM's bf16 output
+    g.has_out_map = 0;
+    if (!pair_ok) return 0;
+    DS_TRY(make_store_map(&g.tmOut, base, ld, T, B));
+    g.has_out_map = 1;
+    return 0;
+  };
   g.a0_c0 = 0; g.kb_a0 = p->FMp / 64; g.n_taps = 1; g.dil = 0; g.kb_a1 = 0; g.b_row0 = 0;
   g.relu = 1; g.bias = (const float*)(pk + p->o_bhead); g.vec_add = dtab; g.vec_sub = nullptr;
   g.out = xt; g.ld_out = C * S; g.out_c0 = 0;
   g.a0_lo = p->FMp; g.w_lo = p->FMp; g.out_lo = C;  // lo-half offsets: only read by the split instantiations
   shape(C / bnC);
+  DS_TRY(out_map(xt, C * S));
   DS_TRY(launch_gemm(bnC, EPI_LINEAR, g, st, split));
   ++*launches;
+  g.has_out_map = 0;
   if (p->fused && !small && !s->medium) {
     for (int l = 0; l < L; ++l) {
       DS_TRY(session_fused_layer(s, l, time_index, st));
@@ -852,6 +861,7 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   g.out = s1; g.ld_out = C * S; g.out_c0 = 0;
   g.a0_lo = L * C; g.w_lo = L * C; g.out_lo = C;
   shape(C / bnC);
+  DS_TRY(out_map(s1, C * S));
   DS_TRY(launch_gemm(bnC, EPI_LINEAR, g, st, split));
   ++*launches;
   // relu(skip_projection)                                                                wavenet.py:97-98
@@ -859,7 +869,9 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   if (pair_ok) g.tmBh = p->tm_wsph;
   g.bias = (const float*)(pk + p->o_bsp); g.out = s2;
   g.a0_lo = C; g.w_lo = C;
+  DS_TRY(out_map(s2, C * S));
   DS_TRY(launch_gemm(bnC, EPI_LINEAR, g, st, split));
+  g.has_out_map = 0;
   ++*launches;
   // output_projection -> fp32 [B][T][F*M]                                                 wavenet.py:99
   g.tmA0 = s->tm_s2; g.tmB = p->tm_wout; g.relu = 0;
@@ -999,6 +1011,10 @@ extern "C" int ds_debug_gemm(const ds_gemm_desc* d, void* stream) {
   if (d->BN == 256) {
     DS_TRY(make_weight_map(&g.tmBh, d->w, d->w_k, d->w_rows, 128));
     g.has_pair = 1;
+    if (d->epi != EPI_OUTF32 && d->epi != EPI_CPROJ && d->ld_out % 8 == 0 && ((uintptr_t)d->out & 15) == 0) {
+      DS_TRY(make_store_map(&g.tmOut, d->out, d->ld_out, d->T, d->B));
+      g.has_out_map = 1;
+    }
   }
   g.T = d->T; g.B = d->B; g.tiles_t = ceil_div(d->T, 128); g.n_tiles = d->n_tiles;
   g.total_tiles = d->B * g.tiles_t * d->n_tiles;

@@ -39,6 +39,22 @@ __device__ __forceinline__ void st_act32(__nv_bfloat16* ptr, int lo_off, const f
   if constexpr (kSplit) st_split_bf16x32(ptr, lo_off, v);
   else st_bf16x32(ptr, v);
 }
+// 32 consecutive output channels of this lane's frame, starting at channel `ch` of p.out: through the warp's staging tile and
+// one TMA store when the kernel provides one (all lanes call this; rows beyond T are clipped by the map), else per-lane stores.
+template <bool kSplit>
+__device__ __forceinline__ void epi_store32(const GemmParams& p, const EpiStage& es, size_t row, int ch, int b, bool valid,
+                                            const float (&v)[32]) {
+  if constexpr (!kSplit) {
+    if (es.on) {
+      uint32_t o[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) o[i] = pack_bf16(v[2 * i], v[2 * i + 1]);
+      warp_store_tile(&p.tmOut, es.sw, es.lane, o, ch, es.tw0, b, es.tw0 < p.T);
+      return;
+    }
+  }
+  if (valid) st_act32<kSplit>(reinterpret_cast<__nv_bfloat16*>(p.out) + row * p.ld_out + ch, p.out_lo, v);
+}
 __device__ __forceinline__ float sigmoid_accurate(float x) { return 1.0f / (1.0f + expf(-x)); }
 
 __device__ __forceinline__ void ld_x4(const __nv_bfloat16* ptr, uint4 (&q)[4]) {
@@ -48,12 +64,12 @@ __device__ __forceinline__ void ld_x4(const __nv_bfloat16* ptr, uint4 (&q)[4]) {
 
 // `half` in {0,1}: the two epilogue warps that share a TMEM lane quadrant interleave the 32-column chunks.
 template <int BN, int EPI, bool kSplit>
-__device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t taddr, int b, int t, bool valid, int nt, int half) {
+__device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t taddr, int b, int t, bool valid, int nt, int half,
+                                              const EpiStage& es) {
   const size_t row = static_cast<size_t>(b) * p.T + (valid ? t : 0);
   if constexpr (EPI == EPI_GATE) {
     // columns [0, BN/2) = gate pre-activations, [BN/2, BN) = filter pre-activations of the SAME channels
     constexpr int H = BN / 2;
-    __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.out) + row * p.ld_out + p.out_c0 + nt * H;
     const float* bias = p.bias + nt * BN;
 #pragma unroll 1
     for (int c = half; c < H / 32; c += 2) {
@@ -75,13 +91,12 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
           z[j] = sg * tanh_approx(fj);
         }
       }
-      if (valid) st_act32<kSplit>(out + c * 32, p.out_lo, z);
+      epi_store32<kSplit>(p, es, row, p.out_c0 + nt * H + c * 32, b, valid, z);
     }
   } else if constexpr (EPI == EPI_SWIGLU) {
     // columns [0, BN/2) = "out" half, [BN/2, BN) = "gate" half of the SAME channels (pack-time row permutation):
     // z = out * silu(gate)   (SwiGLU, modules/commons/common_layers.py; LYNXConvModule, lynxnet.py:57)
     constexpr int H = BN / 2;
-    __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.out) + row * p.ld_out + p.out_c0 + nt * H;
     const float* bias = p.bias + nt * BN;
 #pragma unroll 1
     for (int c = half; c < H / 32; c += 2) {
@@ -99,7 +114,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
         if constexpr (kSplit) z[j] = aj * gj * sigmoid_accurate(gj);
         else z[j] = aj * gj * fmaf(0.5f, tanh_approx(0.5f * gj), 0.5f);  // MUFU path: the tile's MMAs take only 4 k cycles
       }
-      if (valid) st_act32<kSplit>(out + c * 32, p.out_lo, z);
+      epi_store32<kSplit>(p, es, row, p.out_c0 + nt * H + c * 32, b, valid, z);
     }
   } else if constexpr (EPI == EPI_GATEBWD) {
     // training backward of the gated activation, fused behind dy = W2^T [h | dskip] (wavenet.py:41-44 under autograd):
@@ -108,7 +123,6 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
     const int n0 = nt * BN;
     const int Ch = p.n_real;
     const __nv_bfloat16* zr = p.res_in + row * p.ld_res + n0;
-    __nv_bfloat16* dz = reinterpret_cast<__nv_bfloat16*>(p.out) + row * p.ld_out + p.out_c0 + n0;
 #pragma unroll 1
     for (int c = half; c < BN / 32; c += 2) {
       uint32_t a[32];
@@ -137,10 +151,8 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
           }
         }
       }
-      if (valid) {
-        st_bf16x32(dz + c * 32, og);
-        st_bf16x32(dz + Ch + c * 32, of);
-      }
+      epi_store32<false>(p, es, row, p.out_c0 + n0 + c * 32, b, valid, og);
+      epi_store32<false>(p, es, row, p.out_c0 + n0 + Ch + c * 32, b, valid, of);
     }
   } else if constexpr (EPI == EPI_CPROJ) {
     // hoisted conditioner projection (wavenet.py:35, step-invariant): f16 out = (acc + bias) in the gate kernel's packed
@@ -174,7 +186,6 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
     const int n0 = nt * BN;
     const float* rv = p.vec_add + static_cast<size_t>(b) * p.vec_bstride + n0;
     const __nv_bfloat16* xin = p.res_in + row * p.ld_res + n0;
-    __nv_bfloat16* xout = reinterpret_cast<__nv_bfloat16*>(p.out) + row * p.ld_out + p.out_c0 + n0;
     uint4 xq[4];
     ld_x4(xin + half * 32, xq);
 #pragma unroll 1
@@ -210,7 +221,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
           v[j + 1] = fmaf(__uint_as_float(a[j + 1]) + __uint_as_float(w[h] & 0xffff0000u), p.scale, rr[j + 1]);
         }
       }
-      if (valid) st_act32<kSplit>(xout + c * 32, p.out_lo, v);
+      epi_store32<kSplit>(p, es, row, p.out_c0 + n0 + c * 32, b, valid, v);
       if (p.out2) {  // pre-activated copy for the next convolution (HiFi-GAN ResBlock, nsf_hifigan/models.py:60-67)
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = v[j] > 0.0f ? v[j] : v[j] * p.slope2;
@@ -262,7 +273,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] += da[j];
         }
-        if (valid) st_act32<kSplit>(reinterpret_cast<__nv_bfloat16*>(p.out) + row * p.ld_out + p.out_c0 + n0 + c * 32, p.out_lo, v);
+        epi_store32<kSplit>(p, es, row, p.out_c0 + n0 + c * 32, b, valid, v);
       }
     }
   }

@@ -29,6 +29,8 @@ struct GemmParams {
   CUtensorMap tmB;   // packed weights (dims: K, rows)
   CUtensorMap tmBh;  // the same weights with a 128-row box (CTA-pair kernel, gemm_pair_kernel.cuh); valid when has_pair
   int has_pair;
+  CUtensorMap tmOut; // bf16 output as a store map (dims: ld_out channels, T, B; box 32 x 32, SWIZZLE_64B); valid when has_out_map
+  int has_out_map;   // the pair kernel's epilogue warps then write through TMA stores instead of per-lane STG.128
   int T, B, tiles_t, n_tiles, total_tiles;
   int a0_c0;   // channel offset inside A0 (selects a layer's slice of the gated-activation store)
   int kb_a0;   // 64-wide K blocks per tap from A0
@@ -67,8 +69,17 @@ struct GemmCfg {
   static constexpr uint32_t kSmemBytes = 1024 + kStages * (kABytes + kBBytes) + 256;
 };
 
+// Where an epilogue warp stages its 32 x 32 output sub-tiles for TMA stores (warp_store_tile); on = false: direct stores.
+struct EpiStage {
+  uint32_t sw = 0;  // shared-memory address of the warp's 2 KB staging tile
+  int lane = 0;
+  int tw0 = 0;      // first frame of the warp's 32 rows
+  bool on = false;
+};
+
 template <int BN, int EPI, bool kSplit>
-__device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t taddr, int b, int t, bool valid, int nt, int half);
+__device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t taddr, int b, int t, bool valid, int nt, int half,
+                                              const EpiStage& es = EpiStage{});
 
 template <int BN, int EPI, bool kSplit = false>
 __global__ void __launch_bounds__(kGemmThreads, 1) ds_gemm_kernel(const __grid_constant__ GemmParams p) {

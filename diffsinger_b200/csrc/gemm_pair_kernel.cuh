@@ -10,24 +10,28 @@
 //
 // One pipeline stage = TWO 64-wide K blocks (8 UMMAs) under one full / empty barrier pair, three stages of 64 KB.
 // Accumulators: 2 x 256 fp32 TMEM columns per CTA (its own 128 frames x 256 columns), drained by the unchanged
-// epilogue_tile<256, EPI> of gemm_epilogue.cuh.  p.tmBh is the weight map with a 128-row box; p.tiles_t counts 256-frame tiles.
+// epilogue_tile<256, EPI> of gemm_epilogue.cuh, whose bf16 outputs leave through warp-private staging tiles and TMA stores (p.tmOut;
+// the per-lane STG.128 epilogue alone took 64 of the 241 us of the LYNXNet C -> 2I product, tools/gemm_bench.py).  p.tmBh is the weight map with a 128-row box; p.tiles_t counts 256-frame tiles.
 #pragma once
 #include "gemm_epilogue.cuh"
 #include "layer2_kernel.cuh"  // kPairBBytes
 
 namespace dsb {
 
-constexpr int kGpStages = 3;
+constexpr int kGpGroup = 2;   // K blocks per pipeline stage (1 x 6 stages measured the same on LYNXNet, 2.5 % slower in training)
+constexpr int kGpStages = 6 / kGpGroup;
 constexpr uint32_t kGpABytes = 128 * 128;                                // 128 frames x 64 bf16
-constexpr uint32_t kGpStageBytes = 2 * (kGpABytes + kPairBBytes);       // [A blk0][A blk1][B blk0][B blk1]
-constexpr uint32_t kGpSmemBytes = 1024 + kGpStages * kGpStageBytes + 256;
+constexpr uint32_t kGpStageBytes = kGpGroup * (kGpABytes + kPairBBytes);  // [A blk0][A blk1][B blk0][B blk1]
+constexpr uint32_t kGpWarpStage = 2048;                                  // per epilogue warp: 32 frames x 32 channels bf16, SWIZZLE_64B
+constexpr uint32_t kGpSmemBytes = 1024 + kGpStages * kGpStageBytes + 8 * kGpWarpStage + 256;
 
 template <int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1) ds_gemm_pair_kernel(const __grid_constant__ GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);  // SWIZZLE_128B needs 1024-B alignment
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kGpStages * kGpStageBytes);
+  uint8_t* warp_stage = smem + kGpStages * kGpStageBytes;  // 8 x kGpWarpStage, 2 KB aligned
+  uint64_t* bars = reinterpret_cast<uint64_t*>(warp_stage + 8 * kGpWarpStage);
   uint64_t* full = bars;                  // leader: 2 producer arrivals + the bytes of both CTAs
   uint64_t* empty = full + kGpStages;     // per CTA: released by the leader's multicast commit
   uint64_t* tmem_full = empty + kGpStages;
@@ -80,8 +84,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1) ds_
         const int b = tile / (p.n_tiles * p.tiles_t);
         const int t0 = tt * 256 + rank * 128;
         const int row0 = p.b_row0 + nt * 256 + rank * 128;
-        for (int kb0 = 0; kb0 < num_kb; kb0 += 2) {
-          const int n = num_kb - kb0 < 2 ? num_kb - kb0 : 2;
+        for (int kb0 = 0; kb0 < num_kb; kb0 += kGpGroup) {
+          const int n = num_kb - kb0 < kGpGroup ? num_kb - kb0 : kGpGroup;
           mbar_wait(&empty[st], ph ^ 1);
           if (leader) mbar_arrive_expect_tx(&full[st], 2u * n * (kGpABytes + kPairBBytes));
           else mbar_arrive_cluster(&full[st], 0);
@@ -95,7 +99,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1) ds_
             } else {
               tma_load_3d_pair(&p.tmA1, &full[st], s + j * kGpABytes, (kb - kb_taps) * 64, t0, b);
             }
-            tma_load_2d_pair(&p.tmBh, &full[st], s + 2 * kGpABytes + j * kPairBBytes, p.b_k0 + kb * 64, row0);
+            tma_load_2d_pair(&p.tmBh, &full[st], s + kGpGroup * kGpABytes + j * kPairBBytes, p.b_k0 + kb * 64, row0);
           }
           if (++st == kGpStages) { st = 0; ph ^= 1; }
         }
@@ -113,14 +117,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1) ds_
         mbar_wait(&tmem_empty[as], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + as * 256;
-        for (int kb0 = 0; kb0 < num_kb; kb0 += 2) {
-          const int n = num_kb - kb0 < 2 ? num_kb - kb0 : 2;
+        for (int kb0 = 0; kb0 < num_kb; kb0 += kGpGroup) {
+          const int n = num_kb - kb0 < kGpGroup ? num_kb - kb0 : kGpGroup;
           mbar_wait(&full[st], ph);
           tc_fence_after();
           const uint32_t s = smem_u32(smem + st * kGpStageBytes);
           for (int j = 0; j < n; ++j) {
             const uint64_t da = make_kmajor_sw128_desc(s + j * kGpABytes);
-            const uint64_t db = make_kmajor_sw128_desc(s + 2 * kGpABytes + j * kPairBBytes);
+            const uint64_t db = make_kmajor_sw128_desc(s + kGpGroup * kGpABytes + j * kPairBBytes);
 #pragma unroll
             for (int k = 0; k < 4; ++k) umma_bf16_pair(tmem_d, da + 2 * k, db + 2 * k, idesc, ((kb0 + j) | k) != 0);
           }
@@ -144,7 +148,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1) ds_
       tc_fence_after();
       const int t = tt * 256 + rank * 128 + quad * 32 + lane;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * 256;
-      epilogue_tile<256, EPI, false>(p, taddr, b, t, t < p.T, nt, half);
+      EpiStage es;
+      es.sw = smem_u32(warp_stage + (warp - 4) * kGpWarpStage);
+      es.lane = lane;
+      es.tw0 = tt * 256 + rank * 128 + quad * 32;
+      es.on = p.has_out_map != 0;
+      if (p.vec_bstride != -12345) epilogue_tile<256, EPI, false>(p, taddr, b, t, t < p.T, nt, half, es);  // (timing hook of tools/gemm_bench.py)
       tc_fence_before();
       __syncwarp();
       if (lane == 0) {  // release the accumulator on the LEADER's barrier: one arrival per warp
@@ -153,6 +162,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1) ds_
       }
     }
   }
+  if (warp >= 4) bulk_wait_all();  // staging tiles are read out before the CTA's shared memory goes away
   tc_fence_before();
   cluster_sync_all();  // the leader's MMAs read this CTA's shared memory and write its TMEM until the very end
   if (warp == 2) {

@@ -30,24 +30,10 @@ __host__ __device__ inline uint32_t grp_smem_bytes(int max_dil) {
 
 constexpr uint32_t kGrpWarpStage = 2048;  // per epilogue warp: 32 frames x 32 channels bf16, SWIZZLE_64B
 
-// One warp's 32 x 32 bf16 sub-tile: lane = frame row, v = its 32 channels as 16 packed pairs.  Rows go to shared memory in
-// the 64-byte swizzle the store map expects (16-byte chunk index ^= (row >> 1) & 3: conflict-free), then ONE TMA store
-// writes the tile (frames beyond T are clipped by the tensor map) -- instead of 4 STG.128 per lane that each touch 32
-// different 128-byte lines.
+// one warp's 32 x 32 bf16 sub-tile -> swizzled staging tile -> one TMA store (ptx.cuh: warp_store_tile)
 __device__ __forceinline__ void grp_store_tile(const CUtensorMap* map, uint32_t sw, int lane, const uint32_t (&v)[16], int c0, int t0,
                                                int b, bool any_valid) {
-  if (lane == 0) bulk_wait_read_all();  // the previous store of this warp has drained the staging tile
-  __syncwarp();
-  const uint32_t rowa = sw + lane * 64;
-  const uint32_t x = (lane >> 1) & 3;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) st_shared_v4(rowa + ((i ^ x) << 4), v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-  fence_proxy_async_smem();
-  __syncwarp();
-  if (lane == 0 && any_valid) {
-    tma_store_3d(map, reinterpret_cast<const void*>(__cvta_shared_to_generic(sw)), c0, t0, b);
-    bulk_commit_group();
-  }
+  warp_store_tile(map, sw, lane, v, c0, t0, b, any_valid);
 }
 
 // Gate epilogue in packed half precision: z = sigmoid(g + bg) * tanh(f + bf) with sigmoid(x) = 0.5 * tanh(0.5 x) + 0.5.

@@ -59,7 +59,6 @@ __host__ __device__ inline uint32_t layer_smem_bytes(int kb_c, int stages, bool 
   return 1024u + (z_smem ? kb_c : 0) * kLayerABytes + stages * (kLayerABytes + kLayerBBytes) + 256u;
 }
 
-__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;

@@ -2,6 +2,7 @@
 // Everything here is a 1:1 wrapper of one PTX instruction; no library code.
 #pragma once
 #include <cstdint>
+#include <cuda.h>
 #include <cuda_bf16.h>
 
 namespace dsb {
@@ -88,6 +89,28 @@ __device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bu
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+// generic-proxy writes to shared memory -> visible to the async proxy (TMA stores, tensor-core operand reads)
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// One warp's 32 x 32 bf16 sub-tile: lane = frame row, v = its 32 channels as 16 packed pairs.  Rows go to a warp-private 2 KB
+// staging tile `sw` in the 64-byte swizzle the store map expects (16-byte chunk index ^= (row >> 1) & 3: conflict-free), then
+// ONE TMA store writes the tile (frames beyond T are clipped by the tensor map) -- instead of 4 STG.128 per lane that each
+// touch 32 different 128-byte lines.  Must be called by all 32 lanes.
+__device__ __forceinline__ void warp_store_tile(const CUtensorMap* map, uint32_t sw, int lane, const uint32_t (&v)[16], int c0, int t0,
+                                                int b, bool any_valid) {
+  if (lane == 0) bulk_wait_read_all();  // the previous store of this warp has drained the staging tile
+  __syncwarp();
+  const uint32_t rowa = sw + lane * 64;
+  const uint32_t x = (lane >> 1) & 3;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) st_shared_v4(rowa + ((i ^ x) << 4), v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+  fence_proxy_async_smem();
+  __syncwarp();
+  if (lane == 0 && any_valid) {
+    tma_store_3d(map, reinterpret_cast<const void*>(__cvta_shared_to_generic(sw)), c0, t0, b);
+    bulk_commit_group();
+  }
 }
 
 // ---------------------------------------------------------------- tcgen05 / TMEM
