@@ -801,9 +801,9 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   g.tmA0 = s->tm_xb; g.tmB = small ? p->tm_wheads : p->tm_whead;
   const bool pair_ok = !small && !split && p->BN_C == 256;
   g.has_pair = pair_ok; if (pair_ok) g.tmBh = p->tm_wheadh;
-  auto out_map = [&](void* base, int ld) -> int {  // store map of a pair-kernel GEMM's bf16 output
+  auto out_map = [&](void* base, int ld) -> int {  // store map of a GEMM's bf16 output (call after shape())
     g.has_out_map = 0;
-    if (!pair_ok) return 0;
+    if (split || g.total_tiles < g_num_sms) return 0;
     DS_TRY(make_store_map(&g.tmOut, base, ld, T, B));
     g.has_out_map = 1;
     return 0;
@@ -833,6 +833,7 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
     g.out = z; g.ld_out = L * C * S; g.out_c0 = l * C;
     g.a0_lo = C; g.a1_lo = p->H; g.w_lo = p->K1; g.out_lo = L * C;
     shape(2 * C / bnG);
+    DS_TRY(out_map(z, L * C * S));
     DS_TRY(launch_gemm(bnG, EPI_GATE, g, st, split));
     ++*launches;
     if (l + 1 < L) {
@@ -844,6 +845,7 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
       g.res_in = xt; g.ld_res = C * S; g.out = xt; g.ld_out = C * S; g.out_c0 = 0;
       g.a0_lo = L * C; g.w_lo = C; g.out_lo = C; g.res_lo = C;
       shape(C / bnC);
+      DS_TRY(out_map(xt, C * S));
       g.scale = 0.70710678118654752f;  // (x + residual) / sqrt(2)
       DS_TRY(launch_gemm(bnC, EPI_RES, g, st, split));
       g.scale = 1.0f;
@@ -1011,10 +1013,13 @@ extern "C" int ds_debug_gemm(const ds_gemm_desc* d, void* stream) {
   if (d->BN == 256) {
     DS_TRY(make_weight_map(&g.tmBh, d->w, d->w_k, d->w_rows, 128));
     g.has_pair = 1;
-    if (d->epi != EPI_OUTF32 && d->epi != EPI_CPROJ && d->ld_out % 8 == 0 && ((uintptr_t)d->out & 15) == 0) {
-      DS_TRY(make_store_map(&g.tmOut, d->out, d->ld_out, d->T, d->B));
-      g.has_out_map = 1;
-    }
+  }
+  // bf16 outputs leave through TMA stores when the GEMM has at least one tile per SM (below that the per-lane stores' shorter
+  // tail matters more than their LSU cost)
+  if (d->epi != EPI_OUTF32 && d->epi != EPI_CPROJ && d->ld_out % 8 == 0 && ((uintptr_t)d->out & 15) == 0 &&
+      (long)d->B * ceil_div(d->T, 128) * d->n_tiles >= g_num_sms) {
+    DS_TRY(make_store_map(&g.tmOut, d->out, d->ld_out, d->T, d->B));
+    g.has_out_map = 1;
   }
   g.T = d->T; g.B = d->B; g.tiles_t = ceil_div(d->T, 128); g.n_tiles = d->n_tiles;
   g.total_tiles = d->B * g.tiles_t * d->n_tiles;

@@ -66,7 +66,8 @@ struct GemmCfg {
   static constexpr uint32_t kABytes = 128 * 128;  // 128 frames x 64 bf16
   static constexpr uint32_t kBBytes = BN * 128;   // BN rows  x 64 bf16
   static constexpr uint32_t kTmemCols = 2 * BN;   // 128 / 256 / 512: powers of two
-  static constexpr uint32_t kSmemBytes = 1024 + kStages * (kABytes + kBBytes) + 256;
+  static constexpr uint32_t kWarpStage = 2048;    // per epilogue warp: 32 frames x 32 channels bf16 (TMA-store staging, SWIZZLE_64B)
+  static constexpr uint32_t kSmemBytes = 1024 + kStages * (kABytes + kBBytes) + 8 * kWarpStage + 256;
 };
 
 // Where an epilogue warp stages its 32 x 32 output sub-tiles for TMA stores (warp_store_tile); on = false: direct stores.
@@ -91,7 +92,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) ds_gemm_kernel(const __grid_c
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);  // SWIZZLE_128B needs 1024-B alignment
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + S * Cfg::kABytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S * (Cfg::kABytes + Cfg::kBBytes));
+  uint8_t* warp_stage = smem + S * (Cfg::kABytes + Cfg::kBBytes);  // 8 x kWarpStage, 2 KB aligned
+  uint64_t* bars = reinterpret_cast<uint64_t*>(warp_stage + 8 * Cfg::kWarpStage);
   uint64_t* full = bars;
   uint64_t* empty = bars + S;
   uint64_t* tmem_full = bars + 2 * S;
@@ -208,10 +210,16 @@ __global__ void __launch_bounds__(kGemmThreads, 1) ds_gemm_kernel(const __grid_c
       tc_fence_after();
       const int t = tt * 128 + quad * 32 + lane;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * BN;
-      epilogue_tile<BN, EPI, kSplit>(p, taddr, b, t, t < p.T, nt, half);
+      EpiStage es;
+      es.sw = smem_u32(warp_stage + (warp - 4) * Cfg::kWarpStage);
+      es.lane = lane;
+      es.tw0 = tt * 128 + quad * 32;
+      es.on = !kSplit && p.has_out_map != 0;
+      epilogue_tile<BN, EPI, kSplit>(p, taddr, b, t, t < p.T, nt, half, es);
       tc_fence_before();
       mbar_arrive(&tmem_empty[as]);
     }
+    bulk_wait_all();  // staging tiles are read out before the CTA's shared memory goes away
   }
   tc_fence_before();
   __syncthreads();
