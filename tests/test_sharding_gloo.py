@@ -56,7 +56,7 @@ def _worker(rank, world, port, n_total, q):
         noise = sharding.sliced_noise((n_total, 4, 6), 99, lo, hi)
         local = noise * 2.0 + torch.arange(lo, hi, dtype=torch.float32)[:, None, None]
         full = sharding.gather_mels(local, n_total)
-        q.put((rank, full))
+        q.put((rank, full.numpy().copy()))  # by value: a tensor would travel as a shared-memory handle that dies with this process
     finally:
         dist.destroy_process_group()
 
@@ -75,4 +75,4 @@ def test_gather_mels_world2(n_total):
         assert p.exitcode == 0
     expect = sharding.sliced_noise((n_total, 4, 6), 99, 0, n_total) * 2.0 + torch.arange(n_total, dtype=torch.float32)[:, None, None]
     for r in range(world):
-        assert torch.equal(results[r], expect)
+        assert torch.equal(torch.from_numpy(results[r]), expect)
