@@ -979,6 +979,10 @@ extern "C" int ds_session_run(ds_session* s, const ds_op* ops, int32_t n_ops, fl
 }
 
 extern "C" int64_t ds_session_last_launches(const ds_session* s) { return s ? s->last_launches : 0; }
+extern "C" int ds_session_path(const ds_session* s) {
+  if (!s) return fail(DS_ERR_INVALID, "null session");
+  return s->small ? 1 : (s->medium ? 2 : 0);
+}
 
 // ------------------------------------------------------------------------------------ helpers
 extern "C" int ds_lincomb(float* dst, const float* const* srcs, const float* coefs, int32_t n, size_t numel, void* stream) {

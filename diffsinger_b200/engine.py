@@ -122,6 +122,11 @@ class Session:
     def last_launches(self) -> int:
         return int(nat.lib().ds_session_last_launches(self.handle))
 
+    @property
+    def path(self) -> str:
+        """'fused' | 'small' | 'medium': the kernels this session's residual layers run on (include/dsb200.h: ds_session_path)."""
+        return ("fused", "small", "medium")[int(nat.lib().ds_session_path(self.handle))]
+
     def close(self):
         if self.handle:
             nat.lib().ds_session_destroy(self.handle)

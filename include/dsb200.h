@@ -119,6 +119,10 @@ int ds_session_run(ds_session* s, const ds_op* ops, int32_t n_ops, float* const*
                    void* stream);
 /* Number of kernel launches the last ds_session_forward / ds_session_run issued (or replayed). */
 int64_t ds_session_last_launches(const ds_session* s);
+/* Which kernels the session's residual layers run on, chosen at creation from (B, T) and the plan: 0 = one fused kernel per
+ * layer (ds_plan_layer_mode), 1 = unfused GEMMs with narrow N tiles (few frame tiles), 2 = unfused GEMMs with the plan's 256-wide
+ * tiles (between the two); negative on a null session. */
+int ds_session_path(const ds_session* s);
 
 /* ---- stand-alone helpers */
 /* dst = sum coef[i]*src[i] over numel fp32 elements (numel % 4 == 0): the sampler tensor update

@@ -111,3 +111,14 @@ def test_sample_segments_matches_sequential():
         torch.cuda.synchronize()
         assert all(torch.equal(a, b.cpu()) for a, b in zip(seq, par))
     assert ds.sample_segments(m, []) == []
+
+
+@pytest.mark.parametrize("C,B,T,path", [(512, 1, 500, "small"), (512, 1, 2800, "small"), (512, 1, 3000, "medium"), (512, 3, 3500, "medium"),
+                                        (512, 3, 4000, "fused"), (512, 64, 2000, "fused"), (256, 1, 8000, "small"), (256, 2, 8000, "fused")])
+def test_session_path_by_size(C, B, T, path, monkeypatch):
+    """Sessions pick their layer kernels from the tile-pair count and the channel width (small / medium
+    problems); DSB200_SMALL / DSB200_MEDIUM only override."""
+    for v in ("DSB200_SMALL", "DSB200_MEDIUM", "DSB200_LAYER_MODE"):
+        monkeypatch.delenv(v, raising=False)
+    net = _net(random_state_dict(128, 1, 2, C, 256, seed=1), C, 2, 2, 128, 1)
+    assert net.engine().session(B, T).path == path
