@@ -1055,6 +1055,24 @@ extern "C" int ds_layernorm(void* y_bf16, const void* x_bf16, const float* gamma
   __nv_bfloat16* yp = (__nv_bfloat16*)y_bf16;
   const __nv_bfloat16* xp = (const __nv_bfloat16*)x_bf16;
   const __nv_bfloat16* ap = (const __nv_bfloat16*)add_bf16;
+  // rows of <= 512 channels whose byte length is a multiple of 16: bulk-copy kernel (shared-memory ring per warp); DSB200_LN=reg
+  // keeps the register-prefetching kernel
+  static const bool ln_reg = [] { const char* e = getenv("DSB200_LN"); return e && !strcmp(e, "reg"); }();
+  if (!ln_reg && nch <= 2 && channels % 8 == 0 && !(((uintptr_t)x_bf16 | (uintptr_t)add_bf16) & 15)) {
+    const size_t smem = 8 * kLnSlots * 2 * (ap ? 2 : 1) * 1024;
+    const long blocks2 = (rows + 15) / 16;
+    const long cap2 = (long)g_num_sms * 2;
+    const int grid2 = (int)(blocks2 < cap2 ? blocks2 : cap2);
+    if (ap) {
+      CUDA_TRY(cudaFuncSetAttribute(layernorm_bulk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      layernorm_bulk_kernel<true><<<grid2, 256, smem, st>>>(yp, xp, gamma, beta, (long)rows, channels, eps, vec, (long)rows_per_vec, ap);
+    } else {
+      CUDA_TRY(cudaFuncSetAttribute(layernorm_bulk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      layernorm_bulk_kernel<false><<<grid2, 256, smem, st>>>(yp, xp, gamma, beta, (long)rows, channels, eps, vec, (long)rows_per_vec, ap);
+    }
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+  }
   if (nch <= 1) layernorm_kernel<1><<<grid, 256, 0, st>>>(yp, xp, gamma, beta, (long)rows, channels, eps, vec, (long)rows_per_vec, ap);
   else if (nch <= 2) layernorm_kernel<2><<<grid, 256, 0, st>>>(yp, xp, gamma, beta, (long)rows, channels, eps, vec, (long)rows_per_vec, ap);
   else if (nch <= 4) layernorm_kernel<4><<<grid, 256, 0, st>>>(yp, xp, gamma, beta, (long)rows, channels, eps, vec, (long)rows_per_vec, ap);

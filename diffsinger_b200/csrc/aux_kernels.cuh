@@ -356,6 +356,158 @@ __global__ void __launch_bounds__(256) layernorm_kernel(__nv_bfloat16* __restric
   }
 }
 
+// The same LayerNorm for rows of up to 512 channels with the loads taken off the registers: every warp owns a ring of kLnSlots
+// shared-memory slots, each filled by one elected lane with 1-D bulk copies (cp.async.bulk, a row is C * 2 contiguous bytes) of
+// the next two rows (and their second operand) and guarded by an mbarrier -- three row groups per warp are in flight at no
+// register cost, where the register-prefetching kernel above stalls on its loads (long scoreboard 5 per issue,
+// profiles/r01_layernorm_kernel.txt).  The warp that consumes a slot refills it itself (after __syncwarp: all lanes have their
+// values in registers), so no empty barrier is needed.  Statistics and normalisation are unchanged.
+constexpr int kLnSlots = 3;
+__device__ __forceinline__ void bulk_load_1d(uint32_t dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst_smem), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+// dynamic smem = warps * kLnSlots * 2 rows * (kAdd ? 2 : 1) * 1024 B; mbarriers in static shared memory
+template <bool kAdd>
+__global__ void __launch_bounds__(256) layernorm_bulk_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x,
+                                 const float* __restrict__ gamma, const float* __restrict__ beta, long rows, int C, float eps,
+                                 const float* __restrict__ vec, long rows_per_vec, const __nv_bfloat16* __restrict__ add) {
+  constexpr int kRows = 2, kOps = kAdd ? 2 : 1;
+  constexpr uint32_t kSlotBytes = kRows * kOps * 1024;
+  extern __shared__ __align__(128) uint8_t ln_smem[];
+  __shared__ uint64_t ln_bars[8 * kLnSlots];
+  grid_dep_launch();
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const long warp0 = (static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const long nwarps = (static_cast<long>(gridDim.x) * blockDim.x) >> 5;
+  const int nch = (C + 255) / 256;
+  const float inv_c = 1.f / static_cast<float>(C);
+  const uint32_t row_bytes = static_cast<uint32_t>(C) * 2;
+  uint64_t* bars = ln_bars + wib * kLnSlots;
+  const uint32_t ring = smem_u32(ln_smem) + wib * kLnSlots * kSlotBytes;
+  if (lane == 0) {
+    for (int i = 0; i < kLnSlots; ++i) mbar_init(&bars[i], 1);
+    fence_barrier_init();
+  }
+  float gg[2][8], bb[2][8];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int e = (i * 32 + lane) * 8;
+    if (i < nch && e < C) {
+      const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + e)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + e) + 1);
+      const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + e)), b1 = __ldg(reinterpret_cast<const float4*>(beta + e) + 1);
+      gg[i][0] = g0.x; gg[i][1] = g0.y; gg[i][2] = g0.z; gg[i][3] = g0.w; gg[i][4] = g1.x; gg[i][5] = g1.y; gg[i][6] = g1.z; gg[i][7] = g1.w;
+      bb[i][0] = b0.x; bb[i][1] = b0.y; bb[i][2] = b0.z; bb[i][3] = b0.w; bb[i][4] = b1.x; bb[i][5] = b1.y; bb[i][6] = b1.z; bb[i][7] = b1.w;
+    }
+  }
+  __syncwarp();
+  grid_dep_wait();
+  const long stride = nwarps * kRows;
+  auto issue = [&](long r0, int slot) {  // lane 0 only
+    if (r0 >= rows) return;
+    mbar_arrive_expect_tx(&bars[slot], kRows * kOps * row_bytes);
+#pragma unroll
+    for (int q = 0; q < kRows; ++q) {
+      const long r = r0 + q < rows ? r0 + q : rows - 1;  // the tail warp recomputes the last row (same values rewritten)
+      bulk_load_1d(ring + slot * kSlotBytes + q * kOps * 1024, x + r * C, row_bytes, &bars[slot]);
+      if (kAdd) bulk_load_1d(ring + slot * kSlotBytes + q * kOps * 1024 + 1024, add + r * C, row_bytes, &bars[slot]);
+    }
+  };
+  long r0 = warp0 * kRows;
+  if (lane == 0)
+    for (int i = 0; i < kLnSlots; ++i) issue(r0 + i * stride, i);
+  int slot = 0;
+  uint32_t phase = 0;
+  for (; r0 < rows; r0 += stride) {
+    mbar_wait(&bars[slot], phase);
+    float v[kRows][2][8];
+    float sum[kRows];
+    const uint8_t* sl = ln_smem + (wib * kLnSlots + slot) * kSlotBytes;
+#pragma unroll
+    for (int q = 0; q < kRows; ++q) {
+      const long r = r0 + q < rows ? r0 + q : rows - 1;
+      sum[q] = 0.f;
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int e = (i * 32 + lane) * 8;
+        if (i < nch && e < C) {
+          const uint4 qv = *reinterpret_cast<const uint4*>(sl + q * kOps * 1024 + e * 2);
+          const uint32_t w[4] = {qv.x, qv.y, qv.z, qv.w};
+#pragma unroll
+          for (int h = 0; h < 4; ++h) {
+            v[q][i][2 * h] = __uint_as_float(w[h] << 16);
+            v[q][i][2 * h + 1] = __uint_as_float(w[h] & 0xffff0000u);
+          }
+          if (kAdd) {
+            const uint4 qa = *reinterpret_cast<const uint4*>(sl + q * kOps * 1024 + 1024 + e * 2);
+            const uint32_t wa[4] = {qa.x, qa.y, qa.z, qa.w};
+#pragma unroll
+            for (int h = 0; h < 4; ++h) {
+              v[q][i][2 * h] += __uint_as_float(wa[h] << 16);
+              v[q][i][2 * h + 1] += __uint_as_float(wa[h] & 0xffff0000u);
+            }
+          }
+          if (vec) {
+            const float* vr = vec + (r / rows_per_vec) * C + e;
+#pragma unroll
+            for (int h = 0; h < 8; ++h) v[q][i][h] += __ldg(vr + h);
+          }
+#pragma unroll
+          for (int h = 0; h < 8; ++h) sum[q] += v[q][i][h];
+        } else {
+#pragma unroll
+          for (int h = 0; h < 8; ++h) v[q][i][h] = 0.f;
+        }
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < kRows; ++q)  // the butterfly also orders every lane's slot reads before the refill below
+      for (int s = 16; s > 0; s >>= 1) sum[q] += __shfl_xor_sync(0xffffffffu, sum[q], s);
+    if (lane == 0) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy reads of the slot before its async-proxy refill
+      issue(r0 + kLnSlots * stride, slot);
+    }
+    float mean[kRows], sq[kRows];
+#pragma unroll
+    for (int q = 0; q < kRows; ++q) {
+      mean[q] = sum[q] * inv_c;
+      sq[q] = 0.f;
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int e = (i * 32 + lane) * 8;
+        if (i < nch && e < C) {
+#pragma unroll
+          for (int h = 0; h < 8; ++h) {
+            v[q][i][h] -= mean[q];
+            sq[q] = fmaf(v[q][i][h], v[q][i][h], sq[q]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < kRows; ++q)
+      for (int s = 16; s > 0; s >>= 1) sq[q] += __shfl_xor_sync(0xffffffffu, sq[q], s);
+#pragma unroll
+    for (int q = 0; q < kRows; ++q) {
+      const long r = r0 + q < rows ? r0 + q : rows - 1;
+      const float rstd = rsqrtf(sq[q] * inv_c + eps);
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int e = (i * 32 + lane) * 8;
+        if (i < nch && e < C) {
+          float o[8];
+#pragma unroll
+          for (int h = 0; h < 8; ++h) o[h] = fmaf(v[q][i][h] * rstd, gg[i][h], bb[i][h]);
+          uint4 qo;
+          qo.x = pack_bf16(o[0], o[1]); qo.y = pack_bf16(o[2], o[3]); qo.z = pack_bf16(o[4], o[5]); qo.w = pack_bf16(o[6], o[7]);
+          *reinterpret_cast<uint4*>(y + r * C + e) = qo;
+        }
+      }
+    }
+    if (++slot == kLnSlots) { slot = 0; phase ^= 1; }
+  }
+}
+
 // Depthwise Conv1d along time on time-major bf16 activations [B][T][CH] with zero padding, fused bias and activation
 // (0 none, 1 ReLU, 2 PReLU with per-channel slope, 3 SiLU): y[b][t][c] = act(bias[c] + sum_j w[c][j] * x[b][t + j - pad][c]).
 // One thread owns a channel PAIR and kFrames = K * kGroups consecutive frames.  All kFrames + K - 1 input rows of its pair
