@@ -29,7 +29,10 @@ def _desc(**kw):
     return d
 
 
-@pytest.mark.parametrize("rows,Cc", [(1000, 512), (77, 192), (5, 2048), (300, 8)])
+# <= 512 channels: bulk-copy kernel (3-slot ring per warp: single rows, odd row counts, > 6 wraps of the ring, a partial second
+# chunk); wider rows: register kernel
+@pytest.mark.parametrize("rows,Cc", [(1000, 512), (77, 192), (5, 2048), (300, 8), (1, 512), (4737, 256), (30001, 512), (1001, 264),
+                                     (2, 1024)])
 def test_layernorm(rows, Cc):
     torch.manual_seed(0)
     x = _bf(rows, Cc) * 3 + 1
