@@ -37,10 +37,14 @@ def test_layernorm(rows, Cc):
     torch.manual_seed(0)
     x = _bf(rows, Cc) * 3 + 1
     g, b = torch.randn(Cc, device=dev), torch.randn(Cc, device=dev)
-    y = torch.empty_like(x)
+    guard = 4096  # sentinel elements on both sides of the output
+    ybig = torch.full((rows * Cc + 2 * guard,), 1234.0, device=dev, dtype=torch.bfloat16)
+    y = ybig[guard:guard + rows * Cc].view(rows, Cc)
     nat.check(nat.lib().ds_layernorm(y.data_ptr(), x.data_ptr(), g.data_ptr(), b.data_ptr(), rows, Cc, 1e-5, None, 0, None, _st()))
     ref = F.layer_norm(x.float(), (Cc,), g, b, 1e-5)
     assert rel_l2(y.float(), ref) < 4e-3
+    assert (ybig[:guard] == 1234.0).all() and (ybig[-guard:] == 1234.0).all()
+    y = y.clone()  # the variants below write a plain buffer
     # with a per-utterance additive vector (rows_per_vec frames share one)
     rpv = max(1, rows // 3)
     nvec = (rows + rpv - 1) // rpv
@@ -68,8 +72,11 @@ def test_dwconv(k, pad, act, B, T, CH):
     w = torch.randn(CH, k, device=dev) * k ** -0.5
     bias = torch.randn(CH, device=dev)
     slope = torch.rand(CH, device=dev) * 0.5
-    y = torch.empty_like(x)
+    guard = 4096  # sentinel elements on both sides of the output: the kernel writes nothing outside [B, T, CH]
+    ybig = torch.full((B * T * CH + 2 * guard,), 1234.0, device=dev, dtype=torch.bfloat16)
+    y = ybig[guard:guard + B * T * CH].view(B, T, CH)
     nat.check(nat.lib().ds_dwconv(y.data_ptr(), x.data_ptr(), w.data_ptr(), bias.data_ptr(), slope.data_ptr(), B, T, CH, k, pad, act, _st()))
+    assert (ybig[:guard] == 1234.0).all() and (ybig[-guard:] == 1234.0).all()
     ref = F.conv1d(F.pad(x.float().transpose(1, 2), (pad, k - 1 - pad)), w[:, None, :], bias, groups=CH)  # pad = zeros on the left
     ref = {0: lambda v: v, 1: F.relu, 2: lambda v: torch.where(v > 0, v, slope[None, :, None] * v), 3: F.silu}[act](ref).transpose(1, 2)
     assert y.shape == ref.shape
