@@ -1095,15 +1095,29 @@ extern "C" int ds_dwconv(void* y_bf16, const void* x_bf16, const float* w, const
   // tensor-core Toeplitz path (dwconv_mma_kernel.cuh) for the two kernel sizes the models use; DSB200_DWCONV=fma keeps the
   // fp32-FMA kernel for A/B runs and for channel counts that are not a multiple of 32
   static const bool force_fma = [] { const char* e = getenv("DSB200_DWCONV"); return e && !strcmp(e, "fma"); }();
-  if (!force_fma && channels % 32 == 0 && (kernel_size == 31 || kernel_size == 7)) {
+  if (!force_fma && channels % 32 == 0 && (kernel_size == 31 || kernel_size == 7) && !((uintptr_t)x_bf16 & 15)) {
     const int n_tiles = ceil_div(T, 128);
     const long units = (long)n_tiles * B * (channels / 32);
     const int chunks = (int)std::min<long>(16, std::max<long>(1, units / (148 * 6)));
     const dim3 grid(channels / 32, ceil_div(n_tiles, chunks), B);
+    // input box of one tile: 32 channels x kTW frames, SWIZZLE_64B, frames outside [0, T) zero-filled (= the conv's padding)
+    auto make_dw_map = [&](CUtensorMap* m, int rows_box) -> int {
+      cuuint64_t dims[3] = {(cuuint64_t)channels, (cuuint64_t)T, (cuuint64_t)B};
+      cuuint64_t strides[2] = {(cuuint64_t)channels * 2, (cuuint64_t)channels * 2 * (cuuint64_t)T};
+      cuuint32_t box[3] = {32, (cuuint32_t)rows_box, 1};
+      cuuint32_t estr[3] = {1, 1, 1};
+      CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<__nv_bfloat16*>(x), dims, strides, box, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      if (r != CUDA_SUCCESS) return fail(DS_ERR_CUDA, "cuTensorMapEncodeTiled(dwconv input %dx%dx%d) -> %d", channels, T, B, (int)r);
+      return 0;
+    };
+    CUtensorMap tmX;
+    DS_TRY(make_dw_map(&tmX, kernel_size == 31 ? DwMma<31>::kTW : DwMma<7>::kTW));
 #define DS_DW_MMA(KS, ACT)                                                                                                   \
   do {                                                                                                                       \
     CUDA_TRY(cudaFuncSetAttribute(dwconv_mma_kernel<KS, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, DwMma<KS>::kSmemBytes)); \
-    dwconv_mma_kernel<KS, ACT><<<grid, 256, DwMma<KS>::kSmemBytes, st>>>(y, x, w, bias, slope, T, channels, pad_left, chunks); \
+    dwconv_mma_kernel<KS, ACT><<<grid, 256, DwMma<KS>::kSmemBytes, st>>>(tmX, y, w, bias, slope, T, channels, pad_left, chunks); \
   } while (0)
     if (kernel_size == 31) {
       if (act == 0) DS_DW_MMA(31, 0); else if (act == 1) DS_DW_MMA(31, 1); else if (act == 2) DS_DW_MMA(31, 2); else DS_DW_MMA(31, 3);

@@ -9,12 +9,13 @@
 //                                        stored channel-major in shared memory a window starts every 32 bytes, so the B fragments
 //                                        are plain ldmatrix loads of 16-byte chunks; even and odd chunks live in separate halves
 //                                        of the channel row, which makes every 8-row ldmatrix phase conflict-free.
-// Activations arrive time-major ([T][CH]), so every tile is transposed once on its way in: cp.async (16 B, zero fill outside
-// [0, T) = the conv's zero padding) into a natural-layout staging tile, then LDS.128 of two consecutive frames, 8 PRMTs and
-// 8 STS.32 per thread unit into the channel-major tile.  Outputs go back through a time-major tile to 16-byte coalesced stores.
-// A CTA (8 warps x 4 channels) walks `chunks` consecutive 128-frame tiles of one utterance; cp.async runs two tiles ahead
+// Activations arrive time-major ([T][CH]), so every tile is transposed once on its way in: ONE TMA box (32 channels x kTW frames,
+// SWIZZLE_64B; frames outside [0, T) are zero-filled = the conv's zero padding) per tile into a natural-layout staging tile under an
+// mbarrier, then LDS.128 of two consecutive frames, 8 PRMTs and 8 STS.32 per thread unit into the channel-major tile.  Outputs go back through a time-major tile to 16-byte coalesced stores.
+// A CTA (8 warps x 4 channels) walks `chunks` consecutive 128-frame tiles of one utterance; the TMA loads run two tiles ahead
 // (double-buffered staging tile).  Weights are rounded to bf16 (as in every GEMM of the same model); accumulation is fp32.
 #pragma once
+#include <cuda.h>
 #include <cuda_bf16.h>
 #include <cstdint>
 
@@ -22,9 +23,6 @@
 
 namespace dsb {
 
-__device__ __forceinline__ void cp_async_16_zfill(uint32_t smem_addr, const void* gptr, bool valid) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_addr), "l"(gptr), "r"(valid ? 16 : 0) : "memory");
-}
 __device__ __forceinline__ void ldmatrix_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
 }
@@ -53,7 +51,7 @@ template <int K>
 struct DwMma {
   static constexpr int kNK = (16 + K - 1 + 15) / 16;   // k16 steps covering the 16 + K - 1 inputs of 16 consecutive outputs
   static constexpr int kTW = 16 * 7 + 16 * kNK;        // frames the B windows of one 128-frame tile touch (160 for K = 31)
-  static constexpr int kStageRow = 80;                 // bytes per staged frame: 32 channels + 16 B pad (spreads LDS.128 over banks)
+  static constexpr int kStageRow = 64;                 // bytes per staged frame: 32 channels, 16-byte chunks XOR-swizzled by (frame / 2) % 4 (TMA SWIZZLE_64B)
   static constexpr int kStageBytes = kTW * kStageRow;
   static constexpr int kHalf = 12;                     // 16-byte slot of the first odd chunk: 12 * 4 words = 16 (mod 32 banks)
   static constexpr int kXtRow = 24 * 16;               // bytes per channel row: even chunks in slots 0.., odd chunks in slots 12..
@@ -65,18 +63,18 @@ struct DwMma {
 
 // grid = (CH / 32, ceil(ceil(T / 128) / chunks), B), block = 256, dynamic smem = DwMma<K>::kSmemBytes
 template <int K, int kAct>
-__global__ void __launch_bounds__(256) dwconv_mma_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x,
+__global__ void __launch_bounds__(256) dwconv_mma_kernel(const __grid_constant__ CUtensorMap tmX, __nv_bfloat16* __restrict__ y,
                                                          const float* __restrict__ w, const float* __restrict__ bias,
                                                          const float* __restrict__ slope, int T, int CH, int pad, int chunks) {
   using S = DwMma<K>;
-  extern __shared__ __align__(16) uint8_t dwm_smem[];
+  extern __shared__ __align__(1024) uint8_t dwm_smem[];
+  __shared__ uint64_t dwm_bars[2];
   grid_dep_launch();
   const uint32_t stage = smem_u32(dwm_smem), xt = stage + 2 * S::kStageBytes, ot = xt + S::kXtBytes;
   const int tid = threadIdx.x, lane = tid & 31, wq = tid >> 5, g = lane >> 2, q = lane & 3;
   const int c0 = blockIdx.x * 32, b = blockIdx.z;
   const int n_tiles = (T + 127) / 128;
   const int tile0 = blockIdx.y * chunks, tile1 = min(tile0 + chunks, n_tiles);
-  const __nv_bfloat16* xb = x + (static_cast<size_t>(b) * T) * CH + c0;
   __nv_bfloat16* yb = y + (static_cast<size_t>(b) * T) * CH + c0;
 
   // Toeplitz A fragments of this warp's 4 channels: aw[s] = {W[g][16s+2q..], W[g+8][16s+2q..], W[g][16s+2q+8..], W[g+8][16s+2q+8..]}
@@ -100,35 +98,39 @@ __global__ void __launch_bounds__(256) dwconv_mma_kernel(__nv_bfloat16* __restri
   }
   grid_dep_wait();
 
-  // tile -> staging buffer (tile - tile0) % 2; always commits a group (possibly empty) so that wait_group 1 = "all but the newest"
-  auto issue_loads = [&](int tile) {
+  // tile -> staging buffer (tile - tile0) % 2: one TMA box per tile, completion on the buffer's mbarrier
+  if (tid == 0) {
+    tma_prefetch_desc(&tmX);
+    mbar_init(&dwm_bars[0], 1);
+    mbar_init(&dwm_bars[1], 1);
+    fence_barrier_init();
+  }
+  __syncthreads();
+  auto issue_loads = [&](int tile) {  // thread 0 only
     if (tile < tile1) {
-      const int tb = tile * 128 - pad;
-      const uint32_t st = stage + ((tile - tile0) & 1) * S::kStageBytes;
-      for (int idx = tid; idx < S::kTW * 4; idx += 256) {
-        const int i = idx >> 2, o = idx & 3, t = tb + i;
-        const bool valid = t >= 0 && t < T;
-        cp_async_16_zfill(st + i * S::kStageRow + o * 16, xb + static_cast<size_t>(valid ? t : 0) * CH + o * 8, valid);
-      }
+      const int buf = (tile - tile0) & 1;
+      mbar_arrive_expect_tx(&dwm_bars[buf], S::kStageBytes);
+      tma_load_3d(&tmX, &dwm_bars[buf], dwm_smem + buf * S::kStageBytes, c0, tile * 128 - pad, b);
     }
-    asm volatile("cp.async.commit_group;" ::: "memory");
   };
-  issue_loads(tile0);
-  issue_loads(tile0 + 1);
+  if (tid == 0) {
+    issue_loads(tile0);
+    issue_loads(tile0 + 1);
+  }
 
   // ldmatrix lane address inside a channel row: matrix mi = lane / 8 holds chunks 2r + mi (+ 2 per k16 step), r = lane % 8
   const int mi = lane >> 3, r = lane & 7;
   const uint32_t b_lane = xt + (wq * 4) * S::kXtRow + (r + (mi >> 1) + (mi & 1) * S::kHalf) * 16;
 
   for (int tile = tile0; tile < tile1; ++tile) {
-    asm volatile("cp.async.wait_group 1;" ::: "memory");
-    __syncthreads();  // staged tile visible; the previous tile's output tile has been read out
+    mbar_wait(&dwm_bars[(tile - tile0) & 1], ((tile - tile0) >> 1) & 1);  // staged tile landed
     const uint8_t* sg = dwm_smem + ((tile - tile0) & 1) * S::kStageBytes;
     // transpose: unit = (frame pair tp, channel octet o) -> 8 words (c @ 2tp, c @ 2tp + 1) of the channel-major tile
     for (int u = tid; u < (S::kTW / 2) * 4; u += 256) {
       const int o = u / (S::kTW / 2), tp = u - o * (S::kTW / 2);
-      const uint4 r0 = *reinterpret_cast<const uint4*>(sg + (2 * tp) * S::kStageRow + o * 16);
-      const uint4 r1 = *reinterpret_cast<const uint4*>(sg + (2 * tp + 1) * S::kStageRow + o * 16);
+      const int oc = (o ^ (tp & 3)) << 4;  // SWIZZLE_64B: chunk ^= (frame / 2) % 4, the same for frames 2tp and 2tp + 1
+      const uint4 r0 = *reinterpret_cast<const uint4*>(sg + (2 * tp) * S::kStageRow + oc);
+      const uint4 r1 = *reinterpret_cast<const uint4*>(sg + (2 * tp + 1) * S::kStageRow + oc);
       const uint32_t a[4] = {r0.x, r0.y, r0.z, r0.w}, c[4] = {r1.x, r1.y, r1.z, r1.w};
       const int ch = tp >> 2;  // 16-byte chunk (8 frames) -> slot (ch / 2) + (ch % 2) * kHalf
       const uint32_t dst = xt + (o * 8) * S::kXtRow + ((ch >> 1) + (ch & 1) * S::kHalf) * 16 + (tp & 3) * 4;
@@ -138,8 +140,11 @@ __global__ void __launch_bounds__(256) dwconv_mma_kernel(__nv_bfloat16* __restri
         asm volatile("st.shared.b32 [%0], %1;" ::"r"(dst + (2 * p + 1) * S::kXtRow), "r"(prmt(a[p], c[p], 0x7632)) : "memory");
       }
     }
-    __syncthreads();  // channel-major tile complete, this staging buffer free
-    issue_loads(tile + 2);
+    __syncthreads();  // channel-major tile complete, this staging buffer free; the previous tile's output tile has been read out
+    if (tid == 0) {
+      fence_proxy_async_smem();  // generic-proxy reads of the staging buffer before its async-proxy refill
+      issue_loads(tile + 2);
+    }
 
     // 4 channels x (ldmatrix.x4 [+ .x2] + kNK mma); D[g (+8)][2q (+1)] = frame 16 (2q (+1)) + g (+8)
     uint32_t ow[4][2];  // [frame slot v][channel pair] packed bf16
