@@ -120,6 +120,9 @@ def run_reference(args, rank, world):
 
 def workload_name():
     c = CFG
+    if c.get("sampler") == "reflow-euler":  # BASELINE configs[2]: same backbone, RectifiedFlow, Euler, utterances sharded over the GPUs
+        return (f"acoustic RectifiedFlow+WaveNet {c['L']}x{c['C']}ch, {c['M']} mel, batch {c['B']}x{c['T']} frames per GPU, "
+                f"Euler {c['K']} steps (configs[2])")
     return (f"acoustic GaussianDiffusion+WaveNet {c['L']}x{c['C']}ch, {c['M']} mel, batch {c['B']}x{c['T']} frames per GPU, "
             f"DPM-Solver++ {c['K']} steps (configs[1])")
 
@@ -169,9 +172,13 @@ def run_native(args, rank, world, local_rank):
     ds.hparams.clear()
     ds.hparams.update(hidden_size=c["H"], schedule_type="linear", use_shallow_diffusion=False, diff_accelerator=c["algo"],
                       diff_speedup=c["speedup"], K_step=c["timesteps"], K_step_infer=c["timesteps"], timesteps=c["timesteps"])
-    model = ds.GaussianDiffusion(c["M"], c["F"], c["timesteps"], c["timesteps"], "wavenet",
-                                 dict(num_layers=c["L"], num_channels=c["C"], dilation_cycle_length=c["cycle"]),
-                                 spec_min=[-12.0], spec_max=[0.0])
+    bb_args = dict(num_layers=c["L"], num_channels=c["C"], dilation_cycle_length=c["cycle"])
+    if c.get("sampler") == "reflow-euler":
+        ds.hparams.update(sampling_algorithm="euler", sampling_steps=c["K"], time_scale_factor=1000, T_start=0.0, T_start_infer=0.0)
+        model = ds.RectifiedFlow(c["M"], c["F"], 0.0, 1000, "wavenet", bb_args, spec_min=[-12.0], spec_max=[0.0])
+        model.denoise_fn = model.velocity_fn  # one name for the backbone below
+    else:
+        model = ds.GaussianDiffusion(c["M"], c["F"], c["timesteps"], c["timesteps"], "wavenet", bb_args, spec_min=[-12.0], spec_max=[0.0])
     model.denoise_fn.load_state_dict(random_state_dict(c["M"], c["F"], c["L"], c["C"], c["H"], seed=1234))
     model = model.eval().to(dev)
     B, T = c["B"], c["T"]
@@ -279,9 +286,12 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--sampler", default="dpm-solver", choices=["dpm-solver", "reflow-euler"],
+                    help="dpm-solver = BASELINE configs[1] (the contract's workload); reflow-euler = configs[2] (native arm only)")
     ap.add_argument("--batch", type=int, default=None)
     ap.add_argument("--frames", type=int, default=None)
     args = ap.parse_args()
+    CFG["sampler"] = args.sampler
     if args.batch:
         CFG["B"] = args.batch
     if args.frames:
