@@ -65,6 +65,16 @@ def main():
         algo = B * T * C * 4.0
         print(json.dumps({"op": "ds_layernorm", "channels": C, "frames": B * T, "us": s * 1e6, "algo_bytes": algo,
                           "GBps": algo / s * 1e-9}))
+        adds = [torch.randn(B * T, C, device=dev, generator=g).to(torch.bfloat16) for _ in range(2)]  # LYNXNet: + conditioner projection
+
+        def run_add():
+            state["i"] ^= 1
+            ops.layernorm(y, xs[state["i"]], gamma, beta, add=adds[state["i"]])
+
+        s = timed(run_add, iters)
+        algo = B * T * C * 6.0
+        print(json.dumps({"op": "ds_layernorm+add", "channels": C, "frames": B * T, "us": s * 1e6, "algo_bytes": algo,
+                          "GBps": algo / s * 1e-9}))
 
 
 if __name__ == "__main__":
