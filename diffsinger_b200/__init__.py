@@ -4,6 +4,7 @@ Host code is Python/PyTorch plumbing over the C ABI in include/dsb200.h (libdsb2
 from .hparams import hparams, get_hparams
 from .backbones import BACKBONES, build_backbone, WaveNet, LYNXNet
 from .segments import sample_segments
+from .dropin import install_dropin
 from .aux_decoder import AUX_DECODERS, AuxDecoderAdaptor, ConvNeXtDecoder, build_aux_decoder
 from .vocoder import VOCODERS, NsfHifiGAN
 from .core import (GaussianDiffusion, PitchDiffusion, MultiVarianceDiffusion,
@@ -11,5 +12,5 @@ from .core import (GaussianDiffusion, PitchDiffusion, MultiVarianceDiffusion,
 
 __all__ = ["hparams", "get_hparams", "BACKBONES", "build_backbone", "WaveNet", "LYNXNet", "GaussianDiffusion",
            "PitchDiffusion", "MultiVarianceDiffusion", "RectifiedFlow", "PitchRectifiedFlow",
-           "MultiVarianceRectifiedFlow", "sample_segments", "AUX_DECODERS", "AuxDecoderAdaptor", "ConvNeXtDecoder", "build_aux_decoder",
+           "MultiVarianceRectifiedFlow", "sample_segments", "install_dropin", "AUX_DECODERS", "AuxDecoderAdaptor", "ConvNeXtDecoder", "build_aux_decoder",
            "VOCODERS", "NsfHifiGAN"]

@@ -58,6 +58,10 @@ _W = {}
 def shared_weights(ref, M, F):
     """One weight set per (M, F), saved once as weights_m{M}f{F}.npz and loaded into every model."""
     tag = f"m{M}f{F}"
+    existing = os.path.join(OUT, "weights_" + tag + ".npz")
+    if tag not in _W and os.path.exists(existing):  # later fixture batches reuse the committed weight sets
+        z = np.load(existing)
+        _W[tag] = {k: torch.from_numpy(z[k]) for k in z.files if k not in ("cfg", "torch_version")}
     if tag not in _W:
         set_reference_hparams(hidden_size=HIDDEN)
         torch.manual_seed(100 + F)
@@ -286,9 +290,75 @@ def gen_nsf_hifigan(ref):
               **{"w." + k: v.numpy() for k, v in gen.state_dict().items()})
 
 
+def gen_extra(ref):
+    """Round-2 additions: the wrappers / schedules / shallow solver paths that had no fixture.
+      var_multi_ddim      MultiVarianceDiffusion (ddpm.py:448-505), F = 2, DDIM 10 steps
+      var_pitch_euler     PitchRectifiedFlow (reflow.py:184-203), Euler 10 steps
+      ddpm_*_cosine       schedule_type='cosine' (ddpm.py:36-46) through DDIM, DPM-Solver++ (lambda-clip active,
+                          dpm_solver_pytorch.py:114-125) and UniPC (no clip, uni_pc.py:77-86)
+      ddpm_*_shallow      DPM-Solver++ / UniPC with use_shallow_diffusion, K_step = 400: NoiseScheduleVP over betas[:t_max]
+                          (ddpm.py:246-322, trap T9)"""
+    B, T = 1, 29
+    cond = None
+    # MultiVarianceDiffusion
+    set_reference_hparams(hidden_size=HIDDEN, diff_accelerator="ddim", diff_speedup=100)
+    torch.manual_seed(31)
+    m = ref.ddpm.MultiVarianceDiffusion(ranges=[(-96.0, -12.0), (-96.0, -20.0)], clamps=[(-96.0, 0.0), None], repeat_bins=8,
+                                        timesteps=1000, k_step=1000, backbone_type="wavenet", backbone_args=SMALL).eval()
+    wtag, sd = shared_weights(ref, 8, 2)
+    m.denoise_fn.load_state_dict(sd)
+    cond = torch.randn(2, T, HIDDEN)
+    log = []
+    torch.manual_seed(33)
+    with torch.no_grad(), record_randn(log):
+        ys = m(cond, infer=True)
+    _save("var_multi_ddim", cond=cond.numpy(), noise=log[0].numpy(), y=torch.stack(list(ys)).numpy(), weights=np.array(wtag))
+    # PitchRectifiedFlow
+    set_reference_hparams(hidden_size=HIDDEN, sampling_algorithm="euler", sampling_steps=10)
+    torch.manual_seed(35)
+    m = ref.reflow.PitchRectifiedFlow(vmin=-8.0, vmax=8.0, cmin=-12.0, cmax=12.0, repeat_bins=16, backbone_type="wavenet",
+                                      backbone_args=SMALL).eval()
+    wtag, sd = shared_weights(ref, 16, 1)
+    m.velocity_fn.load_state_dict(sd)
+    cond = torch.randn(2, T, HIDDEN)
+    log = []
+    torch.manual_seed(37)
+    with torch.no_grad(), record_randn(log):
+        y = m(cond, infer=True)
+    _save("var_pitch_euler", cond=cond.numpy(), noise=log[0].numpy(), y=y.numpy(), weights=np.array(wtag))
+    # cosine schedule and shallow solver paths
+    M, B, T = 16, 2, 41
+    for name, algo, sched, speedup, k_step in (("ddim_cosine", "ddim", "cosine", 50, 1000),
+                                               ("dpm_solver_cosine", "dpm-solver", "cosine", 50, 1000),
+                                               ("unipc_cosine", "unipc", "cosine", 50, 1000),
+                                               ("dpm_solver_shallow", "dpm-solver", "linear", 20, 400),
+                                               ("unipc_shallow", "unipc", "linear", 20, 400)):
+        shallow = k_step < 1000
+        set_reference_hparams(hidden_size=HIDDEN, diff_accelerator=algo, diff_speedup=speedup, schedule_type=sched,
+                              use_shallow_diffusion=shallow, K_step=k_step, K_step_infer=k_step)
+        torch.manual_seed(41)
+        m = ref.ddpm.GaussianDiffusion(M, 1, 1000, k_step, "wavenet", SMALL, spec_min=[-12.0], spec_max=[0.0]).eval()
+        wtag, sd = shared_weights(ref, M, 1)
+        m.denoise_fn.load_state_dict(sd)
+        cond = torch.randn(B, T, HIDDEN)
+        src = torch.rand(B, T, M) * -10.0 if shallow else None
+        log = []
+        torch.manual_seed(43)
+        with torch.no_grad(), record_randn(log):
+            y = m(cond, src_spec=src, infer=True)
+        assert torch.isfinite(y).all(), name
+        arrs = dict(cond=cond.numpy(), noise=log[0].numpy(), y=y.numpy(), meta=np.array([M, 1, 1000, k_step, speedup, int(shallow)]),
+                    schedule=np.array(sched), weights=np.array(wtag))
+        if src is not None:
+            arrs["src"] = src.numpy()
+        _save("ddpm_" + name, **arrs)
+
+
 def main():
     ref = load_reference()
     only = os.environ.get("GOLDEN_ONLY", "")
+    if not only or "extra" in only:
+        gen_extra(ref)
     if not only or "nsf" in only:
         gen_nsf_hifigan(ref)
     if not only or "auxdec" in only:

@@ -123,3 +123,22 @@ def set_reference_hparams(**over) -> dict:
     ref.hparams.clear()
     ref.hparams.update(default_hparams(**over))
     return ref.hparams
+
+
+def load_reference_config(name: str) -> dict:
+    """The reference's YAML config `configs/<name>` with its `base_config` chain merged (utils/hparams.py:64-82), as a plain dict."""
+    import yaml
+
+    def rec(path):
+        with open(path) as f:
+            c = yaml.safe_load(f)
+        out = {}
+        bases = c.pop("base_config", [])
+        for b in ([bases] if isinstance(bases, str) else bases):
+            out.update(rec(os.path.join(REFERENCE_ROOT, b)))
+        out.update(c)
+        return out
+
+    if not reference_available():
+        raise ReferenceUnavailable(f"reference tree not found at {REFERENCE_ROOT}")
+    return rec(os.path.join(REFERENCE_ROOT, "configs", name))

@@ -124,13 +124,15 @@ def _with_noise(noises, fn):
         torch.randn = real
 
 
-@pytest.mark.parametrize("name", ["ddim", "pndm", "dpm_solver_s50", "dpm_solver_s125", "unipc", "ddpm", "ddim_shallow"])
+@pytest.mark.parametrize("name", ["ddim", "pndm", "dpm_solver_s50", "dpm_solver_s125", "unipc", "ddpm", "ddim_shallow",
+                                  "ddim_cosine", "dpm_solver_cosine", "unipc_cosine", "dpm_solver_shallow", "unipc_shallow"])
 def test_gaussian_diffusion_matches_reference_golden(name):
     d, sd, cfg = load_golden("ddpm_" + name)
     M, F, timesteps, k_step, speedup, shallow = [int(v) for v in d["meta"]]
-    algo = {"dpm_solver_s50": "dpm-solver", "dpm_solver_s125": "dpm-solver", "ddim_shallow": "ddim"}.get(name, name)
+    algo = "dpm-solver" if name.startswith("dpm_solver") else name.split("_")[0]
     ds.hparams.clear()
-    ds.hparams.update(hidden_size=cfg["hidden"], schedule_type="linear", use_shallow_diffusion=bool(shallow),
+    ds.hparams.update(hidden_size=cfg["hidden"], schedule_type="cosine" if name.endswith("cosine") else "linear",
+                      use_shallow_diffusion=bool(shallow),
                       diff_accelerator=algo, diff_speedup=speedup, K_step=k_step, K_step_infer=k_step, timesteps=timesteps)
     m = _diffusion(ds.GaussianDiffusion, sd, cfg, out_dims=M, num_feats=F, timesteps=timesteps, k_step=k_step,
                    spec_min=[-12.0], spec_max=[0.0])
@@ -168,6 +170,18 @@ def test_variance_wrappers_match_reference_golden():
                    clamps=[(-96.0, 0.0), (-96.0, 0.0)], repeat_bins=8)
     ys = _with_noise([d["noise"]], lambda: m(d["cond"].to(dev), infer=True))
     assert rel_l2(torch.stack([v.cpu() for v in ys]), d["y"]) < MEL_TOL
+    # round 2: the two wrappers that had no fixture (ddpm.py:448-505, reflow.py:184-203)
+    d, sd, cfg = load_golden("var_multi_ddim")
+    ds.hparams.update(diff_accelerator="ddim", diff_speedup=100)
+    m = _diffusion(ds.MultiVarianceDiffusion, sd, cfg, ranges=[(-96.0, -12.0), (-96.0, -20.0)], clamps=[(-96.0, 0.0), None],
+                   repeat_bins=8, timesteps=1000, k_step=1000)
+    ys = _with_noise([d["noise"]], lambda: m(d["cond"].to(dev), infer=True))
+    assert len(ys) == 2 and rel_l2(torch.stack([v.cpu() for v in ys]), d["y"]) < MEL_TOL
+    d, sd, cfg = load_golden("var_pitch_euler")
+    ds.hparams.update(sampling_algorithm="euler", sampling_steps=10)
+    m = _diffusion(ds.PitchRectifiedFlow, sd, cfg, vmin=-8.0, vmax=8.0, cmin=-12.0, cmax=12.0, repeat_bins=16)
+    y = _with_noise([d["noise"]], lambda: m(d["cond"].to(dev), infer=True))
+    assert y.shape == d["y"].shape and rel_l2(y.cpu(), d["y"]) < MEL_TOL
 
 
 def test_graph_replay_is_deterministic_and_counts_launches():

@@ -36,11 +36,14 @@ def _start(d, sch, t_max):
     return noise
 
 
-@pytest.mark.parametrize("name", ["ddim", "pndm", "dpm_solver_s50", "dpm_solver_s125", "unipc", "ddpm", "ddim_shallow"])
+@pytest.mark.parametrize("name", ["ddim", "pndm", "dpm_solver_s50", "dpm_solver_s125", "unipc", "ddpm", "ddim_shallow",
+                                  # round 2: schedule_type='cosine' (ddpm.py:36-46; lambda-clip active in DPM-Solver++ only, trap T9)
+                                  # and the solvers over a shallow schedule betas[:400] (ddpm.py:246-322)
+                                  "ddim_cosine", "dpm_solver_cosine", "unipc_cosine", "dpm_solver_shallow", "unipc_shallow"])
 def test_gaussian_diffusion(name):
     d, sd, cfg = load_golden("ddpm_" + name)
     M, F, timesteps, k_step, speedup, shallow = [int(v) for v in d["meta"]]
-    sch = so.Schedule(so.linear_betas(timesteps))
+    sch = so.Schedule(so.cosine_betas(timesteps) if name.endswith("cosine") else so.linear_betas(timesteps))
     model = _model(sd, cfg)
     cond = d["cond"].transpose(1, 2)
     t_max = k_step
@@ -91,6 +94,17 @@ def test_variance_wrappers():
     y = so.finish(x, smin, smax).mean(-1)  # [B,F,T]
     ys = torch.stack([v.clamp(-96.0, 0.0) for v in y.unbind(1)])
     assert rel_l2(ys, d["y"]) < TOL
+    # MultiVarianceDiffusion: ddim 10, F=2, second curve unclamped (ddpm.py:448-505)
+    d, sd, cfg = load_golden("var_multi_ddim")
+    x = so.sample_ddim(_model(sd, cfg), sch, d["noise"], d["cond"].transpose(1, 2), 1000, 100)
+    y = so.finish(x, smin, smax).mean(-1)
+    a, b = y.unbind(1)
+    assert rel_l2(torch.stack([a.clamp(-96.0, 0.0), b]), d["y"]) < TOL
+    # PitchRectifiedFlow: euler 10 (reflow.py:184-203)
+    d, sd, cfg = load_golden("var_pitch_euler")
+    x = sv.sample_reflow(_model(sd, cfg), d["noise"], d["cond"].transpose(1, 2), 10, "euler")
+    y = so.finish(x, torch.tensor([-8.0]), torch.tensor([8.0])).mean(-1).clamp(-12.0, 12.0)
+    assert rel_l2(y, d["y"]) < TOL
 
 
 @pytest.mark.parametrize("tag", ["prelu_f1", "silu_f2", "relu_strong"])

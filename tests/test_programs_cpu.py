@@ -23,11 +23,12 @@ def denorm(x_tm, lo=SPEC_MIN, hi=SPEC_MAX):
     return (x_tm + 1) / 2 * (hi - lo) + lo
 
 
-@pytest.mark.parametrize("name", ["ddim", "pndm", "dpm_solver_s50", "dpm_solver_s125", "unipc", "ddpm", "ddim_shallow"])
+@pytest.mark.parametrize("name", ["ddim", "pndm", "dpm_solver_s50", "dpm_solver_s125", "unipc", "ddpm", "ddim_shallow",
+                                  "ddim_cosine", "dpm_solver_cosine", "unipc_cosine", "dpm_solver_shallow", "unipc_shallow"])
 def test_gaussian_programs(name):
     d, sd, cfg = load_golden("ddpm_" + name)
     M, F, timesteps, k_step, speedup, shallow = [int(v) for v in d["meta"]]
-    sch = so.Schedule(so.linear_betas(timesteps))
+    sch = so.Schedule(so.cosine_betas(timesteps) if name.endswith("cosine") else so.linear_betas(timesteps))
     model = OracleWaveNet(sd, cfg["n_feats"], cfg["dilation_cycle_length"])
     t_max = k_step
     x = d["noise"]
