@@ -984,6 +984,58 @@ extern "C" int ds_session_path(const ds_session* s) {
   return s->small ? 1 : (s->medium ? 2 : 0);
 }
 
+// ------------------------------------------------------------------------------------ no-allocation entry point
+// One backbone evaluation whose whole session workspace (cond / x~ / z / skip buffers, step tables: session_layout) lives in a
+// file-scope device array instead of caller memory, for callers that cannot allocate (CUDA-graph capture, tight serving loops).
+// No counterpart in the reference.  Every GPU that loads the library holds the array
+// until exit.  All calls on a device share it and it keeps the last call's contents: nothing in the workspace has to start at
+// zero (every buffer is written by this call's kernels before it is read -- sessions over torch.empty memory rely on the same),
+// so nothing is cleared; two calls that overlap on the GPU (different streams) race on it.
+static __device__ __align__(256) unsigned char g_static_scratch[DS_STATIC_SCRATCH_BYTES];
+constexpr int kMaxStaticDevices = 64;
+static uint8_t* g_static_scratch_ptr[kMaxStaticDevices] = {};  // device address of the array, per device (host code must not use the symbol itself)
+
+static int static_scratch_base(uint8_t** out) {
+  int dev = 0;
+  CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxStaticDevices) return fail(DS_ERR_INVALID, "device ordinal %d outside [0, %d)", dev, kMaxStaticDevices);
+  if (!g_static_scratch_ptr[dev]) {  // once per device, with that device current
+    void* ptr = nullptr;
+    CUDA_TRY(cudaGetSymbolAddress(&ptr, g_static_scratch));
+    if (!ptr) return fail(DS_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch array");
+    g_static_scratch_ptr[dev] = (uint8_t*)ptr;
+  }
+  *out = g_static_scratch_ptr[dev];
+  return 0;
+}
+
+extern "C" size_t ds_static_scratch_bytes(void) { return (size_t)DS_STATIC_SCRATCH_BYTES; }
+
+extern "C" int ds_forward_static(ds_plan* plan, const float* cond_bth, const float* t_dev, int32_t per_sample_times, const float* x_btc,
+                                 float* out_btc, int32_t B, int32_t T, void* stream) {
+  if (!plan || !cond_bth || !t_dev || !x_btc || !out_btc) return fail(DS_ERR_INVALID, "null argument");
+  if (B <= 0 || T <= 0) return fail(DS_ERR_INVALID, "B and T must be positive");
+  if (!plan->packed_ok) return fail(DS_ERR_STATE, "ds_plan_pack_weights has not been called");
+  DS_TRY(ensure_device());
+  const int ps = per_sample_times ? 1 : 0;
+  const size_t need = ds_session_workspace_bytes(plan, B, T, 1, ps);
+  uint8_t* raw = nullptr;
+  DS_TRY(static_scratch_base(&raw));
+  uint8_t* base = (uint8_t*)align_up((size_t)(uintptr_t)raw, 1024);  // session workspaces are 1024-byte aligned; the array 256
+  const size_t usable = (size_t)DS_STATIC_SCRATCH_BYTES - (size_t)(base - raw);
+  if (need == 0 || need > usable)
+    return fail(DS_ERR_INVALID, "ds_forward_static: B=%d x T=%d needs a %zu-byte workspace, the static scratch array holds %zu (DS_STATIC_SCRATCH_BYTES); "
+                "use ds_session_create with caller memory", (int)B, (int)T, need, usable);
+  // the session object is host bookkeeping (tensor maps are passed to the kernels by value): no device allocation anywhere below
+  ds_session* s = nullptr;
+  DS_TRY(ds_session_create(plan, B, T, 1, ps, base, usable, &s));
+  int r = ds_session_set_cond(s, cond_bth, stream);
+  r = r ? r : ds_session_set_times(s, t_dev, 1, stream);
+  r = r ? r : ds_session_forward(s, x_btc, 0, out_btc, stream);
+  ds_session_destroy(s);
+  return r;
+}
+
 // ------------------------------------------------------------------------------------ helpers
 extern "C" int ds_lincomb(float* dst, const float* const* srcs, const float* coefs, int32_t n, size_t numel, void* stream) {
   if (!dst || !srcs || !coefs) return fail(DS_ERR_INVALID, "null argument");

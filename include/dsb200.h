@@ -124,6 +124,20 @@ int64_t ds_session_last_launches(const ds_session* s);
  * tiles (between the two); negative on a null session. */
 int ds_session_path(const ds_session* s);
 
+/* ---- no-allocation entry point.  NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ * out = WaveNet.forward(x, t, cond) exactly as ds_session_set_cond + ds_session_set_times(1 value) + ds_session_forward compute it,
+ * but the session workspace is a file-scope `static __device__` array of DS_STATIC_SCRATCH_BYTES inside the library (held by every
+ * GPU that loads the library, until exit) instead of caller memory; the call performs no cudaMalloc / cudaFree / allocating
+ * library call.  cond_bth [B][T][H], x_btc / out_btc [B][T][F*M] fp32 device pointers; t_dev: 1 fp32 device value, or B values
+ * when per_sample_times != 0.  Shapes whose workspace (ds_session_workspace_bytes(plan, B, T, 1, per_sample_times)) exceeds the
+ * array are rejected with DS_ERR_INVALID.  Every call on a device shares the one array, which keeps the previous call's
+ * contents (nothing in it needs to start at zero); calls that overlap on the GPU (different streams / threads) RACE on it. */
+#define DS_STATIC_SCRATCH_BYTES (32u << 20)
+size_t ds_static_scratch_bytes(void);
+int ds_forward_static(ds_plan* plan, const float* cond_bth, const float* t_dev, int32_t per_sample_times, const float* x_btc,
+                      float* out_btc, int32_t B, int32_t T, void* stream);
+
 /* ---- stand-alone helpers */
 /* dst = sum coef[i]*src[i] over numel fp32 elements (numel % 4 == 0): the sampler tensor update
  * (ddpm.py:164-166,181-201; dpm_solver_pytorch.py:573-576,827-831; uni_pc.py:548-567; reflow.py:68-100). */
