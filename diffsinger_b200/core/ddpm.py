@@ -123,6 +123,15 @@ class GaussianDiffusion(nn.Module):
             self._programs[key] = prog
         return prog
 
+    def _draw_noise(self, b, T, device):
+        """randn(b, F, M, T) from the global generator like the reference (ddpm.py:227, reflow.py:106) -- unless a caller
+        (sharding.sample_sharded) installed the rows of a world-size independent global batch for this call."""
+        pre = getattr(self, '_noise_override', None)
+        if pre is not None:
+            assert tuple(pre.shape) == (b, self.num_feats, self.out_dims, T), (tuple(pre.shape), (b, self.num_feats, self.out_dims, T))
+            return pre.to(device)
+        return torch.randn(b, self.num_feats, self.out_dims, T, device=device)
+
     @torch.no_grad()
     def inference(self, cond, b=1, x_start=None, device=None):
         """cond [B, H, T]; x_start [B, F, M, T] or None -> [B, T, M] / [B, F, T, M] (ddpm.py:221-351)."""
@@ -133,7 +142,7 @@ class GaussianDiffusion(nn.Module):
             assert depth % speedup == 0, f'Acceleration ratio must be a factor of diffusion depth {depth}.'
 
         T = cond.shape[2]
-        noise = torch.randn(b, self.num_feats, self.out_dims, T, device=device)
+        noise = self._draw_noise(b, T, device)
         t_max = min(depth, self.k_step) if self.use_shallow_diffusion else self.k_step
 
         if t_max >= self.timesteps:

@@ -64,12 +64,21 @@ class RectifiedFlow(nn.Module):
         x = self.inference(cond, b=b, x_end=spec, device=device)
         return self.denorm_spec(x)
 
+    def _draw_noise(self, b, T, device):
+        """randn(b, F, M, T) from the global generator like the reference (ddpm.py:227, reflow.py:106) -- unless a caller
+        (sharding.sample_sharded) installed the rows of a world-size independent global batch for this call."""
+        pre = getattr(self, '_noise_override', None)
+        if pre is not None:
+            assert tuple(pre.shape) == (b, self.num_feats, self.out_dims, T), (tuple(pre.shape), (b, self.num_feats, self.out_dims, T))
+            return pre.to(device)
+        return torch.randn(b, self.num_feats, self.out_dims, T, device=device)
+
     @torch.no_grad()
     def inference(self, cond, b=1, x_end=None, device=None):
         """cond [B, H, T]; x_end [B, F, M, T] or None -> [B, T, M] / [B, F, T, M] (reflow.py:104-138)."""
         hparams = get_hparams()
         T = cond.shape[2]
-        noise = torch.randn(b, self.num_feats, self.out_dims, T, device=device)
+        noise = self._draw_noise(b, T, device)
         t_start = hparams.get('T_start_infer', self.t_start)
         if self.use_shallow_diffusion and t_start > 0:
             assert x_end is not None, 'Missing shallow diffusion source.'

@@ -18,7 +18,8 @@ import os
 import sys
 import types
 
-REFERENCE_ROOT = os.environ.get("DS_REFERENCE_ROOT", "/root/reference")
+_REF_COPY = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")  # oracle/build_ref.py (git-ignored, travels to the GPU box)
+REFERENCE_ROOT = os.environ.get("DS_REFERENCE_ROOT") or ("/root/reference" if os.path.isdir("/root/reference") else _REF_COPY)
 
 
 class ReferenceUnavailable(RuntimeError):
@@ -38,6 +39,12 @@ def _stub(name: str, **attrs) -> types.ModuleType:
     for k, v in attrs.items():
         setattr(mod, k, v)
     return mod
+
+
+def _noop_attr(attr):
+    if attr.startswith("__"):
+        raise AttributeError(attr)
+    return lambda *a, **k: None
 
 
 def _install_stubs() -> None:
@@ -76,7 +83,9 @@ def _install_stubs() -> None:
             try:
                 __import__(name)
             except ModuleNotFoundError:
-                _stub(name, use=lambda *a, **k: None)
+                # any attribute resolves to a no-op callable (`from librosa.filters import mel`, `matplotlib.use(...)`): these
+                # packages serve plotting / the DDSP vocoder / MIDI-name parsing, none of which is on the timed path
+                _stub(name, use=lambda *a, **k: None).__getattr__ = _noop_attr
 
 
 _loaded = None

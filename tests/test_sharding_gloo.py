@@ -76,3 +76,51 @@ def test_gather_mels_world2(n_total):
     expect = sharding.sliced_noise((n_total, 4, 6), 99, 0, n_total) * 2.0 + torch.arange(n_total, dtype=torch.float32)[:, None, None]
     for r in range(world):
         assert torch.equal(torch.from_numpy(results[r]), expect)
+
+
+class _StubDiffusion(torch.nn.Module):
+    """Host-logic stand-in for a sampler: a deterministic per-utterance function of (cond row, noise row) that draws its noise
+    the way GaussianDiffusion / RectifiedFlow do (`_draw_noise`, honouring the override sample_sharded installs)."""
+    num_feats, out_dims = 1, 6
+
+    def __init__(self):
+        super().__init__()
+        self.denoise_fn = torch.nn.Linear(1, 1)
+
+    def forward(self, cond, infer=True):
+        b, T = cond.shape[0], cond.shape[1]
+        pre = self._noise_override
+        assert pre is not None and tuple(pre.shape) == (b, 1, 6, T)
+        return cond.sum(-1, keepdim=True) + pre.reshape(b, 6, T).transpose(1, 2)
+
+
+def _sharded_worker(rank, world, port, n_total, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        cond = torch.randn(n_total, 9, 4, generator=torch.Generator().manual_seed(1))
+        full = sharding.sample_sharded(_StubDiffusion(), cond, seed=321, noise_on_device=False)
+        q.put((rank, full.numpy().copy()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n_total", [4, 5])
+def test_sample_sharded_world2_equals_world1(n_total):
+    world, port = 2, _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_sharded_worker, args=(r, world, port, n_total, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = dict(q.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    cond = torch.randn(n_total, 9, 4, generator=torch.Generator().manual_seed(1))
+    expect = sharding.sample_sharded(_StubDiffusion(), cond, seed=321, noise_on_device=False)  # no process group: world 1
+    parts = [sharding.sample_sharded(_StubDiffusion(), cond, seed=321, world=3, rank=r, gather=False, noise_on_device=False)[0]
+             for r in range(3)]
+    assert torch.equal(torch.cat(parts), expect)
+    for r in range(world):
+        assert torch.equal(torch.from_numpy(results[r]), expect)
