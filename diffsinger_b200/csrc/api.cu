@@ -25,6 +25,7 @@
 #include "dwconv_mma_kernel.cuh"
 #include "gemm_pair_kernel.cuh"
 #include "gemm_splitk_kernel.cuh"
+#include "stack_kernel.cuh"
 
 using namespace dsb;
 
@@ -221,7 +222,7 @@ static int launch_gemm(int BN, int epi, const GemmParams& p, cudaStream_t st, bo
   DS_CASE(128, EPI_GATE) DS_CASE(256, EPI_GATE)
   DS_CASE(64, EPI_RES) DS_CASE(128, EPI_RES) DS_CASE(256, EPI_RES)
   DS_CASE(64, EPI_OUTF32) DS_CASE(128, EPI_OUTF32) DS_CASE(256, EPI_OUTF32)
-  DS_CASE(256, EPI_CPROJ)
+  DS_CASE(256, EPI_CPROJ) DS_CASE(128, EPI_CPROJ)
   DS_CASE(128, EPI_SWIGLU) DS_CASE(256, EPI_SWIGLU)
   DS_CASE(64, EPI_GATEBWD) DS_CASE(128, EPI_GATEBWD) DS_CASE(256, EPI_GATEBWD)
 #undef DS_CASE
@@ -328,6 +329,10 @@ struct ds_plan {
   size_t o_w1s, o_b1s;
   size_t o_b1h;  // f16 gate bias for the packed-half gate epilogue of the grouped kernel
   CUtensorMap tm_w1s, tm_w2s, tm_wsks, tm_wsps, tm_wheads;
+  // whole-network kernel for launch-bound sessions (stack_kernel.cuh): C = 256, dilations <= 16, F*M <= 128
+  int stack_ok;
+  int nout;               // output-projection rows per CTA of the 4-CTA cluster (FMr / 4)
+  CUtensorMap tm_wout_st; // output_projection with a (64, nout) box
 };
 
 static void plan_layout(ds_plan* p) {
@@ -419,6 +424,8 @@ extern "C" int ds_plan_create(const ds_wavenet_config* cfg, ds_plan** out) {
   p->S = p->split ? 2 : 1;
   if (p->split) p->fused = 0;
   p->has_small = (!p->split && p->BN_G == 256) ? 1 : 0;
+  p->nout = p->FMr / kStackKB;
+  p->stack_ok = (p->has_small && C == 64 * kStackKB && p->max_dil <= kStackHalo && FM <= 128 && p->FMp <= 128) ? 1 : 0;
   {
     // opt-in (DSB200_HOIST=1): measured on B200 it does NOT pay -- the MMA work drops 12.5 % (281 vs 325 us MMA-side) but
     // the gate epilogue then reads its 2C f16 values per frame from HBM with per-lane row accesses and becomes the
@@ -510,6 +517,7 @@ extern "C" int ds_plan_pack_weights(ds_plan* p, const ds_wavenet_weights* w, voi
     DS_TRY(make_weight_map(&p->tm_wsps, base + p->o_wsp, C, C, 64));
     DS_TRY(make_weight_map(&p->tm_wheads, base + p->o_whead, p->FMp, C, 64));
   }
+  if (p->stack_ok) DS_TRY(make_weight_map(&p->tm_wout_st, base + p->o_wout, C, p->FMr, p->nout));
   p->packed_ok = true;
   return 0;
 }
@@ -537,6 +545,9 @@ struct ds_session {
   bool pdl = true;     // DSB200_PDL=0 turns programmatic dependent launch off
   bool small = false;  // too few frame tiles to fill the SMs: unfused GEMMs with narrow N tiles (plan->has_small)
   bool medium = false; // between the two: unfused GEMMs with the plan's 256-wide tiles (session_is_medium)
+  bool stack = false;  // one launch per evaluation: the whole network in one cluster kernel (session_is_stack, stack_kernel.cuh)
+  size_t o_scproj = 0, o_edges = 0, o_cnt = 0;  // stack sessions: hoisted conditioner projection, edge-frame buffer, arrival counters
+  int eval_seq = 0;    // index of the next evaluation inside the current program run (edge-counter targets)
 };
 
 // one CTA pair of the fused layer kernel owns a 256-frame tile and walks ALL output channels of it serially (~35 us at
@@ -567,6 +578,40 @@ static bool session_is_medium(const ds_plan* p, int B, int T) {
   return pair_tiles >= kMediumLo && pair_tiles <= kMediumHi;
 }
 
+// Launch-bound sessions (a handful of 128-frame tiles: the batch-1 .ds segments, the variance predictors) run every backbone
+// evaluation as ONE launch of ds_stack_kernel: a 4-CTA cluster per tile, all clusters co-resident (neighbouring tiles exchange
+// edge frames through flags in global memory, so a cluster that is not resident would dead-lock its neighbours).
+// DSB200_STACK=0/1 forbids / forces it (forcing still needs co-residency).
+static int stack_max_clusters() {
+  static int cached = -1;
+  if (cached >= 0) return cached;
+  if (ensure_device() != 0) return 0;  // no device (host-only callers): never cache
+  int n = 0;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(kStackKB * 64); cfg.blockDim = dim3(kGemmThreads); cfg.dynamicSmemBytes = kStackSmemBytes;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = kStackKB; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  if (cudaFuncSetAttribute(ds_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStackSmemBytes) != cudaSuccess ||
+      cudaOccupancyMaxActiveClusters(&n, ds_stack_kernel, &cfg) != cudaSuccess) {
+    cudaGetLastError();
+    n = 0;
+  }
+  cached = n;
+  return cached;
+}
+static bool session_is_stack(const ds_plan* p, int B, int T) {
+  if (!p->stack_ok) return false;
+  const char* se = getenv("DSB200_STACK");
+  if (se && atoi(se) == 0) return false;
+  const long tiles = (long)B * ceil_div(T, 128);
+  const int cap = stack_max_clusters();
+  if (tiles > cap) return false;
+  if (se) return true;
+  return tiles <= cap;
+}
+
 static void session_layout(const ds_plan* p, int B, int T, int max_times, int per_sample, ds_session* s) {
   const size_t rows = (size_t)B * T;
   const size_t C = p->C, L = p->L;
@@ -592,6 +637,13 @@ static void session_layout(const ds_plan* p, int B, int T, int max_times, int pe
   // hoisted conditioner projection: f16 [L][rows][2C] (40 KB per frame at C = 512, L = 20); small sessions never use it
   s->o_cproj = 0;
   if (p->hoist && !session_is_small(p, B, T)) s->o_cproj = take(rows * L * 2 * C * 2);
+  s->o_scproj = s->o_edges = s->o_cnt = 0;
+  if (session_is_stack(p, B, T)) {
+    const size_t tiles = (size_t)B * ceil_div(T, 128);
+    s->o_scproj = take(rows * L * 2 * C * 2);
+    s->o_edges = take(2 * tiles * 2 * kStackKB * kStackEdgeBytes);
+    s->o_cnt = take(tiles * 2 * sizeof(unsigned int));
+  }
   s->ws_bytes = off;
 }
 
@@ -618,8 +670,9 @@ extern "C" int ds_session_create(ds_plan* plan, int32_t B, int32_t T, int32_t ma
     return fail(DS_ERR_INVALID, "workspace too small: %zu < %zu", workspace_bytes, need);
   }
   s->ws = (uint8_t*)workspace;
-  s->small = session_is_small(plan, B, T);
-  s->medium = !s->small && session_is_medium(plan, B, T);
+  s->stack = session_is_stack(plan, B, T);
+  s->small = !s->stack && session_is_small(plan, B, T);
+  s->medium = !s->stack && !s->small && session_is_medium(plan, B, T);
   {
     const char* pe = getenv("DSB200_PDL");
     s->pdl = !(pe && atoi(pe) == 0);
@@ -683,6 +736,25 @@ extern "C" int ds_session_set_cond(ds_session* s, const float* cond_bth, void* s
       g.out = s->ws + s->o_cproj + (size_t)l * s->B * s->T * 2 * C * 2;
       g.bias = (const float*)(p->packed + p->o_b1) + (size_t)l * 2 * C;
       DS_TRY(launch_gemm(256, EPI_CPROJ, g, (cudaStream_t)stream));
+    }
+  }
+  if (s->stack) {
+    // hoisted conditioner projection for the whole-network kernel: cproj[l][row][2C] = W_cond_l * cond + b_dil_l + b_cond_l in the
+    // 128-row-pass column order of the narrow gate pack (64 gate columns pre-multiplied by 0.5 | 64 filter columns), f16
+    const ds_plan* p = s->plan;
+    const int C = p->C, L = p->L;
+    const size_t rows = (size_t)s->B * s->T;
+    GemmParams g;
+    memset(&g, 0, sizeof(g));
+    g.T = s->T; g.B = s->B; g.tiles_t = ceil_div(s->T, 128); g.scale = 1.0f;
+    g.tmA0 = s->tm_cond; g.tmB = p->tm_w1s; g.kb_a0 = H / 64; g.n_taps = 1; g.b_k0 = 3 * C;
+    g.n_tiles = 2 * C / 128; g.total_tiles = s->B * g.tiles_t * g.n_tiles;
+    g.ld_out = 2 * C; g.out_c0 = 0;
+    for (int l = 0; l < L; ++l) {
+      g.b_row0 = l * 2 * C;
+      g.out = s->ws + s->o_scproj + (size_t)l * rows * 2 * C * 2;
+      g.bias = (const float*)(p->packed + p->o_b1s) + (size_t)l * 2 * C;
+      DS_TRY(launch_gemm(128, EPI_CPROJ, g, (cudaStream_t)stream));
     }
   }
   s->cond_set = true;
@@ -776,6 +848,38 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   __nv_bfloat16* s2 = (__nv_bfloat16*)(s->ws + s->o_s2);
   const int tiles_t = ceil_div(T, 128);
 
+  if (s->stack) {
+    StackParams sp;
+    memset(&sp, 0, sizeof(sp));
+    sp.tmW1 = p->tm_w1s; sp.tmW2 = p->tm_w2s; sp.tmWsk = p->tm_wsks; sp.tmWsp = p->tm_wsps; sp.tmWhead = p->tm_wheads;
+    sp.tmWout = p->tm_wout_st;
+    sp.x = x; sp.out = out;
+    sp.cproj = (const uint16_t*)(s->ws + s->o_scproj);
+    sp.bhead = (const float*)(pk + p->o_bhead); sp.dtab = dtab; sp.rtab = rtab;
+    sp.bsk = (const float*)(pk + p->o_bsk); sp.bsp = (const float*)(pk + p->o_bsp); sp.bout = (const float*)(pk + p->o_bout);
+    sp.vec_bstride = vstride;
+    sp.edges = s->ws + s->o_edges; sp.cnt = (unsigned int*)(s->ws + s->o_cnt);
+    sp.cnt_base = 8u * (unsigned)L * (unsigned)s->eval_seq;
+    sp.T = T; sp.B = B; sp.tiles_t = tiles_t; sp.n_tiles = B * tiles_t;
+    sp.L = L; sp.cycle = p->cfg.dilation_cycle_length; sp.C = C; sp.FM = p->FM; sp.FMp = p->FMp; sp.nout = p->nout;
+    sp.inv_sqrt_L = 1.0f / sqrtf((float)L);
+    static bool attr_done = false;
+    if (!attr_done) {
+      CUDA_TRY(cudaFuncSetAttribute(ds_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStackSmemBytes));
+      attr_done = true;
+    }
+    if (s->eval_seq == 0 && tiles_t > 1)  // edge-arrival counters restart with every program run (targets are monotonic inside it)
+      CUDA_TRY(cudaMemsetAsync(s->ws + s->o_cnt, 0, (size_t)B * tiles_t * 2 * sizeof(unsigned int), st));
+    struct PdlScope {
+      bool prev;
+      explicit PdlScope(bool on) : prev(t_pdl) { t_pdl = on; }
+      ~PdlScope() { t_pdl = prev; }
+    } pdl_scope(s->pdl && !(s->eval_seq == 0 && tiles_t > 1));  // a launch right after the memset node is a plain dependency
+    CUDA_TRY(launch_k(ds_stack_kernel, dim3(kStackKB * B * tiles_t), dim3(kGemmThreads), kStackSmemBytes, st, sp));
+    ++s->eval_seq;
+    ++*launches;
+    return 0;
+  }
   const int S = p->S;
   const bool split = p->split != 0;
   const bool small = s->small;  // narrow N tiles, unfused layers (see ds_session_create)
@@ -895,6 +999,7 @@ extern "C" int ds_session_forward(ds_session* s, const float* x_btc, int32_t tim
   if (!s || !x_btc || !out_btc) return fail(DS_ERR_INVALID, "null argument");
   DS_TRY(check_eval_ready(s, time_index));
   s->last_launches = 0;
+  s->eval_seq = 0;
   return session_eval(s, x_btc, time_index, out_btc, (cudaStream_t)stream, &s->last_launches);
 }
 
@@ -919,7 +1024,8 @@ static int run_ops(ds_session* s, const ds_op* ops, int n_ops, float* const* buf
     bool prev;
     explicit PdlScope(bool on) : prev(t_pdl) { t_pdl = on; }
     ~PdlScope() { t_pdl = prev; }
-  } pdl_scope((s->small || s->medium || !s->plan->fused) && s->pdl);
+  } pdl_scope((s->stack || s->small || s->medium || !s->plan->fused) && s->pdl);
+  s->eval_seq = 0;
   for (int i = 0; i < n_ops; ++i) {
     const ds_op& op = ops[i];
     if (op.dst < 0 || op.dst >= n_bufs) return fail(DS_ERR_INVALID, "op %d: dst %d out of range", i, op.dst);
@@ -981,7 +1087,7 @@ extern "C" int ds_session_run(ds_session* s, const ds_op* ops, int32_t n_ops, fl
 extern "C" int64_t ds_session_last_launches(const ds_session* s) { return s ? s->last_launches : 0; }
 extern "C" int ds_session_path(const ds_session* s) {
   if (!s) return fail(DS_ERR_INVALID, "null session");
-  return s->small ? 1 : (s->medium ? 2 : 0);
+  return s->stack ? 3 : (s->small ? 1 : (s->medium ? 2 : 0));
 }
 
 // ------------------------------------------------------------------------------------ no-allocation entry point
@@ -1342,7 +1448,7 @@ extern "C" int ds_wgrad(const ds_wgrad_operands* pairs, int32_t n_pairs, int32_t
 // (whatever the last evaluation left there), for per-kernel CUDA-event timing.
 extern "C" int ds_debug_layer(ds_session* s, int32_t layer, int32_t time_index, void* stream) {
   if (!s) return fail(DS_ERR_INVALID, "null argument");
-  if (!s->plan->fused || s->small) return fail(DS_ERR_STATE, "this session runs the unfused two-GEMM layer path");
+  if (!s->plan->fused || s->small || s->stack) return fail(DS_ERR_STATE, "this session does not run one fused kernel per layer");
   if (layer < 0 || layer >= s->plan->L) return fail(DS_ERR_INVALID, "layer %d out of range", layer);
   DS_TRY(check_eval_ready(s, time_index));
   return session_fused_layer(s, layer, time_index, (cudaStream_t)stream);

@@ -1,0 +1,560 @@
+// Whole-network kernel for LAUNCH-BOUND sessions: ONE launch = one complete backbone evaluation (WaveNet.forward,
+// modules/backbones/wavenet.py:75-107: input projection, all L residual layers, skip sum, skip projection, output
+// projection) for sessions of a few 128-frame tiles -- the batch-1 `.ds` segments of inference/ds_acoustic.py:234-244 and the
+// two sequential variance samplers of modules/toplevel.py:281,302 -- which the per-layer kernels can only run as a chain of
+// ~2L+5 dependent launches per evaluation (each ~6 us of launch -> first TMA -> epilogue -> store latency).
+//
+// Layout of the work: a CLUSTER of KB = C/64 CTAs owns one 128-frame tile; CTA r owns output channels [64r, 64r+64) of every
+// GEMM (N-split), so each SM streams only 1/KB of the weights from L2, and the activations never leave the cluster:
+//   * x~ (with a +-16-frame halo for the dilated conv) and the gated activation z live in SHARED MEMORY as K-major
+//     SWIZZLE_128B operand tiles ([rows][64 channels] per k-block); after each epilogue every CTA broadcasts its 64-channel
+//     slice (16 KB) to the other CTAs of the cluster with `cp.async.bulk.shared::cluster` (DSMEM) that completes on the
+//     RECEIVER's mbarrier -- an all-gather without any cluster-wide barrier; the consumer MMA starts on a k-block as soon
+//     as that block has landed (blocks are sent and consumed in the same rotated order).
+//   * the three conv taps are three UMMA descriptors into the same x~ tile shifted by dil rows (as in layer4_kernel.cuh);
+//   * the skip sum is accumulated in TMEM across all L layers (64 fp32 columns per CTA) and never touches memory
+//     ("skip accumulation kept on-chip");
+//   * the step-invariant conditioner projection is hoisted: ds_session_set_cond computes cproj = W_cond*cond + b once per
+//     sampler call (f16, [L][rows][2C]); the gate epilogue adds its row slice (prefetched before the accumulator wait);
+//   * weights stream through a 5-stage TMA ring that runs ahead across layer boundaries (weights do not depend on data).
+// Utterances longer than 128 frames span several clusters; neighbouring tiles exchange the 16 edge frames of x~ per layer
+// through a small global (L2-resident) buffer guarded by per-tile arrival counters -- point-to-point, no grid-wide barrier.
+// All clusters of a launch must be co-resident (the host checks cudaOccupancyMaxActiveClusters).
+//
+// Warp roles (384 threads): warp0 = weight TMA producer, warp1 = MMA issuer, warp2 = TMEM allocator + halo receiver,
+// warp3 idle, warps 4..11 = epilogue (warp & 3 = TMEM lane quadrant, (warp - 4) >> 2 = which 32 of the CTA's 64 channels).
+#pragma once
+#include <cuda.h>
+#include "gemm_kernel.cuh"
+#include "layer3_kernel.cuh"
+
+namespace dsb {
+
+constexpr int kStackKB = 4;                 // cluster size = C / 64 (C = 256)
+constexpr int kStackHalo = 16;              // halo frames each side = largest supported dilation
+constexpr int kStackXRows = 128 + 2 * kStackHalo;
+constexpr uint32_t kStackXTile = kStackXRows * 128u;   // 20480 B per k-block (1024-aligned)
+constexpr uint32_t kStackZTile = 128u * 128u;          // 16384 B per k-block
+constexpr uint32_t kStackStage = 16384u;               // weight ring stage: [128 rows][64 K] bf16
+constexpr int kStackStages = 5;
+constexpr uint32_t kStackSmemBytes = 1024u + kStackKB * (kStackXTile + kStackZTile) + kStackStages * kStackStage + 1024u;
+constexpr uint32_t kStackEdgeBytes = kStackHalo * 128u;  // one k-block of one edge: 16 rows x 128 B
+
+struct StackParams {
+  CUtensorMap tmW1;     // gate weights, 128-row passes (plan o_w1s): dims (3C + H, L * 2C), box (64, 128)
+  CUtensorMap tmW2;     // residual half of output_projection (o_w2): dims (C, L * C), box (64, 64)
+  CUtensorMap tmWsk;    // deferred-skip matrix (o_wsk): dims (L * C, C), box (64, 64)
+  CUtensorMap tmWsp;    // skip_projection (o_wsp): dims (C, C), box (64, 64)
+  CUtensorMap tmWhead;  // input_projection (o_whead): dims (FMp, C), box (64, 64)
+  CUtensorMap tmWout;   // output_projection (o_wout): dims (C, FMr), box (64, nout)
+  const float* x;       // [B][T][FM] fp32
+  float* out;           // [B][T][FM] fp32
+  const uint16_t* cproj;  // f16 [L][B*T][2C], 128-column passes [64 gate (x0.5, bias included) | 64 filter (bias included)]
+  const float* bhead;   // [C]
+  const float* dtab;    // step-embedding projection of layer 0 for this evaluation: [vec_bstride * b + c]
+  const float* rtab;    // folded residual vectors (b2_l - d_l)/sqrt(2) + d_{l+1}: [vec_bstride * b + l * C + c]
+  const float* bsk;     // [C] summed skip-half biases
+  const float* bsp;     // [C]
+  const float* bout;    // [FMr]
+  int vec_bstride;
+  uint8_t* edges;       // [2 parity][tiles][2 sides][KB][16 rows][128 B]: edge frames of x~ in operand (swizzled) layout
+  unsigned int* cnt;    // [tiles][2]: arrivals per (tile, side), monotonic over the evaluations of one program run
+  unsigned int cnt_base;  // 8 * L * (index of this evaluation in the program): targets are cnt_base + 8 * (seq + 1)
+  int T, B, tiles_t, n_tiles;
+  int L, cycle, C, FM, FMp, nout;
+  float inv_sqrt_L;
+};
+
+// ---------------------------------------------------------------- DSMEM / global bulk copies
+__device__ __forceinline__ uint32_t mapa_shared(uint32_t addr, uint32_t cta) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(cta));
+  return r;
+}
+// local shared memory -> the same offset in CTA `cta`; completes (complete_tx) on that CTA's barrier
+__device__ __forceinline__ void bulk_copy_to_peer(uint32_t dst_local_addr, uint32_t src_addr, uint32_t bytes, uint32_t bar_local_addr,
+                                                  uint32_t cta) {
+  asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(mapa_shared(dst_local_addr, cta)), "r"(src_addr), "r"(bytes), "r"(mapa_shared(bar_local_addr, cta))
+               : "memory");
+}
+__device__ __forceinline__ void bulk_copy_g2s(uint32_t dst_addr, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst_addr), "l"(reinterpret_cast<uint64_t>(src)), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+__device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }  // the 8 epilogue warps
+__device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
+}
+
+// position of 16-byte chunk `j` of row `row` inside a [rows][128 B] SWIZZLE_128B tile at a 1024-aligned base
+__device__ __forceinline__ uint32_t sw128_off(int row, int j) { return static_cast<uint32_t>(row) * 128u + ((j ^ (row & 7)) << 4); }
+
+// GEMM-1 step order of CTA r: the centre tap of every k-block first (needs no halo), k-blocks in arrival order r, r+1, ...;
+// then taps 0 and 2 of every k-block.
+__device__ __forceinline__ void stack_conv_step(int i, int r, int& kb, int& tap) {
+  if (i < kStackKB) { kb = (r + i) % kStackKB; tap = 1; }
+  else { const int k = i - kStackKB; kb = (r + (k >> 1)) % kStackKB; tap = (k & 1) * 2; }
+}
+
+__global__ void __cluster_dims__(kStackKB, 1, 1) __launch_bounds__(kGemmThreads, 1)
+ds_stack_kernel(const __grid_constant__ StackParams p) {
+  constexpr int KB = kStackKB;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+  uint8_t* xs = smem;                                   // KB x [160 rows][128 B]
+  uint8_t* zs = xs + KB * kStackXTile;                  // KB x [128 rows][128 B]
+  uint8_t* ring = zs + KB * kStackZTile;                // kStackStages x 16 KB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ring + kStackStages * kStackStage);
+  uint64_t* w_full = bars;
+  uint64_t* w_empty = w_full + kStackStages;
+  uint64_t* x_full = w_empty + kStackStages;  // per k-block of x~ (count 1 + 16 KB of peer bytes)
+  uint64_t* z_full = x_full + KB;             // per k-block of z
+  uint64_t* acc1_full = z_full + KB;
+  uint64_t* acc2_full = acc1_full + 1;
+  uint64_t* aux_full = acc2_full + 1;         // head input cast done
+  uint64_t* halo_full = aux_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(halo_full + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int r = static_cast<int>(cluster_ctarank());
+  const int tile = blockIdx.x / KB;
+  const int b = tile / p.tiles_t;
+  const int tt = tile % p.tiles_t;
+  const int t0 = tt * 128;
+  const bool has_left = tt > 0, has_right = tt + 1 < p.tiles_t;
+  const bool has_nb = has_left || has_right;
+  const int L = p.L, C = p.C;
+  const int KBh = p.FMp / 64;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tmW1);
+    tma_prefetch_desc(&p.tmW2);
+    tma_prefetch_desc(&p.tmWsk);
+    tma_prefetch_desc(&p.tmWsp);
+    tma_prefetch_desc(&p.tmWhead);
+    tma_prefetch_desc(&p.tmWout);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < kStackStages; ++i) {
+      mbar_init(&w_full[i], 1);
+      mbar_init(&w_empty[i], 1);
+    }
+    for (int i = 0; i < KB; ++i) {
+      mbar_init(&x_full[i], 1);
+      mbar_init(&z_full[i], 1);
+    }
+    mbar_init(acc1_full, 1);
+    mbar_init(acc2_full, 1);
+    mbar_init(aux_full, 1);
+    mbar_init(halo_full, 1);
+    fence_barrier_init();
+    // phase 0 of every REMOTE block: this CTA's arrival + the 16 KB the owner will send
+    for (int i = 0; i < KB; ++i)
+      if (i != r) {
+        mbar_arrive_expect_tx(&x_full[i], kStackZTile);
+        mbar_arrive_expect_tx(&z_full[i], kStackZTile);
+      }
+  }
+  // x~ starts as zeros: halo rows outside the utterance ARE the conv's zero padding and are never written
+  for (uint32_t o = threadIdx.x * 16u; o < KB * kStackXTile; o += kGemmThreads * 16u) st_shared_v4(smem_u32(xs) + o, 0, 0, 0, 0);
+  fence_proxy_async_smem();
+  if (warp == 2) tmem_alloc<256>(tmem_slot);
+  tc_fence_before();
+  cluster_sync_all();  // barriers initialised and x~ zeroed in every CTA before any peer sends bytes
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tm_acc1 = tmem_base, tm_acc2 = tmem_base + 128, tm_skip = tmem_base + 192;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ------------------------------------------------------------ weight producer (never waits for data: weights are constant)
+      int st = 0;
+      uint32_t ph = 0;
+      auto begin = [&](uint32_t bytes) -> uint8_t* {
+        mbar_wait(&w_empty[st], ph ^ 1);
+        mbar_arrive_expect_tx(&w_full[st], bytes);
+        return ring + st * kStackStage;
+      };
+      auto end = [&]() { if (++st == kStackStages) { st = 0; ph ^= 1; } };
+      for (int k = 0; k < KBh; ++k) {
+        uint8_t* s = begin(64 * 128);
+        tma_load_2d(&p.tmWhead, &w_full[st], s, k * 64, 64 * r);
+        end();
+      }
+      for (int l = 0; l < L; ++l) {
+        const int row1 = l * 2 * C + 128 * r;
+        for (int i = 0; i < 3 * KB; ++i) {
+          int kb, tap;
+          stack_conv_step(i, r, kb, tap);
+          uint8_t* s = begin(128 * 128);
+          tma_load_2d(&p.tmW1, &w_full[st], s, (tap * KB + kb) * 64, row1);
+          end();
+        }
+        for (int j = 0; j < KB; ++j) {
+          const int kb = (r + j) % KB;
+          const bool res = l + 1 < L;
+          uint8_t* s = begin((res ? 2u : 1u) * 64 * 128);
+          if (res) tma_load_2d(&p.tmW2, &w_full[st], s, kb * 64, l * C + 64 * r);
+          tma_load_2d(&p.tmWsk, &w_full[st], s + 8192, l * C + kb * 64, 64 * r);
+          end();
+        }
+      }
+      for (int j = 0; j < KB; ++j) {
+        uint8_t* s = begin(64 * 128);
+        tma_load_2d(&p.tmWsp, &w_full[st], s, ((r + j) % KB) * 64, 64 * r);
+        end();
+      }
+      for (int j = 0; j < KB; ++j) {
+        uint8_t* s = begin(p.nout * 128);
+        tma_load_2d(&p.tmWout, &w_full[st], s, ((r + j) % KB) * 64, p.nout * r);
+        end();
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ------------------------------------------------------------ MMA issuer
+      constexpr uint32_t id128 = make_idesc_bf16_f32(128), id64 = make_idesc_bf16_f32(64);
+      const uint32_t idout = make_idesc_bf16_f32(static_cast<uint32_t>(p.nout));
+      int st = 0;
+      uint32_t ph = 0;
+      const uint32_t xs_a = smem_u32(xs), zs_a = smem_u32(zs);
+      auto w_wait = [&]() -> uint32_t {
+        mbar_wait(&w_full[st], ph);
+        tc_fence_after();
+        return smem_u32(ring + st * kStackStage);
+      };
+      auto w_release = [&]() {
+        umma_commit(&w_empty[st]);
+        if (++st == kStackStages) { st = 0; ph ^= 1; }
+      };
+      auto mma4 = [&](uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, bool fresh) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (!fresh) || k != 0);
+      };
+      // waits for block kb of x~ / z at phase `phase`, then (remote blocks) arms the next phase
+      auto blk_wait = [&](uint64_t* barv, int kb, uint32_t phase, bool rearm) {
+        mbar_wait(&barv[kb], phase & 1);
+        if (kb != r && rearm) mbar_arrive_expect_tx(&barv[kb], kStackZTile);
+        tc_fence_after();
+      };
+      // head: relu(input_projection(x)) -- A = the cast input in the z buffer                wavenet.py:86-88
+      mbar_wait(aux_full, 0);
+      tc_fence_after();
+      for (int k = 0; k < KBh; ++k) {
+        const uint32_t s = w_wait();
+        mma4(tm_acc2, make_kmajor_sw128_desc(zs_a + k * kStackZTile), make_kmajor_sw128_desc(s), id64, k == 0);
+        w_release();
+      }
+      umma_commit(acc2_full);
+      for (int l = 0; l < L; ++l) {
+        const int dil = 1 << (l % p.cycle);
+        // GEMM-1: dilated conv, N = 64 gate + 64 filter columns of this CTA's channels         wavenet.py:36-38
+        for (int i = 0; i < 3 * KB; ++i) {
+          int kb, tap;
+          stack_conv_step(i, r, kb, tap);
+          if (i < KB) blk_wait(x_full, kb, l, true);
+          if (i == KB && has_nb) {
+            mbar_wait(halo_full, l & 1);
+            tc_fence_after();
+          }
+          const uint32_t s = w_wait();
+          mma4(tm_acc1, make_kmajor_sw128_desc_row(xs_a + kb * kStackXTile, kStackHalo + (tap - 1) * dil), make_kmajor_sw128_desc(s),
+               id128, i == 0);
+          w_release();
+        }
+        umma_commit(acc1_full);
+        // GEMM-2: residual half (fresh accumulator) and skip half (accumulates over all layers)  wavenet.py:44-48,96
+        for (int j = 0; j < KB; ++j) {
+          const int kb = (r + j) % KB;
+          blk_wait(z_full, kb, l, true);
+          const uint32_t s = w_wait();
+          const uint64_t da = make_kmajor_sw128_desc(zs_a + kb * kStackZTile);
+          if (l + 1 < L) mma4(tm_acc2, da, make_kmajor_sw128_desc(s), id64, j == 0);
+          mma4(tm_skip, da, make_kmajor_sw128_desc(s + 8192), id64, l == 0 && j == 0);
+          w_release();
+        }
+        umma_commit(acc2_full);
+      }
+      // relu(skip_projection(sum / sqrt(L))): s1 travels in the x~ buffer (free since the last GEMM-1; the z buffer may still
+      // be read by a slower peer's last GEMM-2)                                                  wavenet.py:96-98
+      for (int j = 0; j < KB; ++j) {
+        const int kb = (r + j) % KB;
+        blk_wait(x_full, kb, L, false);
+        const uint32_t s = w_wait();
+        mma4(tm_acc2, make_kmajor_sw128_desc_row(xs_a + kb * kStackXTile, kStackHalo), make_kmajor_sw128_desc(s), id64, j == 0);
+        w_release();
+      }
+      umma_commit(acc2_full);
+      // output_projection: s2 travels in the z buffer                                            wavenet.py:99
+      for (int j = 0; j < KB; ++j) {
+        const int kb = (r + j) % KB;
+        blk_wait(z_full, kb, L, false);
+        const uint32_t s = w_wait();
+        mma4(tm_acc1, make_kmajor_sw128_desc(zs_a + kb * kStackZTile), make_kmajor_sw128_desc(s), idout, j == 0);
+        w_release();
+      }
+      umma_commit(acc1_full);
+    }
+  } else if (warp == 2) {
+    // -------------------------------------------------------------- halo receiver (utterances of several tiles)
+    if (lane == 0 && has_nb) {
+      grid_dep_wait();
+      const uint32_t bytes = (has_left ? 1u : 0u) * KB * kStackEdgeBytes + (has_right ? 1u : 0u) * KB * kStackEdgeBytes;
+      for (int seq = 0; seq < L; ++seq) {
+        if (seq > 0) mbar_wait(acc1_full, (seq - 1) & 1);  // GEMM-1 of the previous layer has finished reading the halo rows
+        const unsigned int target = p.cnt_base + 8u * (seq + 1);
+        uint32_t spins = 0;
+        if (has_left)
+          while (ld_acquire_gpu(&p.cnt[(tile - 1) * 2 + 1]) < target)
+            if (++spins > (1u << 24)) __trap();
+        if (has_right)
+          while (ld_acquire_gpu(&p.cnt[(tile + 1) * 2 + 0]) < target)
+            if (++spins > (1u << 24)) __trap();
+        fence_proxy_async_all();  // the edges were written through the generic proxy; the bulk copies read them through the async proxy
+        mbar_arrive_expect_tx(halo_full, bytes);
+        const uint8_t* eb = p.edges + static_cast<size_t>(seq & 1) * p.n_tiles * 2 * KB * kStackEdgeBytes;
+        for (int kb = 0; kb < KB; ++kb) {
+          if (has_left)   // the left tile's LAST 16 frames -> rows [0, 16)
+            bulk_copy_g2s(smem_u32(xs) + kb * kStackXTile, eb + (static_cast<size_t>((tile - 1) * 2 + 1) * KB + kb) * kStackEdgeBytes,
+                          kStackEdgeBytes, halo_full);
+          if (has_right)  // the right tile's FIRST 16 frames -> rows [144, 160)
+            bulk_copy_g2s(smem_u32(xs) + kb * kStackXTile + (128 + kStackHalo) * 128u,
+                          eb + (static_cast<size_t>((tile + 1) * 2 + 0) * KB + kb) * kStackEdgeBytes, kStackEdgeBytes, halo_full);
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // -------------------------------------------------------------- epilogue
+    const int quad = warp & 3;
+    const int half = (warp - 4) >> 2;
+    const int row = quad * 32 + lane;       // frame inside the tile = TMEM lane
+    const int t = t0 + row;
+    const bool valid = t < p.T;
+    const size_t grow = static_cast<size_t>(b) * p.T + (valid ? t : p.T - 1);  // global frame row (clamped for loads)
+    const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+    const int c0 = 64 * r + 32 * half;      // first of this thread's 32 channels
+    const uint32_t xrow_a = smem_u32(xs) + r * kStackXTile;   // this CTA's k-block of x~
+    const uint32_t zrow_a = smem_u32(zs) + r * kStackZTile;
+    const bool leader_thread = threadIdx.x == 128;  // warp 4, lane 0
+    uint32_t ph1 = 0, ph2 = 0;
+
+    // writes this thread's 32 bf16 channels (16 packed pairs) of its row into k-block tile `tile_a` at row `trow`
+    auto put_row = [&](uint32_t tile_a, int trow, const uint32_t (&v)[16]) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) st_shared_v4(tile_a + sw128_off(trow, 4 * half + i), v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+    };
+    // edge frames of x~ -> the global edge buffer (operand layout), then one arrival per warp on the tile's counter
+    auto put_edges = [&](int seq, const uint32_t (&v)[16]) {
+      if (!has_nb) return;
+      const bool top = quad == 0 && lane < kStackHalo, bot = quad == 3 && lane >= 32 - kStackHalo;
+      if ((quad == 0 && has_left) || (quad == 3 && has_right)) {
+        const int side = quad == 0 ? 0 : 1;
+        if (top || bot) {
+          const int er = top ? lane : lane - (32 - kStackHalo);  // (er & 7) == ((row + 16) & 7): same swizzle phase
+          uint8_t* dst = p.edges + ((static_cast<size_t>(seq & 1) * p.n_tiles * 2 + tile * 2 + side) * KB + r) * kStackEdgeBytes;
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            *reinterpret_cast<uint4*>(dst + sw128_off(er, 4 * half + i)) = make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        }
+        __syncwarp();
+        if (lane == 0) {
+          __threadfence();
+          atomicAdd(&p.cnt[tile * 2 + side], 1u);
+        }
+      }
+    };
+    // all-gather of this CTA's slice: local arrival + one bulk copy per peer, peers in the order they will consume
+    auto publish = [&](uint32_t tile_a, uint32_t body_off, uint64_t* barv) {
+      fence_proxy_async_smem();
+      tc_fence_before();
+      epi_bar_sync();
+      if (leader_thread) {
+        mbar_arrive(&barv[r]);
+        for (int j = 1; j < KB; ++j) {
+          const uint32_t peer = static_cast<uint32_t>((r + KB - j) % KB);
+          bulk_copy_to_peer(tile_a + body_off, tile_a + body_off, kStackZTile, smem_u32(&barv[r]), peer);
+        }
+      }
+    };
+
+    // ---- head input: x fp32 [B][T][FM] -> bf16 operand tiles in the z buffer (every CTA keeps its own copy)
+    grid_dep_wait();
+    if (half < KBh) {
+      const float* xr = p.x + grow * p.FM + half * 64;
+      const uint32_t ta = smem_u32(zs) + half * kStackZTile;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float f[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const int c = half * 64 + j * 8 + e;
+          f[e] = (valid && c < p.FM) ? __ldg(xr + j * 8 + e) : 0.0f;
+        }
+        st_shared_v4(ta + sw128_off(row, j), pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+      }
+    }
+    fence_proxy_async_smem();
+    epi_bar_sync();
+    if (leader_thread) mbar_arrive(aux_full);
+
+    // ---- head epilogue: x~_0 = relu(acc + b) + d_0                                              wavenet.py:86-88,36
+    {
+      float bb[32], dd[32];
+      ld_f32x32(p.bhead + c0, bb);
+      ld_f32x32(p.dtab + static_cast<size_t>(b) * p.vec_bstride + c0, dd);
+      mbar_wait(acc2_full, ph2);
+      ph2 ^= 1;
+      tc_fence_after();
+      uint32_t a[32];
+      tmem_ld_32x32(lane_addr + 128 + 32 * half, a);
+      tmem_ld_wait();
+      uint32_t o[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const float v0 = valid ? fmaxf(__uint_as_float(a[2 * i]) + bb[2 * i], 0.0f) + dd[2 * i] : 0.0f;
+        const float v1 = valid ? fmaxf(__uint_as_float(a[2 * i + 1]) + bb[2 * i + 1], 0.0f) + dd[2 * i + 1] : 0.0f;
+        o[i] = pack_bf16(v0, v1);
+      }
+      put_row(xrow_a, row + kStackHalo, o);
+      put_edges(0, o);
+      publish(xrow_a, kStackHalo * 128u, x_full);
+    }
+
+    for (int l = 0; l < L; ++l) {
+      // ---- gate: z = sigmoid(g) * tanh(f), packed-half math as in layer4_kernel.cuh                wavenet.py:40-42
+      {
+        const uint16_t* add = p.cproj + (static_cast<size_t>(l) * p.B * p.T + grow) * (2 * C) + 128 * r + 32 * half;
+        uint4 bg[4], bf[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          bg[i] = __ldg(reinterpret_cast<const uint4*>(add) + i);
+          bf[i] = __ldg(reinterpret_cast<const uint4*>(add + 64) + i);
+        }
+        mbar_wait(acc1_full, ph1);
+        ph1 ^= 1;
+        tc_fence_after();
+        constexpr uint32_t kHalf2 = 0x38003800u;  // (0.5h, 0.5h)
+        uint32_t g[32], f[32];
+        tmem_ld_32x32(lane_addr + 32 * half, g);
+        tmem_ld_32x32(lane_addr + 64 + 32 * half, f);
+        tmem_ld_wait();
+        uint32_t zp[16];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint32_t bgw[4] = {bg[i].x, bg[i].y, bg[i].z, bg[i].w};
+          const uint32_t bfw[4] = {bf[i].x, bf[i].y, bf[i].z, bf[i].w};
+#pragma unroll
+          for (int h = 0; h < 4; ++h) {
+            const int q = 4 * i + h;
+            const uint32_t gq = fma_f16x2(pack_f16(__uint_as_float(g[2 * q]), __uint_as_float(g[2 * q + 1])), kHalf2, bgw[h]);
+            const uint32_t fq = add_f16x2(pack_f16(__uint_as_float(f[2 * q]), __uint_as_float(f[2 * q + 1])), bfw[h]);
+            const uint32_t sg = fma_f16x2(tanh_f16x2(gq), kHalf2, kHalf2);
+            zp[q] = f16x2_to_bf16x2(mul_f16x2(sg, tanh_f16x2(fq)));
+          }
+        }
+        put_row(zrow_a, row, zp);
+        publish(zrow_a, 0u, z_full);
+      }
+      // ---- residual: x~' = (x~ + R) / sqrt(2) + rvec_l  (not after the last layer: wavenet.py:92-94 discards it)
+      if (l + 1 < L) {
+        float rr[32];
+        ld_f32x32(p.rtab + static_cast<size_t>(b) * p.vec_bstride + static_cast<size_t>(l) * C + c0, rr);
+        uint4 xq[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) xq[i] = ld_shared_v4(xrow_a + sw128_off(row + kStackHalo, 4 * half + i));
+        mbar_wait(acc2_full, ph2);
+        ph2 ^= 1;
+        tc_fence_after();
+        uint32_t a[32];
+        tmem_ld_32x32(lane_addr + 128 + 32 * half, a);
+        tmem_ld_wait();
+        uint32_t o[16];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint32_t w[4] = {xq[i].x, xq[i].y, xq[i].z, xq[i].w};
+#pragma unroll
+          for (int h = 0; h < 4; ++h) {
+            const int q = 8 * i + 2 * h;
+            const float v0 = fmaf(__uint_as_float(a[q]) + __uint_as_float(w[h] << 16), 0.70710678118654752f, rr[q]);
+            const float v1 = fmaf(__uint_as_float(a[q + 1]) + __uint_as_float(w[h] & 0xffff0000u), 0.70710678118654752f, rr[q + 1]);
+            o[4 * i + h] = valid ? pack_bf16(v0, v1) : 0u;
+          }
+        }
+        put_row(xrow_a, row + kStackHalo, o);
+        put_edges(l + 1, o);
+        publish(xrow_a, kStackHalo * 128u, x_full);
+      }
+    }
+    // ---- skip sum (TMEM, all layers) -> s1 = (sum + b) / sqrt(L)                                   wavenet.py:96
+    {
+      float bb[32];
+      ld_f32x32(p.bsk + c0, bb);
+      mbar_wait(acc2_full, ph2);
+      ph2 ^= 1;
+      tc_fence_after();
+      uint32_t a[32];
+      tmem_ld_32x32(lane_addr + 192 + 32 * half, a);
+      tmem_ld_wait();
+      uint32_t o[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i)
+        o[i] = pack_bf16((__uint_as_float(a[2 * i]) + bb[2 * i]) * p.inv_sqrt_L, (__uint_as_float(a[2 * i + 1]) + bb[2 * i + 1]) * p.inv_sqrt_L);
+      put_row(xrow_a, row + kStackHalo, o);
+      publish(xrow_a, kStackHalo * 128u, x_full);
+    }
+    // ---- s2 = relu(skip_projection(s1) + b)                                                        wavenet.py:97-98
+    {
+      float bb[32];
+      ld_f32x32(p.bsp + c0, bb);
+      mbar_wait(acc2_full, ph2);
+      ph2 ^= 1;
+      tc_fence_after();
+      uint32_t a[32];
+      tmem_ld_32x32(lane_addr + 128 + 32 * half, a);
+      tmem_ld_wait();
+      uint32_t o[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i)
+        o[i] = pack_bf16(fmaxf(__uint_as_float(a[2 * i]) + bb[2 * i], 0.0f), fmaxf(__uint_as_float(a[2 * i + 1]) + bb[2 * i + 1], 0.0f));
+      put_row(zrow_a, row, o);
+      publish(zrow_a, 0u, z_full);
+    }
+    // ---- output projection -> fp32 [B][T][FM]: this CTA's nout columns, 16 per warp half             wavenet.py:99
+    {
+      mbar_wait(acc1_full, ph1);
+      ph1 ^= 1;
+      tc_fence_after();
+      const int ncols = p.nout / 2;  // 8 or 16 columns per thread
+      const int n0 = p.nout * r + ncols * half;
+      uint32_t a[32];
+      tmem_ld_32x32(lane_addr + ncols * half, a);  // reads 32 columns; only the first `ncols` are this thread's
+      tmem_ld_wait();
+      if (valid) {
+        float* orow = p.out + grow * p.FM;
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+          if (i < ncols && n0 + i < p.FM) orow[n0 + i] = __uint_as_float(a[i]) + __ldg(p.bout + n0 + i);
+      }
+    }
+  }
+  tc_fence_before();
+  cluster_sync_all();  // no CTA leaves while peers may still write its shared memory / read its barriers
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<256>(tmem_base);
+  }
+}
+
+}  // namespace dsb

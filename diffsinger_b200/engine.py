@@ -124,8 +124,9 @@ class Session:
 
     @property
     def path(self) -> str:
-        """'fused' | 'small' | 'medium': the kernels this session's residual layers run on (include/dsb200.h: ds_session_path)."""
-        return ("fused", "small", "medium")[int(nat.lib().ds_session_path(self.handle))]
+        """'fused' | 'small' | 'medium' | 'stack': the kernels this session's residual layers run on (include/dsb200.h:
+        ds_session_path)."""
+        return ("fused", "small", "medium", "stack")[int(nat.lib().ds_session_path(self.handle))]
 
     def close(self):
         if self.handle:

@@ -121,7 +121,8 @@ int ds_session_run(ds_session* s, const ds_op* ops, int32_t n_ops, float* const*
 int64_t ds_session_last_launches(const ds_session* s);
 /* Which kernels the session's residual layers run on, chosen at creation from (B, T) and the plan: 0 = one fused kernel per
  * layer (ds_plan_layer_mode), 1 = unfused GEMMs with narrow N tiles (few frame tiles), 2 = unfused GEMMs with the plan's 256-wide
- * tiles (between the two); negative on a null session. */
+ * tiles (between the two), 3 = the whole network in ONE launch per evaluation (csrc/stack_kernel.cuh: launch-bound sessions of a
+ * few 128-frame tiles at C = 256, e.g. batch-1 .ds segments and the variance predictors); negative on a null session. */
 int ds_session_path(const ds_session* s);
 
 /* ---- no-allocation entry point.  NO COUNTERPART IN THE REFERENCE: added for callers that

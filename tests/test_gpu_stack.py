@@ -1,0 +1,107 @@
+"""The whole-network kernel (csrc/stack_kernel.cuh, session path 'stack'): one launch per backbone evaluation for launch-bound
+sessions (C = 256; batch-1 `.ds` segments, the pitch predictor).  Checked against the CPU oracle at the suite's per-evaluation
+bf16 bar (2e-2), against the per-layer kernel chain (DSB200_STACK=0) to bf16 round-off, and end to end through the samplers
+(final result rel-L2 <= 1e-2).  Cases are ordered from the simplest (one layer, one tile) to the real configurations so that
+`-x` stops at the first construct that breaks."""
+import pytest
+import torch
+
+import diffsinger_b200 as ds
+from conftest import rel_l2
+from oracle.wavenet_oracle import OracleWaveNet, random_state_dict
+from oracle import samplers_oracle as so
+
+pytestmark = pytest.mark.gpu
+dev = "cuda"
+EVAL_TOL = 2e-2
+MEL_TOL = 1e-2
+
+
+def _net(sd, M, F, L, C, cycle, H=256):
+    ds.hparams.clear()
+    ds.hparams.update(hidden_size=H)
+    net = ds.WaveNet(M, F, num_layers=L, num_channels=C, dilation_cycle_length=cycle)
+    net.load_state_dict(sd, strict=True)
+    return net.eval().to(dev)
+
+
+def _path(net):
+    return next(reversed(net.engine().sessions.values())).path
+
+
+@pytest.mark.parametrize("L,cycle,M,F,B,T", [
+    (1, 1, 64, 1, 1, 128),     # head + one layer (no residual exchange) + tail, one full tile
+    (2, 1, 64, 1, 1, 128),     # one residual exchange
+    (4, 4, 128, 1, 1, 97),     # dilations 1..8, ragged single tile (frames >= T must stay zero: conv padding)
+    (20, 5, 64, 1, 1, 128),    # pitch predictor depth, dilation 16
+    (3, 2, 64, 1, 1, 130),     # two tiles: edge frames through global memory (second tile holds 2 frames)
+    (20, 5, 64, 1, 1, 512),    # pitch predictor, four tiles
+    (20, 4, 128, 1, 1, 517),   # config #1 backbone, five tiles
+    (20, 4, 128, 1, 3, 300),   # batch of three utterances x three tiles
+    (6, 3, 24, 2, 2, 200),     # F = 2, F*M = 48 (output rows padded to 64)
+])
+def test_stack_forward_matches_oracle_and_chain(monkeypatch, L, cycle, M, F, B, T):
+    C = 256
+    sd = random_state_dict(M, F, L, C, 256, seed=L * 7 + T)
+    g = torch.Generator().manual_seed(5)
+    spec = torch.randn(B, F, M, T, generator=g)
+    cond = torch.randn(B, T, 256, generator=g).transpose(1, 2)
+    t = torch.tensor([617.25])
+    ref = OracleWaveNet(sd, F, cycle)(spec, t, cond)
+    net = _net(sd, M, F, L, C, cycle)
+    with torch.no_grad():
+        y = net(spec.to(dev), t.to(dev), cond.to(dev))
+    torch.cuda.synchronize()
+    assert _path(net) == "stack"
+    sess = next(reversed(net.engine().sessions.values()))
+    assert sess.last_launches == 1
+    e_oracle = rel_l2(y.cpu(), ref)
+    monkeypatch.setenv("DSB200_STACK", "0")
+    net2 = _net(sd, M, F, L, C, cycle)
+    with torch.no_grad():
+        y2 = net2(spec.to(dev), t.to(dev), cond.to(dev))
+    assert _path(net2) != "stack"
+    e_chain = rel_l2(y.cpu(), y2.cpu())
+    print(f"\n[stack L{L} cycle{cycle} M{M} F{F} B{B} T{T}] vs oracle {e_oracle:.3e}, vs kernel chain {e_chain:.3e} "
+          f"(chain vs oracle {rel_l2(y2.cpu(), ref):.3e})")
+    assert torch.isfinite(y).all()
+    assert e_oracle < EVAL_TOL and e_chain < EVAL_TOL
+    if B > 1:  # per-sample diffusion steps (training-style call, ddpm.py:212-219)
+        monkeypatch.delenv("DSB200_STACK")
+        tb = torch.linspace(3.0, 990.0, B)
+        ref = OracleWaveNet(sd, F, cycle)(spec, tb, cond)
+        with torch.no_grad():
+            y = net(spec.to(dev), tb.to(dev), cond.to(dev))
+        assert rel_l2(y.cpu(), ref) < EVAL_TOL
+
+
+@pytest.mark.parametrize("T", [128, 300])
+def test_pitch_predictor_ddim20_on_the_stack_kernel(T):
+    """configs[3]: PitchDiffusion (WaveNet 20 x 256, cycle 5, 64 repeat bins), DDIM 20 steps, batch 1: 20 evaluation launches +
+    20 sampler updates in one CUDA graph; final curve against the oracle sampler."""
+    M, F, L, C, H, cycle = 64, 1, 20, 256, 256, 5
+    sd = random_state_dict(M, F, L, C, H, seed=33)
+    ds.hparams.clear()
+    ds.hparams.update(hidden_size=H, schedule_type="linear", use_shallow_diffusion=False, diff_accelerator="ddim", diff_speedup=50,
+                      K_step=1000, K_step_infer=1000, timesteps=1000)
+    m = ds.PitchDiffusion(vmin=-8.0, vmax=8.0, cmin=-12.0, cmax=12.0, repeat_bins=M, timesteps=1000, k_step=1000,
+                          backbone_type="wavenet", backbone_args=dict(num_layers=L, num_channels=C, dilation_cycle_length=cycle))
+    m.denoise_fn.load_state_dict(sd)
+    m = m.eval().to(dev)
+    g = torch.Generator().manual_seed(3)
+    cond = torch.randn(1, T, H, generator=g)
+    noise = torch.randn(1, F, M, T, generator=g)
+    outs = []
+    for _ in range(2):  # capture, then replay
+        m._noise_override = noise.to(dev)
+        with torch.no_grad():
+            outs.append(m(cond.to(dev), infer=True).cpu())
+    m._noise_override = None
+    assert torch.equal(outs[0], outs[1])
+    sess = next(iter(m.denoise_fn.engine().sessions.values()))
+    assert sess.path == "stack" and sess.last_launches == 40
+    x = so.sample_ddim(OracleWaveNet(sd, F, cycle), so.Schedule(so.linear_betas(1000)), noise, cond.transpose(1, 2), 1000, 50)
+    ref = so.finish(x, torch.tensor([-8.0]), torch.tensor([8.0])).mean(-1).clamp(-12.0, 12.0)
+    err = rel_l2(outs[0], ref)
+    print(f"\n[pitch predictor ddim-20, T={T}, stack kernel] final curve rel-L2 {err:.3e}")
+    assert err < MEL_TOL
