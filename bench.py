@@ -171,7 +171,7 @@ def workload_name():
             f"DPM-Solver++ {c['K']} steps (configs[1])")
 
 
-LAYER_KERNELS = {0: "ds_gemm_kernel<256, EPI_GATE> + ds_gemm_kernel<256, EPI_RES>", 5: "ds_layer_grp_kernel"}
+LAYER_KERNELS = {0: "ds_gemm_kernel<256, EPI_GATE> + ds_gemm_kernel<256, EPI_RES>", 5: "ds_layer_grp_kernel"}  # ds_plan_layer_mode
 
 
 def time_layer_kernel(session, L, min_launches=2000):

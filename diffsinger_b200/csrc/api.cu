@@ -16,9 +16,6 @@
 #include "aux_kernels.cuh"
 #include "gemm_epilogue.cuh"
 #include "layer_kernel.cuh"
-#include "layer2_kernel.cuh"
-#include "layer3_kernel.cuh"
-#include "layer4_kernel.cuh"
 #include "mma_bench.cuh"
 #include "wgrad_kernel.cuh"
 #include "conv_small_kernel.cuh"
@@ -229,46 +226,6 @@ static int launch_gemm(int BN, int epi, const GemmParams& p, cudaStream_t st, bo
   return fail(DS_ERR_INVALID, "no GEMM instantiation for BN=%d epilogue=%d", BN, epi);
 }
 
-template <int BN2, bool kZSmem>
-static int launch_layer_t(const LayerParams& p, cudaStream_t st) {
-  static bool attr_done = false;
-  auto kern = ds_layer_kernel<BN2, kZSmem>;
-  if (!attr_done) {
-    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
-    attr_done = true;
-  }
-  const int grid = p.total_tiles < g_num_sms ? p.total_tiles : g_num_sms;
-  kern<<<grid, kGemmThreads, layer_smem_bytes(p.kb_c, p.stages, kZSmem), st>>>(p);
-  CUDA_TRY(cudaGetLastError());
-  return 0;
-}
-
-static int launch_layer_pair(const LayerParams& p, cudaStream_t st) {
-  static bool attr_done = false;
-  if (!attr_done) {
-    CUDA_TRY(cudaFuncSetAttribute(ds_layer_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmemBytes));
-    attr_done = true;
-  }
-  const int max_pairs = g_num_sms / 2;
-  const int pairs = p.total_tiles < max_pairs ? p.total_tiles : max_pairs;
-  ds_layer_pair_kernel<<<2 * pairs, kGemmThreads, kPairSmemBytes, st>>>(p);
-  CUDA_TRY(cudaGetLastError());
-  return 0;
-}
-
-static int launch_layer_halo(const LayerParams& p, int max_dil, cudaStream_t st) {
-  static bool attr_done = false;
-  if (!attr_done) {
-    CUDA_TRY(cudaFuncSetAttribute(ds_layer_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kHaloSmemMax));
-    attr_done = true;
-  }
-  const int max_pairs = g_num_sms / 2;
-  const int pairs = p.total_tiles < max_pairs ? p.total_tiles : max_pairs;
-  ds_layer_halo_kernel<<<2 * pairs, kGemmThreads, halo_smem_bytes(max_dil), st>>>(p);
-  CUDA_TRY(cudaGetLastError());
-  return 0;
-}
-
 static int launch_layer_grp(const LayerParams& p, int max_dil, cudaStream_t st) {
   static bool attr_done = false;
   if (!attr_done) {
@@ -303,12 +260,10 @@ struct ds_plan {
   int K1;                // gate GEMM K = 3C + H
   int BN_G, BN_C, BN_O;  // N tile of the gate GEMM / the C-wide GEMMs / the output projection
   int FMr;               // output-projection rows padded to BN_O
-  int fused;             // 0: gate GEMM + residual GEMM; 1: one kernel per layer, z kept in smem; 2: one kernel per
-                         // layer, GEMM-2 re-reads z through TMA (4-deep operand ring); 3: as 2 on CTA pairs (cta_group::2);
-                         // 4: CTA pairs + halo-carrying activation tiles shared by the three conv taps
-                         // 5: as 4 with grouped pipeline stages (12 / 8 UMMAs per mbarrier hand-shake)
+  int fused;             // 0: gate GEMM + residual GEMM; 5: ONE kernel per layer on CTA pairs (layer_kernel.cuh: cta_group::2,
+                         // halo-carrying activation tiles, grouped pipeline stages).  (1-4 were the kernel generations removed in
+                         // round 2; the value 5 is kept so that ds_plan_layer_mode stays comparable with the round-1 profiles.)
   int max_dil;
-  int fused_stages;
   int hoist;             // grouped kernel only: the step-invariant conditioner projection is computed once per sampler
                          // call (ds_session_set_cond) into an f16 buffer and added in the gate epilogue
   int split;             // fp32-accurate mode: every bf16 operand carries a lo half (3 x bf16 split products)
@@ -393,26 +348,13 @@ extern "C" int ds_plan_create(const ds_wavenet_config* cfg, ds_plan** out) {
   p->BN_C = (C % 256 == 0) ? 256 : ((C % 128 == 0) ? 128 : 64);
   p->BN_O = FM > 128 ? 256 : (FM > 64 ? 128 : 64);
   p->FMr = (int)align_up(FM, p->BN_O);
-  // fused layer kernel: needs N=256 gate passes and the whole gated tile (C x 128 bf16) in shared memory
-  p->fused_stages = 0;
-  if (C % 128 == 0) {
-    int st = (int)((232448 - 1280 - (C / 64) * (int)kLayerABytes) / (int)(kLayerABytes + kLayerBBytes));
-    p->fused_stages = st > kLayerMaxStages ? kLayerMaxStages : st;
-  }
-  // DSB200_LAYER_MODE = unfused | smem | global | pair | halo.  Default: halo (CTA pairs, halo-carrying activation tiles)
-  // when C % 256 == 0 and the largest dilation is <= 16; else global (one kernel per layer, single CTA) when
-  // C % 128 == 0; else unfused.  The other modes stay selectable for the parity tests and the A/B numbers in profiles/.
+  // DSB200_LAYER_MODE = grp | unfused.  Default: grp (one kernel per layer) when C % 256 == 0 and the largest dilation is <= 16,
+  // else the two-GEMM path.
   const char* env = getenv("DSB200_LAYER_MODE");
   p->max_dil = 1 << ((cfg->dilation_cycle_length < cfg->num_layers ? cfg->dilation_cycle_length : cfg->num_layers) - 1);
-  const bool can_pair = C % 256 == 0, can_halo = can_pair && p->max_dil <= 16;
-  p->fused = can_halo ? 5 : ((C % 128 == 0) ? 2 : 0);
-  if (env && !strcmp(env, "grp") && can_halo) p->fused = 5;
-  if (env && !strcmp(env, "halo") && can_halo) p->fused = 4;
-  if (env && !strcmp(env, "pair") && can_pair) p->fused = 3;
-  if (env && !strcmp(env, "global") && C % 128 == 0) p->fused = 2;
+  const bool can_grp = C % 256 == 0 && p->max_dil <= 16;
+  p->fused = can_grp ? 5 : 0;
   if (env && !strcmp(env, "unfused")) p->fused = 0;
-  if (env && !strcmp(env, "smem") && p->fused_stages >= 2) p->fused = 1;
-  if (p->fused == 2) p->fused_stages = kLayerMaxStages;
   // precision 1 = fp32-accurate: 3 x bf16 split products on the unfused GEMM path (per-evaluation rel-L2 <= 1e-4 against
   // the fp32 reference; tcgen05 has no fp32 MMA and one-pass TF32 gives ~6e-4).  DSB200_PRECISION=fp32 forces it.
   const char* pe = getenv("DSB200_PRECISION");
@@ -593,8 +535,8 @@ static int stack_max_clusters() {
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = kStackKB; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
   cfg.attrs = at; cfg.numAttrs = 1;
-  if (cudaFuncSetAttribute(ds_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStackSmemBytes) != cudaSuccess ||
-      cudaOccupancyMaxActiveClusters(&n, ds_stack_kernel, &cfg) != cudaSuccess) {
+  if (cudaFuncSetAttribute(ds_stack_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStackSmemBytes) != cudaSuccess ||
+      cudaOccupancyMaxActiveClusters(&n, ds_stack_kernel<false>, &cfg) != cudaSuccess) {
     cudaGetLastError();
     n = 0;
   }
@@ -686,7 +628,7 @@ extern "C" int ds_session_create(ds_plan* plan, int32_t B, int32_t T, int32_t ma
   r = r ? r : make_act_map(&s->tm_z, s->ws + s->o_z, plan->L * plan->C * Sm, T, B);
   r = r ? r : make_act_map(&s->tm_s1, s->ws + s->o_s1, plan->C * Sm, T, B);
   r = r ? r : make_act_map(&s->tm_s2, s->ws + s->o_s2, plan->C * Sm, T, B);
-  if (plan->fused >= 4)
+  if (plan->fused == 5)
     for (int k = 0; (1 << k) <= plan->max_dil; ++k) {
       r = r ? r : make_act_map(&s->tm_xh[0][k], s->ws + s->o_xt, plan->C, T, B, 128 + 2 * (1 << k));
       r = r ? r : make_act_map(&s->tm_xh[1][k], s->ws + s->o_xt1, plan->C, T, B, 128 + 2 * (1 << k));
@@ -780,29 +722,22 @@ extern "C" int ds_session_set_times(ds_session* s, const float* t_dev, int32_t n
   return 0;
 }
 
-// One fused residual layer (modes 1-4): gate GEMM -> gated tile -> residual GEMM in ONE kernel   wavenet.py:33-48
+// One fused residual layer: gate GEMM -> gated tile -> residual GEMM in ONE kernel (layer_kernel.cuh)   wavenet.py:33-48
 static int session_fused_layer(ds_session* s, int l, int time_index, cudaStream_t st) {
   const ds_plan* p = s->plan;
   const int C = p->C, L = p->L, B = s->B, T = s->T;
   const uint8_t* pk = p->packed;
   const int Bt = s->per_sample ? B : 1;
   const float* rtab = (const float*)(s->ws + s->o_r) + (size_t)time_index * Bt * L * C;
-  const int tiles_t = ceil_div(T, 128);
   __nv_bfloat16* xts[2] = {(__nv_bfloat16*)(s->ws + s->o_xt), (__nv_bfloat16*)(s->ws + s->o_xt1)};
   LayerParams lp;
   memset(&lp, 0, sizeof(lp));
-  lp.tmCond = s->tm_cond; lp.tmW1 = p->tm_w1; lp.tmW2 = p->tm_w2; lp.tmZ = s->tm_z;
-  lp.T = T; lp.B = B; lp.tiles_t = tiles_t; lp.total_tiles = B * tiles_t;
-  lp.kb_c = C / 64; lp.kb_h = p->H / 64; lp.p1 = 2 * C / 256; lp.stages = p->fused_stages;
+  lp.tmCond = s->tm_cond; lp.tmW1 = p->tm_w1h; lp.tmW2 = p->tm_w2h; lp.tmZ = s->tm_z;
+  lp.T = T; lp.B = B; lp.tiles_t = ceil_div(T, 256); lp.total_tiles = B * lp.tiles_t;  // 256-frame tiles, one per CTA pair
+  lp.kb_c = C / 64; lp.kb_h = p->H / 64; lp.p1 = 2 * C / 256;
   lp.vec_bstride = s->per_sample ? L * C : 0; lp.z_out = (__nv_bfloat16*)(s->ws + s->o_z); lp.ld_z = L * C;
   lp.trace = g_trace; lp.trace_cap = g_trace_cap;
   { const char* de = getenv("DSB200_DBG"); lp.dbg = de ? atoi(de) : 0; }
-  const bool pair = p->fused >= 3;
-  lp.a_slot = halo_a_slot_bytes(p->max_dil); lp.n_a = halo_n_a(p->max_dil);
-  if (pair) {
-    lp.tmW1 = p->tm_w1h; lp.tmW2 = p->tm_w2h;
-    lp.tiles_t = ceil_div(tiles_t, 2); lp.total_tiles = B * lp.tiles_t;
-  }
   lp.tmX = (l & 1) ? s->tm_xt1 : s->tm_xt;
   lp.x_in = xts[l & 1]; lp.x_out = xts[(l + 1) & 1];
   lp.dil = 1 << (l % p->cfg.dilation_cycle_length);
@@ -811,24 +746,15 @@ static int session_fused_layer(ds_session* s, int l, int time_index, cudaStream_
   lp.bias1 = (const float*)(pk + p->o_b1) + (size_t)l * 2 * C;
   lp.rvec = rtab + (size_t)l * C;
   lp.z_c0 = l * C;
-  if (p->fused == 5) {
-    lp.tmXh = s->tm_xh[l & 1][l % p->cfg.dilation_cycle_length];
-    lp.a_slot = halo_a_slot_bytes(p->max_dil); lp.n_a = grp_stages(p->max_dil);
-    lp.tmZs = s->tm_zs; lp.tmXs = s->tm_xs[(l + 1) & 1];
-    lp.bias1h = (const uint16_t*)(pk + p->o_b1h) + (size_t)l * 2 * C;
-    if (s->o_cproj) {
-      lp.cproj = (const uint16_t*)(s->ws + s->o_cproj) + (size_t)l * B * T * 2 * C; lp.ld_cproj = 2 * C;
-      lp.kb_h = 0;  // the conditioner K blocks are not run per evaluation
-    }
-    return launch_layer_grp(lp, p->max_dil, st);
+  lp.tmXh = s->tm_xh[l & 1][l % p->cfg.dilation_cycle_length];
+  lp.a_slot = halo_a_slot_bytes(p->max_dil); lp.n_a = grp_stages(p->max_dil);
+  lp.tmZs = s->tm_zs; lp.tmXs = s->tm_xs[(l + 1) & 1];
+  lp.bias1h = (const uint16_t*)(pk + p->o_b1h) + (size_t)l * 2 * C;
+  if (s->o_cproj) {
+    lp.cproj = (const uint16_t*)(s->ws + s->o_cproj) + (size_t)l * B * T * 2 * C; lp.ld_cproj = 2 * C;
+    lp.kb_h = 0;  // the conditioner K blocks are not run per evaluation
   }
-  if (p->fused == 4) {
-    lp.tmXh = s->tm_xh[l & 1][l % p->cfg.dilation_cycle_length];
-    return launch_layer_halo(lp, p->max_dil, st);
-  }
-  if (pair) return launch_layer_pair(lp, st);
-  if (p->fused == 1) return p->BN_C == 256 ? launch_layer_t<256, true>(lp, st) : launch_layer_t<128, true>(lp, st);
-  return p->BN_C == 256 ? launch_layer_t<256, false>(lp, st) : launch_layer_t<128, false>(lp, st);
+  return launch_layer_grp(lp, p->max_dil, st);
 }
 
 // One backbone evaluation = 2L+4 launches on `st` (WaveNet.forward, wavenet.py:75-107).
@@ -863,11 +789,15 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
     sp.T = T; sp.B = B; sp.tiles_t = tiles_t; sp.n_tiles = B * tiles_t;
     sp.L = L; sp.cycle = p->cfg.dilation_cycle_length; sp.C = C; sp.FM = p->FM; sp.FMp = p->FMp; sp.nout = p->nout;
     sp.inv_sqrt_L = 1.0f / sqrtf((float)L);
+    { const char* de = getenv("DSB200_DBG"); sp.dbg = de ? atoi(de) : 0; }
+    sp.trace = g_trace; sp.trace_cap = g_trace_cap * 4;  // ds_debug_set_trace counts entries of 4 words
     static bool attr_done = false;
     if (!attr_done) {
-      CUDA_TRY(cudaFuncSetAttribute(ds_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStackSmemBytes));
+      CUDA_TRY(cudaFuncSetAttribute(ds_stack_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStackSmemBytes));
+      CUDA_TRY(cudaFuncSetAttribute(ds_stack_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStackSmemBytes));
       attr_done = true;
     }
+    const bool dbg_build = sp.dbg != 0 || sp.trace != nullptr;  // role switches / timeline: the instrumented instantiation
     if (s->eval_seq == 0 && tiles_t > 1)  // edge-arrival counters restart with every program run (targets are monotonic inside it)
       CUDA_TRY(cudaMemsetAsync(s->ws + s->o_cnt, 0, (size_t)B * tiles_t * 2 * sizeof(unsigned int), st));
     struct PdlScope {
@@ -875,7 +805,8 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
       explicit PdlScope(bool on) : prev(t_pdl) { t_pdl = on; }
       ~PdlScope() { t_pdl = prev; }
     } pdl_scope(s->pdl && !(s->eval_seq == 0 && tiles_t > 1));  // a launch right after the memset node is a plain dependency
-    CUDA_TRY(launch_k(ds_stack_kernel, dim3(kStackKB * B * tiles_t), dim3(kGemmThreads), kStackSmemBytes, st, sp));
+    if (dbg_build) CUDA_TRY(launch_k(ds_stack_kernel<true>, dim3(kStackKB * B * tiles_t), dim3(kGemmThreads), kStackSmemBytes, st, sp));
+    else CUDA_TRY(launch_k(ds_stack_kernel<false>, dim3(kStackKB * B * tiles_t), dim3(kGemmThreads), kStackSmemBytes, st, sp));
     ++s->eval_seq;
     ++*launches;
     return 0;

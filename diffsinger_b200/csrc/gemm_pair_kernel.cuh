@@ -6,7 +6,7 @@
 // single-CTA kernel cannot pass ~2/3 of the tensor peak (measured 1.1 PFLOP/s, profiles/r01_launches_lynxnet.txt).  A pair
 // owns a 256-frame x 256-column tile: each CTA stages its own 128 frames of A and HALF of the weight rows (128), the leader's
 // M = 256 UMMA reads both halves, and the per-CTA traffic drops to 64 + 64 B/clk (the fused layer kernel's arrangement,
-// layer4_kernel.cuh, which reaches 88 % tensor-pipe activity with it).
+// layer_kernel.cuh, which reaches 88 % tensor-pipe activity with it).
 //
 // One pipeline stage = TWO 64-wide K blocks (8 UMMAs) under one full / empty barrier pair, three stages of 64 KB.
 // Accumulators: 2 x 256 fp32 TMEM columns per CTA (its own 128 frames x 256 columns), drained by the unchanged
@@ -14,7 +14,7 @@
 // the per-lane STG.128 epilogue alone took 64 of the 241 us of the LYNXNet C -> 2I product, tools/gemm_bench.py).  p.tmBh is the weight map with a 128-row box; p.tiles_t counts 256-frame tiles.
 #pragma once
 #include "gemm_epilogue.cuh"
-#include "layer2_kernel.cuh"  // kPairBBytes
+#include "layer_kernel.cuh"  // kPairBBytes
 
 namespace dsb {
 

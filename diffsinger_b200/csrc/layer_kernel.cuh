@@ -1,17 +1,24 @@
-// One WaveNet residual layer as ONE persistent tcgen05 kernel (reference: ResidualBlock.forward,
-// modules/backbones/wavenet.py:33-48), for C a multiple of 128.
+// One WaveNet residual layer as ONE persistent tcgen05 kernel on CTA pairs (reference: ResidualBlock.forward,
+// modules/backbones/wavenet.py:33-48; dilated_conv = Conv1d(C, 2C, 3, padding=dilation, dilation=dilation), wavenet.py:22-28).
 //
-// Per 128-frame tile a CTA runs two back-to-back GEMMs without leaving the SM:
-//   GEMM-1  Y[128 x 2C] = [x~(t-d) | x~(t) | x~(t+d) | cond] (K = 3C+H)  x  W1^T      (C/128 passes "P" of N = 256:
-//           128 gate + 128 filter columns of the same channels, TMEM double buffered)
-//           epilogue: z = sigmoid(gate) * tanh(filter) -> bf16 -> gated-activation store in HBM (also the operand
-//           of the deferred skip GEMM), and in the kZSmem variant a K-major SWIZZLE_128B copy in shared memory
-//   GEMM-2  R[128 x C] = z (K = C)  x  W2^T   (residual half of output_projection; C/BN2 chunks "C")
-//           epilogue: x~_next = (x~ + R)/sqrt(2) + [(b - d_l)/sqrt(2) + d_{l+1}]  -> bf16 -> HBM (ping-pong buffer)
-// TMA feeds both GEMMs through one mbarrier ring.  All three roles walk the same static job list; in the default
-// (kZSmem = false) variant the chunks of tile k are interleaved with the passes of tile k+1
-//        P0(k+1) C0(k) P1(k+1) C1(k) P2(k+1) P3(k+1) ...
-// so the z round trip (epilogue -> L2 -> TMA) and the long residual epilogues hide behind GEMM-1 work.
+// Two CTAs of a cluster -- the two SMs of a TPC -- work on 256 consecutive frames (128 each) and run two back-to-back GEMMs per tile
+// without leaving the SM:
+//   GEMM-1  Y[256 x 2C] = [x~(t-d) | x~(t) | x~(t+d) | cond] (K = 3C+H)  x  W1^T   in 2C/256 passes of N = 256 (128 gate + 128 filter
+//           columns of the same channels); epilogue z = sigmoid(gate) * tanh(filter) -> bf16 -> the gated-activation store
+//   GEMM-2  R[256 x C] = z (K = C) x W2^T (residual half of output_projection); epilogue x~' = (x~ + R)/sqrt(2) + rvec
+// Every UMMA is cta_group::2, M = 256 x N = 256: each CTA supplies its own 128 activation rows and HALF of the 256 weight rows, so
+// the weight bytes per SM are halved; only the leader issues MMAs, its commits are multicast to both CTAs.
+//   * halo tiles: the conv's activation stage is ONE TMA box of (128 + 2*dil) frames x 64 channels; the three taps are three UMMA
+//     descriptors into the same tile shifted by dil rows (K-major SWIZZLE_128B, 128-byte row pitch: a row shift is +dil*128 B on
+//     the descriptor start address)
+//   * grouped pipeline stages: one full/empty mbarrier pair guards a whole group of K blocks -- a conv stage = one halo tile + the
+//     three tap weight blocks (12 UMMAs per hand-shake), a 1x1 stage = two activation + two weight blocks (8 UMMAs) -- because the
+//     hand-shake itself (mbarrier operations cost their thread ~285 cycles each) is as expensive as four UMMAs
+//   * TMEM: 2 x 256 fp32 columns, double buffered; GEMM-2 chunks of tile k are interleaved with GEMM-1 passes of tile k+1 (LayerJobs)
+//   * epilogue warps stage 32 x 32 bf16 sub-tiles in shared memory and write them with TMA stores (warp_store_tile, ptx.cuh)
+// Requires C % 256 == 0, H % 128 == 0 and 2^(cycle-1) <= 16; other shapes run the two-GEMM path (gemm_kernel.cuh).
+// (Round 1 also carried four earlier generations of this kernel -- single CTA with z in shared memory / through L2, CTA pairs
+// without halo tiles, CTA pairs with per-K-block stages; they were removed in round 2, their measurements stay in profiles/r01_*.)
 #pragma once
 #include <cuda.h>
 #include "gemm_epilogue.cuh"
@@ -37,11 +44,11 @@ struct LayerParams {
   unsigned long long* trace;  // optional: CTA 0 records {role*16 + kind, local tile*16 + idx, t0, t1} (debug)
   int trace_cap;
   int dbg;  // debug: bit0 = epilogue warps skip all work, bit1 = producer skips the TMA loads (barriers only)
-  // halo variant (layer3_kernel.cuh): x_in map with a (64 x (128 + 2*dil) x 1) box, A ring geometry
+  // x_in map with a (64 x (128 + 2*dil) x 1) box: one halo-carrying activation tile feeds the three conv taps
   CUtensorMap tmXh;
   uint32_t a_slot;
   int n_a;
-  // grouped-stage variant (layer4_kernel.cuh): TMA STORE maps (box 32 channels x 32 frames, SWIZZLE_64B) of the
+  // TMA STORE maps (box 32 channels x 32 frames, SWIZZLE_64B) of the
   // gated-activation store and of x_out -- the epilogue warps stage their 32 x 32 sub-tiles in shared memory
   CUtensorMap tmZs, tmXs;
   const uint16_t* bias1h;  // [2C] f16 copy of bias1 in the same packed order, gate entries pre-multiplied by 0.5
@@ -52,12 +59,7 @@ struct LayerParams {
 };
 
 constexpr uint32_t kLayerABytes = 128 * 128;  // 128 frames x 64 bf16
-constexpr uint32_t kLayerBBytes = 256 * 128;  // up to 256 weight rows x 64 bf16
-constexpr int kLayerMaxStages = 4;
-
-__host__ __device__ inline uint32_t layer_smem_bytes(int kb_c, int stages, bool z_smem) {
-  return 1024u + (z_smem ? kb_c : 0) * kLayerABytes + stages * (kLayerABytes + kLayerBBytes) + 256u;
-}
+constexpr uint32_t kPairBBytes = 128 * 128;   // this CTA's half of a 256-row weight tile: 128 rows x 64 bf16
 
 __device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
@@ -100,281 +102,339 @@ struct LayerJobs {
   }
 };
 
-// kZSmem = true : z stays in shared memory between the two GEMMs (needs C*256 B of smem -> few TMA stages at C=512;
-//                 jobs run tile by tile)
-// kZSmem = false: GEMM-2 re-reads the CTA's own z tile from the gated-activation store through TMA (L2 hit), which
-//                 frees the shared memory for a 4-deep operand ring and allows the interleaved job order.
-template <int BN2, bool kZSmem>
-__global__ void __launch_bounds__(kGemmThreads, 1) ds_layer_kernel(const __grid_constant__ LayerParams p) {
+__host__ __device__ inline uint32_t halo_a_slot_bytes(int max_dil) {
+  const uint32_t b = (128u + 2u * max_dil) * 128u;
+  return (b + 1023u) / 1024u * 1024u;
+}
+
+// K-major SWIZZLE_128B descriptor whose first row is `row` rows into a 1024-byte-aligned tile.  The tensor core applies
+// the swizzle XOR to absolute shared-memory address bits (as TMA did when it wrote the tile), so a row shift is just a
+// start-address offset; the descriptor's base-offset field must stay 0 (setting it to the row phase was measured WRONG).
+__device__ __forceinline__ uint64_t make_kmajor_sw128_desc_row(uint32_t tile_addr, uint32_t row) {
+  return make_kmajor_sw128_desc(tile_addr + row * 128u);
+}
+
+constexpr int kGrpMaxStages = 3;
+constexpr uint32_t kGrpSmemMax = 232448;
+
+__host__ __device__ inline uint32_t grp_stage_bytes(int max_dil) { return halo_a_slot_bytes(max_dil) + 3u * kPairBBytes; }
+__host__ __device__ inline int grp_stages(int max_dil) {
+  const int n = static_cast<int>((kGrpSmemMax - 1024u - 2048u - 8u * 2048u) / grp_stage_bytes(max_dil));
+  return n > kGrpMaxStages ? kGrpMaxStages : n;
+}
+__host__ __device__ inline uint32_t grp_smem_bytes(int max_dil) {
+  return 1024u + grp_stages(max_dil) * grp_stage_bytes(max_dil) + 2048u + 8u * 2048u;
+}
+
+constexpr uint32_t kGrpWarpStage = 2048;  // per epilogue warp: 32 frames x 32 channels bf16, SWIZZLE_64B
+
+// Gate epilogue in packed half precision: z = sigmoid(g + bg) * tanh(f + bf) with sigmoid(x) = 0.5 * tanh(0.5 x) + 0.5.
+// The fp32 accumulators are rounded to f16 (11-bit mantissa; pre-activations are O(1..10)), everything after that runs two
+// channels per instruction (HFMA2 / MUFU.TANH.F16x2), and z is rounded to bf16 as before -- 11 instructions per channel
+// pair instead of 15, half the MUFU work.  bias1h holds 0.5 * bg (gate) and bf (filter) as f16.
+// `add` = the f16 row added to the pre-activations: the broadcast bias (bias1h) or, with the conditioner projection hoisted,
+// this lane's row of cproj; (bg0, bf0) = its first chunk, loaded by the caller before it waits for the accumulator.
+__device__ __forceinline__ void grp_load_add(const uint16_t* add, int c, uint4 (&bg)[4], uint4 (&bf)[4]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    bg[i] = __ldg(reinterpret_cast<const uint4*>(add + c * 32) + i);
+    bf[i] = __ldg(reinterpret_cast<const uint4*>(add + 128 + c * 32) + i);
+  }
+}
+__device__ __forceinline__ void grp_epilogue_gate(const LayerParams& p, uint32_t taddr, int idx, int b, int tw0, const uint16_t* add,
+                                                  const uint4 (&bg0)[4], const uint4 (&bf0)[4], int half, int lane, uint32_t sw) {
+  constexpr uint32_t kHalf2 = 0x38003800u;  // (0.5h, 0.5h)
+  uint4 bg1[4], bf1[4];
+  grp_load_add(add, half + 2, bg1, bf1);  // second chunk's rows: issued first so that an HBM miss hides behind chunk one
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const int c = half + 2 * k;
+    uint32_t g[32], f[32];
+    tmem_ld_32x32(taddr + c * 32, g);
+    tmem_ld_32x32(taddr + 128 + c * 32, f);
+    uint4 bg[4], bf[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      bg[i] = k == 0 ? bg0[i] : bg1[i];
+      bf[i] = k == 0 ? bf0[i] : bf1[i];
+    }
+    tmem_ld_wait();
+    uint32_t zp[16];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint32_t bgw[4] = {bg[i].x, bg[i].y, bg[i].z, bg[i].w};
+      const uint32_t bfw[4] = {bf[i].x, bf[i].y, bf[i].z, bf[i].w};
+#pragma unroll
+      for (int h = 0; h < 4; ++h) {
+        const int q = 4 * i + h;
+        const uint32_t gq = fma_f16x2(pack_f16(__uint_as_float(g[2 * q]), __uint_as_float(g[2 * q + 1])), kHalf2, bgw[h]);
+        const uint32_t fq = add_f16x2(pack_f16(__uint_as_float(f[2 * q]), __uint_as_float(f[2 * q + 1])), bfw[h]);
+        const uint32_t sg = fma_f16x2(tanh_f16x2(gq), kHalf2, kHalf2);
+        zp[q] = f16x2_to_bf16x2(mul_f16x2(sg, tanh_f16x2(fq)));
+      }
+    }
+    warp_store_tile(&p.tmZs, sw, lane, zp, p.z_c0 + idx * 128 + c * 32, tw0, b, tw0 < p.T);
+  }
+}
+
+// Residual epilogue.  `x0` = this lane's first 32-channel chunk of x~ (prefetched by the caller BEFORE it waits for the
+// accumulator: x~ does not depend on the MMAs).  The chunk loop is fully unrolled so that the one-chunk-ahead prefetch of
+// x~ lives in renamed registers (a rolled loop ends in register moves that wait for the prefetch at the END of each
+// iteration -- the top epilogue stall in the ncu source view).
+__device__ __forceinline__ void grp_epilogue_res(const LayerParams& p, uint32_t taddr, int idx, int b, int tw0, const __nv_bfloat16* xin,
+                                                 const uint4 (&x0)[4], int half, int lane, uint32_t sw) {
+  const int n0 = idx * 256;
+  const float* rv = p.rvec + static_cast<size_t>(b) * p.vec_bstride + n0;
+  uint4 xq[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) xq[i] = x0[i];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int c = half + 2 * k;
+    uint32_t a[32];
+    tmem_ld_32x32(taddr + c * 32, a);
+    float rr[32];
+    ld_f32x32(rv + c * 32, rr);
+    uint4 xn[4];
+    if (k < 3) ld_x4(xin + (c + 2) * 32, xn);
+    tmem_ld_wait();
+    uint32_t o[16];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint32_t w[4] = {xq[i].x, xq[i].y, xq[i].z, xq[i].w};
+#pragma unroll
+      for (int h = 0; h < 4; ++h) {
+        const int q = 8 * i + 2 * h;
+        const float v0 = fmaf(__uint_as_float(a[q]) + __uint_as_float(w[h] << 16), 0.70710678118654752f, rr[q]);
+        const float v1 = fmaf(__uint_as_float(a[q + 1]) + __uint_as_float(w[h] & 0xffff0000u), 0.70710678118654752f, rr[q + 1]);
+        o[4 * i + h] = pack_bf16(v0, v1);
+      }
+    }
+    warp_store_tile(&p.tmXs, sw, lane, o, n0 + c * 32, tw0, b, tw0 < p.T);
+    if (k < 3) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) xq[i] = xn[i];
+    }
+  }
+}
+
+// Requires C % 256 == 0, H % 128 == 0 (two-block 1x1 stages) and 2^(cycle-1) <= 16.  LayerParams as for the halo kernel;
+// a_slot = halo_a_slot_bytes(max_dil), n_a = grp_stages(max_dil).
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
-  const int S = p.stages;
-  uint8_t* smem_z = smem;  // kZSmem: kb_c blocks of [128 x 64] bf16, SW128 K-major
-  uint8_t* smem_a = smem_z + (kZSmem ? p.kb_c : 0) * kLayerABytes;
-  uint8_t* smem_b = smem_a + S * kLayerABytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_b + S * kLayerBBytes);
-  uint64_t* full = bars;
-  uint64_t* empty = bars + kLayerMaxStages;
-  uint64_t* tmem_full = bars + 2 * kLayerMaxStages;
-  uint64_t* tmem_empty = tmem_full + 2;
-  uint64_t* z_full = tmem_empty + 2;
+  const int NS = p.n_a;
+  const uint32_t stage_bytes = p.a_slot + 3u * kPairBBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NS * stage_bytes);
+  uint64_t* full = bars;                      // leader: 2 producer arrivals + the bytes of both CTAs
+  uint64_t* empty = full + kGrpMaxStages;     // per CTA: released by the leader's multicast commit
+  uint64_t* tmem_full = empty + kGrpMaxStages;
+  uint64_t* tmem_empty = tmem_full + 2;       // leader: 16 warp arrivals (8 per CTA)
+  uint64_t* z_full = tmem_empty + 2;          // per CTA
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(z_full + 1);
+  uint8_t* warp_stage = reinterpret_cast<uint8_t*>(bars) + 2048;  // 8 x kGrpWarpStage, 2 KB aligned (stage_bytes % 2048 == 0)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
 
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&p.tmX);
+    tma_prefetch_desc(&p.tmXh);
     tma_prefetch_desc(&p.tmCond);
     tma_prefetch_desc(&p.tmW1);
     tma_prefetch_desc(&p.tmW2);
-    if (!kZSmem) tma_prefetch_desc(&p.tmZ);
+    tma_prefetch_desc(&p.tmZ);
   }
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < S; ++i) {
-      mbar_init(&full[i], 1);
+    for (int i = 0; i < NS; ++i) {
+      mbar_init(&full[i], 2);
       mbar_init(&empty[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full[i], 1);
-      mbar_init(&tmem_empty[i], kEpiThreads);
+      mbar_init(&tmem_empty[i], 16);
     }
     mbar_init(z_full, kEpiThreads);
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc<512>(tmem_slot);
+  cluster_sync_all();  // peer barriers are initialised before any remote arrive / multicast commit
+  if (warp == 2) tmem_alloc_pair<512>(tmem_slot);
   tc_fence_before();
-  __syncthreads();
+  cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int kb_taps = 3 * p.kb_c;
-  const int kb1 = kb_taps + p.kb_h;
-  const int n_local = (p.total_tiles > static_cast<int>(blockIdx.x))
-                          ? (p.total_tiles - 1 - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x) + 1 : 0;
-  const bool tracing = p.trace != nullptr && blockIdx.x == 0 && p.p2 > 0;
-  // De-synchronise the CTAs: each walks the K blocks (and the passes) in its own rotated order, so that at any instant
-  // the chip reads many different weight blocks instead of all SMs hitting the same few L2 slices.
-  const int prot = (p.dbg & 8) ? 0 : static_cast<int>(blockIdx.x) % p.p1;
-  const int krot1 = (p.dbg & 4) ? 0 : (static_cast<int>(blockIdx.x) / p.p1 * 5) % kb1;
-  const int krot2 = (p.dbg & 4) ? 0 : static_cast<int>(blockIdx.x) % p.kb_c;
+  const int pair_id = blockIdx.x >> 1;
+  const int n_pairs = gridDim.x >> 1;
+  const int n_local = (p.total_tiles > pair_id) ? (p.total_tiles - 1 - pair_id) / n_pairs + 1 : 0;
+  const uint32_t halo_bytes = (128u + 2u * p.dil) * 128u;
+  // stage layout: conv  [halo A tile (a_slot)] [B tap0] [B tap1] [B tap2]
+  //               1x1   [A blk0 16K] [A blk1 16K] [B blk0 16K] [B blk1 16K]      (fits: a_slot + 48K >= 64K)
+  constexpr uint32_t kOne = kLayerABytes;  // 16 KB
 
   if (warp == 0) {
     if (lane == 0) {
-      // ------------------------------------------------------------ TMA producer
-      int stage = 0;
-      uint32_t phase = 0;
-      LayerJobs jobs(n_local, p.p1, p.p2, !kZSmem);
+      // ------------------------------------------------------------ TMA producer (both CTAs)
+      int st = 0;
+      uint32_t ph = 0;
+      auto begin_stage = [&](uint32_t bytes_per_cta) -> uint8_t* {
+        mbar_wait(&empty[st], ph ^ 1);
+        if (leader) {
+          if (p.dbg & 2) mbar_arrive(&full[st]);  // debug: barriers only, no bytes
+          else mbar_arrive_expect_tx(&full[st], 2 * bytes_per_cta);
+        } else {
+          mbar_arrive_cluster(&full[st], 0);
+        }
+        return smem + st * stage_bytes;
+      };
+      auto end_stage = [&]() { if (++st == NS) { st = 0; ph ^= 1; } };
+      // 1x1 stages: blocks [k, k + n) of activation map `am` (channel offset ac0) against weight columns wk0 + ...
+      auto one_by_one = [&](const CUtensorMap* am, int ac0, const CUtensorMap* wm, int wk0, int nblk, int row0, int t0, int b) {
+        for (int k = 0; k < nblk; k += 2) {
+          const int n = nblk - k < 2 ? nblk - k : 2;
+          uint8_t* s = begin_stage(n * (kOne + kPairBBytes));
+          for (int j = 0; j < n && !(p.dbg & 2); ++j) {
+            tma_load_3d_pair(am, &full[st], s + j * kOne, ac0 + (k + j) * 64, t0, b);
+            tma_load_2d_pair(wm, &full[st], s + 2 * kOne + j * kPairBBytes, wk0 + (k + j) * 64, row0);
+          }
+          end_stage();
+        }
+      };
+      LayerJobs jobs(n_local, p.p1, p.p2, true);
       int kind, j, idx;
       while (jobs.next(kind, j, idx)) {
-        const int tile = blockIdx.x + j * gridDim.x;
-        const int t0 = (tile % p.tiles_t) * 128;
+        const int tile = pair_id + j * n_pairs;
+        const int t0 = (tile % p.tiles_t) * 256 + rank * 128;
         const int b = tile / p.tiles_t;
         if (kind == 0) {
-          const int row0 = p.w1_row0 + ((idx + prot) % p.p1) * 256;
-          for (int ki = 0; ki < kb1; ++ki) {
-            int kb = ki + krot1;
-            if (kb >= kb1) kb -= kb1;
-            mbar_wait(&empty[stage], phase ^ 1);
-            if (p.dbg & 2) { mbar_arrive(&full[stage]); if (++stage == S) { stage = 0; phase ^= 1; } continue; }
-            mbar_arrive_expect_tx(&full[stage], kLayerABytes + kLayerBBytes);
-            uint8_t* sa = smem_a + stage * kLayerABytes;
-            if (kb < kb_taps) {
-              const int tap = kb / p.kb_c;
-              const int cb = kb - tap * p.kb_c;
-              tma_load_3d(&p.tmX, &full[stage], sa, cb * 64, t0 + (tap - 1) * p.dil, b);
-            } else {
-              tma_load_3d(&p.tmCond, &full[stage], sa, (kb - kb_taps) * 64, t0, b);
-            }
-            tma_load_2d(&p.tmW1, &full[stage], smem_b + stage * kLayerBBytes, kb * 64, row0);
-            if (++stage == S) { stage = 0; phase ^= 1; }
+          const int row0 = p.w1_row0 + idx * 256 + rank * 128;
+          for (int cb = 0; cb < p.kb_c; ++cb) {
+            uint8_t* s = begin_stage(halo_bytes + 3 * kPairBBytes);
+            if (!(p.dbg & 2)) tma_load_3d_pair(&p.tmXh, &full[st], s, cb * 64, t0 - p.dil, b);
+#pragma unroll
+            for (int tap = 0; tap < 3 && !(p.dbg & 2); ++tap)
+              tma_load_2d_pair(&p.tmW1, &full[st], s + p.a_slot + tap * kPairBBytes, (tap * p.kb_c + cb) * 64, row0);
+            end_stage();
           }
+          one_by_one(&p.tmCond, 0, &p.tmW1, 3 * p.kb_c * 64, p.kb_h, row0, t0, b);
         } else {
-          if (!kZSmem && idx == 0) mbar_wait(z_full, j & 1);  // tile j's z has been published to global memory
-          const int row0 = p.w2_row0 + idx * BN2;
-          for (int ki = 0; ki < p.kb_c; ++ki) {
-            int kb = ki + krot2;
-            if (kb >= p.kb_c) kb -= p.kb_c;
-            mbar_wait(&empty[stage], phase ^ 1);
-            if (p.dbg & 2) { mbar_arrive(&full[stage]); if (++stage == S) { stage = 0; phase ^= 1; } continue; }
-            mbar_arrive_expect_tx(&full[stage], BN2 * 128 + (kZSmem ? 0u : kLayerABytes));
-            if (!kZSmem) tma_load_3d(&p.tmZ, &full[stage], smem_a + stage * kLayerABytes, p.z_c0 + kb * 64, t0, b);
-            tma_load_2d(&p.tmW2, &full[stage], smem_b + stage * kLayerBBytes, kb * 64, row0);
-            if (++stage == S) { stage = 0; phase ^= 1; }
-          }
+          if (idx == 0) mbar_wait(z_full, j & 1);  // this CTA's z rows of tile j are in global memory
+          const int row0 = p.w2_row0 + idx * 256 + rank * 128;
+          one_by_one(&p.tmZ, p.z_c0, &p.tmW2, 0, p.kb_c, row0, t0, b);
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      // ------------------------------------------------------------ MMA issuer
-      constexpr uint32_t idesc1 = make_idesc_bf16_f32(256);
-      constexpr uint32_t idesc2 = make_idesc_bf16_f32(BN2);
-      int stage = 0;
-      uint32_t phase = 0;
+    if (lane == 0 && leader) {
+      // ------------------------------------------------------------ MMA issuer (leader CTA only)
+      constexpr uint32_t idesc = make_idesc_bf16_f32_m(256, 256);
+      int st = 0;
+      uint32_t ph = 0;
       uint32_t acc_it = 0;
-      int ntrace = 0;
-      LayerJobs jobs(n_local, p.p1, p.p2, !kZSmem);
+      auto mma4 = [&](uint32_t tmem_d, uint64_t da, uint64_t db, bool fresh) {
+        if (p.dbg & 4) return;  // debug: commits only
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_bf16_pair(tmem_d, da + 2 * k, db + 2 * k, idesc, (!fresh) || k != 0);
+      };
+      auto release = [&](bool last_of_job, uint32_t as) {
+        umma_commit_pair(&empty[st]);
+        if (last_of_job) umma_commit_pair(&tmem_full[as]);
+        if (++st == NS) { st = 0; ph ^= 1; }
+      };
+      auto one_by_one = [&](uint32_t tmem_d, int nblk, bool fresh_first, uint32_t as) {
+        for (int k = 0; k < nblk; k += 2) {
+          const int n = nblk - k < 2 ? nblk - k : 2;
+          mbar_wait(&full[st], ph);
+          tc_fence_after();
+          const uint32_t s = smem_u32(smem + st * stage_bytes);
+          for (int jj = 0; jj < n; ++jj)
+            mma4(tmem_d, make_kmajor_sw128_desc(s + jj * kOne), make_kmajor_sw128_desc(s + 2 * kOne + jj * kPairBBytes),
+                 fresh_first && k == 0 && jj == 0);
+          release(k + n >= nblk, as);
+        }
+      };
+      LayerJobs jobs(n_local, p.p1, p.p2, true);
       int kind, j, idx;
       while (jobs.next(kind, j, idx)) {
         const uint32_t as = acc_it & 1;
-        const unsigned long long ts0 = tracing ? globaltimer_ns() : 0ull;
-        if (kZSmem && kind == 1 && idx == 0) {
-          mbar_wait(z_full, j & 1);  // all epilogue threads have published tile j's z to shared memory
-          tc_fence_after();
-        }
         mbar_wait(&tmem_empty[as], ((acc_it >> 1) & 1) ^ 1);
         tc_fence_after();
-        const unsigned long long ts1 = tracing ? globaltimer_ns() : 0ull;
         const uint32_t tmem_d = tmem_base + as * 256;
-        const int nkb = kind == 0 ? kb1 : p.kb_c;
-        for (int kb = 0; kb < nkb; ++kb) {
-          mbar_wait(&full[stage], phase);
-          tc_fence_after();
-          const uint8_t* a_src = (kZSmem && kind == 1) ? smem_z + ((kb + krot2) % p.kb_c) * kLayerABytes : smem_a + stage * kLayerABytes;
-          const uint64_t da = make_kmajor_sw128_desc(smem_u32(a_src));
-          const uint64_t db = make_kmajor_sw128_desc(smem_u32(smem_b + stage * kLayerBBytes));
-          if (kind == 0) {
+        if (kind == 0) {
+          for (int cb = 0; cb < p.kb_c; ++cb) {
+            mbar_wait(&full[st], ph);
+            tc_fence_after();
+            const uint32_t s = smem_u32(smem + st * stage_bytes);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc1, (kb | k) != 0);
-          } else {
-#pragma unroll
-            for (int k = 0; k < 4; ++k) umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc2, (kb | k) != 0);
+            for (int tap = 0; tap < 3; ++tap)
+              mma4(tmem_d, make_kmajor_sw128_desc_row(s, tap * p.dil), make_kmajor_sw128_desc(s + p.a_slot + tap * kPairBBytes),
+                   cb == 0 && tap == 0);
+            release(p.kb_h == 0 && cb == p.kb_c - 1, as);
           }
-          umma_commit(&empty[stage]);
-          if (kb == nkb - 1) umma_commit(&tmem_full[as]);
-          if (++stage == S) { stage = 0; phase ^= 1; }
-        }
-        if (tracing && ntrace < p.trace_cap / 2) {
-          unsigned long long* e = p.trace + 4 * ntrace++;
-          e[0] = 16 + kind; e[1] = j * 16 + idx; e[2] = ts0; e[3] = ts1;
+          one_by_one(tmem_d, p.kb_h, false, as);
+        } else {
+          one_by_one(tmem_d, p.kb_c, true, as);
         }
         ++acc_it;
       }
     }
   } else if (warp >= 4) {
-    // -------------------------------------------------------------- epilogue (256 threads, thread <-> frame;
-    // the two warps of a lane quadrant interleave 32-column chunks)
+    // -------------------------------------------------------------- epilogue (both CTAs; 256 threads each)
     const int quad = warp & 3;
     const int half = (warp - 4) >> 2;
-    const int r = quad * 32 + lane;  // row inside the tile == TMEM lane
+    const int rr = quad * 32 + lane;
     const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
     uint32_t acc_it = 0;
-    int ntrace = 0;
-    LayerJobs jobs(n_local, p.p1, p.p2, !kZSmem);
+    LayerJobs jobs(n_local, p.p1, p.p2, true);
     int kind, j, idx;
     while (jobs.next(kind, j, idx)) {
-      const int tile = blockIdx.x + j * gridDim.x;
+      const int tile = pair_id + j * n_pairs;
       const int b = tile / p.tiles_t;
-      const int t = (tile % p.tiles_t) * 128 + r;
+      const int t = (tile % p.tiles_t) * 256 + rank * 128 + rr;
       const bool valid = t < p.T;
       const size_t row = static_cast<size_t>(b) * p.T + (valid ? t : 0);
       const uint32_t as = acc_it & 1;
+      const __nv_bfloat16* xin = p.x_in + row * (p.kb_c * 64) + idx * 256;
+      uint4 x0[4], bg0[4], bf0[4];
+      const uint16_t* add = p.cproj ? p.cproj + row * p.ld_cproj + idx * 256 : p.bias1h + idx * 256;
+      if (!(p.dbg & 1)) {  // in flight while the job's MMAs finish
+        if (kind == 1) ld_x4(xin + half * 32, x0);
+        else grp_load_add(add, half, bg0, bf0);
+      }
       mbar_wait(&tmem_full[as], (acc_it >> 1) & 1);
       tc_fence_after();
-      const unsigned long long ts0 = (tracing && threadIdx.x == 128) ? globaltimer_ns() : 0ull;
       const uint32_t taddr = lane_addr + as * 256;
-      if (p.dbg & 1) {
-        tc_fence_before();
-        mbar_arrive(&tmem_empty[as]);
-        if (kind == 0 && idx == p.p1 - 1 && p.p2 > 0) mbar_arrive(z_full);
+      const int tw0 = (tile % p.tiles_t) * 256 + rank * 128 + quad * 32;  // first frame of this warp's 32 rows
+      const uint32_t sw = smem_u32(warp_stage + (warp - 4) * kGrpWarpStage);
+      if (p.dbg & 1) {  // debug: epilogue warps only hand the accumulator back
       } else if (kind == 0) {
-        const int pidx = (idx + prot) % p.p1;
-        const float* bias = p.bias1 + pidx * 256;
-        __nv_bfloat16* zg = p.z_out + row * p.ld_z + p.z_c0 + pidx * 128;
-#pragma unroll 1
-        for (int c = half; c < 4; c += 2) {
-          uint32_t g[32], f[32];
-          tmem_ld_32x32(taddr + c * 32, g);
-          tmem_ld_32x32(taddr + 128 + c * 32, f);
-          float bg[32], bf[32];
-          ld_f32x32(bias + c * 32, bg);
-          ld_f32x32(bias + 128 + c * 32, bf);
-          tmem_ld_wait();
-          uint32_t zp[16];
-#pragma unroll
-          for (int q = 0; q < 16; ++q) {
-            float z2[2];
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-              const float gj = __uint_as_float(g[2 * q + h]) + bg[2 * q + h];
-              const float fj = __uint_as_float(f[2 * q + h]) + bf[2 * q + h];
-              z2[h] = fmaf(0.5f, tanh_approx(0.5f * gj), 0.5f) * tanh_approx(fj);
-            }
-            zp[q] = pack_bf16(z2[0], z2[1]);
-          }
-          if (kZSmem && p.p2 > 0) {
-            // K-major SWIZZLE_128B: block = 64 channels, row pitch 128 B, 16-B piece q -> q ^ (row & 7)
-            uint8_t* blk = smem_z + (pidx * 2 + (c >> 1)) * kLayerABytes + r * 128;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const int q = (c & 1) * 4 + i;
-              *reinterpret_cast<uint4*>(blk + ((q ^ (r & 7)) << 4)) = make_uint4(zp[4 * i], zp[4 * i + 1], zp[4 * i + 2], zp[4 * i + 3]);
-            }
-          }
-          if (valid) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-              reinterpret_cast<uint4*>(zg + c * 32)[i] = make_uint4(zp[4 * i], zp[4 * i + 1], zp[4 * i + 2], zp[4 * i + 3]);
-          }
-        }
-        tc_fence_before();
-        mbar_arrive(&tmem_empty[as]);
-        if (idx == p.p1 - 1 && p.p2 > 0) {
-          if (kZSmem) {
-            fence_proxy_async_smem();  // generic-proxy z writes -> visible to the tensor core's async-proxy reads
-          } else {
-            __threadfence();             // z stores reach L2 ...
-            fence_proxy_async_global();  // ... and are ordered before the TMA (async proxy) re-read
-          }
-          mbar_arrive(z_full);
-        }
+        grp_epilogue_gate(p, taddr, idx, b, tw0, add, bg0, bf0, half, lane, sw);
       } else {
-        const int n0 = idx * BN2;
-        const float* rv = p.rvec + static_cast<size_t>(b) * p.vec_bstride + n0;
-        const __nv_bfloat16* xin = p.x_in + row * (p.kb_c * 64) + n0;
-        __nv_bfloat16* xout = p.x_out + row * (p.kb_c * 64) + n0;
-        uint4 xq[4];
-        ld_x4(xin + half * 32, xq);
-#pragma unroll 1
-        for (int c = half; c < BN2 / 32; c += 2) {
-          uint32_t a[32];
-          tmem_ld_32x32(taddr + c * 32, a);
-          float v[32], rr[32];
-          ld_f32x32(rv + c * 32, rr);
-          uint4 xn[4];
-          if (c + 2 < BN2 / 32) ld_x4(xin + (c + 2) * 32, xn);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const uint32_t w[4] = {xq[i].x, xq[i].y, xq[i].z, xq[i].w};
-#pragma unroll
-            for (int h = 0; h < 4; ++h) {
-              const int q = 8 * i + 2 * h;
-              v[q] = fmaf(__uint_as_float(a[q]) + __uint_as_float(w[h] << 16), 0.70710678118654752f, rr[q]);
-              v[q + 1] = fmaf(__uint_as_float(a[q + 1]) + __uint_as_float(w[h] & 0xffff0000u), 0.70710678118654752f, rr[q + 1]);
-            }
-          }
-          if (valid) st_bf16x32(xout + c * 32, v);
-#pragma unroll
-          for (int i = 0; i < 4; ++i) xq[i] = xn[i];
-        }
-        tc_fence_before();
-        mbar_arrive(&tmem_empty[as]);
+        grp_epilogue_res(p, taddr, idx, b, tw0, xin, x0, half, lane, sw);
       }
-      if (tracing && threadIdx.x == 128 && ntrace < p.trace_cap / 2) {
-        unsigned long long* e = p.trace + 4 * (p.trace_cap / 2 + ntrace++);
-        e[0] = kind; e[1] = j * 16 + idx; e[2] = ts0; e[3] = globaltimer_ns();
+      // release the accumulator on the LEADER's barrier: one arrival per warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (leader) mbar_arrive(&tmem_empty[as]);
+        else mbar_arrive_cluster(&tmem_empty[as], 0);
+      }
+      if (kind == 0 && idx == p.p1 - 1 && p.p2 > 0) {
+        bulk_wait_all();  // this warp's TMA stores of z are complete before the producer's TMA re-reads them
+        mbar_arrive(z_full);
       }
       ++acc_it;
     }
   }
+  if (warp >= 4) bulk_wait_all();  // staging tiles are read out before the CTA's shared memory goes away
   tc_fence_before();
-  __syncthreads();
+  cluster_sync_all();  // the leader's MMAs read this CTA's shared memory and write its TMEM until the very end
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc<512>(tmem_base);
+    tmem_dealloc_pair<512>(tmem_base);
   }
 }
 

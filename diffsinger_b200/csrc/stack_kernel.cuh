@@ -11,7 +11,7 @@
 //     slice (16 KB) to the other CTAs of the cluster with `cp.async.bulk.shared::cluster` (DSMEM) that completes on the
 //     RECEIVER's mbarrier -- an all-gather without any cluster-wide barrier; the consumer MMA starts on a k-block as soon
 //     as that block has landed (blocks are sent and consumed in the same rotated order).
-//   * the three conv taps are three UMMA descriptors into the same x~ tile shifted by dil rows (as in layer4_kernel.cuh);
+//   * the three conv taps are three UMMA descriptors into the same x~ tile shifted by dil rows (as in layer_kernel.cuh);
 //   * the skip sum is accumulated in TMEM across all L layers (64 fp32 columns per CTA) and never touches memory
 //     ("skip accumulation kept on-chip");
 //   * the step-invariant conditioner projection is hoisted: ds_session_set_cond computes cproj = W_cond*cond + b once per
@@ -21,12 +21,12 @@
 // through a small global (L2-resident) buffer guarded by per-tile arrival counters -- point-to-point, no grid-wide barrier.
 // All clusters of a launch must be co-resident (the host checks cudaOccupancyMaxActiveClusters).
 //
-// Warp roles (384 threads): warp0 = weight TMA producer, warp1 = MMA issuer, warp2 = TMEM allocator + halo receiver,
-// warp3 idle, warps 4..11 = epilogue (warp & 3 = TMEM lane quadrant, (warp - 4) >> 2 = which 32 of the CTA's 64 channels).
+// Warp roles (384 threads): warps 0 / 3 / 2 (lane 0) = weight TMA producers, warp1 = MMA issuer, warp2 = TMEM allocator +
+// halo receiver (lane 1), warps 4..11 = epilogue (warp & 3 = TMEM lane quadrant, (warp - 4) >> 2 = which 32 of the CTA's 64 channels).
 #pragma once
 #include <cuda.h>
 #include "gemm_kernel.cuh"
-#include "layer3_kernel.cuh"
+#include "layer_kernel.cuh"
 
 namespace dsb {
 
@@ -37,6 +37,7 @@ constexpr uint32_t kStackXTile = kStackXRows * 128u;   // 20480 B per k-block (1
 constexpr uint32_t kStackZTile = 128u * 128u;          // 16384 B per k-block
 constexpr uint32_t kStackStage = 16384u;               // weight ring stage: [128 rows][64 K] bf16
 constexpr int kStackStages = 5;
+constexpr int kStackProducers = 3;            // weight-issuing threads (warp 0, warp 3, warp 2)
 constexpr uint32_t kStackSmemBytes = 1024u + kStackKB * (kStackXTile + kStackZTile) + kStackStages * kStackStage + 1024u;
 constexpr uint32_t kStackEdgeBytes = kStackHalo * 128u;  // one k-block of one edge: 16 rows x 128 B
 
@@ -63,6 +64,9 @@ struct StackParams {
   int T, B, tiles_t, n_tiles;
   int L, cycle, C, FM, FMp, nout;
   float inv_sqrt_L;
+  int dbg;  // debug (DSB200_DBG, timing only -- results are wrong): bit 1 = no weight loads, bit 2 = no MMAs, bit 3 = no peer copies
+  unsigned long long* trace;  // debug (ds_debug_set_trace): CTA 0 records %globaltimer at 10 points per layer, [L][10] words
+  int trace_cap;
 };
 
 // ---------------------------------------------------------------- DSMEM / global bulk copies
@@ -106,9 +110,38 @@ __device__ __forceinline__ void stack_conv_step(int i, int r, int& kb, int& tap)
   else { const int k = i - kStackKB; kb = (r + (k >> 1)) % kStackKB; tap = (k & 1) * 2; }
 }
 
+// Lean wait for the single-thread roles: every instruction on those threads is serial latency (~6 cycles each, no other warp hides
+// it), so no spin counter; the bounded mbar_wait (traps instead of hanging) is used in the kDbg instantiation.
+__device__ __forceinline__ void mbar_wait_lean(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred P;\n\t"
+      "LAB_WAIT:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P, [%0], %1;\n\t"
+      "@P bra LAB_DONE;\n\t"
+      "bra LAB_WAIT;\n\t"
+      "LAB_DONE:\n\t}\n"
+      ::"r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+}
+
+// kDbg = true: role switches (StackParams::dbg), %globaltimer trace, bounded waits.  The production instantiation carries none of
+// it: the MMA issuer is ONE thread whose instruction count per weight stage is the kernel's critical path (tools/stack_trace.py:
+// ~285 cycles per mbarrier operation, ~55 per tcgen05.mma issue).
+template <bool kDbg>
 __global__ void __cluster_dims__(kStackKB, 1, 1) __launch_bounds__(kGemmThreads, 1)
 ds_stack_kernel(const __grid_constant__ StackParams p) {
   constexpr int KB = kStackKB;
+  const int dbg = kDbg ? p.dbg : 0;
+  auto bwait = [&](uint64_t* bar, uint32_t parity) {
+    if constexpr (kDbg) mbar_wait(bar, parity);
+    else mbar_wait_lean(bar, parity);
+  };
+  const bool tracing = kDbg && p.trace != nullptr && blockIdx.x == 0;
+  auto mark = [&](int l, int slot) {
+    if constexpr (kDbg) {
+      if (tracing && (l * 10 + slot) < p.trace_cap) p.trace[l * 10 + slot] = globaltimer_ns();
+    }
+  };
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
@@ -118,13 +151,16 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
   uint64_t* bars = reinterpret_cast<uint64_t*>(ring + kStackStages * kStackStage);
   uint64_t* w_full = bars;
   uint64_t* w_empty = w_full + kStackStages;
-  uint64_t* x_full = w_empty + kStackStages;  // per k-block of x~ (count 1 + 16 KB of peer bytes)
-  uint64_t* z_full = x_full + KB;             // per k-block of z
-  uint64_t* acc1_full = z_full + KB;
+  uint64_t* x_loc = w_empty + kStackStages;   // this CTA's own k-block of x~ is written (epilogue arrival)
+  uint64_t* x_rem = x_loc + 1;                // the KB-1 peer blocks have landed: 1 arrival (arming) + (KB-1) * 16 KB
+  uint64_t* z_loc = x_rem + 1;
+  uint64_t* z_rem = z_loc + 1;
+  uint64_t* acc1_full = z_rem + 1;
   uint64_t* acc2_full = acc1_full + 1;
   uint64_t* aux_full = acc2_full + 1;         // head input cast done
   uint64_t* halo_full = aux_full + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(halo_full + 1);
+  constexpr uint32_t kRemBytes = (KB - 1) * kStackZTile;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -151,21 +187,18 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
       mbar_init(&w_full[i], 1);
       mbar_init(&w_empty[i], 1);
     }
-    for (int i = 0; i < KB; ++i) {
-      mbar_init(&x_full[i], 1);
-      mbar_init(&z_full[i], 1);
-    }
+    mbar_init(x_loc, 1);
+    mbar_init(x_rem, 1);
+    mbar_init(z_loc, 1);
+    mbar_init(z_rem, 1);
     mbar_init(acc1_full, 1);
     mbar_init(acc2_full, 1);
     mbar_init(aux_full, 1);
     mbar_init(halo_full, 1);
     fence_barrier_init();
-    // phase 0 of every REMOTE block: this CTA's arrival + the 16 KB the owner will send
-    for (int i = 0; i < KB; ++i)
-      if (i != r) {
-        mbar_arrive_expect_tx(&x_full[i], kStackZTile);
-        mbar_arrive_expect_tx(&z_full[i], kStackZTile);
-      }
+    // phase 0 of the REMOTE blocks: this CTA's arrival + the 16 KB each of the KB-1 owners will send
+    if (dbg & 8) { mbar_arrive(x_rem); mbar_arrive(z_rem); }
+    else { mbar_arrive_expect_tx(x_rem, kRemBytes); mbar_arrive_expect_tx(z_rem, kRemBytes); }
   }
   // x~ starts as zeros: halo rows outside the utterance ARE the conv's zero padding and are never written
   for (uint32_t o = threadIdx.x * 16u; o < KB * kStackXTile; o += kGemmThreads * 16u) st_shared_v4(smem_u32(xs) + o, 0, 0, 0, 0);
@@ -177,112 +210,141 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t tm_acc1 = tmem_base, tm_acc2 = tmem_base + 128, tm_skip = tmem_base + 192;
 
-  if (warp == 0) {
-    if (lane == 0) {
-      // ------------------------------------------------------------ weight producer (never waits for data: weights are constant)
-      int st = 0;
-      uint32_t ph = 0;
-      auto begin = [&](uint32_t bytes) -> uint8_t* {
-        mbar_wait(&w_empty[st], ph ^ 1);
-        mbar_arrive_expect_tx(&w_full[st], bytes);
-        return ring + st * kStackStage;
-      };
-      auto end = [&]() { if (++st == kStackStages) { st = 0; ph ^= 1; } };
-      for (int k = 0; k < KBh; ++k) {
-        uint8_t* s = begin(64 * 128);
-        tma_load_2d(&p.tmWhead, &w_full[st], s, k * 64, 64 * r);
-        end();
+  // ------------------------------------------------------------ weight producers (never wait for data: weights are constant)
+  // A thread pays ~285 cycles for every mbarrier operation and bulk-copy issue (measured, tools/tma_bw_bench.cu: 16 KB stages from
+  // one issuing thread = 55 GB/s, from three threads in different warps = 165 GB/s), so the stage sequence is dealt round robin to
+  // kStackProducers threads; each walks the whole schedule and issues the stages whose sequence number is its own.
+  // Stage order of one layer (the MMA issuer consumes in the same order): the centre tap of k-blocks r, r+1, .. (no halo needed,
+  // blocks in arrival order), then taps 0 and 2 of the same k-blocks, then the 1x1 blocks.
+  auto produce = [&](int me) {
+    int q = 0;  // stage sequence number over the whole kernel; ring slot q % kStackStages, ring pass q / kStackStages
+    auto begin = [&](uint32_t bytes, uint64_t*& bar) -> uint8_t* {
+      const int st = q % kStackStages;
+      const bool mine = (q % kStackProducers) == me;
+      if (mine) {
+        bwait(&w_empty[st], ((q / kStackStages) & 1) ^ 1);
+        if (dbg & 2) mbar_arrive(&w_full[st]);  // debug: barriers only, no bytes
+        else mbar_arrive_expect_tx(&w_full[st], bytes);
       }
-      for (int l = 0; l < L; ++l) {
-        const int row1 = l * 2 * C + 128 * r;
-        for (int i = 0; i < 3 * KB; ++i) {
-          int kb, tap;
-          stack_conv_step(i, r, kb, tap);
-          uint8_t* s = begin(128 * 128);
-          tma_load_2d(&p.tmW1, &w_full[st], s, (tap * KB + kb) * 64, row1);
-          end();
-        }
-        for (int j = 0; j < KB; ++j) {
-          const int kb = (r + j) % KB;
-          const bool res = l + 1 < L;
-          uint8_t* s = begin((res ? 2u : 1u) * 64 * 128);
-          if (res) tma_load_2d(&p.tmW2, &w_full[st], s, kb * 64, l * C + 64 * r);
-          tma_load_2d(&p.tmWsk, &w_full[st], s + 8192, l * C + kb * 64, 64 * r);
-          end();
-        }
-      }
+      bar = &w_full[st];
+      ++q;
+      return (mine && !(dbg & 2)) ? ring + st * kStackStage : nullptr;
+    };
+    uint64_t* bar;
+    for (int k = 0; k < KBh; ++k)
+      if (uint8_t* s = begin(64 * 128, bar)) tma_load_2d(&p.tmWhead, bar, s, k * 64, 64 * r);
+    for (int l = 0; l < L; ++l) {
+      const int row1 = l * 2 * C + 128 * r;
+      for (int j = 0; j < KB; ++j)
+        if (uint8_t* s = begin(128 * 128, bar)) tma_load_2d(&p.tmW1, bar, s, (KB + ((r + j) & (KB - 1))) * 64, row1);
+      for (int j = 0; j < KB; ++j)
+        for (int tap = 0; tap < 3; tap += 2)
+          if (uint8_t* s = begin(128 * 128, bar)) tma_load_2d(&p.tmW1, bar, s, (tap * KB + ((r + j) & (KB - 1))) * 64, row1);
       for (int j = 0; j < KB; ++j) {
-        uint8_t* s = begin(64 * 128);
-        tma_load_2d(&p.tmWsp, &w_full[st], s, ((r + j) % KB) * 64, 64 * r);
-        end();
-      }
-      for (int j = 0; j < KB; ++j) {
-        uint8_t* s = begin(p.nout * 128);
-        tma_load_2d(&p.tmWout, &w_full[st], s, ((r + j) % KB) * 64, p.nout * r);
-        end();
+        const int kb = (r + j) & (KB - 1);
+        const bool res = l + 1 < L;
+        if (uint8_t* s = begin((res ? 2u : 1u) * 64 * 128, bar)) {
+          if (res) tma_load_2d(&p.tmW2, bar, s, kb * 64, l * C + 64 * r);
+          tma_load_2d(&p.tmWsk, bar, s + 8192, l * C + kb * 64, 64 * r);
+        }
       }
     }
+    for (int j = 0; j < KB; ++j)
+      if (uint8_t* s = begin(64 * 128, bar)) tma_load_2d(&p.tmWsp, bar, s, ((r + j) & (KB - 1)) * 64, 64 * r);
+    for (int j = 0; j < KB; ++j)
+      if (uint8_t* s = begin(p.nout * 128, bar)) tma_load_2d(&p.tmWout, bar, s, ((r + j) & (KB - 1)) * 64, p.nout * r);
+  };
+
+  if (warp == 0) {
+    if (lane == 0) produce(0);
+  } else if (warp == 3) {
+    if (lane == 0) produce(1);
   } else if (warp == 1) {
     if (lane == 0) {
       // ------------------------------------------------------------ MMA issuer
+      // ONE thread on purpose.  Two issuers on alternating stages were tried (results stayed correct, but no faster -- the weight
+      // ring's refill round trip, not the issuer, bounds a stage -- and the accumulation order, hence the low bits, varied from
+      // run to run).
       constexpr uint32_t id128 = make_idesc_bf16_f32(128), id64 = make_idesc_bf16_f32(64);
       const uint32_t idout = make_idesc_bf16_f32(static_cast<uint32_t>(p.nout));
       int st = 0;
       uint32_t ph = 0;
-      const uint32_t xs_a = smem_u32(xs), zs_a = smem_u32(zs);
-      auto w_wait = [&]() -> uint32_t {
-        mbar_wait(&w_full[st], ph);
-        tc_fence_after();
-        return smem_u32(ring + st * kStackStage);
+      // descriptors = a constant (swizzle mode, SBO, version) + (shared address >> 4): all addresses here are < 256 KB
+      const uint64_t d0 = make_kmajor_sw128_desc(0);
+      const uint64_t dx = d0 + (smem_u32(xs) >> 4), dz = d0 + (smem_u32(zs) >> 4), dw = d0 + (smem_u32(ring) >> 4);
+      constexpr uint32_t kXT = kStackXTile >> 4, kZT = kStackZTile >> 4, kST = kStackStage >> 4;
+      auto w_wait = [&]() -> uint64_t {  // no tcgen05.fence here: TMA wrote the bytes, the tensor core reads them (async proxy both)
+        bwait(&w_full[st], ph);
+        return dw + static_cast<uint32_t>(st) * kST;
       };
       auto w_release = [&]() {
         umma_commit(&w_empty[st]);
         if (++st == kStackStages) { st = 0; ph ^= 1; }
       };
       auto mma4 = [&](uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, bool fresh) {
+        if (dbg & 4) return;  // debug: commits only
 #pragma unroll
         for (int k = 0; k < 4; ++k) umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (!fresh) || k != 0);
       };
-      // waits for block kb of x~ / z at phase `phase`, then (remote blocks) arms the next phase
-      auto blk_wait = [&](uint64_t* barv, int kb, uint32_t phase, bool rearm) {
-        mbar_wait(&barv[kb], phase & 1);
-        if (kb != r && rearm) mbar_arrive_expect_tx(&barv[kb], kStackZTile);
-        tc_fence_after();
+      auto rearm = [&](uint64_t* bar) {
+        if (dbg & 8) mbar_arrive(bar);
+        else mbar_arrive_expect_tx(bar, kRemBytes);
       };
       // head: relu(input_projection(x)) -- A = the cast input in the z buffer                wavenet.py:86-88
-      mbar_wait(aux_full, 0);
+      bwait(aux_full, 0);
       tc_fence_after();
       for (int k = 0; k < KBh; ++k) {
-        const uint32_t s = w_wait();
-        mma4(tm_acc2, make_kmajor_sw128_desc(zs_a + k * kStackZTile), make_kmajor_sw128_desc(s), id64, k == 0);
+        const uint64_t db = w_wait();
+        mma4(tm_acc2, dz + k * kZT, db, id64, k == 0);
         w_release();
       }
       umma_commit(acc2_full);
       for (int l = 0; l < L; ++l) {
+        const uint32_t lp = l & 1;
         const int dil = 1 << (l % p.cycle);
         // GEMM-1: dilated conv, N = 64 gate + 64 filter columns of this CTA's channels         wavenet.py:36-38
-        for (int i = 0; i < 3 * KB; ++i) {
-          int kb, tap;
-          stack_conv_step(i, r, kb, tap);
-          if (i < KB) blk_wait(x_full, kb, l, true);
-          if (i == KB && has_nb) {
-            mbar_wait(halo_full, l & 1);
+        for (int j = 0; j < KB; ++j) {  // centre tap: row offset = the halo
+          if (j == 0) {
+            bwait(x_loc, lp);
             tc_fence_after();
+            mark(l, 0);
+          } else if (j == 1) {
+            bwait(x_rem, lp);
+            rearm(x_rem);  // phase l+1 (the last one, L, carries s1)
+            mark(l, 1);
           }
-          const uint32_t s = w_wait();
-          mma4(tm_acc1, make_kmajor_sw128_desc_row(xs_a + kb * kStackXTile, kStackHalo + (tap - 1) * dil), make_kmajor_sw128_desc(s),
-               id128, i == 0);
+          const uint64_t db = w_wait();
+          mma4(tm_acc1, dx + ((r + j) & (KB - 1)) * kXT + kStackHalo * 8, db, id128, j == 0);
           w_release();
+        }
+        if (has_nb) bwait(halo_full, lp);
+        for (int j = 0; j < KB; ++j) {
+          const uint64_t da = dx + ((r + j) & (KB - 1)) * kXT + kStackHalo * 8;
+#pragma unroll
+          for (int sgn = -1; sgn <= 1; sgn += 2) {
+            const uint64_t db = w_wait();
+            if (j == KB - 1 && sgn == 1) mark(l, 2);
+            mma4(tm_acc1, da + sgn * dil * 8, db, id128, false);
+            w_release();
+          }
         }
         umma_commit(acc1_full);
         // GEMM-2: residual half (fresh accumulator) and skip half (accumulates over all layers)  wavenet.py:44-48,96
         for (int j = 0; j < KB; ++j) {
-          const int kb = (r + j) % KB;
-          blk_wait(z_full, kb, l, true);
-          const uint32_t s = w_wait();
-          const uint64_t da = make_kmajor_sw128_desc(zs_a + kb * kStackZTile);
-          if (l + 1 < L) mma4(tm_acc2, da, make_kmajor_sw128_desc(s), id64, j == 0);
-          mma4(tm_skip, da, make_kmajor_sw128_desc(s + 8192), id64, l == 0 && j == 0);
+          if (j == 0) {
+            bwait(z_loc, lp);
+            tc_fence_after();
+            mark(l, 3);
+          } else if (j == 1) {
+            bwait(z_rem, lp);
+            rearm(z_rem);
+            mark(l, 4);
+          }
+          const uint64_t db = w_wait();
+          if (j == KB - 1) mark(l, 5);
+          const uint64_t da = dz + ((r + j) & (KB - 1)) * kZT;
+          if (l + 1 < L) mma4(tm_acc2, da, db, id64, j == 0);
+          mma4(tm_skip, da, db + (8192 >> 4), id64, l == 0 && j == 0);
           w_release();
         }
         umma_commit(acc2_full);
@@ -290,30 +352,31 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
       // relu(skip_projection(sum / sqrt(L))): s1 travels in the x~ buffer (free since the last GEMM-1; the z buffer may still
       // be read by a slower peer's last GEMM-2)                                                  wavenet.py:96-98
       for (int j = 0; j < KB; ++j) {
-        const int kb = (r + j) % KB;
-        blk_wait(x_full, kb, L, false);
-        const uint32_t s = w_wait();
-        mma4(tm_acc2, make_kmajor_sw128_desc_row(xs_a + kb * kStackXTile, kStackHalo), make_kmajor_sw128_desc(s), id64, j == 0);
+        if (j == 0) { bwait(x_loc, L & 1); tc_fence_after(); }
+        else if (j == 1) bwait(x_rem, L & 1);
+        const uint64_t db = w_wait();
+        mma4(tm_acc2, dx + ((r + j) & (KB - 1)) * kXT + kStackHalo * 8, db, id64, j == 0);
         w_release();
       }
       umma_commit(acc2_full);
       // output_projection: s2 travels in the z buffer                                            wavenet.py:99
       for (int j = 0; j < KB; ++j) {
-        const int kb = (r + j) % KB;
-        blk_wait(z_full, kb, L, false);
-        const uint32_t s = w_wait();
-        mma4(tm_acc1, make_kmajor_sw128_desc(zs_a + kb * kStackZTile), make_kmajor_sw128_desc(s), idout, j == 0);
+        if (j == 0) { bwait(z_loc, L & 1); tc_fence_after(); }
+        else if (j == 1) bwait(z_rem, L & 1);
+        const uint64_t db = w_wait();
+        mma4(tm_acc1, dz + ((r + j) & (KB - 1)) * kZT, db, idout, j == 0);
         w_release();
       }
       umma_commit(acc1_full);
     }
   } else if (warp == 2) {
-    // -------------------------------------------------------------- halo receiver (utterances of several tiles)
-    if (lane == 0 && has_nb) {
+    // -------------------------------------------------------------- third producer (lane 0) and halo receiver (lane 1)
+    if (lane == 0) produce(2);
+    if (lane == 1 && has_nb) {
       grid_dep_wait();
       const uint32_t bytes = (has_left ? 1u : 0u) * KB * kStackEdgeBytes + (has_right ? 1u : 0u) * KB * kStackEdgeBytes;
       for (int seq = 0; seq < L; ++seq) {
-        if (seq > 0) mbar_wait(acc1_full, (seq - 1) & 1);  // GEMM-1 of the previous layer has finished reading the halo rows
+        if (seq > 0) bwait(acc1_full, (seq - 1) & 1);  // GEMM-1 of the previous layer has finished reading the halo rows
         const unsigned int target = p.cnt_base + 8u * (seq + 1);
         uint32_t spins = 0;
         if (has_left)
@@ -376,15 +439,17 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
       }
     };
     // all-gather of this CTA's slice: local arrival + one bulk copy per peer, peers in the order they will consume
-    auto publish = [&](uint32_t tile_a, uint32_t body_off, uint64_t* barv) {
+    // (the KB-1 copies are issued by lane 0 of KB-1 different warps: issuing one costs a thread ~285 cycles)
+    auto publish = [&](uint32_t tile_a, uint32_t body_off, uint64_t* bar_loc, uint64_t* bar_rem) {
       fence_proxy_async_smem();
       tc_fence_before();
       epi_bar_sync();
-      if (leader_thread) {
-        mbar_arrive(&barv[r]);
-        for (int j = 1; j < KB; ++j) {
-          const uint32_t peer = static_cast<uint32_t>((r + KB - j) % KB);
-          bulk_copy_to_peer(tile_a + body_off, tile_a + body_off, kStackZTile, smem_u32(&barv[r]), peer);
+      if (lane == 0) {
+        const int j = warp - 4;  // 0 .. 7
+        if (j == KB - 1) mbar_arrive(bar_loc);
+        if (j < KB - 1 && !(dbg & 8)) {
+          const uint32_t peer = static_cast<uint32_t>((r + KB - 1 - j) & (KB - 1));
+          bulk_copy_to_peer(tile_a + body_off, tile_a + body_off, kStackZTile, smem_u32(bar_rem), peer);
         }
       }
     };
@@ -414,7 +479,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
       float bb[32], dd[32];
       ld_f32x32(p.bhead + c0, bb);
       ld_f32x32(p.dtab + static_cast<size_t>(b) * p.vec_bstride + c0, dd);
-      mbar_wait(acc2_full, ph2);
+      bwait(acc2_full, ph2);
       ph2 ^= 1;
       tc_fence_after();
       uint32_t a[32];
@@ -429,11 +494,11 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
       }
       put_row(xrow_a, row + kStackHalo, o);
       put_edges(0, o);
-      publish(xrow_a, kStackHalo * 128u, x_full);
+      publish(xrow_a, kStackHalo * 128u, x_loc, x_rem);
     }
 
     for (int l = 0; l < L; ++l) {
-      // ---- gate: z = sigmoid(g) * tanh(f), packed-half math as in layer4_kernel.cuh                wavenet.py:40-42
+      // ---- gate: z = sigmoid(g) * tanh(f), packed-half math as in layer_kernel.cuh                wavenet.py:40-42
       {
         const uint16_t* add = p.cproj + (static_cast<size_t>(l) * p.B * p.T + grow) * (2 * C) + 128 * r + 32 * half;
         uint4 bg[4], bf[4];
@@ -442,9 +507,10 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
           bg[i] = __ldg(reinterpret_cast<const uint4*>(add) + i);
           bf[i] = __ldg(reinterpret_cast<const uint4*>(add + 64) + i);
         }
-        mbar_wait(acc1_full, ph1);
+        bwait(acc1_full, ph1);
         ph1 ^= 1;
         tc_fence_after();
+        if (leader_thread) mark(l, 6);
         constexpr uint32_t kHalf2 = 0x38003800u;  // (0.5h, 0.5h)
         uint32_t g[32], f[32];
         tmem_ld_32x32(lane_addr + 32 * half, g);
@@ -465,7 +531,8 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
           }
         }
         put_row(zrow_a, row, zp);
-        publish(zrow_a, 0u, z_full);
+        publish(zrow_a, 0u, z_loc, z_rem);
+        if (leader_thread) mark(l, 7);
       }
       // ---- residual: x~' = (x~ + R) / sqrt(2) + rvec_l  (not after the last layer: wavenet.py:92-94 discards it)
       if (l + 1 < L) {
@@ -474,9 +541,10 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
         uint4 xq[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) xq[i] = ld_shared_v4(xrow_a + sw128_off(row + kStackHalo, 4 * half + i));
-        mbar_wait(acc2_full, ph2);
+        bwait(acc2_full, ph2);
         ph2 ^= 1;
         tc_fence_after();
+        if (leader_thread) mark(l, 8);
         uint32_t a[32];
         tmem_ld_32x32(lane_addr + 128 + 32 * half, a);
         tmem_ld_wait();
@@ -494,14 +562,15 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
         }
         put_row(xrow_a, row + kStackHalo, o);
         put_edges(l + 1, o);
-        publish(xrow_a, kStackHalo * 128u, x_full);
+        publish(xrow_a, kStackHalo * 128u, x_loc, x_rem);
+        if (leader_thread) mark(l, 9);
       }
     }
     // ---- skip sum (TMEM, all layers) -> s1 = (sum + b) / sqrt(L)                                   wavenet.py:96
     {
       float bb[32];
       ld_f32x32(p.bsk + c0, bb);
-      mbar_wait(acc2_full, ph2);
+      bwait(acc2_full, ph2);
       ph2 ^= 1;
       tc_fence_after();
       uint32_t a[32];
@@ -512,13 +581,13 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
       for (int i = 0; i < 16; ++i)
         o[i] = pack_bf16((__uint_as_float(a[2 * i]) + bb[2 * i]) * p.inv_sqrt_L, (__uint_as_float(a[2 * i + 1]) + bb[2 * i + 1]) * p.inv_sqrt_L);
       put_row(xrow_a, row + kStackHalo, o);
-      publish(xrow_a, kStackHalo * 128u, x_full);
+      publish(xrow_a, kStackHalo * 128u, x_loc, x_rem);
     }
     // ---- s2 = relu(skip_projection(s1) + b)                                                        wavenet.py:97-98
     {
       float bb[32];
       ld_f32x32(p.bsp + c0, bb);
-      mbar_wait(acc2_full, ph2);
+      bwait(acc2_full, ph2);
       ph2 ^= 1;
       tc_fence_after();
       uint32_t a[32];
@@ -529,11 +598,11 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
       for (int i = 0; i < 16; ++i)
         o[i] = pack_bf16(fmaxf(__uint_as_float(a[2 * i]) + bb[2 * i], 0.0f), fmaxf(__uint_as_float(a[2 * i + 1]) + bb[2 * i + 1], 0.0f));
       put_row(zrow_a, row, o);
-      publish(zrow_a, 0u, z_full);
+      publish(zrow_a, 0u, z_loc, z_rem);
     }
     // ---- output projection -> fp32 [B][T][FM]: this CTA's nout columns, 16 per warp half             wavenet.py:99
     {
-      mbar_wait(acc1_full, ph1);
+      bwait(acc1_full, ph1);
       ph1 ^= 1;
       tc_fence_after();
       const int ncols = p.nout / 2;  // 8 or 16 columns per thread

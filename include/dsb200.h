@@ -231,8 +231,8 @@ int ds_debug_set_trace(void* dev_buf, int32_t n_entries);
 /* Debug / bench: launch ONLY the fused kernel of residual layer `layer` (ResidualBlock.forward, wavenet.py:33-48) on the
  * session's current activation buffers -- the per-kernel timing hook bench.py's roofline uses. */
 int ds_debug_layer(ds_session* s, int32_t layer, int32_t time_index, void* stream);
-/* 0 unfused (two GEMM launches per layer), 1 smem-z, 2 global-z, 3 CTA pair, 4 CTA pair + halo tiles,
- * 5 CTA pair + halo tiles + grouped pipeline stages (csrc/api.cu). */
+/* 0 = two GEMM launches per layer, 5 = one fused kernel per layer (csrc/layer_kernel.cuh: CTA pairs, halo tiles, grouped pipeline
+ * stages; 1-4 were earlier generations of that kernel, removed). */
 int ds_plan_layer_mode(const ds_plan* plan);
 /* 0 bf16, 1 fp32-accurate (ds_wavenet_config.precision, or DSB200_PRECISION=fp32 in the environment). */
 int ds_plan_precision(const ds_plan* plan);
