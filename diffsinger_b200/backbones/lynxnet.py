@@ -158,7 +158,7 @@ class LYNXNet(nn.Module):
     # ------------------------------------------------------------------ forward
     def forward(self, spec, diffusion_step, cond):
         """spec [B, F, M, T], diffusion_step [B] or [1], cond [B, H, T] -> [B, F, M, T]."""
-        if torch.is_grad_enabled() and (spec.requires_grad or any(p.requires_grad for p in self.parameters())):
+        if torch.is_grad_enabled() and (spec.requires_grad or cond.requires_grad or any(p.requires_grad for p in self.parameters())):
             return self._forward_autograd(spec, diffusion_step, cond)
         return self._forward_native(spec, diffusion_step, cond)
 

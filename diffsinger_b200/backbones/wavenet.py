@@ -88,6 +88,13 @@ class WaveNet(nn.Module):
         # autograd (training) path on CUDA: 'native' = the residual stack's forward / data gradients on the tcgen05 kernels
         # (training.py), 'torch' = differentiable torch ops throughout (the fp32 reference the parity tests compare with)
         self.train_path = os.environ.get('DSB200_TRAIN', 'native')
+        self.register_load_state_dict_post_hook(lambda module, incompatible: module.invalidate_native())
+
+    def invalidate_native(self):
+        """Drop the packed bf16 weights and cached step tables (they are rebuilt on the next call).  Needed only after parameter
+        writes the fingerprint cannot see (`p.data.copy_`, storage aliasing); `load_state_dict` calls it through a hook."""
+        if getattr(self, '_engine', None) is not None:
+            self._engine.invalidate()
 
     def set_precision(self, precision: str):
         """Select the arithmetic of the native path; drops the plan so that weights are repacked."""
@@ -137,6 +144,12 @@ class WaveNet(nn.Module):
         :param diffusion_step: [B] or [1], long or float
         :param cond: [B, H, T] (may be a transposed view of [B, T, H])
         :return: [B, F, M, T]
+
+        Dispatch: the native kernels serve calls that need no gradient.  With autograd ON and any of (spec, cond, parameters)
+        requiring grad -- the default for a freshly built module -- the call is a TRAINING forward (native WaveNetStack on CUDA,
+        torch ops otherwise).  The reference's samplers run under @torch.no_grad(), but `GaussianDiffusion.inference` itself is
+        undecorated (modules/core/ddpm.py:221): a caller that swaps only this backbone must keep its own `torch.no_grad()` (as
+        inference/ds_acoustic.py:183 does) to get the inference kernels.  CPU tensors never run an inference path here.
         """
         if torch.is_grad_enabled() and (spec.requires_grad or cond.requires_grad or any(p.requires_grad for p in self.parameters())):
             if spec.is_cuda and self.train_path == 'native':
@@ -151,7 +164,12 @@ class WaveNet(nn.Module):
         B, Fn, M, T = spec.shape
         per_sample = diffusion_step.numel() > 1
         sess = eng.session(B, T, max_times=1, per_sample=per_sample)
-        sess.set_cond(cond.transpose(1, 2))  # [B, T, H]; a no-copy view when cond came from [B,T,H]
+        # a sampler of the reference that calls forward() once per step (only BACKBONES['wavenet'] swapped)
+        # passes the same cond tensor every time: it is staged (and, on the whole-network path, projected for all layers) once
+        ckey = (cond.data_ptr(), cond._version, tuple(cond.shape), tuple(cond.stride()), eng.weights_key)
+        if sess._cond_key != ckey:
+            sess.set_cond(cond.transpose(1, 2))  # [B, T, H]; a no-copy view when cond came from [B,T,H]
+            sess._cond_key = ckey
         t = diffusion_step.to(torch.float32).reshape(1, -1) if per_sample else diffusion_step.to(torch.float32).reshape(1)
         sess.set_times(t)
         x = spec.reshape(B, Fn * M, T).transpose(1, 2).contiguous().float()  # time-major [B, T, F*M]

@@ -38,6 +38,8 @@ beta_schedule = {"cosine": cosine_beta_schedule, "linear": linear_beta_schedule}
 
 
 class GaussianDiffusion(nn.Module):
+    ANCESTRAL_BLOCK = 32  # steps per program of the ancestral sampler (one CUDA graph and one ring of noise buffers per block)
+
     def __init__(self, out_dims, num_feats=1, timesteps=1000, k_step=1000,
                  backbone_type=None, backbone_args=None, betas=None,
                  spec_min=None, spec_max=None):
@@ -116,8 +118,8 @@ class GaussianDiffusion(nn.Module):
                 prog = programs.dpm_solver_pp_program(self.betas[:t_max], t_max // speedup)
             elif algorithm == 'unipc':
                 prog = programs.unipc_program(self.betas[:t_max], t_max // speedup)
-            elif algorithm == '__ancestral__':
-                prog = programs.ddpm_program(self, t_max)
+            elif algorithm == '__ancestral__':  # block [speedup, t_max) of the ancestral chain (see inference)
+                prog = programs.ddpm_program(self, t_max, speedup)
             else:
                 raise ValueError(f"Unsupported acceleration algorithm for DDPM: {algorithm}.")
             self._programs[key] = prog
@@ -154,15 +156,20 @@ class GaussianDiffusion(nn.Module):
             assert x_start is not None, 'Missing shallow diffusion source.'
             x = x_start
 
-        if t_max > 0:
-            if speedup > 1:
-                prog = self._program(hparams['diff_accelerator'], t_max, speedup)
-                extra = []
-            else:
-                prog = self._program('__ancestral__', t_max, 1)
-                # fresh noise per step from the global generator, same draw order as noise_like (ddpm.py:153)
-                extra = [torch.randn(b, self.num_feats, self.out_dims, T, device=device) for _ in range(t_max)]
-            x_tm = run_program(self.denoise_fn, prog, to_time_major(x), cond, [to_time_major(e) for e in extra])
+        if t_max > 0 and speedup > 1:
+            prog = self._program(hparams['diff_accelerator'], t_max, speedup)
+            x_tm = run_program(self.denoise_fn, prog, to_time_major(x), cond, [])
+        elif t_max > 0:
+            # ancestral chain (ddpm.py:346-349), ANCESTRAL_BLOCK steps per program: the reference holds one noise tensor at a time;
+            # pre-drawing all t_max of them (plus their time-major copies and the session buffers) would cost 3 * t_max * B*T*F*M*4
+            # bytes.  Fresh noise per step comes from the global generator in noise_like's draw order (ddpm.py:153).
+            x_tm = to_time_major(x)
+            for hi in range(t_max, 0, -self.ANCESTRAL_BLOCK):
+                lo = max(hi - self.ANCESTRAL_BLOCK, 0)
+                prog = self._program('__ancestral__', hi, lo)
+                extra = [to_time_major(torch.randn(b, self.num_feats, self.out_dims, T, device=device)) for _ in range(hi - lo)]
+                x_tm = run_program(self.denoise_fn, prog, x_tm, cond, extra)
+                del extra
         else:
             x_tm = to_time_major(x)
         # [B, T, F*M] -> [B, T, M] (F == 1) or [B, F, T, M]

@@ -74,14 +74,15 @@ def pndm_program(alphas_cumprod: torch.Tensor, t_max: int, interval: int) -> Pro
     return p
 
 
-def ddpm_program(sched, t_max: int) -> Program:
-    """Ancestral p_sample, ddpm.py:123-156, loop :346-349.  Buffers 2.. hold the per-step noise
-    (buffer 2+k is the randn drawn at iteration k; the last iteration, t = 0, uses none)."""
+def ddpm_program(sched, t_hi: int, t_lo: int = 0) -> Program:
+    """Ancestral p_sample, ddpm.py:123-156, loop :346-349, for the timesteps t_hi-1 ... t_lo (a block of the full loop: the
+    sampler runs long ancestral chains block by block so that only one block of per-step noise is alive at a time).  Buffers 2..
+    hold the per-step noise (buffer 2+k is the randn drawn at the block's iteration k; t = 0 uses none)."""
     f = lambda name: getattr(sched, name).detach().cpu().double().numpy()
     c1, c2 = f('sqrt_recip_alphas_cumprod'), f('sqrt_recipm1_alphas_cumprod')
     pc1, pc2, plv = f('posterior_mean_coef1'), f('posterior_mean_coef2'), f('posterior_log_variance_clipped')
-    p = Program(2 + t_max)
-    for k, i in enumerate(reversed(range(0, t_max))):
+    p = Program(2 + (t_hi - t_lo))
+    for k, i in enumerate(reversed(range(t_lo, t_hi))):
         ti = p.add_time(i)
         p.eval(E, X, ti)
         terms = [(pc1[i] * c1[i] + pc2[i], X), (-pc1[i] * c2[i], E)]

@@ -286,7 +286,8 @@ struct ds_plan {
   CUtensorMap tm_w1s, tm_w2s, tm_wsks, tm_wsps, tm_wheads;
   // whole-network kernel for launch-bound sessions (stack_kernel.cuh): C = 256, dilations <= 16, F*M <= 128
   int stack_ok;
-  int nout;               // output-projection rows per CTA of the 4-CTA cluster (FMr / 4)
+  int stack_kb;           // CTAs per tile = C / 64
+  int nout;               // output-projection rows per CTA of the cluster
   CUtensorMap tm_wout_st; // output_projection with a (64, nout) box
 };
 
@@ -366,8 +367,12 @@ extern "C" int ds_plan_create(const ds_wavenet_config* cfg, ds_plan** out) {
   p->S = p->split ? 2 : 1;
   if (p->split) p->fused = 0;
   p->has_small = (!p->split && p->BN_G == 256) ? 1 : 0;
-  p->nout = p->FMr / kStackKB;
-  p->stack_ok = (p->has_small && C == 64 * kStackKB && p->max_dil <= kStackHalo && FM <= 128 && p->FMp <= 128) ? 1 : 0;
+  // whole-network kernel: C = 256 (4 CTAs per tile, the narrow gate pack's 128-row passes) or C = 192 (3 CTAs; the regular pack
+  // already has 128-row passes and 64-row boxes there)
+  p->stack_kb = C / 64;
+  p->nout = (int)align_up((size_t)ceil_div(FM, p->stack_kb), 16);  // output-projection rows per CTA (a UMMA N: multiple of 16)
+  p->stack_ok = (!p->split && ((C == 256 && p->has_small) || (C == 192 && p->BN_G == 128 && p->BN_C == 64)) &&
+                 p->max_dil <= kStackHalo && FM <= 128 && p->FMp <= 128 && p->nout <= 32) ? 1 : 0;
   {
     // opt-in (DSB200_HOIST=1): measured on B200 it does NOT pay -- the MMA work drops 12.5 % (281 vs 325 us MMA-side) but
     // the gate epilogue then reads its 2C f16 values per frame from HBM with per-lane row accesses and becomes the
@@ -468,7 +473,10 @@ extern "C" int ds_plan_pack_weights(ds_plan* p, const ds_wavenet_weights* w, voi
 struct GraphEntry {
   cudaGraphExec_t exec = nullptr;
   int64_t launches = 0;
+  uint64_t last_use = 0;  // LRU stamp
 };
+constexpr size_t kMaxSessionGraphs = 16;  // captured graphs kept per session; a caller that passes fresh buffers every call
+                                          // (the key holds the buffer addresses) recycles the least recently used entry
 
 struct ds_session {
   ds_plan* plan;
@@ -482,6 +490,7 @@ struct ds_session {
   CUtensorMap tm_zs, tm_xs[2];  // TMA store maps (grouped kernel)
   cudaStream_t cap_stream = nullptr;
   std::map<std::string, GraphEntry> graphs;
+  uint64_t graph_clock = 0;
   int64_t last_launches = 0;
   bool cond_set = false;
   bool pdl = true;     // DSB200_PDL=0 turns programmatic dependent launch off
@@ -524,31 +533,34 @@ static bool session_is_medium(const ds_plan* p, int B, int T) {
 // evaluation as ONE launch of ds_stack_kernel: a 4-CTA cluster per tile, all clusters co-resident (neighbouring tiles exchange
 // edge frames through flags in global memory, so a cluster that is not resident would dead-lock its neighbours).
 // DSB200_STACK=0/1 forbids / forces it (forcing still needs co-residency).
-static int stack_max_clusters() {
+template <int KB>
+static int stack_max_clusters_t() {
   static int cached = -1;
   if (cached >= 0) return cached;
   if (ensure_device() != 0) return 0;  // no device (host-only callers): never cache
   int n = 0;
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(kStackKB * 64); cfg.blockDim = dim3(kGemmThreads); cfg.dynamicSmemBytes = kStackSmemBytes;
+  cfg.gridDim = dim3(KB * 64); cfg.blockDim = dim3(kGemmThreads); cfg.dynamicSmemBytes = stack_smem_bytes(KB);
   cudaLaunchAttribute at[1];
   at[0].id = cudaLaunchAttributeClusterDimension;
-  at[0].val.clusterDim.x = kStackKB; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  at[0].val.clusterDim.x = KB; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
   cfg.attrs = at; cfg.numAttrs = 1;
-  if (cudaFuncSetAttribute(ds_stack_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStackSmemBytes) != cudaSuccess ||
-      cudaOccupancyMaxActiveClusters(&n, ds_stack_kernel<false>, &cfg) != cudaSuccess) {
+  if (cudaFuncSetAttribute(ds_stack_kernel<KB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stack_smem_bytes(KB)) != cudaSuccess ||
+      cudaFuncSetAttribute(ds_stack_kernel<KB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stack_smem_bytes(KB)) != cudaSuccess ||
+      cudaOccupancyMaxActiveClusters(&n, ds_stack_kernel<KB, false>, &cfg) != cudaSuccess) {
     cudaGetLastError();
     n = 0;
   }
   cached = n;
   return cached;
 }
+static int stack_max_clusters(int kb) { return kb == 4 ? stack_max_clusters_t<4>() : stack_max_clusters_t<3>(); }
 static bool session_is_stack(const ds_plan* p, int B, int T) {
   if (!p->stack_ok) return false;
   const char* se = getenv("DSB200_STACK");
   if (se && atoi(se) == 0) return false;
   const long tiles = (long)B * ceil_div(T, 128);
-  const int cap = stack_max_clusters();
+  const int cap = stack_max_clusters(p->stack_kb);
   if (tiles > cap) return false;
   if (se) return true;
   return tiles <= cap;
@@ -583,7 +595,7 @@ static void session_layout(const ds_plan* p, int B, int T, int max_times, int pe
   if (session_is_stack(p, B, T)) {
     const size_t tiles = (size_t)B * ceil_div(T, 128);
     s->o_scproj = take(rows * L * 2 * C * 2);
-    s->o_edges = take(2 * tiles * 2 * kStackKB * kStackEdgeBytes);
+    s->o_edges = take(2 * tiles * 2 * p->stack_kb * kStackEdgeBytes);
     s->o_cnt = take(tiles * 2 * sizeof(unsigned int));
   }
   s->ws_bytes = off;
@@ -689,13 +701,13 @@ extern "C" int ds_session_set_cond(ds_session* s, const float* cond_bth, void* s
     GemmParams g;
     memset(&g, 0, sizeof(g));
     g.T = s->T; g.B = s->B; g.tiles_t = ceil_div(s->T, 128); g.scale = 1.0f;
-    g.tmA0 = s->tm_cond; g.tmB = p->tm_w1s; g.kb_a0 = H / 64; g.n_taps = 1; g.b_k0 = 3 * C;
+    g.tmA0 = s->tm_cond; g.tmB = p->has_small ? p->tm_w1s : p->tm_w1; g.kb_a0 = H / 64; g.n_taps = 1; g.b_k0 = 3 * C;
     g.n_tiles = 2 * C / 128; g.total_tiles = s->B * g.tiles_t * g.n_tiles;
     g.ld_out = 2 * C; g.out_c0 = 0;
     for (int l = 0; l < L; ++l) {
       g.b_row0 = l * 2 * C;
       g.out = s->ws + s->o_scproj + (size_t)l * rows * 2 * C * 2;
-      g.bias = (const float*)(p->packed + p->o_b1s) + (size_t)l * 2 * C;
+      g.bias = (const float*)(p->packed + (p->has_small ? p->o_b1s : p->o_b1)) + (size_t)l * 2 * C;
       DS_TRY(launch_gemm(128, EPI_CPROJ, g, (cudaStream_t)stream));
     }
   }
@@ -777,7 +789,11 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   if (s->stack) {
     StackParams sp;
     memset(&sp, 0, sizeof(sp));
-    sp.tmW1 = p->tm_w1s; sp.tmW2 = p->tm_w2s; sp.tmWsk = p->tm_wsks; sp.tmWsp = p->tm_wsps; sp.tmWhead = p->tm_wheads;
+    if (p->has_small) {
+      sp.tmW1 = p->tm_w1s; sp.tmW2 = p->tm_w2s; sp.tmWsk = p->tm_wsks; sp.tmWsp = p->tm_wsps; sp.tmWhead = p->tm_wheads;
+    } else {  // C = 192: the regular pack has 128-row gate passes and 64-row boxes already
+      sp.tmW1 = p->tm_w1; sp.tmW2 = p->tm_w2; sp.tmWsk = p->tm_wsk; sp.tmWsp = p->tm_wsp; sp.tmWhead = p->tm_whead;
+    }
     sp.tmWout = p->tm_wout_st;
     sp.x = x; sp.out = out;
     sp.cproj = (const uint16_t*)(s->ws + s->o_scproj);
@@ -785,18 +801,14 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
     sp.bsk = (const float*)(pk + p->o_bsk); sp.bsp = (const float*)(pk + p->o_bsp); sp.bout = (const float*)(pk + p->o_bout);
     sp.vec_bstride = vstride;
     sp.edges = s->ws + s->o_edges; sp.cnt = (unsigned int*)(s->ws + s->o_cnt);
-    sp.cnt_base = 8u * (unsigned)L * (unsigned)s->eval_seq;
+    sp.cnt_base = 2u * (unsigned)p->stack_kb * (unsigned)L * (unsigned)s->eval_seq;
     sp.T = T; sp.B = B; sp.tiles_t = tiles_t; sp.n_tiles = B * tiles_t;
     sp.L = L; sp.cycle = p->cfg.dilation_cycle_length; sp.C = C; sp.FM = p->FM; sp.FMp = p->FMp; sp.nout = p->nout;
     sp.inv_sqrt_L = 1.0f / sqrtf((float)L);
     { const char* de = getenv("DSB200_DBG"); sp.dbg = de ? atoi(de) : 0; }
     sp.trace = g_trace; sp.trace_cap = g_trace_cap * 4;  // ds_debug_set_trace counts entries of 4 words
-    static bool attr_done = false;
-    if (!attr_done) {
-      CUDA_TRY(cudaFuncSetAttribute(ds_stack_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStackSmemBytes));
-      CUDA_TRY(cudaFuncSetAttribute(ds_stack_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStackSmemBytes));
-      attr_done = true;
-    }
+    const int KBs = p->stack_kb;
+    (void)stack_max_clusters(KBs);  // also sets the kernels' dynamic shared-memory attribute
     const bool dbg_build = sp.dbg != 0 || sp.trace != nullptr;  // role switches / timeline: the instrumented instantiation
     if (s->eval_seq == 0 && tiles_t > 1)  // edge-arrival counters restart with every program run (targets are monotonic inside it)
       CUDA_TRY(cudaMemsetAsync(s->ws + s->o_cnt, 0, (size_t)B * tiles_t * 2 * sizeof(unsigned int), st));
@@ -805,8 +817,15 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
       explicit PdlScope(bool on) : prev(t_pdl) { t_pdl = on; }
       ~PdlScope() { t_pdl = prev; }
     } pdl_scope(s->pdl && !(s->eval_seq == 0 && tiles_t > 1));  // a launch right after the memset node is a plain dependency
-    if (dbg_build) CUDA_TRY(launch_k(ds_stack_kernel<true>, dim3(kStackKB * B * tiles_t), dim3(kGemmThreads), kStackSmemBytes, st, sp));
-    else CUDA_TRY(launch_k(ds_stack_kernel<false>, dim3(kStackKB * B * tiles_t), dim3(kGemmThreads), kStackSmemBytes, st, sp));
+    const dim3 grid(KBs * B * tiles_t);
+    const size_t smem_b = stack_smem_bytes(KBs);
+    if (KBs == 4) {
+      if (dbg_build) CUDA_TRY(launch_k(ds_stack_kernel<4, true>, grid, dim3(kGemmThreads), smem_b, st, sp));
+      else CUDA_TRY(launch_k(ds_stack_kernel<4, false>, grid, dim3(kGemmThreads), smem_b, st, sp));
+    } else {
+      if (dbg_build) CUDA_TRY(launch_k(ds_stack_kernel<3, true>, grid, dim3(kGemmThreads), smem_b, st, sp));
+      else CUDA_TRY(launch_k(ds_stack_kernel<3, false>, grid, dim3(kGemmThreads), smem_b, st, sp));
+    }
     ++s->eval_seq;
     ++*launches;
     return 0;
@@ -1008,8 +1027,17 @@ extern "C" int ds_session_run(ds_session* s, const ds_op* ops, int32_t n_ops, fl
     ce = cudaGraphInstantiate(&e.exec, graph, 0);
     cudaGraphDestroy(graph);
     if (ce != cudaSuccess) return fail(DS_ERR_CUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(ce));
+    if (s->graphs.size() >= kMaxSessionGraphs) {
+      auto old = s->graphs.begin();
+      for (auto jt = s->graphs.begin(); jt != s->graphs.end(); ++jt)
+        if (jt->second.last_use < old->second.last_use) old = jt;
+      // an exec that is still running keeps its resources until it finishes (cudaGraphExecDestroy is deferred by the runtime)
+      if (old->second.exec) cudaGraphExecDestroy(old->second.exec);
+      s->graphs.erase(old);
+    }
     it = s->graphs.emplace(key, e).first;
   }
+  it->second.last_use = ++s->graph_clock;
   CUDA_TRY(cudaGraphLaunch(it->second.exec, st));
   s->last_launches = it->second.launches;
   return 0;

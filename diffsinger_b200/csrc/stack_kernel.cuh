@@ -30,15 +30,18 @@
 
 namespace dsb {
 
-constexpr int kStackKB = 4;                 // cluster size = C / 64 (C = 256)
+constexpr int kStackMaxKB = 4;              // cluster size KB = C / 64: 4 (C = 256: pitch predictor, acoustic 20 x 256) or 3 (C = 192:
+                                            // multi-variance predictor)
 constexpr int kStackHalo = 16;              // halo frames each side = largest supported dilation
 constexpr int kStackXRows = 128 + 2 * kStackHalo;
 constexpr uint32_t kStackXTile = kStackXRows * 128u;   // 20480 B per k-block (1024-aligned)
 constexpr uint32_t kStackZTile = 128u * 128u;          // 16384 B per k-block
 constexpr uint32_t kStackStage = 16384u;               // weight ring stage: [128 rows][64 K] bf16
-constexpr int kStackStages = 5;
+__host__ __device__ constexpr int stack_stages(int kb) { return kb == 4 ? 5 : 7; }  // weight-ring depth that fits beside x~ and z
 constexpr int kStackProducers = 3;            // weight-issuing threads (warp 0, warp 3, warp 2)
-constexpr uint32_t kStackSmemBytes = 1024u + kStackKB * (kStackXTile + kStackZTile) + kStackStages * kStackStage + 1024u;
+__host__ __device__ constexpr uint32_t stack_smem_bytes(int kb) {
+  return 1024u + kb * (kStackXTile + kStackZTile) + stack_stages(kb) * kStackStage + 1024u;
+}
 constexpr uint32_t kStackEdgeBytes = kStackHalo * 128u;  // one k-block of one edge: 16 rows x 128 B
 
 struct StackParams {
@@ -60,7 +63,7 @@ struct StackParams {
   int vec_bstride;
   uint8_t* edges;       // [2 parity][tiles][2 sides][KB][16 rows][128 B]: edge frames of x~ in operand (swizzled) layout
   unsigned int* cnt;    // [tiles][2]: arrivals per (tile, side), monotonic over the evaluations of one program run
-  unsigned int cnt_base;  // 8 * L * (index of this evaluation in the program): targets are cnt_base + 8 * (seq + 1)
+  unsigned int cnt_base;  // 2 KB * L * (index of this evaluation in the program): targets are cnt_base + 2 KB * (seq + 1)
   int T, B, tiles_t, n_tiles;
   int L, cycle, C, FM, FMp, nout;
   float inv_sqrt_L;
@@ -103,13 +106,6 @@ __device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
 // position of 16-byte chunk `j` of row `row` inside a [rows][128 B] SWIZZLE_128B tile at a 1024-aligned base
 __device__ __forceinline__ uint32_t sw128_off(int row, int j) { return static_cast<uint32_t>(row) * 128u + ((j ^ (row & 7)) << 4); }
 
-// GEMM-1 step order of CTA r: the centre tap of every k-block first (needs no halo), k-blocks in arrival order r, r+1, ...;
-// then taps 0 and 2 of every k-block.
-__device__ __forceinline__ void stack_conv_step(int i, int r, int& kb, int& tap) {
-  if (i < kStackKB) { kb = (r + i) % kStackKB; tap = 1; }
-  else { const int k = i - kStackKB; kb = (r + (k >> 1)) % kStackKB; tap = (k & 1) * 2; }
-}
-
 // Lean wait for the single-thread roles: every instruction on those threads is serial latency (~6 cycles each, no other warp hides
 // it), so no spin counter; the bounded mbar_wait (traps instead of hanging) is used in the kDbg instantiation.
 __device__ __forceinline__ void mbar_wait_lean(uint64_t* bar, uint32_t parity) {
@@ -127,10 +123,10 @@ __device__ __forceinline__ void mbar_wait_lean(uint64_t* bar, uint32_t parity) {
 // kDbg = true: role switches (StackParams::dbg), %globaltimer trace, bounded waits.  The production instantiation carries none of
 // it: the MMA issuer is ONE thread whose instruction count per weight stage is the kernel's critical path (tools/stack_trace.py:
 // ~285 cycles per mbarrier operation, ~55 per tcgen05.mma issue).
-template <bool kDbg>
-__global__ void __cluster_dims__(kStackKB, 1, 1) __launch_bounds__(kGemmThreads, 1)
+template <int KB, bool kDbg>
+__global__ void __cluster_dims__(KB, 1, 1) __launch_bounds__(kGemmThreads, 1)
 ds_stack_kernel(const __grid_constant__ StackParams p) {
-  constexpr int KB = kStackKB;
+  constexpr int kStackStages = stack_stages(KB);
   const int dbg = kDbg ? p.dbg : 0;
   auto bwait = [&](uint64_t* bar, uint32_t parity) {
     if constexpr (kDbg) mbar_wait(bar, parity);
@@ -236,12 +232,12 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
     for (int l = 0; l < L; ++l) {
       const int row1 = l * 2 * C + 128 * r;
       for (int j = 0; j < KB; ++j)
-        if (uint8_t* s = begin(128 * 128, bar)) tma_load_2d(&p.tmW1, bar, s, (KB + ((r + j) & (KB - 1))) * 64, row1);
+        if (uint8_t* s = begin(128 * 128, bar)) tma_load_2d(&p.tmW1, bar, s, (KB + ((r + j) % KB)) * 64, row1);
       for (int j = 0; j < KB; ++j)
         for (int tap = 0; tap < 3; tap += 2)
-          if (uint8_t* s = begin(128 * 128, bar)) tma_load_2d(&p.tmW1, bar, s, (tap * KB + ((r + j) & (KB - 1))) * 64, row1);
+          if (uint8_t* s = begin(128 * 128, bar)) tma_load_2d(&p.tmW1, bar, s, (tap * KB + ((r + j) % KB)) * 64, row1);
       for (int j = 0; j < KB; ++j) {
-        const int kb = (r + j) & (KB - 1);
+        const int kb = (r + j) % KB;
         const bool res = l + 1 < L;
         if (uint8_t* s = begin((res ? 2u : 1u) * 64 * 128, bar)) {
           if (res) tma_load_2d(&p.tmW2, bar, s, kb * 64, l * C + 64 * r);
@@ -250,9 +246,9 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
       }
     }
     for (int j = 0; j < KB; ++j)
-      if (uint8_t* s = begin(64 * 128, bar)) tma_load_2d(&p.tmWsp, bar, s, ((r + j) & (KB - 1)) * 64, 64 * r);
+      if (uint8_t* s = begin(64 * 128, bar)) tma_load_2d(&p.tmWsp, bar, s, ((r + j) % KB) * 64, 64 * r);
     for (int j = 0; j < KB; ++j)
-      if (uint8_t* s = begin(p.nout * 128, bar)) tma_load_2d(&p.tmWout, bar, s, ((r + j) & (KB - 1)) * 64, p.nout * r);
+      if (uint8_t* s = begin(p.nout * 128, bar)) tma_load_2d(&p.tmWout, bar, s, ((r + j) % KB) * 64, p.nout * r);
   };
 
   if (warp == 0) {
@@ -314,12 +310,12 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
             mark(l, 1);
           }
           const uint64_t db = w_wait();
-          mma4(tm_acc1, dx + ((r + j) & (KB - 1)) * kXT + kStackHalo * 8, db, id128, j == 0);
+          mma4(tm_acc1, dx + ((r + j) % KB) * kXT + kStackHalo * 8, db, id128, j == 0);
           w_release();
         }
         if (has_nb) bwait(halo_full, lp);
         for (int j = 0; j < KB; ++j) {
-          const uint64_t da = dx + ((r + j) & (KB - 1)) * kXT + kStackHalo * 8;
+          const uint64_t da = dx + ((r + j) % KB) * kXT + kStackHalo * 8;
 #pragma unroll
           for (int sgn = -1; sgn <= 1; sgn += 2) {
             const uint64_t db = w_wait();
@@ -342,7 +338,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
           }
           const uint64_t db = w_wait();
           if (j == KB - 1) mark(l, 5);
-          const uint64_t da = dz + ((r + j) & (KB - 1)) * kZT;
+          const uint64_t da = dz + ((r + j) % KB) * kZT;
           if (l + 1 < L) mma4(tm_acc2, da, db, id64, j == 0);
           mma4(tm_skip, da, db + (8192 >> 4), id64, l == 0 && j == 0);
           w_release();
@@ -355,7 +351,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
         if (j == 0) { bwait(x_loc, L & 1); tc_fence_after(); }
         else if (j == 1) bwait(x_rem, L & 1);
         const uint64_t db = w_wait();
-        mma4(tm_acc2, dx + ((r + j) & (KB - 1)) * kXT + kStackHalo * 8, db, id64, j == 0);
+        mma4(tm_acc2, dx + ((r + j) % KB) * kXT + kStackHalo * 8, db, id64, j == 0);
         w_release();
       }
       umma_commit(acc2_full);
@@ -364,7 +360,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
         if (j == 0) { bwait(z_loc, L & 1); tc_fence_after(); }
         else if (j == 1) bwait(z_rem, L & 1);
         const uint64_t db = w_wait();
-        mma4(tm_acc1, dz + ((r + j) & (KB - 1)) * kZT, db, idout, j == 0);
+        mma4(tm_acc1, dz + ((r + j) % KB) * kZT, db, idout, j == 0);
         w_release();
       }
       umma_commit(acc1_full);
@@ -377,7 +373,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
       const uint32_t bytes = (has_left ? 1u : 0u) * KB * kStackEdgeBytes + (has_right ? 1u : 0u) * KB * kStackEdgeBytes;
       for (int seq = 0; seq < L; ++seq) {
         if (seq > 0) bwait(acc1_full, (seq - 1) & 1);  // GEMM-1 of the previous layer has finished reading the halo rows
-        const unsigned int target = p.cnt_base + 8u * (seq + 1);
+        const unsigned int target = p.cnt_base + 2u * KB * (seq + 1);  // two epilogue warps per CTA arrive per edge
         uint32_t spins = 0;
         if (has_left)
           while (ld_acquire_gpu(&p.cnt[(tile - 1) * 2 + 1]) < target)
@@ -448,7 +444,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
         const int j = warp - 4;  // 0 .. 7
         if (j == KB - 1) mbar_arrive(bar_loc);
         if (j < KB - 1 && !(dbg & 8)) {
-          const uint32_t peer = static_cast<uint32_t>((r + KB - 1 - j) & (KB - 1));
+          const uint32_t peer = static_cast<uint32_t>((r + KB - 1 - j) % KB);
           bulk_copy_to_peer(tile_a + body_off, tile_a + body_off, kStackZTile, smem_u32(bar_rem), peer);
         }
       }

@@ -83,6 +83,7 @@ class Session:
         """cond [B, T, H] fp32 contiguous."""
         assert cond_bth.shape == (self.B, self.T, self.engine.H), (cond_bth.shape, (self.B, self.T, self.engine.H))
         cond_bth = _f32c(cond_bth)
+        self._cond_key = None  # callers that cache by tensor identity (WaveNet._forward_native) set it after this call
         nat.check(nat.lib().ds_session_set_cond(self.handle, _ptr(cond_bth), _stream()))
 
     def set_times(self, t: torch.Tensor):
@@ -200,6 +201,15 @@ class WaveNetEngine:
         nat.check(nat.lib().ds_plan_pack_weights(self.plan, C.byref(w), self._packed_base, self._packed_bytes, _stream()))
         torch.cuda.current_stream().synchronize()  # the fp32 staging copies in `keep` may be freed after this
         self.weights_key = self.weights_fingerprint(module)
+
+    def invalidate(self):
+        """Forget the packed weights: the next use repacks from the module's current parameters.  The fingerprint
+        (data_ptr, _version) does not see writes through `.data` / storage aliases (EMA helpers, weight swaps): call this -- or
+        module.invalidate_native() -- after such an update.  load_state_dict does it by itself (post hook)."""
+        self.weights_key = None
+        for s in self.sessions.values():
+            s._times_key = None
+            s._cond_key = None
 
     def session(self, B: int, T: int, max_times: int = 64, per_sample: bool = False) -> Session:
         key = (B, T, per_sample, _stream())  # a session's buffers belong to the stream its kernels run on

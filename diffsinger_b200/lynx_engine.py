@@ -240,15 +240,18 @@ class LynxEngine:
         if not use_graph or len(prog.ops) > 1024:
             ws.last_launches = pre + self._run_ops(ws, prog, bufs, vecs, hoist)
             return bufs[0].clone()
-        graph = ws.graphs.get(gkey)
-        if graph is None:
+        entry = ws.graphs.get(gkey)
+        if entry is None:
+            if len(ws.graphs) >= 8:  # bounded: every captured graph owns a private activation pool
+                ws.graphs.pop(next(iter(ws.graphs)))
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
-                ws.graph_launches = self._run_ops(ws, prog, bufs, vecs, hoist)
-            ws.graphs[gkey] = graph
-            ws._graph_refs = getattr(ws, "_graph_refs", []) + [prog, vecs]  # keep ids / device pointers valid
-        graph.replay()
-        ws.last_launches = pre + ws.graph_launches
+                n_launch = self._run_ops(ws, prog, bufs, vecs, hoist)
+            # the entry keeps the Program (its id is the key) and the step vectors (device pointers baked into the graph) alive
+            # exactly as long as the graph: clearing ws.graphs frees all three
+            entry = ws.graphs[gkey] = (graph, n_launch, prog, vecs)
+        entry[0].replay()
+        ws.last_launches = pre + entry[1]
         return bufs[0].clone()
 
     def _run_ops(self, ws: LynxWorkspace, prog: Program, bufs: List[torch.Tensor], vecs: torch.Tensor, hoisted: bool = False) -> int:

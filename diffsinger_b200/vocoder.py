@@ -181,7 +181,7 @@ class Generator(nn.Module):
     def forward(self, x, f0, rand_ini=None, noise=None):
         """x [B, num_mels, T] (natural-log mel), f0 [B, T] (Hz, 0 = unvoiced) -> [B, 1, T * hop]."""
         har = self.m_source(f0, self.upp, rand_ini, noise).transpose(1, 2)                    # [B, 1, T * upp]
-        if torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in self.parameters())) or not x.is_cuda:
+        if torch.is_grad_enabled() and (x.requires_grad or f0.requires_grad or any(p.requires_grad for p in self.parameters())) or not x.is_cuda:
             return self._forward_torch(x, har)
         return self._forward_native(x, har)
 

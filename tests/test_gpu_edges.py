@@ -23,11 +23,14 @@ def _net(sd, C, L, cycle, M, F, H=256):
     return net.eval().to(dev)
 
 
-@pytest.mark.parametrize("small", ["0", "1"])
+@pytest.mark.parametrize("path", ["stack", "small", "fused"])
 @pytest.mark.parametrize("T", [1, 5, 17, 127, 128, 129, 255, 256, 257, 383, 600])
-def test_sequence_length_edges(T, small, monkeypatch):
-    """cycle 5 -> dilations up to 16, so T = 1, 5 sit entirely inside the conv's zero padding."""
-    monkeypatch.setenv("DSB200_SMALL", small)
+def test_sequence_length_edges(T, path, monkeypatch):
+    """cycle 5 -> dilations up to 16, so T = 1, 5 sit entirely inside the conv's zero padding.  Every kernel family that can run
+    this shape: the whole-network cluster kernel (default here), the narrow-tile GEMM chain, one fused kernel per layer."""
+    if path != "stack":
+        monkeypatch.setenv("DSB200_STACK", "0")
+        monkeypatch.setenv("DSB200_SMALL", "1" if path == "small" else "0")
     C, L, cycle, M, F, B = 256, 6, 5, 64, 1, 3
     sd = random_state_dict(M, F, L, C, 256, seed=31)
     net = _net(sd, C, L, cycle, M, F)
@@ -38,8 +41,42 @@ def test_sequence_length_edges(T, small, monkeypatch):
     ref = OracleWaveNet(sd, F, cycle)(spec, t, cond)
     with torch.no_grad():
         y = net(spec.to(dev), t.to(dev), cond.to(dev)).cpu()
+    assert next(iter(net.engine().sessions.values())).path == path
     assert y.shape == ref.shape and torch.isfinite(y).all()
     assert rel_l2(y, ref) < EVAL_TOL
+
+
+def test_session_graph_cache_is_bounded():
+    """ds_session_run keys its captured graphs by (ops, buffer addresses); a caller that brings fresh buffers every call must not
+    grow the cache without bound (kMaxSessionGraphs = 16, least recently used entry recycled) -- and results stay right."""
+    C, L, cycle, M, F, B, T = 256, 2, 2, 64, 1, 1, 96
+    sd = random_state_dict(M, F, L, C, 256, seed=3)
+    net = _net(sd, C, L, cycle, M, F)
+    eng = net.engine()
+    sess = eng.session(B, T, max_times=4)
+    from diffsinger_b200.engine import Program
+    prog = Program(2)
+    ti = prog.add_time(321.0)
+    prog.eval(1, 0, ti)
+    prog.lincomb(0, [(0.5, 0), (-0.25, 1)])
+    g = torch.Generator().manual_seed(1)
+    cond = torch.randn(B, T, 256, generator=g).to(dev)
+    x0 = torch.randn(B, T, F * M, generator=g).to(dev)
+    sess.set_cond(cond)
+    sess.set_program_times(prog.times)
+    want = None
+    keep = []
+    for i in range(40):  # 40 distinct buffer pairs > 16 cached graphs
+        bufs = [x0.clone(), torch.empty_like(x0)]
+        keep.append(bufs)
+        sess.run(prog, bufs, use_graph=True)
+        if want is None:
+            ref = [x0.clone(), torch.empty_like(x0)]
+            sess.run(prog, ref, use_graph=False)
+            want = ref[0].clone()
+        assert torch.equal(bufs[0], want)
+    sess.run(prog, keep[0], use_graph=True)  # long evicted: captured again
+    torch.cuda.synchronize()
 
 
 def test_ragged_lengths_one_session_each():

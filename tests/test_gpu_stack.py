@@ -29,7 +29,7 @@ def _path(net):
     return next(reversed(net.engine().sessions.values())).path
 
 
-@pytest.mark.parametrize("L,cycle,M,F,B,T", [
+@pytest.mark.parametrize("L,cycle,M,F,B,T,C", [(*c, 256) if len(c) == 6 else c for c in [
     (1, 1, 64, 1, 1, 128),     # head + one layer (no residual exchange) + tail, one full tile
     (2, 1, 64, 1, 1, 128),     # one residual exchange
     (4, 4, 128, 1, 1, 97),     # dilations 1..8, ragged single tile (frames >= T must stay zero: conv padding)
@@ -39,9 +39,11 @@ def _path(net):
     (20, 4, 128, 1, 1, 517),   # config #1 backbone, five tiles
     (20, 4, 128, 1, 3, 300),   # batch of three utterances x three tiles
     (6, 3, 24, 2, 2, 200),     # F = 2, F*M = 48 (output rows padded to 64)
-])
-def test_stack_forward_matches_oracle_and_chain(monkeypatch, L, cycle, M, F, B, T):
-    C = 256
+    (10, 4, 24, 2, 1, 128, 192),   # multi-variance predictor: C = 192 -> clusters of THREE CTAs
+    (10, 4, 24, 2, 2, 300, 192),   # ... several tiles and utterances
+    (3, 2, 64, 1, 1, 77, 192),
+]])
+def test_stack_forward_matches_oracle_and_chain(monkeypatch, L, cycle, M, F, B, T, C):
     sd = random_state_dict(M, F, L, C, 256, seed=L * 7 + T)
     g = torch.Generator().manual_seed(5)
     spec = torch.randn(B, F, M, T, generator=g)
@@ -62,7 +64,7 @@ def test_stack_forward_matches_oracle_and_chain(monkeypatch, L, cycle, M, F, B, 
         y2 = net2(spec.to(dev), t.to(dev), cond.to(dev))
     assert _path(net2) != "stack"
     e_chain = rel_l2(y.cpu(), y2.cpu())
-    print(f"\n[stack L{L} cycle{cycle} M{M} F{F} B{B} T{T}] vs oracle {e_oracle:.3e}, vs kernel chain {e_chain:.3e} "
+    print(f"\n[stack C{C} L{L} cycle{cycle} M{M} F{F} B{B} T{T}] vs oracle {e_oracle:.3e}, vs kernel chain {e_chain:.3e} "
           f"(chain vs oracle {rel_l2(y2.cpu(), ref):.3e})")
     assert torch.isfinite(y).all()
     assert e_oracle < EVAL_TOL and e_chain < EVAL_TOL
@@ -104,4 +106,34 @@ def test_pitch_predictor_ddim20_on_the_stack_kernel(T):
     ref = so.finish(x, torch.tensor([-8.0]), torch.tensor([8.0])).mean(-1).clamp(-12.0, 12.0)
     err = rel_l2(outs[0], ref)
     print(f"\n[pitch predictor ddim-20, T={T}, stack kernel] final curve rel-L2 {err:.3e}")
+    assert err < MEL_TOL
+
+
+def test_multi_variance_predictor_euler20_on_three_cta_clusters():
+    """configs[3], second sampler: MultiVarianceRectifiedFlow (WaveNet 10 x 192, 2 x 24 bins), Euler 20 steps, batch 1."""
+    M, F, L, C, H, cycle, T = 24, 2, 10, 192, 256, 4, 300
+    sd = random_state_dict(M, F, L, C, H, seed=34)
+    ds.hparams.clear()
+    ds.hparams.update(hidden_size=H, sampling_algorithm="euler", sampling_steps=20, T_start=0.0, T_start_infer=0.0,
+                      use_shallow_diffusion=False, time_scale_factor=1000)
+    m = ds.MultiVarianceRectifiedFlow(ranges=[(-96.0, -12.0), (-96.0, -20.0)], clamps=[(-96.0, 0.0), (-96.0, 0.0)], repeat_bins=M,
+                                      backbone_type="wavenet", backbone_args=dict(num_layers=L, num_channels=C, dilation_cycle_length=cycle))
+    m.velocity_fn.load_state_dict(sd)
+    m = m.eval().to(dev)
+    g = torch.Generator().manual_seed(4)
+    cond = torch.randn(1, T, H, generator=g)
+    noise = torch.randn(1, F, M, T, generator=g)
+    m._noise_override = noise.to(dev)
+    with torch.no_grad():
+        ys = [v.cpu() for v in m(cond.to(dev), infer=True)]
+    m._noise_override = None
+    sess = next(iter(m.velocity_fn.engine().sessions.values()))
+    assert sess.path == "stack" and sess.last_launches == 40
+    from oracle import solvers_oracle as sv
+    x = sv.sample_reflow(OracleWaveNet(sd, F, cycle), noise, cond.transpose(1, 2), 20, "euler")
+    smin = torch.tensor([[-96.0], [-96.0]])[None, None].transpose(-3, -2)
+    smax = torch.tensor([[-12.0], [-20.0]])[None, None].transpose(-3, -2)
+    ref = torch.stack([v.clamp(-96.0, 0.0) for v in so.finish(x, smin, smax).mean(-1).unbind(1)])
+    err = rel_l2(torch.stack(ys), ref)
+    print(f"\n[multi-variance predictor euler-20, T={T}, stack kernel, 3-CTA clusters] final curves rel-L2 {err:.3e}")
     assert err < MEL_TOL

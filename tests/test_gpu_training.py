@@ -25,12 +25,18 @@ def _model(C, L, M, F, cycle, hidden=256):
     return m.cuda()
 
 
+COS_FLOOR = 0.995  # per tensor: a wrong / missing term (e.g. a bias gradient off by a factor) fails this even inside a loose rel-L2
+
+
 def _check(grads, tol):
     errs = {}
     for name, g_ref in grads[1].items():
         g = grads[0][name]
         assert g is not None and g.shape == g_ref.shape, name
         errs[name] = rel_l2(g, g_ref)
+        if float(g_ref.double().norm()) > 0:
+            cos = float((g.double() * g_ref.double()).sum() / (g.double().norm() * g_ref.double().norm()).clamp_min(1e-30))
+            assert cos > COS_FLOOR, (name, cos)
     worst = max(errs, key=errs.get)
     print(f"worst gradient rel-L2 {errs[worst]:.3e} ({worst})")
     bad = {n: f"{e:.3e}" for n, e in errs.items() if not e < tol}

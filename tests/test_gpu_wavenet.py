@@ -185,6 +185,21 @@ def test_variance_wrappers_match_reference_golden():
     assert y.shape == d["y"].shape and rel_l2(y.cpu(), d["y"]) < MEL_TOL
 
 
+def test_ancestral_sampler_in_blocks_matches_reference_golden(monkeypatch):
+    """ddpm.py:346-349 run as blocks of ANCESTRAL_BLOCK steps (here 5: the 12-step golden chain becomes 5 + 5 + 2)."""
+    d, sd, cfg = load_golden("ddpm_ddpm")
+    M, F, timesteps, k_step, speedup, shallow = [int(v) for v in d["meta"]]
+    ds.hparams.clear()
+    ds.hparams.update(hidden_size=cfg["hidden"], schedule_type="linear", use_shallow_diffusion=True, diff_accelerator="ddpm",
+                      diff_speedup=1, K_step=k_step, K_step_infer=k_step, timesteps=timesteps)
+    m = _diffusion(ds.GaussianDiffusion, sd, cfg, out_dims=M, num_feats=F, timesteps=timesteps, k_step=k_step,
+                   spec_min=[-12.0], spec_max=[0.0])
+    monkeypatch.setattr(ds.GaussianDiffusion, "ANCESTRAL_BLOCK", 5)
+    y = _with_noise([d["noise"]] + list(d["step_noise"]), lambda: m(d["cond"].to(dev), src_spec=d["src"].to(dev), infer=True))
+    assert rel_l2(y.cpu(), d["y"]) < MEL_TOL
+    assert sorted(k[1:] for k in m._programs) == [(2, 0), (7, 2), (12, 7)]
+
+
 def test_graph_replay_is_deterministic_and_counts_launches():
     d, sd, cfg = load_golden("reflow_euler")
     ds.hparams.clear()

@@ -81,3 +81,22 @@ def test_lower_order_final_small_k():
         prog = programs.dpm_solver_pp_program(sch.betas, K)
         y = run_program_cpu(model, prog, tm(d["noise"]), cond, 1)
         assert rel_l2(y, tm(ref)) < TOL
+
+
+def test_ancestral_chain_in_blocks():
+    """The ancestral sampler runs block by block (GaussianDiffusion.ANCESTRAL_BLOCK steps per program, so that only one block of
+    per-step noise is alive at a time): chaining the block programs reproduces the reference's 12-step golden run."""
+    d, sd, cfg = load_golden("ddpm_ddpm")
+    M, F, timesteps, k_step, speedup, shallow = [int(v) for v in d["meta"]]
+    sch = so.Schedule(so.linear_betas(timesteps))
+    model = OracleWaveNet(sd, cfg["n_feats"], cfg["dilation_cycle_length"])
+    src = (d["src"] - SPEC_MIN) / (SPEC_MAX - SPEC_MIN) * 2 - 1
+    x = tm(so.q_sample(sch, src.transpose(-2, -1)[:, None], k_step - 1, d["noise"]))
+    noise = [tm(n) for n in d["step_noise"]]
+    for hi in range(k_step, 0, -5):
+        lo = max(hi - 5, 0)
+        prog = programs.ddpm_program(sch, hi, lo)
+        assert prog.n_bufs == 2 + hi - lo and prog.nfe == hi - lo
+        x = run_program_cpu(model, prog, x, d["cond"].transpose(1, 2), F, noise[k_step - hi:k_step - lo])
+    assert rel_l2(denorm(x), d["y"]) < TOL
+    assert model.calls == k_step
