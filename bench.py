@@ -288,7 +288,7 @@ def extra_corners(model, dev, c):
 def extra_config1(ds, dev, random_state_dict, threads):
     """BASELINE configs[0] on its REAL inputs: the 30 segments of samples/00_*.ds through the reference's own front end and encoder
     (oracle/_ref: preprocess_input -> FastSpeech2Acoustic -> condition), then DDIM-20 over WaveNet 20 x 256, batch 1 per segment
-    like inference/ds_acoustic.py:234-244.  GPU: segment by segment and 8 segments in flight (diffsinger_b200.sample_segments).
+    like inference/ds_acoustic.py:234-244.  GPU: segment by segment and several segments in flight (diffsinger_b200.sample_segments).
     CPU arm: the reference's own `model.diffusion(cond, infer=True)` on the first segments (bounded to ~10 s); those segments
     also give a final-mel parity figure on real inputs."""
     from oracle.ref_harness import reference_available
@@ -315,10 +315,13 @@ def extra_config1(ds, dev, random_state_dict, threads):
             m(cd, infer=True)
         torch.cuda.synchronize()
         seq_ms = (time.perf_counter() - t0) * 1e3
-        ds.sample_segments(m, dconds, n_streams=8)
+        from diffsinger_b200 import _native as nat
+        cap = int(nat.lib().ds_plan_stack_capacity(m.denoise_fn.engine().plan))
+        n_streams = 6  # with ~36 tile clusters resident at once, six streams can each keep a <= 6-tile (768-frame) segment in flight
+        ds.sample_segments(m, dconds, n_streams=n_streams)
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        ds.sample_segments(m, dconds, n_streams=8)
+        ds.sample_segments(m, dconds, n_streams=n_streams)
         torch.cuda.synchronize()
         par_ms = (time.perf_counter() - t0) * 1e3
     # CPU arm + parity on the same noise
@@ -340,7 +343,8 @@ def extra_config1(ds, dev, random_state_dict, threads):
     return {"workload": "samples/00 .ds: 30 segments (286-1917 frames, 18289 total), reference encoder -> cond, GaussianDiffusion+WaveNet "
                         "20x256, DDIM 20 steps, batch 1 per segment (configs[0])",
             "gpu_sequential_ms": round(seq_ms, 1), "gpu_sequential_frames_per_s": round(frames / (seq_ms * 1e-3), 1),
-            "gpu_8_streams_ms": round(par_ms, 1), "gpu_8_streams_frames_per_s": round(frames / (par_ms * 1e-3), 1),
+            "gpu_streams": n_streams, "stack_capacity_tiles": cap,
+            "gpu_streams_ms": round(par_ms, 1), "gpu_streams_frames_per_s": round(frames / (par_ms * 1e-3), 1),
             "cpu_reference_frames_per_s": round(cpu_frames / cpu_s, 1), "cpu_reference_segments": len(errs), "cpu_cores": threads,
             "final_mel_rel_l2_vs_reference": [round(e, 6) for e in errs]}
 

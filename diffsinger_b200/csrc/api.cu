@@ -1044,6 +1044,12 @@ extern "C" int ds_session_run(ds_session* s, const ds_op* ops, int32_t n_ops, fl
 }
 
 extern "C" int64_t ds_session_last_launches(const ds_session* s) { return s ? s->last_launches : 0; }
+extern "C" int ds_plan_stack_capacity(const ds_plan* plan) {
+  if (!plan || !plan->stack_ok) return 0;
+  const char* se = getenv("DSB200_STACK");
+  if (se && atoi(se) == 0) return 0;
+  return stack_max_clusters(plan->stack_kb);
+}
 extern "C" int ds_session_path(const ds_session* s) {
   if (!s) return fail(DS_ERR_INVALID, "null session");
   return s->stack ? 3 : (s->small ? 1 : (s->medium ? 2 : 0));

@@ -29,15 +29,34 @@ def sample_segments(diffusion, conditions: Sequence[torch.Tensor], n_streams: in
     if pool is None or len(pool) < n_streams or pool[0].device != dev:
         pool = diffusion._segment_streams = [torch.cuda.Stream(device=dev) for _ in range(n_streams)]
     backbone = getattr(diffusion, 'denoise_fn', None) or getattr(diffusion, 'velocity_fn')
-    backbone.engine()  # weights are packed once, on the current stream, before any side stream starts
+    eng = backbone.engine()  # weights are packed once, on the current stream, before any side stream starts
+    # Segments on the whole-network kernel (one cluster per 128-frame tile; neighbouring tiles wait for each other's edge frames)
+    # need all their clusters resident at once, so the tiles in flight over all streams stay within the device's capacity:
+    # a segment with more than capacity / n_streams tiles runs alone (the streams meet before and after it), the others share.
+    cap = 0
+    if hasattr(eng, 'plan'):
+        from . import _native as nat
+        cap = int(nat.lib().ds_plan_stack_capacity(eng.plan))
+    share = cap // n_streams if cap else 0
     outs: List[torch.Tensor] = []
     for st in pool[:n_streams]:
         st.wait_stream(main)
+    k = 0
     for i, cond in enumerate(conditions):
-        st = pool[i % n_streams]
-        kw = {k: (v[i] if isinstance(v, (list, tuple)) else v) for k, v in forward_kwargs.items()}
+        tiles = cond.shape[0] * -(-cond.shape[1] // 128)
+        alone = bool(cap) and 1 < tiles <= cap and tiles > share
+        st = pool[0] if alone else pool[k % n_streams]
+        if alone:
+            for other in pool[1:n_streams]:
+                st.wait_stream(other)
+        else:
+            k += 1
+        kw = {k_: (v[i] if isinstance(v, (list, tuple)) else v) for k_, v in forward_kwargs.items()}
         with torch.cuda.stream(st):
             y = diffusion(cond, infer=True, **kw)
+        if alone:
+            for other in pool[1:n_streams]:
+                other.wait_stream(st)
         for t in (y if isinstance(y, (list, tuple)) else [y]):
             t.record_stream(main)
         outs.append(y)

@@ -124,6 +124,12 @@ int64_t ds_session_last_launches(const ds_session* s);
  * tiles (between the two), 3 = the whole network in ONE launch per evaluation (csrc/stack_kernel.cuh: launch-bound sessions of a
  * few 128-frame tiles at C = 256, e.g. batch-1 .ds segments and the variance predictors); negative on a null session. */
 int ds_session_path(const ds_session* s);
+/* Sessions of this plan with at most this many 128-frame tiles (B * ceil(T / 128)) run on the whole-network kernel (path 3); 0 when
+ * the plan cannot (C not 192 / 256, dilations > 16, ...) or DSB200_STACK=0.  It is also the number of tile clusters the device can
+ * hold at once: neighbouring tiles of an utterance wait for each other's edge frames, so all clusters of a launch must be resident,
+ * and callers that run several such sessions CONCURRENTLY (different streams) should keep the tiles in flight below this number
+ * (diffsinger_b200.sample_segments does).  No counterpart in the reference (it launches ~240 library kernels per evaluation). */
+int ds_plan_stack_capacity(const ds_plan* plan);
 
 /* ---- no-allocation entry point.  NO COUNTERPART IN THE REFERENCE: added for callers that
  * cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
