@@ -287,7 +287,8 @@ def extra_corners(model, dev, c):
 
 def extra_config1(ds, dev, random_state_dict, threads):
     """BASELINE configs[0] on its REAL inputs: the 30 segments of samples/00_*.ds through the reference's own front end and encoder
-    (oracle/_ref: preprocess_input -> FastSpeech2Acoustic -> condition), then DDIM-20 over WaveNet 20 x 256, batch 1 per segment
+    (oracle/_ref: preprocess_input -> tokens / mel2ph / f0), this package's condition producer (FastSpeech2Acoustic with the
+    reference encoder's weights) on the GPU, then DDIM-20 over WaveNet 20 x 256, batch 1 per segment
     like inference/ds_acoustic.py:234-244.  GPU: segment by segment and several segments in flight (diffsinger_b200.sample_segments).
     CPU arm: the reference's own `model.diffusion(cond, infer=True)` on the first segments (bounded to ~10 s); those segments
     also give a final-mel parity figure on real inputs."""
@@ -296,8 +297,10 @@ def extra_config1(ds, dev, random_state_dict, threads):
         return {"unavailable": "oracle/_ref missing (run __graft_entry__.build() where /root/reference exists)"}
     from oracle import ref_runner as rr
     torch.set_num_threads(threads)
-    ref_model, conds = rr.config1_model_and_conditions()
+    ref_model, conds, batches = rr.config1_model_and_conditions()
     lens = [int(cd.shape[1]) for cd in conds]
+    from oracle.ref_harness import load_reference
+    ref_model_hparams = dict(load_reference().hparams)
     ds.hparams.clear()
     ds.hparams.update(hidden_size=256, schedule_type="linear", use_shallow_diffusion=False, diff_accelerator="ddim", diff_speedup=50,
                       K_step=1000, K_step_infer=1000, timesteps=1000)
@@ -305,7 +308,26 @@ def extra_config1(ds, dev, random_state_dict, threads):
                              spec_min=ref_model.diffusion.spec_min.flatten().tolist(), spec_max=ref_model.diffusion.spec_max.flatten().tolist())
     m.load_state_dict(ref_model.diffusion.state_dict(), strict=True)  # the reference's checkpoint layout, unchanged
     m = m.eval().to(dev)
-    dconds = [cd.to(dev) for cd in conds]
+    # the condition producer on the GPU too: this package's FastSpeech2Acoustic with the reference encoder's checkpoint, fed the
+    # reference front end's tensors (tokens, mel2ph, f0, key shift, speed)
+    ds.hparams.update({k: ref_model_hparams[k] for k in ref_model_hparams})
+    enc = ds.FastSpeech2Acoustic(ref_model.fs2.txt_embed.weight.shape[0])
+    enc.load_state_dict(ref_model.fs2.state_dict(), strict=True)
+    enc = enc.eval().to(dev)
+    dbatches = [{k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in bt.items()} for bt in batches]
+
+    def encode(bt):
+        return enc(bt['tokens'], bt['mel2ph'], bt['f0'], key_shift=bt.get('key_shift'), speed=bt.get('speed'), languages=bt.get('languages'))
+
+    with torch.no_grad():
+        dconds = [encode(bt) for bt in dbatches]
+        enc_err = max(float((dc.cpu() - cd).norm() / cd.norm()) for dc, cd in zip(dconds, conds))
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for bt in dbatches:
+            encode(bt)
+        torch.cuda.synchronize()
+        enc_ms = (time.perf_counter() - t0) * 1e3
     with torch.no_grad():
         for cd in dconds:  # sessions + graphs per distinct length
             m(cd, infer=True)
@@ -345,6 +367,7 @@ def extra_config1(ds, dev, random_state_dict, threads):
             "gpu_sequential_ms": round(seq_ms, 1), "gpu_sequential_frames_per_s": round(frames / (seq_ms * 1e-3), 1),
             "gpu_streams": n_streams, "stack_capacity_tiles": cap,
             "gpu_streams_ms": round(par_ms, 1), "gpu_streams_frames_per_s": round(frames / (par_ms * 1e-3), 1),
+            "gpu_encoder_ms_all_segments": round(enc_ms, 2), "encoder_cond_rel_l2_vs_reference_max": round(enc_err, 6),
             "cpu_reference_frames_per_s": round(cpu_frames / cpu_s, 1), "cpu_reference_segments": len(errs), "cpu_cores": threads,
             "final_mel_rel_l2_vs_reference": [round(e, 6) for e in errs]}
 

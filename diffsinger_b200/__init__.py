@@ -6,6 +6,7 @@ from .backbones import BACKBONES, build_backbone, WaveNet, LYNXNet
 from .segments import sample_segments
 from .dropin import install_dropin
 from .sharding import sample_sharded
+from .fastspeech import FastSpeech2Acoustic
 from .aux_decoder import AUX_DECODERS, AuxDecoderAdaptor, ConvNeXtDecoder, build_aux_decoder
 from .vocoder import VOCODERS, NsfHifiGAN
 from .core import (GaussianDiffusion, PitchDiffusion, MultiVarianceDiffusion,
@@ -13,5 +14,5 @@ from .core import (GaussianDiffusion, PitchDiffusion, MultiVarianceDiffusion,
 
 __all__ = ["hparams", "get_hparams", "BACKBONES", "build_backbone", "WaveNet", "LYNXNet", "GaussianDiffusion",
            "PitchDiffusion", "MultiVarianceDiffusion", "RectifiedFlow", "PitchRectifiedFlow",
-           "MultiVarianceRectifiedFlow", "sample_segments", "install_dropin", "sample_sharded", "AUX_DECODERS", "AuxDecoderAdaptor", "ConvNeXtDecoder", "build_aux_decoder",
+           "MultiVarianceRectifiedFlow", "sample_segments", "install_dropin", "sample_sharded", "FastSpeech2Acoustic", "AUX_DECODERS", "AuxDecoderAdaptor", "ConvNeXtDecoder", "build_aux_decoder",
            "VOCODERS", "NsfHifiGAN"]

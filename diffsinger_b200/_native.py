@@ -23,7 +23,7 @@ EXPORTS = [
     "ds_plan_packed_bytes", "ds_plan_pack_weights", "ds_session_workspace_bytes", "ds_session_create",
     "ds_session_destroy", "ds_session_set_cond", "ds_session_set_times", "ds_session_forward",
     "ds_session_run", "ds_session_last_launches", "ds_session_path", "ds_plan_stack_capacity", "ds_lincomb", "ds_transpose", "ds_debug_gemm", "ds_debug_set_trace", "ds_debug_mma_rate",
-    "ds_debug_layer", "ds_static_scratch_bytes", "ds_forward_static", "ds_plan_layer_mode", "ds_plan_precision", "ds_gemm", "ds_layernorm", "ds_dwconv", "ds_cast_bf16", "ds_gate_fwd", "ds_gate_bwd", "ds_wgrad", "ds_source_conv", "ds_mean3_lrelu", "ds_conv_small",
+    "ds_debug_layer", "ds_static_scratch_bytes", "ds_forward_static", "ds_plan_layer_mode", "ds_plan_precision", "ds_gemm", "ds_layernorm", "ds_dwconv", "ds_cast_bf16", "ds_gate_fwd", "ds_gate_bwd", "ds_wgrad", "ds_source_conv", "ds_mean3_lrelu", "ds_conv_small", "ds_attention", "ds_mask_rows", "ds_length_regulate",
 ]
 
 
@@ -59,6 +59,11 @@ class WgradOperands(C.Structure):
     """ds_wgrad_operands (include/dsb200.h)."""
     _fields_ = [("g_bf16", C.c_void_p), ("x_bf16", C.c_void_p), ("g_channels", C.c_int32), ("g_batch_rows", C.c_int32),
                 ("x_channels", C.c_int32), ("x_batch_rows", C.c_int32)]
+
+
+class CurveEmbed(C.Structure):
+    """ds_curve_embed (include/dsb200.h)."""
+    _fields_ = [("value", C.c_void_p), ("stride_b", C.c_int64), ("stride_t", C.c_int64), ("weight", C.c_void_p), ("bias", C.c_void_p)]
 
 
 class GemmDesc(C.Structure):
@@ -165,6 +170,11 @@ def lib() -> C.CDLL:
     L.ds_dwconv.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                             C.c_int32, C.c_int32, C.c_void_p]
     L.ds_cast_bf16.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p]
+    L.ds_attention.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_float,
+                               C.c_void_p]
+    L.ds_mask_rows.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]
+    L.ds_length_regulate.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(CurveEmbed),
+                                     C.c_int32, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]
     L.ds_static_scratch_bytes.restype = C.c_size_t
     L.ds_static_scratch_bytes.argtypes = []
     L.ds_forward_static.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,

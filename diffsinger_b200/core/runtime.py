@@ -49,6 +49,10 @@ def run_program(backbone, prog: Program, x_tm: torch.Tensor, cond_bht: torch.Ten
     than silently emulated in PyTorch."""
     if not hasattr(backbone, 'engine'):
         raise TypeError("run_program needs a diffsinger_b200 backbone with a native engine (WaveNet, LYNXNet)")
+    if use_graph and torch.cuda.is_current_stream_capturing():
+        # the caller is capturing a bigger graph (e.g. tokens -> encoder -> sampler -> vocoder in one torch.cuda.CUDAGraph): the
+        # program's kernels are launched into THAT capture instead of replaying / capturing the session's own graph
+        use_graph = False
     eng = backbone.engine()
     if hasattr(eng, 'run_program'):  # LYNXNet: host-composed primitive ops, one torch CUDA graph per (program, B, T)
         return eng.run_program(backbone, prog, x_tm, cond_bht, extra, use_graph)

@@ -23,6 +23,7 @@
 #include "gemm_pair_kernel.cuh"
 #include "gemm_splitk_kernel.cuh"
 #include "stack_kernel.cuh"
+#include "encoder_kernels.cuh"
 
 using namespace dsb;
 
@@ -1316,6 +1317,59 @@ extern "C" int ds_mean3_lrelu(void* y_bf16, const void* a_bf16, const void* b_bf
   DS_TRY(ensure_device());
   mean3_lrelu_kernel<<<ew_grid((long)n / 8, 256), 256, 0, (cudaStream_t)stream>>>(
       (__nv_bfloat16*)y_bf16, (const __nv_bfloat16*)a_bf16, (const __nv_bfloat16*)b_bf16, (const __nv_bfloat16*)c_bf16, (long)n / 8, slope);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// ---- condition producer (FastSpeech2 acoustic encoder): the non-GEMM pieces
+extern "C" int ds_attention(void* qkv_bf16, void* out_bf16, const uint8_t* key_pad_mask, int32_t B, int32_t T, int32_t H, int32_t heads,
+                            int32_t rope, float theta, void* stream) {
+  if (!qkv_bf16 || !out_bf16 || B <= 0 || T <= 0 || H <= 0 || heads <= 0) return fail(DS_ERR_INVALID, "ds_attention: bad argument");
+  if (H % heads || (H / heads) % 32 || H / heads > 128) return fail(DS_ERR_INVALID, "ds_attention: head size %d must be 32, 64, 96 or 128", heads ? H / heads : 0);
+  if (B > 65535 || heads > 65535) return fail(DS_ERR_INVALID, "ds_attention: B / heads too large");
+  DS_TRY(ensure_device());
+  cudaStream_t st = (cudaStream_t)stream;
+  __nv_bfloat16* qkv = (__nv_bfloat16*)qkv_bf16;
+  if (rope) rope_kernel<<<ew_grid((long)B * T * H, 256), 256, 0, st>>>(qkv, B, T, H, heads, theta);
+  const dim3 grid(ceil_div(T, 8), heads, B);
+  switch (H / heads / 32) {
+    case 1: attention_kernel<1><<<grid, 256, 0, st>>>(qkv, (__nv_bfloat16*)out_bf16, key_pad_mask, T, H); break;
+    case 2: attention_kernel<2><<<grid, 256, 0, st>>>(qkv, (__nv_bfloat16*)out_bf16, key_pad_mask, T, H); break;
+    case 3: attention_kernel<3><<<grid, 256, 0, st>>>(qkv, (__nv_bfloat16*)out_bf16, key_pad_mask, T, H); break;
+    default: attention_kernel<4><<<grid, 256, 0, st>>>(qkv, (__nv_bfloat16*)out_bf16, key_pad_mask, T, H); break;
+  }
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ds_mask_rows(void* x_bf16, const uint8_t* mask, int64_t rows, int32_t channels, void* stream) {
+  if (!x_bf16 || !mask || rows <= 0 || channels <= 0 || channels % 8) return fail(DS_ERR_INVALID, "ds_mask_rows: bad argument");
+  if ((uintptr_t)x_bf16 & 15) return fail(DS_ERR_INVALID, "ds_mask_rows: x must be 16-byte aligned");
+  DS_TRY(ensure_device());
+  mask_rows_kernel<<<ew_grid((long)rows * (channels / 8), 256), 256, 0, (cudaStream_t)stream>>>((__nv_bfloat16*)x_bf16, mask, (long)rows,
+                                                                                             channels / 8);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ds_length_regulate(float* cond_bth, const void* enc_bf16, const int64_t* mel2ph, int32_t B, int32_t T, int32_t T_txt, int32_t H,
+                                  const ds_curve_embed* curves, int32_t n_curves, const float* add, int64_t add_stride_b,
+                                  int64_t add_stride_t, void* stream) {
+  if (!cond_bth || !enc_bf16 || !mel2ph || B <= 0 || T <= 0 || T_txt <= 0 || H <= 0 || H % 4) return fail(DS_ERR_INVALID, "ds_length_regulate: bad argument");
+  if (n_curves < 0 || n_curves > kLrMaxCurves || (n_curves && !curves)) return fail(DS_ERR_INVALID, "ds_length_regulate: n_curves=%d outside [0, %d]", n_curves, kLrMaxCurves);
+  DS_TRY(ensure_device());
+  LrParams p;
+  memset(&p, 0, sizeof(p));
+  p.n = n_curves;
+  for (int j = 0; j < n_curves; ++j) {
+    if (!curves[j].value || !curves[j].weight || !curves[j].bias) return fail(DS_ERR_INVALID, "ds_length_regulate: curve %d has a null pointer", j);
+    if (((uintptr_t)curves[j].weight | (uintptr_t)curves[j].bias) & 15) return fail(DS_ERR_INVALID, "ds_length_regulate: curve %d weights must be 16-byte aligned", j);
+    p.c[j].v = curves[j].value; p.c[j].sb = (long)curves[j].stride_b; p.c[j].st = (long)curves[j].stride_t;
+    p.c[j].w = curves[j].weight; p.c[j].bias = curves[j].bias;
+  }
+  p.add = add; p.add_sb = (long)add_stride_b; p.add_st = (long)add_stride_t;
+  length_regulate_kernel<<<ew_grid((long)B * T * (H / 4), 256), 256, 0, (cudaStream_t)stream>>>(
+      cond_bth, (const __nv_bfloat16*)enc_bf16, (const long long*)mel2ph, B, T, T_txt, H, p);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }

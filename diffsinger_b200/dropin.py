@@ -7,6 +7,7 @@ top-level model is built.  It swaps
   * the six sampler classes where the reference binds them BY NAME at import time: ``modules.core``,
     ``modules.toplevel`` (toplevel.py:15-18) and ``modules.fastspeech.param_adaptor`` (param_adaptor.py:6; the default
     ``cls=`` of ``build_adaptor`` is re-pointed too)
+  * ``modules.toplevel.FastSpeech2Acoustic`` (the condition producer, toplevel.py:19,40-42) for rotary-embedding configurations
 and returns a callable that undoes all of it.
 """
 from __future__ import annotations
@@ -15,7 +16,7 @@ SAMPLER_CLASSES = ('GaussianDiffusion', 'PitchDiffusion', 'MultiVarianceDiffusio
                    'RectifiedFlow', 'PitchRectifiedFlow', 'MultiVarianceRectifiedFlow')
 
 
-def install_dropin(samplers: bool = True, aux_decoder: bool = True):
+def install_dropin(samplers: bool = True, aux_decoder: bool = True, encoder: bool = True):
     import diffsinger_b200 as dsb
     import modules.backbones as mb  # the reference package, must be on sys.path
     undo = []
@@ -43,6 +44,18 @@ def install_dropin(samplers: bool = True, aux_decoder: bool = True):
             for mod in (mc, mt, pa):
                 if hasattr(mod, name):
                     swap_attr(mod, name, getattr(dsb, name))
+        if encoder:
+            # the condition producer: toplevel.py:19 binds FastSpeech2Acoustic by name and calls it as FastSpeech2Acoustic(vocab_size=...).
+            # Configurations this package does not build (rel_pos / sinusoidal position embeddings) keep the reference's class.
+            ref_fs2 = mt.FastSpeech2Acoustic
+
+            def fs2_factory(vocab_size):
+                try:
+                    return dsb.FastSpeech2Acoustic(vocab_size)
+                except NotImplementedError:
+                    return ref_fs2(vocab_size)
+
+            swap_attr(mt, 'FastSpeech2Acoustic', fs2_factory)
         # build_adaptor(self, cls=MultiVarianceDiffusion) captured the class object as a default argument
         fn = pa.ParameterAdaptorModule.build_adaptor
         if fn.__defaults__:

@@ -88,6 +88,9 @@ class Session:
 
     def set_times(self, t: torch.Tensor):
         """t: fp32 device tensor [n] (shared over the batch) or [n, B] (per-sample session)."""
+        if not t.is_cuda:  # pinned staging: the copy is then legal inside a CUDA-graph capture too (it becomes a memcpy node)
+            self._t_host = t.to(dtype=torch.float32).contiguous().pin_memory()
+            t = self._t_host.to(device=self.engine.device, non_blocking=True)
         t = t.to(device=self.engine.device, dtype=torch.float32).contiguous()
         n = t.shape[0]
         assert t.numel() == n * (self.B if self.per_sample else 1)

@@ -205,6 +205,29 @@ int ds_source_conv(void* y_bf16, const float* src, const float* w, const float* 
 int ds_conv_small(const void* x_bf16, int32_t c_in, const void* w_img_bf16, int32_t c_out, const float* bias, const void* res_bf16,
                   void* out, void* out2_bf16, int32_t B, int32_t T, int32_t taps, int32_t dil, int32_t act, float slope, void* stream);
 int ds_mean3_lrelu(void* y_bf16, const void* a_bf16, const void* b_bf16, const void* c_bf16, int64_t n, float slope, void* stream);
+/* Condition producer: the FastSpeech2 acoustic encoder in front of the sampler (modules/fastspeech/
+ * acoustic_encoder.py:82-118, tts_modules.py:353-440, commons/common_layers.py:120-258).  Its Linear / Conv1d / LayerNorm calls are
+ * ds_gemm / ds_layernorm; these three are the rest:
+ *   ds_attention: multi-head self-attention over the token axis with optional rotary position embedding
+ *     (MultiheadSelfAttentionWithRoPE.forward, common_layers.py:175-213; rotary_embedding_torch.py:35-39,119,174-188).  qkv bf16
+ *     [B][T][3H] = in_proj output (q | k | v, heads contiguous; q and k are rotated IN PLACE when rope != 0), out bf16 [B][T][H] =
+ *     softmax(q k^T / sqrt(D) | key not padded) v with heads concatenated; key_pad_mask [B][T] (nonzero = padded key) or NULL.
+ *   ds_mask_rows: x[row][:] = 0 where mask[row] != 0 (`x * (1 - padding_mask)`, common_layers.py:246,253).
+ *   ds_length_regulate: cond[b][t][:] = enc[b][mel2ph[b][t] - 1][:] (zeros for mel2ph == 0) + sum_j (weight_j * value_j[b, t] + bias_j)
+ *     + add[b][t][:] -- the torch.gather length regulation plus pitch / variance / key-shift / speed embeddings (each nn.Linear(1, H))
+ *     and the speaker embedding of acoustic_encoder.py:97-116, one pass, fp32 out [B][T][H] (what GaussianDiffusion.forward takes). */
+typedef struct {
+  const float* value;          /* curve sample of (b, t) at value[b * stride_b + t * stride_t] (a stride of 0 broadcasts) */
+  int64_t stride_b, stride_t;
+  const float* weight;         /* [H], 16-byte aligned */
+  const float* bias;           /* [H], 16-byte aligned */
+} ds_curve_embed;
+int ds_attention(void* qkv_bf16, void* out_bf16, const uint8_t* key_pad_mask, int32_t B, int32_t T, int32_t H, int32_t heads, int32_t rope,
+                 float theta, void* stream);
+int ds_mask_rows(void* x_bf16, const uint8_t* mask, int64_t rows, int32_t channels, void* stream);
+int ds_length_regulate(float* cond_bth, const void* enc_bf16, const int64_t* mel2ph, int32_t B, int32_t T, int32_t T_txt, int32_t H,
+                       const ds_curve_embed* curves, int32_t n_curves, const float* add, int64_t add_stride_b, int64_t add_stride_t,
+                       void* stream);
 /* Training path (ddpm.py:212-219 / reflow.py:36-41 under autograd).  z = [gate | filter] pre-activations of
  * one residual layer (wavenet.py:40), bf16 [rows][ld_z], plain channel order:
  *   ds_gate_fwd:  y[r][c] = sigmoid(z[r][c]) * tanh(z[r][channels + c])                                       (wavenet.py:41-42)

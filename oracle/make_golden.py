@@ -353,10 +353,53 @@ def gen_extra(ref):
             arrs["src"] = src.numpy()
         _save("ddpm_" + name, **arrs)
 
+FS2_HP = dict(hidden_size=64, enc_layers=2, num_heads=2, enc_ffn_kernel_size=3, ffn_act="gelu", dropout=0.1, use_pos_embed=True,
+              use_rope=True, rel_pos=True, use_lang_id=False, use_spk_id=True, num_spk=3)
+
+
+def gen_fs2(ref):
+    """The condition producer: FastSpeech2Acoustic (modules/fastspeech/acoustic_encoder.py:14-118) with the rotary-embedding encoder of
+    configs/acoustic.yaml at a small width; padded tokens and frames in the batch, every optional per-frame embedding in (a) and
+    none of them in (b)."""
+    from modules.fastspeech.acoustic_encoder import FastSpeech2Acoustic
+    for tag, extra in (("a", dict(use_energy_embed=True, use_breathiness_embed=True, use_key_shift_embed=True, use_speed_embed=True)),
+                       ("b", dict(use_energy_embed=False, use_breathiness_embed=False, use_key_shift_embed=False, use_speed_embed=False,
+                                  use_spk_id=False))):
+        set_reference_hparams(**dict(FS2_HP, **extra))
+        torch.manual_seed(600 + len(tag) + (tag == "b"))
+        m = FastSpeech2Acoustic(17).eval()
+        with torch.no_grad():
+            for k, v in m.state_dict().items():  # LayerNorm affine / biases away from their (1, 0) defaults
+                if "layer_norm" in k and k.endswith("weight"):
+                    v.copy_(1.0 + 0.2 * torch.randn_like(v))
+                elif k.endswith("bias"):
+                    v.copy_(0.1 * torch.randn_like(v))
+        B, Tt, T = 2, 11, 57
+        tok = torch.randint(1, 17, (B, Tt))
+        tok[1, 8:] = 0
+        n_real = [Tt, 8]
+        mel2ph = torch.zeros(B, T, dtype=torch.long)
+        for b, (n, frames) in enumerate(zip(n_real, (T, 44))):
+            mel2ph[b, :frames] = torch.sort(torch.randint(1, n + 1, (frames,))).values
+        f0 = torch.rand(B, T) * 300 + 80
+        kw = {}
+        if extra["use_energy_embed"]:
+            kw.update(energy=torch.randn(B, T) * 10 - 40, breathiness=torch.randn(B, T) * 10 - 50, key_shift=torch.randn(B, 1) * 3,
+                      speed=torch.rand(B, T) + 0.5)
+        if extra.get("use_spk_id", True):
+            kw.update(spk_embed_id=torch.tensor([2, 0]))
+        with torch.no_grad():
+            y = m(tok, mel2ph, f0, **kw)
+        _save(f"fs2_{tag}", tokens=tok.numpy(), mel2ph=mel2ph.numpy(), f0=f0.numpy(), y=y.numpy(),
+              hp_json=np.array(__import__("json").dumps(dict(FS2_HP, **extra))),
+              **{"in." + k: v.numpy() for k, v in kw.items()}, **{"w." + k: v.numpy() for k, v in m.state_dict().items()})
+
 
 def main():
     ref = load_reference()
     only = os.environ.get("GOLDEN_ONLY", "")
+    if not only or "fs2" in only:
+        gen_fs2(ref)
     if not only or "extra" in only:
         gen_extra(ref)
     if not only or "nsf" in only:

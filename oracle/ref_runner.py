@@ -71,7 +71,7 @@ CONFIG1_OVERRIDES = dict(diffusion_type="ddpm", backbone_type="wavenet",
 def config1_model_and_conditions(ds_name: str = "00_", seed: int = 0):
     """Random-init `DiffSingerAcoustic` (GaussianDiffusion + WaveNet 20 x 256, 128 mel; no checkpoint is shipped) built by the
     reference from configs/acoustic.yaml, and the conditions its own encoder produces for every segment of samples/00_*.ds.
-    Returns (model, [cond [1, T, 256] per segment])."""
+    Returns (model, [cond [1, T, 256] per segment], [the encoder's input batch per segment: tokens, mel2ph, f0, ...])."""
     import glob
     ref = load_reference()
     ref.hparams.clear()
@@ -93,7 +93,7 @@ def config1_model_and_conditions(ds_name: str = "00_", seed: int = 0):
     inf.model, inf.lr = model, LengthRegulator()
     path = sorted(glob.glob(os.path.join(REFERENCE_ROOT, "samples", ds_name + "*.ds")))[0]
     params = json.load(open(path, encoding="utf8"))
-    conds = []
+    conds, batches = [], []
     grab = model.fs2.register_forward_hook(lambda mod, a, out: conds.append(out.detach().clone()))
     stop = _StopAfterEncoder()
     model.diffusion.register_forward_pre_hook(stop)
@@ -103,6 +103,7 @@ def config1_model_and_conditions(ds_name: str = "00_", seed: int = 0):
         for i, param in enumerate(params):
             with contextlib.redirect_stdout(io.StringIO()):
                 batch = inf.preprocess_input(param, idx=i)
+            batches.append(batch)
             try:
                 with torch.no_grad():
                     inf.forward_model(batch)
@@ -111,7 +112,7 @@ def config1_model_and_conditions(ds_name: str = "00_", seed: int = 0):
     finally:
         grab.remove()
         stop.armed = False
-    return model, conds
+    return model, conds, batches
 
 
 class _Stop(Exception):

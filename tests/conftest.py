@@ -64,3 +64,13 @@ def centered_rel_l2(a, b):
     """rel-L2 of a - b against the VARIATION of b (outputs that sit on a large constant would flatter a plain rel-L2)."""
     a, b = a.double(), b.double()
     return float((a - b).norm() / (b - b.mean()).norm().clamp_min(1e-30))
+
+
+def load_fs2_golden(tag):
+    """-> (inputs dict, reference output, state_dict, hparams dict) for a tests/golden/fs2_*.npz fixture."""
+    import json
+    z = np.load(os.path.join(GOLDEN, f"fs2_{tag}.npz"))
+    d = {k: torch.from_numpy(z[k]) for k in ("tokens", "mel2ph", "f0")}
+    d.update({k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("in.")})
+    sd = {k[2:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("w.")}
+    return d, torch.from_numpy(z["y"]), sd, json.loads(str(z["hp_json"]))

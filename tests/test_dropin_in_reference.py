@@ -16,6 +16,7 @@ CASES = {
     "acoustic_default_lynxnet": ("acoustic.yaml", {}),
     "acoustic_reflow_wavenet_shallow": ("acoustic.yaml", dict(WAVENET)),
     "acoustic_ddpm_wavenet": ("acoustic.yaml", dict(WAVENET, diffusion_type="ddpm", use_shallow_diffusion=False, K_step=1000)),
+    "acoustic_rel_pos_encoder": ("acoustic.yaml", dict(WAVENET, use_rope=False)),  # encoder configuration this package does not build
     "acoustic_ddpm_wavenet_shallow": ("acoustic.yaml", dict(WAVENET, diffusion_type="ddpm", K_step=400, K_step_infer=400)),
     # variance.yaml defaults: reflow, pitch WaveNet 20x256 cycle 5 + multi-variance WaveNet 10x192
     "variance_reflow": ("variance.yaml", dict(predict_energy=True, predict_breathiness=True)),
@@ -62,6 +63,9 @@ def test_reference_toplevel_models_build_on_the_dropin(case):
     assert len(_samplers(ours)) == len(_samplers(stock)) >= 1
     if getattr(stock, "use_shallow_diffusion", False):
         assert type(ours.aux_decoder.decoder).__module__.startswith("diffsinger_b200")
+    if cfg_name.startswith("acoustic"):  # the condition producer (configs/acoustic.yaml: use_rope true)
+        want = "diffsinger_b200.fastspeech" if ref.hparams.get("use_rope") else "modules.fastspeech.acoustic_encoder"
+        assert type(ours.fs2).__module__ == want and type(stock.fs2).__module__.startswith("modules.")
     # ... and after uninstall the stock classes are back
     again = _build(ref, cfg_name, over)
     assert type(_samplers(again)[0]).__module__.startswith("modules.core")
