@@ -7,8 +7,6 @@ Program (core/programs.py) and runs it through the native session (one CUDA grap
 """
 from __future__ import annotations
 
-from typing import List, Tuple
-
 import numpy as np
 import torch
 from torch import nn
@@ -16,6 +14,7 @@ from torch import nn
 from ..backbones import build_backbone
 from ..hparams import get_hparams
 from . import programs
+from .curves import ClampedCurve, CurveList, RepeatBins
 from .runtime import run_program, to_time_major
 
 
@@ -203,100 +202,26 @@ class GaussianDiffusion(nn.Module):
         return (x + 1) / 2 * (self.spec_max - self.spec_min) + self.spec_min
 
 
-class RepetitiveDiffusion(GaussianDiffusion):
-    """reference ddpm.py:386-421: a scalar curve repeated over `repeat_bins`, mean over bins on the way out."""
+class RepetitiveDiffusion(RepeatBins, GaussianDiffusion):
+    """reference ddpm.py:386-421 -- core/curves.py:RepeatBins over the DDPM sampler."""
 
-    def __init__(self, vmin: float | int | list, vmax: float | int | list,
-                 repeat_bins: int, timesteps=1000, k_step=1000,
-                 backbone_type=None, backbone_args=None,
+    def __init__(self, vmin, vmax, repeat_bins, timesteps=1000, k_step=1000, backbone_type=None, backbone_args=None, betas=None):
+        super().__init__(vmin, vmax, repeat_bins, timesteps=timesteps, k_step=k_step,
+                         backbone_type=backbone_type, backbone_args=backbone_args, betas=betas)
+
+
+class PitchDiffusion(ClampedCurve, GaussianDiffusion):
+    """reference ddpm.py:424-445 -- core/curves.py:ClampedCurve over the DDPM sampler."""
+
+    def __init__(self, vmin, vmax, cmin, cmax, repeat_bins, timesteps=1000, k_step=1000, backbone_type=None, backbone_args=None,
                  betas=None):
-        assert (isinstance(vmin, (float, int)) and isinstance(vmin, (float, int))) or len(vmin) == len(vmax)
-        num_feats = 1 if isinstance(vmin, (float, int)) else len(vmin)
-        spec_min = [vmin] if num_feats == 1 else [[v] for v in vmin]
-        spec_max = [vmax] if num_feats == 1 else [[v] for v in vmax]
-        self.repeat_bins = repeat_bins
-        super().__init__(
-            out_dims=repeat_bins, num_feats=num_feats,
-            timesteps=timesteps, k_step=k_step,
-            backbone_type=backbone_type, backbone_args=backbone_args,
-            betas=betas, spec_min=spec_min, spec_max=spec_max
-        )
-
-    def norm_spec(self, x):
-        """[B, T] or [B, F, T] -> [B, T, R] or [B, F, T, R]"""
-        repeats = [1, 1, self.repeat_bins] if self.num_feats == 1 else [1, 1, 1, self.repeat_bins]
-        return super().norm_spec(x.unsqueeze(-1).repeat(repeats))
-
-    def denorm_spec(self, x):
-        """[B, T, R] or [B, F, T, R] -> [B, T] or [B, F, T]"""
-        return super().denorm_spec(x).mean(dim=-1)
+        super().__init__(vmin, vmax, cmin, cmax, repeat_bins, timesteps=timesteps, k_step=k_step,
+                         backbone_type=backbone_type, backbone_args=backbone_args, betas=betas)
 
 
-class PitchDiffusion(RepetitiveDiffusion):
-    """reference ddpm.py:424-445."""
+class MultiVarianceDiffusion(CurveList, GaussianDiffusion):
+    """reference ddpm.py:448-505 -- core/curves.py:CurveList over the DDPM sampler."""
 
-    def __init__(self, vmin: float, vmax: float,
-                 cmin: float, cmax: float, repeat_bins,
-                 timesteps=1000, k_step=1000,
-                 backbone_type=None, backbone_args=None,
-                 betas=None):
-        self.vmin = vmin  # norm min
-        self.vmax = vmax  # norm max
-        self.cmin = cmin  # clip min
-        self.cmax = cmax  # clip max
-        super().__init__(
-            vmin=vmin, vmax=vmax, repeat_bins=repeat_bins,
-            timesteps=timesteps, k_step=k_step,
-            backbone_type=backbone_type, backbone_args=backbone_args,
-            betas=betas
-        )
-
-    def norm_spec(self, x):
-        return super().norm_spec(x.clamp(min=self.cmin, max=self.cmax))
-
-    def denorm_spec(self, x):
-        return super().denorm_spec(x).clamp(min=self.cmin, max=self.cmax)
-
-
-class MultiVarianceDiffusion(RepetitiveDiffusion):
-    """reference ddpm.py:448-505."""
-
-    def __init__(
-            self, ranges: List[Tuple[float, float]],
-            clamps: List[Tuple[float | None, float | None] | None],
-            repeat_bins, timesteps=1000, k_step=1000,
-            backbone_type=None, backbone_args=None,
-            betas=None
-    ):
-        assert len(ranges) == len(clamps)
-        self.clamps = clamps
-        vmin = [r[0] for r in ranges]
-        vmax = [r[1] for r in ranges]
-        if len(vmin) == 1:
-            vmin = vmin[0]
-        if len(vmax) == 1:
-            vmax = vmax[0]
-        super().__init__(
-            vmin=vmin, vmax=vmax, repeat_bins=repeat_bins,
-            timesteps=timesteps, k_step=k_step,
-            backbone_type=backbone_type, backbone_args=backbone_args,
-            betas=betas
-        )
-
-    def clamp_spec(self, xs: list | tuple):
-        return [x if c is None else x.clamp(min=c[0], max=c[1]) for x, c in zip(xs, self.clamps)]
-
-    def norm_spec(self, xs: list | tuple):
-        """sequence of [B, T] -> [B, F, T] -> [B, F, T, R]"""
-        assert len(xs) == self.num_feats
-        xs = torch.stack(self.clamp_spec(xs), dim=1)  # [B, F, T]
-        if self.num_feats == 1:
-            xs = xs.squeeze(1)  # [B, T]
-        return super().norm_spec(xs)
-
-    def denorm_spec(self, xs):
-        """[B, T, R] or [B, F, T, R] -> sequence of [B, T]"""
-        xs = super().denorm_spec(xs)
-        xs = [xs] if self.num_feats == 1 else xs.unbind(dim=1)
-        assert len(xs) == self.num_feats
-        return self.clamp_spec(xs)
+    def __init__(self, ranges, clamps, repeat_bins, timesteps=1000, k_step=1000, backbone_type=None, backbone_args=None, betas=None):
+        super().__init__(ranges, clamps, repeat_bins, timesteps=timesteps, k_step=k_step,
+                         backbone_type=backbone_type, backbone_args=backbone_args, betas=betas)

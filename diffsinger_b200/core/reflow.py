@@ -6,14 +6,13 @@ and run by the native session.
 """
 from __future__ import annotations
 
-from typing import List, Tuple
-
 import torch
 import torch.nn as nn
 
 from ..backbones import build_backbone
 from ..hparams import get_hparams
 from . import programs
+from .curves import ClampedCurve, CurveList, RepeatBins
 from .runtime import run_program, to_time_major
 
 
@@ -113,91 +112,25 @@ class RectifiedFlow(nn.Module):
         return (x + 1) / 2 * (self.spec_max - self.spec_min) + self.spec_min
 
 
-class RepetitiveRectifiedFlow(RectifiedFlow):
-    """reference reflow.py:147-181."""
+class RepetitiveRectifiedFlow(RepeatBins, RectifiedFlow):
+    """reference reflow.py:147-181 -- core/curves.py:RepeatBins over the rectified-flow sampler."""
 
-    def __init__(self, vmin: float | int | list, vmax: float | int | list,
-                 repeat_bins: int, time_scale_factor=1000,
-                 backbone_type=None, backbone_args=None):
-        assert (isinstance(vmin, (float, int)) and isinstance(vmin, (float, int))) or len(vmin) == len(vmax)
-        num_feats = 1 if isinstance(vmin, (float, int)) else len(vmin)
-        spec_min = [vmin] if num_feats == 1 else [[v] for v in vmin]
-        spec_max = [vmax] if num_feats == 1 else [[v] for v in vmax]
-        self.repeat_bins = repeat_bins
-        super().__init__(
-            out_dims=repeat_bins, num_feats=num_feats,
-            time_scale_factor=time_scale_factor,
-            backbone_type=backbone_type, backbone_args=backbone_args,
-            spec_min=spec_min, spec_max=spec_max
-        )
-
-    def norm_spec(self, x):
-        repeats = [1, 1, self.repeat_bins] if self.num_feats == 1 else [1, 1, 1, self.repeat_bins]
-        return super().norm_spec(x.unsqueeze(-1).repeat(repeats))
-
-    def denorm_spec(self, x):
-        return super().denorm_spec(x).mean(dim=-1)
+    def __init__(self, vmin, vmax, repeat_bins, time_scale_factor=1000, backbone_type=None, backbone_args=None):
+        super().__init__(vmin, vmax, repeat_bins, time_scale_factor=time_scale_factor,
+                         backbone_type=backbone_type, backbone_args=backbone_args)
 
 
-class PitchRectifiedFlow(RepetitiveRectifiedFlow):
-    """reference reflow.py:184-203."""
+class PitchRectifiedFlow(ClampedCurve, RectifiedFlow):
+    """reference reflow.py:184-203 -- core/curves.py:ClampedCurve over the rectified-flow sampler."""
 
-    def __init__(self, vmin: float, vmax: float,
-                 cmin: float, cmax: float, repeat_bins,
-                 time_scale_factor=1000,
-                 backbone_type=None, backbone_args=None):
-        self.vmin = vmin
-        self.vmax = vmax
-        self.cmin = cmin
-        self.cmax = cmax
-        super().__init__(
-            vmin=vmin, vmax=vmax, repeat_bins=repeat_bins,
-            time_scale_factor=time_scale_factor,
-            backbone_type=backbone_type, backbone_args=backbone_args
-        )
-
-    def norm_spec(self, x):
-        return super().norm_spec(x.clamp(min=self.cmin, max=self.cmax))
-
-    def denorm_spec(self, x):
-        return super().denorm_spec(x).clamp(min=self.cmin, max=self.cmax)
+    def __init__(self, vmin, vmax, cmin, cmax, repeat_bins, time_scale_factor=1000, backbone_type=None, backbone_args=None):
+        super().__init__(vmin, vmax, cmin, cmax, repeat_bins, time_scale_factor=time_scale_factor,
+                         backbone_type=backbone_type, backbone_args=backbone_args)
 
 
-class MultiVarianceRectifiedFlow(RepetitiveRectifiedFlow):
-    """reference reflow.py:206-261."""
+class MultiVarianceRectifiedFlow(CurveList, RectifiedFlow):
+    """reference reflow.py:206-261 -- core/curves.py:CurveList over the rectified-flow sampler."""
 
-    def __init__(
-            self, ranges: List[Tuple[float, float]],
-            clamps: List[Tuple[float | None, float | None] | None],
-            repeat_bins, time_scale_factor=1000,
-            backbone_type=None, backbone_args=None
-    ):
-        assert len(ranges) == len(clamps)
-        self.clamps = clamps
-        vmin = [r[0] for r in ranges]
-        vmax = [r[1] for r in ranges]
-        if len(vmin) == 1:
-            vmin = vmin[0]
-        if len(vmax) == 1:
-            vmax = vmax[0]
-        super().__init__(
-            vmin=vmin, vmax=vmax, repeat_bins=repeat_bins,
-            time_scale_factor=time_scale_factor,
-            backbone_type=backbone_type, backbone_args=backbone_args
-        )
-
-    def clamp_spec(self, xs: list | tuple):
-        return [x if c is None else x.clamp(min=c[0], max=c[1]) for x, c in zip(xs, self.clamps)]
-
-    def norm_spec(self, xs: list | tuple):
-        assert len(xs) == self.num_feats
-        xs = torch.stack(self.clamp_spec(xs), dim=1)
-        if self.num_feats == 1:
-            xs = xs.squeeze(1)
-        return super().norm_spec(xs)
-
-    def denorm_spec(self, xs):
-        xs = super().denorm_spec(xs)
-        xs = [xs] if self.num_feats == 1 else xs.unbind(dim=1)
-        assert len(xs) == self.num_feats
-        return self.clamp_spec(xs)
+    def __init__(self, ranges, clamps, repeat_bins, time_scale_factor=1000, backbone_type=None, backbone_args=None):
+        super().__init__(ranges, clamps, repeat_bins, time_scale_factor=time_scale_factor,
+                         backbone_type=backbone_type, backbone_args=backbone_args)

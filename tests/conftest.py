@@ -24,6 +24,16 @@ def pytest_collection_modifyitems(config, items):
             item.add_marker(skip)
 
 
+@pytest.fixture(autouse=True)
+def _reference_hparams_do_not_leak():
+    """A test that imports the reference leaves `utils.hparams.hparams` filled, and diffsinger_b200.get_hparams() adopts a
+    non-empty reference dict (hparams.py) -- the NEXT test's `ds.hparams.update(...)` would then be ignored."""
+    yield
+    mod = sys.modules.get("utils.hparams")
+    if mod is not None and isinstance(getattr(mod, "hparams", None), dict):
+        mod.hparams.clear()
+
+
 def load_golden(name):
     """-> (dict of torch tensors / scalars, state_dict of the shared weight set, cfg)."""
     z = np.load(os.path.join(GOLDEN, name + ".npz"))
