@@ -498,8 +498,8 @@ struct ds_session {
   bool small = false;  // too few frame tiles to fill the SMs: unfused GEMMs with narrow N tiles (plan->has_small)
   bool medium = false; // between the two: unfused GEMMs with the plan's 256-wide tiles (session_is_medium)
   bool stack = false;  // one launch per evaluation: the whole network in one cluster kernel (session_is_stack, stack_kernel.cuh)
-  size_t o_scproj = 0, o_edges = 0, o_cnt = 0;  // stack sessions: hoisted conditioner projection, edge-frame buffer, arrival counters
-  int eval_seq = 0;    // index of the next evaluation inside the current program run (edge-counter targets)
+  size_t o_scproj = 0, o_edges = 0;  // stack sessions: hoisted conditioner projection, edge-frame packet buffer
+  int eval_seq = 0;    // index of the next evaluation inside the current program run (edge-packet flags)
 };
 
 // one CTA pair of the fused layer kernel owns a 256-frame tile and walks ALL output channels of it serially (~35 us at
@@ -592,12 +592,11 @@ static void session_layout(const ds_plan* p, int B, int T, int max_times, int pe
   // hoisted conditioner projection: f16 [L][rows][2C] (40 KB per frame at C = 512, L = 20); small sessions never use it
   s->o_cproj = 0;
   if (p->hoist && !session_is_small(p, B, T)) s->o_cproj = take(rows * L * 2 * C * 2);
-  s->o_scproj = s->o_edges = s->o_cnt = 0;
+  s->o_scproj = s->o_edges = 0;
   if (session_is_stack(p, B, T)) {
     const size_t tiles = (size_t)B * ceil_div(T, 128);
     s->o_scproj = take(rows * L * 2 * C * 2);
     s->o_edges = take(2 * tiles * 2 * p->stack_kb * kStackEdgeBytes);
-    s->o_cnt = take(tiles * 2 * sizeof(unsigned int));
   }
   s->ws_bytes = off;
 }
@@ -801,8 +800,8 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
     sp.bhead = (const float*)(pk + p->o_bhead); sp.dtab = dtab; sp.rtab = rtab;
     sp.bsk = (const float*)(pk + p->o_bsk); sp.bsp = (const float*)(pk + p->o_bsp); sp.bout = (const float*)(pk + p->o_bout);
     sp.vec_bstride = vstride;
-    sp.edges = s->ws + s->o_edges; sp.cnt = (unsigned int*)(s->ws + s->o_cnt);
-    sp.cnt_base = 2u * (unsigned)p->stack_kb * (unsigned)L * (unsigned)s->eval_seq;
+    sp.edges = s->ws + s->o_edges;
+    sp.flag_base = (unsigned)L * (unsigned)s->eval_seq;
     sp.T = T; sp.B = B; sp.tiles_t = tiles_t; sp.n_tiles = B * tiles_t;
     sp.L = L; sp.cycle = p->cfg.dilation_cycle_length; sp.C = C; sp.FM = p->FM; sp.FMp = p->FMp; sp.nout = p->nout;
     sp.inv_sqrt_L = 1.0f / sqrtf((float)L);
@@ -811,8 +810,8 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
     const int KBs = p->stack_kb;
     (void)stack_max_clusters(KBs);  // also sets the kernels' dynamic shared-memory attribute
     const bool dbg_build = sp.dbg != 0 || sp.trace != nullptr;  // role switches / timeline: the instrumented instantiation
-    if (s->eval_seq == 0 && tiles_t > 1)  // edge-arrival counters restart with every program run (targets are monotonic inside it)
-      CUDA_TRY(cudaMemsetAsync(s->ws + s->o_cnt, 0, (size_t)B * tiles_t * 2 * sizeof(unsigned int), st));
+    if (s->eval_seq == 0 && tiles_t > 1)  // edge packets restart with every program run: flags are unique only inside one
+      CUDA_TRY(cudaMemsetAsync(s->ws + s->o_edges, 0, (size_t)2 * B * tiles_t * 2 * KBs * kStackEdgeBytes, st));
     struct PdlScope {
       bool prev;
       explicit PdlScope(bool on) : prev(t_pdl) { t_pdl = on; }

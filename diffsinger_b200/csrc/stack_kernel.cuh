@@ -18,11 +18,13 @@
 //     sampler call (f16, [L][rows][2C]); the gate epilogue adds its row slice (prefetched before the accumulator wait);
 //   * weights stream through a 5-stage TMA ring that runs ahead across layer boundaries (weights do not depend on data).
 // Utterances longer than 128 frames span several clusters; neighbouring tiles exchange the 16 edge frames of x~ per layer
-// through a small global (L2-resident) buffer guarded by per-tile arrival counters -- point-to-point, no grid-wide barrier.
+// through a small global (L2-resident) buffer of self-validating packets ({data, flag} per 8 bytes, the "LL" idea of NCCL):
+// the sender's epilogue threads just store, the receiver's epilogue threads (idle while the centre taps run) poll the packets
+// and write the halo rows -- point-to-point, no fence, no counter, no grid-wide barrier.
 // All clusters of a launch must be co-resident (the host checks cudaOccupancyMaxActiveClusters).
 //
-// Warp roles (384 threads): warps 0 / 3 / 2 (lane 0) = weight TMA producers, warp1 = MMA issuer, warp2 = TMEM allocator +
-// halo receiver (lane 1), warps 4..11 = epilogue (warp & 3 = TMEM lane quadrant, (warp - 4) >> 2 = which 32 of the CTA's 64 channels).
+// Warp roles (384 threads): warps 0 / 3 / 2 = weight TMA producers, warp1 = MMA issuer (all four run converged with one elected
+// issuing lane), warp2 also allocates TMEM, warps 4..11 = epilogue + halo receive (warp & 3 = TMEM lane quadrant, (warp - 4) >> 2 = which 32 of the CTA's 64 channels).
 #pragma once
 #include <cuda.h>
 #include "gemm_kernel.cuh"
@@ -42,7 +44,7 @@ constexpr int kStackProducers = 3;            // weight-issuing threads (warp 0,
 __host__ __device__ constexpr uint32_t stack_smem_bytes(int kb) {
   return 1024u + kb * (kStackXTile + kStackZTile) + stack_stages(kb) * kStackStage + 1024u;
 }
-constexpr uint32_t kStackEdgeBytes = kStackHalo * 128u;  // one k-block of one edge: 16 rows x 128 B
+constexpr uint32_t kStackEdgeBytes = kStackHalo * 256u;  // one k-block of one edge: 16 rows x 8 chunks x 32 B (flagged packets, below)
 
 struct StackParams {
   CUtensorMap tmW1;     // gate weights, 128-row passes (plan o_w1s): dims (3C + H, L * 2C), box (64, 128)
@@ -61,9 +63,10 @@ struct StackParams {
   const float* bsp;     // [C]
   const float* bout;    // [FMr]
   int vec_bstride;
-  uint8_t* edges;       // [2 parity][tiles][2 sides][KB][16 rows][128 B]: edge frames of x~ in operand (swizzled) layout
-  unsigned int* cnt;    // [tiles][2]: arrivals per (tile, side), monotonic over the evaluations of one program run
-  unsigned int cnt_base;  // 2 KB * L * (index of this evaluation in the program): targets are cnt_base + 2 KB * (seq + 1)
+  uint8_t* edges;       // [2 parity][tiles][2 sides][KB][16 rows][8 chunks][32 B]: edge frames of x~ as FLAGGED packets: every 8
+                        // bytes = {2 bf16 channels, flag}; the receiver polls the data itself (one L2 round trip, no fence, no
+                        // counter).  Zeroed by the host at the start of every program run; flags are never 0.
+  unsigned int flag_base;  // L * (index of this evaluation in the program run): layer seq's packets carry flag_base + seq + 1
   int T, B, tiles_t, n_tiles;
   int L, cycle, C, FM, FMp, nout;
   float inv_sqrt_L;
@@ -91,10 +94,13 @@ __device__ __forceinline__ void bulk_copy_g2s(uint32_t dst_addr, const void* src
                : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
-__device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
-  unsigned int v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+__device__ __forceinline__ uint4 ld_volatile_v4(const void* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
   return v;
+}
+__device__ __forceinline__ void st_volatile_v4(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }  // the 8 epilogue warps
 __device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
@@ -135,7 +141,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
   const bool tracing = kDbg && p.trace != nullptr && blockIdx.x == 0;
   auto mark = [&](int l, int slot) {
     if constexpr (kDbg) {
-      if (tracing && (l * 10 + slot) < p.trace_cap) p.trace[l * 10 + slot] = globaltimer_ns();
+      if (tracing && (threadIdx.x & 31) == 0 && (l * 10 + slot) < p.trace_cap) p.trace[l * 10 + slot] = globaltimer_ns();
     }
   };
   extern __shared__ uint8_t smem_raw[];
@@ -158,7 +164,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(halo_full + 1);
   constexpr uint32_t kRemBytes = (KB - 1) * kStackZTile;
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // the shuffle tells the compiler the value is warp-uniform
   const int lane = threadIdx.x & 31;
   const int r = static_cast<int>(cluster_ctarank());
   const int tile = blockIdx.x / KB;
@@ -212,52 +218,59 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
   // kStackProducers threads; each walks the whole schedule and issues the stages whose sequence number is its own.
   // Stage order of one layer (the MMA issuer consumes in the same order): the centre tap of k-blocks r, r+1, .. (no halo needed,
   // blocks in arrival order), then taps 0 and 2 of the same k-blocks, then the 1x1 blocks.
-  auto produce = [&](int me) {
+  auto produce = [&](int me, bool lead) {  // `lead`: the one lane that issues (the rest of a converged warp only follows the waits)
     int q = 0;  // stage sequence number over the whole kernel; ring slot q % kStackStages, ring pass q / kStackStages
-    auto begin = [&](uint32_t bytes, uint64_t*& bar) -> uint8_t* {
+    // one stage: wait for the slot, issue the copies, THEN arm the barrier (complete_tx may precede expect_tx: the phase cannot
+    // finish before this thread's arrival) -- the copy leaves one mbarrier operation earlier in the ring's refill round trip
+    auto stage = [&](uint32_t bytes, auto&& issue) {
       const int st = q % kStackStages;
-      const bool mine = (q % kStackProducers) == me;
-      if (mine) {
+      if ((q % kStackProducers) == me) {
         bwait(&w_empty[st], ((q / kStackStages) & 1) ^ 1);
-        if (dbg & 2) mbar_arrive(&w_full[st]);  // debug: barriers only, no bytes
-        else mbar_arrive_expect_tx(&w_full[st], bytes);
+        if (lead) {
+          if (dbg & 2) mbar_arrive(&w_full[st]);  // debug: barriers only, no bytes
+          else {
+            issue(ring + st * kStackStage, &w_full[st]);
+            mbar_arrive_expect_tx(&w_full[st], bytes);
+          }
+        }
       }
-      bar = &w_full[st];
       ++q;
-      return (mine && !(dbg & 2)) ? ring + st * kStackStage : nullptr;
     };
-    uint64_t* bar;
     for (int k = 0; k < KBh; ++k)
-      if (uint8_t* s = begin(64 * 128, bar)) tma_load_2d(&p.tmWhead, bar, s, k * 64, 64 * r);
+      stage(64 * 128, [&](uint8_t* s, uint64_t* bar) { tma_load_2d(&p.tmWhead, bar, s, k * 64, 64 * r); });
     for (int l = 0; l < L; ++l) {
       const int row1 = l * 2 * C + 128 * r;
       for (int j = 0; j < KB; ++j)
-        if (uint8_t* s = begin(128 * 128, bar)) tma_load_2d(&p.tmW1, bar, s, (KB + ((r + j) % KB)) * 64, row1);
+        stage(128 * 128, [&](uint8_t* s, uint64_t* bar) { tma_load_2d(&p.tmW1, bar, s, (KB + ((r + j) % KB)) * 64, row1); });
       for (int j = 0; j < KB; ++j)
         for (int tap = 0; tap < 3; tap += 2)
-          if (uint8_t* s = begin(128 * 128, bar)) tma_load_2d(&p.tmW1, bar, s, (tap * KB + ((r + j) % KB)) * 64, row1);
+          stage(128 * 128, [&](uint8_t* s, uint64_t* bar) { tma_load_2d(&p.tmW1, bar, s, (tap * KB + ((r + j) % KB)) * 64, row1); });
       for (int j = 0; j < KB; ++j) {
         const int kb = (r + j) % KB;
         const bool res = l + 1 < L;
-        if (uint8_t* s = begin((res ? 2u : 1u) * 64 * 128, bar)) {
+        stage((res ? 2u : 1u) * 64 * 128, [&](uint8_t* s, uint64_t* bar) {
           if (res) tma_load_2d(&p.tmW2, bar, s, kb * 64, l * C + 64 * r);
           tma_load_2d(&p.tmWsk, bar, s + 8192, l * C + kb * 64, 64 * r);
-        }
+        });
       }
     }
     for (int j = 0; j < KB; ++j)
-      if (uint8_t* s = begin(64 * 128, bar)) tma_load_2d(&p.tmWsp, bar, s, ((r + j) % KB) * 64, 64 * r);
+      stage(64 * 128, [&](uint8_t* s, uint64_t* bar) { tma_load_2d(&p.tmWsp, bar, s, ((r + j) % KB) * 64, 64 * r); });
     for (int j = 0; j < KB; ++j)
-      if (uint8_t* s = begin(p.nout * 128, bar)) tma_load_2d(&p.tmWout, bar, s, ((r + j) % KB) * 64, p.nout * r);
+      stage(p.nout * 128, [&](uint8_t* s, uint64_t* bar) { tma_load_2d(&p.tmWout, bar, s, ((r + j) % KB) * 64, p.nout * r); });
   };
 
   if (warp == 0) {
-    if (lane == 0) produce(0);
+    produce(0, elect_one());  // converged warp, one issuing lane (see the MMA issuer below)
   } else if (warp == 3) {
-    if (lane == 0) produce(1);
+    produce(1, elect_one());
   } else if (warp == 1) {
-    if (lane == 0) {
+    {
       // ------------------------------------------------------------ MMA issuer
+      // The WHOLE warp runs this role converged (waits, stage bookkeeping and descriptor arithmetic stay in uniform registers);
+      // one elected lane issues.  Running the role inside `if (lane == 0)` made ptxas wrap every tcgen05.mma / commit in a
+      // vector->uniform register "waterfall" loop (ELECT / R2UR.BROADCAST / BRA.U.ANY), ~55 cycles per MMA.
+      const bool lead = elect_one();
       // ONE thread on purpose.  Two issuers on alternating stages were tried (results stayed correct, but no faster -- the weight
       // ring's refill round trip, not the issuer, bounds a stage -- and the accumulation order, hence the low bits, varied from
       // run to run).
@@ -269,20 +282,28 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
       const uint64_t d0 = make_kmajor_sw128_desc(0);
       const uint64_t dx = d0 + (smem_u32(xs) >> 4), dz = d0 + (smem_u32(zs) >> 4), dw = d0 + (smem_u32(ring) >> 4);
       constexpr uint32_t kXT = kStackXTile >> 4, kZT = kStackZTile >> 4, kST = kStackStage >> 4;
+      // The wait on a stage's barrier is PROBED one stage early (test_wait issued before the previous stage's MMAs): the probe's
+      // result latency (~285 cycles) then overlaps the MMA issue instead of adding to every stage.
+      uint32_t pre = mbar_test_wait(&w_full[0], 0) ? 1u : 0u;
       auto w_wait = [&]() -> uint64_t {  // no tcgen05.fence here: TMA wrote the bytes, the tensor core reads them (async proxy both)
-        bwait(&w_full[st], ph);
+        if (!pre) bwait(&w_full[st], ph);
+        const int ns = st + 1 == kStackStages ? 0 : st + 1;
+        pre = mbar_test_wait(&w_full[ns], ns == 0 ? ph ^ 1 : ph) ? 1u : 0u;
         return dw + static_cast<uint32_t>(st) * kST;
       };
       auto w_release = [&]() {
-        umma_commit(&w_empty[st]);
+        if (lead) umma_commit(&w_empty[st]);
         if (++st == kStackStages) { st = 0; ph ^= 1; }
       };
       auto mma4 = [&](uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, bool fresh) {
         if (dbg & 4) return;  // debug: commits only
+        if (lead) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (!fresh) || k != 0);
+          for (int k = 0; k < 4; ++k) umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (!fresh) || k != 0);
+        }
       };
       auto rearm = [&](uint64_t* bar) {
+        if (!lead) return;
         if (dbg & 8) mbar_arrive(bar);
         else mbar_arrive_expect_tx(bar, kRemBytes);
       };
@@ -294,7 +315,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
         mma4(tm_acc2, dz + k * kZT, db, id64, k == 0);
         w_release();
       }
-      umma_commit(acc2_full);
+      if (lead) umma_commit(acc2_full);
       for (int l = 0; l < L; ++l) {
         const uint32_t lp = l & 1;
         const int dil = 1 << (l % p.cycle);
@@ -324,7 +345,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
             w_release();
           }
         }
-        umma_commit(acc1_full);
+        if (lead) umma_commit(acc1_full);
         // GEMM-2: residual half (fresh accumulator) and skip half (accumulates over all layers)  wavenet.py:44-48,96
         for (int j = 0; j < KB; ++j) {
           if (j == 0) {
@@ -343,7 +364,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
           mma4(tm_skip, da, db + (8192 >> 4), id64, l == 0 && j == 0);
           w_release();
         }
-        umma_commit(acc2_full);
+        if (lead) umma_commit(acc2_full);
       }
       // relu(skip_projection(sum / sqrt(L))): s1 travels in the x~ buffer (free since the last GEMM-1; the z buffer may still
       // be read by a slower peer's last GEMM-2)                                                  wavenet.py:96-98
@@ -354,7 +375,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
         mma4(tm_acc2, dx + ((r + j) % KB) * kXT + kStackHalo * 8, db, id64, j == 0);
         w_release();
       }
-      umma_commit(acc2_full);
+      if (lead) umma_commit(acc2_full);
       // output_projection: s2 travels in the z buffer                                            wavenet.py:99
       for (int j = 0; j < KB; ++j) {
         if (j == 0) { bwait(z_loc, L & 1); tc_fence_after(); }
@@ -363,37 +384,10 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
         mma4(tm_acc1, dz + ((r + j) % KB) * kZT, db, idout, j == 0);
         w_release();
       }
-      umma_commit(acc1_full);
+      if (lead) umma_commit(acc1_full);
     }
   } else if (warp == 2) {
-    // -------------------------------------------------------------- third producer (lane 0) and halo receiver (lane 1)
-    if (lane == 0) produce(2);
-    if (lane == 1 && has_nb) {
-      grid_dep_wait();
-      const uint32_t bytes = (has_left ? 1u : 0u) * KB * kStackEdgeBytes + (has_right ? 1u : 0u) * KB * kStackEdgeBytes;
-      for (int seq = 0; seq < L; ++seq) {
-        if (seq > 0) bwait(acc1_full, (seq - 1) & 1);  // GEMM-1 of the previous layer has finished reading the halo rows
-        const unsigned int target = p.cnt_base + 2u * KB * (seq + 1);  // two epilogue warps per CTA arrive per edge
-        uint32_t spins = 0;
-        if (has_left)
-          while (ld_acquire_gpu(&p.cnt[(tile - 1) * 2 + 1]) < target)
-            if (++spins > (1u << 24)) __trap();
-        if (has_right)
-          while (ld_acquire_gpu(&p.cnt[(tile + 1) * 2 + 0]) < target)
-            if (++spins > (1u << 24)) __trap();
-        fence_proxy_async_all();  // the edges were written through the generic proxy; the bulk copies read them through the async proxy
-        mbar_arrive_expect_tx(halo_full, bytes);
-        const uint8_t* eb = p.edges + static_cast<size_t>(seq & 1) * p.n_tiles * 2 * KB * kStackEdgeBytes;
-        for (int kb = 0; kb < KB; ++kb) {
-          if (has_left)   // the left tile's LAST 16 frames -> rows [0, 16)
-            bulk_copy_g2s(smem_u32(xs) + kb * kStackXTile, eb + (static_cast<size_t>((tile - 1) * 2 + 1) * KB + kb) * kStackEdgeBytes,
-                          kStackEdgeBytes, halo_full);
-          if (has_right)  // the right tile's FIRST 16 frames -> rows [144, 160)
-            bulk_copy_g2s(smem_u32(xs) + kb * kStackXTile + (128 + kStackHalo) * 128u,
-                          eb + (static_cast<size_t>((tile + 1) * 2 + 0) * KB + kb) * kStackEdgeBytes, kStackEdgeBytes, halo_full);
-        }
-      }
-    }
+    produce(2, elect_one());
   } else if (warp >= 4) {
     // -------------------------------------------------------------- epilogue
     const int quad = warp & 3;
@@ -414,25 +408,63 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
 #pragma unroll
       for (int i = 0; i < 4; ++i) st_shared_v4(tile_a + sw128_off(trow, 4 * half + i), v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
     };
-    // edge frames of x~ -> the global edge buffer (operand layout), then one arrival per warp on the tile's counter
+    // edge frames of x~ -> flagged packets in the global edge buffer: chunk j (8 channels) of row er = 32 bytes
+    //   {ch0-1, flag, ch2-3, flag | ch4-5, flag, ch6-7, flag}; every 8-byte half validates itself
     auto put_edges = [&](int seq, const uint32_t (&v)[16]) {
       if (!has_nb) return;
-      const bool top = quad == 0 && lane < kStackHalo, bot = quad == 3 && lane >= 32 - kStackHalo;
-      if ((quad == 0 && has_left) || (quad == 3 && has_right)) {
-        const int side = quad == 0 ? 0 : 1;
-        if (top || bot) {
-          const int er = top ? lane : lane - (32 - kStackHalo);  // (er & 7) == ((row + 16) & 7): same swizzle phase
-          uint8_t* dst = p.edges + ((static_cast<size_t>(seq & 1) * p.n_tiles * 2 + tile * 2 + side) * KB + r) * kStackEdgeBytes;
+      const bool top = quad == 0 && lane < kStackHalo && has_left, bot = quad == 3 && lane >= 32 - kStackHalo && has_right;
+      if (top || bot) {
+        const uint32_t flag = p.flag_base + seq + 1;
+        const int side = top ? 0 : 1;
+        const int er = top ? lane : lane - (32 - kStackHalo);
+        uint8_t* dst = p.edges + ((static_cast<size_t>(seq & 1) * p.n_tiles * 2 + tile * 2 + side) * KB + r) * kStackEdgeBytes +
+                       (er * 8 + 4 * half) * 32;
 #pragma unroll
-          for (int i = 0; i < 4; ++i)
-            *reinterpret_cast<uint4*>(dst + sw128_off(er, 4 * half + i)) = make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-        }
-        __syncwarp();
-        if (lane == 0) {
-          __threadfence();
-          atomicAdd(&p.cnt[tile * 2 + side], 1u);
+        for (int i = 0; i < 4; ++i) {
+          st_volatile_v4(dst + 32 * i, v[4 * i], flag, v[4 * i + 1], flag);
+          st_volatile_v4(dst + 32 * i + 16, v[4 * i + 2], flag, v[4 * i + 3], flag);
         }
       }
+    };
+    // halo rows of x~ for layer `seq` <- the neighbours' packets.  Runs on all 256 epilogue threads right after they published
+    // x~ (they would otherwise idle until the gate accumulator is ready); the previous layer's GEMM-1 -- the last reader of the
+    // halo rows -- finished before the epilogue got here (it waited on acc1_full).  One chunk = two 16-byte loads; all of a
+    // thread's loads are in flight together, chunks whose flags are not there yet are re-read.
+    auto get_halo = [&](int seq) {
+      if (!has_nb) return;
+      const uint32_t flag = p.flag_base + seq + 1;
+      const int te = threadIdx.x - 128;
+      constexpr int kPerSide = KB * kStackHalo * 8;          // chunks per side
+      constexpr int kMine = (2 * kPerSide + 255) / 256;      // chunks per thread over both sides
+      const uint8_t* eb = p.edges + static_cast<size_t>(seq & 1) * p.n_tiles * 2 * KB * kStackEdgeBytes;
+      const uint8_t* src[kMine];
+      uint32_t dst[kMine];
+      uint4 a[kMine], bq[kMine];
+#pragma unroll
+      for (int i = 0; i < kMine; ++i) {
+        const int c = te + 256 * i;
+        const int side = c / kPerSide, cc = c % kPerSide;    // side 0: my rows [0, 16) <- the left tile's LAST 16 frames
+        const bool on = side < 2 && (side == 0 ? has_left : has_right);
+        const int kb = cc / (kStackHalo * 8), rem = cc % (kStackHalo * 8);
+        const int nb_tile = side == 0 ? tile - 1 : tile + 1;
+        src[i] = on ? eb + (static_cast<size_t>(nb_tile * 2 + (1 - side)) * KB + kb) * kStackEdgeBytes + rem * 32 : nullptr;
+        dst[i] = smem_u32(xs) + kb * kStackXTile + sw128_off((side == 0 ? 0 : 128 + kStackHalo) + rem / 8, rem % 8);
+        if (on) { a[i] = ld_volatile_v4(src[i]); bq[i] = ld_volatile_v4(src[i] + 16); }
+      }
+#pragma unroll
+      for (int i = 0; i < kMine; ++i) {
+        if (src[i] == nullptr) continue;
+        uint32_t spins = 0;
+        while (a[i].y != flag || a[i].w != flag || bq[i].y != flag || bq[i].w != flag) {
+          if (++spins > (1u << 24)) __trap();
+          a[i] = ld_volatile_v4(src[i]);
+          bq[i] = ld_volatile_v4(src[i] + 16);
+        }
+        st_shared_v4(dst[i], a[i].x, a[i].z, bq[i].x, bq[i].z);
+      }
+      fence_proxy_async_smem();
+      epi_bar_sync();
+      if (leader_thread) mbar_arrive(halo_full);
     };
     // all-gather of this CTA's slice: local arrival + one bulk copy per peer, peers in the order they will consume
     // (the KB-1 copies are issued by lane 0 of KB-1 different warps: issuing one costs a thread ~285 cycles)
@@ -440,7 +472,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
       fence_proxy_async_smem();
       tc_fence_before();
       epi_bar_sync();
-      if (lane == 0) {
+      if (elect_one()) {
         const int j = warp - 4;  // 0 .. 7
         if (j == KB - 1) mbar_arrive(bar_loc);
         if (j < KB - 1 && !(dbg & 8)) {
@@ -488,9 +520,10 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
         const float v1 = valid ? fmaxf(__uint_as_float(a[2 * i + 1]) + bb[2 * i + 1], 0.0f) + dd[2 * i + 1] : 0.0f;
         o[i] = pack_bf16(v0, v1);
       }
-      put_row(xrow_a, row + kStackHalo, o);
       put_edges(0, o);
+      put_row(xrow_a, row + kStackHalo, o);
       publish(xrow_a, kStackHalo * 128u, x_loc, x_rem);
+      get_halo(0);
     }
 
     for (int l = 0; l < L; ++l) {
@@ -556,10 +589,11 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
             o[4 * i + h] = valid ? pack_bf16(v0, v1) : 0u;
           }
         }
+        put_edges(l + 1, o);  // first: the neighbour tile's wait for these packets is the longer path
         put_row(xrow_a, row + kStackHalo, o);
-        put_edges(l + 1, o);
         publish(xrow_a, kStackHalo * 128u, x_loc, x_rem);
         if (leader_thread) mark(l, 9);
+        get_halo(l + 1);
       }
     }
     // ---- skip sum (TMEM, all layers) -> s1 = (sum + b) / sqrt(L)                                   wavenet.py:96
