@@ -100,7 +100,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) ds_gemm_kernel(const __grid_c
   uint64_t* tmem_empty = bars + 2 * S + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 4);
 
-  const int warp = threadIdx.x >> 5;
+  // warp index through a shuffle: the compiler then knows it is warp-uniform, and the single-lane roles below can run as CONVERGED
+  // warps (waits and index arithmetic on all lanes, in uniform registers) with one elected lane issuing -- inside `if (lane == 0)`
+  // ptxas wraps every tcgen05.mma / commit / TMA issue in a vector->uniform register waterfall loop (~55 cycles per MMA)
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
   const int lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {
@@ -130,8 +133,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) ds_gemm_kernel(const __grid_c
   const int num_kb = p.n_taps * p.kb_a0 + p.kb_a1;
 
   if (warp == 0) {
-    if (lane == 0) {
+    {
       // ------------------------------------------------------------ TMA producer
+      const bool lead = elect_one();
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
@@ -145,18 +149,20 @@ __global__ void __launch_bounds__(kGemmThreads, 1) ds_gemm_kernel(const __grid_c
 #pragma unroll 1
           for (int sub = 0; sub < kSub; ++sub) {  // split: (A hi, W hi), (A lo, W hi), (A hi, W lo)
             mbar_wait(&empty[stage], phase ^ 1);
-            mbar_arrive_expect_tx(&full[stage], Cfg::kABytes + Cfg::kBBytes);
             uint8_t* sa = smem_a + stage * Cfg::kABytes;
             uint8_t* sb = smem_b + stage * Cfg::kBBytes;
-            if (kb < kb_taps) {
-              const int tap = kb / p.kb_a0;
-              const int cb = kb - tap * p.kb_a0;
-              tma_load_3d(&p.tmA0, &full[stage], sa, p.a0_c0 + cb * 64 + (sub == 1 ? p.a0_lo : 0),
-                          t0 + (tap - p.n_taps / 2) * p.dil, b);
-            } else {
-              tma_load_3d(&p.tmA1, &full[stage], sa, (kb - kb_taps) * 64 + (sub == 1 ? p.a1_lo : 0), t0, b);
+            if (lead) {
+              mbar_arrive_expect_tx(&full[stage], Cfg::kABytes + Cfg::kBBytes);
+              if (kb < kb_taps) {
+                const int tap = kb / p.kb_a0;
+                const int cb = kb - tap * p.kb_a0;
+                tma_load_3d(&p.tmA0, &full[stage], sa, p.a0_c0 + cb * 64 + (sub == 1 ? p.a0_lo : 0),
+                            t0 + (tap - p.n_taps / 2) * p.dil, b);
+              } else {
+                tma_load_3d(&p.tmA1, &full[stage], sa, (kb - kb_taps) * 64 + (sub == 1 ? p.a1_lo : 0), t0, b);
+              }
+              tma_load_2d(&p.tmB, &full[stage], sb, p.b_k0 + kb * 64 + (sub == 2 ? p.w_lo : 0), row0);
             }
-            tma_load_2d(&p.tmB, &full[stage], sb, p.b_k0 + kb * 64 + (sub == 2 ? p.w_lo : 0), row0);
             if (++stage == S) {
               stage = 0;
               phase ^= 1;
@@ -166,8 +172,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) ds_gemm_kernel(const __grid_c
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {
       // ------------------------------------------------------------ MMA issuer
+      const bool lead = elect_one();
       constexpr uint32_t idesc = make_idesc_bf16_f32(BN);
       int stage = 0;
       uint32_t phase = 0;
@@ -183,11 +190,13 @@ __global__ void __launch_bounds__(kGemmThreads, 1) ds_gemm_kernel(const __grid_c
           tc_fence_after();
           const uint64_t da = make_kmajor_sw128_desc(smem_u32(smem_a + stage * Cfg::kABytes));
           const uint64_t db = make_kmajor_sw128_desc(smem_u32(smem_b + stage * Cfg::kBBytes));
+          if (lead) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k)  // 4 x (K = 16) per 64-wide block: +32 B on the start address
-            umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
-          umma_commit(&empty[stage]);
-          if (kb == num_kb * kSub - 1) umma_commit(&tmem_full[as]);
+            for (int k = 0; k < 4; ++k)  // 4 x (K = 16) per 64-wide block: +32 B on the start address
+              umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            umma_commit(&empty[stage]);
+            if (kb == num_kb * kSub - 1) umma_commit(&tmem_full[as]);
+          }
           if (++stage == S) {
             stage = 0;
             phase ^= 1;

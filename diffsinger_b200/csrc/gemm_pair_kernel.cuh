@@ -38,7 +38,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1) ds_
   uint64_t* tmem_empty = tmem_full + 2;   // leader: 16 warp arrivals (8 per CTA)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // warp-uniform to the compiler: converged single-issuer roles (gemm_kernel.cuh)
   const int lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
   const bool leader = rank == 0;
@@ -73,8 +73,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1) ds_
   const int n_pairs = gridDim.x >> 1;
 
   if (warp == 0) {
-    if (lane == 0) {
+    {
       // ------------------------------------------------------------ TMA producer (both CTAs)
+      const bool lead = elect_one();
       int st = 0;
       uint32_t ph = 0;
       const int kb_taps = p.n_taps * p.kb_a0;
@@ -87,10 +88,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1) ds_
         for (int kb0 = 0; kb0 < num_kb; kb0 += kGpGroup) {
           const int n = num_kb - kb0 < kGpGroup ? num_kb - kb0 : kGpGroup;
           mbar_wait(&empty[st], ph ^ 1);
-          if (leader) mbar_arrive_expect_tx(&full[st], 2u * n * (kGpABytes + kPairBBytes));
-          else mbar_arrive_cluster(&full[st], 0);
+          if (lead) {
+            if (leader) mbar_arrive_expect_tx(&full[st], 2u * n * (kGpABytes + kPairBBytes));
+            else mbar_arrive_cluster(&full[st], 0);
+          }
           uint8_t* s = smem + st * kGpStageBytes;
-          for (int j = 0; j < n; ++j) {
+          for (int j = 0; j < n && lead; ++j) {
             const int kb = kb0 + j;
             if (kb < kb_taps) {
               const int tap = kb / p.kb_a0;
@@ -106,8 +109,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1) ds_
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && leader) {
+    if (leader) {
       // ------------------------------------------------------------ MMA issuer (leader CTA only)
+      const bool lead = elect_one();
       constexpr uint32_t idesc = make_idesc_bf16_f32_m(256, 256);
       int st = 0;
       uint32_t ph = 0;
@@ -122,14 +126,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1) ds_
           mbar_wait(&full[st], ph);
           tc_fence_after();
           const uint32_t s = smem_u32(smem + st * kGpStageBytes);
-          for (int j = 0; j < n; ++j) {
+          for (int j = 0; j < n && lead; ++j) {
             const uint64_t da = make_kmajor_sw128_desc(s + j * kGpABytes);
             const uint64_t db = make_kmajor_sw128_desc(s + kGpGroup * kGpABytes + j * kPairBBytes);
 #pragma unroll
             for (int k = 0; k < 4; ++k) umma_bf16_pair(tmem_d, da + 2 * k, db + 2 * k, idesc, ((kb0 + j) | k) != 0);
           }
-          umma_commit_pair(&empty[st]);
-          if (kb0 + n >= num_kb) umma_commit_pair(&tmem_full[as]);
+          if (lead) {
+            umma_commit_pair(&empty[st]);
+            if (kb0 + n >= num_kb) umma_commit_pair(&tmem_full[as]);
+          }
           if (++st == kGpStages) { st = 0; ph ^= 1; }
         }
       }

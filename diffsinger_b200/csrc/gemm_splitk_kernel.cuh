@@ -66,7 +66,7 @@ __global__ void __cluster_dims__(kSplitK, 1, 1) __launch_bounds__(kGemmThreads, 
   uint64_t* tmem_full = bars + 2 * S;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 1);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // warp-uniform to the compiler: converged single-issuer roles (gemm_kernel.cuh)
   const int lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
 
@@ -99,8 +99,9 @@ __global__ void __cluster_dims__(kSplitK, 1, 1) __launch_bounds__(kGemmThreads, 
   const int kb_begin = static_cast<int>(rank) * num_kb / kSplitK, kb_end = static_cast<int>(rank + 1) * num_kb / kSplitK;
 
   if (warp == 0) {
-    if (lane == 0) {
+    {
       // ------------------------------------------------------------ TMA producer: this CTA's K blocks
+      const bool lead = elect_one();
       int stage = 0;
       uint32_t phase = 0;
       const int t0 = tt * 128;
@@ -108,17 +109,19 @@ __global__ void __cluster_dims__(kSplitK, 1, 1) __launch_bounds__(kGemmThreads, 
       const int kb_taps = p.n_taps * p.kb_a0;
       for (int kb = kb_begin; kb < kb_end; ++kb) {
         mbar_wait(&empty[stage], phase ^ 1);
-        mbar_arrive_expect_tx(&full[stage], Cfg::kABytes + Cfg::kBBytes);
         uint8_t* sa = smem_a + stage * Cfg::kABytes;
         uint8_t* sb = smem_b + stage * Cfg::kBBytes;
-        if (kb < kb_taps) {
-          const int tap = kb / p.kb_a0;
-          const int cb = kb - tap * p.kb_a0;
-          tma_load_3d(&p.tmA0, &full[stage], sa, p.a0_c0 + cb * 64, t0 + (tap - p.n_taps / 2) * p.dil, b);
-        } else {
-          tma_load_3d(&p.tmA1, &full[stage], sa, (kb - kb_taps) * 64, t0, b);
+        if (lead) {
+          mbar_arrive_expect_tx(&full[stage], Cfg::kABytes + Cfg::kBBytes);
+          if (kb < kb_taps) {
+            const int tap = kb / p.kb_a0;
+            const int cb = kb - tap * p.kb_a0;
+            tma_load_3d(&p.tmA0, &full[stage], sa, p.a0_c0 + cb * 64, t0 + (tap - p.n_taps / 2) * p.dil, b);
+          } else {
+            tma_load_3d(&p.tmA1, &full[stage], sa, (kb - kb_taps) * 64, t0, b);
+          }
+          tma_load_2d(&p.tmB, &full[stage], sb, p.b_k0 + kb * 64, row0);
         }
-        tma_load_2d(&p.tmB, &full[stage], sb, p.b_k0 + kb * 64, row0);
         if (++stage == S) {
           stage = 0;
           phase ^= 1;
@@ -126,8 +129,9 @@ __global__ void __cluster_dims__(kSplitK, 1, 1) __launch_bounds__(kGemmThreads, 
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {
       // ------------------------------------------------------------ MMA issuer
+      const bool lead = elect_one();
       constexpr uint32_t idesc = make_idesc_bf16_f32(BN);
       int stage = 0;
       uint32_t phase = 0;
@@ -136,10 +140,12 @@ __global__ void __cluster_dims__(kSplitK, 1, 1) __launch_bounds__(kGemmThreads, 
         tc_fence_after();
         const uint64_t da = make_kmajor_sw128_desc(smem_u32(smem_a + stage * Cfg::kABytes));
         const uint64_t db = make_kmajor_sw128_desc(smem_u32(smem_b + stage * Cfg::kBBytes));
+        if (lead) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) umma_bf16(tmem_base, da + 2 * k, db + 2 * k, idesc, (kb != kb_begin || k != 0));
-        umma_commit(&empty[stage]);
-        if (kb == kb_end - 1) umma_commit(tmem_full);
+          for (int k = 0; k < 4; ++k) umma_bf16(tmem_base, da + 2 * k, db + 2 * k, idesc, (kb != kb_begin || k != 0));
+          umma_commit(&empty[stage]);
+          if (kb == kb_end - 1) umma_commit(tmem_full);
+        }
         if (++stage == S) {
           stage = 0;
           phase ^= 1;

@@ -236,7 +236,7 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(z_full + 1);
   uint8_t* warp_stage = reinterpret_cast<uint8_t*>(bars) + 2048;  // 8 x kGrpWarpStage, 2 KB aligned (stage_bytes % 2048 == 0)
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // warp-uniform to the compiler: converged single-issuer roles (gemm_kernel.cuh)
   const int lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
   const bool leader = rank == 0;
@@ -276,17 +276,21 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
   constexpr uint32_t kOne = kLayerABytes;  // 16 KB
 
   if (warp == 0) {
-    if (lane == 0) {
+    {
       // ------------------------------------------------------------ TMA producer (both CTAs)
+      const bool lead = elect_one();
+      const bool load = lead && !(p.dbg & 2);
       int st = 0;
       uint32_t ph = 0;
       auto begin_stage = [&](uint32_t bytes_per_cta) -> uint8_t* {
         mbar_wait(&empty[st], ph ^ 1);
-        if (leader) {
-          if (p.dbg & 2) mbar_arrive(&full[st]);  // debug: barriers only, no bytes
-          else mbar_arrive_expect_tx(&full[st], 2 * bytes_per_cta);
-        } else {
-          mbar_arrive_cluster(&full[st], 0);
+        if (lead) {
+          if (leader) {
+            if (p.dbg & 2) mbar_arrive(&full[st]);  // debug: barriers only, no bytes
+            else mbar_arrive_expect_tx(&full[st], 2 * bytes_per_cta);
+          } else {
+            mbar_arrive_cluster(&full[st], 0);
+          }
         }
         return smem + st * stage_bytes;
       };
@@ -296,7 +300,7 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
         for (int k = 0; k < nblk; k += 2) {
           const int n = nblk - k < 2 ? nblk - k : 2;
           uint8_t* s = begin_stage(n * (kOne + kPairBBytes));
-          for (int j = 0; j < n && !(p.dbg & 2); ++j) {
+          for (int j = 0; j < n && load; ++j) {
             tma_load_3d_pair(am, &full[st], s + j * kOne, ac0 + (k + j) * 64, t0, b);
             tma_load_2d_pair(wm, &full[st], s + 2 * kOne + j * kPairBBytes, wk0 + (k + j) * 64, row0);
           }
@@ -313,9 +317,9 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
           const int row0 = p.w1_row0 + idx * 256 + rank * 128;
           for (int cb = 0; cb < p.kb_c; ++cb) {
             uint8_t* s = begin_stage(halo_bytes + 3 * kPairBBytes);
-            if (!(p.dbg & 2)) tma_load_3d_pair(&p.tmXh, &full[st], s, cb * 64, t0 - p.dil, b);
+            if (load) tma_load_3d_pair(&p.tmXh, &full[st], s, cb * 64, t0 - p.dil, b);
 #pragma unroll
-            for (int tap = 0; tap < 3 && !(p.dbg & 2); ++tap)
+            for (int tap = 0; tap < 3 && load; ++tap)
               tma_load_2d_pair(&p.tmW1, &full[st], s + p.a_slot + tap * kPairBBytes, (tap * p.kb_c + cb) * 64, row0);
             end_stage();
           }
@@ -328,20 +332,23 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && leader) {
+    if (leader) {
       // ------------------------------------------------------------ MMA issuer (leader CTA only)
+      const bool lead = elect_one();
       constexpr uint32_t idesc = make_idesc_bf16_f32_m(256, 256);
       int st = 0;
       uint32_t ph = 0;
       uint32_t acc_it = 0;
       auto mma4 = [&](uint32_t tmem_d, uint64_t da, uint64_t db, bool fresh) {
-        if (p.dbg & 4) return;  // debug: commits only
+        if ((p.dbg & 4) || !lead) return;  // debug: commits only
 #pragma unroll
         for (int k = 0; k < 4; ++k) umma_bf16_pair(tmem_d, da + 2 * k, db + 2 * k, idesc, (!fresh) || k != 0);
       };
       auto release = [&](bool last_of_job, uint32_t as) {
-        umma_commit_pair(&empty[st]);
-        if (last_of_job) umma_commit_pair(&tmem_full[as]);
+        if (lead) {
+          umma_commit_pair(&empty[st]);
+          if (last_of_job) umma_commit_pair(&tmem_full[as]);
+        }
         if (++st == NS) { st = 0; ph ^= 1; }
       };
       auto one_by_one = [&](uint32_t tmem_d, int nblk, bool fresh_first, uint32_t as) {
