@@ -199,7 +199,7 @@ def time_layer_kernel(session, L, min_launches=2000):
 
 def measured_traffic(kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed ncu --set full capture
-    (profiles/r01_layer_grp_kernel.txt); it is a property of the kernel and shape, not re-measured by this run."""
+    (profiles/r02_layer_grp_kernel.txt); it is a property of the kernel and shape, not re-measured by this run."""
     path = os.path.join(ROOT, "profiles", "layer_kernel_traffic.json")
     try:
         return json.load(open(path)).get(kernel)
@@ -557,7 +557,7 @@ def run_native(args, rank, world, local_rank, emit):
         "clocks": clocks,
         "roofline": {"bound": "tensor", "achieved": achieved, "peak": pk["bf16"], "unit": "TFLOP/s", "frac": achieved / pk["bf16"],
                      "frac_of_sustained": achieved / pk["bf16_sustained"],
-                     "traffic": measured_traffic(LAYER_KERNELS.get(mode, "")), "traffic_source": "profiles/r01_layer_grp_kernel.txt (ncu --set full)",
+                     "traffic": measured_traffic(LAYER_KERNELS.get(mode, "")), "traffic_source": "profiles/r02_layer_grp_kernel.txt (ncu --set full)",
                      "kernel": LAYER_KERNELS.get(mode, f"layer mode {mode}"), "kernel_ms": layer_ms, "kernel_launches_timed": layer_n,
                      "kernel_window_sm_mhz": kclocks["sm_mhz"] if kclocks else None,
                      "flops_per_launch": layer_flops, "peak_source": pk["src"],
