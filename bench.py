@@ -340,12 +340,24 @@ def extra_config1(ds, dev, random_state_dict, threads):
         from diffsinger_b200 import _native as nat
         cap = int(nat.lib().ds_plan_stack_capacity(m.denoise_fn.engine().plan))
         n_streams = 6  # with ~36 tile clusters resident at once, six streams can each keep a <= 6-tile (768-frame) segment in flight
-        ds.sample_segments(m, dconds, n_streams=n_streams)
+        ds.sample_segments(m, dconds, n_streams=n_streams, ragged=False)
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        ds.sample_segments(m, dconds, n_streams=n_streams)
+        ds.sample_segments(m, dconds, n_streams=n_streams, ragged=False)
         torch.cuda.synchronize()
         par_ms = (time.perf_counter() - t0) * 1e3
+        # ragged batches: segments of different lengths padded into one [B, T_max] launch per evaluation, every utterance with its
+        # own end (ds_session_set_lengths); results are bit-identical to segment by segment (tests/test_gpu_stack.py)
+        torch.manual_seed(99)
+        one_by_one = [m(cd, infer=True) for cd in dconds]
+        torch.manual_seed(99)
+        rag = ds.sample_segments(m, dconds)
+        rag_equal = all(torch.equal(a, b) for a, b in zip(one_by_one, rag))
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        ds.sample_segments(m, dconds)
+        torch.cuda.synchronize()
+        rag_ms = (time.perf_counter() - t0) * 1e3
     # CPU arm + parity on the same noise
     cpu_frames, cpu_s, errs = 0, 0.0, []
     for i, cd in enumerate(conds):
@@ -367,6 +379,8 @@ def extra_config1(ds, dev, random_state_dict, threads):
             "gpu_sequential_ms": round(seq_ms, 1), "gpu_sequential_frames_per_s": round(frames / (seq_ms * 1e-3), 1),
             "gpu_streams": n_streams, "stack_capacity_tiles": cap,
             "gpu_streams_ms": round(par_ms, 1), "gpu_streams_frames_per_s": round(frames / (par_ms * 1e-3), 1),
+            "gpu_ragged_batches_ms": round(rag_ms, 1), "gpu_ragged_frames_per_s": round(frames / (rag_ms * 1e-3), 1),
+            "gpu_ragged_equals_one_by_one": bool(rag_equal),
             "gpu_encoder_ms_all_segments": round(enc_ms, 2), "encoder_cond_rel_l2_vs_reference_max": round(enc_err, 6),
             "cpu_reference_frames_per_s": round(cpu_frames / cpu_s, 1), "cpu_reference_segments": len(errs), "cpu_cores": threads,
             "final_mel_rel_l2_vs_reference": [round(e, 6) for e in errs]}

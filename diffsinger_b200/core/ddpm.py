@@ -157,11 +157,12 @@ class GaussianDiffusion(nn.Module):
 
         if t_max > 0 and speedup > 1:
             prog = self._program(hparams['diff_accelerator'], t_max, speedup)
-            x_tm = run_program(self.denoise_fn, prog, to_time_major(x), cond, [])
+            x_tm = run_program(self.denoise_fn, prog, to_time_major(x), cond, [], lengths=getattr(self, '_lengths_override', None))
         elif t_max > 0:
             # ancestral chain (ddpm.py:346-349), ANCESTRAL_BLOCK steps per program: the reference holds one noise tensor at a time;
             # pre-drawing all t_max of them (plus their time-major copies and the session buffers) would cost 3 * t_max * B*T*F*M*4
             # bytes.  Fresh noise per step comes from the global generator in noise_like's draw order (ddpm.py:153).
+            assert getattr(self, '_lengths_override', None) is None, 'ragged batches are not offered for the ancestral chain'
             x_tm = to_time_major(x)
             for hi in range(t_max, 0, -self.ANCESTRAL_BLOCK):
                 lo = max(hi - self.ANCESTRAL_BLOCK, 0)

@@ -100,7 +100,7 @@ class RectifiedFlow(nn.Module):
                 prog = self._programs[key] = programs.reflow_program(algorithm, infer_step, float(t_start),
                                                                      float(self.time_scale_factor))
             if infer_step > 0:
-                x_tm = run_program(self.velocity_fn, prog, x_tm, cond)
+                x_tm = run_program(self.velocity_fn, prog, x_tm, cond, lengths=getattr(self, '_lengths_override', None))
         if self.num_feats == 1:
             return x_tm
         return x_tm.reshape(b, T, self.num_feats, self.out_dims).permute(0, 2, 1, 3)

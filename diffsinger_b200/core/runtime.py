@@ -41,9 +41,11 @@ def max_chunk_batch(eng, B: int, T: int, n_bufs: int, n_times: int) -> int:
 
 @torch.no_grad()
 def run_program(backbone, prog: Program, x_tm: torch.Tensor, cond_bht: torch.Tensor,
-                extra: List[torch.Tensor] = (), use_graph: bool = True) -> torch.Tensor:
+                extra: List[torch.Tensor] = (), use_graph: bool = True, lengths=None) -> torch.Tensor:
     """Runs `prog` with buffer 0 = x_tm (time-major start state), buffers 2.. optionally preset from
     `extra`.  cond_bht is the [B, H, T] tensor the reference passes to the backbone.  Returns buffer 0.
+    lengths: optional per-utterance frame counts of a RAGGED batch (segments.sample_segments); frames beyond them are zero
+    padding for the convolutions and their outputs are undefined -- needs a session on the whole-network kernel.
 
     The backbone must be one of this package's native backbones (WaveNet, LYNXNet); anything else is rejected rather
     than silently emulated in PyTorch."""
@@ -55,11 +57,13 @@ def run_program(backbone, prog: Program, x_tm: torch.Tensor, cond_bht: torch.Ten
         use_graph = False
     eng = backbone.engine()
     if hasattr(eng, 'run_program'):  # LYNXNet: host-composed primitive ops, one torch CUDA graph per (program, B, T)
+        if lengths is not None:
+            raise nat.NativeError("ragged batches (lengths=...) are only supported by the WaveNet whole-network kernel")
         return eng.run_program(backbone, prog, x_tm, cond_bht, extra, use_graph)
     B, T, FM = x_tm.shape
     bc = max_chunk_batch(eng, B, T, prog.n_bufs, len(prog.times))
-    if bc >= B:
-        return _run_chunk(eng, prog, x_tm, cond_bht, extra, use_graph).clone()
+    if bc >= B or lengths is not None:
+        return _run_chunk(eng, prog, x_tm, cond_bht, extra, use_graph, lengths).clone()
     out = torch.empty_like(x_tm)
     for lo in range(0, B, bc):
         hi = min(B, lo + bc)
@@ -67,9 +71,10 @@ def run_program(backbone, prog: Program, x_tm: torch.Tensor, cond_bht: torch.Ten
     return out
 
 
-def _run_chunk(eng, prog: Program, x_tm, cond_bht, extra, use_graph) -> torch.Tensor:
+def _run_chunk(eng, prog: Program, x_tm, cond_bht, extra, use_graph, lengths=None) -> torch.Tensor:
     B, T, FM = x_tm.shape
     sess = eng.session(B, T, max_times=len(prog.times), per_sample=False)
+    sess.set_lengths(lengths)  # None restores a full-length batch on a session that ran ragged before
     bufs = sess_buffers(sess, prog.n_bufs)
     bufs[0].copy_(x_tm)
     for k, e in enumerate(extra):

@@ -498,7 +498,9 @@ struct ds_session {
   bool small = false;  // too few frame tiles to fill the SMs: unfused GEMMs with narrow N tiles (plan->has_small)
   bool medium = false; // between the two: unfused GEMMs with the plan's 256-wide tiles (session_is_medium)
   bool stack = false;  // one launch per evaluation: the whole network in one cluster kernel (session_is_stack, stack_kernel.cuh)
-  size_t o_scproj = 0, o_edges = 0;  // stack sessions: hoisted conditioner projection, edge-frame packet buffer
+  size_t o_scproj = 0, o_edges = 0, o_len = 0;  // stack sessions: hoisted conditioner projection, edge-frame packet buffer, lengths
+  bool has_len = false;  // ds_session_set_lengths: per-utterance frame counts in ws + o_len
+  std::vector<int32_t> len_host;
   int eval_seq = 0;    // index of the next evaluation inside the current program run (edge-packet flags)
 };
 
@@ -592,11 +594,12 @@ static void session_layout(const ds_plan* p, int B, int T, int max_times, int pe
   // hoisted conditioner projection: f16 [L][rows][2C] (40 KB per frame at C = 512, L = 20); small sessions never use it
   s->o_cproj = 0;
   if (p->hoist && !session_is_small(p, B, T)) s->o_cproj = take(rows * L * 2 * C * 2);
-  s->o_scproj = s->o_edges = 0;
+  s->o_scproj = s->o_edges = s->o_len = 0;
   if (session_is_stack(p, B, T)) {
     const size_t tiles = (size_t)B * ceil_div(T, 128);
     s->o_scproj = take(rows * L * 2 * C * 2);
     s->o_edges = take(2 * tiles * 2 * p->stack_kb * kStackEdgeBytes);
+    s->o_len = take((size_t)B * sizeof(int32_t));
   }
   s->ws_bytes = off;
 }
@@ -801,6 +804,7 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
     sp.bsk = (const float*)(pk + p->o_bsk); sp.bsp = (const float*)(pk + p->o_bsp); sp.bout = (const float*)(pk + p->o_bout);
     sp.vec_bstride = vstride;
     sp.edges = s->ws + s->o_edges;
+    sp.len = s->has_len ? (const int*)(s->ws + s->o_len) : nullptr;
     sp.flag_base = (unsigned)L * (unsigned)s->eval_seq;
     sp.T = T; sp.B = B; sp.tiles_t = tiles_t; sp.n_tiles = B * tiles_t;
     sp.L = L; sp.cycle = p->cfg.dilation_cycle_length; sp.C = C; sp.FM = p->FM; sp.FMp = p->FMp; sp.nout = p->nout;
@@ -1009,6 +1013,7 @@ extern "C" int ds_session_run(ds_session* s, const ds_op* ops, int32_t n_ops, fl
   }
   std::string key((const char*)ops, sizeof(ds_op) * n_ops);
   key.append((const char*)bufs, sizeof(float*) * n_bufs);
+  key.push_back(s->has_len ? 'r' : 'f');  // ragged launches carry the lengths pointer in their kernel parameters
   auto it = s->graphs.find(key);
   if (it == s->graphs.end()) {
     if (!s->cap_stream) CUDA_TRY(cudaStreamCreateWithFlags(&s->cap_stream, cudaStreamNonBlocking));
@@ -1049,6 +1054,25 @@ extern "C" int ds_plan_stack_capacity(const ds_plan* plan) {
   const char* se = getenv("DSB200_STACK");
   if (se && atoi(se) == 0) return 0;
   return stack_max_clusters(plan->stack_kb);
+}
+extern "C" int ds_session_set_lengths(ds_session* s, const int32_t* lengths_host, int32_t n, void* stream) {
+  if (!s) return fail(DS_ERR_INVALID, "null session");
+  if (!lengths_host || n == 0) {
+    if (s->has_len) {  // graphs captured while ragged keep reading the array: make it say "every utterance is T frames long"
+      s->len_host.assign((size_t)s->B, s->T);
+      CUDA_TRY(cudaMemcpyAsync(s->ws + s->o_len, s->len_host.data(), (size_t)s->B * sizeof(int32_t), cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    }
+    return 0;
+  }
+  if (!s->stack) return fail(DS_ERR_INVALID, "per-utterance lengths need a session on the whole-network kernel (ds_session_path == 3)");
+  if (n != s->B) return fail(DS_ERR_INVALID, "ds_session_set_lengths: n=%d but the session has B=%d utterances", n, s->B);
+  for (int i = 0; i < n; ++i)
+    if (lengths_host[i] < 1 || lengths_host[i] > s->T)
+      return fail(DS_ERR_INVALID, "ds_session_set_lengths: lengths[%d]=%d outside [1, T=%d]", i, lengths_host[i], s->T);
+  s->len_host.assign(lengths_host, lengths_host + n);  // the async copy reads from memory the session owns
+  CUDA_TRY(cudaMemcpyAsync(s->ws + s->o_len, s->len_host.data(), (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, (cudaStream_t)stream));
+  s->has_len = true;
+  return 0;
 }
 extern "C" int ds_session_path(const ds_session* s) {
   if (!s) return fail(DS_ERR_INVALID, "null session");

@@ -68,6 +68,7 @@ struct StackParams {
                         // counter).  Zeroed by the host at the start of every program run; flags are never 0.
   unsigned int flag_base;  // L * (index of this evaluation in the program run): layer seq's packets carry flag_base + seq + 1
   int T, B, tiles_t, n_tiles;
+  const int* len;       // optional [B]: frames of utterance b (ds_session_set_lengths); nullptr = every utterance has T frames
   int L, cycle, C, FM, FMp, nout;
   float inv_sqrt_L;
   int dbg;  // debug (DSB200_DBG, timing only -- results are wrong): bit 1 = no weight loads, bit 2 = no MMAs, bit 3 = no peer copies
@@ -171,7 +172,9 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
   const int b = tile / p.tiles_t;
   const int tt = tile % p.tiles_t;
   const int t0 = tt * 128;
-  const bool has_left = tt > 0, has_right = tt + 1 < p.tiles_t;
+  const int Tb = p.len != nullptr ? __ldg(p.len + b) : p.T;  // frames of this utterance (ragged batches)
+  if (t0 >= Tb) return;  // tile beyond the utterance's end: the whole cluster leaves before any barrier exists; nobody waits for it
+  const bool has_left = tt > 0, has_right = t0 + 128 < Tb;
   const bool has_nb = has_left || has_right;
   const int L = p.L, C = p.C;
   const int KBh = p.FMp / 64;
@@ -394,8 +397,8 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
     const int half = (warp - 4) >> 2;
     const int row = quad * 32 + lane;       // frame inside the tile = TMEM lane
     const int t = t0 + row;
-    const bool valid = t < p.T;
-    const size_t grow = static_cast<size_t>(b) * p.T + (valid ? t : p.T - 1);  // global frame row (clamped for loads)
+    const bool valid = t < Tb;
+    const size_t grow = static_cast<size_t>(b) * p.T + (valid ? t : Tb - 1);  // global frame row (clamped for loads)
     const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
     const int c0 = 64 * r + 32 * half;      // first of this thread's 32 channels
     const uint32_t xrow_a = smem_u32(xs) + r * kStackXTile;   // this CTA's k-block of x~

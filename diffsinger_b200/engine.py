@@ -78,6 +78,7 @@ class Session:
         self._cond_key = None
         self._times_key = None
         self._t_dev = None
+        self._lengths = None
 
     def set_cond(self, cond_bth: torch.Tensor):
         """cond [B, T, H] fp32 contiguous."""
@@ -85,6 +86,21 @@ class Session:
         cond_bth = _f32c(cond_bth)
         self._cond_key = None  # callers that cache by tensor identity (WaveNet._forward_native) set it after this call
         nat.check(nat.lib().ds_session_set_cond(self.handle, _ptr(cond_bth), _stream()))
+
+    def set_lengths(self, lengths: Sequence[int] | None):
+        """Ragged batch (include/dsb200.h: ds_session_set_lengths): utterance b has lengths[b] <= T frames; None = all T.
+        Only sessions on the whole-network kernel accept lengths."""
+        if lengths is None:
+            if self._lengths is not None:
+                nat.check(nat.lib().ds_session_set_lengths(self.handle, None, 0, _stream()))
+                self._lengths = None
+            return
+        lengths = tuple(int(v) for v in lengths)
+        if lengths == self._lengths:
+            return
+        arr = (C.c_int32 * len(lengths))(*lengths)
+        nat.check(nat.lib().ds_session_set_lengths(self.handle, arr, len(lengths), _stream()))
+        self._lengths = lengths
 
     def set_times(self, t: torch.Tensor):
         """t: fp32 device tensor [n] (shared over the batch) or [n, B] (per-sample session)."""

@@ -1,5 +1,7 @@
 """Segment-parallel sampling: many independent short utterances (the `.ds` segments inference/ds_acoustic.py feeds one by
-one through `forward_model`) run concurrently on several CUDA streams.
+one through `forward_model`) run together -- as RAGGED BATCHES on the whole-network kernel where the
+backbone allows it (one launch per evaluation covers several segments of different lengths, each ending in its own zero
+padding exactly as if it ran alone), otherwise concurrently on several CUDA streams.
 
 One batch-1 segment of a few hundred frames cannot fill a B200 -- each of its kernels occupies at most a few dozen of
 the 148 SMs and the 20-step loop is a latency-bound chain of ~900 small kernels -- but segments are independent, so
@@ -13,16 +15,88 @@ from typing import List, Sequence
 import torch
 
 
+def _ragged_capacity(diffusion, t_longest: int) -> int:
+    """Tiles one ragged launch may hold (0: this sampler / backbone / configuration cannot run ragged batches)."""
+    from . import _native as nat
+    from .hparams import get_hparams
+    backbone = getattr(diffusion, 'denoise_fn', None) or getattr(diffusion, 'velocity_fn')
+    eng = backbone.engine()
+    if not hasattr(eng, 'plan'):
+        return 0  # LYNXNet: host-composed ops, no per-utterance edge
+    hp = get_hparams()
+    if hasattr(diffusion, 'denoise_fn') and hp.get('diff_speedup', 0) <= 1:
+        return 0  # ancestral chain draws fresh noise every step
+    if getattr(diffusion, 'use_shallow_diffusion', False):
+        return 0  # needs a per-segment source spectrogram
+    cap = int(nat.lib().ds_plan_stack_capacity(eng.plan))
+    return cap if cap >= -(-t_longest // 128) else 0
+
+
+def _ragged_groups(lengths: Sequence[int], cap: int) -> List[List[int]]:
+    """Segment indices grouped for ragged batches: similar lengths together (longest first), B * ceil(T_max / 128) <= cap tiles."""
+    order = sorted(range(len(lengths)), key=lambda i: -lengths[i])
+    groups: List[List[int]] = []
+    cur: List[int] = []
+    for i in order:
+        t_max = lengths[cur[0]] if cur else lengths[i]
+        if cur and (len(cur) + 1) * -(-t_max // 128) > cap:
+            groups.append(cur)
+            cur = []
+        cur.append(i)
+    if cur:
+        groups.append(cur)
+    return groups
+
+
+def _sample_ragged(diffusion, conditions, cap: int) -> List[torch.Tensor]:
+    """All batch-1 segments through ragged batches.  Noise is drawn segment by segment in the caller's order from the global
+    generator -- the values a segment-by-segment loop would draw -- then padded; outputs are cut back to each segment's length."""
+    dev = conditions[0].device
+    lens = [int(c.shape[1]) for c in conditions]
+    F, M = diffusion.num_feats, diffusion.out_dims
+    noise = [torch.randn(1, F, M, t, device=dev) for t in lens]
+    outs: List = [None] * len(conditions)
+    for grp in _ragged_groups(lens, cap):
+        t_max = max(lens[i] for i in grp)
+        cond = conditions[0].new_zeros(len(grp), t_max, conditions[0].shape[2])
+        z = torch.zeros(len(grp), F, M, t_max, device=dev)
+        for b, i in enumerate(grp):
+            cond[b, :lens[i]] = conditions[i][0]
+            z[b, ..., :lens[i]] = noise[i][0]
+        diffusion._noise_override, diffusion._lengths_override = z, [lens[i] for i in grp]
+        try:
+            y = diffusion(cond, infer=True)
+        finally:
+            diffusion._noise_override = diffusion._lengths_override = None
+        for b, i in enumerate(grp):
+            if isinstance(y, (list, tuple)):   # multi-variance: list of [B, T] curves
+                outs[i] = [c[b:b + 1, :lens[i]].clone() for c in y]
+            elif y.dim() == 4:                 # [B, F, T, M]
+                outs[i] = y[b:b + 1, :, :lens[i]].clone()
+            else:                              # [B, T, M] mel or [B, T] curve
+                outs[i] = y[b:b + 1, :lens[i]].clone()
+    return outs
+
+
 @torch.no_grad()
-def sample_segments(diffusion, conditions: Sequence[torch.Tensor], n_streams: int = 4, **forward_kwargs) -> List[torch.Tensor]:
-    """`diffusion(cond, infer=True, **forward_kwargs)` for every `cond` ([B, T_i, H], any lengths) with up to `n_streams`
-    segments in flight.  Per-segment keyword tensors (e.g. `src_spec`) are passed as lists of the same length as
-    `conditions`.  Returns the outputs in order; they are safe to use on the current stream."""
+def sample_segments(diffusion, conditions: Sequence[torch.Tensor], n_streams: int = 4, ragged: bool = True,
+                    **forward_kwargs) -> List[torch.Tensor]:
+    """`diffusion(cond, infer=True, **forward_kwargs)` for every `cond` ([B, T_i, H], any lengths).  Returns the outputs in
+    order; they are safe to use on the current stream.
+
+    ragged=True (default): when every segment is batch 1, no per-segment keyword tensors are given and the backbone runs on the
+    whole-network kernel, segments are padded into ragged batches (include/dsb200.h: ds_session_set_lengths) -- one launch per
+    evaluation for up to `ds_plan_stack_capacity` tiles.  Otherwise up to `n_streams` segments are in flight on CUDA streams;
+    per-segment keyword tensors (e.g. `src_spec`) are passed as lists of the same length as `conditions`."""
     if not conditions:
         return []
     dev = conditions[0].device
     if dev.type != 'cuda':
         raise RuntimeError("sample_segments needs CUDA tensors (there is no CPU path)")
+    if ragged and not forward_kwargs and all(c.shape[0] == 1 for c in conditions) and len(conditions) > 1:
+        cap = _ragged_capacity(diffusion, max(int(c.shape[1]) for c in conditions))
+        if cap:
+            return _sample_ragged(diffusion, conditions, cap)
     main = torch.cuda.current_stream(dev)
     n_streams = max(1, min(n_streams, len(conditions)))
     pool = getattr(diffusion, '_segment_streams', None)

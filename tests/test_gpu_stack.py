@@ -137,3 +137,65 @@ def test_multi_variance_predictor_euler20_on_three_cta_clusters():
     err = rel_l2(torch.stack(ys), ref)
     print(f"\n[multi-variance predictor euler-20, T={T}, stack kernel, 3-CTA clusters] final curves rel-L2 {err:.3e}")
     assert err < MEL_TOL
+
+
+@pytest.mark.parametrize("family", ["acoustic_ddim", "pitch_euler"])
+def test_ragged_batches_equal_segment_by_segment(family):
+    """sample_segments packs batch-1 segments of different lengths into ragged batches (ds_session_set_lengths): every segment
+    must come out BIT-identical to running it alone (same noise draw order, its own zero padding at its own end)."""
+    H = 256
+    lens = [300, 128, 515, 77, 257, 512]
+    ds.hparams.clear()
+    if family == "acoustic_ddim":
+        M, F, L, C, cycle = 128, 1, 4, 256, 4
+        ds.hparams.update(hidden_size=H, diff_speedup=100, diff_accelerator="ddim", timesteps=1000, K_step=1000, use_shallow_diffusion=False,
+                          schedule_type="linear")
+        m = ds.GaussianDiffusion(M, 1, 1000, 1000, "wavenet", dict(num_layers=L, num_channels=C, dilation_cycle_length=cycle),
+                                 spec_min=[-12.0], spec_max=[0.0])
+        m.denoise_fn.load_state_dict(random_state_dict(M, F, L, C, H, seed=91))
+        net = m.denoise_fn
+    else:
+        M, F, L, C, cycle = 64, 1, 5, 256, 5
+        ds.hparams.update(hidden_size=H, sampling_algorithm="euler", sampling_steps=10, T_start=0.0, T_start_infer=0.0,
+                          use_shallow_diffusion=False, time_scale_factor=1000)
+        m = ds.PitchRectifiedFlow(vmin=-8.0, vmax=8.0, cmin=-12.0, cmax=12.0, repeat_bins=M, backbone_type="wavenet",
+                                  backbone_args=dict(num_layers=L, num_channels=C, dilation_cycle_length=cycle))
+        m.velocity_fn.load_state_dict(random_state_dict(M, F, L, C, H, seed=92))
+        net = m.velocity_fn
+    m = m.eval().to(dev)
+    g = torch.Generator().manual_seed(17)
+    conds = [torch.randn(1, t, H, generator=g).to(dev) for t in lens]
+    torch.manual_seed(5)
+    with torch.no_grad():
+        alone = [m(c, infer=True).cpu() for c in conds]
+    torch.manual_seed(5)
+    batched = [y.cpu() for y in ds.sample_segments(m, conds)]
+    paths = {s.path for s in net.engine().sessions.values()}
+    assert paths == {"stack"}
+    assert any(s._lengths is not None for s in net.engine().sessions.values()), "the ragged path did not run"
+    for t, a, b in zip(lens, alone, batched):
+        assert a.shape == b.shape and a.shape[1] == t
+        assert torch.equal(a, b), f"segment of {t} frames differs: {rel_l2(b, a):.3e}"
+    # a ragged session falls back to full lengths when asked to
+    torch.manual_seed(5)
+    streams = [y.cpu() for y in ds.sample_segments(m, conds, ragged=False)]
+    for a, b in zip(alone, streams):
+        assert torch.equal(a, b)
+
+
+def test_lengths_are_rejected_off_the_stack_path(monkeypatch):
+    monkeypatch.setenv("DSB200_STACK", "0")
+    M, F, L, C, H, cycle = 64, 1, 3, 256, 256, 3
+    net = _net(random_state_dict(M, F, L, C, H, seed=93), M, F, L, C, cycle)
+    sess = net.engine().session(2, 200)
+    assert sess.path != "stack"
+    with pytest.raises(Exception, match="whole-network"):
+        sess.set_lengths([100, 200])
+    monkeypatch.delenv("DSB200_STACK")
+    net2 = _net(random_state_dict(M, F, L, C, H, seed=93), M, F, L, C, cycle)
+    sess2 = net2.engine().session(2, 200)
+    assert sess2.path == "stack"
+    with pytest.raises(Exception, match="outside"):
+        sess2.set_lengths([100, 201])
+    with pytest.raises(Exception, match="n=1"):
+        sess2.set_lengths([100])
