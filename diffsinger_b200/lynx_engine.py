@@ -125,6 +125,16 @@ class LynxEngine:
                 w6=f32(sd[q + "6.weight"])[:, :, 0].to(bf).contiguous(), b6=f32(sd[q + "6.bias"])))
         self.w = dict(w_in=w_in, b_in=f32(sd["input_projection.bias"]), w_out=w_out, b_out=b_out,
                       norm_g=f32(sd["norm.weight"]), norm_b=f32(sd["norm.bias"]), layers=layers)
+        if self.strong:
+            # strong_cond (the shipped default): the stream a layer keeps is u = x + W_c cond + b_c, and the NEXT layer's injection is
+            # linear in cond, so it rides in the producing GEMM as extra K blocks:  u_{l+1} = u_l + [W6_l | Wc_{l+1}] [dw_l ; cond] +
+            # (b6_l + bc_{l+1}); the head likewise (no GELU in this mode).  One launch and one [rows, C] round trip less per layer.
+            self.w["w_in_c"] = torch.cat([w_in, layers[0]["wc"]], dim=1).contiguous()
+            self.w["b_in_c"] = self.w["b_in"] + layers[0]["bc"]
+            for i, lw in enumerate(layers):
+                nxt = layers[i + 1] if i + 1 < self.L else None
+                lw["w6c"] = torch.cat([lw["w6"], nxt["wc"]], dim=1).contiguous() if nxt else lw["w6"]
+                lw["b6c"] = lw["b6"] + nxt["bc"] if nxt else lw["b6"]
         self.weights_key = self.weights_fingerprint(module)
         self._vec_cache.clear()
         for ws in self.workspaces.values():
@@ -184,15 +194,23 @@ class LynxEngine:
         rows = B * T
         Bt = vecs.shape[1]
         ops.cast_bf16(ws.xb, x_f32.view(rows, self.FM))
-        ops.gemm(ops.EPI_LINEAR, self.bn_c, B, T, ws.xb, w["w_in"], ws.h, bias=w["b_in"], act=ops.ACT_NONE if self.strong else ops.ACT_GELU)
+        if self.strong:
+            ops.gemm(ops.EPI_LINEAR, self.bn_c, B, T, ws.xb, w["w_in_c"], ws.u, a1=ws.cond, bias=w["b_in_c"], act=ops.ACT_NONE)
+            for i, lw in enumerate(w["layers"]):
+                ops.layernorm(ws.n, ws.u, lw["ln_g"], lw["ln_b"], 1e-5, vecs[i], T if Bt > 1 else rows)
+                ops.gemm(ops.EPI_SWIGLU, self.bn_g, B, T, ws.n, lw["w2"], ws.g, bias=lw["b2"])
+                ops.dwconv(ws.dw, ws.g, lw["dw_w"], lw["dw_b"], B, T, self.k, self.act, lw["slope"])
+                ops.gemm(ops.EPI_RES, self.bn_c, B, T, ws.dw, lw["w6c"], ws.u, a1=ws.cond if i + 1 < self.L else None,
+                         vec=lw["b6c"], vec_bstride=0, res=ws.u)
+            ops.layernorm(ws.n, ws.u, w["norm_g"], w["norm_b"], 1e-5)
+            ops.gemm(ops.EPI_OUTF32, self.bn_o, B, T, ws.n, w["w_out"], out_f32.view(rows, self.FM), bias=w["b_out"], n_real=self.FM)
+            return 4 * self.L + 4
+        ops.gemm(ops.EPI_LINEAR, self.bn_c, B, T, ws.xb, w["w_in"], ws.h, bias=w["b_in"], act=ops.ACT_GELU)
         for i, lw in enumerate(w["layers"]):
             dvec = vecs[i]  # [Bt, C]
             if hoisted:      # res_x = x; LayerNorm(x + cproj + (bias + step vector))
                 ops.layernorm(ws.n, ws.h, lw["ln_g"], lw["ln_b"], 1e-5, dvec, T if Bt > 1 else rows, add=ws.cproj[i])
                 res = ws.h
-            elif self.strong:  # res_x = x + cond projection; the step vector is added on the way into the norm
-                ops.gemm(ops.EPI_RES, self.bn_c, B, T, ws.cond, lw["wc"], ws.u, vec=lw["bc"], vec_bstride=0, res=ws.h)
-                res, ln_vec = ws.u, dvec
             else:            # res_x = x; u = x + cond projection + (bias + step vector)
                 ops.gemm(ops.EPI_RES, self.bn_c, B, T, ws.cond, lw["wc"], ws.u, vec=dvec, vec_bstride=Cc if Bt > 1 else 0, res=ws.h)
                 res, ln_vec = ws.h, None

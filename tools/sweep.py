@@ -67,11 +67,13 @@ def acoustic(kind, algo, B, T, C=512, L=20, iters=3, precision="bf16"):
     return out
 
 
-def lynx(algo, B, T, iters=3):
-    """The reference's default acoustic backbone (LYNXNet 6 x 512, expansion 2, k = 31; configs/acoustic.yaml:73-79)."""
-    M, L, C = 128, 6, 512
+def lynx(algo, B, T, iters=3, C=512, strong=False):
+    """The reference's default acoustic backbone family (LYNXNet, expansion 2, k = 31).  configs/acoustic.yaml:72-78 ships
+    6 x 1024 with strong_cond = true; 6 x 512 without it is the round-1 measurement point."""
+    M, L = 128, 6
     hp(diff_accelerator=algo)
-    m = ds.GaussianDiffusion(M, 1, 1000, 1000, "lynxnet", dict(num_layers=L, num_channels=C, expansion_factor=2, kernel_size=31),
+    m = ds.GaussianDiffusion(M, 1, 1000, 1000, "lynxnet", dict(num_layers=L, num_channels=C, expansion_factor=2, kernel_size=31,
+                                                                strong_cond=strong),
                              spec_min=[-12.0], spec_max=[0.0])
     m.denoise_fn.load_state_dict(random_lynx_state_dict(M, 1, L, C, 256, seed=1234))
     m = m.eval().to(dev)
@@ -80,7 +82,7 @@ def lynx(algo, B, T, iters=3):
         ms = timed(lambda: m(cond, infer=True), iters)
     ws = next(iter(m.denoise_fn.engine().workspaces.values()))
     flops = 2.0 * B * T * 20 * (L * (256 * C + C * 4 * C + 2 * C * C) + 2 * M * C)  # 1x1 convs only (depthwise / norms are HBM-bound)
-    print(json.dumps(dict(case=f"lynxnet/{algo}", C=C, L=L, B=B, T=T, ms=round(ms, 3), frames_per_s=round(B * T / ms * 1e3, 1),
+    print(json.dumps(dict(case=f"lynxnet/{algo}", C=C, L=L, strong_cond=strong, B=B, T=T, ms=round(ms, 3), frames_per_s=round(B * T / ms * 1e3, 1),
                           gemm_tflops=round(flops / ms / 1e9, 1), launches=ws.last_launches)), flush=True)
     del m, cond
     torch.cuda.empty_cache()
@@ -127,6 +129,8 @@ def main():
     if "lynxnet" in what:
         for B, T in ((64, 2000), (8, 1000), (1, 500)):
             lynx("dpm-solver", B, T)
+        for B, T in ((32, 2000), (1, 500)):  # the shipped default: 6 x 1024, strong_cond
+            lynx("dpm-solver", B, T, C=1024, strong=True)
     if "reflow" in what:
         for algo in ("euler", "rk2", "rk4"):
             acoustic("reflow", algo, 64, 2000, iters=2)
