@@ -773,7 +773,14 @@ static int session_fused_layer(ds_session* s, int l, int time_index, cudaStream_
 }
 
 // One backbone evaluation = 2L+4 launches on `st` (WaveNet.forward, wavenet.py:75-107).
-static int session_eval(ds_session* s, const float* x, int time_index, float* out, cudaStream_t st, int64_t* launches) {
+struct FusedUpdate {  // a LINCOMB that the whole-network kernel applies in its output epilogue (run_ops peephole)
+  int n;
+  float coef[8];
+  const float* src[8];
+  float* dst;
+};
+static int session_eval(ds_session* s, const float* x, int time_index, float* out, cudaStream_t st, int64_t* launches,
+                        const FusedUpdate* upd = nullptr) {
   const ds_plan* p = s->plan;
   const int C = p->C, L = p->L, B = s->B, T = s->T;
   const long rows = (long)B * T;
@@ -805,6 +812,10 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
     sp.vec_bstride = vstride;
     sp.edges = s->ws + s->o_edges;
     sp.len = s->has_len ? (const int*)(s->ws + s->o_len) : nullptr;
+    if (upd) {
+      sp.upd_n = upd->n; sp.upd_dst = upd->dst;
+      for (int k = 0; k < upd->n; ++k) { sp.upd_coef[k] = upd->coef[k]; sp.upd_src[k] = upd->src[k]; }
+    }
     sp.flag_base = (unsigned)L * (unsigned)s->eval_seq;
     sp.T = T; sp.B = B; sp.tiles_t = tiles_t; sp.n_tiles = B * tiles_t;
     sp.L = L; sp.cycle = p->cfg.dilation_cycle_length; sp.C = C; sp.FM = p->FM; sp.FMp = p->FMp; sp.nout = p->nout;
@@ -980,12 +991,35 @@ static int run_ops(ds_session* s, const ds_op* ops, int n_ops, float* const* buf
     ~PdlScope() { t_pdl = prev; }
   } pdl_scope((s->stack || s->small || s->medium || !s->plan->fused) && s->pdl);
   s->eval_seq = 0;
+  // DSB200_FUSE_UPDATE=1: bit-identical results and half the launches, but measured 1-3 % SLOWER than the separate lincomb launch
+  // (tools/stack_time.py): the small update kernel sits in a programmatic-dependent-launch chain and overlaps the next evaluation's
+  // start-up, while the fused form adds its loads and stores to the last epilogue of the critical path.  Off by default.
+  const char* fe = getenv("DSB200_FUSE_UPDATE");
+  const bool fuse_update = fe && atoi(fe) != 0;
   for (int i = 0; i < n_ops; ++i) {
     const ds_op& op = ops[i];
     if (op.dst < 0 || op.dst >= n_bufs) return fail(DS_ERR_INVALID, "op %d: dst %d out of range", i, op.dst);
     if (op.kind == DS_OP_EVAL) {
       if (op.src[0] < 0 || op.src[0] >= n_bufs || op.src[0] == op.dst) return fail(DS_ERR_INVALID, "op %d: bad EVAL source", i);
       DS_TRY(check_eval_ready(s, op.time));
+      // whole-network kernel: a sampler update that directly follows the evaluation runs in its output epilogue ("sampler update
+      // fused into the tail") -- one launch per sampler step instead of two
+      if (s->stack && fuse_update && i + 1 < n_ops && ops[i + 1].kind == DS_OP_LINCOMB && ops[i + 1].n > 0 && ops[i + 1].n <= 8 &&
+          ops[i + 1].dst >= 0 && ops[i + 1].dst < n_bufs) {
+        const ds_op& u = ops[i + 1];
+        FusedUpdate fu;
+        fu.n = u.n; fu.dst = bufs[u.dst];
+        bool ok = true;
+        for (int k = 0; k < u.n; ++k) {
+          if (u.src[k] < 0 || u.src[k] >= n_bufs) { ok = false; break; }
+          fu.src[k] = bufs[u.src[k]]; fu.coef[k] = u.coef[k];
+        }
+        if (ok) {
+          DS_TRY(session_eval(s, bufs[op.src[0]], op.time, bufs[op.dst], st, launches, &fu));
+          ++i;  // the LINCOMB is done
+          continue;
+        }
+      }
       DS_TRY(session_eval(s, bufs[op.src[0]], op.time, bufs[op.dst], st, launches));
     } else if (op.kind == DS_OP_LINCOMB) {
       const float* srcs[8];

@@ -68,6 +68,12 @@ struct StackParams {
                         // counter).  Zeroed by the host at the start of every program run; flags are never 0.
   unsigned int flag_base;  // L * (index of this evaluation in the program run): layer seq's packets carry flag_base + seq + 1
   int T, B, tiles_t, n_tiles;
+  // sampler update fused into the output epilogue (ds_session_run peephole: EVAL followed by LINCOMB): upd_dst = sum_k upd_coef[k] *
+  // upd_src[k], evaluated like lincomb_kernel (fma chain from 0 in term order); a source equal to `out` is this evaluation's result
+  int upd_n;
+  float upd_coef[8];
+  const float* upd_src[8];
+  float* upd_dst;
   const int* len;       // optional [B]: frames of utterance b (ds_session_set_lengths); nullptr = every utterance has T frames
   int L, cycle, C, FM, FMp, nout;
   float inv_sqrt_L;
@@ -214,6 +220,10 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t tm_acc1 = tmem_base, tm_acc2 = tmem_base + 128, tm_skip = tmem_base + 192;
+  // The next evaluation's launch may be scheduled NOW (programmatic dependent launch): a session of a few tiles leaves most SMs
+  // idle, so its clusters set up (barriers, TMEM, the first weight stages) beside this launch and only wait -- griddepcontrol.wait in
+  // the epilogue, before the first read of x -- for this one to finish.  Its start-up latency disappears from the step.
+  grid_dep_launch();
 
   // ------------------------------------------------------------ weight producers (never wait for data: weights are constant)
   // A thread pays ~285 cycles for every mbarrier operation and bulk-copy issue (measured, tools/tma_bw_bench.cu: 16 KB stages from
@@ -635,11 +645,23 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
     }
     // ---- output projection -> fp32 [B][T][FM]: this CTA's nout columns, 16 per warp half             wavenet.py:99
     {
+      const int ncols = p.nout / 2;  // 8 or 16 columns per thread
+      const int n0 = p.nout * r + ncols * half;
+      const size_t at0 = grow * p.FM + n0;
+      // sampler update (if fused): the other operands of up to 3 terms are fetched BEFORE the accumulator wait
+      constexpr int kPre = 3;
+      float pre[kPre][16];
+      const bool prefetch = p.upd_n > 0 && p.upd_n <= kPre && valid;
+      if (prefetch) {
+#pragma unroll
+        for (int k = 0; k < kPre; ++k)
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            pre[k][i] = (k < p.upd_n && p.upd_src[k] != p.out && i < ncols && n0 + i < p.FM) ? p.upd_src[k][at0 + i] : 0.0f;
+      }
       bwait(acc1_full, ph1);
       ph1 ^= 1;
       tc_fence_after();
-      const int ncols = p.nout / 2;  // 8 or 16 columns per thread
-      const int n0 = p.nout * r + ncols * half;
       uint32_t a[32];
       tmem_ld_32x32(lane_addr + ncols * half, a);  // reads 32 columns; only the first `ncols` are this thread's
       tmem_ld_wait();
@@ -647,7 +669,21 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
         float* orow = p.out + grow * p.FM;
 #pragma unroll
         for (int i = 0; i < 16; ++i)
-          if (i < ncols && n0 + i < p.FM) orow[n0 + i] = __uint_as_float(a[i]) + __ldg(p.bout + n0 + i);
+          if (i < ncols && n0 + i < p.FM) {
+            const float e = __uint_as_float(a[i]) + __ldg(p.bout + n0 + i);
+            orow[n0 + i] = e;
+            if (p.upd_n > 0) {  // the sampler's update of this element: lincomb_kernel's fma chain (plain loads: dst may alias a source)
+              float acc = 0.0f;
+              if (prefetch) {
+#pragma unroll
+                for (int k = 0; k < kPre; ++k)
+                  if (k < p.upd_n) acc = fmaf(p.upd_coef[k], p.upd_src[k] == p.out ? e : pre[k][i], acc);
+              } else {
+                for (int k = 0; k < p.upd_n; ++k) acc = fmaf(p.upd_coef[k], p.upd_src[k] == p.out ? e : p.upd_src[k][at0 + i], acc);
+              }
+              p.upd_dst[at0 + i] = acc;
+            }
+          }
       }
     }
   }

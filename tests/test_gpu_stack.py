@@ -199,3 +199,34 @@ def test_lengths_are_rejected_off_the_stack_path(monkeypatch):
         sess2.set_lengths([100, 201])
     with pytest.raises(Exception, match="n=1"):
         sess2.set_lengths([100])
+
+
+@pytest.mark.parametrize("algo", ["ddim", "dpm-solver", "unipc", "pndm"])
+def test_update_fused_into_the_output_epilogue_is_bit_identical(monkeypatch, algo):
+    """DSB200_FUSE_UPDATE=1: ds_session_run folds the LINCOMB that follows an evaluation into the whole-network kernel's output
+    epilogue; the result must equal the separate lincomb launch bit for bit (same fma chain), for samplers whose update reads
+    history buffers too.  (Off by default: measured 1-3 % slower than the PDL-chained lincomb launch, api.cu:run_ops.)"""
+    M, F, L, C, H, cycle, T = 64, 1, 4, 256, 256, 4, 300
+    ds.hparams.clear()
+    ds.hparams.update(hidden_size=H, diff_speedup=100, diff_accelerator=algo, timesteps=1000, K_step=1000, use_shallow_diffusion=False,
+                      schedule_type="linear")
+    m = ds.GaussianDiffusion(M, 1, 1000, 1000, "wavenet", dict(num_layers=L, num_channels=C, dilation_cycle_length=cycle),
+                             spec_min=[-12.0], spec_max=[0.0])
+    m.denoise_fn.load_state_dict(random_state_dict(M, F, L, C, H, seed=77))
+    m = m.eval().to(dev)
+    cond = torch.randn(1, T, H, generator=torch.Generator().manual_seed(3)).to(dev)
+    outs, launches = [], []
+    for fuse in ("1", "0"):
+        monkeypatch.setenv("DSB200_FUSE_UPDATE", fuse)
+        if m.denoise_fn._engine is not None:  # new engine and sessions: graphs are cached per op list, not per switch
+            m.denoise_fn._engine.close()
+            m.denoise_fn._engine = None
+        torch.manual_seed(11)
+        with torch.no_grad():
+            outs.append(m(cond, infer=True).cpu())
+        sess = next(reversed(m.denoise_fn.engine().sessions.values()))
+        assert sess.path == "stack"
+        launches.append(sess.last_launches)
+    assert torch.equal(outs[0], outs[1])
+    assert launches[0] < launches[1], launches
+    print(f"\n[{algo}] launches per call: fused {launches[0]}, separate {launches[1]}")
