@@ -63,11 +63,12 @@ def _sample_ragged(diffusion, conditions, cap: int) -> List[torch.Tensor]:
         for b, i in enumerate(grp):
             cond[b, :lens[i]] = conditions[i][0]
             z[b, ..., :lens[i]] = noise[i][0]
+        saved = getattr(diffusion, '_noise_override', None), getattr(diffusion, '_lengths_override', None)
         diffusion._noise_override, diffusion._lengths_override = z, [lens[i] for i in grp]
         try:
             y = diffusion(cond, infer=True)
         finally:
-            diffusion._noise_override = diffusion._lengths_override = None
+            diffusion._noise_override, diffusion._lengths_override = saved
         for b, i in enumerate(grp):
             if isinstance(y, (list, tuple)):   # multi-variance: list of [B, T] curves
                 outs[i] = [c[b:b + 1, :lens[i]].clone() for c in y]
