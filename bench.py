@@ -273,6 +273,22 @@ def extra_corners(model, dev, c):
         model(cond, infer=True)
         ts = [timed(lambda: model(cond, infer=True), 1) for _ in range(10)]
         out["B1_T500"] = {"ms_per_call": round(statistics.median(ts), 3), "frames_per_s": round(500 / (statistics.median(ts) * 1e-3), 1)}
+        # the 30 segment lengths of config #1 on THIS network (20 x 512): one by one (the reference's loop) vs ragged batches
+        import diffsinger_b200 as ds
+        lens = [504, 522, 539, 720, 1197, 550, 550, 515, 550, 539, 539, 540, 1917, 549, 550, 515, 687, 549, 549, 549, 460, 286, 578, 545,
+                515, 566, 572, 542, 516, 579]
+        conds = [torch.randn(1, t, c["H"], device=dev) for t in lens]
+        torch.manual_seed(7)
+        one = [model(cd, infer=True) for cd in conds]
+        torch.manual_seed(7)
+        rag = ds.sample_segments(model, conds)
+        err = max(float((a - b).norm() / b.norm()) for a, b in zip(rag, one))
+        ms_one = timed(lambda: [model(cd, infer=True) for cd in conds], 1)
+        ms_rag = timed(lambda: ds.sample_segments(model, conds), 1)
+        out["segments_30_ragged"] = {"frames": sum(lens), "one_by_one_ms": round(ms_one, 1), "ragged_batches_ms": round(ms_rag, 1),
+                                     "ragged_frames_per_s": round(sum(lens) / (ms_rag * 1e-3), 1),
+                                     "ragged_vs_one_by_one_rel_l2_max": round(err, 7)}
+        del conds, one, rag
         eng = model.denoise_fn.engine()
         B, T = 1024, 2000
         bc = max_chunk_batch(eng, B, T, 3, c["K"])

@@ -45,7 +45,7 @@ def run_program(backbone, prog: Program, x_tm: torch.Tensor, cond_bht: torch.Ten
     """Runs `prog` with buffer 0 = x_tm (time-major start state), buffers 2.. optionally preset from
     `extra`.  cond_bht is the [B, H, T] tensor the reference passes to the backbone.  Returns buffer 0.
     lengths: optional per-utterance frame counts of a RAGGED batch (segments.sample_segments); frames beyond them are zero
-    padding for the convolutions and their outputs are undefined -- needs a session on the whole-network kernel.
+    padding for the convolutions (each utterance keeps its batch-1 result) and their outputs are undefined.
 
     The backbone must be one of this package's native backbones (WaveNet, LYNXNet); anything else is rejected rather
     than silently emulated in PyTorch."""
@@ -58,7 +58,7 @@ def run_program(backbone, prog: Program, x_tm: torch.Tensor, cond_bht: torch.Ten
     eng = backbone.engine()
     if hasattr(eng, 'run_program'):  # LYNXNet: host-composed primitive ops, one torch CUDA graph per (program, B, T)
         if lengths is not None:
-            raise nat.NativeError("ragged batches (lengths=...) are only supported by the WaveNet whole-network kernel")
+            raise nat.NativeError("ragged batches (lengths=...) are only supported by the WaveNet backbone")
         return eng.run_program(backbone, prog, x_tm, cond_bht, extra, use_graph)
     B, T, FM = x_tm.shape
     bc = max_chunk_batch(eng, B, T, prog.n_bufs, len(prog.times))

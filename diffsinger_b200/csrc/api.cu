@@ -594,12 +594,12 @@ static void session_layout(const ds_plan* p, int B, int T, int max_times, int pe
   // hoisted conditioner projection: f16 [L][rows][2C] (40 KB per frame at C = 512, L = 20); small sessions never use it
   s->o_cproj = 0;
   if (p->hoist && !session_is_small(p, B, T)) s->o_cproj = take(rows * L * 2 * C * 2);
-  s->o_scproj = s->o_edges = s->o_len = 0;
+  s->o_scproj = s->o_edges = 0;
+  s->o_len = take((size_t)B * sizeof(int32_t));  // ds_session_set_lengths
   if (session_is_stack(p, B, T)) {
     const size_t tiles = (size_t)B * ceil_div(T, 128);
     s->o_scproj = take(rows * L * 2 * C * 2);
     s->o_edges = take(2 * tiles * 2 * p->stack_kb * kStackEdgeBytes);
-    s->o_len = take((size_t)B * sizeof(int32_t));
   }
   s->ws_bytes = off;
 }
@@ -747,6 +747,7 @@ static int session_fused_layer(ds_session* s, int l, int time_index, cudaStream_
   __nv_bfloat16* xts[2] = {(__nv_bfloat16*)(s->ws + s->o_xt), (__nv_bfloat16*)(s->ws + s->o_xt1)};
   LayerParams lp;
   memset(&lp, 0, sizeof(lp));
+  lp.len = s->has_len ? (const int*)(s->ws + s->o_len) : nullptr;
   lp.tmCond = s->tm_cond; lp.tmW1 = p->tm_w1h; lp.tmW2 = p->tm_w2h; lp.tmZ = s->tm_z;
   lp.T = T; lp.B = B; lp.tiles_t = ceil_div(T, 256); lp.total_tiles = B * lp.tiles_t;  // 256-frame tiles, one per CTA pair
   lp.kb_c = C / 64; lp.kb_h = p->H / 64; lp.p1 = 2 * C / 256;
@@ -862,6 +863,7 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   GemmParams g;
   memset(&g, 0, sizeof(g));
   g.T = T; g.B = B; g.tiles_t = tiles_t; g.scale = 1.0f; g.vec_bstride = vstride;
+  g.len = s->has_len ? (const int*)(s->ws + s->o_len) : nullptr;  // ragged batch: the x~ writers store zeros beyond an utterance's end
   auto shape = [&](int n_tiles) {
     g.n_tiles = n_tiles;
     g.total_tiles = B * tiles_t * n_tiles;
@@ -1098,7 +1100,6 @@ extern "C" int ds_session_set_lengths(ds_session* s, const int32_t* lengths_host
     }
     return 0;
   }
-  if (!s->stack) return fail(DS_ERR_INVALID, "per-utterance lengths need a session on the whole-network kernel (ds_session_path == 3)");
   if (n != s->B) return fail(DS_ERR_INVALID, "ds_session_set_lengths: n=%d but the session has B=%d utterances", n, s->B);
   for (int i = 0; i < n; ++i)
     if (lengths_host[i] < 1 || lengths_host[i] > s->T)

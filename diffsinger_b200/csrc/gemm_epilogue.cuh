@@ -67,6 +67,7 @@ template <int BN, int EPI, bool kSplit>
 __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t taddr, int b, int t, bool valid, int nt, int half,
                                               const EpiStage& es) {
   const size_t row = static_cast<size_t>(b) * p.T + (valid ? t : 0);
+  const bool live = p.len == nullptr || t < __ldg(p.len + b);  // ragged batch: frames beyond the utterance's end are stored as zeros
   if constexpr (EPI == EPI_GATE) {
     // columns [0, BN/2) = gate pre-activations, [BN/2, BN) = filter pre-activations of the SAME channels
     constexpr int H = BN / 2;
@@ -221,6 +222,10 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
           v[j + 1] = fmaf(__uint_as_float(a[j + 1]) + __uint_as_float(w[h] & 0xffff0000u), p.scale, rr[j + 1]);
         }
       }
+      if (!live) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = 0.0f;
+      }
       epi_store32<kSplit>(p, es, row, p.out_c0 + n0 + c * 32, b, valid, v);
       if (p.out2) {  // pre-activated copy for the next convolution (HiFi-GAN ResBlock, nsf_hifigan/models.py:60-67)
 #pragma unroll
@@ -272,6 +277,10 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
           ld_f32x32(vadd + c * 32, da);
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] += da[j];
+        }
+        if (!live) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0.0f;
         }
         epi_store32<kSplit>(p, es, row, p.out_c0 + n0 + c * 32, b, valid, v);
       }

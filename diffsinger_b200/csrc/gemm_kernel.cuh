@@ -32,6 +32,8 @@ struct GemmParams {
   CUtensorMap tmOut; // bf16 output as a store map (dims: ld_out channels, T, B; box 32 x 32, SWIZZLE_64B); valid when has_out_map
   int has_out_map;   // the pair kernel's epilogue warps then write through TMA stores instead of per-lane STG.128
   int T, B, tiles_t, n_tiles, total_tiles;
+  const int* len;  // optional [B] (ragged batch, ds_session_set_lengths): bf16 outputs of frames t >= len[b] are written as ZEROS,
+                   // so that the next dilated convolution reads the utterance's own zero padding there
   int a0_c0;   // channel offset inside A0 (selects a layer's slice of the gated-activation store)
   int kb_a0;   // 64-wide K blocks per tap from A0
   int n_taps;  // 1 (plain 1x1) or 3 (dilated conv)

@@ -29,6 +29,7 @@ struct LayerParams {
   CUtensorMap tmX, tmCond, tmW1, tmW2;
   CUtensorMap tmZ;  // gated-activation store (dims L*C, T, B): A operand of GEMM-2 in the kZSmem = false variant
   int T, B, tiles_t, total_tiles;
+  const int* len;  // optional [B] (ragged batch): x~ rows of frames t >= len[b] are written as zeros (the utterance's own conv padding)
   int kb_c, kb_h;  // C/64, H/64
   int dil;
   int p1, p2;      // GEMM-1 passes (2C/256), GEMM-2 chunks (C/BN2; 0 for the last layer)
@@ -182,7 +183,7 @@ __device__ __forceinline__ void grp_epilogue_gate(const LayerParams& p, uint32_t
 // x~ lives in renamed registers (a rolled loop ends in register moves that wait for the prefetch at the END of each
 // iteration -- the top epilogue stall in the ncu source view).
 __device__ __forceinline__ void grp_epilogue_res(const LayerParams& p, uint32_t taddr, int idx, int b, int tw0, const __nv_bfloat16* xin,
-                                                 const uint4 (&x0)[4], int half, int lane, uint32_t sw) {
+                                                 const uint4 (&x0)[4], int half, int lane, uint32_t sw, bool live) {
   const int n0 = idx * 256;
   const float* rv = p.rvec + static_cast<size_t>(b) * p.vec_bstride + n0;
   uint4 xq[4];
@@ -207,7 +208,7 @@ __device__ __forceinline__ void grp_epilogue_res(const LayerParams& p, uint32_t 
         const int q = 8 * i + 2 * h;
         const float v0 = fmaf(__uint_as_float(a[q]) + __uint_as_float(w[h] << 16), 0.70710678118654752f, rr[q]);
         const float v1 = fmaf(__uint_as_float(a[q + 1]) + __uint_as_float(w[h] & 0xffff0000u), 0.70710678118654752f, rr[q + 1]);
-        o[4 * i + h] = pack_bf16(v0, v1);
+        o[4 * i + h] = live ? pack_bf16(v0, v1) : 0u;
       }
     }
     warp_store_tile(&p.tmXs, sw, lane, o, n0 + c * 32, tw0, b, tw0 < p.T);
@@ -420,7 +421,7 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
       } else if (kind == 0) {
         grp_epilogue_gate(p, taddr, idx, b, tw0, add, bg0, bf0, half, lane, sw);
       } else {
-        grp_epilogue_res(p, taddr, idx, b, tw0, xin, x0, half, lane, sw);
+        grp_epilogue_res(p, taddr, idx, b, tw0, xin, x0, half, lane, sw, p.len == nullptr || t < __ldg(p.len + b));
       }
       // release the accumulator on the LEADER's barrier: one arrival per warp
       tc_fence_before();

@@ -88,8 +88,7 @@ class Session:
         nat.check(nat.lib().ds_session_set_cond(self.handle, _ptr(cond_bth), _stream()))
 
     def set_lengths(self, lengths: Sequence[int] | None):
-        """Ragged batch (include/dsb200.h: ds_session_set_lengths): utterance b has lengths[b] <= T frames; None = all T.
-        Only sessions on the whole-network kernel accept lengths."""
+        """Ragged batch (include/dsb200.h: ds_session_set_lengths): utterance b has lengths[b] <= T frames; None = all T."""
         if lengths is None:
             if self._lengths is not None:
                 nat.check(nat.lib().ds_session_set_lengths(self.handle, None, 0, _stream()))

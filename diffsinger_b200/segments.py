@@ -15,31 +15,41 @@ from typing import List, Sequence
 import torch
 
 
-def _ragged_capacity(diffusion, t_longest: int) -> int:
-    """Tiles one ragged launch may hold (0: this sampler / backbone / configuration cannot run ragged batches)."""
+MAX_RAGGED_FRAMES = 1 << 16  # padded frames (B * T_max) of one ragged batch on the per-layer kernels
+
+
+def _ragged_capacity(diffusion, t_longest: int):
+    """(tiles of 128 frames one ragged batch may hold, shortest segment of a batch as a fraction of its longest); (0, 0): this
+    sampler / backbone / configuration cannot run ragged batches.  Plans on the whole-network kernel are bounded by the
+    co-resident clusters (ds_plan_stack_capacity) as long as the longest segment fits, and padding costs them nothing (tiles beyond
+    an utterance's end exit at once); everything else runs the per-layer kernels, which compute the padding too: batches of at most
+    MAX_RAGGED_FRAMES padded frames whose segments are at least half as long as the longest."""
     from . import _native as nat
     from .hparams import get_hparams
     backbone = getattr(diffusion, 'denoise_fn', None) or getattr(diffusion, 'velocity_fn')
     eng = backbone.engine()
     if not hasattr(eng, 'plan'):
-        return 0  # LYNXNet: host-composed ops, no per-utterance edge
+        return 0, 0.0  # LYNXNet: host-composed ops, no per-utterance edge
     hp = get_hparams()
     if hasattr(diffusion, 'denoise_fn') and hp.get('diff_speedup', 0) <= 1:
-        return 0  # ancestral chain draws fresh noise every step
+        return 0, 0.0  # ancestral chain draws fresh noise every step
     if getattr(diffusion, 'use_shallow_diffusion', False):
-        return 0  # needs a per-segment source spectrogram
+        return 0, 0.0  # needs a per-segment source spectrogram
     cap = int(nat.lib().ds_plan_stack_capacity(eng.plan))
-    return cap if cap >= -(-t_longest // 128) else 0
+    if cap >= -(-t_longest // 128):
+        return cap, 0.0
+    return max(MAX_RAGGED_FRAMES // 128, -(-t_longest // 128)), 0.5
 
 
-def _ragged_groups(lengths: Sequence[int], cap: int) -> List[List[int]]:
-    """Segment indices grouped for ragged batches: similar lengths together (longest first), B * ceil(T_max / 128) <= cap tiles."""
+def _ragged_groups(lengths: Sequence[int], cap: int, min_fill: float = 0.0) -> List[List[int]]:
+    """Segment indices grouped for ragged batches: similar lengths together (longest first), B * ceil(T_max / 128) <= cap tiles,
+    every segment at least min_fill * T_max frames long."""
     order = sorted(range(len(lengths)), key=lambda i: -lengths[i])
     groups: List[List[int]] = []
     cur: List[int] = []
     for i in order:
         t_max = lengths[cur[0]] if cur else lengths[i]
-        if cur and (len(cur) + 1) * -(-t_max // 128) > cap:
+        if cur and ((len(cur) + 1) * -(-t_max // 128) > cap or lengths[i] < min_fill * t_max):
             groups.append(cur)
             cur = []
         cur.append(i)
@@ -48,7 +58,7 @@ def _ragged_groups(lengths: Sequence[int], cap: int) -> List[List[int]]:
     return groups
 
 
-def _sample_ragged(diffusion, conditions, cap: int) -> List[torch.Tensor]:
+def _sample_ragged(diffusion, conditions, cap: int, min_fill: float) -> List[torch.Tensor]:
     """All batch-1 segments through ragged batches.  Noise is drawn segment by segment in the caller's order from the global
     generator -- the values a segment-by-segment loop would draw -- then padded; outputs are cut back to each segment's length."""
     dev = conditions[0].device
@@ -56,7 +66,7 @@ def _sample_ragged(diffusion, conditions, cap: int) -> List[torch.Tensor]:
     F, M = diffusion.num_feats, diffusion.out_dims
     noise = [torch.randn(1, F, M, t, device=dev) for t in lens]
     outs: List = [None] * len(conditions)
-    for grp in _ragged_groups(lens, cap):
+    for grp in _ragged_groups(lens, cap, min_fill):
         t_max = max(lens[i] for i in grp)
         cond = conditions[0].new_zeros(len(grp), t_max, conditions[0].shape[2])
         z = torch.zeros(len(grp), F, M, t_max, device=dev)
@@ -85,9 +95,9 @@ def sample_segments(diffusion, conditions: Sequence[torch.Tensor], n_streams: in
     """`diffusion(cond, infer=True, **forward_kwargs)` for every `cond` ([B, T_i, H], any lengths).  Returns the outputs in
     order; they are safe to use on the current stream.
 
-    ragged=True (default): when every segment is batch 1, no per-segment keyword tensors are given and the backbone runs on the
-    whole-network kernel, segments are padded into ragged batches (include/dsb200.h: ds_session_set_lengths) -- one launch per
-    evaluation for up to `ds_plan_stack_capacity` tiles.  Otherwise up to `n_streams` segments are in flight on CUDA streams;
+    ragged=True (default): when every segment is batch 1, no per-segment keyword tensors are given and the backbone is a WaveNet,
+    segments are padded into ragged batches (include/dsb200.h: ds_session_set_lengths): every utterance keeps its own end, so each
+    output equals the segment-by-segment result.  Otherwise up to `n_streams` segments are in flight on CUDA streams;
     per-segment keyword tensors (e.g. `src_spec`) are passed as lists of the same length as `conditions`."""
     if not conditions:
         return []
@@ -95,9 +105,9 @@ def sample_segments(diffusion, conditions: Sequence[torch.Tensor], n_streams: in
     if dev.type != 'cuda':
         raise RuntimeError("sample_segments needs CUDA tensors (there is no CPU path)")
     if ragged and not forward_kwargs and all(c.shape[0] == 1 for c in conditions) and len(conditions) > 1:
-        cap = _ragged_capacity(diffusion, max(int(c.shape[1]) for c in conditions))
+        cap, min_fill = _ragged_capacity(diffusion, max(int(c.shape[1]) for c in conditions))
         if cap:
-            return _sample_ragged(diffusion, conditions, cap)
+            return _sample_ragged(diffusion, conditions, cap, min_fill)
     main = torch.cuda.current_stream(dev)
     n_streams = max(1, min(n_streams, len(conditions)))
     pool = getattr(diffusion, '_segment_streams', None)

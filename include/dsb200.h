@@ -130,13 +130,14 @@ int ds_session_path(const ds_session* s);
  * and callers that run several such sessions CONCURRENTLY (different streams) should keep the tiles in flight below this number
  * (diffsinger_b200.sample_segments does).  No counterpart in the reference (it launches ~240 library kernels per evaluation). */
 int ds_plan_stack_capacity(const ds_plan* plan);
-/* Ragged batch on the whole-network kernel: utterance b of the session's [B, T] layout has only lengths[b] (1 .. T) frames; frames
- * at and beyond it are the convolution's zero padding (exactly as if the utterance ran alone), their outputs are not written and
- * tiles entirely beyond it do no work.  lengths = NULL (or n = 0) restores B full-length utterances.  The values are copied into
- * session memory on `stream` (graphs captured by ds_session_run read them at replay).  Only for sessions on path 3
- * (DS_ERR_INVALID otherwise): the per-layer kernels have no per-utterance edge.  This is how diffsinger_b200.sample_segments
- * runs many batch-1 `.ds` segments of different lengths (inference/ds_acoustic.py:234-244 loops over them one by one) as ONE
- * launch per evaluation.  No counterpart in the reference (its batches are padded and unmasked, SURVEY.md trap T4). */
+/* Ragged batch: utterance b of the session's [B, T] layout has only lengths[b] (1 .. T) frames.  Frames at and beyond it are the
+ * dilated convolutions' zero padding, exactly as if the utterance ran alone: every kernel that writes the residual stream x~ stores
+ * zeros there (whole-network kernel: tiles entirely beyond the end also exit at once), so batching utterances of different lengths
+ * does not change any utterance's result.  Output rows beyond lengths[b] are undefined.  lengths = NULL (or n = 0) restores B
+ * full-length utterances.  The values are copied into session memory on `stream` (graphs captured by ds_session_run read them at
+ * replay).  This is how diffsinger_b200.sample_segments runs many batch-1 `.ds` segments of different lengths
+ * (inference/ds_acoustic.py:234-244 loops over them one by one) as one batch.  No counterpart in the reference (its batches are
+ * padded and unmasked, SURVEY.md trap T4). */
 int ds_session_set_lengths(ds_session* s, const int32_t* lengths_host, int32_t n, void* stream);
 
 /* ---- no-allocation entry point.  NO COUNTERPART IN THE REFERENCE: added for callers that
