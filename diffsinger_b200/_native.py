@@ -78,6 +78,9 @@ class GemmDesc(C.Structure):
         ("out", C.c_void_p), ("ld_out", C.c_int32), ("out_c0", C.c_int32), ("n_real", C.c_int32),
         ("relu", C.c_int32), ("scale", C.c_float),
         ("out2", C.c_void_p), ("slope2", C.c_float),
+        ("stats_out", C.c_void_p), ("stats_d", C.c_void_p), ("stats_d_bstride", C.c_int32),
+        ("ln_stats", C.c_void_p), ("ln_parts", C.c_int32), ("ln_channels", C.c_int32), ("ln_eps", C.c_float),
+        ("ln_s", C.c_void_p), ("ln_e", C.c_void_p), ("ln_e_bstride", C.c_int32),
     ]
 
 

@@ -1214,6 +1214,19 @@ extern "C" int ds_debug_gemm(const ds_gemm_desc* d, void* stream) {
   g.vec_bstride = d->vec_bstride; g.res_in = (const __nv_bfloat16*)d->res_in; g.ld_res = d->ld_res;
   g.out = d->out; g.ld_out = d->ld_out; g.out_c0 = d->out_c0; g.n_real = d->n_real;
   g.out2 = (__nv_bfloat16*)d->out2; g.slope2 = d->slope2;
+  if (d->stats_out) {
+    if (d->epi != EPI_LINEAR && d->epi != EPI_RES) return fail(DS_ERR_INVALID, "ds_gemm: stats_out needs the linear or the residual epilogue");
+    if ((uintptr_t)d->stats_out & 15) return fail(DS_ERR_INVALID, "ds_gemm: stats_out must be 16-byte aligned");
+    g.stats_out = (float4*)d->stats_out; g.stats_d = d->stats_d; g.stats_d_bstride = d->stats_d_bstride;
+  }
+  if (d->ln_stats) {
+    if (d->epi != EPI_SWIGLU || !d->ln_s || !d->ln_e || d->ln_parts <= 0 || d->ln_channels <= 0)
+      return fail(DS_ERR_INVALID, "ds_gemm: a folded LayerNorm needs the SwiGLU epilogue, ln_s, ln_e, ln_parts and ln_channels");
+    if (((uintptr_t)d->ln_stats | (uintptr_t)d->ln_s | (uintptr_t)d->ln_e) & 15 || d->ln_e_bstride % 4)
+      return fail(DS_ERR_INVALID, "ds_gemm: ln_stats / ln_s / ln_e must be 16-byte aligned");
+    g.ln_stats = (const float4*)d->ln_stats; g.ln_parts = d->ln_parts; g.ln_channels = d->ln_channels; g.ln_eps = d->ln_eps;
+    g.ln_s = d->ln_s; g.ln_e = d->ln_e; g.ln_e_bstride = d->ln_e_bstride; g.ln_n = d->w_rows;
+  }
   return launch_gemm(d->BN, d->epi, g, (cudaStream_t)stream);
 }
 

@@ -62,6 +62,19 @@ __device__ __forceinline__ void ld_x4(const __nv_bfloat16* ptr, uint4 (&q)[4]) {
   for (int i = 0; i < 4; ++i) q[i] = __ldg(reinterpret_cast<const uint4*>(ptr) + i);
 }
 
+// partial sums of a folded LayerNorm's input (GemmParams::stats_out): r = the bf16 value that is stored, d = the step vector chunk
+__device__ __forceinline__ void ln_stats_acc(const float (&v)[32], const float* d, float& s1, float& s2, float& s3) {
+  float dv[32];
+  if (d != nullptr) ld_f32x32(d, dv);
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    const float r = __bfloat162float(__float2bfloat16_rn(v[j]));
+    s1 += r;
+    s2 = fmaf(r, r, s2);
+    if (d != nullptr) s3 = fmaf(r, dv[j], s3);
+  }
+}
+
 // `half` in {0,1}: the two epilogue warps that share a TMEM lane quadrant interleave the 32-column chunks.
 template <int BN, int EPI, bool kSplit>
 __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t taddr, int b, int t, bool valid, int nt, int half,
@@ -99,6 +112,25 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
     // z = out * silu(gate)   (SwiGLU, modules/commons/common_layers.py; LYNXConvModule, lynxnet.py:57)
     constexpr int H = BN / 2;
     const float* bias = p.bias + nt * BN;
+    // folded LayerNorm (GemmParams::ln_*): this row's mean / rstd from the producer's partial sums
+    float mu = 0.0f, rstd = 1.0f;
+    const float* ls = nullptr;
+    const float* le = nullptr;
+    if (p.ln_stats != nullptr) {
+      const float* erow = p.ln_e + static_cast<size_t>(b) * p.ln_e_bstride;
+      float s1 = __ldg(erow + p.ln_n), s2 = __ldg(erow + p.ln_n + 1);  // sum d, sum d^2
+      const float4* st = p.ln_stats + row * p.ln_parts;
+      for (int k = 0; k < p.ln_parts; ++k) {
+        const float4 q = __ldg(st + k);
+        s1 += q.x;
+        s2 += q.y + 2.0f * q.z;
+      }
+      const float inv = 1.0f / static_cast<float>(p.ln_channels);
+      mu = s1 * inv;
+      rstd = rsqrtf(fmaxf(s2 * inv - mu * mu, 0.0f) + p.ln_eps);
+      ls = p.ln_s + nt * BN;
+      le = erow + nt * BN;
+    }
 #pragma unroll 1
     for (int c = half; c < H / 32; c += 2) {
       uint32_t a[32], g[32];
@@ -108,6 +140,17 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
       ld_f32x32(bias + c * 32, ba);
       ld_f32x32(bias + H + c * 32, bgt);
       tmem_ld_wait();
+      if (ls != nullptr) {  // acc <- rstd * (acc + e - mean * s)
+        float sv[32], ev[32];
+        ld_f32x32(ls + c * 32, sv);
+        ld_f32x32(le + c * 32, ev);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) a[j] = __float_as_uint(rstd * (__uint_as_float(a[j]) + ev[j] - mu * sv[j]));
+        ld_f32x32(ls + H + c * 32, sv);
+        ld_f32x32(le + H + c * 32, ev);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) g[j] = __float_as_uint(rstd * (__uint_as_float(g[j]) + ev[j] - mu * sv[j]));
+      }
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
         const float aj = __uint_as_float(a[j]) + ba[j];
@@ -189,6 +232,8 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
     const __nv_bfloat16* xin = p.res_in + row * p.ld_res + n0;
     uint4 xq[4];
     ld_x4(xin + half * 32, xq);
+    float s1 = 0.0f, s2 = 0.0f, s3 = 0.0f;
+    const float* sd = p.stats_d ? p.stats_d + static_cast<size_t>(b) * p.stats_d_bstride + n0 : nullptr;
 #pragma unroll 1
     for (int c = half; c < BN / 32; c += 2) {
       uint32_t a[32];
@@ -226,6 +271,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = 0.0f;
       }
+      if (p.stats_out != nullptr) ln_stats_acc(v, sd ? sd + c * 32 : nullptr, s1, s2, s3);
       epi_store32<kSplit>(p, es, row, p.out_c0 + n0 + c * 32, b, valid, v);
       if (p.out2) {  // pre-activated copy for the next convolution (HiFi-GAN ResBlock, nsf_hifigan/models.py:60-67)
 #pragma unroll
@@ -235,10 +281,13 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
 #pragma unroll
       for (int i = 0; i < 4; ++i) xq[i] = xn[i];
     }
+    if (p.stats_out != nullptr && valid) p.stats_out[row * (2 * p.n_tiles) + 2 * nt + half] = make_float4(s1, s2, s3, 0.0f);
   } else {
     const int n0 = nt * BN;
     const float* bias = p.bias + n0;
     const float* vadd = p.vec_add ? p.vec_add + static_cast<size_t>(b) * p.vec_bstride + n0 : nullptr;
+    float s1 = 0.0f, s2 = 0.0f, s3 = 0.0f;
+    const float* sd = p.stats_d ? p.stats_d + static_cast<size_t>(b) * p.stats_d_bstride + n0 : nullptr;
 #pragma unroll 1
     for (int c = half; c < BN / 32; c += 2) {
       uint32_t a[32];
@@ -282,8 +331,12 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = 0.0f;
         }
+        if (p.stats_out != nullptr) ln_stats_acc(v, sd ? sd + c * 32 : nullptr, s1, s2, s3);
         epi_store32<kSplit>(p, es, row, p.out_c0 + n0 + c * 32, b, valid, v);
       }
+    }
+    if constexpr (EPI != EPI_OUTF32) {
+      if (p.stats_out != nullptr && valid) p.stats_out[row * (2 * p.n_tiles) + 2 * nt + half] = make_float4(s1, s2, s3, 0.0f);
     }
   }
 }

@@ -60,6 +60,20 @@ struct GemmParams {
   // three times (hi*hi, lo*hi, hi*lo) into the same fp32 accumulator.
   int a0_lo, a1_lo, w_lo;  // offsets of the lo halves in A0 / A1 (channels) and W (K)
   int out_lo, res_lo;      // offsets of the lo halves in out / res_in (channels)
+  // LayerNorm folded into the GEMMs around it (LYNXNet strong_cond, lynxnet.py:52-56 with the step vector added before the norm):
+  //   producer (LINEAR / RES epilogues): per row and per (N tile, warp half) the partial sums {sum r, sum r^2, sum r d, 0} of the
+  //   bf16-ROUNDED outputs r and the next norm's step vector d -> stats_out[row][parts] (float4), parts = 2 * n_tiles;
+  //   consumer (SWIGLU epilogue): mean / rstd of (r + d) over ln_channels from those sums (+ sum d, sum d^2 stored behind e), and
+  //   y[n] = rstd * (acc[n] + e[n] - mean * s[n]) + bias[n]  with  s = W~ 1,  e = W~ d,  W~ = W diag(gamma),  bias = W beta + b.
+  float4* stats_out;
+  const float* stats_d;  // [Bt][N] (row stride stats_d_bstride; 0 = one vector for every utterance); may be null (d = 0)
+  int stats_d_bstride;
+  const float4* ln_stats;
+  int ln_parts, ln_channels;
+  float ln_eps;
+  const float* ln_s;     // [N] packed column order
+  const float* ln_e;     // [Bt][N + 4]: e, then sum d, sum d^2 (row stride ln_e_bstride; 0 = shared)
+  int ln_e_bstride, ln_n;
 };
 
 template <int BN>

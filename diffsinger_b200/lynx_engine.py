@@ -40,6 +40,8 @@ class LynxWorkspace:
         mk = lambda ch: torch.empty(rows, ch, dtype=bf, device=dev)
         self.xb, self.cond = mk(eng.FMp), mk(eng.H)
         self.h, self.u, self.n, self.g, self.dw = mk(eng.C), mk(eng.C), mk(eng.C), mk(eng.I), mk(eng.I)
+        # partial sums of the folded LayerNorm (strong_cond): [rows, 2 * C / bn_c, 4] fp32
+        self.stats = torch.empty(rows, 2 * (eng.C // eng.bn_c), 4, dtype=torch.float32, device=dev) if eng.fold_ln else None
         self.cproj = None  # [L, rows, C] bf16: W_c cond of every layer, hoisted out of a sampler program's loop
         self._bufs: List[torch.Tensor] = []
         self.graphs: Dict[Tuple, torch.cuda.CUDAGraph] = {}
@@ -78,6 +80,8 @@ class LynxEngine:
         self.k = module.kernel_size
         self.act = {'ReLU': 1, 'PReLU': 2, 'SiLU': 3}[module.activation]
         self.strong = bool(module.strong_cond)
+        # strong_cond: the per-layer LayerNorm is folded into the GEMMs around it (pack()); DSB200_LYNX_LN=separate keeps the kernel
+        self.fold_ln = self.strong and os.environ.get("DSB200_LYNX_LN", "fold") != "separate"
         for name, v in (("num_channels", self.C), ("hidden_size", self.H), ("inner dim", self.I)):
             if v % 64:
                 raise nat.NativeError(f"LYNXNet {name}={v} must be a multiple of 64")
@@ -135,6 +139,15 @@ class LynxEngine:
                 nxt = layers[i + 1] if i + 1 < self.L else None
                 lw["w6c"] = torch.cat([lw["w6"], nxt["wc"]], dim=1).contiguous() if nxt else lw["w6"]
                 lw["b6c"] = lw["b6"] + nxt["bc"] if nxt else lw["b6"]
+        if self.fold_ln:
+            # LayerNorm(u + d) -> Conv1d(C, 2I, 1) as ONE GEMM over the raw stream u:  y = rstd (W~ u + W~ d - mean W~ 1) + (W beta + b),
+            # W~ = W diag(gamma).  mean / rstd come from partial sums the producing GEMM's epilogue writes (ops.gemm: stats_out);
+            # s = W~ 1 uses the bf16-rounded W~ the tensor cores multiply with, so that the mean cancels exactly.
+            for i, lw in enumerate(layers):
+                w2f = f32(sd[f"residual_layers.{i}.convmodule.net.2.weight"])[:, :, 0][perm]
+                lw["w2t"] = (w2f * lw["ln_g"][None, :]).to(bf).contiguous()
+                lw["ln_s"] = lw["w2t"].float().sum(dim=1).contiguous()
+                lw["b2t"] = (lw["b2"] + w2f @ lw["ln_b"]).contiguous()
         self.weights_key = self.weights_fingerprint(module)
         self._vec_cache.clear()
         for ws in self.workspaces.values():
@@ -154,6 +167,17 @@ class LynxEngine:
             rows.append(v if self.strong else v + l.conditioner_projection.bias)
         out = torch.stack(rows, dim=0)  # [L, n_times * Bt, C]
         return out.reshape(self.L, -1, Bt, self.C).permute(1, 0, 2, 3).float().contiguous()
+
+    @torch.no_grad()
+    def ln_vectors(self, vecs: torch.Tensor) -> torch.Tensor:
+        """Folded LayerNorm: fp32 [..., L, Bt, 2I + 4] = (W~_l d, sum d, sum d^2, 0, 0) for step vectors d = vecs[..., l, b, :]."""
+        out = torch.zeros(*vecs.shape[:-1], 2 * self.I + 4, dtype=torch.float32, device=vecs.device)
+        for l, lw in enumerate(self.w["layers"]):
+            d = vecs[..., l, :, :]
+            out[..., l, :, :2 * self.I] = d @ lw["w2t"].float().t()
+            out[..., l, :, 2 * self.I] = d.sum(-1)
+            out[..., l, :, 2 * self.I + 1] = (d * d).sum(-1)
+        return out.contiguous()
 
     def workspace(self, B: int, T: int) -> LynxWorkspace:
         key = (B, T, _st())
@@ -186,14 +210,32 @@ class LynxEngine:
         return -(-B // n_chunks)
 
     # ------------------------------------------------------------------ one evaluation
-    def eval(self, ws: LynxWorkspace, x_f32: torch.Tensor, vecs: torch.Tensor, out_f32: torch.Tensor, hoisted: bool = False) -> int:
+    def eval(self, ws: LynxWorkspace, x_f32: torch.Tensor, vecs: torch.Tensor, out_f32: torch.Tensor, hoisted: bool = False,
+             evecs: torch.Tensor | None = None) -> int:
         """x / out: fp32 [B, T, F*M] time-major; vecs: fp32 [L, Bt, C] step vectors of this evaluation.  hoisted: ws.cproj
-        holds W_c cond of every layer (strong_cond = False only).  Returns #launches."""
+        holds W_c cond of every layer (strong_cond = False only).  evecs: ln_vectors(vecs) (folded LayerNorm; computed here when
+        the caller has none).  Returns #launches."""
         hoisted = hoisted and not self.strong
         w, B, T, Cc = self.w, ws.B, ws.T, self.C
         rows = B * T
         Bt = vecs.shape[1]
         ops.cast_bf16(ws.xb, x_f32.view(rows, self.FM))
+        if self.fold_ln:
+            if evecs is None:
+                evecs = self.ln_vectors(vecs)
+            st = ws.stats
+            ops.gemm(ops.EPI_LINEAR, self.bn_c, B, T, ws.xb, w["w_in_c"], ws.u, a1=ws.cond, bias=w["b_in_c"], act=ops.ACT_NONE,
+                     stats_out=st, stats_d=vecs[0])
+            for i, lw in enumerate(w["layers"]):
+                last = i + 1 == self.L
+                ops.gemm(ops.EPI_SWIGLU, self.bn_g, B, T, ws.u, lw["w2t"], ws.g, bias=lw["b2t"],
+                         ln=dict(stats=st, channels=Cc, eps=1e-5, s=lw["ln_s"], e=evecs[i]))
+                ops.dwconv(ws.dw, ws.g, lw["dw_w"], lw["dw_b"], B, T, self.k, self.act, lw["slope"])
+                ops.gemm(ops.EPI_RES, self.bn_c, B, T, ws.dw, lw["w6c"], ws.u, a1=None if last else ws.cond, vec=lw["b6c"], vec_bstride=0,
+                         res=ws.u, stats_out=None if last else st, stats_d=None if last else vecs[i + 1])
+            ops.layernorm(ws.n, ws.u, w["norm_g"], w["norm_b"], 1e-5)
+            ops.gemm(ops.EPI_OUTF32, self.bn_o, B, T, ws.n, w["w_out"], out_f32.view(rows, self.FM), bias=w["b_out"], n_real=self.FM)
+            return 3 * self.L + 4
         if self.strong:
             ops.gemm(ops.EPI_LINEAR, self.bn_c, B, T, ws.xb, w["w_in_c"], ws.u, a1=ws.cond, bias=w["b_in_c"], act=ops.ACT_NONE)
             for i, lw in enumerate(w["layers"]):
@@ -253,7 +295,8 @@ class LynxEngine:
         if vecs is None:
             if len(self._vec_cache) > 16:
                 self._vec_cache.clear()
-            vecs = self._vec_cache[vkey] = self.step_vectors(module, torch.tensor(prog.times, dtype=torch.float32), B, False)
+            vecs = self.step_vectors(module, torch.tensor(prog.times, dtype=torch.float32), B, False)
+            vecs = self._vec_cache[vkey] = (vecs, self.ln_vectors(vecs) if self.fold_ln else None)
         gkey = (id(prog), vkey)
         if not use_graph or len(prog.ops) > 1024:
             ws.last_launches = pre + self._run_ops(ws, prog, bufs, vecs, hoist)
@@ -276,7 +319,7 @@ class LynxEngine:
         launches = 0
         for kind, dst, time, srcs, coefs in prog.ops:
             if kind == nat.DS_OP_EVAL:
-                launches += self.eval(ws, bufs[srcs[0]], vecs[time], bufs[dst], hoisted)
+                launches += self.eval(ws, bufs[srcs[0]], vecs[0][time], bufs[dst], hoisted, None if vecs[1] is None else vecs[1][time])
             else:
                 ops.lincomb(bufs[dst], [bufs[s] for s in srcs], coefs)
                 launches += 1

@@ -183,6 +183,16 @@ typedef struct {
   void* out2;    /* epilogue 2 (residual), optional: second bf16 output LeakyReLU(out, slope2), same ld / offset as out --
                   * the pre-activated copy the next convolution of a HiFi-GAN ResBlock reads (nsf_hifigan/models.py:60-67) */
   float slope2;
+  /* LayerNorm folded into the GEMMs around it (the reference normalises between them: lynxnet.py:52-56 LayerNorm -> Conv1d(dim,
+   * 2*inner, 1) -> SwiGLU, with the step vector added to the norm's input, :82-89).  Producer side (epilogues 0 / 2): per frame and
+   * per (N tile, warp half) the partial sums {sum r, sum r^2, sum r*d} over the bf16 outputs r and the NEXT norm's step vector d
+   * (stats_d, [B or 1][N]) are written to stats_out[frame][2 * n_tiles] (float4).  Consumer side (epilogue 5): the frame's mean /
+   * rstd of (r + d) over ln_channels come from those sums, and y[n] = rstd * (acc[n] + e[n] - mean * s[n]) + bias[n] with the
+   * host-folded s = W~ 1, e = W~ d, W~ = W diag(gamma), bias = W beta + b; ln_e rows are [N + 4]: e, then sum d, sum d^2.  All NULL /
+   * zero: plain epilogues. */
+  void* stats_out; const float* stats_d; int32_t stats_d_bstride;
+  const void* ln_stats; int32_t ln_parts; int32_t ln_channels; float ln_eps;
+  const float* ln_s; const float* ln_e; int32_t ln_e_bstride;
 } ds_gemm_desc;
 int ds_debug_gemm(const ds_gemm_desc* d, void* stream);
 int ds_gemm(const ds_gemm_desc* d, void* stream);

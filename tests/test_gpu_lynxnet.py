@@ -43,6 +43,7 @@ def test_forward_matches_reference_golden(tag):
     (512, 6, 128, 1, 31, "PReLU", False, 2, 300),  # default acoustic backbone
     (256, 3, 64, 1, 31, "SiLU", True, 3, 131),
     (192, 2, 24, 2, 7, "ReLU", False, 1, 77),
+    (1024, 6, 128, 1, 31, "PReLU", True, 2, 300),  # configs/acoustic.yaml:72-78 as shipped: 6 x 1024, strong_cond (folded LayerNorm)
 ])
 def test_forward_matches_oracle_real_sizes(C, L, M, F, k, act, strong, B, T):
     sd = random_lynx_state_dict(M, F, L, C, 256, expansion_factor=2, kernel_size=k, activation=act, seed=C + L)
