@@ -161,15 +161,15 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
   uint64_t* w_full = bars;
   uint64_t* w_empty = w_full + kStackStages;
   uint64_t* x_loc = w_empty + kStackStages;   // this CTA's own k-block of x~ is written (epilogue arrival)
-  uint64_t* x_rem = x_loc + 1;                // the KB-1 peer blocks have landed: 1 arrival (arming) + (KB-1) * 16 KB
-  uint64_t* z_loc = x_rem + 1;
-  uint64_t* z_rem = z_loc + 1;
-  uint64_t* acc1_full = z_rem + 1;
+  uint64_t* x_rem = x_loc + 1;                // [KB-1]: peer block (r + 1 + i) % KB has landed: 1 arrival (arming) + 16 KB
+  uint64_t* z_loc = x_rem + (KB - 1);
+  uint64_t* z_rem = z_loc + 1;                // [KB-1]
+  uint64_t* acc1_full = z_rem + (KB - 1);
   uint64_t* acc2_full = acc1_full + 1;
   uint64_t* aux_full = acc2_full + 1;         // head input cast done
   uint64_t* halo_full = aux_full + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(halo_full + 1);
-  constexpr uint32_t kRemBytes = (KB - 1) * kStackZTile;
+  constexpr uint32_t kRemBytes = kStackZTile;  // one peer block per barrier: the consumer starts on a block as soon as IT has landed
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // the shuffle tells the compiler the value is warp-uniform
   const int lane = threadIdx.x & 31;
@@ -199,17 +199,22 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
       mbar_init(&w_empty[i], 1);
     }
     mbar_init(x_loc, 1);
-    mbar_init(x_rem, 1);
     mbar_init(z_loc, 1);
-    mbar_init(z_rem, 1);
+    for (int i = 0; i < KB - 1; ++i) {
+      mbar_init(&x_rem[i], 1);
+      mbar_init(&z_rem[i], 1);
+    }
     mbar_init(acc1_full, 1);
     mbar_init(acc2_full, 1);
     mbar_init(aux_full, 1);
     mbar_init(halo_full, 1);
     fence_barrier_init();
-    // phase 0 of the REMOTE blocks: this CTA's arrival + the 16 KB each of the KB-1 owners will send
-    if (dbg & 8) { mbar_arrive(x_rem); mbar_arrive(z_rem); }
-    else { mbar_arrive_expect_tx(x_rem, kRemBytes); mbar_arrive_expect_tx(z_rem, kRemBytes); }
+    // phase 0 of the REMOTE blocks: this CTA's arrival + the 16 KB its owner will send (later phases are armed by the epilogue
+    // lanes that send this CTA's own block of the same phase: publish())
+    for (int i = 0; i < KB - 1; ++i) {
+      if (dbg & 8) { mbar_arrive(&x_rem[i]); mbar_arrive(&z_rem[i]); }
+      else { mbar_arrive_expect_tx(&x_rem[i], kRemBytes); mbar_arrive_expect_tx(&z_rem[i], kRemBytes); }
+    }
   }
   // x~ starts as zeros: halo rows outside the utterance ARE the conv's zero padding and are never written
   for (uint32_t o = threadIdx.x * 16u; o < KB * kStackXTile; o += kGemmThreads * 16u) st_shared_v4(smem_u32(xs) + o, 0, 0, 0, 0);
@@ -315,11 +320,6 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
           for (int k = 0; k < 4; ++k) umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (!fresh) || k != 0);
         }
       };
-      auto rearm = [&](uint64_t* bar) {
-        if (!lead) return;
-        if (dbg & 8) mbar_arrive(bar);
-        else mbar_arrive_expect_tx(bar, kRemBytes);
-      };
       // head: relu(input_projection(x)) -- A = the cast input in the z buffer                wavenet.py:86-88
       bwait(aux_full, 0);
       tc_fence_after();
@@ -338,10 +338,9 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
             bwait(x_loc, lp);
             tc_fence_after();
             mark(l, 0);
-          } else if (j == 1) {
-            bwait(x_rem, lp);
-            rearm(x_rem);  // phase l+1 (the last one, L, carries s1)
-            mark(l, 1);
+          } else {
+            bwait(&x_rem[j - 1], lp);
+            if (j == KB - 1) mark(l, 1);
           }
           const uint64_t db = w_wait();
           mma4(tm_acc1, dx + ((r + j) % KB) * kXT + kStackHalo * 8, db, id128, j == 0);
@@ -365,10 +364,9 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
             bwait(z_loc, lp);
             tc_fence_after();
             mark(l, 3);
-          } else if (j == 1) {
-            bwait(z_rem, lp);
-            rearm(z_rem);
-            mark(l, 4);
+          } else {
+            bwait(&z_rem[j - 1], lp);
+            if (j == KB - 1) mark(l, 4);
           }
           const uint64_t db = w_wait();
           if (j == KB - 1) mark(l, 5);
@@ -383,7 +381,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
       // be read by a slower peer's last GEMM-2)                                                  wavenet.py:96-98
       for (int j = 0; j < KB; ++j) {
         if (j == 0) { bwait(x_loc, L & 1); tc_fence_after(); }
-        else if (j == 1) bwait(x_rem, L & 1);
+        else bwait(&x_rem[j - 1], L & 1);
         const uint64_t db = w_wait();
         mma4(tm_acc2, dx + ((r + j) % KB) * kXT + kStackHalo * 8, db, id64, j == 0);
         w_release();
@@ -392,7 +390,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
       // output_projection: s2 travels in the z buffer                                            wavenet.py:99
       for (int j = 0; j < KB; ++j) {
         if (j == 0) { bwait(z_loc, L & 1); tc_fence_after(); }
-        else if (j == 1) bwait(z_rem, L & 1);
+        else bwait(&z_rem[j - 1], L & 1);
         const uint64_t db = w_wait();
         mma4(tm_acc1, dz + ((r + j) % KB) * kZT, db, idout, j == 0);
         w_release();
@@ -481,16 +479,26 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
     };
     // all-gather of this CTA's slice: local arrival + one bulk copy per peer, peers in the order they will consume
     // (the KB-1 copies are issued by lane 0 of KB-1 different warps: issuing one costs a thread ~285 cycles)
-    auto publish = [&](uint32_t tile_a, uint32_t body_off, uint64_t* bar_loc, uint64_t* bar_rem) {
+    // Copy j goes to the peer that consumes this block at ITS stage j + 1, i.e. completes that peer's bar_rem[j]; the same lane arms
+    // this CTA's own bar_rem[j] for the phase being published (`arm`; phase 0 was armed at start-up) -- its previous phase is over:
+    // the MMAs that read that block finished before the accumulator this epilogue just consumed was committed.
+    auto publish = [&](uint32_t tile_a, uint32_t body_off, uint64_t* bar_loc, uint64_t* bar_rem, bool arm) {
       fence_proxy_async_smem();
       tc_fence_before();
       epi_bar_sync();
       if (elect_one()) {
-        const int j = warp - 4;  // 0 .. 7
-        if (j == KB - 1) mbar_arrive(bar_loc);
-        if (j < KB - 1 && !(dbg & 8)) {
-          const uint32_t peer = static_cast<uint32_t>((r + KB - 1 - j) % KB);
-          bulk_copy_to_peer(tile_a + body_off, tile_a + body_off, kStackZTile, smem_u32(bar_rem), peer);
+        if (warp == 5) mbar_arrive(bar_loc);
+        if (warp == 4) {  // ONE lane sends all peer copies, in the order the peers consume them: the first lands after 1/(KB-1) of the time
+          for (int j = 0; j < KB - 1; ++j) {
+            if (arm) {
+              if (dbg & 8) mbar_arrive(&bar_rem[j]);
+              else mbar_arrive_expect_tx(&bar_rem[j], kRemBytes);
+            }
+            if (!(dbg & 8)) {
+              const uint32_t peer = static_cast<uint32_t>((r + KB - 1 - j) % KB);
+              bulk_copy_to_peer(tile_a + body_off, tile_a + body_off, kStackZTile, smem_u32(&bar_rem[j]), peer);
+            }
+          }
         }
       }
     };
@@ -535,7 +543,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
       }
       put_edges(0, o);
       put_row(xrow_a, row + kStackHalo, o);
-      publish(xrow_a, kStackHalo * 128u, x_loc, x_rem);
+      publish(xrow_a, kStackHalo * 128u, x_loc, x_rem, false);
       get_halo(0);
     }
 
@@ -573,7 +581,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
           }
         }
         put_row(zrow_a, row, zp);
-        publish(zrow_a, 0u, z_loc, z_rem);
+        publish(zrow_a, 0u, z_loc, z_rem, l > 0);
         if (leader_thread) mark(l, 7);
       }
       // ---- residual: x~' = (x~ + R) / sqrt(2) + rvec_l  (not after the last layer: wavenet.py:92-94 discards it)
@@ -604,7 +612,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
         }
         put_edges(l + 1, o);  // first: the neighbour tile's wait for these packets is the longer path
         put_row(xrow_a, row + kStackHalo, o);
-        publish(xrow_a, kStackHalo * 128u, x_loc, x_rem);
+        publish(xrow_a, kStackHalo * 128u, x_loc, x_rem, true);
         if (leader_thread) mark(l, 9);
         get_halo(l + 1);
       }
@@ -624,7 +632,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
       for (int i = 0; i < 16; ++i)
         o[i] = pack_bf16((__uint_as_float(a[2 * i]) + bb[2 * i]) * p.inv_sqrt_L, (__uint_as_float(a[2 * i + 1]) + bb[2 * i + 1]) * p.inv_sqrt_L);
       put_row(xrow_a, row + kStackHalo, o);
-      publish(xrow_a, kStackHalo * 128u, x_loc, x_rem);
+      publish(xrow_a, kStackHalo * 128u, x_loc, x_rem, true);
     }
     // ---- s2 = relu(skip_projection(s1) + b)                                                        wavenet.py:97-98
     {
@@ -641,7 +649,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
       for (int i = 0; i < 16; ++i)
         o[i] = pack_bf16(fmaxf(__uint_as_float(a[2 * i]) + bb[2 * i], 0.0f), fmaxf(__uint_as_float(a[2 * i + 1]) + bb[2 * i + 1], 0.0f));
       put_row(zrow_a, row, o);
-      publish(zrow_a, 0u, z_loc, z_rem);
+      publish(zrow_a, 0u, z_loc, z_rem, true);
     }
     // ---- output projection -> fp32 [B][T][FM]: this CTA's nout columns, 16 per warp half             wavenet.py:99
     {
