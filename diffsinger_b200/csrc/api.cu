@@ -227,15 +227,17 @@ static int launch_gemm(int BN, int epi, const GemmParams& p, cudaStream_t st, bo
   return fail(DS_ERR_INVALID, "no GEMM instantiation for BN=%d epilogue=%d", BN, epi);
 }
 
-static int launch_layer_grp(const LayerParams& p, int max_dil, cudaStream_t st) {
+static int launch_layer_grp(const LayerParams& p, int max_dil, cudaStream_t st, bool split) {
   static bool attr_done = false;
   if (!attr_done) {
-    CUDA_TRY(cudaFuncSetAttribute(ds_layer_grp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGrpSmemMax));
+    CUDA_TRY(cudaFuncSetAttribute(ds_layer_grp_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGrpSmemMax));
+    CUDA_TRY(cudaFuncSetAttribute(ds_layer_grp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGrpSmemMax));
     attr_done = true;
   }
   const int max_pairs = g_num_sms / 2;
   const int pairs = p.total_tiles < max_pairs ? p.total_tiles : max_pairs;
-  ds_layer_grp_kernel<<<2 * pairs, kGemmThreads, grp_smem_bytes(max_dil), st>>>(p);
+  if (split) ds_layer_grp_kernel<true><<<2 * pairs, kGemmThreads, grp_smem_bytes(max_dil), st>>>(p);
+  else ds_layer_grp_kernel<false><<<2 * pairs, kGemmThreads, grp_smem_bytes(max_dil), st>>>(p);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -366,7 +368,8 @@ extern "C" int ds_plan_create(const ds_wavenet_config* cfg, ds_plan** out) {
     return fail(DS_ERR_INVALID, "precision=%d must be 0 (bf16) or 1 (fp32-accurate)", cfg->precision);
   }
   p->S = p->split ? 2 : 1;
-  if (p->split) p->fused = 0;
+  // (the fused layer kernel has a split instantiation too -- ds_layer_grp_kernel<true> -- taken by sessions of at least one wave of
+  // tile pairs, session_use_fused; smaller fp32-accurate sessions stay on the unfused GEMMs)
   p->has_small = (!p->split && p->BN_G == 256) ? 1 : 0;
   // whole-network kernel: C = 256 (4 CTAs per tile, the narrow gate pack's 128-row passes) or C = 192 (3 CTAs; the regular pack
   // already has 128-row passes and 64-row boxes there)
@@ -379,7 +382,7 @@ extern "C" int ds_plan_create(const ds_wavenet_config* cfg, ds_plan** out) {
     // the gate epilogue then reads its 2C f16 values per frame from HBM with per-lane row accesses and becomes the
     // critical role (epilogue alone 154 -> 210 us), so the kernel stays at ~357 us and the per-call precompute is extra.
     const char* he = getenv("DSB200_HOIST");
-    p->hoist = (p->fused == 5 && he && atoi(he) == 1) ? 1 : 0;
+    p->hoist = (p->fused == 5 && !p->split && he && atoi(he) == 1) ? 1 : 0;
   }
   plan_layout(p);
   *out = p;
@@ -532,6 +535,16 @@ static bool session_is_medium(const ds_plan* p, int B, int T) {
   return pair_tiles >= kMediumLo && pair_tiles <= kMediumHi;
 }
 
+// fp32-accurate plans: the fused kernel's split instantiation pays from one wave of tile pairs on; below that the unfused GEMMs
+// (tiles over frames x channels) fill the SMs better.  DSB200_FP32_FUSED=0/1 forces the choice.
+static bool session_use_fused(const ds_plan* p, int B, int T) {
+  if (!p->fused) return false;
+  if (!p->split) return true;
+  const char* se = getenv("DSB200_FP32_FUSED");
+  if (se) return atoi(se) != 0;
+  return B * ceil_div(T, 256) >= (g_num_sms ? g_num_sms : 148) / 2;
+}
+
 // Launch-bound sessions (a handful of 128-frame tiles: the batch-1 .ds segments, the variance predictors) run every backbone
 // evaluation as ONE launch of ds_stack_kernel: a 4-CTA cluster per tile, all clusters co-resident (neighbouring tiles exchange
 // edge frames through flags in global memory, so a cluster that is not resident would dead-lock its neighbours).
@@ -645,13 +658,13 @@ extern "C" int ds_session_create(ds_plan* plan, int32_t B, int32_t T, int32_t ma
   r = r ? r : make_act_map(&s->tm_s2, s->ws + s->o_s2, plan->C * Sm, T, B);
   if (plan->fused == 5)
     for (int k = 0; (1 << k) <= plan->max_dil; ++k) {
-      r = r ? r : make_act_map(&s->tm_xh[0][k], s->ws + s->o_xt, plan->C, T, B, 128 + 2 * (1 << k));
-      r = r ? r : make_act_map(&s->tm_xh[1][k], s->ws + s->o_xt1, plan->C, T, B, 128 + 2 * (1 << k));
+      r = r ? r : make_act_map(&s->tm_xh[0][k], s->ws + s->o_xt, plan->C * Sm, T, B, 128 + 2 * (1 << k));
+      r = r ? r : make_act_map(&s->tm_xh[1][k], s->ws + s->o_xt1, plan->C * Sm, T, B, 128 + 2 * (1 << k));
     }
   if (plan->fused == 5) {
-    r = r ? r : make_store_map(&s->tm_zs, s->ws + s->o_z, plan->L * plan->C, T, B);
-    r = r ? r : make_store_map(&s->tm_xs[0], s->ws + s->o_xt, plan->C, T, B);
-    r = r ? r : make_store_map(&s->tm_xs[1], s->ws + s->o_xt1, plan->C, T, B);
+    r = r ? r : make_store_map(&s->tm_zs, s->ws + s->o_z, plan->L * plan->C * Sm, T, B);
+    r = r ? r : make_store_map(&s->tm_xs[0], s->ws + s->o_xt, plan->C * Sm, T, B);
+    r = r ? r : make_store_map(&s->tm_xs[1], s->ws + s->o_xt1, plan->C * Sm, T, B);
   }
   if (r) {
     delete s;
@@ -766,11 +779,12 @@ static int session_fused_layer(ds_session* s, int l, int time_index, cudaStream_
   lp.a_slot = halo_a_slot_bytes(p->max_dil); lp.n_a = grp_stages(p->max_dil);
   lp.tmZs = s->tm_zs; lp.tmXs = s->tm_xs[(l + 1) & 1];
   lp.bias1h = (const uint16_t*)(pk + p->o_b1h) + (size_t)l * 2 * C;
+  lp.x_lo = C; lp.cond_lo = p->H; lp.z_lo = L * C; lp.w1_lo = p->K1; lp.w2_lo = C;  // read by the split instantiation only
   if (s->o_cproj) {
     lp.cproj = (const uint16_t*)(s->ws + s->o_cproj) + (size_t)l * B * T * 2 * C; lp.ld_cproj = 2 * C;
     lp.kb_h = 0;  // the conditioner K blocks are not run per evaluation
   }
-  return launch_layer_grp(lp, p->max_dil, st);
+  return launch_layer_grp(lp, p->max_dil, st, p->split != 0);
 }
 
 // One backbone evaluation = 2L+4 launches on `st` (WaveNet.forward, wavenet.py:75-107).
@@ -855,7 +869,7 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
     bool prev;
     explicit PdlScope(bool on) : prev(t_pdl) { t_pdl = on; }
     ~PdlScope() { t_pdl = prev; }
-  } pdl_scope((s->small || s->medium || !s->plan->fused) && s->pdl);
+  } pdl_scope((s->small || s->medium || !session_use_fused(s->plan, s->B, s->T)) && s->pdl);
   CUDA_TRY(launch_k(f32_to_bf16_pad_kernel, dim3(ew_grid(rows * p->FMp / 4, 256)), dim3(256), 0, st, xb, x, rows, p->FM, p->FMp,
                     (long)p->FMp * S, split ? p->FMp : 0));
   ++*launches;
@@ -888,7 +902,7 @@ static int session_eval(ds_session* s, const float* x, int time_index, float* ou
   DS_TRY(launch_gemm(bnC, EPI_LINEAR, g, st, split));
   ++*launches;
   g.has_out_map = 0;
-  if (p->fused && !small && !s->medium) {
+  if (session_use_fused(p, B, T) && !small && !s->medium) {
     for (int l = 0; l < L; ++l) {
       DS_TRY(session_fused_layer(s, l, time_index, st));
       ++*launches;
@@ -991,7 +1005,7 @@ static int run_ops(ds_session* s, const ds_op* ops, int n_ops, float* const* buf
     bool prev;
     explicit PdlScope(bool on) : prev(t_pdl) { t_pdl = on; }
     ~PdlScope() { t_pdl = prev; }
-  } pdl_scope((s->stack || s->small || s->medium || !s->plan->fused) && s->pdl);
+  } pdl_scope((s->stack || s->small || s->medium || !session_use_fused(s->plan, s->B, s->T)) && s->pdl);
   s->eval_seq = 0;
   // DSB200_FUSE_UPDATE=1: bit-identical results and half the launches, but measured 1-3 % SLOWER than the separate lincomb launch
   // (tools/stack_time.py): the small update kernel sits in a programmatic-dependent-launch chain and overlaps the next evaluation's

@@ -57,6 +57,9 @@ struct LayerParams {
   // (kb_h conditioner K blocks run inside the kernel and bias1h is added instead).
   const uint16_t* cproj;
   int ld_cproj;
+  // fp32-accurate ("split") instantiation: every bf16 operand is hi = bf16(v) followed, `*_lo` elements further along its channel
+  // / K axis, by lo = bf16(v - hi); each K stage is issued three times (hi*hi, lo*hi, hi*lo) into the same accumulator
+  int x_lo, cond_lo, z_lo, w1_lo, w2_lo;
 };
 
 constexpr uint32_t kLayerABytes = 128 * 128;  // 128 frames x 64 bf16
@@ -219,10 +222,77 @@ __device__ __forceinline__ void grp_epilogue_res(const LayerParams& p, uint32_t 
   }
 }
 
+// fp32-accurate instantiation: gate and residual epilogues in full precision (expf / tanhf, fp32 bias), outputs as hi / lo bf16
+// pairs (two staged TMA stores per 32 x 32 sub-tile: hi at its channel, lo `*_lo` channels further).
+__device__ __forceinline__ void split_store_tile(const CUtensorMap* map, uint32_t sw, int lane, const float (&v)[32], int c0, int lo_off,
+                                                 int tw0, int b, bool any) {
+  uint32_t hi[16], lo[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const float a = v[2 * i], c = v[2 * i + 1];
+    const float ah = __bfloat162float(__float2bfloat16_rn(a)), ch = __bfloat162float(__float2bfloat16_rn(c));
+    hi[i] = pack_bf16(a, c);
+    lo[i] = pack_bf16(a - ah, c - ch);
+  }
+  warp_store_tile(map, sw, lane, hi, c0, tw0, b, any);
+  warp_store_tile(map, sw, lane, lo, c0 + lo_off, tw0, b, any);
+}
+__device__ __forceinline__ void grp_epilogue_gate_split(const LayerParams& p, uint32_t taddr, int idx, int b, int tw0, int half, int lane,
+                                                        uint32_t sw) {
+  const float* bias = p.bias1 + idx * 256;
+#pragma unroll 1
+  for (int k = 0; k < 2; ++k) {
+    const int c = half + 2 * k;
+    uint32_t g[32], f[32];
+    tmem_ld_32x32(taddr + c * 32, g);
+    tmem_ld_32x32(taddr + 128 + c * 32, f);
+    float bg[32], bf[32], z[32];
+    ld_f32x32(bias + c * 32, bg);
+    ld_f32x32(bias + 128 + c * 32, bf);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 32; ++j) z[j] = sigmoid_accurate(__uint_as_float(g[j]) + bg[j]) * tanhf(__uint_as_float(f[j]) + bf[j]);
+    split_store_tile(&p.tmZs, sw, lane, z, p.z_c0 + idx * 128 + c * 32, p.z_lo, tw0, b, tw0 < p.T);
+  }
+}
+__device__ __forceinline__ void grp_epilogue_res_split(const LayerParams& p, uint32_t taddr, int idx, int b, int tw0, const __nv_bfloat16* xin,
+                                                       int half, int lane, uint32_t sw, bool live) {
+  const int n0 = idx * 256;
+  const float* rv = p.rvec + static_cast<size_t>(b) * p.vec_bstride + n0;
+#pragma unroll 1
+  for (int k = 0; k < 4; ++k) {
+    const int c = half + 2 * k;
+    uint32_t a[32];
+    tmem_ld_32x32(taddr + c * 32, a);
+    float rr[32], v[32];
+    ld_f32x32(rv + c * 32, rr);
+    uint4 xh[4], xl[4];
+    ld_x4(xin + c * 32, xh);
+    ld_x4(xin + p.x_lo + c * 32, xl);
+    tmem_ld_wait();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint32_t wh[4] = {xh[i].x, xh[i].y, xh[i].z, xh[i].w};
+      const uint32_t wl[4] = {xl[i].x, xl[i].y, xl[i].z, xl[i].w};
+#pragma unroll
+      for (int h = 0; h < 4; ++h) {
+        const int q = 8 * i + 2 * h;
+        const float x0 = __uint_as_float(wh[h] << 16) + __uint_as_float(wl[h] << 16);
+        const float x1 = __uint_as_float(wh[h] & 0xffff0000u) + __uint_as_float(wl[h] & 0xffff0000u);
+        v[q] = live ? fmaf(__uint_as_float(a[q]) + x0, 0.70710678118654752f, rr[q]) : 0.0f;
+        v[q + 1] = live ? fmaf(__uint_as_float(a[q + 1]) + x1, 0.70710678118654752f, rr[q + 1]) : 0.0f;
+      }
+    }
+    split_store_tile(&p.tmXs, sw, lane, v, n0 + c * 32, p.x_lo, tw0, b, tw0 < p.T);
+  }
+}
+
 // Requires C % 256 == 0, H % 128 == 0 (two-block 1x1 stages) and 2^(cycle-1) <= 16.  LayerParams as for the halo kernel;
 // a_slot = halo_a_slot_bytes(max_dil), n_a = grp_stages(max_dil).
+template <bool kSplit>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
+  constexpr int kSub = kSplit ? 3 : 1;  // split: (A hi, W hi), (A lo, W hi), (A hi, W lo)
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
@@ -297,15 +367,19 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
       };
       auto end_stage = [&]() { if (++st == NS) { st = 0; ph ^= 1; } };
       // 1x1 stages: blocks [k, k + n) of activation map `am` (channel offset ac0) against weight columns wk0 + ...
-      auto one_by_one = [&](const CUtensorMap* am, int ac0, const CUtensorMap* wm, int wk0, int nblk, int row0, int t0, int b) {
+      auto one_by_one = [&](const CUtensorMap* am, int ac0, int a_lo, const CUtensorMap* wm, int wk0, int w_lo, int nblk, int row0, int t0,
+                            int b) {
         for (int k = 0; k < nblk; k += 2) {
           const int n = nblk - k < 2 ? nblk - k : 2;
-          uint8_t* s = begin_stage(n * (kOne + kPairBBytes));
-          for (int j = 0; j < n && load; ++j) {
-            tma_load_3d_pair(am, &full[st], s + j * kOne, ac0 + (k + j) * 64, t0, b);
-            tma_load_2d_pair(wm, &full[st], s + 2 * kOne + j * kPairBBytes, wk0 + (k + j) * 64, row0);
+#pragma unroll 1
+          for (int sub = 0; sub < kSub; ++sub) {
+            uint8_t* s = begin_stage(n * (kOne + kPairBBytes));
+            for (int j = 0; j < n && load; ++j) {
+              tma_load_3d_pair(am, &full[st], s + j * kOne, ac0 + (k + j) * 64 + (sub == 1 ? a_lo : 0), t0, b);
+              tma_load_2d_pair(wm, &full[st], s + 2 * kOne + j * kPairBBytes, wk0 + (k + j) * 64 + (sub == 2 ? w_lo : 0), row0);
+            }
+            end_stage();
           }
-          end_stage();
         }
       };
       LayerJobs jobs(n_local, p.p1, p.p2, true);
@@ -317,18 +391,22 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
         if (kind == 0) {
           const int row0 = p.w1_row0 + idx * 256 + rank * 128;
           for (int cb = 0; cb < p.kb_c; ++cb) {
-            uint8_t* s = begin_stage(halo_bytes + 3 * kPairBBytes);
-            if (load) tma_load_3d_pair(&p.tmXh, &full[st], s, cb * 64, t0 - p.dil, b);
+#pragma unroll 1
+            for (int sub = 0; sub < kSub; ++sub) {
+              uint8_t* s = begin_stage(halo_bytes + 3 * kPairBBytes);
+              if (load) tma_load_3d_pair(&p.tmXh, &full[st], s, cb * 64 + (sub == 1 ? p.x_lo : 0), t0 - p.dil, b);
 #pragma unroll
-            for (int tap = 0; tap < 3 && load; ++tap)
-              tma_load_2d_pair(&p.tmW1, &full[st], s + p.a_slot + tap * kPairBBytes, (tap * p.kb_c + cb) * 64, row0);
-            end_stage();
+              for (int tap = 0; tap < 3 && load; ++tap)
+                tma_load_2d_pair(&p.tmW1, &full[st], s + p.a_slot + tap * kPairBBytes, (tap * p.kb_c + cb) * 64 + (sub == 2 ? p.w1_lo : 0),
+                                 row0);
+              end_stage();
+            }
           }
-          one_by_one(&p.tmCond, 0, &p.tmW1, 3 * p.kb_c * 64, p.kb_h, row0, t0, b);
+          one_by_one(&p.tmCond, 0, p.cond_lo, &p.tmW1, 3 * p.kb_c * 64, p.w1_lo, p.kb_h, row0, t0, b);
         } else {
           if (idx == 0) mbar_wait(z_full, j & 1);  // this CTA's z rows of tile j are in global memory
           const int row0 = p.w2_row0 + idx * 256 + rank * 128;
-          one_by_one(&p.tmZ, p.z_c0, &p.tmW2, 0, p.kb_c, row0, t0, b);
+          one_by_one(&p.tmZ, p.z_c0, p.z_lo, &p.tmW2, 0, p.w2_lo, p.kb_c, row0, t0, b);
         }
       }
     }
@@ -355,13 +433,16 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
       auto one_by_one = [&](uint32_t tmem_d, int nblk, bool fresh_first, uint32_t as) {
         for (int k = 0; k < nblk; k += 2) {
           const int n = nblk - k < 2 ? nblk - k : 2;
-          mbar_wait(&full[st], ph);
-          tc_fence_after();
-          const uint32_t s = smem_u32(smem + st * stage_bytes);
-          for (int jj = 0; jj < n; ++jj)
-            mma4(tmem_d, make_kmajor_sw128_desc(s + jj * kOne), make_kmajor_sw128_desc(s + 2 * kOne + jj * kPairBBytes),
-                 fresh_first && k == 0 && jj == 0);
-          release(k + n >= nblk, as);
+#pragma unroll 1
+          for (int sub = 0; sub < kSub; ++sub) {
+            mbar_wait(&full[st], ph);
+            tc_fence_after();
+            const uint32_t s = smem_u32(smem + st * stage_bytes);
+            for (int jj = 0; jj < n; ++jj)
+              mma4(tmem_d, make_kmajor_sw128_desc(s + jj * kOne), make_kmajor_sw128_desc(s + 2 * kOne + jj * kPairBBytes),
+                   fresh_first && k == 0 && jj == 0 && sub == 0);
+            release(k + n >= nblk && sub == kSub - 1, as);
+          }
         }
       };
       LayerJobs jobs(n_local, p.p1, p.p2, true);
@@ -373,14 +454,17 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
         const uint32_t tmem_d = tmem_base + as * 256;
         if (kind == 0) {
           for (int cb = 0; cb < p.kb_c; ++cb) {
-            mbar_wait(&full[st], ph);
-            tc_fence_after();
-            const uint32_t s = smem_u32(smem + st * stage_bytes);
+#pragma unroll 1
+            for (int sub = 0; sub < kSub; ++sub) {
+              mbar_wait(&full[st], ph);
+              tc_fence_after();
+              const uint32_t s = smem_u32(smem + st * stage_bytes);
 #pragma unroll
-            for (int tap = 0; tap < 3; ++tap)
-              mma4(tmem_d, make_kmajor_sw128_desc_row(s, tap * p.dil), make_kmajor_sw128_desc(s + p.a_slot + tap * kPairBBytes),
-                   cb == 0 && tap == 0);
-            release(p.kb_h == 0 && cb == p.kb_c - 1, as);
+              for (int tap = 0; tap < 3; ++tap)
+                mma4(tmem_d, make_kmajor_sw128_desc_row(s, tap * p.dil), make_kmajor_sw128_desc(s + p.a_slot + tap * kPairBBytes),
+                     cb == 0 && tap == 0 && sub == 0);
+              release(p.kb_h == 0 && cb == p.kb_c - 1 && sub == kSub - 1, as);
+            }
           }
           one_by_one(tmem_d, p.kb_h, false, as);
         } else {
@@ -405,10 +489,10 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
       const bool valid = t < p.T;
       const size_t row = static_cast<size_t>(b) * p.T + (valid ? t : 0);
       const uint32_t as = acc_it & 1;
-      const __nv_bfloat16* xin = p.x_in + row * (p.kb_c * 64) + idx * 256;
+      const __nv_bfloat16* xin = p.x_in + row * (p.kb_c * 64 * (kSplit ? 2 : 1)) + idx * 256;
       uint4 x0[4], bg0[4], bf0[4];
       const uint16_t* add = p.cproj ? p.cproj + row * p.ld_cproj + idx * 256 : p.bias1h + idx * 256;
-      if (!(p.dbg & 1)) {  // in flight while the job's MMAs finish
+      if (!kSplit && !(p.dbg & 1)) {  // in flight while the job's MMAs finish
         if (kind == 1) ld_x4(xin + half * 32, x0);
         else grp_load_add(add, half, bg0, bf0);
       }
@@ -417,11 +501,15 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
       const uint32_t taddr = lane_addr + as * 256;
       const int tw0 = (tile % p.tiles_t) * 256 + rank * 128 + quad * 32;  // first frame of this warp's 32 rows
       const uint32_t sw = smem_u32(warp_stage + (warp - 4) * kGrpWarpStage);
+      const bool live = p.len == nullptr || t < __ldg(p.len + b);
       if (p.dbg & 1) {  // debug: epilogue warps only hand the accumulator back
+      } else if constexpr (kSplit) {
+        if (kind == 0) grp_epilogue_gate_split(p, taddr, idx, b, tw0, half, lane, sw);
+        else grp_epilogue_res_split(p, taddr, idx, b, tw0, xin, half, lane, sw, live);
       } else if (kind == 0) {
         grp_epilogue_gate(p, taddr, idx, b, tw0, add, bg0, bf0, half, lane, sw);
       } else {
-        grp_epilogue_res(p, taddr, idx, b, tw0, xin, x0, half, lane, sw, p.len == nullptr || t < __ldg(p.len + b));
+        grp_epilogue_res(p, taddr, idx, b, tw0, xin, x0, half, lane, sw, live);
       }
       // release the accumulator on the LEADER's barrier: one arrival per warp
       tc_fence_before();

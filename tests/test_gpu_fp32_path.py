@@ -104,3 +104,39 @@ def test_sampler_fp32_path_final_mel(algo):
     err = rel_l2(y.cpu(), ref)
     print(f"fp32 path {algo} 20 steps final mel rel-L2 {err:.3e}")
     assert err < STEP_TOL
+
+
+@pytest.mark.parametrize("C,L,cycle,B,T", [(512, 5, 4, 2, 300), (256, 6, 5, 3, 517), (512, 3, 3, 1, 77)])
+def test_fused_layer_kernel_split_instantiation(monkeypatch, C, L, cycle, B, T):
+    """ds_layer_grp_kernel<true>: the fused residual-layer kernel with 3 x bf16 split products, accurate gate math and hi / lo
+    outputs -- forced here for small sessions (by default it is taken from one wave of tile pairs on), same 1e-4 bar; a ragged batch
+    must still give every utterance its own conv edge."""
+    monkeypatch.setenv("DSB200_FP32_FUSED", "1")
+    monkeypatch.setenv("DSB200_STACK", "0")
+    M, F = 128, 1
+    sd = random_state_dict(M, F, L, C, 256, seed=C + L + 1)
+    cfg = dict(in_dims=M, n_feats=F, num_layers=L, num_channels=C, dilation_cycle_length=cycle, hidden=256)
+    net = _net(sd, cfg)
+    g = torch.Generator().manual_seed(6)
+    spec = torch.randn(B, F, M, T, generator=g)
+    cond = torch.randn(B, T, 256, generator=g).transpose(1, 2)
+    for t in (torch.tensor([617.25]), torch.linspace(3.0, 990.0, B)):
+        if t.numel() > 1 and B == 1:
+            continue
+        ref = OracleWaveNet(sd, F, cycle)(spec, t, cond)
+        with torch.no_grad():
+            y = net(spec.to(dev), t.to(dev), cond.to(dev))
+        err = rel_l2(y.cpu(), ref)
+        print(f"fp32 fused C={C} L={L} t={t.tolist()[:1]} rel-L2 {err:.3e}")
+        assert err < STEP_TOL
+    sess = next(reversed(net.engine().sessions.values()))
+    assert sess.path == "fused" and sess.last_launches == L + 5  # one kernel per residual layer
+    if B > 1:  # ragged: utterance 1 is shorter
+        lens = [T, T - 41] + [T] * (B - 2)
+        sess.set_lengths(lens)
+        x = spec.reshape(B, F * M, T).transpose(1, 2).contiguous().to(dev)
+        out = sess.forward(x, 0)
+        torch.cuda.synchronize()
+        ref1 = OracleWaveNet(sd, F, cycle)(spec[1:2, ..., :lens[1]], torch.linspace(3.0, 990.0, B)[1:2], cond[1:2, :, :lens[1]])
+        got = out[1, :lens[1]].t().reshape(1, F, M, lens[1]).cpu()
+        assert rel_l2(got, ref1) < STEP_TOL

@@ -43,7 +43,7 @@ def test_plan_validation_without_device():
     # fp32-accurate plan: hi/lo halves of every bf16 matrix, unfused path, no second gate pack
     p32 = C.c_void_p()
     assert L.ds_plan_create(C.byref(nat.WaveNetConfig(128, 1, 20, 512, 4, 256, 1)), C.byref(p32)) == 0
-    assert L.ds_plan_precision(p32) == 1 and L.ds_plan_layer_mode(p32) == 0
+    assert L.ds_plan_precision(p32) == 1 and L.ds_plan_layer_mode(p32) == 5  # the fused kernel has a 3 x bf16 split instantiation
     assert 200e6 < L.ds_plan_packed_bytes(p32) < 260e6
     L.ds_plan_destroy(p32)
     assert L.ds_plan_create(C.byref(nat.WaveNetConfig(128, 1, 20, 512, 4, 256, 7)), C.byref(p32)) == -1
