@@ -489,6 +489,7 @@ struct ds_session {
   uint8_t* ws;
   // workspace offsets
   size_t o_cond, o_xb, o_xt, o_xt1, o_z, o_s1, o_s2, o_g, o_d, o_r, o_tmp, o_cproj, ws_bytes;
+  size_t o_cproj32 = 0;  // fp32-accurate fused sessions: hoisted conditioner projection, fp32 [L][rows][2C]
   CUtensorMap tm_cond, tm_xb, tm_xt, tm_xt1, tm_z, tm_s1, tm_s2;
   CUtensorMap tm_xh[2][5];  // halo maps of the two x~ buffers, one per dilation 2^k (k < 5)
   CUtensorMap tm_zs, tm_xs[2];  // TMA store maps (grouped kernel)
@@ -607,6 +608,15 @@ static void session_layout(const ds_plan* p, int B, int T, int max_times, int pe
   // hoisted conditioner projection: f16 [L][rows][2C] (40 KB per frame at C = 512, L = 20); small sessions never use it
   s->o_cproj = 0;
   if (p->hoist && !session_is_small(p, B, T)) s->o_cproj = take(rows * L * 2 * C * 2);
+  // fp32-accurate fused sessions can hoist too (DSB200_FP32_HOIST=1: fp32 values, 4 KB per frame and layer at C = 512): there the
+  // MMA phase is three times as long as the epilogue, so reading a row per frame in the gate epilogue is free and 1/8 of the MMA
+  // work disappears -- measured +3 % (213 -> 220 k frames/s at B64 x T2000, tools/fp32_bench.py) for 80 KB of workspace per frame,
+  // so it is opt-in.
+  s->o_cproj32 = 0;
+  {
+    const char* he = getenv("DSB200_FP32_HOIST");
+    if (p->split && session_use_fused(p, B, T) && he && atoi(he) != 0) s->o_cproj32 = take(rows * L * 2 * C * 4);
+  }
   s->o_scproj = s->o_edges = 0;
   s->o_len = take((size_t)B * sizeof(int32_t));  // ds_session_set_lengths
   if (session_is_stack(p, B, T)) {
@@ -708,6 +718,24 @@ extern "C" int ds_session_set_cond(ds_session* s, const float* cond_bth, void* s
       DS_TRY(launch_gemm(256, EPI_CPROJ, g, (cudaStream_t)stream));
     }
   }
+  if (s->o_cproj32) {
+    // fp32-accurate fused sessions: cproj32[l][row][packed n] = W_cond_l * cond + b_dil_l + b_cond_l by the split GEMM (3 x bf16), fp32
+    const ds_plan* p = s->plan;
+    const int C = p->C, L = p->L;
+    GemmParams g;
+    memset(&g, 0, sizeof(g));
+    g.T = s->T; g.B = s->B; g.tiles_t = ceil_div(s->T, 128); g.scale = 1.0f;
+    g.tmA0 = s->tm_cond; g.tmB = p->tm_w1; g.kb_a0 = H / 64; g.n_taps = 1; g.b_k0 = 3 * C;
+    g.a0_lo = H; g.w_lo = p->K1;
+    g.n_tiles = 2 * C / 256; g.total_tiles = s->B * g.tiles_t * g.n_tiles;
+    g.ld_out = 2 * C; g.n_real = 2 * C;
+    for (int l = 0; l < L; ++l) {
+      g.b_row0 = l * 2 * C;
+      g.out = s->ws + s->o_cproj32 + (size_t)l * s->B * s->T * 2 * C * 4;
+      g.bias = (const float*)(p->packed + p->o_b1) + (size_t)l * 2 * C;
+      DS_TRY(launch_gemm(256, EPI_OUTF32, g, (cudaStream_t)stream, true));
+    }
+  }
   if (s->stack) {
     // hoisted conditioner projection for the whole-network kernel: cproj[l][row][2C] = W_cond_l * cond + b_dil_l + b_cond_l in the
     // 128-row-pass column order of the narrow gate pack (64 gate columns pre-multiplied by 0.5 | 64 filter columns), f16
@@ -783,6 +811,10 @@ static int session_fused_layer(ds_session* s, int l, int time_index, cudaStream_
   if (s->o_cproj) {
     lp.cproj = (const uint16_t*)(s->ws + s->o_cproj) + (size_t)l * B * T * 2 * C; lp.ld_cproj = 2 * C;
     lp.kb_h = 0;  // the conditioner K blocks are not run per evaluation
+  }
+  if (s->o_cproj32) {
+    lp.cproj32 = (const float*)(s->ws + s->o_cproj32) + (size_t)l * B * T * 2 * C;
+    lp.kb_h = 0;
   }
   return launch_layer_grp(lp, p->max_dil, st, p->split != 0);
 }

@@ -60,6 +60,9 @@ struct LayerParams {
   // fp32-accurate ("split") instantiation: every bf16 operand is hi = bf16(v) followed, `*_lo` elements further along its channel
   // / K axis, by lo = bf16(v - hi); each K stage is issued three times (hi*hi, lo*hi, hi*lo) into the same accumulator
   int x_lo, cond_lo, z_lo, w1_lo, w2_lo;
+  // ... and its hoisted conditioner projection: fp32 [B*T][2C] of THIS layer in packed column order (W_cond * cond + b_dil + b_cond,
+  // computed once per sampler call by the split GEMM); NULL: the conditioner K blocks run inside the kernel and bias1 is added
+  const float* cproj32;
 };
 
 constexpr uint32_t kLayerABytes = 128 * 128;  // 128 frames x 64 bf16
@@ -238,8 +241,8 @@ __device__ __forceinline__ void split_store_tile(const CUtensorMap* map, uint32_
   warp_store_tile(map, sw, lane, lo, c0 + lo_off, tw0, b, any);
 }
 __device__ __forceinline__ void grp_epilogue_gate_split(const LayerParams& p, uint32_t taddr, int idx, int b, int tw0, int half, int lane,
-                                                        uint32_t sw) {
-  const float* bias = p.bias1 + idx * 256;
+                                                        uint32_t sw, size_t row) {
+  const float* bias = (p.cproj32 ? p.cproj32 + row * (p.kb_c * 128) : p.bias1) + idx * 256;  // this frame's row, or the broadcast bias
 #pragma unroll 1
   for (int k = 0; k < 2; ++k) {
     const int c = half + 2 * k;
@@ -504,7 +507,7 @@ ds_layer_grp_kernel(const __grid_constant__ LayerParams p) {
       const bool live = p.len == nullptr || t < __ldg(p.len + b);
       if (p.dbg & 1) {  // debug: epilogue warps only hand the accumulator back
       } else if constexpr (kSplit) {
-        if (kind == 0) grp_epilogue_gate_split(p, taddr, idx, b, tw0, half, lane, sw);
+        if (kind == 0) grp_epilogue_gate_split(p, taddr, idx, b, tw0, half, lane, sw, row);
         else grp_epilogue_res_split(p, taddr, idx, b, tw0, xin, half, lane, sw, live);
       } else if (kind == 0) {
         grp_epilogue_gate(p, taddr, idx, b, tw0, add, bg0, bf0, half, lane, sw);

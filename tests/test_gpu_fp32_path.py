@@ -106,12 +106,14 @@ def test_sampler_fp32_path_final_mel(algo):
     assert err < STEP_TOL
 
 
+@pytest.mark.parametrize("hoist", ["1", "0"])
 @pytest.mark.parametrize("C,L,cycle,B,T", [(512, 5, 4, 2, 300), (256, 6, 5, 3, 517), (512, 3, 3, 1, 77)])
-def test_fused_layer_kernel_split_instantiation(monkeypatch, C, L, cycle, B, T):
+def test_fused_layer_kernel_split_instantiation(monkeypatch, C, L, cycle, B, T, hoist):
     """ds_layer_grp_kernel<true>: the fused residual-layer kernel with 3 x bf16 split products, accurate gate math and hi / lo
     outputs -- forced here for small sessions (by default it is taken from one wave of tile pairs on), same 1e-4 bar; a ragged batch
     must still give every utterance its own conv edge."""
     monkeypatch.setenv("DSB200_FP32_FUSED", "1")
+    monkeypatch.setenv("DSB200_FP32_HOIST", hoist)  # conditioner projection once per call (fp32 rows added in the gate epilogue) or in-kernel
     monkeypatch.setenv("DSB200_STACK", "0")
     M, F = 128, 1
     sd = random_state_dict(M, F, L, C, 256, seed=C + L + 1)
