@@ -81,6 +81,7 @@ class GemmDesc(C.Structure):
         ("stats_out", C.c_void_p), ("stats_d", C.c_void_p), ("stats_d_bstride", C.c_int32),
         ("ln_stats", C.c_void_p), ("ln_parts", C.c_int32), ("ln_channels", C.c_int32), ("ln_eps", C.c_float),
         ("ln_s", C.c_void_p), ("ln_e", C.c_void_p), ("ln_e_bstride", C.c_int32),
+        ("lengths", C.c_void_p),
     ]
 
 

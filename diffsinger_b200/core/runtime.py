@@ -57,9 +57,7 @@ def run_program(backbone, prog: Program, x_tm: torch.Tensor, cond_bht: torch.Ten
         use_graph = False
     eng = backbone.engine()
     if hasattr(eng, 'run_program'):  # LYNXNet: host-composed primitive ops, one torch CUDA graph per (program, B, T)
-        if lengths is not None:
-            raise nat.NativeError("ragged batches (lengths=...) are only supported by the WaveNet backbone")
-        return eng.run_program(backbone, prog, x_tm, cond_bht, extra, use_graph)
+        return eng.run_program(backbone, prog, x_tm, cond_bht, extra, use_graph, lengths)
     B, T, FM = x_tm.shape
     bc = max_chunk_batch(eng, B, T, prog.n_bufs, len(prog.times))
     if bc >= B or lengths is not None:

@@ -1273,6 +1273,7 @@ extern "C" int ds_debug_gemm(const ds_gemm_desc* d, void* stream) {
     g.ln_stats = (const float4*)d->ln_stats; g.ln_parts = d->ln_parts; g.ln_channels = d->ln_channels; g.ln_eps = d->ln_eps;
     g.ln_s = d->ln_s; g.ln_e = d->ln_e; g.ln_e_bstride = d->ln_e_bstride; g.ln_n = d->w_rows;
   }
+  g.len = d->lengths;
   return launch_gemm(d->BN, d->epi, g, (cudaStream_t)stream);
 }
 

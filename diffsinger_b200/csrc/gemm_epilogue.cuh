@@ -158,6 +158,10 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
         if constexpr (kSplit) z[j] = aj * gj * sigmoid_accurate(gj);
         else z[j] = aj * gj * fmaf(0.5f, tanh_approx(0.5f * gj), 0.5f);  // MUFU path: the tile's MMAs take only 4 k cycles
       }
+      if (!live) {  // ragged batch: the depthwise conv that follows reads zeros beyond the utterance's end
+#pragma unroll
+        for (int j = 0; j < 32; ++j) z[j] = 0.0f;
+      }
       epi_store32<kSplit>(p, es, row, p.out_c0 + nt * H + c * 32, b, valid, z);
     }
   } else if constexpr (EPI == EPI_GATEBWD) {

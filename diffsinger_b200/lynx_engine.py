@@ -43,6 +43,10 @@ class LynxWorkspace:
         # partial sums of the folded LayerNorm (strong_cond): [rows, 2 * C / bn_c, 4] fp32
         self.stats = torch.empty(rows, 2 * (eng.C // eng.bn_c), 4, dtype=torch.float32, device=dev) if eng.fold_ln else None
         self.cproj = None  # [L, rows, C] bf16: W_c cond of every layer, hoisted out of a sampler program's loop
+        # ragged batch: frame count of every utterance (device array read by the SwiGLU GEMM's epilogue: the depthwise conv then sees
+        # zeros beyond an utterance's end); None = B full-length utterances.  The tensor persists so that captured graphs follow it.
+        self.lengths = None
+        self._len_dev = torch.full((B,), T, dtype=torch.int32, device=dev)
         self._bufs: List[torch.Tensor] = []
         self.graphs: Dict[Tuple, torch.cuda.CUDAGraph] = {}
         self.last_launches = 0
@@ -51,6 +55,19 @@ class LynxWorkspace:
         c = cond_bth.detach().to(torch.float32).contiguous()
         assert c.shape == (self.B, self.T, self.eng.H), c.shape
         ops.cast_bf16(self.cond, c.view(self.B * self.T, self.eng.H))
+
+    def set_lengths(self, lengths):
+        if lengths is None:
+            if self.lengths is not None:
+                self._len_dev.fill_(self.T)
+                self.lengths = None
+            return
+        lengths = tuple(int(v) for v in lengths)
+        if len(lengths) != self.B or min(lengths) < 1 or max(lengths) > self.T:
+            raise nat.NativeError(f"ragged batch: need {self.B} lengths in [1, {self.T}], got {lengths}")
+        if lengths != self.lengths:
+            self._len_dev.copy_(torch.tensor(lengths, dtype=torch.int32), non_blocking=False)
+            self.lengths = lengths
 
     def hoist_cond(self):
         """cproj[l] = W_c_l cond (bias excluded: it travels with the step vector).  L launches, once per sampler run."""
@@ -219,6 +236,7 @@ class LynxEngine:
         w, B, T, Cc = self.w, ws.B, ws.T, self.C
         rows = B * T
         Bt = vecs.shape[1]
+        lens = ws._len_dev if ws.lengths is not None else None
         ops.cast_bf16(ws.xb, x_f32.view(rows, self.FM))
         if self.fold_ln:
             if evecs is None:
@@ -228,7 +246,7 @@ class LynxEngine:
                      stats_out=st, stats_d=vecs[0])
             for i, lw in enumerate(w["layers"]):
                 last = i + 1 == self.L
-                ops.gemm(ops.EPI_SWIGLU, self.bn_g, B, T, ws.u, lw["w2t"], ws.g, bias=lw["b2t"],
+                ops.gemm(ops.EPI_SWIGLU, self.bn_g, B, T, ws.u, lw["w2t"], ws.g, bias=lw["b2t"], lengths=lens,
                          ln=dict(stats=st, channels=Cc, eps=1e-5, s=lw["ln_s"], e=evecs[i]))
                 ops.dwconv(ws.dw, ws.g, lw["dw_w"], lw["dw_b"], B, T, self.k, self.act, lw["slope"])
                 ops.gemm(ops.EPI_RES, self.bn_c, B, T, ws.dw, lw["w6c"], ws.u, a1=None if last else ws.cond, vec=lw["b6c"], vec_bstride=0,
@@ -240,7 +258,7 @@ class LynxEngine:
             ops.gemm(ops.EPI_LINEAR, self.bn_c, B, T, ws.xb, w["w_in_c"], ws.u, a1=ws.cond, bias=w["b_in_c"], act=ops.ACT_NONE)
             for i, lw in enumerate(w["layers"]):
                 ops.layernorm(ws.n, ws.u, lw["ln_g"], lw["ln_b"], 1e-5, vecs[i], T if Bt > 1 else rows)
-                ops.gemm(ops.EPI_SWIGLU, self.bn_g, B, T, ws.n, lw["w2"], ws.g, bias=lw["b2"])
+                ops.gemm(ops.EPI_SWIGLU, self.bn_g, B, T, ws.n, lw["w2"], ws.g, bias=lw["b2"], lengths=lens)
                 ops.dwconv(ws.dw, ws.g, lw["dw_w"], lw["dw_b"], B, T, self.k, self.act, lw["slope"])
                 ops.gemm(ops.EPI_RES, self.bn_c, B, T, ws.dw, lw["w6c"], ws.u, a1=ws.cond if i + 1 < self.L else None,
                          vec=lw["b6c"], vec_bstride=0, res=ws.u)
@@ -258,7 +276,7 @@ class LynxEngine:
                 res, ln_vec = ws.h, None
             if not hoisted:
                 ops.layernorm(ws.n, ws.u, lw["ln_g"], lw["ln_b"], 1e-5, ln_vec, T if Bt > 1 else rows)
-            ops.gemm(ops.EPI_SWIGLU, self.bn_g, B, T, ws.n, lw["w2"], ws.g, bias=lw["b2"])
+            ops.gemm(ops.EPI_SWIGLU, self.bn_g, B, T, ws.n, lw["w2"], ws.g, bias=lw["b2"], lengths=lens)
             ops.dwconv(ws.dw, ws.g, lw["dw_w"], lw["dw_b"], B, T, self.k, self.act, lw["slope"])
             ops.gemm(ops.EPI_RES, self.bn_c, B, T, ws.dw, lw["w6"], ws.h, vec=lw["b6"], vec_bstride=0, res=res)
         ops.layernorm(ws.n, ws.h, w["norm_g"], w["norm_b"], 1e-5)
@@ -268,11 +286,13 @@ class LynxEngine:
     # ------------------------------------------------------------------ sampler programs
     @torch.no_grad()
     def run_program(self, module, prog: Program, x_tm: torch.Tensor, cond_bht: torch.Tensor, extra: Sequence[torch.Tensor] = (),
-                    use_graph: bool = True) -> torch.Tensor:
+                    use_graph: bool = True, lengths=None) -> torch.Tensor:
         """Runs a sampler Program (core/programs.py) with this backbone: EVAL = self.eval, LINCOMB = ds_lincomb, the whole op
         list captured in one CUDA graph per (program, B, T) and replayed on later calls."""
         B, T, FM = x_tm.shape
         bc = self.max_chunk_batch(B, T, prog.n_bufs)
+        if bc < B and lengths is not None:
+            raise nat.NativeError("a ragged batch must fit the device in one piece")
         if bc < B:  # utterances are independent: a batch that does not fit runs as consecutive chunks (same graph)
             out = torch.empty_like(x_tm)
             launches = 0
@@ -283,6 +303,7 @@ class LynxEngine:
             self.last_launches = launches
             return out
         ws = self.workspace(B, T)
+        ws.set_lengths(lengths)  # None: back to B full-length utterances
         bufs = ws.bufs(prog.n_bufs)
         bufs[0].copy_(x_tm)
         for k, e in enumerate(extra):
@@ -297,7 +318,7 @@ class LynxEngine:
                 self._vec_cache.clear()
             vecs = self.step_vectors(module, torch.tensor(prog.times, dtype=torch.float32), B, False)
             vecs = self._vec_cache[vkey] = (vecs, self.ln_vectors(vecs) if self.fold_ln else None)
-        gkey = (id(prog), vkey)
+        gkey = (id(prog), vkey, ws.lengths is not None)  # ragged launches carry the lengths pointer
         if not use_graph or len(prog.ops) > 1024:
             ws.last_launches = pre + self._run_ops(ws, prog, bufs, vecs, hoist)
             return bufs[0].clone()

@@ -39,14 +39,14 @@ def gemm(epi: int, BN: int, B: int, T: int, a: torch.Tensor, w: torch.Tensor, ou
          vec: Optional[torch.Tensor] = None, vec_bstride: int = 0, res: Optional[torch.Tensor] = None, act: int = ACT_NONE,
          n_real: int = 0, scale: float = 1.0, out_c0: int = 0, out2: Optional[torch.Tensor] = None, slope2: float = 0.0,
          res_c0: int = 0, stats_out: Optional[torch.Tensor] = None, stats_d: Optional[torch.Tensor] = None,
-         ln: Optional[dict] = None):
+         ln: Optional[dict] = None, lengths: Optional[torch.Tensor] = None):
     """out[b, t, out_c0 + n] = epilogue(sum_tap sum_k a[b, t + (tap - n_taps // 2) * dil, a_c0 + k] * w[n, tap * K + k]
     + sum_h a1[b, t, h] * w[n, n_taps * K + h]); frames outside [0, T) read as zeros (the conv's zero padding).
     a: [B*T, ld_a] bf16 (K = k_per_tap columns from a_c0), a1: optional second operand [B*T, H] (one tap),
     w: [rows, n_taps * K (+ H)] bf16, out: [B*T, ld_out] bf16 (fp32 for EPI_OUTF32), res: [B*T, ld_res] bf16 (EPI_RES).
     Folded LayerNorm (include/dsb200.h: ds_gemm_desc): stats_out fp32 [B*T, 2 * rows / BN, 4] receives the producer's partial sums
     (stats_d: the next norm's step vector [Bt, rows]); ln = dict(stats, channels, eps, s [rows], e [Bt, rows + 4]) makes the SwiGLU
-    epilogue apply the norm."""
+    epilogue apply the norm.  lengths: int32 [B] device tensor of a ragged batch (outputs beyond an utterance's end are zeros)."""
     a_ch = a.shape[1]
     k = a_ch if k_per_tap is None else k_per_tap
     h = a1.shape[1] if a1 is not None else 0
@@ -71,6 +71,9 @@ def gemm(epi: int, BN: int, B: int, T: int, a: torch.Tensor, w: torch.Tensor, ou
         assert e.shape[-1] == rows + 4 and ln["s"].numel() == rows
         d.ln_stats, d.ln_parts, d.ln_channels, d.ln_eps = st.data_ptr(), st.numel() // (B * T * 4), ln["channels"], ln["eps"]
         d.ln_s, d.ln_e, d.ln_e_bstride = ln["s"].data_ptr(), e.data_ptr(), (e.shape[-1] if e.shape[0] > 1 else 0)
+    if lengths is not None:
+        assert lengths.dtype == torch.int32 and lengths.numel() == B and lengths.is_cuda
+        d.lengths = lengths.data_ptr()
     nat.check(nat.lib().ds_gemm(C.byref(d), stream()))
 
 

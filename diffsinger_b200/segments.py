@@ -18,7 +18,7 @@ import torch
 MAX_RAGGED_FRAMES = 1 << 16  # padded frames (B * T_max) of one ragged batch on the per-layer kernels
 
 
-def _ragged_capacity(diffusion, t_longest: int):
+def _ragged_capacity(diffusion, t_longest: int, have_src: bool = False):
     """(tiles of 128 frames one ragged batch may hold, shortest segment of a batch as a fraction of its longest); (0, 0): this
     sampler / backbone / configuration cannot run ragged batches.  Plans on the whole-network kernel are bounded by the
     co-resident clusters (ds_plan_stack_capacity) as long as the longest segment fits, and padding costs them nothing (tiles beyond
@@ -28,13 +28,13 @@ def _ragged_capacity(diffusion, t_longest: int):
     from .hparams import get_hparams
     backbone = getattr(diffusion, 'denoise_fn', None) or getattr(diffusion, 'velocity_fn')
     eng = backbone.engine()
-    if not hasattr(eng, 'plan'):
-        return 0, 0.0  # LYNXNet: host-composed ops, no per-utterance edge
     hp = get_hparams()
     if hasattr(diffusion, 'denoise_fn') and hp.get('diff_speedup', 0) <= 1:
         return 0, 0.0  # ancestral chain draws fresh noise every step
-    if getattr(diffusion, 'use_shallow_diffusion', False):
-        return 0, 0.0  # needs a per-segment source spectrogram
+    if getattr(diffusion, 'use_shallow_diffusion', False) and not have_src:
+        return 0, 0.0  # shallow diffusion needs the per-segment source spectrograms (src_spec=[...])
+    if not hasattr(eng, 'plan'):  # LYNXNet: the SwiGLU GEMM masks the depthwise conv's input (lynx_engine.LynxWorkspace.set_lengths)
+        return max(MAX_RAGGED_FRAMES // 128, -(-t_longest // 128)), 0.5
     cap = int(nat.lib().ds_plan_stack_capacity(eng.plan))
     if cap >= -(-t_longest // 128):
         return cap, 0.0
@@ -58,7 +58,7 @@ def _ragged_groups(lengths: Sequence[int], cap: int, min_fill: float = 0.0) -> L
     return groups
 
 
-def _sample_ragged(diffusion, conditions, cap: int, min_fill: float) -> List[torch.Tensor]:
+def _sample_ragged(diffusion, conditions, cap: int, min_fill: float, src_specs=None) -> List[torch.Tensor]:
     """All batch-1 segments through ragged batches.  Noise is drawn segment by segment in the caller's order from the global
     generator -- the values a segment-by-segment loop would draw -- then padded; outputs are cut back to each segment's length."""
     dev = conditions[0].device
@@ -70,13 +70,16 @@ def _sample_ragged(diffusion, conditions, cap: int, min_fill: float) -> List[tor
         t_max = max(lens[i] for i in grp)
         cond = conditions[0].new_zeros(len(grp), t_max, conditions[0].shape[2])
         z = torch.zeros(len(grp), F, M, t_max, device=dev)
+        src = None if src_specs is None else src_specs[0].new_zeros(len(grp), t_max, *src_specs[0].shape[2:])
         for b, i in enumerate(grp):
             cond[b, :lens[i]] = conditions[i][0]
             z[b, ..., :lens[i]] = noise[i][0]
+            if src is not None:
+                src[b, :lens[i]] = src_specs[i][0]
         saved = getattr(diffusion, '_noise_override', None), getattr(diffusion, '_lengths_override', None)
         diffusion._noise_override, diffusion._lengths_override = z, [lens[i] for i in grp]
         try:
-            y = diffusion(cond, infer=True)
+            y = diffusion(cond, infer=True) if src is None else diffusion(cond, src_spec=src, infer=True)
         finally:
             diffusion._noise_override, diffusion._lengths_override = saved
         for b, i in enumerate(grp):
@@ -95,19 +98,23 @@ def sample_segments(diffusion, conditions: Sequence[torch.Tensor], n_streams: in
     """`diffusion(cond, infer=True, **forward_kwargs)` for every `cond` ([B, T_i, H], any lengths).  Returns the outputs in
     order; they are safe to use on the current stream.
 
-    ragged=True (default): when every segment is batch 1, no per-segment keyword tensors are given and the backbone is a WaveNet,
-    segments are padded into ragged batches (include/dsb200.h: ds_session_set_lengths): every utterance keeps its own end, so each
-    output equals the segment-by-segment result.  Otherwise up to `n_streams` segments are in flight on CUDA streams;
+    ragged=True (default): when every segment is batch 1 (keyword tensors: at most `src_spec=[...]`, the shallow-diffusion sources
+    [1, T_i, M]), segments are padded into ragged batches (include/dsb200.h: ds_session_set_lengths; LYNXNet: the SwiGLU GEMM masks the
+    depthwise conv's input): every utterance keeps its own end, so each output equals the segment-by-segment result.  Otherwise up to
+    `n_streams` segments are in flight on CUDA streams;
     per-segment keyword tensors (e.g. `src_spec`) are passed as lists of the same length as `conditions`."""
     if not conditions:
         return []
     dev = conditions[0].device
     if dev.type != 'cuda':
         raise RuntimeError("sample_segments needs CUDA tensors (there is no CPU path)")
-    if ragged and not forward_kwargs and all(c.shape[0] == 1 for c in conditions) and len(conditions) > 1:
-        cap, min_fill = _ragged_capacity(diffusion, max(int(c.shape[1]) for c in conditions))
+    src_specs = forward_kwargs.get('src_spec')
+    only_src = set(forward_kwargs) <= {'src_spec'} and (src_specs is None or (isinstance(src_specs, (list, tuple)) and
+                                                                             all(v.dim() == 3 for v in src_specs)))
+    if ragged and only_src and all(c.shape[0] == 1 for c in conditions) and len(conditions) > 1:
+        cap, min_fill = _ragged_capacity(diffusion, max(int(c.shape[1]) for c in conditions), src_specs is not None)
         if cap:
-            return _sample_ragged(diffusion, conditions, cap, min_fill)
+            return _sample_ragged(diffusion, conditions, cap, min_fill, src_specs)
     main = torch.cuda.current_stream(dev)
     n_streams = max(1, min(n_streams, len(conditions)))
     pool = getattr(diffusion, '_segment_streams', None)

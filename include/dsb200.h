@@ -193,6 +193,10 @@ typedef struct {
   void* stats_out; const float* stats_d; int32_t stats_d_bstride;
   const void* ln_stats; int32_t ln_parts; int32_t ln_channels; float ln_eps;
   const float* ln_s; const float* ln_e; int32_t ln_e_bstride;
+  /* Ragged batch (see ds_session_set_lengths): optional device array [B] of frame counts; the bf16 outputs of epilogues 0 / 2 / 5 for
+   * frames t >= lengths[b] are written as ZEROS, so that a convolution over time that reads them next (LYNXNet's depthwise k = 31
+   * after the SwiGLU GEMM, lynxnet.py:57-59) sees the utterance's own zero padding. */
+  const int32_t* lengths;
 } ds_gemm_desc;
 int ds_debug_gemm(const ds_gemm_desc* d, void* stream);
 int ds_gemm(const ds_gemm_desc* d, void* stream);

@@ -131,3 +131,57 @@ def test_lynxnet_batch_chunking_is_bitwise_identical(monkeypatch):
         with torch.no_grad():
             outs.append(m(cond, infer=True).cpu())
     assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+
+
+@pytest.mark.parametrize("C,strong,shallow", [(256, True, True), (512, False, False)])
+def test_ragged_batches_of_segments(C, strong, shallow):
+    """sample_segments with LYNXNet: segments of different lengths padded into ragged batches; the SwiGLU GEMM stores zeros beyond an
+    utterance's end, so the depthwise k = 31 conv sees each utterance's own padding.  Shallow diffusion sources ride along
+    (src_spec=[...]).  The batch may run on other GEMM variants than a lone short segment (pair / split-K kernels): equality to bf16
+    noise, also on the LAST frames of every utterance, where a wrong edge would show."""
+    M, F, L, H, k = 128, 1, 3, 256, 31
+    sd = random_lynx_state_dict(M, F, L, C, H, expansion_factor=2, kernel_size=k, activation="PReLU", seed=C)
+    ds.hparams.clear()
+    ds.hparams.update(hidden_size=H, use_shallow_diffusion=shallow, sampling_algorithm="euler", sampling_steps=6, T_start=0.4 if shallow else 0.0,
+                      T_start_infer=0.4 if shallow else 0.0, time_scale_factor=1000)
+    m = ds.RectifiedFlow(M, 1, t_start=0.4 if shallow else 0.0, backbone_type="lynxnet",
+                         backbone_args=dict(num_layers=L, num_channels=C, expansion_factor=2, kernel_size=k, strong_cond=strong),
+                         spec_min=[-12.0], spec_max=[0.0])
+    m.velocity_fn.load_state_dict(sd)
+    m = m.eval().to(dev)
+    lens = [300, 77, 515, 257, 512, 640]
+    g = torch.Generator().manual_seed(21)
+    conds = [torch.randn(1, t, H, generator=g).to(dev) for t in lens]
+    srcs = [(torch.rand(1, t, M, generator=g) * 12 - 12).to(dev) for t in lens] if shallow else None
+    kw = dict(src_spec=srcs) if shallow else {}
+    torch.manual_seed(8)
+    with torch.no_grad():
+        alone = [m(c, infer=True, **({"src_spec": srcs[i]} if shallow else {})).cpu() for i, c in enumerate(conds)]
+    torch.manual_seed(8)
+    batched = [y.cpu() for y in ds.sample_segments(m, conds, **kw)]
+    eng = m.velocity_fn.engine()
+    assert any(ws.lengths is not None for ws in eng.workspaces.values()), "the ragged path did not run"
+    worst = 0.0
+    for t, a, b in zip(lens, alone, batched):
+        assert a.shape == b.shape and a.shape[1] == t
+        worst = max(worst, rel_l2(b, a), rel_l2(b[:, -24:], a[:, -24:]), rel_l2(b[:, :24], a[:, :24]))
+    print(f"[LYNXNet ragged, C={C}, strong={strong}, shallow={shallow}] worst rel-L2 vs one by one: {worst:.3e}")
+    assert worst < 1e-2
+    # the test can see a wrong edge: the same padded batch WITHOUT lengths changes the last frames of a short utterance
+    if not shallow:
+        t_max, i = max(lens), 1
+        cond = torch.zeros(2, t_max, H, device=dev)
+        cond[0, :lens[i]] = conds[i][0]
+        cond[1] = conds[lens.index(t_max)][0]
+        noise = torch.randn(2, F, M, t_max, generator=g).to(dev)
+        m._noise_override = noise
+        try:
+            with torch.no_grad():
+                padded = m(cond, infer=True).cpu()
+            m._noise_override = noise[:1, ..., :lens[i]].contiguous()
+            with torch.no_grad():
+                lone = m(conds[i], infer=True).cpu()
+        finally:
+            m._noise_override = None
+        assert rel_l2(padded[0:1, lens[i] - 12:lens[i]], lone[:, -12:]) > 1e-2
+        assert rel_l2(padded[0:1, :lens[i] - 40], lone[:, :-40]) < 1e-2

@@ -88,6 +88,31 @@ def lynx(algo, B, T, iters=3, C=512, strong=False):
     torch.cuda.empty_cache()
 
 
+def lynx_segments(C=1024, strong=True):
+    """The 30 segment lengths of config #1 on the shipped default backbone: one by one (the reference's loop) vs ragged batches."""
+    M, L = 128, 6
+    hp(diff_accelerator="dpm-solver")
+    m = ds.GaussianDiffusion(M, 1, 1000, 1000, "lynxnet", dict(num_layers=L, num_channels=C, expansion_factor=2, kernel_size=31,
+                                                                strong_cond=strong),
+                             spec_min=[-12.0], spec_max=[0.0])
+    m.denoise_fn.load_state_dict(random_lynx_state_dict(M, 1, L, C, 256, seed=1234))
+    m = m.eval().to(dev)
+    lens = [504, 522, 539, 720, 1197, 550, 550, 515, 550, 539, 539, 540, 1917, 549, 550, 515, 687, 549, 549, 549, 460, 286, 578, 545, 515,
+            566, 572, 542, 516, 579]
+    conds = [torch.randn(1, t, 256, device=dev) for t in lens]
+    with torch.no_grad():
+        torch.manual_seed(7)
+        one = [m(c, infer=True) for c in conds]
+        torch.manual_seed(7)
+        rag = ds.sample_segments(m, conds)
+        err = max(float((a - b).norm() / b.norm()) for a, b in zip(rag, one))
+        ms_one = timed(lambda: [m(c, infer=True) for c in conds], 1)
+        ms_rag = timed(lambda: ds.sample_segments(m, conds), 1)
+    print(json.dumps(dict(case="lynxnet/segments30", C=C, L=L, strong_cond=strong, frames=sum(lens), one_by_one_ms=round(ms_one, 1),
+                          ragged_ms=round(ms_rag, 1), ragged_frames_per_s=round(sum(lens) / ms_rag * 1e3, 1),
+                          ragged_vs_one_by_one_rel_l2_max=round(err, 7))), flush=True)
+
+
 def variance(T, iters=20):
     """config #4: PitchDiffusion (C256 L20 cycle5, 64 repeat bins) + MultiVarianceDiffusion (C192 L10 cycle4, 2 x 24 bins), B=1."""
     for algo in ("ddim", "dpm-solver", "unipc"):
@@ -131,6 +156,7 @@ def main():
             lynx("dpm-solver", B, T)
         for B, T in ((32, 2000), (1, 500)):  # the shipped default: 6 x 1024, strong_cond
             lynx("dpm-solver", B, T, C=1024, strong=True)
+        lynx_segments()
     if "reflow" in what:
         for algo in ("euler", "rk2", "rk4"):
             acoustic("reflow", algo, 64, 2000, iters=2)
