@@ -22,7 +22,7 @@ EXPORTS = [
     "ds_last_error", "ds_abi_version", "ds_device_check", "ds_plan_create", "ds_plan_destroy",
     "ds_plan_packed_bytes", "ds_plan_pack_weights", "ds_session_workspace_bytes", "ds_session_create",
     "ds_session_destroy", "ds_session_set_cond", "ds_session_set_times", "ds_session_forward",
-    "ds_session_run", "ds_session_last_launches", "ds_session_path", "ds_plan_stack_capacity", "ds_session_set_lengths", "ds_lincomb", "ds_transpose", "ds_debug_gemm", "ds_debug_set_trace", "ds_debug_mma_rate",
+    "ds_session_run", "ds_session_last_launches", "ds_session_path", "ds_plan_stack_capacity", "ds_session_set_lengths", "ds_lincomb", "ds_transpose", "ds_shallow_start", "ds_debug_gemm", "ds_debug_set_trace", "ds_debug_mma_rate",
     "ds_debug_layer", "ds_static_scratch_bytes", "ds_forward_static", "ds_plan_layer_mode", "ds_plan_precision", "ds_gemm", "ds_layernorm", "ds_dwconv", "ds_cast_bf16", "ds_gate_fwd", "ds_gate_bwd", "ds_wgrad", "ds_source_conv", "ds_mean3_lrelu", "ds_conv_small", "ds_attention", "ds_mask_rows", "ds_length_regulate",
 ]
 
@@ -136,6 +136,7 @@ def lib() -> C.CDLL:
     L.ds_session_workspace_bytes.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32]
     L.ds_session_last_launches.restype = C.c_int64
     L.ds_session_last_launches.argtypes = [C.c_void_p]
+    L.ds_shallow_start.argtypes = [C.c_void_p] * 5 + [C.c_float, C.c_float, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
     L.ds_session_set_lengths.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.c_int32, C.c_void_p]
     L.ds_plan_stack_capacity.restype = C.c_int
     L.ds_plan_stack_capacity.argtypes = [C.c_void_p]

@@ -15,7 +15,7 @@ from ..backbones import build_backbone
 from ..hparams import get_hparams
 from . import programs
 from .curves import ClampedCurve, CurveList, RepeatBins
-from .runtime import run_program, to_time_major
+from .runtime import run_program, shallow_start, to_time_major
 
 
 def linear_beta_schedule(timesteps, max_beta=0.01):
@@ -133,9 +133,25 @@ class GaussianDiffusion(nn.Module):
             return pre.to(device)
         return torch.randn(b, self.num_feats, self.out_dims, T, device=device)
 
+    def _host_coef(self, name: str, index: int) -> float:
+        """One entry of a schedule buffer as a host float (cached copy: no device sync per call)."""
+        buf = getattr(self, name)
+        key = (name, buf.data_ptr(), buf._version)
+        cache = self.__dict__.setdefault('_coef_cache', {})
+        if key not in cache:
+            cache.clear()
+            cache[key] = buf.detach().cpu()
+        return float(cache[key][index])
+
+    def _fusable_start(self, src_spec) -> bool:
+        """norm_spec + q_sample + transpose as one kernel (runtime.shallow_start): plain mel spectrograms on the GPU only."""
+        return (src_spec is not None and src_spec.is_cuda and self.num_feats == 1 and src_spec.dim() == 3
+                and type(self).norm_spec is GaussianDiffusion.norm_spec and self.spec_min.numel() in (1, self.out_dims))
+
     @torch.no_grad()
-    def inference(self, cond, b=1, x_start=None, device=None):
-        """cond [B, H, T]; x_start [B, F, M, T] or None -> [B, T, M] / [B, F, T, M] (ddpm.py:221-351)."""
+    def inference(self, cond, b=1, x_start=None, device=None, src_raw=None):
+        """cond [B, H, T]; x_start [B, F, M, T] or None -> [B, T, M] / [B, F, T, M] (ddpm.py:221-351).  src_raw: the un-normalised
+        shallow-diffusion source [B, T, M] instead of x_start (forward passes it when the start state can be built in one kernel)."""
         hparams = get_hparams()
         depth = hparams.get('K_step_infer', self.k_step)
         speedup = hparams['diff_speedup']
@@ -146,24 +162,32 @@ class GaussianDiffusion(nn.Module):
         noise = self._draw_noise(b, T, device)
         t_max = min(depth, self.k_step) if self.use_shallow_diffusion else self.k_step
 
+        if src_raw is not None and not 0 < t_max < self.timesteps:  # no mix to fuse: the plain path
+            x_start = self.norm_spec(src_raw).transpose(-2, -1)[:, None, :, :]
+            src_raw = None
         if t_max >= self.timesteps:
             x = noise
         elif t_max > 0:
-            assert x_start is not None, 'Missing shallow diffusion source.'
-            x = self.q_sample(x_start, torch.full((b,), t_max - 1, device=device, dtype=torch.long), noise)
+            assert x_start is not None or src_raw is not None, 'Missing shallow diffusion source.'
+            if src_raw is not None:  # norm_spec -> q_sample -> time-major in one pass
+                x = shallow_start(src_raw, noise, self.spec_min, self.spec_max, self._host_coef('sqrt_alphas_cumprod', t_max - 1),
+                                  self._host_coef('sqrt_one_minus_alphas_cumprod', t_max - 1))
+            else:
+                x = self.q_sample(x_start, torch.full((b,), t_max - 1, device=device, dtype=torch.long), noise)
         else:
             assert x_start is not None, 'Missing shallow diffusion source.'
             x = x_start
+        as_tm = (lambda v: v) if (src_raw is not None and 0 < t_max < self.timesteps) else to_time_major
 
         if t_max > 0 and speedup > 1:
             prog = self._program(hparams['diff_accelerator'], t_max, speedup)
-            x_tm = run_program(self.denoise_fn, prog, to_time_major(x), cond, [], lengths=getattr(self, '_lengths_override', None))
+            x_tm = run_program(self.denoise_fn, prog, as_tm(x), cond, [], lengths=getattr(self, '_lengths_override', None))
         elif t_max > 0:
             # ancestral chain (ddpm.py:346-349), ANCESTRAL_BLOCK steps per program: the reference holds one noise tensor at a time;
             # pre-drawing all t_max of them (plus their time-major copies and the session buffers) would cost 3 * t_max * B*T*F*M*4
             # bytes.  Fresh noise per step comes from the global generator in noise_like's draw order (ddpm.py:153).
             assert getattr(self, '_lengths_override', None) is None, 'ragged batches are not offered for the ancestral chain'
-            x_tm = to_time_major(x)
+            x_tm = as_tm(x)
             for hi in range(t_max, 0, -self.ANCESTRAL_BLOCK):
                 lo = max(hi - self.ANCESTRAL_BLOCK, 0)
                 prog = self._program('__ancestral__', hi, lo)
@@ -171,7 +195,7 @@ class GaussianDiffusion(nn.Module):
                 x_tm = run_program(self.denoise_fn, prog, x_tm, cond, extra)
                 del extra
         else:
-            x_tm = to_time_major(x)
+            x_tm = as_tm(x)
         # [B, T, F*M] -> [B, T, M] (F == 1) or [B, F, T, M]
         if self.num_feats == 1:
             return x_tm
@@ -187,6 +211,8 @@ class GaussianDiffusion(nn.Module):
                 spec = spec[:, None, :, :]
             t = torch.randint(0, self.k_step, (b,), device=device).long()
             return self.p_losses(spec, t, cond=cond)
+        if self._fusable_start(src_spec):
+            return self.denorm_spec(self.inference(cond, b=b, device=device, src_raw=src_spec))
         if src_spec is not None:
             spec = self.norm_spec(src_spec).transpose(-2, -1)
             if self.num_feats == 1:

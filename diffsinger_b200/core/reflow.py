@@ -13,7 +13,7 @@ from ..backbones import build_backbone
 from ..hparams import get_hparams
 from . import programs
 from .curves import ClampedCurve, CurveList, RepeatBins
-from .runtime import run_program, to_time_major
+from .runtime import run_program, shallow_start, to_time_major
 
 
 class RectifiedFlow(nn.Module):
@@ -54,6 +54,10 @@ class RectifiedFlow(nn.Module):
             t = self.t_start + (1.0 - self.t_start) * torch.rand((b,), device=device)
             v_pred, v_gt = self.p_losses(spec, t, cond=cond)
             return v_pred, v_gt, t
+        if (src_spec is not None and src_spec.is_cuda and self.num_feats == 1 and src_spec.dim() == 3
+                and type(self).norm_spec is RectifiedFlow.norm_spec and self.spec_min.numel() in (1, self.out_dims)):
+            # norm_spec -> linear mix with the noise -> time-major as one kernel (runtime.shallow_start)
+            return self.denorm_spec(self.inference(cond, b=b, device=device, src_raw=src_spec))
         if src_spec is not None:
             spec = self.norm_spec(src_spec).transpose(-2, -1)
             if self.num_feats == 1:
@@ -73,17 +77,24 @@ class RectifiedFlow(nn.Module):
         return torch.randn(b, self.num_feats, self.out_dims, T, device=device)
 
     @torch.no_grad()
-    def inference(self, cond, b=1, x_end=None, device=None):
-        """cond [B, H, T]; x_end [B, F, M, T] or None -> [B, T, M] / [B, F, T, M] (reflow.py:104-138)."""
+    def inference(self, cond, b=1, x_end=None, device=None, src_raw=None):
+        """cond [B, H, T]; x_end [B, F, M, T] or None -> [B, T, M] / [B, F, T, M] (reflow.py:104-138).  src_raw: the un-normalised
+        shallow-diffusion source [B, T, M] instead of x_end (forward passes it when the start state can be built in one kernel)."""
         hparams = get_hparams()
         T = cond.shape[2]
         noise = self._draw_noise(b, T, device)
         t_start = hparams.get('T_start_infer', self.t_start)
+        x_tm = None
+        if src_raw is not None and not (self.use_shallow_diffusion and 0. < t_start < 1.):  # no mix to fuse: the plain path
+            x_end = self.norm_spec(src_raw).transpose(-2, -1)[:, None, :, :]
+            src_raw = None
         if self.use_shallow_diffusion and t_start > 0:
-            assert x_end is not None, 'Missing shallow diffusion source.'
+            assert x_end is not None or src_raw is not None, 'Missing shallow diffusion source.'
             if t_start >= 1.:
                 t_start = 1.
                 x = x_end
+            elif src_raw is not None:
+                x_tm = shallow_start(src_raw, noise, self.spec_min, self.spec_max, t_start, 1 - t_start)
             else:
                 x = t_start * x_end + (1 - t_start) * noise
         else:
@@ -92,7 +103,8 @@ class RectifiedFlow(nn.Module):
 
         algorithm = hparams['sampling_algorithm']
         infer_step = hparams['sampling_steps']
-        x_tm = to_time_major(x)
+        if x_tm is None:
+            x_tm = to_time_major(x)
         if t_start < 1:
             key = (algorithm, infer_step, float(t_start), float(self.time_scale_factor))
             prog = self._programs.get(key)

@@ -16,6 +16,22 @@ def to_time_major(x: torch.Tensor) -> torch.Tensor:
     return x.reshape(B, F * M, T).transpose(1, 2).contiguous().float()
 
 
+def shallow_start(src_btm: torch.Tensor, noise_bfmt: torch.Tensor, spec_min: torch.Tensor, spec_max: torch.Tensor, ca: float,
+                  cb: float) -> torch.Tensor:
+    """Time-major start state of shallow diffusion, ca * norm_spec(src) + cb * noise, in one kernel (include/dsb200.h:
+    ds_shallow_start; bit-identical to norm_spec -> q_sample / linear mix -> to_time_major).  src [B, T, M], noise [B, 1, M, T]."""
+    B, T, M = src_btm.shape
+    src = src_btm.contiguous().float()
+    noise = noise_bfmt.contiguous().float()
+    smin = spec_min.reshape(-1).float().expand(M).contiguous() if spec_min.numel() == 1 else spec_min.reshape(-1).float().contiguous()
+    smax = spec_max.reshape(-1).float().expand(M).contiguous() if spec_max.numel() == 1 else spec_max.reshape(-1).float().contiguous()
+    assert smin.numel() == M and smax.numel() == M and noise.shape == (B, 1, M, T)
+    out = torch.empty(B, T, M, dtype=torch.float32, device=src.device)
+    nat.check(nat.lib().ds_shallow_start(out.data_ptr(), src.data_ptr(), noise.data_ptr(), smin.data_ptr(), smax.data_ptr(), float(ca),
+                                         float(cb), B, T, M, torch.cuda.current_stream().cuda_stream))
+    return out
+
+
 def max_chunk_batch(eng, B: int, T: int, n_bufs: int, n_times: int) -> int:
     """Largest per-launch batch whose session workspace + sampler buffers fit the device (the gated-activation store
     alone is L*C*2 bytes per frame: 20 KB at C=512, L=20, so B=1024 x T=8000 would need 168 GB).  Utterances are

@@ -1228,6 +1228,16 @@ extern "C" int ds_transpose(float* dst, const float* src, int32_t B, int32_t R, 
   return 0;
 }
 
+extern "C" int ds_shallow_start(float* x_btm, const float* src_btm, const float* noise_bmt, const float* spec_min, const float* spec_max,
+                                float ca, float cb, int32_t B, int32_t T, int32_t M, void* stream) {
+  if (!x_btm || !src_btm || !noise_bmt || !spec_min || !spec_max || B <= 0 || T <= 0 || M <= 0) return fail(DS_ERR_INVALID, "bad argument");
+  if (B > 65535) return fail(DS_ERR_INVALID, "B too large for ds_shallow_start");
+  dim3 grid(ceil_div(M, 32), ceil_div(T, 32), B);
+  shallow_start_kernel<<<grid, dim3(32, 8), 0, (cudaStream_t)stream>>>(x_btm, src_btm, noise_bmt, spec_min, spec_max, ca, cb, T, M);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
 extern "C" int ds_debug_gemm(const ds_gemm_desc* d, void* stream) {
   if (!d) return fail(DS_ERR_INVALID, "null argument");
   if (!d->a0 || !d->w || !d->out) return fail(DS_ERR_INVALID, "ds_gemm: null operand");

@@ -183,6 +183,33 @@ __global__ void transpose_kernel(float* __restrict__ dst, const float* __restric
   }
 }
 
+// Shallow-diffusion start state in ONE pass (ddpm.py:235-239,379-380 and reflow.py:112-118: norm_spec, then q_sample / the linear mix
+// with the noise, then the transpose to the kernels' time-major layout):
+//   x[b][t][m] = ca * ((src[b][t][m] - min[m]) / (max[m] - min[m]) * 2 - 1) + cb * noise[b][m][t]
+// Every operation is rounded separately (no FMA contraction), in the reference's order, so the result equals the eager sequence bit
+// for bit.  The noise arrives [B][M][T] and is transposed through a 32 x 33 tile.
+__global__ void shallow_start_kernel(float* __restrict__ x, const float* __restrict__ src, const float* __restrict__ noise,
+                                     const float* __restrict__ smin, const float* __restrict__ smax, float ca, float cb, int T, int M) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z;
+  const int m0 = blockIdx.x * 32, t0 = blockIdx.y * 32;
+  const float* nz = noise + static_cast<long>(b) * M * T;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {  // rows = mel bins, columns = frames (contiguous in the noise)
+    const int m = m0 + i, t = t0 + threadIdx.x;
+    if (m < M && t < T) tile[i][threadIdx.x] = nz[static_cast<long>(m) * T + t];
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {  // rows = frames, columns = mel bins (contiguous in src / x)
+    const int t = t0 + i, m = m0 + threadIdx.x;
+    if (t < T && m < M) {
+      const long at = (static_cast<long>(b) * T + t) * M + m;
+      const float lo = __ldg(smin + m), hi = __ldg(smax + m);
+      const float nrm = __fsub_rn(__fmul_rn(__fdiv_rn(__fsub_rn(src[at], lo), __fsub_rn(hi, lo)), 2.0f), 1.0f);
+      x[at] = __fadd_rn(__fmul_rn(ca, nrm), __fmul_rn(cb, tile[threadIdx.x][i]));
+    }
+  }
+}
+
 // ------------------------------------------------------------------ sampler update
 // dst = sum_i coef[i] * src[i]  (n <= 8 terms), fp32, float4-vectorised, grid-stride.
 // Covers every sampler family's tensor update (DDIM / PLMS / ancestral / DPM-Solver++ / UniPC /

@@ -160,6 +160,13 @@ int ds_forward_static(ds_plan* plan, const float* cond_bth, const float* t_dev, 
 int ds_lincomb(float* dst, const float* const* srcs, const float* coefs, int32_t n, size_t numel, void* stream);
 /* [B][R][C] -> [B][C][R] fp32 (spec [B,F*M,T] <-> time-major; ddpm.py:350, reflow.py:137). */
 int ds_transpose(float* dst, const float* src, int32_t B, int32_t R, int32_t C, void* stream);
+/* Start state of shallow diffusion in one pass (the step immediately before the loop): replaces norm_spec
+ * (ddpm.py:379-380) + q_sample (ddpm.py:206-210,235-239) -- or RectifiedFlow's `t_start * x_end + (1 - t_start) * noise`
+ * (reflow.py:112-118) -- + the transpose to time-major:  x[b][t][m] = ca * ((src[b][t][m] - min[m]) / (max[m] - min[m]) * 2 - 1) +
+ * cb * noise[b][m][t].  src: the aux decoder's mel [B][T][M] fp32, noise: [B][M][T] fp32 as torch.randn(B, 1, M, T) draws it;
+ * every operation rounded separately in the reference's order (bit-identical to the eager sequence). */
+int ds_shallow_start(float* x_btm, const float* src_btm, const float* noise_bmt, const float* spec_min, const float* spec_max, float ca,
+                     float cb, int32_t B, int32_t T, int32_t M, void* stream);
 
 /* ---- primitive ops: one tcgen05 GEMM launch with an explicit epilogue, LayerNorm, depthwise conv.  They are the unit-test
  * hooks of the kernels above and the building blocks of the path's neighbours behind the same registry (LYNXNet,

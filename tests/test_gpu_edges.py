@@ -159,3 +159,45 @@ def test_session_path_by_size(C, B, T, path, monkeypatch):
         monkeypatch.delenv(v, raising=False)
     net = _net(random_state_dict(128, 1, 2, C, 256, seed=1), C, 2, 2, 128, 1)
     assert net.engine().session(B, T).path == path
+
+
+@pytest.mark.parametrize("family", ["ddpm", "reflow"])
+def test_shallow_start_kernel_equals_the_eager_sequence(family):
+    """ds_shallow_start (norm_spec -> q_sample / linear mix -> time-major in one kernel) is bit-identical to the eager
+    torch sequence it replaces, and the samplers take it for plain mel sources."""
+    from diffsinger_b200.core.runtime import shallow_start, to_time_major
+    B, T, M = 3, 517, 128
+    g = torch.Generator().manual_seed(2)
+    src = (torch.rand(B, T, M, generator=g) * 12 - 12).to(dev)
+    noise = torch.randn(B, 1, M, T, generator=g).to(dev)
+    smin = torch.linspace(-12.0, -10.0, M)[None, None, :].to(dev)
+    smax = torch.linspace(0.0, 1.0, M)[None, None, :].to(dev)
+    ca, cb = (0.6180339887, 0.7861513778) if family == "ddpm" else (0.4, 1 - 0.4)
+    norm = ((src - smin) / (smax - smin) * 2 - 1).transpose(-2, -1)[:, None]
+    ref = to_time_major(ca * norm + cb * noise)
+    got = shallow_start(src, noise, smin, smax, ca, cb)
+    assert torch.equal(got, ref)
+    # through the sampler: same final mel with the fused start state and with the eager one
+    H, L, C = 256, 3, 256
+    ds.hparams.clear()
+    ds.hparams.update(hidden_size=H, use_shallow_diffusion=True, K_step=400, K_step_infer=400, diff_speedup=100, diff_accelerator="ddim",
+                      timesteps=1000, schedule_type="linear", sampling_algorithm="euler", sampling_steps=5, T_start=0.4, T_start_infer=0.4,
+                      time_scale_factor=1000)
+    bb = dict(num_layers=L, num_channels=C, dilation_cycle_length=3)
+    if family == "ddpm":
+        m = ds.GaussianDiffusion(M, 1, 1000, 400, "wavenet", bb, spec_min=[-12.0], spec_max=[0.0])
+        net = m.denoise_fn
+    else:
+        m = ds.RectifiedFlow(M, 1, t_start=0.4, backbone_type="wavenet", backbone_args=bb, spec_min=[-12.0], spec_max=[0.0])
+        net = m.velocity_fn
+    net.load_state_dict(random_state_dict(M, 1, L, C, H, seed=12))
+    m = m.eval().to(dev)
+    cond = torch.randn(B, T, H, generator=g).to(dev)
+    torch.manual_seed(9)
+    fused = m(cond, src_spec=src, infer=True)
+    torch.manual_seed(9)
+    with torch.no_grad():  # the eager start state, as the reference composes it
+        spec = m.norm_spec(src).transpose(-2, -1)[:, None]
+        kw = dict(x_start=spec) if family == "ddpm" else dict(x_end=spec)
+        eager = m.denorm_spec(m.inference(cond.transpose(1, 2), b=B, device=cond.device, **kw))
+    assert torch.equal(fused, eager)
