@@ -737,7 +737,7 @@ extern "C" int ds_session_set_cond(ds_session* s, const float* cond_bth, void* s
     }
   }
   if (s->stack) {
-    // hoisted conditioner projection for the whole-network kernel: cproj[row][l][2C] = W_cond_l * cond + b_dil_l + b_cond_l in the
+    // hoisted conditioner projection for the whole-network kernel: cproj[l][row][2C] = W_cond_l * cond + b_dil_l + b_cond_l in the
     // 128-row-pass column order of the narrow gate pack (64 gate columns pre-multiplied by 0.5 | 64 filter columns), f16
     const ds_plan* p = s->plan;
     const int C = p->C, L = p->L;
@@ -746,13 +746,14 @@ extern "C" int ds_session_set_cond(ds_session* s, const float* cond_bth, void* s
     memset(&g, 0, sizeof(g));
     g.T = s->T; g.B = s->B; g.tiles_t = ceil_div(s->T, 128); g.scale = 1.0f;
     g.tmA0 = s->tm_cond; g.tmB = p->has_small ? p->tm_w1s : p->tm_w1; g.kb_a0 = H / 64; g.n_taps = 1; g.b_k0 = 3 * C;
-    // ONE launch for all L layers: their conditioner rows are consecutive in the packed gate matrix, so the GEMM has N = L * 2C
-    // and writes [row][l][2C] (a 20-launch loop here was 2 % of a pitch-predictor call)
+    // ONE launch for all L layers: their conditioner rows are consecutive in the packed gate matrix, so the GEMM has N = L * 2C; the
+    // epilogue scatters layer l's columns to [l][row][2C] (GemmParams::grp_n) -- a [row][l][2C] layout made the gate epilogue's row
+    // reads 10 % of a multi-tile evaluation slower; the 20-launch loop this replaces was 2 % of a pitch-predictor call
     g.n_tiles = L * 2 * C / 128; g.total_tiles = s->B * g.tiles_t * g.n_tiles;
-    g.ld_out = L * 2 * C; g.out_c0 = 0; g.b_row0 = 0;
+    g.ld_out = 2 * C; g.out_c0 = 0; g.b_row0 = 0;
+    g.grp_n = 2 * C; g.grp_stride = (long)rows * 2 * C;
     g.out = s->ws + s->o_scproj;
     g.bias = (const float*)(p->packed + (p->has_small ? p->o_b1s : p->o_b1));
-    (void)rows;
     DS_TRY(launch_gemm(128, EPI_CPROJ, g, (cudaStream_t)stream));
   }
   s->cond_set = true;

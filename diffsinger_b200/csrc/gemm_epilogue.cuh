@@ -207,7 +207,8 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
     // column order, gate columns (first half of every BN-column pass) pre-multiplied by 0.5 for sigmoid-by-tanh
     const int n0 = nt * BN;
     const float* bias = p.bias + n0;
-    uint16_t* out = reinterpret_cast<uint16_t*>(p.out) + row * p.ld_out + p.out_c0 + n0;
+    const int grp = p.grp_n > 0 ? n0 / p.grp_n : 0;  // a BN-column pass never straddles two groups (grp_n % BN == 0)
+    uint16_t* out = reinterpret_cast<uint16_t*>(p.out) + grp * p.grp_stride + row * p.ld_out + p.out_c0 + (n0 - grp * p.grp_n);
 #pragma unroll 1
     for (int c = half; c < BN / 32; c += 2) {
       uint32_t a[32];

@@ -60,6 +60,10 @@ struct GemmParams {
   // three times (hi*hi, lo*hi, hi*lo) into the same fp32 accumulator.
   int a0_lo, a1_lo, w_lo;  // offsets of the lo halves in A0 / A1 (channels) and W (K)
   int out_lo, res_lo;      // offsets of the lo halves in out / res_in (channels)
+  // EPI_CPROJ over several layers in one launch: output column n belongs to group n / grp_n and is stored at
+  // out + (n / grp_n) * grp_stride + row * ld_out + n % grp_n  (elements; grp_n = 0: one group)
+  int grp_n;
+  long grp_stride;
   // LayerNorm folded into the GEMMs around it (LYNXNet strong_cond, lynxnet.py:52-56 with the step vector added before the norm):
   //   producer (LINEAR / RES epilogues): per row and per (N tile, warp half) the partial sums {sum r, sum r^2, sum r d, 0} of the
   //   bf16-ROUNDED outputs r and the next norm's step vector d -> stats_out[row][parts] (float4), parts = 2 * n_tiles;

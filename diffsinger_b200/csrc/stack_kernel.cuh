@@ -55,7 +55,7 @@ struct StackParams {
   CUtensorMap tmWout;   // output_projection (o_wout): dims (C, FMr), box (64, nout)
   const float* x;       // [B][T][FM] fp32
   float* out;           // [B][T][FM] fp32
-  const uint16_t* cproj;  // f16 [B*T][L][2C], 128-column passes [64 gate (x0.5, bias included) | 64 filter (bias included)]
+  const uint16_t* cproj;  // f16 [L][B*T][2C], 128-column passes [64 gate (x0.5, bias included) | 64 filter (bias included)]
   const float* bhead;   // [C]
   const float* dtab;    // step-embedding projection of layer 0 for this evaluation: [vec_bstride * b + c]
   const float* rtab;    // folded residual vectors (b2_l - d_l)/sqrt(2) + d_{l+1}: [vec_bstride * b + l * C + c]
@@ -550,7 +550,7 @@ ds_stack_kernel(const __grid_constant__ StackParams p) {
     for (int l = 0; l < L; ++l) {
       // ---- gate: z = sigmoid(g) * tanh(f), packed-half math as in layer_kernel.cuh                wavenet.py:40-42
       {
-        const uint16_t* add = p.cproj + (grow * L + l) * (2 * C) + 128 * r + 32 * half;
+        const uint16_t* add = p.cproj + (static_cast<size_t>(l) * p.B * p.T + grow) * (2 * C) + 128 * r + 32 * half;
         uint4 bg[4], bf[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
