@@ -57,14 +57,18 @@ class ConvNeXtDecoder(nn.Module):
         return d
 
     # noinspection PyUnusedLocal
-    def forward(self, x, infer=False):
-        """x [B, T, in_dims] -> [B, T, out_dims]"""
+    def forward(self, x, infer=False, lengths=None):
+        """x [B, T, in_dims] -> [B, T, out_dims].  lengths (native path only): frame counts of a ragged batch whose rows beyond an
+        utterance's end are ZERO in x; the residual stream is then kept at zero there, so the k = 7 convolutions see each utterance's
+        own padding and every utterance equals its batch-1 result (outputs beyond the end are undefined)."""
         if torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in self.parameters())):
+            if lengths is not None:
+                raise RuntimeError("ragged batches are an inference feature of the native path")
             x = self.inconv(x.transpose(1, 2))
             for conv in self.conv:
                 x = conv(x)
             return self.outconv(x).transpose(1, 2)
-        return self._forward_native(x)
+        return self._forward_native(x, lengths)
 
     # ------------------------------------------------------------------ native path
     def _pack(self, dev):
@@ -97,8 +101,14 @@ class ConvNeXtDecoder(nn.Module):
         return self._packed
 
     @torch.no_grad()
-    def _forward_native(self, x):
+    def _forward_native(self, x, lengths=None):
         B, T, _ = x.shape
+        lens = None
+        if lengths is not None:
+            lengths = [int(v) for v in lengths]
+            if len(lengths) != B or min(lengths) < 1 or max(lengths) > T:
+                raise ValueError(f"ragged batch: need {B} lengths in [1, {T}], got {lengths}")
+            lens = torch.tensor(lengths, dtype=torch.int32).to(x.device)
         P = self._pack(x.device)
         C, rows, bf = self.num_channels, B * T, torch.bfloat16
         bkey = (B, T, ops.stream())
@@ -111,12 +121,12 @@ class ConvNeXtDecoder(nn.Module):
         xb, h, d, n, m = bufs["xb"], bufs["h"], bufs["d"], bufs["n"], bufs["m"]
         ops.cast_bf16(xb, x.detach().to(torch.float32).contiguous().view(rows, self.in_dims))
         bn_c = ops.tile_n(C)
-        ops.gemm(ops.EPI_LINEAR, bn_c, B, T, xb, P["w_in"], h, n_taps=self.kernel_size, bias=P["b_in"])
+        ops.gemm(ops.EPI_LINEAR, bn_c, B, T, xb, P["w_in"], h, n_taps=self.kernel_size, bias=P["b_in"], lengths=lens)
         for blk in P["blocks"]:
             ops.dwconv(d, h, blk["dw_w"], blk["dw_b"], B, T, 7)
             ops.layernorm(n, d, blk["ln_g"], blk["ln_b"], 1e-6)
             ops.gemm(ops.EPI_LINEAR, ops.tile_n(4 * C), B, T, n, blk["w1"], m, bias=blk["b1"], act=ops.ACT_GELU)
-            ops.gemm(ops.EPI_RES, bn_c, B, T, m, blk["w2"], h, vec=blk["b2"], vec_bstride=0, res=h)
+            ops.gemm(ops.EPI_RES, bn_c, B, T, m, blk["w2"], h, vec=blk["b2"], vec_bstride=0, res=h, lengths=lens)
         out = torch.empty(B, T, self.out_dims, dtype=torch.float32, device=x.device)
         ops.gemm(ops.EPI_OUTF32, P["bn_o"], B, T, h, P["w_out"], out.view(rows, self.out_dims), n_taps=self.kernel_size, bias=P["b_out"],
                  n_real=self.out_dims)
@@ -163,8 +173,8 @@ class AuxDecoderAdaptor(nn.Module):
         b = (self.spec_max + self.spec_min) / 2.
         return x * k + b
 
-    def forward(self, condition, infer=False):
-        x = self.decoder(condition, infer=infer)  # [B, T, F x C]
+    def forward(self, condition, infer=False, lengths=None):
+        x = self.decoder(condition, infer=infer) if lengths is None else self.decoder(condition, infer=infer, lengths=lengths)  # [B, T, F x C]
         if self.n_feats > 1:
             x = x.reshape(-1, x.shape[1], self.n_feats, self.out_dims).transpose(1, 2)  # [B, F, T, C]
         if infer:

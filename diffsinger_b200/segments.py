@@ -58,7 +58,7 @@ def _ragged_groups(lengths: Sequence[int], cap: int, min_fill: float = 0.0) -> L
     return groups
 
 
-def _sample_ragged(diffusion, conditions, cap: int, min_fill: float, src_specs=None) -> List[torch.Tensor]:
+def _sample_ragged(diffusion, conditions, cap: int, min_fill: float, src_specs=None, aux_decoder=None) -> List[torch.Tensor]:
     """All batch-1 segments through ragged batches.  Noise is drawn segment by segment in the caller's order from the global
     generator -- the values a segment-by-segment loop would draw -- then padded; outputs are cut back to each segment's length."""
     dev = conditions[0].device
@@ -76,6 +76,8 @@ def _sample_ragged(diffusion, conditions, cap: int, min_fill: float, src_specs=N
             z[b, ..., :lens[i]] = noise[i][0]
             if src is not None:
                 src[b, :lens[i]] = src_specs[i][0]
+        if aux_decoder is not None:  # the shallow-diffusion source of the whole ragged batch in one pass
+            src = aux_decoder(cond, infer=True, lengths=[lens[i] for i in grp])
         saved = getattr(diffusion, '_noise_override', None), getattr(diffusion, '_lengths_override', None)
         diffusion._noise_override, diffusion._lengths_override = z, [lens[i] for i in grp]
         try:
@@ -93,7 +95,7 @@ def _sample_ragged(diffusion, conditions, cap: int, min_fill: float, src_specs=N
 
 
 @torch.no_grad()
-def sample_segments(diffusion, conditions: Sequence[torch.Tensor], n_streams: int = 4, ragged: bool = True,
+def sample_segments(diffusion, conditions: Sequence[torch.Tensor], n_streams: int = 4, ragged: bool = True, aux_decoder=None,
                     **forward_kwargs) -> List[torch.Tensor]:
     """`diffusion(cond, infer=True, **forward_kwargs)` for every `cond` ([B, T_i, H], any lengths).  Returns the outputs in
     order; they are safe to use on the current stream.
@@ -102,19 +104,30 @@ def sample_segments(diffusion, conditions: Sequence[torch.Tensor], n_streams: in
     [1, T_i, M]), segments are padded into ragged batches (include/dsb200.h: ds_session_set_lengths; LYNXNet: the SwiGLU GEMM masks the
     depthwise conv's input): every utterance keeps its own end, so each output equals the segment-by-segment result.  Otherwise up to
     `n_streams` segments are in flight on CUDA streams;
-    per-segment keyword tensors (e.g. `src_spec`) are passed as lists of the same length as `conditions`."""
+    per-segment keyword tensors (e.g. `src_spec`) are passed as lists of the same length as `conditions`.
+
+    aux_decoder: a diffsinger_b200.AuxDecoderAdaptor -- the shallow-diffusion sources are then computed here (for a ragged batch in
+    one pass with the same lengths), i.e. the call covers `aux_decoder(condition, infer=True)` -> `diffusion(condition, src_spec=...)`
+    of modules/toplevel.py:94-103."""
     if not conditions:
         return []
     dev = conditions[0].device
     if dev.type != 'cuda':
         raise RuntimeError("sample_segments needs CUDA tensors (there is no CPU path)")
+    if aux_decoder is not None:
+        if 'src_spec' in forward_kwargs:
+            raise ValueError("pass either aux_decoder or src_spec")
+        if not hasattr(aux_decoder, 'decoder') or not hasattr(aux_decoder.decoder, '_forward_native'):
+            raise TypeError("aux_decoder must be a diffsinger_b200.AuxDecoderAdaptor")
     src_specs = forward_kwargs.get('src_spec')
     only_src = set(forward_kwargs) <= {'src_spec'} and (src_specs is None or (isinstance(src_specs, (list, tuple)) and
                                                                              all(v.dim() == 3 for v in src_specs)))
     if ragged and only_src and all(c.shape[0] == 1 for c in conditions) and len(conditions) > 1:
-        cap, min_fill = _ragged_capacity(diffusion, max(int(c.shape[1]) for c in conditions), src_specs is not None)
+        cap, min_fill = _ragged_capacity(diffusion, max(int(c.shape[1]) for c in conditions), src_specs is not None or aux_decoder is not None)
         if cap:
-            return _sample_ragged(diffusion, conditions, cap, min_fill, src_specs)
+            return _sample_ragged(diffusion, conditions, cap, min_fill, src_specs, aux_decoder)
+    if aux_decoder is not None:  # the stream path: one source per segment, as the reference's DiffSingerAcoustic.forward computes it
+        forward_kwargs = dict(forward_kwargs, src_spec=[aux_decoder(c, infer=True) for c in conditions])
     main = torch.cuda.current_stream(dev)
     n_streams = max(1, min(n_streams, len(conditions)))
     pool = getattr(diffusion, '_segment_streams', None)

@@ -51,3 +51,50 @@ def test_default_size_matches_oracle(B, T):
     with pytest.raises(RuntimeError, match="no CPU inference path"):
         with torch.no_grad():
             ds.ConvNeXtDecoder(256, 128)(cond)
+
+
+def test_ragged_pipeline_aux_decoder_then_shallow_sampler():
+    """The default acoustic pipeline after the encoder (modules/toplevel.py:94-103: aux decoder -> shallow diffusion) over segments of
+    different lengths as ragged batches: `sample_segments(diffusion, conds, aux_decoder=...)` must equal the segment-by-segment loop
+    (each utterance keeps its own conv edges in the ConvNeXt decoder AND in the LYNXNet denoiser)."""
+    from diffsinger_b200.synthetic import random_lynx_state_dict
+    H, M, C = 256, 128, 256
+    torch.manual_seed(0)
+    ad = ds.AuxDecoderAdaptor(H, M, 1, [-12.0], [0.0], "convnext", dict(num_channels=256, num_layers=2, kernel_size=7, dropout_rate=0.1))
+    with torch.no_grad():
+        for blk in ad.decoder.conv:
+            blk.gamma.fill_(0.3)  # layer scale away from its 1e-6 initialisation, or the blocks are invisible
+    ad = ad.eval().to(dev)
+    ds.hparams.clear()
+    ds.hparams.update(hidden_size=H, use_shallow_diffusion=True, sampling_algorithm="euler", sampling_steps=4, T_start=0.4, T_start_infer=0.4,
+                      time_scale_factor=1000)
+    m = ds.RectifiedFlow(M, 1, t_start=0.4, backbone_type="lynxnet",
+                         backbone_args=dict(num_layers=2, num_channels=C, expansion_factor=2, kernel_size=31, strong_cond=True),
+                         spec_min=[-12.0], spec_max=[0.0])
+    m.velocity_fn.load_state_dict(random_lynx_state_dict(M, 1, 2, C, H, expansion_factor=2, kernel_size=31, activation="PReLU", seed=4))
+    m = m.eval().to(dev)
+    lens = [300, 77, 515, 257]
+    g = torch.Generator().manual_seed(31)
+    conds = [torch.randn(1, t, H, generator=g).to(dev) for t in lens]
+    torch.manual_seed(5)
+    with torch.no_grad():
+        alone = [m(c, src_spec=ad(c, infer=True), infer=True).cpu() for c in conds]
+    torch.manual_seed(5)
+    batched = [y.cpu() for y in ds.sample_segments(m, conds, aux_decoder=ad)]
+    assert any(ws.lengths is not None for ws in m.velocity_fn.engine().workspaces.values()), "the ragged path did not run"
+    worst = 0.0
+    for t, a, b in zip(lens, alone, batched):
+        assert a.shape == b.shape == (1, t, M)
+        worst = max(worst, rel_l2(b, a), rel_l2(b[:, -24:], a[:, -24:]), rel_l2(b[:, :24], a[:, :24]))
+    print(f"[ragged aux decoder + LYNXNet shallow reflow] worst rel-L2 vs one by one: {worst:.3e}")
+    assert worst < 1e-2
+    # the aux decoder alone: a padded batch with lengths equals the lone run, without them the last frames differ
+    t_max = max(lens)
+    cond = torch.zeros(2, t_max, H, device=dev)
+    cond[0, :lens[0]], cond[1] = conds[0][0], conds[2][0]
+    with torch.no_grad():
+        lone = ad(conds[0], infer=True).cpu()
+        masked = ad(cond, infer=True, lengths=[lens[0], lens[2]]).cpu()
+        plain = ad(cond, infer=True).cpu()
+    assert rel_l2(masked[0:1, :lens[0]], lone) < 1e-3
+    assert rel_l2(plain[0:1, lens[0] - 6:lens[0]], lone[:, -6:]) > 1e-2
