@@ -374,6 +374,17 @@ def extra_config1(ds, dev, random_state_dict, threads):
         ds.sample_segments(m, dconds)
         torch.cuda.synchronize()
         rag_ms = (time.perf_counter() - t0) * 1e3
+        # tokens -> mel in one call: padded encoder batches + ragged sampler batches (diffsinger_b200.infer_segments)
+        tensor_batches = [{k: bt[k] for k in ('tokens', 'mel2ph', 'f0', 'key_shift', 'speed', 'languages') if torch.is_tensor(bt.get(k))}
+                          for bt in dbatches]
+        torch.manual_seed(99)
+        pipe = ds.infer_segments(enc, m, tensor_batches)
+        pipe_err = max(float((a - b).norm() / b.norm()) for a, b in zip(pipe, one_by_one))
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        ds.infer_segments(enc, m, tensor_batches)
+        torch.cuda.synchronize()
+        pipe_ms = (time.perf_counter() - t0) * 1e3
     # CPU arm + parity on the same noise
     cpu_frames, cpu_s, errs = 0, 0.0, []
     for i, cd in enumerate(conds):
@@ -397,6 +408,7 @@ def extra_config1(ds, dev, random_state_dict, threads):
             "gpu_streams_ms": round(par_ms, 1), "gpu_streams_frames_per_s": round(frames / (par_ms * 1e-3), 1),
             "gpu_ragged_batches_ms": round(rag_ms, 1), "gpu_ragged_frames_per_s": round(frames / (rag_ms * 1e-3), 1),
             "gpu_ragged_equals_one_by_one": bool(rag_equal),
+            "gpu_tokens_to_mel_ms": round(pipe_ms, 1), "gpu_tokens_to_mel_vs_one_by_one_rel_l2_max": round(pipe_err, 7),
             "gpu_encoder_ms_all_segments": round(enc_ms, 2), "encoder_cond_rel_l2_vs_reference_max": round(enc_err, 6),
             "cpu_reference_frames_per_s": round(cpu_frames / cpu_s, 1), "cpu_reference_segments": len(errs), "cpu_cores": threads,
             "final_mel_rel_l2_vs_reference": [round(e, 6) for e in errs]}

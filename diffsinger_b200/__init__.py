@@ -3,7 +3,7 @@ the WaveNet backbone (BACKBONES['wavenet']) and the GaussianDiffusion / Rectifie
 Host code is Python/PyTorch plumbing over the C ABI in include/dsb200.h (libdsb200.so)."""
 from .hparams import hparams, get_hparams
 from .backbones import BACKBONES, build_backbone, WaveNet, LYNXNet
-from .segments import sample_segments
+from .segments import encode_segments, infer_segments, sample_segments
 from .dropin import install_dropin
 from .sharding import sample_sharded
 from .fastspeech import FastSpeech2Acoustic
@@ -14,5 +14,5 @@ from .core import (GaussianDiffusion, PitchDiffusion, MultiVarianceDiffusion,
 
 __all__ = ["hparams", "get_hparams", "BACKBONES", "build_backbone", "WaveNet", "LYNXNet", "GaussianDiffusion",
            "PitchDiffusion", "MultiVarianceDiffusion", "RectifiedFlow", "PitchRectifiedFlow",
-           "MultiVarianceRectifiedFlow", "sample_segments", "install_dropin", "sample_sharded", "FastSpeech2Acoustic", "AUX_DECODERS", "AuxDecoderAdaptor", "ConvNeXtDecoder", "build_aux_decoder",
+           "MultiVarianceRectifiedFlow", "sample_segments", "encode_segments", "infer_segments", "install_dropin", "sample_sharded", "FastSpeech2Acoustic", "AUX_DECODERS", "AuxDecoderAdaptor", "ConvNeXtDecoder", "build_aux_decoder",
            "VOCODERS", "NsfHifiGAN"]

@@ -168,3 +168,61 @@ def sample_segments(diffusion, conditions: Sequence[torch.Tensor], n_streams: in
     for st in pool[:n_streams]:
         main.wait_stream(st)
     return outs
+
+
+TOKEN_LEVEL_KEYS = ('tokens', 'languages')  # [1, T_txt] inputs of the encoder; every other tensor of a segment is per frame ([1, T]) or broadcast
+
+
+@torch.no_grad()
+def encode_segments(encoder, batches: Sequence[dict], max_frames: int = MAX_RAGGED_FRAMES) -> List[torch.Tensor]:
+    """Conditions of many segments from the condition producer (diffsinger_b200.FastSpeech2Acoustic) in padded batches.
+
+    batches: one dict per segment as the reference's preprocess_input builds it (inference/ds_acoustic.py:70-207): `tokens`
+    [1, T_txt], `mel2ph` [1, T], `f0` [1, T], optionally `key_shift` / `speed` / variance curves [1, T], `languages` [1, T_txt],
+    `spk_mix_embed` [1, T or 1, H].  Segments of similar length are padded together -- tokens with the padding index 0, frames with
+    mel2ph = 0 -- which the encoder masks exactly (padded keys take no part in the attention, padded positions are zeroed after every
+    sub-layer), so every segment's condition equals its batch-1 result.  Returns [1, T_i, H] per segment, in order."""
+    if not batches:
+        return []
+    lens = [int(bt['mel2ph'].shape[1]) for bt in batches]
+    outs: List = [None] * len(batches)
+    for grp in _ragged_groups(lens, max(max_frames // 128, -(-max(lens) // 128)), 0.5):
+        t_max = max(lens[i] for i in grp)
+        tt_max = max(int(batches[i]['tokens'].shape[1]) for i in grp)
+        keys = [k for k, v in batches[grp[0]].items() if torch.is_tensor(v)]
+        packed = {}
+        for k in keys:
+            first = batches[grp[0]][k]
+            if first.dim() < 2:  # one value per segment (e.g. spk_embed_id [1])
+                packed[k] = torch.cat([batches[i][k].reshape(1) for i in grp])
+                continue
+            n = tt_max if k in TOKEN_LEVEL_KEYS else (1 if all(batches[i][k].shape[1] == 1 for i in grp) else t_max)
+            buf = first.new_zeros(len(grp), n, *first.shape[2:])
+            for b, i in enumerate(grp):
+                v = batches[i][k]
+                if v.shape[1] == n:
+                    buf[b] = v[0]
+                elif v.shape[1] == 1:
+                    buf[b] = v[0].expand(n, *v.shape[2:])
+                else:
+                    buf[b, :v.shape[1]] = v[0]
+            packed[k] = buf
+        extra = {k: v for k, v in packed.items() if k not in ('tokens', 'mel2ph', 'f0', 'key_shift', 'speed', 'languages', 'spk_embed_id')}
+        spk_id = packed.get('spk_embed_id')
+        if spk_id is not None and spk_id.dim() > 1:
+            spk_id = spk_id[:, 0]
+        cond = encoder(packed['tokens'], packed['mel2ph'], packed['f0'], key_shift=packed.get('key_shift'), speed=packed.get('speed'),
+                       spk_embed_id=spk_id, languages=packed.get('languages'), **extra)
+        for b, i in enumerate(grp):
+            outs[i] = cond[b:b + 1, :lens[i]].contiguous()
+    return outs
+
+
+@torch.no_grad()
+def infer_segments(encoder, diffusion, batches: Sequence[dict], aux_decoder=None, **kw) -> List[torch.Tensor]:
+    """tokens -> mel for all segments of a `.ds` file: encode_segments (padded encoder batches), then sample_segments (ragged
+    batches through the optional aux decoder and the sampler) -- the reference's DiffSingerAcoustic.forward (modules/toplevel.py:
+    82-122) applied to its per-segment inference loop (inference/ds_acoustic.py:234-244) at once.  Every segment's result equals
+    the one-by-one loop's (same noise draw order)."""
+    conds = encode_segments(encoder, batches)
+    return sample_segments(diffusion, conds, aux_decoder=aux_decoder, **kw)

@@ -126,3 +126,41 @@ def test_tokens_to_mel_in_one_cuda_graph():
         graph.replay()
         torch.cuda.synchronize()
     assert torch.isfinite(s_out).all() and rel_l2(s_out.cpu(), eager2.cpu()) < 1e-6
+
+
+def test_segments_pipeline_tokens_to_mel_in_padded_and_ragged_batches():
+    """encode_segments / infer_segments: the per-segment loop of inference/ds_acoustic.py:234-244 (tokens -> condition -> sampler) over
+    segments of different lengths as padded encoder batches + ragged sampler batches; every segment equals its batch-1 result."""
+    from diffsinger_b200.synthetic import random_state_dict
+    H, heads, layers, vocab, M = 256, 2, 2, 61, 128
+    ds.hparams.clear()
+    ds.hparams.update(hidden_size=H, enc_layers=layers, num_heads=heads, enc_ffn_kernel_size=3, ffn_act="gelu", dropout=0.1, use_pos_embed=True,
+                      use_rope=True, rel_pos=True, use_lang_id=False, use_spk_id=False, use_key_shift_embed=True, use_speed_embed=True,
+                      diff_speedup=200, diff_accelerator="ddim", timesteps=1000, K_step=1000, use_shallow_diffusion=False,
+                      schedule_type="linear")
+    torch.manual_seed(5)
+    enc = ds.FastSpeech2Acoustic(vocab).eval().to(dev)
+    m = ds.GaussianDiffusion(M, 1, 1000, 1000, "wavenet", dict(num_layers=3, num_channels=256, dilation_cycle_length=3),
+                             spec_min=[-12.0], spec_max=[0.0])
+    m.denoise_fn.load_state_dict(random_state_dict(M, 1, 3, 256, H, seed=8))
+    m = m.eval().to(dev)
+    g = torch.Generator().manual_seed(6)
+    batches = []
+    for Tt, T in ((31, 300), (9, 77), (60, 515), (27, 257), (44, 512)):
+        tok = torch.randint(1, vocab, (1, Tt), generator=g)
+        mel2ph = torch.sort(torch.randint(1, Tt + 1, (1, T), generator=g), dim=1).values
+        batches.append(_to(dict(tokens=tok, mel2ph=mel2ph, f0=torch.rand(1, T, generator=g) * 300 + 80,
+                                key_shift=torch.full((1, 1), 2.0), speed=torch.full((1, 1), 1.0))))
+    with torch.no_grad():
+        conds_alone = [enc(b["tokens"], b["mel2ph"], b["f0"], key_shift=b["key_shift"], speed=b["speed"]) for b in batches]
+        torch.manual_seed(3)
+        mels_alone = [m(c, infer=True) for c in conds_alone]
+    conds = ds.encode_segments(enc, batches)
+    for a, b in zip(conds_alone, conds):
+        assert a.shape == b.shape
+        assert rel_l2(b.cpu(), a.cpu()) < 1e-6, rel_l2(b.cpu(), a.cpu())
+    torch.manual_seed(3)
+    mels = ds.infer_segments(enc, m, batches)
+    for a, b in zip(mels_alone, mels):
+        assert a.shape == b.shape
+        assert rel_l2(b.cpu(), a.cpu()) < 1e-5
