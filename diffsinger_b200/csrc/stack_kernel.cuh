@@ -9,8 +9,9 @@
 //   * x~ (with a +-16-frame halo for the dilated conv) and the gated activation z live in SHARED MEMORY as K-major
 //     SWIZZLE_128B operand tiles ([rows][64 channels] per k-block); after each epilogue every CTA broadcasts its 64-channel
 //     slice (16 KB) to the other CTAs of the cluster with `cp.async.bulk.shared::cluster` (DSMEM) that completes on the
-//     RECEIVER's mbarrier -- an all-gather without any cluster-wide barrier; the consumer MMA starts on a k-block as soon
-//     as that block has landed (blocks are sent and consumed in the same rotated order).
+//     RECEIVER's mbarrier -- an all-gather without any cluster-wide barrier; every peer block has its own barrier and the
+//     copies leave one after the other in the order the peers consume them, so the consumer MMA starts on a k-block as
+//     soon as that block has landed (DSMEM moves only ~17-21 B/clk per SM: the exchange is bandwidth-bound);
 //   * the three conv taps are three UMMA descriptors into the same x~ tile shifted by dil rows (as in layer_kernel.cuh);
 //   * the skip sum is accumulated in TMEM across all L layers (64 fp32 columns per CTA) and never touches memory
 //     ("skip accumulation kept on-chip");
@@ -21,7 +22,9 @@
 // through a small global (L2-resident) buffer of self-validating packets ({data, flag} per 8 bytes, the "LL" idea of NCCL):
 // the sender's epilogue threads just store, the receiver's epilogue threads (idle while the centre taps run) poll the packets
 // and write the halo rows -- point-to-point, no fence, no counter, no grid-wide barrier.
-// All clusters of a launch must be co-resident (the host checks cudaOccupancyMaxActiveClusters).
+// All clusters of a launch must be co-resident (the host checks cudaOccupancyMaxActiveClusters).  Ragged batches
+// (StackParams::len): every utterance has its own frame count -- validity masks, the right-neighbour flag and the early exit of
+// tiles beyond the end follow it, so a short utterance in a padded batch computes exactly what it computes alone.
 //
 // Warp roles (384 threads): warps 0 / 3 / 2 = weight TMA producers, warp1 = MMA issuer (all four run converged with one elected
 // issuing lane), warp2 also allocates TMEM, warps 4..11 = epilogue + halo receive (warp & 3 = TMEM lane quadrant, (warp - 4) >> 2 = which 32 of the CTA's 64 channels).
