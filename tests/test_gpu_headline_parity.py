@@ -124,3 +124,43 @@ def test_twenty_step_final_mel_at_20x512_fused(kind, B, T):
     # here, lincomb_kernel there), which the bf16 rounding of the next evaluation's input amplifies a little (measured 8e-5)
     mel_walk = (x_nat.cpu() + 1) / 2 * (SPEC_MAX - SPEC_MIN) + SPEC_MIN
     assert rel_l2(mel_walk, mel.cpu()) < 1e-3
+
+
+def test_full_size_configs1_properties():
+    """BASELINE configs[1] at its FULL size (64 utterances x 2000 frames, 20 x 512, DPM-Solver++ 20 steps) through size-independent
+    properties: (1) the call is deterministic (graph capture == replay, bit for bit); (2) an utterance's mel does not depend on
+    its batch: rows of the 64-utterance batch equal the same rows sampled as a 37-utterance batch bit for bit (both on the fused
+    kernel: tiles are scheduled differently, the per-tile arithmetic is the same); (3) one full-length utterance against the oracle
+    (final mel <= 1e-2)."""
+    B, T = 64, 2000
+    sd = random_state_dict(M, F, L, C, H, seed=2025)
+    m = _model("dpm-solver", sd)
+    g = torch.Generator().manual_seed(7)
+    cond = torch.randn(B, T, H, generator=g)
+    noise = torch.randn(B, F, M, T, generator=g)
+    dcond, dnoise = cond.to(dev), noise.to(dev)
+
+    def sample(rows):
+        m._noise_override = dnoise[rows].contiguous()
+        try:
+            with torch.no_grad():
+                return m(dcond[rows].contiguous(), infer=True)
+        finally:
+            m._noise_override = None
+
+    full = sample(slice(0, B))
+    again = sample(slice(0, B))
+    sess = next(iter(m.denoise_fn.engine().sessions.values()))
+    assert sess.path == "fused" and (sess.B, sess.T) == (B, T)
+    assert torch.equal(full, again)
+    part = sample(slice(20, 57))  # 37 utterances: still more than one wave of tile pairs -> the fused kernel
+    assert {s.path for s in m.denoise_fn.engine().sessions.values()} == {"fused"}
+    assert torch.equal(part, full[20:57])
+    assert torch.isfinite(full).all()
+    prog, _ = _program("dpm-solver", m)
+    row = 41
+    x_ref = run_program_cpu(OracleWaveNet(sd, F, CYCLE), prog, to_time_major(noise[row:row + 1]), cond[row:row + 1].transpose(1, 2), F)
+    mel_ref = (x_ref + 1) / 2 * (SPEC_MAX - SPEC_MIN) + SPEC_MIN
+    err = rel_l2(full[row:row + 1].cpu(), mel_ref)
+    print(f"\n[configs[1] full size B{B} x T{T}] deterministic, batch-invariant; utterance {row} final mel rel-L2 vs oracle {err:.3e}")
+    assert err < MEL_TOL
