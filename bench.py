@@ -284,7 +284,8 @@ def extra_corners(model, dev, c):
         rag = ds.sample_segments(model, conds)
         err = max(float((a - b).norm() / b.norm()) for a, b in zip(rag, one))
         ms_one = timed(lambda: [model(cd, infer=True) for cd in conds], 1)
-        ms_rag = timed(lambda: ds.sample_segments(model, conds), 1)
+        ds.sample_segments(model, conds)  # the one-by-one loop above walked 30 other sessions: touch the ragged ones again
+        ms_rag = timed(lambda: ds.sample_segments(model, conds), 2)
         out["segments_30_ragged"] = {"frames": sum(lens), "one_by_one_ms": round(ms_one, 1), "ragged_batches_ms": round(ms_rag, 1),
                                      "ragged_frames_per_s": round(sum(lens) / (ms_rag * 1e-3), 1),
                                      "ragged_vs_one_by_one_rel_l2_max": round(err, 7)}
@@ -382,9 +383,10 @@ def extra_config1(ds, dev, random_state_dict, threads):
         pipe_err = max(float((a - b).norm() / b.norm()) for a, b in zip(pipe, one_by_one))
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        ds.infer_segments(enc, m, tensor_batches)
+        for _ in range(2):
+            ds.infer_segments(enc, m, tensor_batches)
         torch.cuda.synchronize()
-        pipe_ms = (time.perf_counter() - t0) * 1e3
+        pipe_ms = (time.perf_counter() - t0) * 1e3 / 2
     # CPU arm + parity on the same noise
     cpu_frames, cpu_s, errs = 0, 0.0, []
     for i, cd in enumerate(conds):

@@ -16,10 +16,12 @@ import torch
 
 
 MAX_RAGGED_FRAMES = 1 << 16  # padded frames (B * T_max) of one ragged batch on the per-layer kernels
+CALL_OVERHEAD_TILES = 62     # ... and the fixed cost of one sampler call there, in 128-frame tile-times (see _ragged_groups)
 
 
 def _ragged_capacity(diffusion, t_longest: int, have_src: bool = False):
-    """(tiles of 128 frames one ragged batch may hold, shortest segment of a batch as a fraction of its longest); (0, 0): this
+    """(tiles of 128 frames one ragged batch may hold, shortest segment of a batch as a fraction of its longest, (floor, overhead)
+    of the grouping cost model in tiles); (0, 0, (0, 0)): this
     sampler / backbone / configuration cannot run ragged batches.  Plans on the whole-network kernel are bounded by the
     co-resident clusters (ds_plan_stack_capacity) as long as the longest segment fits, and padding costs them nothing (tiles beyond
     an utterance's end exit at once); everything else runs the per-layer kernels, which compute the padding too: batches of at most
@@ -30,35 +32,48 @@ def _ragged_capacity(diffusion, t_longest: int, have_src: bool = False):
     eng = backbone.engine()
     hp = get_hparams()
     if hasattr(diffusion, 'denoise_fn') and hp.get('diff_speedup', 0) <= 1:
-        return 0, 0.0  # ancestral chain draws fresh noise every step
+        return 0, 0.0, (0, 0)  # ancestral chain draws fresh noise every step
     if getattr(diffusion, 'use_shallow_diffusion', False) and not have_src:
-        return 0, 0.0  # shallow diffusion needs the per-segment source spectrograms (src_spec=[...])
+        return 0, 0.0, (0, 0)  # shallow diffusion needs the per-segment source spectrograms (src_spec=[...])
     if not hasattr(eng, 'plan'):  # LYNXNet: the SwiGLU GEMM masks the depthwise conv's input (lynx_engine.LynxWorkspace.set_lengths)
-        return max(MAX_RAGGED_FRAMES // 128, -(-t_longest // 128)), 0.5
+        return max(MAX_RAGGED_FRAMES // 128, -(-t_longest // 128)), 0.25, (0, CALL_OVERHEAD_TILES)
     cap = int(nat.lib().ds_plan_stack_capacity(eng.plan))
     if cap >= -(-t_longest // 128):
-        return cap, 0.0
-    return max(MAX_RAGGED_FRAMES // 128, -(-t_longest // 128)), 0.5
+        return cap, 0.0, (cap, 0)  # one launch per evaluation whatever its size: fewest groups
+    return max(MAX_RAGGED_FRAMES // 128, -(-t_longest // 128)), 0.25, (0, CALL_OVERHEAD_TILES)
 
 
-def _ragged_groups(lengths: Sequence[int], cap: int, min_fill: float = 0.0) -> List[List[int]]:
-    """Segment indices grouped for ragged batches: similar lengths together (longest first), B * ceil(T_max / 128) <= cap tiles,
-    every segment at least min_fill * T_max frames long."""
+def _ragged_groups(lengths: Sequence[int], cap: int, min_fill: float = 0.0, floor: int = 0, overhead: int = 0) -> List[List[int]]:
+    """Segment indices grouped for ragged batches.  Segments are taken longest first and a group is a run of that order (similar
+    lengths together), B * ceil(T_max / 128) <= cap tiles (a single segment is always allowed), every segment at least
+    min_fill * T_max frames long.  Among those partitions the one with the least estimated cost is chosen, a group costing
+    max(B * ceil(T_max / 128), floor) + overhead tile-times.  Whole-network kernel: floor = cap (one launch per evaluation costs
+    the same whatever its size, i.e. fewest groups).  Per-layer kernels: overhead = the fixed cost of a sampler call in tile-times
+    (measured at 20 x 512, 20 steps: ~9 ms + 0.145 ms per 128-frame tile -> 62)."""
     order = sorted(range(len(lengths)), key=lambda i: -lengths[i])
+    n = len(order)
+    if n == 0:
+        return []
+    tiles = [-(-lengths[i] // 128) for i in order]
+    best = [0.0] + [float('inf')] * n   # best[k]: least cost of the first k segments
+    cut = [0] * (n + 1)
+    for k in range(1, n + 1):
+        for j in range(k - 1, -1, -1):  # group = order[j:k], its longest segment is order[j]
+            size = k - j
+            if size > 1 and (size * tiles[j] > cap or lengths[order[k - 1]] < min_fill * lengths[order[j]]):
+                break
+            cost = best[j] + max(size * tiles[j], floor) + overhead + 1e-6 * size * tiles[j]
+            if cost < best[k]:
+                best[k], cut[k] = cost, j
     groups: List[List[int]] = []
-    cur: List[int] = []
-    for i in order:
-        t_max = lengths[cur[0]] if cur else lengths[i]
-        if cur and ((len(cur) + 1) * -(-t_max // 128) > cap or lengths[i] < min_fill * t_max):
-            groups.append(cur)
-            cur = []
-        cur.append(i)
-    if cur:
-        groups.append(cur)
-    return groups
+    k = n
+    while k > 0:
+        groups.append(order[cut[k]:k])
+        k = cut[k]
+    return groups[::-1]
 
 
-def _sample_ragged(diffusion, conditions, cap: int, min_fill: float, src_specs=None, aux_decoder=None) -> List[torch.Tensor]:
+def _sample_ragged(diffusion, conditions, cap: int, min_fill: float, src_specs=None, aux_decoder=None, cost=(0, 0)) -> List[torch.Tensor]:
     """All batch-1 segments through ragged batches.  Noise is drawn segment by segment in the caller's order from the global
     generator -- the values a segment-by-segment loop would draw -- then padded; outputs are cut back to each segment's length."""
     dev = conditions[0].device
@@ -66,7 +81,7 @@ def _sample_ragged(diffusion, conditions, cap: int, min_fill: float, src_specs=N
     F, M = diffusion.num_feats, diffusion.out_dims
     noise = [torch.randn(1, F, M, t, device=dev) for t in lens]
     outs: List = [None] * len(conditions)
-    for grp in _ragged_groups(lens, cap, min_fill):
+    for grp in _ragged_groups(lens, cap, min_fill, *cost):
         t_max = max(lens[i] for i in grp)
         cond = conditions[0].new_zeros(len(grp), t_max, conditions[0].shape[2])
         z = torch.zeros(len(grp), F, M, t_max, device=dev)
@@ -123,9 +138,10 @@ def sample_segments(diffusion, conditions: Sequence[torch.Tensor], n_streams: in
     only_src = set(forward_kwargs) <= {'src_spec'} and (src_specs is None or (isinstance(src_specs, (list, tuple)) and
                                                                              all(v.dim() == 3 for v in src_specs)))
     if ragged and only_src and all(c.shape[0] == 1 for c in conditions) and len(conditions) > 1:
-        cap, min_fill = _ragged_capacity(diffusion, max(int(c.shape[1]) for c in conditions), src_specs is not None or aux_decoder is not None)
+        cap, min_fill, cost = _ragged_capacity(diffusion, max(int(c.shape[1]) for c in conditions),
+                                                src_specs is not None or aux_decoder is not None)
         if cap:
-            return _sample_ragged(diffusion, conditions, cap, min_fill, src_specs, aux_decoder)
+            return _sample_ragged(diffusion, conditions, cap, min_fill, src_specs, aux_decoder, cost)
     if aux_decoder is not None:  # the stream path: one source per segment, as the reference's DiffSingerAcoustic.forward computes it
         forward_kwargs = dict(forward_kwargs, src_spec=[aux_decoder(c, infer=True) for c in conditions])
     main = torch.cuda.current_stream(dev)
@@ -186,7 +202,7 @@ def encode_segments(encoder, batches: Sequence[dict], max_frames: int = MAX_RAGG
         return []
     lens = [int(bt['mel2ph'].shape[1]) for bt in batches]
     outs: List = [None] * len(batches)
-    for grp in _ragged_groups(lens, max(max_frames // 128, -(-max(lens) // 128)), 0.5):
+    for grp in _ragged_groups(lens, max(max_frames // 128, -(-max(lens) // 128)), 0.25, 0, 8):  # the encoder's call overhead is small
         t_max = max(lens[i] for i in grp)
         tt_max = max(int(batches[i]['tokens'].shape[1]) for i in grp)
         keys = [k for k, v in batches[grp[0]].items() if torch.is_tensor(v)]

@@ -16,17 +16,22 @@ def _check(groups, lengths, cap, min_fill):
 
 
 def test_whole_network_kernel_grouping_respects_the_cluster_capacity():
-    groups = _ragged_groups(CONFIG1, 33)
+    groups = _ragged_groups(CONFIG1, 33, 0.0, 33, 0)  # every launch costs the same: fewest groups
     _check(groups, CONFIG1, 33, 0.0)
     assert len(groups) == 6  # 30 segments in six launches per evaluation
     assert sum(len(g) * -(-CONFIG1[g[0]] // 128) for g in groups) <= 6 * 33
 
 
-def test_per_layer_grouping_bounds_the_padding():
-    groups = _ragged_groups(CONFIG1, 512, 0.5)
-    _check(groups, CONFIG1, 512, 0.5)
+def test_per_layer_grouping_trades_padding_against_call_overhead():
+    groups = _ragged_groups(CONFIG1, 512, 0.25, 0, 62)  # a sampler call costs as much as 62 tiles of work
+    _check(groups, CONFIG1, 512, 0.25)
+    assert len(groups) == 2
     padded = sum(len(g) * CONFIG1[g[0]] for g in groups)
-    assert padded < 1.35 * sum(CONFIG1), padded
+    assert padded < 1.5 * sum(CONFIG1), padded
+    cheap = _ragged_groups(CONFIG1, 512, 0.25, 0, 8)     # cheap calls: more groups, less padding
+    _check(cheap, CONFIG1, 512, 0.25)
+    assert len(cheap) > len(groups)
+    assert sum(len(g) * CONFIG1[g[0]] for g in cheap) < padded
 
 
 def test_degenerate_inputs():
