@@ -599,7 +599,12 @@ def run_native(args, rank, world, local_rank, emit):
                 "d2h_bytes_per_step": out_host[0].numel() * 4, "overlap": "double-buffered on a copy stream"},
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "roofline": {"bound": "tensor", "achieved": achieved, "peak": pk["bf16"], "unit": "TFLOP/s", "frac": achieved / pk["bf16"],
+        # the kernel is timed over ~2000 back-to-back launches (a long step: the chip sits at its power-capped clock), so the
+        # SUSTAINED cuBLAS figure of MEASURED_PEAKS.json is the peak that applies; the burst figure is reported beside it
+        "roofline": {"bound": "tensor", "achieved": achieved, "peak": pk["bf16_sustained"], "unit": "TFLOP/s",
+                     "frac": achieved / pk["bf16_sustained"],
+                     "peak_kind": "sustained (kernel timed inside a long run of back-to-back launches)",
+                     "burst_peak": pk["bf16"], "frac_of_burst": achieved / pk["bf16"],
                      "frac_of_sustained": achieved / pk["bf16_sustained"],
                      "traffic": measured_traffic(LAYER_KERNELS.get(mode, "")), "traffic_source": "profiles/r02_layer_grp_kernel.txt (ncu --set full)",
                      "kernel": LAYER_KERNELS.get(mode, f"layer mode {mode}"), "kernel_ms": layer_ms, "kernel_launches_timed": layer_n,
